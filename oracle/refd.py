@@ -1,0 +1,226 @@
+"""oracle/refd.py -- TEST INFRASTRUCTURE: ctypes bindings for the oracle.
+
+`Ref` wraps oracle/_ref/libref_driver.so (oracle/ref_driver.c, a plain-pointer driver over the
+unmodified reference CHOLMOD in oracle/_ref/libcholmod_ref.so); `port_factor` / `port_solve`
+wrap the plain-C restatement oracle/super_numeric_port.c (oracle/_ref/libsnport.so).
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_REF = os.path.join(_HERE, "_ref")
+
+CHOLMOD_NATURAL, CHOLMOD_GIVEN, CHOLMOD_AMD, CHOLMOD_METIS, CHOLMOD_NESDIS = 0, 1, 2, 3, 4
+CHOLMOD_SIMPLICIAL, CHOLMOD_AUTO, CHOLMOD_SUPERNODAL = 0, 1, 2
+CHOLMOD_OK, CHOLMOD_NOT_POSDEF = 0, 1
+
+
+def have_ref():
+    return os.path.exists(os.path.join(_REF, "libref_driver.so"))
+
+
+def have_port():
+    return os.path.exists(os.path.join(_REF, "libsnport.so"))
+
+
+_lib = None
+
+
+def _driver():
+    global _lib
+    if _lib is None:
+        lib = C.CDLL(os.path.join(_REF, "libref_driver.so"))
+        lib.refd_open.restype = C.c_void_p
+        lib.refd_open.argtypes = [C.c_int]
+        lib.refd_close.argtypes = [C.c_void_p]
+        lib.refd_set_matrix.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        lib.refd_read_matrix.argtypes = [C.c_void_p, C.c_char_p]
+        lib.refd_analyze.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        lib.refd_seam.argtypes = [C.c_void_p]
+        lib.refd_super_numeric.argtypes = [C.c_void_p, C.c_double]
+        lib.refd_factorize.argtypes = [C.c_void_p, C.c_double]
+        lib.refd_numeric_Lx.restype = C.c_void_p
+        lib.refd_numeric_Lx.argtypes = [C.c_void_p, C.c_int]
+        lib.refd_set_minor.argtypes = [C.c_void_p, C.c_int64]
+        lib.refd_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        lib.refd_resid.restype = C.c_double
+        lib.refd_resid.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.refd_get_int.restype = C.c_int64
+        lib.refd_get_int.argtypes = [C.c_void_p, C.c_char_p]
+        lib.refd_get_double.restype = C.c_double
+        lib.refd_get_double.argtypes = [C.c_void_p, C.c_char_p]
+        lib.refd_get_ptr.restype = C.c_void_p
+        lib.refd_get_ptr.argtypes = [C.c_void_p, C.c_char_p]
+        _lib = lib
+    return _lib
+
+
+def _view(ptr, count, dtype):
+    if count == 0 or not ptr:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_char * (count * np.dtype(dtype).itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype, count=count)
+
+
+class Ref:
+    """One reference CHOLMOD session (cholmod_common + A + symbolic/numeric L)."""
+
+    def __init__(self, nthreads=0):
+        self.lib = _driver()
+        self.h = self.lib.refd_open(int(nthreads))
+        self.single = False
+
+    def close(self):
+        if self.h:
+            self.lib.refd_close(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def geti(self, name):
+        return int(self.lib.refd_get_int(self.h, name.encode()))
+
+    def getd(self, name):
+        return float(self.lib.refd_get_double(self.h, name.encode()))
+
+    def _ptr(self, name):
+        return self.lib.refd_get_ptr(self.h, name.encode())
+
+    def set_matrix(self, n, Ap, Ai, Ax, stype=-1, single=False):
+        Ap = np.ascontiguousarray(Ap, dtype=np.int64)
+        Ai = np.ascontiguousarray(Ai, dtype=np.int64)
+        Ax = np.ascontiguousarray(Ax, dtype=np.float64)
+        self.single = bool(single)
+        rc = self.lib.refd_set_matrix(self.h, n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, stype, int(single))
+        if rc:
+            raise RuntimeError("refd_set_matrix failed")
+
+    def read_matrix(self, path):
+        rc = self.lib.refd_read_matrix(self.h, path.encode())
+        if rc:
+            raise RuntimeError("refd_read_matrix failed: %d" % rc)
+
+    def matrix(self):
+        n, nz = self.geti("n"), self.geti("nnzA")
+        xd = np.float32 if self.single else np.float64
+        return (n, _view(self._ptr("Ap"), n + 1, np.int64).copy(), _view(self._ptr("Ai"), nz, np.int64).copy(),
+                _view(self._ptr("Ax"), nz, xd).copy(), self.geti("stypeA"))
+
+    def analyze(self, ordering=CHOLMOD_AMD, supernodal=CHOLMOD_SUPERNODAL):
+        rc = self.lib.refd_analyze(self.h, ordering, supernodal)
+        if rc < 0:
+            raise RuntimeError("refd_analyze failed: %d" % rc)
+        return rc
+
+    def symbolic(self):
+        """The supernodal symbolic factor as numpy copies (what the numeric seam reads)."""
+        n, ns, ss = self.geti("n"), self.geti("nsuper"), self.geti("ssize")
+        return dict(
+            n=n, nsuper=ns, ssize=ss, xsize=self.geti("xsize"), maxcsize=self.geti("maxcsize"),
+            maxesize=self.geti("maxesize"), fl=self.getd("fl"), lnz=self.getd("lnz"),
+            Perm=_view(self._ptr("Perm"), n, np.int64).copy(),
+            super=_view(self._ptr("super"), ns + 1, np.int64).copy(),
+            pi=_view(self._ptr("pi"), ns + 1, np.int64).copy(),
+            px=_view(self._ptr("px"), ns + 1, np.int64).copy(),
+            s=_view(self._ptr("s"), ss, np.int64).copy())
+
+    def seam(self):
+        """S = tril(P A P') in CSC, as cholmod_factorize_p hands it to cholmod_super_numeric."""
+        rc = self.lib.refd_seam(self.h)
+        if rc:
+            raise RuntimeError("refd_seam failed")
+        n, nz = self.geti("n"), self.geti("nnzS")
+        xd = np.float32 if self.single else np.float64
+        return (_view(self._ptr("Sp"), n + 1, np.int64).copy(), _view(self._ptr("Si"), nz, np.int64).copy(),
+                _view(self._ptr("Sx"), nz, xd).copy())
+
+    def super_numeric(self, beta=0.0):
+        """Reference CPU numeric phase at the seam; returns Common->status."""
+        return int(self.lib.refd_super_numeric(self.h, float(beta)))
+
+    def factorize(self, beta=0.0):
+        """Reference cholmod_l_factorize_p (permute + numeric); returns Common->status."""
+        return int(self.lib.refd_factorize(self.h, float(beta)))
+
+    def Lx(self):
+        xd = np.float32 if self.geti("dtype") == 4 else np.float64
+        return _view(self._ptr("Lx"), self.geti("xsize"), xd)
+
+    def numeric_Lx(self):
+        """Host L->x (allocated like cholmod_super_numeric.c:219-231 if L is still symbolic)."""
+        p = self.lib.refd_numeric_Lx(self.h, int(self.single))
+        if not p:
+            raise RuntimeError("refd_numeric_Lx failed")
+        return _view(p, self.geti("xsize"), np.float32 if self.single else np.float64)
+
+    def set_minor(self, minor):
+        self.lib.refd_set_minor(self.h, int(minor))
+
+    def solve(self, b):
+        b = np.asfortranarray(b, dtype=np.float64)
+        n = self.geti("n")
+        nrhs = 1 if b.ndim == 1 else b.shape[1]
+        x = np.zeros_like(b, order="F")
+        rc = self.lib.refd_solve(self.h, b.ctypes.data, x.ctypes.data, nrhs)
+        if rc:
+            raise RuntimeError("refd_solve failed: %d" % rc)
+        assert x.shape[0] == n
+        return x
+
+    def resid(self, x, b):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        return float(self.lib.refd_resid(self.h, x.ctypes.data, b.ctypes.data))
+
+
+_port = None
+
+
+def _portlib():
+    global _port
+    if _port is None:
+        lib = C.CDLL(os.path.join(_REF, "libsnport.so"))
+        for f in (lib.sn_port_d, lib.sn_port_s):
+            f.restype = C.c_int
+            f.argtypes = [C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
+        lib.sn_port_solve_d.argtypes = [C.c_int64] + [C.c_void_p] * 6
+        _port = lib
+    return _port
+
+
+def port_factor(sym, Sp, Si, Sx, beta=0.0, quick_return=False, Snz=None):
+    """Run the plain-C restatement.  Returns (status, minor, Lx)."""
+    lib = _portlib()
+    single = (np.asarray(Sx).dtype == np.float32)
+    xd = np.float32 if single else np.float64
+    Sp = np.ascontiguousarray(Sp, dtype=np.int64)
+    Si = np.ascontiguousarray(Si, dtype=np.int64)
+    Sx = np.ascontiguousarray(Sx, dtype=xd)
+    Lx = np.full(sym["xsize"], np.nan, dtype=xd)
+    minor = C.c_int64(-1)
+    sup, pi, px, s = (np.ascontiguousarray(sym[k], dtype=np.int64) for k in ("super", "pi", "px", "s"))
+    fn = lib.sn_port_s if single else lib.sn_port_d
+    nzp = None if Snz is None else np.ascontiguousarray(Snz, dtype=np.int64).ctypes.data
+    st = fn(sym["n"], sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
+            sym["xsize"], Sp.ctypes.data, Si.ctypes.data, nzp, Sx.ctypes.data, float(beta), int(quick_return),
+            Lx.ctypes.data, C.byref(minor))
+    return int(st), int(minor.value), Lx
+
+
+def port_solve(sym, Lx, b_perm):
+    """Solve L L' x = b in the permuted ordering with the plain-C restatement."""
+    lib = _portlib()
+    sup, pi, px, s = (np.ascontiguousarray(sym[k], dtype=np.int64) for k in ("super", "pi", "px", "s"))
+    Lx = np.ascontiguousarray(Lx, dtype=np.float64)
+    x = np.array(b_perm, dtype=np.float64, copy=True)
+    lib.sn_port_solve_d(sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
+                        Lx.ctypes.data, x.ctypes.data)
+    return x
