@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""bench.py -- cholmod_factorize (supernodal numeric phase) FP64 GFLOP/s on a synthetic 3-D Laplacian.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one numeric factorization of the workload matrix (analysis is done once, untimed, by the
+reference's own host code as BASELINE.json's north_star prescribes).  Prints ONE JSON line:
+
+  value      Common->fl / t with A and L resident in HBM (t = device time from CUDA events on the
+             library's stream: zero + scatter A + every update/potrf/trsm launch), aggregated over ranks.
+  e2e        the same metric through the host-buffer C-ABI call b200_super_numeric_d: H2D of A, the
+             factorization, D2H of all of L->x, timed on the host clock around the call.
+  roofline   the dominant kernel (128x128 DMMA update) against the FP64 tensor peak measured live on
+             this device with a register-resident DMMA loop (MEASURED_PEAKS.json has no FP64 figure).
+  cpu_baseline  the reference CPU supernodal path (oracle/_ref, all host cores) on a bounded sample.
+
+`--impl reference` times the reference's CPU cholmod_l_factorize on the bounded sample instead.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cholmod_factorize_fp64_gflops"
+UNIT = "GFLOP/s"
+WORKLOADS = {
+    # name: (generator, size, CHOLMOD ordering code, description)
+    "cfg2": ("lap3d7", 100, 3, "3-D 7-point Laplacian 100^3 (n=1M), double, METIS"),
+    "cfg1": ("lap2d5", 100, 2, "2-D 5-point Laplacian 100x100 (n=10k), double, AMD"),
+    "cfg5": ("lap2d9", 2000, 3, "2-D 9-point Laplacian 2000x2000 (n=4M), double, METIS"),
+    "cfg3": ("el27", 80, 3, "3-D 27-point 3-dof elasticity-style 80^3 (n=1.5M), double, METIS"),
+    "lap3d7_64": ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262k), double, METIS"),
+    "lap3d7_40": ("lap3d7", 40, 3, "3-D 7-point Laplacian 40^3 (n=64k), double, METIS"),
+}
+CPU_SAMPLE = ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262144), METIS: same generator and ordering as the "
+              "workload, reduced so one CPU factorization takes ~10 s")
+
+
+def analyze(kind, size, ordering, nthreads=0):
+    """Reference host analysis (ordering, etree, supernodes) + the seam matrix."""
+    from oracle import refd
+    from suitesparse_b200 import matrices
+    gen = getattr(matrices, kind)
+    n, Ap, Ai, Ax = gen(size)
+    ref = refd.Ref(nthreads)
+    ref.set_matrix(n, Ap, Ai, Ax, -1)
+    t = time.time()
+    ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
+    t_an = time.time() - t
+    return ref, t_an
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_reference_steps(steps, warmup, nthreads):
+    """Reference CPU cholmod_l_factorize on the bounded sample; returns (GFLOP/s, ms/step, cores, fl)."""
+    kind, size, ordering, _ = CPU_SAMPLE
+    ref, _ = analyze(kind, size, ordering, nthreads)
+    fl = ref.getd("fl")
+    for _ in range(warmup):
+        ref.factorize(0.0)
+    ts = []
+    for _ in range(steps):
+        st = ref.factorize(0.0)
+        assert st == 0, st
+        ts.append(ref.getd("t_factor"))
+    cores = ref.geti("nthreads_max")
+    t = float(np.sum(ts))
+    ref.close()
+    return fl * steps / t / 1e9, 1e3 * t / steps, cores, fl
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(ncores))
+    gf, ms, cores, fl = cpu_reference_steps(args.steps, args.warmup, ncores)
+    out = {
+        "impl": "reference", "metric": METRIC, "value": gf, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][3], "sample": CPU_SAMPLE[3]},
+        "cpu_baseline": {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": CPU_SAMPLE[3]},
+        "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from suitesparse_b200 import b200
+    if not b200.probe(local):
+        raise SystemExit("bench.py: no sm_100 device %d visible (there is no CPU fallback)" % local)
+
+    kind, size, ordering, desc = WORKLOADS[args.workload]
+    ref, t_an = analyze(kind, size, ordering)
+    sym = ref.symbolic()
+    Sp, Si, Sx = ref.seam()
+    fl = sym["fl"]
+    t0 = time.time()
+    F = b200.Factor(sym, device=local)
+    t_plan = time.time() - t0
+    Lx_host = np.empty(sym["xsize"], dtype=np.float64)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident metric: A in HBM -> L in HBM ---------------------------------------------
+    F.upload_matrix(Sp, Si, Sx)
+    for _ in range(args.warmup):
+        st = F.factor_device()
+        assert st == b200.OK, st
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    wall0 = time.time()
+    ms_dev = 0.0
+    launches = 0
+    for _ in range(args.steps):
+        st = F.factor_device()
+        assert st == b200.OK, st
+        ms_dev += F.getd("ms_factor")
+        launches += F.geti("kernel_launches")
+    barrier()
+    wall = time.time() - wall0
+    clocks = sampler.stop()
+    if world > 1:
+        tt = torch.tensor([ms_dev], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_dev = float(tt.item())
+    ms_step = ms_dev / args.steps
+    value = world * fl / (ms_step * 1e-3) / 1e9
+
+    # ---- end to end through the host-buffer C-ABI call ----------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(2):                      # first call pins the caller's L->x (once per factor object)
+            F.super_numeric(Sp, Si, Sx, Lx=Lx_host)
+        barrier()
+        t0 = time.time()
+        for _ in range(args.steps):
+            st, _ = F.super_numeric(Sp, Si, Sx, Lx=Lx_host)
+            assert st == b200.OK
+        barrier()
+        t_e2e = (time.time() - t0) / args.steps
+        if world > 1:
+            tt = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t_e2e = float(tt.item())
+        e2e = {"value": world * fl / t_e2e / 1e9, "unit": UNIT, "ms_per_step": 1e3 * t_e2e,
+               "h2d_bytes_per_step": int(Sp.nbytes + Si.nbytes + Sx.nbytes),
+               "d2h_bytes_per_step": int(Lx_host.nbytes),
+               "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h")}
+
+    if rank != 0:
+        F.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel, from one profiled (untimed) factorization --------------------
+    peak = b200.dmma_peak_tflops(local, 20000)
+    F.seti("profile", 1)
+    F.factor_device()
+    F.seti("profile", 0)
+    kinds = {}
+    names = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf", "trsm"]
+    for k, nm in enumerate(names):
+        kinds[nm] = {"ms": F.getd("ms_kind%d" % k), "launches": F.geti("launches_kind%d" % k),
+                     "gflop": F.getd("flops_kind%d" % k) / 1e9}
+    dom = max(("upd_dmma128", "upd_dmma64"), key=lambda nm: kinds[nm]["ms"])
+    dk = kinds[dom]
+    ach = (dk["gflop"] / 1e3) / (dk["ms"] * 1e-3) if dk["ms"] > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "k_upd_dmma<%s>" % ("128,128,32,64" if dom == "upd_dmma128" else "64,64,32,32"),
+                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak > 0 else None,
+                "traffic": None,
+                "peak_source": "FP64 DMMA peak measured live by b200_dmma_peak_tflops (not in MEASURED_PEAKS.json)",
+                "flops_per_launch": dk["gflop"] * 1e9 / max(1, dk["launches"]),
+                "avg_launch_ms": dk["ms"] / max(1, dk["launches"]), "share_of_step": dk["ms"] / max(1e-9, sum(v["ms"] for v in kinds.values()))}
+    whole = {"achieved_tflops": fl / (ms_step * 1e-3) / 1e12, "frac_of_fp64_peak": fl / (ms_step * 1e-3) / 1e12 / peak if peak > 0 else None,
+             "executed_tflops": F.getd("flops_executed") / (ms_step * 1e-3) / 1e12}
+
+    # ---- CPU baseline: the reference on a bounded sample, rank 0, N = 1 only ----------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        ncores = os.cpu_count() or 1
+        gf, ms, cores, _ = cpu_reference_steps(1, 1, ncores)
+        cpu = {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": CPU_SAMPLE[3],
+               "ms_per_factorization": ms}
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "n": int(sym["n"]), "nsuper": int(sym["nsuper"]), "fl": fl, "lnz": sym["lnz"],
+                   "xsize": int(sym["xsize"]), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
+                   "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * 8 / 1e9),
+                   "parallelism": "replicas" if world > 1 else "1 GPU",
+                   "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
+        "kernels": kinds, "cpu_baseline": cpu,
+    }
+    print(json.dumps(out))
+    F.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

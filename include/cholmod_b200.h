@@ -1,0 +1,148 @@
+/* cholmod_b200.h -- C ABI of the CHOLMOD/B200 module: a B200-native (sm_100a) supernodal numeric
+ * Cholesky for CHOLMOD.  It replaces CHOLMOD/GPU/t_cholmod_gpu.c + cholmod_gpu.c +
+ * cholmod_gpu_kernels.cu and the useGPU branch of CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c
+ * of SuiteSparse 7.8.3 / CHOLMOD 5.3.0.  Paths cited below are relative to the SuiteSparse tree.
+ *
+ * Everything here is plain pointers and sizes: no cholmod.h, no torch, no C++ types.  Indices are
+ * int64 (the reference GPU path is "cholmod_l_" only, t_cholmod_super_numeric_worker.c:174),
+ * values are double (…_d) or float (…_s).  The cholmod_common / cholmod_factor level glue
+ * (cholmod_l_b200_* and the rd_/rs_ worker entry) is the thin C file csrc/cholmod_b200_shim.c;
+ * INTEGRATION.md shows where a maintainer hooks it into the reference tree.
+ *
+ * Status codes are CHOLMOD's (CHOLMOD/Include/cholmod.h:829-840).  There is NO CPU fallback: if the
+ * device or the kernels are unavailable every entry point fails with B200_GPU_PROBLEM.
+ */
+#ifndef CHOLMOD_B200_H
+#define CHOLMOD_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK              0      /* CHOLMOD_OK */
+#define B200_NOT_POSDEF      1      /* CHOLMOD_NOT_POSDEF (a warning: the call itself succeeded) */
+#define B200_OUT_OF_MEMORY (-2)     /* CHOLMOD_OUT_OF_MEMORY */
+#define B200_TOO_LARGE     (-3)     /* CHOLMOD_TOO_LARGE */
+#define B200_INVALID       (-4)     /* CHOLMOD_INVALID */
+#define B200_GPU_PROBLEM   (-5)     /* CHOLMOD_GPU_PROBLEM */
+
+#define B200_DOUBLE 0               /* CHOLMOD_DOUBLE */
+#define B200_SINGLE 4               /* CHOLMOD_SINGLE */
+
+/* Opaque factorization context: device-resident symbolic tables, the launch plan derived from them,
+ * the L->x arena in HBM, streams and events.  One per (analysis, device); it is reused by every
+ * numeric factorization of the same symbolic factor (cholmod_factorize.c:67-70). */
+typedef struct b200_factor b200_factor ;
+
+/* 1 if `device` exists and is an sm_100 part this library can run on, else 0.
+ * Replaces cholmod_l_gpu_probe (CHOLMOD/GPU/cholmod_gpu.c:148-177). */
+int b200_probe (int device) ;
+
+/* Number of visible CUDA devices (0 when there is no driver). */
+int b200_device_count (void) ;
+
+/* Free and total bytes of HBM on `device`.  Replaces cholmod_l_gpu_memorysize (cholmod_gpu.c:63-136).
+ * Returns B200_OK or B200_GPU_PROBLEM. */
+int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes) ;
+
+/* Build the context for one supernodal symbolic factor: L->super [nsuper+1], L->pi [nsuper+1],
+ * L->px [nsuper+1], L->s [pi[nsuper]] exactly as cholmod_super_symbolic2 produced them
+ * (CHOLMOD/Supernodal/cholmod_super_symbolic.c:147-938).  Computes -- on the host, once -- everything
+ * the reference recomputes per factorization and that is purely symbolic: the supernodal etree and its
+ * levels, the list of (descendant, ancestor) update pairs with ndrow1/ndrow2
+ * (t_cholmod_super_numeric_worker.c:686-698, :950-967), their relative maps (:897-903), and the
+ * level-ordered launch plan; then uploads the tables and allocates the L->x arena.
+ * Replaces gpu_init (CHOLMOD/GPU/t_cholmod_gpu.c:84-160) and cholmod_l_gpu_allocate
+ * (cholmod_gpu.c:426-543).  device < 0 builds the host-side plan only (no CUDA call is made; used by
+ * the CPU tests of the planner) -- such a context cannot factorize.
+ * dtype is B200_DOUBLE or B200_SINGLE.  On failure returns NULL and sets *status. */
+b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
+    const int64_t *px, const int64_t *s, int dtype, int device, int *status) ;
+
+/* Release everything.  Replaces cholmod_l_gpu_deallocate / gpu_end (cholmod_gpu.c:187-228, :319-420). */
+void b200_destroy (b200_factor *f) ;
+
+/* Integer property of the context by name: "n", "nsuper", "xsize", "nlevels", "npairs",
+ * "relmap_len", "ntiles", "nlaunches", "device_bytes", "device", "kernel_launches" (kernels launched
+ * by the last factorization), "ngpus".  Returns -1 for an unknown name. */
+int64_t b200_get_int (const b200_factor *f, const char *name) ;
+
+/* Floating-point property by name: "flops_executed" (supernodal flop count of the plan:
+ * sum over pairs of ndcol*ndrow1*(2*ndrow2-ndrow1) plus nscol^3/3 + nscol^2*(nsrow-nscol) per
+ * supernode), "ms_factor" (device time of the last b200_factor_device, CUDA events), "ms_h2d",
+ * "ms_d2h", "ms_scatter", "ms_solve".  Returns -1 for an unknown name. */
+double b200_get_double (const b200_factor *f, const char *name) ;
+
+/* --- the numeric phase, host buffers in and out (the drop-in call) --------------------------------
+ * Same contract as rd_/rs_cholmod_super_numeric_worker (t_cholmod_super_numeric_worker.c:133-145) for
+ * the symmetric case (A->stype < 0, F unused): A = tril (P A P') in CSC (Ap [n+1], Ai, Ax; Anz [n]
+ * non-NULL iff A is unpacked; columns may be unsorted; entries outside the pattern of L are dropped,
+ * :455-468), beta [0] is added to the diagonal (:510-520).  Fills host Lx [xsize] with the supernodal
+ * factor in the reference layout (column-major per supernode, lda = nsrow, :342-348).
+ * Returns B200_OK, or B200_NOT_POSDEF with *minor = the failing column and L zeroed / partially
+ * factorized exactly as :1084-1146 prescribe (quick_return_if_not_posdef as in cholmod_common), or a
+ * negative status on a fatal error.  *minor = n on success (:1269). */
+int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const double *Ax, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor) ;
+int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const float *Ax, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor) ;
+
+/* --- the same phase in three steps, for callers that keep A and L resident in HBM ---------------- */
+
+/* Copy A (host CSC as above, values of the context's dtype) to the device.  The pattern may change from
+ * call to call.  Replaces the per-supernode host scatter + H2D of t_cholmod_gpu.c:669-700. */
+int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax) ;
+
+/* Factorize the device-resident A into the device-resident L: zero + scatter A (:361-520), then level by
+ * level the batched descendant updates (dsyrk/dgemm/assemble, :769-930) and the per-supernode
+ * dpotrf/dtrsm (:1023-1181).  Blocks until the device is done.  Returns status and *minor as above. */
+int b200_factor_device (b200_factor *f, double beta, int quick_return_if_not_posdef, int64_t *minor) ;
+
+/* Copy the device-resident factor to host Lx [xsize] (values of the context's dtype).
+ * Replaces the per-supernode D2H of t_cholmod_gpu.c:1263-1273, :1403-1443. */
+int b200_download_factor (b200_factor *f, void *Lx) ;
+
+/* Device address of the L->x arena (xsize values of the context's dtype), or NULL. */
+void *b200_device_Lx (b200_factor *f) ;
+
+/* Overwrite the device-resident factor with host values (used to solve with a factor computed
+ * elsewhere, and by tests). */
+int b200_upload_factor (b200_factor *f, const void *Lx) ;
+
+/* --- solve with the device-resident factor -------------------------------------------------------
+ * X = L'\(L\B) in the permuted ordering, B and X n-by-nrhs column-major doubles on the host (X may
+ * alias B).  Device counterpart of cholmod_super_lsolve / cholmod_super_ltsolve
+ * (CHOLMOD/Supernodal/t_cholmod_super_solve_worker.c:20-303, :309-586). */
+int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
+
+/* --- diagnostics (the reference's counterparts are the BLAS_TIMER counters and cholmod_gpu_stats,
+ * CHOLMOD/Check/cholmod_check.c:615-674) -------------------------------------------------------- */
+
+/* Set an integer option by name.  "profile" = 1 brackets every kernel launch of the next factorizations
+ * with CUDA events and accumulates device time per kernel kind ("ms_kind0".."ms_kind4" in
+ * b200_get_double; kinds: 0 SIMT update, 1 DMMA 64x64 update, 2 DMMA 128x128 update, 3 POTRF, 4 TRSM;
+ * "flops_kind<k>" are the algorithmic flops of each kind).  Profiling serialises nothing but adds
+ * event overhead: never time a benchmark step with it on. */
+int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
+
+/* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):
+ * "level", "parent", "relmap", "items", "tiles", "potrf", "trsm", "launches" (layouts in
+ * csrc/plan.hpp).  Works on a device < 0 context; used by the CPU tests of the planner. */
+int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, int64_t out_bytes) ;
+
+/* Measured FP64 tensor-pipe (DMMA, mma.sync.m8n8k4.f64) peak of `device` in TFLOP/s from a
+ * register-resident loop of `iters` iterations per warp; < 0 on failure.  This is the roofline
+ * denominator bench.py reports against (MEASURED_PEAKS.json carries no FP64 figure). */
+double b200_dmma_peak_tflops (int device, int iters) ;
+
+/* Library/kernels self-description, e.g. "cholmod_b200 0.1 sm_100a".  Never NULL. */
+const char *b200_version (void) ;
+
+#ifdef __cplusplus
+}
+#endif
+#endif

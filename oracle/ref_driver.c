@@ -42,6 +42,7 @@ void *refd_open (int nthreads_max)
     cholmod_l_start (&h->cm) ;
     h->cm.useGPU = 0 ;
     h->cm.error_handler = quiet_handler ;
+    h->cm.print = 0 ;
     if (nthreads_max > 0) h->cm.nthreads_max = nthreads_max ;
     return h ;
 }
@@ -246,6 +247,16 @@ double refd_resid (void *hv, const double *x, const double *b)
     }
     free (r) ; free (rowsum) ;
     return rn / (an * xn + bn + (n == 0 ? 1 : 0)) ;
+}
+
+int refd_set_int (void *hv, const char *name, int64_t v)
+{
+    refd *h = (refd *) hv ;
+    if (!strcmp (name, "quick_return_if_not_posdef")) { h->cm.quick_return_if_not_posdef = (int) v ; return 0 ; }
+    if (!strcmp (name, "nthreads_max")) { h->cm.nthreads_max = (int) v ; return 0 ; }
+    if (!strcmp (name, "print")) { h->cm.print = (int) v ; return 0 ; }
+    if (!strcmp (name, "try_catch")) { h->cm.try_catch = (int) v ; return 0 ; }
+    return -1 ;
 }
 
 int64_t refd_get_int (void *hv, const char *name)

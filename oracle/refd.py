@@ -48,6 +48,7 @@ def _driver():
         lib.refd_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
         lib.refd_resid.restype = C.c_double
         lib.refd_resid.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.refd_set_int.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
         lib.refd_get_int.restype = C.c_int64
         lib.refd_get_int.argtypes = [C.c_void_p, C.c_char_p]
         lib.refd_get_double.restype = C.c_double
@@ -86,6 +87,10 @@ class Ref:
 
     def geti(self, name):
         return int(self.lib.refd_get_int(self.h, name.encode()))
+
+    def seti(self, name, v):
+        if self.lib.refd_set_int(self.h, name.encode(), int(v)):
+            raise KeyError(name)
 
     def getd(self, name):
         return float(self.lib.refd_get_double(self.h, name.encode()))

@@ -1,0 +1,214 @@
+"""ctypes binding of the CHOLMOD/B200 C ABI (include/cholmod_b200.h).
+
+This is the host-side mirror of the reference's numeric seam: `Factor(sym)` plays the role of the
+GPU-side state the reference hangs on cholmod_common (CHOLMOD/GPU/cholmod_gpu.c), and
+`Factor.super_numeric(Ap, Ai, Ax, beta)` has the contract of `cholmod_super_numeric`
+(CHOLMOD/Supernodal/cholmod_super_numeric.c:100) for a symmetric lower-stored matrix.
+
+There is no CPU fallback: if lib/libcholmod_b200.so is missing, or no sm_100 device is visible,
+everything that computes raises `B200Error`.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+OK, NOT_POSDEF, OUT_OF_MEMORY, TOO_LARGE, INVALID, GPU_PROBLEM = 0, 1, -2, -3, -4, -5
+DOUBLE, SINGLE = 0, 4
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libcholmod_b200.so")
+
+# every symbol include/cholmod_b200.h declares
+SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", "b200_destroy",
+           "b200_get_int", "b200_get_double", "b200_super_numeric_d", "b200_super_numeric_s",
+           "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
+           "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
+           "b200_dmma_peak_tflops"]
+
+
+class B200Error(RuntimeError):
+    def __init__(self, status, what):
+        super().__init__("%s failed with status %d" % (what, status))
+        self.status = status
+
+
+_lib = None
+
+
+def lib():
+    """Load the shared library (raises B200Error if it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200Error(GPU_PROBLEM, "loading %s (run `python -c 'import __graft_entry__ as g; g.build()'`)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, i64, dbl, cint = C.c_void_p, C.c_int64, C.c_double, C.c_int
+    L.b200_probe.argtypes = [cint]; L.b200_probe.restype = cint
+    L.b200_device_count.argtypes = []; L.b200_device_count.restype = cint
+    L.b200_memorysize.argtypes = [cint, vp, vp]; L.b200_memorysize.restype = cint
+    L.b200_create.argtypes = [i64, i64, vp, vp, vp, vp, cint, cint, vp]; L.b200_create.restype = vp
+    L.b200_destroy.argtypes = [vp]; L.b200_destroy.restype = None
+    L.b200_get_int.argtypes = [vp, C.c_char_p]; L.b200_get_int.restype = i64
+    L.b200_get_double.argtypes = [vp, C.c_char_p]; L.b200_get_double.restype = dbl
+    for fn in (L.b200_super_numeric_d, L.b200_super_numeric_s):
+        fn.argtypes = [vp, vp, vp, vp, vp, dbl, cint, vp, vp]; fn.restype = cint
+    L.b200_upload_matrix.argtypes = [vp, vp, vp, vp, vp]; L.b200_upload_matrix.restype = cint
+    L.b200_factor_device.argtypes = [vp, dbl, cint, vp]; L.b200_factor_device.restype = cint
+    L.b200_download_factor.argtypes = [vp, vp]; L.b200_download_factor.restype = cint
+    L.b200_upload_factor.argtypes = [vp, vp]; L.b200_upload_factor.restype = cint
+    L.b200_device_Lx.argtypes = [vp]; L.b200_device_Lx.restype = vp
+    L.b200_solve_d.argtypes = [vp, vp, vp, i64]; L.b200_solve_d.restype = cint
+    L.b200_version.argtypes = []; L.b200_version.restype = C.c_char_p
+    L.b200_set_int.argtypes = [vp, C.c_char_p, i64]; L.b200_set_int.restype = cint
+    L.b200_dmma_peak_tflops.argtypes = [cint, cint]; L.b200_dmma_peak_tflops.restype = dbl
+    L.b200_plan_export.argtypes = [vp, C.c_char_p, vp, i64]; L.b200_plan_export.restype = i64
+    _lib = L
+    return L
+
+
+def device_count():
+    return int(lib().b200_device_count())
+
+
+def probe(device=0):
+    return bool(lib().b200_probe(int(device)))
+
+
+def dmma_peak_tflops(device=0, iters=20000):
+    """Measured FP64 tensor (DMMA) peak of the device in TFLOP/s."""
+    return float(lib().b200_dmma_peak_tflops(int(device), int(iters)))
+
+
+def _i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+class Factor:
+    """Device-resident supernodal factorization context for one symbolic factor.
+
+    `sym` is a dict with n, nsuper, super, pi, px, s (the arrays of cholmod_factor after
+    cholmod_analyze with a supernodal strategy).  device=-1 builds the host-side plan only.
+    """
+
+    def __init__(self, sym, dtype=np.float64, device=0):
+        self.L = lib()
+        self.n, self.nsuper = int(sym["n"]), int(sym["nsuper"])
+        self.dtype = np.dtype(dtype)
+        if self.dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
+            raise ValueError("dtype must be float64 or float32")
+        sup, pi, px, s = _i64(sym["super"]), _i64(sym["pi"]), _i64(sym["px"]), _i64(sym["s"])
+        st = C.c_int(0)
+        self.h = self.L.b200_create(self.n, self.nsuper, sup.ctypes.data, pi.ctypes.data, px.ctypes.data,
+                                    s.ctypes.data, DOUBLE if self.dtype == np.float64 else SINGLE,
+                                    int(device), C.byref(st))
+        if not self.h:
+            raise B200Error(st.value, "b200_create")
+        self.xsize = self.geti("xsize")
+        self.minor = self.n
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def geti(self, name):
+        return int(self.L.b200_get_int(self.h, name.encode()))
+
+    def getd(self, name):
+        return float(self.L.b200_get_double(self.h, name.encode()))
+
+    def seti(self, name, value):
+        st = self.L.b200_set_int(self.h, name.encode(), int(value))
+        if st < 0:
+            raise B200Error(st, "b200_set_int(%s)" % name)
+
+    # -- the drop-in call: host A in, host L->x out ------------------------------------------------
+    def super_numeric(self, Ap, Ai, Ax, beta=0.0, quick_return=False, Lx=None, Anz=None):
+        """Returns (status, Lx); status is OK or NOT_POSDEF (self.minor then holds L->minor)."""
+        Ap, Ai = _i64(Ap), _i64(Ai)
+        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+        if Lx is None:
+            Lx = np.empty(self.xsize, dtype=self.dtype)
+        assert Lx.dtype == self.dtype and Lx.size == self.xsize and Lx.flags.c_contiguous
+        nzp = None if Anz is None else _i64(Anz)
+        minor = C.c_int64(-1)
+        fn = self.L.b200_super_numeric_d if self.dtype == np.float64 else self.L.b200_super_numeric_s
+        st = fn(self.h, Ap.ctypes.data, Ai.ctypes.data, None if nzp is None else nzp.ctypes.data,
+                Ax.ctypes.data, float(beta), int(quick_return), Lx.ctypes.data, C.byref(minor))
+        if st < 0:
+            raise B200Error(st, "b200_super_numeric")
+        self.minor = int(minor.value)
+        return st, Lx
+
+    # -- the same in three steps ---------------------------------------------------------------------
+    def upload_matrix(self, Ap, Ai, Ax, Anz=None):
+        Ap, Ai = _i64(Ap), _i64(Ai)
+        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+        nzp = None if Anz is None else _i64(Anz)
+        st = self.L.b200_upload_matrix(self.h, Ap.ctypes.data, Ai.ctypes.data,
+                                       None if nzp is None else nzp.ctypes.data, Ax.ctypes.data)
+        if st < 0:
+            raise B200Error(st, "b200_upload_matrix")
+
+    def factor_device(self, beta=0.0, quick_return=False):
+        minor = C.c_int64(-1)
+        st = self.L.b200_factor_device(self.h, float(beta), int(quick_return), C.byref(minor))
+        if st < 0:
+            raise B200Error(st, "b200_factor_device")
+        self.minor = int(minor.value)
+        return st
+
+    def download_factor(self, Lx=None):
+        if Lx is None:
+            Lx = np.empty(self.xsize, dtype=self.dtype)
+        st = self.L.b200_download_factor(self.h, Lx.ctypes.data)
+        if st < 0:
+            raise B200Error(st, "b200_download_factor")
+        return Lx
+
+    def upload_factor(self, Lx):
+        Lx = np.ascontiguousarray(Lx, dtype=self.dtype)
+        st = self.L.b200_upload_factor(self.h, Lx.ctypes.data)
+        if st < 0:
+            raise B200Error(st, "b200_upload_factor")
+
+    def device_Lx(self):
+        return self.L.b200_device_Lx(self.h)
+
+    def solve(self, B):
+        """X = L'\\(L\\B) in the permuted ordering; B is n or n-by-nrhs."""
+        B = np.asfortranarray(B, dtype=np.float64)
+        nrhs = 1 if B.ndim == 1 else B.shape[1]
+        X = np.empty_like(B, order="F")
+        st = self.L.b200_solve_d(self.h, B.ctypes.data, X.ctypes.data, nrhs)
+        if st < 0:
+            raise B200Error(st, "b200_solve_d")
+        return X
+
+    # -- plan introspection (tests of the host planner) ------------------------------------------------
+    def plan_table(self, which, dtype):
+        nbytes = int(self.L.b200_plan_export(self.h, which.encode(), None, 0))
+        if nbytes < 0:
+            raise KeyError(which)
+        out = np.zeros(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+        if nbytes:
+            self.L.b200_plan_export(self.h, which.encode(), out.ctypes.data, nbytes)
+        return out
+
+
+ITEM_DT = np.dtype([("a_off", "<i8"), ("c_off", "<i8"), ("map_off", "<i8"), ("lda", "<i4"), ("ldc", "<i4"),
+                    ("M", "<i4"), ("N", "<i4"), ("K", "<i4"), ("pad", "<i4")])
+TILE_DT = np.dtype([("item", "<i4"), ("ti", "<u2"), ("tj", "<u2"), ("k0", "<i4"), ("k1", "<i4")])
+POTRF_DT = np.dtype([("off", "<i8"), ("col", "<i8"), ("lda", "<i4"), ("jb", "<i4")])
+TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("nrows", "<i4"),
+                    ("pad", "<i4")])
+LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("pad", "<i4")])
+K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF, K_TRSM = 0, 1, 2, 3, 4
+TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 128)}

@@ -1,0 +1,658 @@
+// b200_api.cu -- the C ABI of include/cholmod_b200.h: context, device memory, and the executor that
+// walks the launch plan on one CUDA stream.  No CPU fallback anywhere: without a usable device every
+// numeric entry point returns B200_GPU_PROBLEM.
+#include "../../include/cholmod_b200.h"
+#include "plan.hpp"
+#include "kernels.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace b200 ;
+
+namespace {
+
+template <typename T> struct DevBuf
+{
+    T *p = nullptr ; size_t n = 0 ;
+    cudaError_t alloc (size_t count)
+    {
+        release () ;
+        n = count ;
+        if (count == 0) return cudaSuccess ;
+        cudaError_t e = cudaMalloc ((void **) &p, count * sizeof (T)) ;
+        if (e != cudaSuccess) { p = nullptr ; n = 0 ; }
+        return e ;
+    }
+    cudaError_t upload (const std::vector<T> &v, cudaStream_t st)
+    {
+        cudaError_t e = alloc (v.size ()) ;
+        if (e != cudaSuccess || v.empty ()) return e ;
+        return cudaMemcpyAsync (p, v.data (), v.size () * sizeof (T), cudaMemcpyHostToDevice, st) ;
+    }
+    void release () { if (p) cudaFree (p) ; p = nullptr ; n = 0 ; }
+    size_t bytes () const { return n * sizeof (T) ; }
+} ;
+
+}   // namespace
+
+struct b200_factor
+{
+    Plan plan ;
+    int dtype = B200_DOUBLE ;
+    int device = -1 ;
+    size_t esize = 8 ;
+    std::vector<int64_t> h_super, h_pi, h_px ;
+
+    cudaStream_t stream = nullptr ;
+    cudaEvent_t ev [8] = {} ;
+    // symbolic tables
+    DevBuf<int64_t> d_super, d_pi, d_px ;
+    DevBuf<int32_t> d_Ls, d_supermap, d_relmap, d_level_list ;
+    DevBuf<UpdItem> d_items ;
+    DevBuf<UpdTile> d_tiles ;
+    DevBuf<PotrfBlk> d_potrf ;
+    DevBuf<TrsmTile> d_trsm ;
+    // numeric
+    DevBuf<unsigned char> d_Lx ;
+    DevBuf<int64_t> d_Ap, d_Ai, d_Anz ;
+    DevBuf<unsigned char> d_Ax ;
+    DevBuf<unsigned long long> d_minor ;
+    DevBuf<double> d_X ;
+    bool have_A = false, A_unpacked = false ;
+    int64_t A_nz = 0 ;
+    // host-registered output buffer (pinned once, reused by later factorizations)
+    void *reg_ptr = nullptr ; size_t reg_bytes = 0 ;
+
+    int64_t kernel_launches = 0 ;
+    int profile = 0 ;                       // 1: bracket every launch with events (diagnostic runs only)
+    std::vector<cudaEvent_t> prof_ev ;
+    double ms_kind [5] = {0, 0, 0, 0, 0} ;
+    int64_t launches_kind [5] = {0, 0, 0, 0, 0} ;
+    float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
+    size_t device_bytes = 0 ;
+} ;
+
+namespace {
+
+bool cuda_ok (cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess) return true ;
+    fprintf (stderr, "cholmod_b200: %s: %s\n", what, cudaGetErrorString (e)) ;
+    return false ;
+}
+
+#define CK(call, what) do { if (!cuda_ok ((call), what)) return B200_GPU_PROBLEM ; } while (0)
+
+int set_device (const b200_factor *f)
+{
+    if (!f || f->device < 0) return B200_GPU_PROBLEM ;
+    CK (cudaSetDevice (f->device), "cudaSetDevice") ;
+    return B200_OK ;
+}
+
+bool g_attr_done [64] = {} ;
+
+int kernel_attrs (int device)
+{
+    if (device < 64 && g_attr_done [device]) return B200_OK ;
+    CK (cudaFuncSetAttribute (k_upd_dmma<128, 128, 32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) dmma_smem_bytes<128, 128> ()), "attr d128") ;
+    CK (cudaFuncSetAttribute (k_upd_dmma<64, 64, 32, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) dmma_smem_bytes<64, 64> ()), "attr d64") ;
+    CK (cudaFuncSetAttribute (k_solve_fwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
+    CK (cudaFuncSetAttribute (k_solve_bwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
+    CK (cudaFuncSetAttribute (k_solve_fwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
+    CK (cudaFuncSetAttribute (k_solve_bwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
+    if (device < 64) g_attr_done [device] = true ;
+    return B200_OK ;
+}
+
+// run the launch list [first, last) of a plan on the context's stream
+template <typename T>
+int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const UpdTile *tiles,
+    const PotrfBlk *potrf, const TrsmTile *trsm, const int32_t *relmap)
+{
+    T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
+    cudaStream_t st = f->stream ;
+    size_t nev = 0 ;
+    if (f->profile)
+    {
+        while (f->prof_ev.size () < 2 * P.launches.size ())
+        {
+            cudaEvent_t e ;
+            CK (cudaEventCreate (&e), "profile event") ;
+            f->prof_ev.push_back (e) ;
+        }
+    }
+    for (const Launch &L : P.launches)
+    {
+        if (L.count <= 0) continue ;
+        if (f->profile) cudaEventRecord (f->prof_ev [nev++], st) ;
+        switch (L.kind)
+        {
+            case K_UPD_SIMT:
+            {
+                int64_t nthreads = (int64_t) L.count * 32 ;
+                unsigned grid = (unsigned) ((nthreads + 255) / 256) ;
+                k_upd_simt<T><<<grid, 256, 0, st>>> (tiles + L.first, L.count, items, relmap, Lx) ;
+                break ;
+            }
+            case K_UPD_D64:
+                if (sizeof (T) != 8) return B200_INVALID ;
+                k_upd_dmma<64, 64, 32, 32><<<(unsigned) L.count, 128, dmma_smem_bytes<64, 64> (), st>>>
+                    (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                break ;
+            case K_UPD_D128:
+                if (sizeof (T) != 8) return B200_INVALID ;
+                k_upd_dmma<128, 128, 32, 64><<<(unsigned) L.count, 256, dmma_smem_bytes<128, 128> (), st>>>
+                    (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                break ;
+            case K_POTRF:
+                k_potrf<T><<<(unsigned) L.count, 256, 0, st>>> (potrf + L.first, Lx, f->d_minor.p) ;
+                break ;
+            case K_TRSM:
+                k_trsm<T><<<(unsigned) L.count, TRSM_ROWS, 0, st>>> (trsm + L.first, Lx) ;
+                break ;
+            default:
+                return B200_INVALID ;
+        }
+        f->kernel_launches++ ;
+        if (f->profile) cudaEventRecord (f->prof_ev [nev++], st) ;
+    }
+    CK (cudaGetLastError (), "kernel launch") ;
+    if (f->profile)
+    {
+        CK (cudaStreamSynchronize (st), "profile sync") ;
+        size_t e = 0 ;
+        for (const Launch &L : P.launches)
+        {
+            if (L.count <= 0) continue ;
+            float ms = 0 ;
+            cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
+            e += 2 ;
+            f->ms_kind [L.kind] += ms ;
+            f->launches_kind [L.kind]++ ;
+        }
+    }
+    return B200_OK ;
+}
+
+template <typename T>
+int scatter_A (b200_factor *f, int64_t kfirst, int64_t klast, double beta)
+{
+    if (klast <= kfirst) return B200_OK ;
+    unsigned grid = (unsigned) ((klast - kfirst + 255) / 256) ;
+    k_scatter_A<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
+        f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_supermap.p,
+        f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (T) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
+    f->kernel_launches++ ;
+    CK (cudaGetLastError (), "k_scatter_A") ;
+    return B200_OK ;
+}
+
+// SNW:1084-1146 on the device: the matrix is not positive definite at global column `minor`.  Zero
+// supernode s and everything after it; unless info == 1 or quick return, rebuild supernode s from A and
+// its descendants and factorize only its first info-1 columns, leaving its other columns zero.
+template <typename T>
+int repair_not_posdef (b200_factor *f, int64_t minor, double beta, int quick)
+{
+    const Plan &P = f->plan ;
+    const int64_t s = P.supermap [minor] ;
+    const int64_t k1 = f->h_super [s], nscol = f->h_super [s+1] - k1 ;
+    const int64_t psx = f->h_px [s], nsrow = f->h_pi [s+1] - f->h_pi [s] ;
+    const int64_t info = minor - k1 + 1 ;
+    T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
+    CK (cudaMemsetAsync (Lx + psx, 0, (size_t) (P.xsize - psx) * sizeof (T), f->stream), "memset tail") ;
+    if (info == 1 || quick) return B200_OK ;
+    const int64_t nscol_new = info - 1 ;
+    Plan R ;
+    int st = build_repair_plan (P, f->h_super.data (), f->h_pi.data (), f->h_px.data (), s, nscol_new,
+        f->dtype == B200_DOUBLE, R) ;
+    if (st) return st ;
+    DevBuf<UpdItem> items ; DevBuf<UpdTile> tiles ; DevBuf<PotrfBlk> potrf ; DevBuf<TrsmTile> trsm ;
+    bool ok = items.upload (R.items, f->stream) == cudaSuccess && tiles.upload (R.tiles, f->stream) == cudaSuccess
+        && potrf.upload (R.potrf, f->stream) == cudaSuccess && trsm.upload (R.trsm, f->stream) == cudaSuccess ;
+    if (ok)
+    {
+        st = scatter_A<T> (f, k1, k1 + nscol, beta) ;
+        if (!st) st = run_launches<T> (f, R, items.p, tiles.p, potrf.p, trsm.p, f->d_relmap.p) ;
+        if (!st && cudaMemsetAsync (Lx + psx + nsrow * nscol_new, 0, (size_t) (nsrow * (nscol - nscol_new)) * sizeof (T),
+            f->stream) != cudaSuccess) st = B200_GPU_PROBLEM ;
+        if (cudaStreamSynchronize (f->stream) != cudaSuccess) st = B200_GPU_PROBLEM ;
+    }
+    else st = B200_OUT_OF_MEMORY ;
+    items.release () ; tiles.release () ; potrf.release () ; trsm.release () ;
+    return st ;
+}
+
+}   // namespace
+
+// -------------------------------------------------------------------------------------------------
+// C ABI
+// -------------------------------------------------------------------------------------------------
+
+extern "C" {
+
+double b200_dmma_peak_tflops (int device, int iters)
+{
+    if (!b200_probe (device) || iters <= 0) return -1 ;
+    if (cudaSetDevice (device) != cudaSuccess) return -1 ;
+    cudaDeviceProp prop ;
+    if (cudaGetDeviceProperties (&prop, device) != cudaSuccess) return -1 ;
+    double *out = nullptr ;
+    const int grid = prop.multiProcessorCount * 4, block = 256 ;
+    if (cudaMalloc ((void **) &out, (size_t) grid * block * sizeof (double)) != cudaSuccess) return -1 ;
+    cudaEvent_t e0, e1 ;
+    cudaEventCreate (&e0) ; cudaEventCreate (&e1) ;
+    k_dmma_peak<<<grid, block>>> (out, iters / 4 + 1) ;          // warm-up
+    cudaEventRecord (e0) ;
+    k_dmma_peak<<<grid, block>>> (out, iters) ;
+    cudaEventRecord (e1) ;
+    double tf = -1 ;
+    if (cudaEventSynchronize (e1) == cudaSuccess)
+    {
+        float ms = 0 ;
+        cudaEventElapsedTime (&ms, e0, e1) ;
+        // 16 m8n8k4 DMMAs (512 flops each) per warp and iteration
+        double flops = (double) grid * (block / 32) * (double) iters * 16.0 * 512.0 ;
+        tf = flops / (ms * 1e-3) / 1e12 ;
+    }
+    cudaEventDestroy (e0) ; cudaEventDestroy (e1) ; cudaFree (out) ;
+    cudaGetLastError () ;
+    return tf ;
+}
+
+const char *b200_version (void) { return "cholmod_b200 0.1 sm_100a" ; }
+
+int b200_device_count (void)
+{
+    int n = 0 ;
+    if (cudaGetDeviceCount (&n) != cudaSuccess) { cudaGetLastError () ; return 0 ; }
+    return n ;
+}
+
+int b200_probe (int device)
+{
+    int n = b200_device_count () ;
+    if (device < 0 || device >= n) return 0 ;
+    cudaDeviceProp prop ;
+    if (cudaGetDeviceProperties (&prop, device) != cudaSuccess) { cudaGetLastError () ; return 0 ; }
+    return (prop.major == 10) ? 1 : 0 ;
+}
+
+int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes)
+{
+    if (!b200_probe (device)) return B200_GPU_PROBLEM ;
+    CK (cudaSetDevice (device), "cudaSetDevice") ;
+    size_t fr = 0, tot = 0 ;
+    CK (cudaMemGetInfo (&fr, &tot), "cudaMemGetInfo") ;
+    if (free_bytes) *free_bytes = fr ;
+    if (total_bytes) *total_bytes = tot ;
+    return B200_OK ;
+}
+
+static int create_device_side (b200_factor *f, const int64_t *Ls)
+{
+    const Plan &P = f->plan ;
+    if (!b200_probe (f->device)) return B200_GPU_PROBLEM ;
+    CK (cudaSetDevice (f->device), "cudaSetDevice") ;
+    int st = kernel_attrs (f->device) ;
+    if (st != B200_OK) return st ;
+    CK (cudaStreamCreateWithFlags (&f->stream, cudaStreamNonBlocking), "stream") ;
+    for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
+    std::vector<int32_t> Ls32 ((size_t) P.ssize) ;
+    for (int64_t k = 0 ; k < P.ssize ; k++) Ls32 [k] = (int32_t) Ls [k] ;
+    cudaStream_t s = f->stream ;
+    bool ok = true ;
+    ok = ok && f->d_super.upload (f->h_super, s) == cudaSuccess ;
+    ok = ok && f->d_pi.upload (f->h_pi, s) == cudaSuccess ;
+    ok = ok && f->d_px.upload (f->h_px, s) == cudaSuccess ;
+    ok = ok && f->d_Ls.upload (Ls32, s) == cudaSuccess ;
+    ok = ok && f->d_supermap.upload (P.supermap, s) == cudaSuccess ;
+    ok = ok && f->d_relmap.upload (P.relmap, s) == cudaSuccess ;
+    ok = ok && f->d_level_list.upload (P.level_list, s) == cudaSuccess ;
+    ok = ok && f->d_items.upload (P.items, s) == cudaSuccess ;
+    ok = ok && f->d_tiles.upload (P.tiles, s) == cudaSuccess ;
+    ok = ok && f->d_potrf.upload (P.potrf, s) == cudaSuccess ;
+    ok = ok && f->d_trsm.upload (P.trsm, s) == cudaSuccess ;
+    ok = ok && f->d_Lx.alloc ((size_t) P.xsize * f->esize) == cudaSuccess ;
+    ok = ok && f->d_minor.alloc (1) == cudaSuccess ;
+    if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
+    CK (cudaStreamSynchronize (s), "upload symbolic") ;
+    f->device_bytes = f->d_super.bytes () + f->d_pi.bytes () + f->d_px.bytes () + f->d_Ls.bytes ()
+        + f->d_supermap.bytes () + f->d_relmap.bytes () + f->d_level_list.bytes () + f->d_items.bytes ()
+        + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () ;
+    return B200_OK ;
+}
+
+b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
+    const int64_t *px, const int64_t *s, int dtype, int device, int *status)
+{
+    int dummy ; if (!status) status = &dummy ;
+    *status = B200_OK ;
+    if (dtype != B200_DOUBLE && dtype != B200_SINGLE) { *status = B200_INVALID ; return nullptr ; }
+    b200_factor *f = new (std::nothrow) b200_factor ;
+    if (!f) { *status = B200_OUT_OF_MEMORY ; return nullptr ; }
+    f->dtype = dtype ; f->esize = (dtype == B200_DOUBLE) ? 8 : 4 ; f->device = device ;
+    try
+    {
+        *status = build_plan (n, nsuper, super, pi, px, s, dtype == B200_DOUBLE, f->plan) ;
+        if (*status == B200_OK)
+        {
+            f->h_super.assign (super, super + nsuper + 1) ;
+            f->h_pi.assign (pi, pi + nsuper + 1) ;
+            f->h_px.assign (px, px + nsuper + 1) ;
+        }
+    }
+    catch (const std::bad_alloc &) { *status = B200_OUT_OF_MEMORY ; }
+    if (*status == B200_OK && device >= 0)
+    {
+        try { *status = create_device_side (f, s) ; }
+        catch (const std::bad_alloc &) { *status = B200_OUT_OF_MEMORY ; }
+    }
+    if (*status != B200_OK) { b200_destroy (f) ; return nullptr ; }
+    return f ;
+}
+
+void b200_destroy (b200_factor *f)
+{
+    if (!f) return ;
+    if (f->device >= 0 && f->stream)
+    {
+        cudaSetDevice (f->device) ;
+        cudaStreamSynchronize (f->stream) ;
+        if (f->reg_ptr) cudaHostUnregister (f->reg_ptr) ;
+        f->d_super.release () ; f->d_pi.release () ; f->d_px.release () ; f->d_Ls.release () ;
+        f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
+        f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
+        f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
+        f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ;
+        for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
+        for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
+        cudaStreamDestroy (f->stream) ;
+        cudaGetLastError () ;
+    }
+    delete f ;
+}
+
+int64_t b200_get_int (const b200_factor *f, const char *name)
+{
+    if (!f || !name) return -1 ;
+    const Plan &P = f->plan ;
+    if (!strcmp (name, "n")) return P.n ;
+    if (!strcmp (name, "nsuper")) return P.nsuper ;
+    if (!strcmp (name, "xsize")) return P.xsize ;
+    if (!strcmp (name, "ssize")) return P.ssize ;
+    if (!strcmp (name, "nlevels")) return P.nlevels ;
+    if (!strcmp (name, "npairs")) return P.npairs ;
+    if (!strcmp (name, "relmap_len")) return (int64_t) P.relmap.size () ;
+    if (!strcmp (name, "nitems")) return (int64_t) P.items.size () ;
+    if (!strcmp (name, "ntiles")) return (int64_t) P.tiles.size () ;
+    if (!strcmp (name, "npotrf")) return (int64_t) P.potrf.size () ;
+    if (!strcmp (name, "ntrsm")) return (int64_t) P.trsm.size () ;
+    if (!strcmp (name, "nlaunches")) return (int64_t) P.launches.size () ;
+    if (!strcmp (name, "device_bytes")) return (int64_t) f->device_bytes ;
+    if (!strcmp (name, "device")) return f->device ;
+    if (!strcmp (name, "dtype")) return f->dtype ;
+    if (!strcmp (name, "kernel_launches")) return f->kernel_launches ;
+    if (!strcmp (name, "ngpus")) return f->device >= 0 ? 1 : 0 ;
+    if (!strcmp (name, "profile")) return f->profile ;
+    if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] <= '4') return f->launches_kind [name [13] - '0'] ;
+    if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] <= '4') return P.count_kind [name [10] - '0'] ;
+    return -1 ;
+}
+
+int b200_set_int (b200_factor *f, const char *name, int64_t value)
+{
+    if (!f || !name) return B200_INVALID ;
+    if (!strcmp (name, "profile")) { f->profile = value ? 1 : 0 ; return B200_OK ; }
+    return B200_INVALID ;
+}
+
+double b200_get_double (const b200_factor *f, const char *name)
+{
+    if (!f || !name) return -1 ;
+    const Plan &P = f->plan ;
+    if (!strcmp (name, "flops_executed")) return P.flops_update + P.flops_potrf + P.flops_trsm ;
+    if (!strcmp (name, "flops_update")) return P.flops_update ;
+    if (!strcmp (name, "flops_potrf")) return P.flops_potrf ;
+    if (!strcmp (name, "flops_trsm")) return P.flops_trsm ;
+    if (!strcmp (name, "ms_factor")) return f->ms_factor ;
+    if (!strcmp (name, "ms_h2d")) return f->ms_h2d ;
+    if (!strcmp (name, "ms_d2h")) return f->ms_d2h ;
+    if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
+    if (!strcmp (name, "ms_solve")) return f->ms_solve ;
+    if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '4') return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] <= '4') return P.flops_kind [name [10] - '0'] ;
+    return -1 ;
+}
+
+// Copy plan tables to caller buffers (tests of the host planner; works on a device < 0 context).
+// which: "level" int32[nsuper], "relmap" int32[relmap_len], "items" (nitems x 48 bytes),
+// "tiles" (ntiles x 16), "potrf" (npotrf x 24), "trsm" (ntrsm x 32), "launches" (nlaunches x 24),
+// "parent" int64[nsuper].  Returns the number of bytes written, or -1.
+int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, int64_t out_bytes)
+{
+    if (!f || !which) return -1 ;
+    const Plan &P = f->plan ;
+    const void *src = nullptr ; size_t bytes = 0 ;
+    if (!strcmp (which, "level")) { src = P.level.data () ; bytes = P.level.size () * sizeof (int32_t) ; }
+    else if (!strcmp (which, "parent")) { src = P.parent.data () ; bytes = P.parent.size () * sizeof (int64_t) ; }
+    else if (!strcmp (which, "relmap")) { src = P.relmap.data () ; bytes = P.relmap.size () * sizeof (int32_t) ; }
+    else if (!strcmp (which, "items")) { src = P.items.data () ; bytes = P.items.size () * sizeof (UpdItem) ; }
+    else if (!strcmp (which, "tiles")) { src = P.tiles.data () ; bytes = P.tiles.size () * sizeof (UpdTile) ; }
+    else if (!strcmp (which, "potrf")) { src = P.potrf.data () ; bytes = P.potrf.size () * sizeof (PotrfBlk) ; }
+    else if (!strcmp (which, "trsm")) { src = P.trsm.data () ; bytes = P.trsm.size () * sizeof (TrsmTile) ; }
+    else if (!strcmp (which, "launches")) { src = P.launches.data () ; bytes = P.launches.size () * sizeof (Launch) ; }
+    else return -1 ;
+    if (!out) return (int64_t) bytes ;
+    if ((int64_t) bytes > out_bytes) return -1 ;
+    if (bytes) memcpy (out, src, bytes) ;
+    return (int64_t) bytes ;
+}
+
+int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!Ap || (!Ai && f->plan.n > 0)) return B200_INVALID ;
+    const int64_t n = f->plan.n ;
+    // unpacked matrices: entries of column k live at Ap [k] .. Ap [k] + Anz [k]; copy up to max end
+    int64_t nz = Ap [n] ;
+    if (Anz) for (int64_t k = 0 ; k < n ; k++) nz = (Ap [k] + Anz [k] > nz) ? Ap [k] + Anz [k] : nz ;
+    if (nz < 0) return B200_INVALID ;
+    cudaStream_t s = f->stream ;
+    if (f->d_Ap.n < (size_t) n + 1 && f->d_Ap.alloc ((size_t) n + 1) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (f->d_Ai.n < (size_t) nz && f->d_Ai.alloc ((size_t) nz) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (f->d_Ax.n < (size_t) nz * f->esize && f->d_Ax.alloc ((size_t) nz * f->esize) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (Anz && f->d_Anz.n < (size_t) n && f->d_Anz.alloc ((size_t) n) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    CK (cudaEventRecord (f->ev [0], s), "record") ;
+    CK (cudaMemcpyAsync (f->d_Ap.p, Ap, (size_t) (n + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
+    if (nz > 0)
+    {
+        CK (cudaMemcpyAsync (f->d_Ai.p, Ai, (size_t) nz * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ai") ;
+        CK (cudaMemcpyAsync (f->d_Ax.p, Ax, (size_t) nz * f->esize, cudaMemcpyHostToDevice, s), "H2D Ax") ;
+    }
+    if (Anz && n > 0) CK (cudaMemcpyAsync (f->d_Anz.p, Anz, (size_t) n * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
+    CK (cudaEventRecord (f->ev [1], s), "record") ;
+    CK (cudaStreamSynchronize (s), "H2D A") ;
+    cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
+    f->have_A = true ; f->A_unpacked = (Anz != nullptr) ; f->A_nz = nz ;
+    return B200_OK ;
+}
+
+}   // extern "C"
+
+template <typename T>
+static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *minor_out)
+{
+    const Plan &P = f->plan ;
+    cudaStream_t s = f->stream ;
+    const unsigned long long big = ~0ull ;
+    f->kernel_launches = 0 ;
+    for (int k = 0 ; k < 5 ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
+    CK (cudaEventRecord (f->ev [2], s), "record") ;
+    CK (cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, s), "minor init") ;
+    if (P.xsize > 0) CK (cudaMemsetAsync (f->d_Lx.p, 0, (size_t) P.xsize * sizeof (T), s), "memset Lx") ;
+    int st = scatter_A<T> (f, 0, P.n, beta) ;
+    if (st) return st ;
+    CK (cudaEventRecord (f->ev [3], s), "record") ;
+    st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p) ;
+    if (st) return st ;
+    unsigned long long minor = big ;
+    CK (cudaMemcpyAsync (&minor, f->d_minor.p, sizeof (minor), cudaMemcpyDeviceToHost, s), "minor read") ;
+    CK (cudaEventRecord (f->ev [4], s), "record") ;
+    CK (cudaStreamSynchronize (s), "factorize") ;
+    cudaEventElapsedTime (&f->ms_scatter, f->ev [2], f->ev [3]) ;
+    cudaEventElapsedTime (&f->ms_factor, f->ev [2], f->ev [4]) ;
+    if (minor == big)
+    {
+        if (minor_out) *minor_out = P.n ;
+        return B200_OK ;
+    }
+    // not positive definite: reproduce SNW:1084-1146
+    if (minor_out) *minor_out = (int64_t) minor ;
+    st = repair_not_posdef<T> (f, (int64_t) minor, beta, quick) ;
+    if (st < 0) return st ;
+    CK (cudaStreamSynchronize (s), "repair") ;
+    return B200_NOT_POSDEF ;
+}
+
+extern "C" {
+
+int b200_factor_device (b200_factor *f, double beta, int quick_return_if_not_posdef, int64_t *minor)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!f->have_A) return B200_INVALID ;
+    return (f->dtype == B200_DOUBLE) ? factor_device_T<double> (f, beta, quick_return_if_not_posdef, minor)
+                                     : factor_device_T<float> (f, beta, quick_return_if_not_posdef, minor) ;
+}
+
+int b200_download_factor (b200_factor *f, void *Lx)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
+    size_t bytes = (size_t) f->plan.xsize * f->esize ;
+    if (bytes == 0) return B200_OK ;
+    // pin the caller's buffer once: later factorizations into the same L->x then copy at PCIe speed
+    if (f->reg_ptr != Lx || f->reg_bytes != bytes)
+    {
+        if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
+        if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterDefault) == cudaSuccess)
+        {
+            f->reg_ptr = Lx ; f->reg_bytes = bytes ;
+        }
+        else cudaGetLastError () ;
+    }
+    CK (cudaEventRecord (f->ev [5], f->stream), "record") ;
+    CK (cudaMemcpyAsync (Lx, f->d_Lx.p, bytes, cudaMemcpyDeviceToHost, f->stream), "D2H Lx") ;
+    CK (cudaEventRecord (f->ev [6], f->stream), "record") ;
+    CK (cudaStreamSynchronize (f->stream), "D2H Lx") ;
+    cudaEventElapsedTime (&f->ms_d2h, f->ev [5], f->ev [6]) ;
+    return B200_OK ;
+}
+
+int b200_upload_factor (b200_factor *f, const void *Lx)
+{
+    int st = set_device (f) ; if (st) return st ;
+    size_t bytes = (size_t) f->plan.xsize * f->esize ;
+    if (bytes == 0) return B200_OK ;
+    if (!Lx) return B200_INVALID ;
+    CK (cudaMemcpyAsync (f->d_Lx.p, Lx, bytes, cudaMemcpyHostToDevice, f->stream), "H2D Lx") ;
+    CK (cudaStreamSynchronize (f->stream), "H2D Lx") ;
+    return B200_OK ;
+}
+
+void *b200_device_Lx (b200_factor *f) { return (f && f->device >= 0) ? (void *) f->d_Lx.p : nullptr ; }
+
+int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const double *Ax, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor)
+{
+    if (!f || f->dtype != B200_DOUBLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
+    int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
+    if (st < 0) return st ;
+    int fst = b200_factor_device (f, beta, quick_return_if_not_posdef, minor) ;
+    if (fst < 0) return fst ;
+    st = b200_download_factor (f, Lx) ;
+    return st < 0 ? st : fst ;
+}
+
+int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const float *Ax, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor)
+{
+    if (!f || f->dtype != B200_SINGLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
+    int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
+    if (st < 0) return st ;
+    int fst = b200_factor_device (f, beta, quick_return_if_not_posdef, minor) ;
+    if (fst < 0) return fst ;
+    st = b200_download_factor (f, Lx) ;
+    return st < 0 ? st : fst ;
+}
+
+}   // extern "C"
+
+template <typename T>
+static int solve_T (b200_factor *f, int nrhs)
+{
+    const Plan &P = f->plan ;
+    cudaStream_t s = f->stream ;
+    const int64_t cap = (200 * 1024) / 8 ;
+    const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
+    for (int lev = 0 ; lev < P.nlevels ; lev++)
+    {
+        int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
+        if (cnt <= 0) continue ;
+        int64_t maxcol = 0 ;
+        for (int64_t q = 0 ; q < cnt ; q++)
+        {
+            int32_t sn = P.level_list [first + q] ;
+            maxcol = std::max (maxcol, f->h_super [sn+1] - f->h_super [sn]) ;
+        }
+        size_t sm = (size_t) std::min (maxcol, cap) * 8 ;
+        k_solve_fwd<T><<<(unsigned) cnt, 256, sm, s>>> (f->d_level_list.p + first, f->d_super.p, f->d_pi.p,
+            f->d_px.p, f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+    }
+    for (int lev = P.nlevels - 1 ; lev >= 0 ; lev--)
+    {
+        int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
+        if (cnt <= 0) continue ;
+        int64_t maxcol = 0 ;
+        for (int64_t q = 0 ; q < cnt ; q++)
+        {
+            int32_t sn = P.level_list [first + q] ;
+            maxcol = std::max (maxcol, f->h_super [sn+1] - f->h_super [sn]) ;
+        }
+        size_t sm = (size_t) std::min (maxcol, cap) * 8 ;
+        k_solve_bwd<T><<<(unsigned) cnt, 256, sm, s>>> (f->d_level_list.p + first, f->d_super.p, f->d_pi.p,
+            f->d_px.p, f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+    }
+    CK (cudaGetLastError (), "solve kernels") ;
+    return B200_OK ;
+}
+
+extern "C" {
+
+int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs)
+{
+    int st = set_device (f) ; if (st) return st ;
+    const int64_t n = f->plan.n ;
+    if (nrhs < 0 || (!B && n * nrhs > 0) || (!X && n * nrhs > 0)) return B200_INVALID ;
+    if (n == 0 || nrhs == 0) return B200_OK ;
+    size_t cnt = (size_t) n * (size_t) nrhs ;
+    if (f->d_X.n < cnt && f->d_X.alloc (cnt) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    cudaStream_t s = f->stream ;
+    CK (cudaMemcpyAsync (f->d_X.p, B, cnt * 8, cudaMemcpyHostToDevice, s), "H2D B") ;
+    CK (cudaEventRecord (f->ev [0], s), "record") ;
+    st = (f->dtype == B200_DOUBLE) ? solve_T<double> (f, (int) nrhs) : solve_T<float> (f, (int) nrhs) ;
+    if (st) return st ;
+    CK (cudaEventRecord (f->ev [1], s), "record") ;
+    CK (cudaMemcpyAsync (X, f->d_X.p, cnt * 8, cudaMemcpyDeviceToHost, s), "D2H X") ;
+    CK (cudaStreamSynchronize (s), "solve") ;
+    cudaEventElapsedTime (&f->ms_solve, f->ev [0], f->ev [1]) ;
+    return B200_OK ;
+}
+
+}   // extern "C"

@@ -1,0 +1,486 @@
+// kernels.cuh -- sm_100a kernels of the CHOLMOD/B200 numeric phase.
+//
+//   k_scatter_A   zero-initialised supernodes <- A, + beta on the diagonal          (SNW:361-520)
+//   k_upd_simt    small descendant updates, one warp per 32x8 tile                  (SNW:769-930)
+//   k_upd_dmma    descendant / trailing updates on the FP64 tensor pipe (DMMA),
+//                 cp.async-staged shared-memory tiles, fused relative-map scatter    (SNW:769-930)
+//   k_potrf       dense Cholesky of one <=64-wide diagonal block per CTA             (SNW:1023)
+//   k_trsm        X <- X * L11^{-T} for 128 rows per CTA                             (SNW:1175)
+//   k_solve_*     supernodal forward / backward solve                               (SSOL:20-586)
+//
+// "SNW" = CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c, "SSOL" = t_cholmod_super_solve_worker.c.
+// FP64 has no tcgen05 kind: the FP64 tensor path on sm_100a is mma.sync (SASS DMMA), so operands are
+// staged global -> shared with cp.async (panels have arbitrary 8-byte-aligned leading dimensions, which
+// rules out TMA tensor maps) and fed to mma.sync.m8n8k4 from registers.
+#pragma once
+#include "plan.hpp"
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------
+// scatter A
+// ---------------------------------------------------------------------------------------------
+
+// One thread per column k of A.  Lx must already be zero.  Row i >= k of column k goes to local row
+// Map [i] of supernode s = SuperMap [k]; the reference's Map array is replaced by: i - k1 inside the
+// diagonal block, a binary search of the (ascending) off-diagonal row list otherwise.  Entries above the
+// diagonal or outside the pattern of L are dropped (SNW:455-468); duplicates: the last one wins, as in
+// the reference's assignment.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_scatter_A (int64_t kfirst, int64_t klast,
+    const int64_t *__restrict__ Ap, const int64_t *__restrict__ Ai, const int64_t *__restrict__ Anz,
+    const T *__restrict__ Ax, const int32_t *__restrict__ supermap, const int64_t *__restrict__ super,
+    const int64_t *__restrict__ pi, const int64_t *__restrict__ px, const int32_t *__restrict__ Ls,
+    T beta, T *__restrict__ Lx)
+{
+    int64_t k = kfirst + (int64_t) blockIdx.x * blockDim.x + threadIdx.x ;
+    if (k >= klast) return ;
+    int32_t s = supermap [k] ;
+    int64_t k1 = super [s], k2 = super [s+1], psi = pi [s] ;
+    int64_t nsrow = pi [s+1] - psi, nscol = k2 - k1 ;
+    T *col = Lx + px [s] + (k - k1) * nsrow ;
+    int64_t p = Ap [k], pend = Anz ? p + Anz [k] : Ap [k+1] ;
+    for ( ; p < pend ; p++)
+    {
+        int64_t i = Ai [p] ;
+        if (i < k) continue ;
+        int64_t pos ;
+        if (i < k2)
+        {
+            pos = i - k1 ;
+        }
+        else
+        {
+            int64_t lo = nscol, hi = nsrow ;        // first position with Ls >= i
+            while (lo < hi)
+            {
+                int64_t mid = (lo + hi) >> 1 ;
+                if ((int64_t) Ls [psi + mid] < i) lo = mid + 1 ; else hi = mid ;
+            }
+            if (lo >= nsrow || (int64_t) Ls [psi + lo] != i) continue ;
+            pos = lo ;
+        }
+        col [pos] = Ax [p] ;
+    }
+    if (beta != (T) 0) col [k - k1] += beta ;
+}
+
+// ---------------------------------------------------------------------------------------------
+// small updates: one warp per 32 x 8 tile, operands straight from L1/L2
+// ---------------------------------------------------------------------------------------------
+
+template <typename T>
+__global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ tiles, int ntiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, T *Lx)
+{
+    int w = (int) (((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5) ;
+    int lane = threadIdx.x & 31 ;
+    if (w >= ntiles) return ;
+    UpdTile t = tiles [w] ;
+    const UpdItem it = items [t.item] ;
+    const int i = (int) t.ti * SIMT_TM + lane ;
+    const int j0 = (int) t.tj * SIMT_TN ;
+    const int nj = min (SIMT_TN, it.N - j0) ;
+    const bool rowok = i < it.M ;
+    const T *A = Lx + it.a_off ;
+    const int64_t lda = it.lda ;
+    T acc [SIMT_TN] ;
+    #pragma unroll
+    for (int jj = 0 ; jj < SIMT_TN ; jj++) acc [jj] = 0 ;
+    for (int k = t.k0 ; k < t.k1 ; k++)
+    {
+        const T *Ak = A + (int64_t) k * lda ;
+        T a = rowok ? Ak [i] : (T) 0 ;
+        #pragma unroll
+        for (int jj = 0 ; jj < SIMT_TN ; jj++)
+        {
+            T b = (jj < nj) ? Ak [j0 + jj] : (T) 0 ;
+            acc [jj] += a * b ;
+        }
+    }
+    if (!rowok) return ;
+    const bool mapped = it.map_off >= 0 ;
+    const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+    const int64_t ri = mapped ? (int64_t) map [i] : (int64_t) i ;
+    T *C = Lx + it.c_off + ri ;
+    #pragma unroll
+    for (int jj = 0 ; jj < SIMT_TN ; jj++)
+    {
+        int j = j0 + jj ;
+        if (jj < nj && i >= j)
+        {
+            int64_t cj = mapped ? (int64_t) map [j] : (int64_t) j ;
+            atomicAdd (C + cj * it.ldc, -acc [jj]) ;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// DMMA update kernel
+// ---------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ void cp_async8 (void *smem_dst, const void *gsrc, bool valid)
+{
+    unsigned d = (unsigned) __cvta_generic_to_shared (smem_dst) ;
+    int sz = valid ? 8 : 0 ;
+    asm volatile ("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" :: "r" (d), "l" (gsrc), "r" (sz)) ;
+}
+__device__ __forceinline__ void cp_async_commit () { asm volatile ("cp.async.commit_group;\n" ::) ; }
+template <int N> __device__ __forceinline__ void cp_async_wait () { asm volatile ("cp.async.wait_group %0;\n" :: "n" (N)) ; }
+
+__device__ __forceinline__ void dmma884 (double &d0, double &d1, double a, double b)
+{
+    asm volatile ("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+        : "+d" (d0), "+d" (d1) : "d" (a), "d" (b)) ;
+}
+
+constexpr int DM_KC = 16 ;          // K depth of one pipeline stage
+constexpr int DM_STAGES = 3 ;
+
+template <int TM, int TN> constexpr size_t dmma_smem_bytes ()
+{
+    return (size_t) DM_STAGES * DM_KC * ((TM + 4) + (TN + 4)) * sizeof (double) + (TM + TN) * sizeof (int32_t) ;
+}
+
+// C tile (TM x TN) of one item, inner range [k0,k1): CTA of (TM/WM)*(TN/WN) warps, each warp owns a
+// WM x WN sub-tile as (WM/8) x (WN/8) m8n8k4 accumulators.  Shared tiles are stored [k][m] with the row
+// pitch padded to TM+4 doubles, so that the 16 lanes of a half-warp (k = lane%4, m = lane/4) hit 16
+// distinct 8-byte banks.  Epilogue: red.global.add.f64 of -C through the relative map.
+template <int TM, int TN, int WM, int WN>
+__global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const UpdTile *__restrict__ tiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, double *Lx)
+{
+    constexpr int NW_M = TM / WM, NW_N = TN / WN ;
+    constexpr int NT = NW_M * NW_N * 32 ;
+    constexpr int LDA_S = TM + 4, LDB_S = TN + 4 ;
+    constexpr int MT = WM / 8, NTL = WN / 8 ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    double *sA = reinterpret_cast<double *> (smem_raw) ;                 // [STAGES][KC][LDA_S]
+    double *sB = sA + DM_STAGES * DM_KC * LDA_S ;                        // [STAGES][KC][LDB_S]
+    int32_t *smap_r = reinterpret_cast<int32_t *> (sB + DM_STAGES * DM_KC * LDB_S) ;    // [TM]
+    int32_t *smap_c = smap_r + TM ;                                      // [TN]
+
+    const UpdTile t = tiles [blockIdx.x] ;
+    const UpdItem it = items [t.item] ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
+    const int wm = warp % NW_M, wn = warp / NW_M ;
+    const int i0 = (int) t.ti * TM, j0 = (int) t.tj * TN ;
+    const int mA = min (TM, it.M - i0), nB = min (TN, it.N - j0) ;
+    const int64_t lda = it.lda ;
+    const double *A = Lx + it.a_off ;
+    const double *Arow = A + i0, *Brow = A + j0 ;
+    const int kbeg = t.k0, kend = t.k1 ;
+    const int nk = (kend - kbeg + DM_KC - 1) / DM_KC ;
+
+    // relative maps of this tile's rows and columns
+    {
+        const bool mapped = it.map_off >= 0 ;
+        const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+        for (int m = tid ; m < TM ; m += NT) smap_r [m] = (m < mA) ? (mapped ? map [i0 + m] : i0 + m) : 0 ;
+        for (int m = tid ; m < TN ; m += NT) smap_c [m] = (m < nB) ? (mapped ? map [j0 + m] : j0 + m) : 0 ;
+    }
+
+    auto load_stage = [&] (int kt, int buf)
+    {
+        const int kb = kbeg + kt * DM_KC ;
+        double *dA = sA + buf * DM_KC * LDA_S ;
+        double *dB = sB + buf * DM_KC * LDB_S ;
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TM ; e += NT)
+        {
+            int m = e % TM, k = e / TM ;
+            bool ok = (m < mA) && (kb + k < kend) ;
+            cp_async8 (dA + k * LDA_S + m, ok ? (const void *) (Arow + m + (int64_t) (kb + k) * lda) : (const void *) A, ok) ;
+        }
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TN ; e += NT)
+        {
+            int m = e % TN, k = e / TN ;
+            bool ok = (m < nB) && (kb + k < kend) ;
+            cp_async8 (dB + k * LDB_S + m, ok ? (const void *) (Brow + m + (int64_t) (kb + k) * lda) : (const void *) A, ok) ;
+        }
+    } ;
+
+    double acc [MT][NTL][2] ;
+    #pragma unroll
+    for (int a = 0 ; a < MT ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) { acc [a][b][0] = 0.0 ; acc [a][b][1] = 0.0 ; }
+
+    // a warp whose whole sub-tile lies strictly above the diagonal has nothing to compute
+    const bool warp_live = (i0 + wm * WM + WM - 1) >= (j0 + wn * WN) ;
+
+    #pragma unroll
+    for (int s = 0 ; s < DM_STAGES - 1 ; s++)
+    {
+        if (s < nk) load_stage (s, s) ;
+        cp_async_commit () ;
+    }
+    const int fk = lane & 3, fm = lane >> 2 ;
+    for (int kt = 0 ; kt < nk ; kt++)
+    {
+        cp_async_wait<DM_STAGES - 2> () ;
+        __syncthreads () ;
+        {
+            int nxt = kt + DM_STAGES - 1 ;
+            if (nxt < nk) load_stage (nxt, nxt % DM_STAGES) ;
+            cp_async_commit () ;
+        }
+        if (warp_live)
+        {
+            const double *cA = sA + (kt % DM_STAGES) * DM_KC * LDA_S + wm * WM + fm ;
+            const double *cB = sB + (kt % DM_STAGES) * DM_KC * LDB_S + wn * WN + fm ;
+            #pragma unroll
+            for (int kk = 0 ; kk < DM_KC ; kk += 4)
+            {
+                double fa [MT], fb [NTL] ;
+                #pragma unroll
+                for (int a = 0 ; a < MT ; a++) fa [a] = cA [(kk + fk) * LDA_S + a * 8] ;
+                #pragma unroll
+                for (int b = 0 ; b < NTL ; b++) fb [b] = cB [(kk + fk) * LDB_S + b * 8] ;
+                #pragma unroll
+                for (int a = 0 ; a < MT ; a++)
+                    #pragma unroll
+                    for (int b = 0 ; b < NTL ; b++)
+                        dmma884 (acc [a][b][0], acc [a][b][1], fa [a], fb [b]) ;
+            }
+        }
+    }
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    if (!warp_live) return ;
+
+    // epilogue: C (i,j) held by lane: i = 8a + lane/4, j = 8b + 2*(lane%4) + {0,1} within the warp tile
+    double *C = Lx + it.c_off ;
+    const int64_t ldc = it.ldc ;
+    #pragma unroll
+    for (int b = 0 ; b < NTL ; b++)
+    {
+        #pragma unroll
+        for (int e = 0 ; e < 2 ; e++)
+        {
+            const int jl = wn * WN + b * 8 + 2 * fk + e ;
+            if (jl >= nB) continue ;
+            const int j = j0 + jl ;
+            double *Cj = C + (int64_t) smap_c [jl] * ldc ;
+            #pragma unroll
+            for (int a = 0 ; a < MT ; a++)
+            {
+                const int il = wm * WM + a * 8 + fm ;
+                if (il < mA && i0 + il >= j) atomicAdd (Cj + smap_r [il], -acc [a][b][e]) ;
+            }
+        }
+    }
+}
+
+// Register-resident DMMA loop: the FP64 tensor peak this chip sustains (MEASURED_PEAKS.json has no FP64
+// figure, so bench.py measures the roofline denominator with this kernel on the box it runs on).
+__global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)
+{
+    double acc [16][2] ;
+    #pragma unroll
+    for (int i = 0 ; i < 16 ; i++) { acc [i][0] = 0.0 ; acc [i][1] = 0.0 ; }
+    double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9 ;
+    for (int it = 0 ; it < iters ; it++)
+    {
+        #pragma unroll
+        for (int i = 0 ; i < 16 ; i++) dmma884 (acc [i][0], acc [i][1], a, b) ;
+    }
+    double sum = 0 ;
+    #pragma unroll
+    for (int i = 0 ; i < 16 ; i++) sum += acc [i][0] + acc [i][1] ;
+    out [(size_t) blockIdx.x * blockDim.x + threadIdx.x] = sum ;
+}
+
+// ---------------------------------------------------------------------------------------------
+// dense Cholesky of one diagonal block (jb <= 64) per CTA, right-looking in shared memory
+// ---------------------------------------------------------------------------------------------
+
+constexpr int PB_LD = POTRF_NB + 1 ;
+
+// On a pivot that is not > 0 (or NaN) the global column index is recorded in *minor (atomicMin): the
+// smallest failing column over the whole factorization is the reference's L->minor (SNW:1097).
+template <typename T>
+__global__ void __launch_bounds__ (256) k_potrf (const PotrfBlk *__restrict__ blks, T *Lx,
+    unsigned long long *minor)
+{
+    __shared__ T s [POTRF_NB * PB_LD] ;         // s [c * PB_LD + r], lower part used
+    const PotrfBlk b = blks [blockIdx.x] ;
+    const int jb = b.jb ;
+    const int64_t lda = b.lda ;
+    T *D = Lx + b.off ;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5 ;
+    for (int c = ty ; c < jb ; c += 8)
+        for (int r = c + tx ; r < jb ; r += 32)
+            s [c * PB_LD + r] = D [r + c * lda] ;
+    __syncthreads () ;
+    for (int j = 0 ; j < jb ; j++)
+    {
+        T d = s [j * PB_LD + j] ;
+        if (!(d > (T) 0))
+        {
+            if (threadIdx.x == 0) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        }
+        T ljj = sqrt (d) ;
+        __syncthreads () ;                      // everyone has read the pivot
+        for (int r = j + threadIdx.x ; r < jb ; r += 256)
+            s [j * PB_LD + r] = (r == j) ? ljj : s [j * PB_LD + r] / ljj ;
+        __syncthreads () ;
+        const T *lj = s + j * PB_LD ;
+        for (int c = j + 1 + ty ; c < jb ; c += 8)
+        {
+            T ljc = lj [c] ;
+            for (int r = c + tx ; r < jb ; r += 32)
+                s [c * PB_LD + r] -= lj [r] * ljc ;
+        }
+        __syncthreads () ;
+    }
+    for (int c = ty ; c < jb ; c += 8)
+        for (int r = c + tx ; r < jb ; r += 32)
+            D [r + c * lda] = s [c * PB_LD + r] ;
+}
+
+// ---------------------------------------------------------------------------------------------
+// triangular solve of the rows below a factorized diagonal block: one thread per row
+// ---------------------------------------------------------------------------------------------
+
+template <typename T, int NB>
+__device__ __forceinline__ void trsm_row (const T *sL, T *X, int64_t lda, int jb)
+{
+    T x [NB] ;
+    #pragma unroll
+    for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : (T) 0 ;
+    #pragma unroll
+    for (int j = 0 ; j < NB ; j++)
+    {
+        // columns >= jb of sL hold the identity, so the padded part is a no-op
+        T xj = x [j] / sL [j * PB_LD + j] ;
+        x [j] = xj ;
+        #pragma unroll
+        for (int k = j + 1 ; k < NB ; k++) x [k] -= xj * sL [j * PB_LD + k] ;
+    }
+    #pragma unroll
+    for (int j = 0 ; j < NB ; j++) if (j < jb) X [j * lda] = x [j] ;
+}
+
+template <typename T>
+__global__ void __launch_bounds__ (TRSM_ROWS) k_trsm (const TrsmTile *__restrict__ tiles, T *Lx)
+{
+    __shared__ T sL [POTRF_NB * PB_LD] ;
+    const TrsmTile t = tiles [blockIdx.x] ;
+    const int jb = t.jb ;
+    const int64_t lda = t.lda ;
+    const int nbp = (jb <= 8) ? 8 : (jb <= 16) ? 16 : (jb <= 32) ? 32 : 64 ;
+    const T *D = Lx + t.diag_off ;
+    for (int e = threadIdx.x ; e < nbp * nbp ; e += TRSM_ROWS)
+    {
+        int r = e % nbp, c = e / nbp ;
+        T v ;
+        if (r < jb && c < jb) v = (r >= c) ? D [r + c * lda] : (T) 0 ;
+        else v = (r == c) ? (T) 1 : (T) 0 ;
+        sL [c * PB_LD + r] = v ;
+    }
+    __syncthreads () ;
+    if ((int) threadIdx.x >= t.nrows) return ;
+    T *X = Lx + t.row_off + threadIdx.x ;
+    if (nbp == 8) trsm_row<T, 8> (sL, X, lda, jb) ;
+    else if (nbp == 16) trsm_row<T, 16> (sL, X, lda, jb) ;
+    else if (nbp == 32) trsm_row<T, 32> (sL, X, lda, jb) ;
+    else trsm_row<T, 64> (sL, X, lda, jb) ;
+}
+
+// ---------------------------------------------------------------------------------------------
+// supernodal solve, one CTA per supernode of a level (forward: leaves first; backward: root first)
+// ---------------------------------------------------------------------------------------------
+
+// forward:  x1 <- L11 \ x1 ;  x [rows below] -= L21 * x1      (SSOL:20-303; atomics because siblings of
+// one level update common ancestor rows concurrently)
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_fwd (const int32_t *__restrict__ list,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs, int64_t smem_cap)
+{
+    extern __shared__ double sx_smem [] ;       // [min (nscol, smem_cap)]
+    const int s = list [blockIdx.x] ;
+    const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
+    const T *L = Lx + px [s] ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        double *x = X + (int64_t) rhs * n ;
+        // work in shared memory when the supernode's columns fit, else in place in global memory
+        const bool in_smem = nscol <= smem_cap ;
+        double *sx = in_smem ? sx_smem : x + k1 ;
+        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) sx [j] = x [k1 + j] ;
+        __syncthreads () ;
+        for (int64_t j = 0 ; j < nscol ; j++)
+        {
+            double xj = sx [j] / (double) L [j + j * nsrow] ;
+            __syncthreads () ;
+            if (threadIdx.x == 0) sx [j] = xj ;
+            for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
+                sx [i] -= (double) L [i + j * nsrow] * xj ;
+            __syncthreads () ;
+        }
+        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) x [k1 + j] = sx [j] ;
+        for (int64_t i = nscol + threadIdx.x ; i < nsrow ; i += blockDim.x)
+        {
+            double acc = 0 ;
+            for (int64_t j = 0 ; j < nscol ; j++) acc += (double) L [i + j * nsrow] * sx [j] ;
+            atomicAdd (x + Ls [psi + i], -acc) ;
+        }
+        __syncthreads () ;
+    }
+}
+
+// backward:  x1 <- L11' \ (x1 - L21' * x [rows below])        (SSOL:309-586)
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__ list,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs, int64_t smem_cap)
+{
+    extern __shared__ double sx_smem [] ;       // [min (nscol, smem_cap)]
+    __shared__ double red [8] ;
+    const int s = list [blockIdx.x] ;
+    const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
+    const T *L = Lx + px [s] ;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5 ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        double *x = X + (int64_t) rhs * n ;
+        const bool in_smem = nscol <= smem_cap ;
+        double *sx = in_smem ? sx_smem : x + k1 ;
+        // sx [j] = x [k1+j] - sum_{i >= nscol} L (i,j) * x [Ls [i]] : one warp per column
+        for (int64_t j = warp ; j < nscol ; j += nwarps)
+        {
+            double acc = 0 ;
+            for (int64_t i = nscol + lane ; i < nsrow ; i += 32)
+                acc += (double) L [i + j * nsrow] * x [Ls [psi + i]] ;
+            for (int o = 16 ; o > 0 ; o >>= 1) acc += __shfl_xor_sync (0xffffffffu, acc, o) ;
+            if (lane == 0) sx [j] = x [k1 + j] - acc ;
+        }
+        __syncthreads () ;
+        for (int64_t j = nscol - 1 ; j >= 0 ; j--)
+        {
+            // xj = (sx [j] - sum_{i > j, i < nscol} L (i,j) * sx [i]) / L (j,j)
+            double acc = 0 ;
+            for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
+                acc += (double) L [i + j * nsrow] * sx [i] ;
+            for (int o = 16 ; o > 0 ; o >>= 1) acc += __shfl_xor_sync (0xffffffffu, acc, o) ;
+            if (lane == 0) red [warp] = acc ;
+            __syncthreads () ;
+            if (threadIdx.x == 0)
+            {
+                double tot = 0 ;
+                for (int w = 0 ; w < nwarps ; w++) tot += red [w] ;
+                sx [j] = (sx [j] - tot) / (double) L [j + j * nsrow] ;
+            }
+            __syncthreads () ;
+        }
+        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) x [k1 + j] = sx [j] ;
+        __syncthreads () ;
+    }
+}
+
+}   // namespace b200

@@ -1,0 +1,353 @@
+// plan.cpp -- builds the level-ordered launch plan from the supernodal symbolic factor (host, once
+// per analysis).  See plan.hpp.  Reference behaviour restated here (not copied):
+//   * pair enumeration = the walk cholmod_super_symbolic.c:896-921 uses to size C, which visits exactly
+//     the (d, s) pairs the numeric loop later visits through its Head/Next/Lpos lists (SNW:588-969);
+//   * relative map of a pair = Map [Ls [pdi1 + i]] with Map built from the rows of s (SNW:388-399, :897-903);
+//   * etree parent of s = SuperMap [Ls [pi [s] + nscol]] (SNW:1226).
+#include "plan.hpp"
+#include "../../include/cholmod_b200.h"
+#include <algorithm>
+#include <cstring>
+
+namespace b200 {
+
+namespace {
+
+struct TileSink
+{
+    std::vector<UpdTile> cls [3] ;      // per update kernel class
+    void clear () { for (auto &v : cls) v.clear () ; }
+} ;
+
+inline int64_t cdiv (int64_t a, int64_t b) { return (a + b - 1) / b ; }
+
+// choose the kernel class of an item and emit its tiles
+void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bool use_dmma)
+{
+    const int64_t M = it.M, N = it.N, K = it.K ;
+    int cls ;
+    if (!use_dmma || N < 16 || K < 8 || M * N < 2048)
+    {
+        cls = K_UPD_SIMT ;
+    }
+    else
+    {
+        // padded work of the two DMMA tilings; the 64-tile kernel re-reads operands twice as often
+        double c64  = 1.25 * (double) (cdiv (M, 64) * 64) * (double) (cdiv (N, 64) * 64) ;
+        double c128 = (double) (cdiv (M, 128) * 128) * (double) (cdiv (N, 128) * 128) ;
+        cls = (c128 <= c64) ? K_UPD_D128 : K_UPD_D64 ;
+    }
+    const int TM = (cls == K_UPD_SIMT) ? SIMT_TM : (cls == K_UPD_D64 ? 64 : 128) ;
+    const int TN = (cls == K_UPD_SIMT) ? SIMT_TN : (cls == K_UPD_D64 ? 64 : 128) ;
+    const int64_t nti = cdiv (M, TM), ntj = cdiv (N, TN) ;
+    // count the tiles that intersect the lower trapezoid
+    int64_t ntiles = 0 ;
+    for (int64_t tj = 0 ; tj < ntj ; tj++)
+    {
+        int64_t ti0 = (tj * TN) / TM ;          // first tile row whose last row reaches column tj*TN
+        ntiles += nti - ti0 ;
+    }
+    // split K when a long inner dimension meets few tiles (the output is accumulated with atomics,
+    // so partial sums need no workspace)
+    int64_t nsplit = 1 ;
+    if (cls != K_UPD_SIMT && K >= 1024 && ntiles < 296)
+    {
+        nsplit = std::min<int64_t> (K / 256, cdiv (592, ntiles)) ;
+        if (nsplit < 1) nsplit = 1 ;
+    }
+    int64_t kchunk = cdiv (cdiv (K, nsplit), 16) * 16 ;
+    auto &out = sink.cls [cls] ;
+    P.flops_kind [cls] += (double) K * (double) N * (2.0 * (double) M - (double) N) ;
+    for (int64_t tj = 0 ; tj < ntj ; tj++)
+    {
+        int64_t ti0 = (tj * TN) / TM ;
+        for (int64_t ti = ti0 ; ti < nti ; ti++)
+        {
+            for (int64_t k0 = 0 ; k0 < K ; k0 += kchunk)
+            {
+                UpdTile t ;
+                t.item = item_id ;
+                t.ti = (uint16_t) ti ; t.tj = (uint16_t) tj ;
+                t.k0 = (int32_t) k0 ; t.k1 = (int32_t) std::min<int64_t> (K, k0 + kchunk) ;
+                out.push_back (t) ;
+            }
+        }
+    }
+}
+
+void flush_tiles (Plan &P, TileSink &sink, int level)
+{
+    for (int c = 0 ; c < 3 ; c++)
+    {
+        auto &v = sink.cls [c] ;
+        if (v.empty ()) continue ;
+        Launch L ;
+        L.kind = c ; L.count = (int32_t) v.size () ; L.first = (int64_t) P.tiles.size () ;
+        L.level = level ; L.pad = 0 ;
+        P.count_kind [c] += L.count ;
+        P.tiles.insert (P.tiles.end (), v.begin (), v.end ()) ;
+        P.launches.push_back (L) ;
+    }
+    sink.clear () ;
+}
+
+// the descendant updates into supernode s
+void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const int64_t *pi,
+    const int64_t *px, int64_t s, TileSink &sink, bool use_dmma)
+{
+    for (int64_t t = P.target_ptr [s] ; t < P.target_ptr [s+1] ; t++)
+    {
+        const int32_t pid = P.target_list [t] ;
+        const Pair &pr = P.pairs [pid] ;
+        const int64_t d = pr.d ;
+        UpdItem it ;
+        it.lda = (int32_t) (pi [d+1] - pi [d]) ;
+        it.a_off = px [d] + pr.lpos ;
+        it.c_off = px [s] ;
+        it.ldc = (int32_t) (pi [s+1] - pi [s]) ;
+        it.map_off = P.pair_map [pid] ;
+        it.M = pr.ndrow2 ; it.N = pr.ndrow1 ; it.K = (int32_t) (super [d+1] - super [d]) ;
+        it.pad = 0 ;
+        out.items.push_back (it) ;
+        emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+    }
+}
+
+// blocked dpotrf + dtrsm of a set of independent supernodes, one POTRF_NB-wide block column per step.
+// ncol_eff [q] = number of leading columns of supernode S [q] to factorize (its nscol normally).
+void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int64_t *px,
+    const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma)
+{
+    int64_t maxcol = 0 ;
+    for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
+    for (int64_t j0 = 0 ; j0 < maxcol ; j0 += POTRF_NB)
+    {
+        Launch LP, LT ;
+        LP.kind = K_POTRF ; LP.first = (int64_t) out.potrf.size () ; LP.level = level ; LP.pad = 0 ;
+        LT.kind = K_TRSM ;  LT.first = (int64_t) out.trsm.size () ;  LT.level = level ; LT.pad = 0 ;
+        for (int64_t q = 0 ; q < ns ; q++)
+        {
+            const int64_t s = S [q] ;
+            const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
+            if (nscol <= j0) continue ;
+            const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
+            PotrfBlk b ;
+            b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
+            b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
+            out.potrf.push_back (b) ;
+            out.flops_kind [K_POTRF] += (double) jb * jb * jb / 3.0 ;
+            out.count_kind [K_POTRF]++ ;
+            const int64_t r0 = j0 + jb ;
+            for (int64_t r = r0 ; r < nsrow ; r += TRSM_ROWS)
+            {
+                TrsmTile t ;
+                t.diag_off = b.off ; t.row_off = px [s] + r + j0 * nsrow ;
+                t.lda = (int32_t) nsrow ; t.jb = (int32_t) jb ;
+                t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.pad = 0 ;
+                out.trsm.push_back (t) ;
+                out.flops_kind [K_TRSM] += (double) t.nrows * jb * jb ;
+                out.count_kind [K_TRSM]++ ;
+            }
+            // trailing updates inside the supernode (two-level blocking)
+            const int64_t J0 = (j0 / OUTER_NB) * OUTER_NB ;
+            const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
+            UpdItem it ;
+            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ;
+            if (r0 < Jend)
+            {
+                // inner: columns [r0, Jend) of the current outer block, K = jb
+                it.a_off = px [s] + r0 + j0 * nsrow ;
+                it.c_off = px [s] + r0 + r0 * nsrow ;
+                it.M = (int32_t) (nsrow - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
+                out.items.push_back (it) ;
+                emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+            }
+            else if (Jend < nscol)
+            {
+                // outer: all remaining columns [Jend, nscol), K = width of the finished outer block
+                it.a_off = px [s] + Jend + J0 * nsrow ;
+                it.c_off = px [s] + Jend + Jend * nsrow ;
+                it.M = (int32_t) (nsrow - Jend) ; it.N = (int32_t) (nscol - Jend) ;
+                it.K = (int32_t) (Jend - J0) ;
+                out.items.push_back (it) ;
+                emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+            }
+        }
+        LP.count = (int32_t) (out.potrf.size () - (size_t) LP.first) ;
+        LT.count = (int32_t) (out.trsm.size () - (size_t) LT.first) ;
+        if (LP.count > 0) out.launches.push_back (LP) ;
+        if (LT.count > 0) out.launches.push_back (LT) ;
+        flush_tiles (out, sink, level) ;
+    }
+}
+
+}   // namespace
+
+int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
+    const int64_t *Ls, bool use_dmma, Plan &P)
+{
+    if (n < 0 || nsuper < 0 || !super || !pi || !px || (!Ls && nsuper > 0)) return B200_INVALID ;
+    if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
+    P = Plan () ;
+    P.n = n ; P.nsuper = nsuper ;
+    if (nsuper == 0)
+    {
+        if (n != 0) return B200_INVALID ;
+        P.level_ptr.assign (1, 0) ;
+        P.target_ptr.assign (1, 0) ;
+        return B200_OK ;
+    }
+    if (super [0] != 0 || super [nsuper] != n || pi [0] != 0) return B200_INVALID ;
+    P.ssize = pi [nsuper] ; P.xsize = px [nsuper] ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
+        if (nscol <= 0 || nsrow < nscol || px [s+1] - px [s] != nscol * nsrow) return B200_INVALID ;
+        if (nsrow >= (int64_t) 1 << 30) return B200_TOO_LARGE ;
+        // the leading rows of a supernode are its own columns, in order (cholmod_super_symbolic.c:779-782)
+        if (Ls [pi [s]] != super [s] || Ls [pi [s] + nscol - 1] != super [s+1] - 1) return B200_INVALID ;
+    }
+
+    // column -> supernode
+    P.supermap.resize ((size_t) n) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+        for (int64_t k = super [s] ; k < super [s+1] ; k++) P.supermap [k] = (int32_t) s ;
+
+    // supernodal etree and levels (children precede parents: the factor is postordered)
+    P.parent.assign ((size_t) nsuper, -1) ;
+    P.level.assign ((size_t) nsuper, 0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
+        if (nsrow > nscol)
+        {
+            int64_t r = Ls [pi [s] + nscol] ;
+            if (r < super [s+1] || r >= n) return B200_INVALID ;
+            int64_t p = P.supermap [r] ;
+            P.parent [s] = p ;
+            P.level [p] = std::max (P.level [p], P.level [s] + 1) ;
+        }
+    }
+    int32_t nlevels = 0 ;
+    for (int64_t s = 0 ; s < nsuper ; s++) nlevels = std::max (nlevels, P.level [s] + 1) ;
+    P.nlevels = nlevels ;
+    P.level_ptr.assign ((size_t) nlevels + 1, 0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++) P.level_ptr [P.level [s] + 1]++ ;
+    for (int l = 0 ; l < nlevels ; l++) P.level_ptr [l+1] += P.level_ptr [l] ;
+    P.level_list.resize ((size_t) nsuper) ;
+    {
+        std::vector<int64_t> w (P.level_ptr.begin (), P.level_ptr.end () - 1) ;
+        for (int64_t s = 0 ; s < nsuper ; s++) P.level_list [w [P.level [s]]++] = (int32_t) s ;
+    }
+
+    // enumerate the update pairs (d -> s) by walking the rows of every descendant
+    std::vector<Pair> &pairs = P.pairs ;
+    std::vector<int64_t> &tcount = P.target_ptr ;
+    tcount.assign ((size_t) nsuper + 1, 0) ;
+    for (int64_t d = 0 ; d < nsuper ; d++)
+    {
+        int64_t ndcol = super [d+1] - super [d] ;
+        int64_t p = pi [d] + ndcol, pend = pi [d+1] ;
+        while (p < pend)
+        {
+            int64_t r = Ls [p] ;
+            if (r < 0 || r >= n) return B200_INVALID ;
+            int64_t s = P.supermap [r] ;
+            if (s <= d) return B200_INVALID ;
+            int64_t k2 = super [s+1], q = p ;
+            while (q < pend && Ls [q] < k2) q++ ;
+            Pair pr ;
+            pr.d = (int32_t) d ; pr.s = (int32_t) s ; pr.lpos = (int32_t) (p - pi [d]) ;
+            pr.ndrow1 = (int32_t) (q - p) ; pr.ndrow2 = (int32_t) (pend - p) ;
+            pairs.push_back (pr) ;
+            tcount [s+1]++ ;
+            P.flops_update += (double) ndcol * (double) pr.ndrow1 * (2.0 * pr.ndrow2 - pr.ndrow1) ;
+            p = q ;
+        }
+    }
+    if (pairs.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;
+    P.npairs = (int64_t) pairs.size () ;
+    for (int64_t s = 0 ; s < nsuper ; s++) tcount [s+1] += tcount [s] ;
+    P.target_list.resize (pairs.size ()) ;
+    {
+        std::vector<int64_t> w (tcount.begin (), tcount.end () - 1) ;
+        for (size_t k = 0 ; k < pairs.size () ; k++) P.target_list [w [pairs [k].s]++] = (int32_t) k ;
+    }
+
+    // relative maps: position of every remaining row of d inside the row list of s
+    P.pair_map.resize (pairs.size ()) ;
+    {
+        int64_t total = 0 ;
+        for (size_t k = 0 ; k < pairs.size () ; k++) total += pairs [k].ndrow2 ;
+        P.relmap.resize ((size_t) total) ;
+        std::vector<int32_t> Map ((size_t) n, -1), stamp ((size_t) n, -1) ;
+        int64_t off = 0 ;
+        for (int64_t s = 0 ; s < nsuper ; s++)
+        {
+            if (tcount [s] == tcount [s+1]) continue ;
+            int64_t nsrow = pi [s+1] - pi [s] ;
+            for (int64_t k = 0 ; k < nsrow ; k++)
+            {
+                int64_t r = Ls [pi [s] + k] ;
+                if (r < 0 || r >= n) return B200_INVALID ;
+                Map [r] = (int32_t) k ; stamp [r] = (int32_t) s ;
+            }
+            for (int64_t t = tcount [s] ; t < tcount [s+1] ; t++)
+            {
+                const int32_t pid = P.target_list [t] ;
+                const Pair &pr = pairs [pid] ;
+                P.pair_map [pid] = off ;
+                const int64_t *rows = Ls + pi [pr.d] + pr.lpos ;
+                for (int32_t i = 0 ; i < pr.ndrow2 ; i++)
+                {
+                    int64_t r = rows [i] ;
+                    if (stamp [r] != (int32_t) s) return B200_INVALID ;  // pattern of d not inside pattern of s
+                    P.relmap [off + i] = Map [r] ;
+                }
+                off += pr.ndrow2 ;
+            }
+        }
+    }
+
+    // flop counts of the dense factorizations
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        double nscol = (double) (super [s+1] - super [s]), nsrow = (double) (pi [s+1] - pi [s]) ;
+        P.flops_potrf += nscol * nscol * nscol / 3.0 ;
+        P.flops_trsm += nscol * nscol * (nsrow - nscol) ;
+    }
+
+    // the launch plan, level by level: (1) every descendant update whose target lives on the level,
+    // (2) the blocked factorization of the level's supernodes
+    TileSink sink ;
+    std::vector<int64_t> ncols ;
+    for (int lev = 0 ; lev < nlevels ; lev++)
+    {
+        const int32_t *S = P.level_list.data () + P.level_ptr [lev] ;
+        const int64_t ns = P.level_ptr [lev+1] - P.level_ptr [lev] ;
+        for (int64_t q = 0 ; q < ns ; q++) plan_updates_into (P, P, super, pi, px, S [q], sink, use_dmma) ;
+        flush_tiles (P, sink, lev) ;
+        ncols.resize ((size_t) ns) ;
+        for (int64_t q = 0 ; q < ns ; q++) ncols [q] = super [S [q] + 1] - super [S [q]] ;
+        plan_factor (P, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma) ;
+    }
+    if (P.items.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;
+    return B200_OK ;
+}
+
+int build_repair_plan (const Plan &P, const int64_t *super, const int64_t *pi, const int64_t *px,
+    int64_t s, int64_t nscol_new, bool use_dmma, Plan &R)
+{
+    R = Plan () ;
+    R.n = P.n ; R.nsuper = P.nsuper ; R.xsize = P.xsize ; R.ssize = P.ssize ;
+    if (s < 0 || s >= P.nsuper || nscol_new < 0 || nscol_new > super [s+1] - super [s]) return B200_INVALID ;
+    TileSink sink ;
+    plan_updates_into (R, P, super, pi, px, s, sink, use_dmma) ;
+    flush_tiles (R, sink, P.level [s]) ;
+    const int32_t S [1] = { (int32_t) s } ;
+    const int64_t nc [1] = { nscol_new } ;
+    if (nscol_new > 0) plan_factor (R, super, pi, px, S, nc, 1, P.level [s], sink, use_dmma) ;
+    return B200_OK ;
+}
+
+}   // namespace b200

@@ -1,0 +1,118 @@
+// plan.hpp -- host-side launch plan of the CHOLMOD/B200 numeric phase.
+//
+// Everything the reference recomputes per factorization that depends only on the symbolic factor
+// (CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c "SNW": descendant lists :531-551, ndrow1/ndrow2
+// :686-698, relative maps :897-903, re-linking :950-967, parent links :1222-1235) is computed here once
+// per analysis and turned into flat tables the kernels index directly.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace b200 {
+
+// One dense product  C (M x N) = A (M x K) * B (N x K)',  where B is the first N rows of A and only the
+// lower trapezoid (i >= j) of C is wanted.  It is subtracted from the factor:
+//   map_off >= 0 :  Lx [c_off + map [i] + map [j] * ldc] -= C (i,j)     (descendant -> ancestor update,
+//                   the dsyrk + dgemm + assembly of SNW:769-930; map = the pair's relative map)
+//   map_off <  0 :  Lx [c_off + i + j * ldc]             -= C (i,j)     (trailing update inside a supernode
+//                   during its blocked dpotrf/dtrsm, SNW:1023-1181)
+struct UpdItem
+{
+    int64_t a_off ;     // Lx offset of A (0,0); A is column-major with leading dimension lda
+    int64_t c_off ;     // Lx offset of the target (supernode origin px [s], or C (0,0) when direct)
+    int64_t map_off ;   // offset into the relative-map table, or -1
+    int32_t lda, ldc ;
+    int32_t M, N, K ;
+    int32_t pad ;
+} ;
+
+// One tile of one item: rows [ti*TM, ..), columns [tj*TN, ..), inner range [k0, k1).
+struct UpdTile
+{
+    int32_t item ;
+    uint16_t ti, tj ;
+    int32_t k0, k1 ;
+} ;
+
+// Diagonal block of a supernode to factorize in place (jb <= POTRF_NB), lower Cholesky.
+struct PotrfBlk
+{
+    int64_t off ;       // Lx offset of the block's (0,0)
+    int64_t col ;       // global column index of the block's first column (for L->minor)
+    int32_t lda, jb ;
+} ;
+
+// Rows below a factorized diagonal block:  X <- X * L11^{-T}   (the dtrsm of SNW:1175, R,L,C,N)
+struct TrsmTile
+{
+    int64_t diag_off ;  // Lx offset of L11 (0,0)
+    int64_t row_off ;   // Lx offset of X (0,0)
+    int32_t lda, jb, nrows, pad ;
+} ;
+
+enum LaunchKind : int32_t
+{
+    K_UPD_SIMT = 0,     // UpdTile list, 32 x 8 tiles, one warp each
+    K_UPD_D64  = 1,     // UpdTile list, 64 x 64 DMMA tiles
+    K_UPD_D128 = 2,     // UpdTile list, 128 x 128 DMMA tiles
+    K_POTRF    = 3,     // PotrfBlk list
+    K_TRSM     = 4,     // TrsmTile list
+} ;
+
+struct Launch
+{
+    int32_t kind ;
+    int32_t count ;     // number of list entries
+    int64_t first ;     // first entry in the kind's list
+    int32_t level ;     // etree level this launch belongs to
+    int32_t pad ;
+} ;
+
+constexpr int POTRF_NB   = 64 ;     // width of a block column factorized by one POTRF block
+constexpr int OUTER_NB   = 256 ;    // width of an outer block column (trailing updates with K = OUTER_NB)
+constexpr int TRSM_ROWS  = 128 ;    // rows per TRSM tile
+constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
+
+// One (descendant d, ancestor s) update: rows lpos.. of d; the first ndrow1 fall in the columns of s.
+struct Pair { int32_t d, s, lpos, ndrow1, ndrow2 ; } ;
+
+struct Plan
+{
+    int64_t n = 0, nsuper = 0, ssize = 0, xsize = 0 ;
+    int32_t nlevels = 0 ;
+    int64_t npairs = 0 ;
+    double flops_update = 0, flops_potrf = 0, flops_trsm = 0 ;
+    double flops_kind [5] = {0, 0, 0, 0, 0} ;   // algorithmic flops executed by each launch kind
+    int64_t count_kind [5] = {0, 0, 0, 0, 0} ;  // list entries (tiles / blocks) per launch kind
+
+    std::vector<int32_t> level ;        // [nsuper] height above the leaves in the supernodal etree
+    std::vector<int64_t> parent ;       // [nsuper] etree parent or -1
+    std::vector<int32_t> supermap ;     // [n] column -> supernode (cholmod_super_numeric.c:276-285)
+    std::vector<int32_t> relmap ;       // concatenated relative maps of all pairs
+    std::vector<UpdItem> items ;
+    std::vector<UpdTile> tiles ;
+    std::vector<PotrfBlk> potrf ;
+    std::vector<TrsmTile> trsm ;
+    std::vector<Launch> launches ;
+
+    std::vector<Pair> pairs ;           // all update pairs, in descendant order
+    std::vector<int64_t> pair_map ;     // [npairs] offset of the pair's relative map in relmap
+    std::vector<int64_t> target_ptr ;   // [nsuper+1] pairs grouped by target supernode ...
+    std::vector<int32_t> target_list ;  // ... as indices into pairs
+
+    // solve schedule: supernodes grouped by level (forward: ascending levels; backward: descending)
+    std::vector<int64_t> level_ptr ;    // [nlevels+1]
+    std::vector<int32_t> level_list ;   // [nsuper] supernodes sorted by level
+} ;
+
+// Builds the plan.  Returns 0, or a negative B200_* status (invalid input / too large).
+// use_dmma = false (single precision) routes every update through the SIMT kernel class.
+int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
+    const int64_t *Ls, bool use_dmma, Plan &plan) ;
+
+// SNW:1084-1146: a one-supernode plan that re-applies every descendant update to supernode s and then
+// factorizes only its first nscol_new columns (dtrsm on all rows below them).  Reuses P.relmap.
+int build_repair_plan (const Plan &P, const int64_t *super, const int64_t *pi, const int64_t *px,
+    int64_t s, int64_t nscol_new, bool use_dmma, Plan &R) ;
+
+}   // namespace b200

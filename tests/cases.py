@@ -1,0 +1,57 @@
+"""Shared helpers of the tests: build a reference session for a synthetic matrix, compare factors."""
+import functools
+
+import numpy as np
+
+from oracle import refd
+from suitesparse_b200 import matrices as M
+
+GEN = {"lap2d5": M.lap2d5, "lap2d9": M.lap2d9, "lap3d7": M.lap3d7, "el27": M.el27}
+
+
+def make_matrix(kind, size, shift_diag=None):
+    n, Ap, Ai, Ax = GEN[kind](size)
+    if shift_diag is not None:
+        # make the matrix indefinite: overwrite one diagonal entry (column k's first stored entry is the diagonal)
+        k, val = shift_diag
+        assert Ai[Ap[k]] == k
+        Ax = Ax.copy()
+        Ax[Ap[k]] = val
+    return n, Ap, Ai, Ax
+
+
+class Case:
+    """Reference analysis + seam matrix + reference CPU factor for one matrix."""
+
+    def __init__(self, kind, size, ordering, single=False, shift_diag=None, beta=0.0, factor=True):
+        self.kind, self.size, self.single, self.beta = kind, size, single, beta
+        self.n, self.Ap, self.Ai, self.Ax = make_matrix(kind, size, shift_diag)
+        self.ref = refd.Ref()
+        self.ref.set_matrix(self.n, self.Ap, self.Ai, self.Ax, -1, single=single)
+        self.ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
+        self.sym = self.ref.symbolic()
+        self.Sp, self.Si, self.Sx = self.ref.seam()
+        if factor:
+            self.status = self.ref.super_numeric(beta)
+            self.Lref = self.ref.Lx().copy()
+            self.minor = self.ref.geti("minor")
+
+    def rel_err(self, Lx):
+        """max |dL| / max |L| over the supernodal storage."""
+        Lx = np.asarray(Lx, dtype=np.float64)
+        Lr = self.Lref.astype(np.float64)
+        scale = np.max(np.abs(Lr))
+        return float(np.max(np.abs(Lx - Lr)) / (scale if scale > 0 else 1.0))
+
+    def residual_with(self, Lx):
+        """Push factor values through the reference's own cholmod_l_solve; the demo's scaled residual."""
+        host = self.ref.numeric_Lx()
+        host[:] = Lx
+        b = M.rhs(self.n)
+        x = self.ref.solve(b)
+        return self.ref.resid(x, b)
+
+
+@functools.lru_cache(maxsize=None)
+def get_case(kind, size, ordering, single=False, shift_diag=None, beta=0.0):
+    return Case(kind, size, ordering, single=single, shift_diag=shift_diag, beta=beta)

@@ -1,0 +1,112 @@
+"""Test-only numpy interpreter of the CHOLMOD/B200 launch plan.
+
+Executes the plan tables exported by `b200_plan_export` (UpdItem/UpdTile/PotrfBlk/TrsmTile/Launch, see
+suitesparse_b200/csrc/plan.hpp) with the semantics the CUDA kernels implement, so that the host planner
+(levels, pairs, relative maps, tiling, two-level blocking, split-K) can be checked on a machine without
+a GPU.  It is NOT a fallback: nothing in the product imports it.
+"""
+import numpy as np
+from numpy.lib.stride_tricks import as_strided
+
+from suitesparse_b200 import b200
+
+
+def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None):
+    """What k_scatter_A does (Lx already zero on the touched supernodes)."""
+    n = sym["n"]
+    klast = n if klast is None else klast
+    sup, pi, px, Ls = sym["super"], sym["pi"], sym["px"], sym["s"]
+    supermap = np.repeat(np.arange(sym["nsuper"]), np.diff(sup))
+    for k in range(kfirst, klast):
+        s = supermap[k]
+        k1, k2 = sup[s], sup[s + 1]
+        nsrow = pi[s + 1] - pi[s]
+        rows = Ls[pi[s]:pi[s + 1]]
+        base = px[s] + (k - k1) * nsrow
+        for p in range(Sp[k], Sp[k + 1]):
+            i = Si[p]
+            if i < k:
+                continue
+            if i < k2:
+                pos = i - k1
+            else:
+                pos = np.searchsorted(rows, i)
+                if pos >= nsrow or rows[pos] != i:
+                    continue
+            Lx[base + pos] = Sx[p]
+        if beta != 0:
+            Lx[base + (k - k1)] += beta
+
+
+def _view(Lx, off, rows, cols, ld):
+    return as_strided(Lx[off:], shape=(rows, cols), strides=(Lx.itemsize, ld * Lx.itemsize), writeable=True)
+
+
+def run_plan(F, Lx, tables=None):
+    """Execute every launch of Factor F's plan on the flat factor array Lx.  Returns the smallest failing
+    column (what the kernels record through atomicMin) or None."""
+    if tables is None:
+        tables = dict(items=F.plan_table("items", b200.ITEM_DT), tiles=F.plan_table("tiles", b200.TILE_DT),
+                      potrf=F.plan_table("potrf", b200.POTRF_DT), trsm=F.plan_table("trsm", b200.TRSM_DT),
+                      launches=F.plan_table("launches", b200.LAUNCH_DT), relmap=F.plan_table("relmap", np.int32))
+    items, tiles, potrf, trsm = tables["items"], tables["tiles"], tables["potrf"], tables["trsm"]
+    relmap = tables["relmap"]
+    minor = None
+    for L in tables["launches"]:
+        kind, cnt, first = int(L["kind"]), int(L["count"]), int(L["first"])
+        if kind in b200.TILE_SHAPE:
+            TM, TN = b200.TILE_SHAPE[kind]
+            # all tiles of a launch read operands that no tile of the same launch writes: gather the
+            # products first, then apply them
+            pending = []
+            for t in tiles[first:first + cnt]:
+                it = items[t["item"]]
+                M, N, lda = int(it["M"]), int(it["N"]), int(it["lda"])
+                i0, j0 = int(t["ti"]) * TM, int(t["tj"]) * TN
+                i1, j1 = min(M, i0 + TM), min(N, j0 + TN)
+                assert i0 < M and j0 < N and i1 - 1 >= j0, "tile outside the lower trapezoid"
+                k0, k1 = int(t["k0"]), int(t["k1"])
+                assert 0 <= k0 < k1 <= it["K"]
+                A = _view(Lx, int(it["a_off"]), M, int(it["K"]), lda)
+                Cpart = A[i0:i1, k0:k1] @ A[j0:j1, k0:k1].T
+                ii, jj = np.meshgrid(np.arange(i0, i1), np.arange(j0, j1), indexing="ij")
+                keep = ii >= jj
+                if it["map_off"] >= 0:
+                    m = relmap[int(it["map_off"]):int(it["map_off"]) + M].astype(np.int64)
+                    dst = int(it["c_off"]) + m[ii[keep]] + m[jj[keep]] * int(it["ldc"])
+                else:
+                    dst = int(it["c_off"]) + ii[keep] + jj[keep] * int(it["ldc"])
+                pending.append((dst, Cpart[keep]))
+            for dst, val in pending:
+                np.subtract.at(Lx, dst, val)
+        elif kind == b200.K_POTRF:
+            for b in potrf[first:first + cnt]:
+                jb, lda = int(b["jb"]), int(b["lda"])
+                D = _view(Lx, int(b["off"]), jb, jb, lda)
+                Dl = np.tril(D)
+                Dsym = Dl + np.tril(Dl, -1).T
+                # unblocked right-looking Cholesky with the kernel's failure rule
+                Lc = Dsym.copy()
+                for j in range(jb):
+                    d = Lc[j, j]
+                    if not d > 0:
+                        col = int(b["col"]) + j
+                        minor = col if minor is None else min(minor, col)
+                    with np.errstate(all="ignore"):
+                        ljj = np.sqrt(d)
+                        Lc[j:, j] = Lc[j:, j] / ljj
+                        Lc[j, j] = ljj
+                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
+                r, c = np.tril_indices(jb)
+                D[r, c] = Lc[r, c]
+        elif kind == b200.K_TRSM:
+            for t in trsm[first:first + cnt]:
+                jb, lda, nr = int(t["jb"]), int(t["lda"]), int(t["nrows"])
+                L11 = np.tril(_view(Lx, int(t["diag_off"]), jb, jb, lda))
+                X = _view(Lx, int(t["row_off"]), nr, jb, lda)
+                with np.errstate(all="ignore"):
+                    X[:, :] = np.linalg.solve(L11, X.T).T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
+                        else np.full_like(X, np.nan)
+        else:
+            raise AssertionError("unknown launch kind %d" % kind)
+    return minor

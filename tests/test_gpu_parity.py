@@ -1,0 +1,185 @@
+"""GPU parity tests: the CUDA numeric phase, called through the C ABI, against the oracle on the same
+inputs.  Tolerances are BASELINE.json's: factor values max|dL|/max|L| <= 1e-10 (double), scaled residual
+||Ax-b||/(||A|| ||x|| + ||b||) <= 1e-12; symbolic structure is shared with the reference (same host
+analysis) and therefore identical by construction.  Single precision uses 1e-4 / 1e-5."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import refd
+from suitesparse_b200 import b200, matrices as M
+from cases import Case, get_case
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOL_L, TOL_RES = 1e-10, 1e-12
+
+
+def unpermute(sym, xperm):
+    x = np.empty_like(xperm)
+    x[sym["Perm"]] = xperm
+    return x
+
+
+@pytest.mark.parametrize("kind,size,ordering", [
+    ("lap2d5", 100, refd.CHOLMOD_AMD),          # config 1
+    ("lap3d7", 16, refd.CHOLMOD_METIS),
+    ("lap3d7", 40, refd.CHOLMOD_METIS),         # the survey's extra case: root ~ 1.6k columns
+    ("lap2d9", 200, refd.CHOLMOD_METIS),        # config 5 shape, reduced
+    ("el27", 12, refd.CHOLMOD_METIS),           # config 3 shape, reduced
+    ("lap2d5", 17, refd.CHOLMOD_NATURAL),
+])
+def test_factor_matches_reference(kind, size, ordering):
+    c = get_case(kind, size, ordering)
+    F = b200.Factor(c.sym, device=0)
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
+    assert st == b200.OK and F.minor == c.n
+    assert F.geti("kernel_launches") > 0
+    assert c.rel_err(Lx) <= TOL_L
+    # the strict upper triangles of the diagonal blocks stay zero like the reference's (SNW:361-379)
+    assert np.array_equal(Lx == 0, c.Lref == 0) or np.count_nonzero((Lx == 0) != (c.Lref == 0)) < 1e-6 * Lx.size
+    # reference solve on our factor, and our device solve
+    assert c.residual_with(Lx) <= TOL_RES
+    b = M.rhs(c.n)
+    x = unpermute(c.sym, F.solve(b[c.sym["Perm"]]))
+    assert c.ref.resid(x, b) <= TOL_RES
+    F.close()
+
+
+def test_golden_fixtures_on_gpu():
+    for f in sorted(glob.glob(os.path.join(HERE, "golden", "*.npz"))):
+        g = np.load(f)
+        sym = dict(n=int(g["n"]), nsuper=int(g["nsuper"]), xsize=int(g["xsize"]), super=g["super"], pi=g["pi"],
+                   px=g["px"], s=g["s"])
+        F = b200.Factor(sym, device=0)
+        st, Lx = F.super_numeric(g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]))
+        assert st == int(g["status"]) and F.minor == int(g["minor"]), f
+        Lref = g["Lx"]
+        assert np.max(np.abs(Lx - Lref)) <= TOL_L * max(1.0, np.max(np.abs(Lref))), f
+        assert np.array_equal(Lx == 0, Lref == 0), f
+        F.close()
+
+
+def test_port_agrees_too():
+    c = get_case("lap3d7", 16, refd.CHOLMOD_METIS)
+    st, minor, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx)
+    F = b200.Factor(c.sym, device=0)
+    _, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
+    assert np.max(np.abs(Lx - Lp)) <= TOL_L * np.max(np.abs(Lp))
+    F.close()
+
+
+def test_beta_and_refactorization():
+    """One analysis, several numeric factorizations with new values (cholmod_factorize.c:67-70)."""
+    c = get_case("lap2d9", 60, refd.CHOLMOD_METIS)
+    F = b200.Factor(c.sym, device=0)
+    for scale, beta in [(1.0, 0.0), (2.5, 0.0), (1.0, 0.75)]:
+        st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx * scale, beta=beta)
+        stp, _, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx * scale, beta=beta)
+        assert st == stp == 0
+        assert np.max(np.abs(Lx - Lp)) <= TOL_L * np.max(np.abs(Lp))
+    F.close()
+
+
+def test_unpacked_unsorted_and_extra_entries():
+    """The seam accepts unpacked (A->nz) and unsorted columns, ignores the strictly upper part and
+    entries outside the pattern of L (SNW:449-468)."""
+    c = get_case("lap2d5", 30, refd.CHOLMOD_AMD)
+    n, Sp, Si, Sx = c.n, c.Sp, c.Si, c.Sx
+    rng = np.random.default_rng(7)
+    cnt = np.diff(Sp)
+    Up = np.zeros(n + 1, dtype=np.int64)
+    Up[1:] = np.cumsum(cnt + 3)                          # 3 slack slots per column
+    Ui = np.full(Up[-1], 0, dtype=np.int64)
+    Ux = np.full(Up[-1], 123.0)
+    Unz = np.zeros(n, dtype=np.int64)
+    for k in range(n):
+        rows, vals = Si[Sp[k]:Sp[k + 1]], Sx[Sp[k]:Sp[k + 1]]
+        extra_r, extra_v = [], []
+        if k > 0:
+            extra_r.append(k - 1); extra_v.append(55.0)  # strictly upper entry: ignored
+        perm = rng.permutation(len(rows) + len(extra_r))
+        rr = np.concatenate([rows, extra_r]).astype(np.int64)[perm]
+        vv = np.concatenate([vals, extra_v])[perm]
+        Ui[Up[k]:Up[k] + len(rr)] = rr
+        Ux[Up[k]:Up[k] + len(rr)] = vv
+        Unz[k] = len(rr)
+    F = b200.Factor(c.sym, device=0)
+    st, Lx = F.super_numeric(Up, Ui, Ux, Anz=Unz)
+    assert st == 0 and c.rel_err(Lx) <= TOL_L
+    stp, _, Lp = refd.port_factor(c.sym, Up, Ui, Ux, Snz=Unz)
+    assert stp == 0 and np.max(np.abs(Lx - Lp)) <= TOL_L * np.max(np.abs(Lp))
+    F.close()
+
+
+@pytest.mark.parametrize("col,quick", [(0, False), (37, False), (37, True), (250, False), (399, False)])
+def test_not_posdef_semantics(col, quick):
+    """status, L->minor, the zeroed tail and the partially factorized supernode of SNW:1084-1146."""
+    c = Case("lap2d5", 20, refd.CHOLMOD_AMD, shift_diag=(col, -1.0), factor=False)
+    c.ref.seti("quick_return_if_not_posdef", int(quick))
+    assert c.ref.super_numeric(0.0) == refd.CHOLMOD_NOT_POSDEF
+    Lref, minor_ref = c.ref.Lx().copy(), c.ref.geti("minor")
+    F = b200.Factor(c.sym, device=0)
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx, quick_return=quick)
+    assert st == b200.NOT_POSDEF and F.minor == minor_ref
+    assert np.array_equal(Lx == 0, Lref == 0)
+    assert np.max(np.abs(Lx - Lref)) <= TOL_L * max(1.0, np.max(np.abs(Lref)))
+    # the context is still usable afterwards
+    good = get_case("lap2d5", 20, refd.CHOLMOD_AMD)
+    st, Lx = F.super_numeric(good.Sp, good.Si, good.Sx)
+    assert st == b200.OK and good.rel_err(Lx) <= TOL_L
+    F.close()
+
+
+def test_single_precision():
+    c = Case("lap3d7", 14, refd.CHOLMOD_METIS, single=True)
+    F = b200.Factor(c.sym, dtype=np.float32, device=0)
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
+    assert st == 0 and Lx.dtype == np.float32
+    assert c.rel_err(Lx) <= 1e-4
+    b = M.rhs(c.n)
+    x = unpermute(c.sym, F.solve(b[c.sym["Perm"]]))
+    assert c.ref.resid(x, b) <= 1e-5
+    F.close()
+
+
+def test_device_resident_steps_and_multi_rhs_solve():
+    c = get_case("lap3d7", 16, refd.CHOLMOD_METIS)
+    F = b200.Factor(c.sym, device=0)
+    F.upload_matrix(c.Sp, c.Si, c.Sx)
+    assert F.factor_device() == b200.OK
+    assert F.getd("ms_factor") > 0
+    Lx = F.download_factor()
+    assert c.rel_err(Lx) <= TOL_L
+    B = np.asfortranarray(np.stack([M.rhs(c.n), np.ones(c.n), np.cos(np.arange(c.n))], axis=1))
+    Xp = F.solve(B[c.sym["Perm"], :])
+    for j in range(B.shape[1]):
+        assert c.ref.resid(unpermute(c.sym, Xp[:, j].copy()), B[:, j].copy()) <= TOL_RES
+    # solve with a factor computed elsewhere (the reference's), uploaded into the arena
+    F.upload_factor(c.Lref)
+    x = unpermute(c.sym, F.solve(M.rhs(c.n)[c.sym["Perm"]]))
+    assert c.ref.resid(x, M.rhs(c.n)) <= TOL_RES
+    F.close()
+
+
+def test_full_size_properties_config2_shape():
+    """A size the plain-C oracle cannot finish quickly (lap3d7 64^3, n = 262k): size-independent
+    properties instead -- solve residual with our own factor, and L L' x = A x for a random x."""
+    n, Ap, Ai, Ax = M.lap3d7(64)
+    ref = refd.Ref()
+    ref.set_matrix(n, Ap, Ai, Ax, -1)
+    ref.analyze(refd.CHOLMOD_METIS, refd.CHOLMOD_SUPERNODAL)
+    sym = ref.symbolic()
+    Sp, Si, Sx = ref.seam()
+    F = b200.Factor(sym, device=0)
+    st, Lx = F.super_numeric(Sp, Si, Sx)
+    assert st == b200.OK and np.all(np.isfinite(Lx))
+    b = M.rhs(n)
+    x = unpermute(sym, F.solve(b[sym["Perm"]]))
+    assert ref.resid(x, b) <= TOL_RES
+    host = ref.numeric_Lx()
+    host[:] = Lx
+    assert ref.resid(ref.solve(b), b) <= TOL_RES
+    F.close()

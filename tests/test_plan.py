@@ -1,0 +1,135 @@
+"""CPU tests of the host side of CHOLMOD/B200: the C ABI loads and exports every declared symbol, the
+planner's tables reproduce the reference factor when executed by the numpy interpreter
+(tests/plan_interp.py), and a context without a device refuses to compute (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import refd
+from suitesparse_b200 import b200
+from cases import Case, get_case
+import plan_interp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+needs_ref = pytest.mark.skipif(not refd.have_ref(), reason="oracle/_ref/libref_driver.so not built")
+
+
+def test_abi_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "cholmod_b200.h")).read()
+    declared = set(re.findall(r"\b(b200_[A-Za-z0-9_]+)\s*\(", hdr))
+    assert declared == set(b200.SYMBOLS), declared ^ set(b200.SYMBOLS)
+    L = C.CDLL(b200.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in b200.lib().b200_version()
+
+
+def test_library_is_sm100a_only():
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", b200.LIB_PATH], stdout=subprocess.PIPE, text=True).stdout
+    if not out.strip():
+        pytest.skip("cuobjdump not available")
+    assert "sm_100a" in out and not re.search(r"sm_(?!100a)\d+", out), out
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,size,ordering", [("lap2d5", 40, refd.CHOLMOD_AMD), ("lap3d7", 12, refd.CHOLMOD_METIS),
+                                                ("lap2d9", 30, refd.CHOLMOD_METIS), ("el27", 7, refd.CHOLMOD_METIS),
+                                                ("lap3d7", 22, refd.CHOLMOD_METIS)])
+def test_plan_reproduces_reference_factor(kind, size, ordering):
+    c = get_case(kind, size, ordering)
+    F = b200.Factor(c.sym, device=-1)
+    Lx = np.zeros(c.sym["xsize"])
+    plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
+    minor = plan_interp.run_plan(F, Lx)
+    assert minor is None
+    assert c.rel_err(Lx) <= 1e-12
+    # the plan's flop count is the supernodal formula of SURVEY.md 8d: never below Common->fl's leading terms
+    assert F.getd("flops_executed") > 0
+    F.close()
+
+
+@needs_ref
+def test_plan_structure():
+    c = get_case("lap3d7", 22, refd.CHOLMOD_METIS)
+    F = b200.Factor(c.sym, device=-1)
+    level = F.plan_table("level", np.int32)
+    parent = F.plan_table("parent", np.int64)
+    assert level.size == c.sym["nsuper"] and F.geti("nlevels") == level.max() + 1
+    has_parent = parent >= 0
+    assert np.all(level[parent[has_parent]] > level[has_parent])
+    assert np.all(parent[has_parent] > np.nonzero(has_parent)[0])          # postordered
+    launches = F.plan_table("launches", b200.LAUNCH_DT)
+    assert np.all(np.diff(launches["level"]) >= 0)                           # level by level
+    items = F.plan_table("items", b200.ITEM_DT)
+    tiles = F.plan_table("tiles", b200.TILE_DT)
+    assert tiles["item"].max() < items.size
+    # every pair's relative map addresses rows inside its target supernode
+    relmap = F.plan_table("relmap", np.int32)
+    mapped = items[items["map_off"] >= 0]
+    assert mapped.size == F.geti("npairs")
+    for it in mapped[:: max(1, mapped.size // 200)]:
+        m = relmap[it["map_off"]:it["map_off"] + it["M"]]
+        assert np.all(np.diff(m) > 0) and m[-1] < it["ldc"]
+    # a wide supernode exercises the two-level blocking and the DMMA tile classes
+    assert np.diff(c.sym["super"]).max() > 256
+    kinds = set(launches["kind"].tolist())
+    assert {b200.K_POTRF, b200.K_TRSM, b200.K_UPD_SIMT} <= kinds and (b200.K_UPD_D64 in kinds or b200.K_UPD_D128 in kinds)
+    F.close()
+
+
+def test_plan_rejects_bad_symbolic():
+    sym = dict(n=4, nsuper=2, super=np.array([0, 2, 4]), pi=np.array([0, 3, 5]), px=np.array([0, 6, 10]),
+               s=np.array([0, 1, 3, 2, 3]))
+    F = b200.Factor(sym, device=-1)                 # valid: supernode 0 = cols 0-1 rows {0,1,3}; 1 = cols 2-3
+    assert F.geti("npairs") == 1 and F.geti("nlevels") == 2
+    F.close()
+    bad = dict(sym, px=np.array([0, 5, 9]))
+    with pytest.raises(b200.B200Error) as e:
+        b200.Factor(bad, device=-1)
+    assert e.value.status == b200.INVALID
+    bad = dict(sym, s=np.array([0, 1, 1, 2, 3]))   # parent row inside the supernode itself
+    with pytest.raises(b200.B200Error):
+        b200.Factor(bad, device=-1)
+
+
+def test_empty_matrix_plan():
+    sym = dict(n=0, nsuper=0, super=np.array([0]), pi=np.array([0]), px=np.array([0]), s=np.zeros(0, dtype=np.int64))
+    F = b200.Factor(sym, device=-1)
+    assert F.geti("nlaunches") == 0 and F.geti("xsize") == 0
+    F.close()
+
+
+def test_no_cpu_fallback():
+    """A context without a device must fail loudly instead of computing on the host."""
+    sym = dict(n=4, nsuper=2, super=np.array([0, 2, 4]), pi=np.array([0, 3, 5]), px=np.array([0, 6, 10]),
+               s=np.array([0, 1, 3, 2, 3]))
+    F = b200.Factor(sym, device=-1)
+    Ap = np.array([0, 1, 2, 3, 4]); Ai = np.arange(4); Ax = np.ones(4)
+    with pytest.raises(b200.B200Error) as e:
+        F.super_numeric(Ap, Ai, Ax)
+    assert e.value.status == b200.GPU_PROBLEM
+    with pytest.raises(b200.B200Error):
+        F.solve(np.ones(4))
+    F.close()
+    if b200.device_count() == 0:
+        with pytest.raises(b200.B200Error) as e:
+            b200.Factor(sym, device=0)
+        assert e.value.status == b200.GPU_PROBLEM
+
+
+@needs_ref
+def test_repair_plan_semantics_match_reference_notposdef():
+    """The not-positive-definite path of the executor (zero tail, rebuild supernode s, factor info-1
+    columns) restated with the interpreter agrees with the reference's L, zero pattern and L->minor."""
+    c = Case("lap2d5", 20, refd.CHOLMOD_AMD, shift_diag=(250, -1.0))
+    assert c.status == refd.CHOLMOD_NOT_POSDEF
+    F = b200.Factor(c.sym, device=-1)
+    Lx = np.zeros(c.sym["xsize"])
+    plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
+    minor = plan_interp.run_plan(F, Lx)
+    assert minor == c.minor
+    F.close()
