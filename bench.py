@@ -246,8 +246,7 @@ def main():
     F.factor_device()
     F.seti("profile", 0)
     kinds = {}
-    names = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf", "trsm"]
-    for k, nm in enumerate(names):
+    for k, nm in enumerate(b200.KIND_NAMES):
         kinds[nm] = {"ms": F.getd("ms_kind%d" % k), "launches": F.geti("launches_kind%d" % k),
                      "gflop": F.getd("flops_kind%d" % k) / 1e9}
     dom = max(("upd_dmma128", "upd_dmma64"), key=lambda nm: kinds[nm]["ms"])

@@ -206,9 +206,13 @@ class Factor:
 ITEM_DT = np.dtype([("a_off", "<i8"), ("c_off", "<i8"), ("map_off", "<i8"), ("lda", "<i4"), ("ldc", "<i4"),
                     ("M", "<i4"), ("N", "<i4"), ("K", "<i4"), ("pad", "<i4")])
 TILE_DT = np.dtype([("item", "<i4"), ("ti", "<u2"), ("tj", "<u2"), ("k0", "<i4"), ("k1", "<i4")])
-POTRF_DT = np.dtype([("off", "<i8"), ("col", "<i8"), ("lda", "<i4"), ("jb", "<i4")])
+POTRF_DT = np.dtype([("off", "<i8"), ("col", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("slot", "<i4"), ("pad", "<i4")])
 TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("nrows", "<i4"),
-                    ("pad", "<i4")])
+                    ("slot", "<i4")])
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("pad", "<i4")])
-K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF, K_TRSM = 0, 1, 2, 3, 4
+K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
+K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
+K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)
+KIND_NAMES = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf16", "potrf32", "potrf64", "trsm_subst", "trsm_inv32",
+              "trsm_inv64"]
 TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 128)}

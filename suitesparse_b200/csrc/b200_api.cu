@@ -60,6 +60,7 @@ struct b200_factor
     DevBuf<int64_t> d_Ap, d_Ai, d_Anz ;
     DevBuf<unsigned char> d_Ax ;
     DevBuf<unsigned long long> d_minor ;
+    DevBuf<unsigned char> d_winv ;          // scratch: inverses of the diagonal blocks of one launch
     DevBuf<double> d_X ;
     bool have_A = false, A_unpacked = false ;
     int64_t A_nz = 0 ;
@@ -69,8 +70,8 @@ struct b200_factor
     int64_t kernel_launches = 0 ;
     int profile = 0 ;                       // 1: bracket every launch with events (diagnostic runs only)
     std::vector<cudaEvent_t> prof_ev ;
-    double ms_kind [5] = {0, 0, 0, 0, 0} ;
-    int64_t launches_kind [5] = {0, 0, 0, 0, 0} ;
+    double ms_kind [K_NKINDS] = {} ;
+    int64_t launches_kind [K_NKINDS] = {} ;
     float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
     size_t device_bytes = 0 ;
 } ;
@@ -102,6 +103,10 @@ int kernel_attrs (int device)
         (int) dmma_smem_bytes<128, 128> ()), "attr d128") ;
     CK (cudaFuncSetAttribute (k_upd_dmma<64, 64, 32, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) dmma_smem_bytes<64, 64> ()), "attr d64") ;
+    CK (cudaFuncSetAttribute (k_trsm_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) trsm_inv_smem_bytes<32> ()), "attr trsm_inv32") ;
+    CK (cudaFuncSetAttribute (k_trsm_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) trsm_inv_smem_bytes<64> ()), "attr trsm_inv64") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
@@ -116,8 +121,10 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     const PotrfBlk *potrf, const TrsmTile *trsm, const int32_t *relmap)
 {
     T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
+    T *winv = reinterpret_cast<T *> (f->d_winv.p) ;
     cudaStream_t st = f->stream ;
     size_t nev = 0 ;
+    if ((size_t) P.winv_slots * WINV_LD * WINV_LD * sizeof (T) > f->d_winv.n) return B200_INVALID ;
     if (f->profile)
     {
         while (f->prof_ev.size () < 2 * P.launches.size ())
@@ -150,11 +157,27 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                 k_upd_dmma<128, 128, 32, 64><<<(unsigned) L.count, 256, dmma_smem_bytes<128, 128> (), st>>>
                     (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
                 break ;
-            case K_POTRF:
-                k_potrf<T><<<(unsigned) L.count, 256, 0, st>>> (potrf + L.first, Lx, f->d_minor.p) ;
+            case K_POTRF16:
+                k_potrf<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
+                break ;
+            case K_POTRF32:
+                k_potrf<T, 32><<<(unsigned) ((L.count + 1) / 2), 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
+                break ;
+            case K_POTRF64:
+                k_potrf<T, 64><<<(unsigned) L.count, 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
                 break ;
             case K_TRSM:
                 k_trsm<T><<<(unsigned) L.count, TRSM_ROWS, 0, st>>> (trsm + L.first, Lx) ;
+                break ;
+            case K_TRSM_INV32:
+                if (sizeof (T) != 8) return B200_INVALID ;
+                k_trsm_inv<32><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<32> (), st>>>
+                    (trsm + L.first, reinterpret_cast<double *> (Lx), reinterpret_cast<const double *> (winv)) ;
+                break ;
+            case K_TRSM_INV64:
+                if (sizeof (T) != 8) return B200_INVALID ;
+                k_trsm_inv<64><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<64> (), st>>>
+                    (trsm + L.first, reinterpret_cast<double *> (Lx), reinterpret_cast<const double *> (winv)) ;
                 break ;
             default:
                 return B200_INVALID ;
@@ -320,11 +343,12 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     ok = ok && f->d_trsm.upload (P.trsm, s) == cudaSuccess ;
     ok = ok && f->d_Lx.alloc ((size_t) P.xsize * f->esize) == cudaSuccess ;
     ok = ok && f->d_minor.alloc (1) == cudaSuccess ;
+    ok = ok && f->d_winv.alloc ((size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize) == cudaSuccess ;
     if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
     CK (cudaStreamSynchronize (s), "upload symbolic") ;
     f->device_bytes = f->d_super.bytes () + f->d_pi.bytes () + f->d_px.bytes () + f->d_Ls.bytes ()
         + f->d_supermap.bytes () + f->d_relmap.bytes () + f->d_level_list.bytes () + f->d_items.bytes ()
-        + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () ;
+        + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () + f->d_winv.bytes () ;
     return B200_OK ;
 }
 
@@ -369,7 +393,7 @@ void b200_destroy (b200_factor *f)
         f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
-        f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ;
+        f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
         cudaStreamDestroy (f->stream) ;
@@ -394,14 +418,15 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "npotrf")) return (int64_t) P.potrf.size () ;
     if (!strcmp (name, "ntrsm")) return (int64_t) P.trsm.size () ;
     if (!strcmp (name, "nlaunches")) return (int64_t) P.launches.size () ;
+    if (!strcmp (name, "winv_slots")) return P.winv_slots ;
     if (!strcmp (name, "device_bytes")) return (int64_t) f->device_bytes ;
     if (!strcmp (name, "device")) return f->device ;
     if (!strcmp (name, "dtype")) return f->dtype ;
     if (!strcmp (name, "kernel_launches")) return f->kernel_launches ;
     if (!strcmp (name, "ngpus")) return f->device >= 0 ? 1 : 0 ;
     if (!strcmp (name, "profile")) return f->profile ;
-    if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] <= '4') return f->launches_kind [name [13] - '0'] ;
-    if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] <= '4') return P.count_kind [name [10] - '0'] ;
+    if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] < '0' + K_NKINDS) return f->launches_kind [name [13] - '0'] ;
+    if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.count_kind [name [10] - '0'] ;
     return -1 ;
 }
 
@@ -425,8 +450,8 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_d2h")) return f->ms_d2h ;
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
-    if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '4') return f->ms_kind [name [7] - '0'] ;
-    if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] <= '4') return P.flops_kind [name [10] - '0'] ;
+    if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.flops_kind [name [10] - '0'] ;
     return -1 ;
 }
 
@@ -493,7 +518,7 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     cudaStream_t s = f->stream ;
     const unsigned long long big = ~0ull ;
     f->kernel_launches = 0 ;
-    for (int k = 0 ; k < 5 ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
+    for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
     CK (cudaEventRecord (f->ev [2], s), "record") ;
     CK (cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, s), "minor init") ;
     if (P.xsize > 0) CK (cudaMemsetAsync (f->d_Lx.p, 0, (size_t) P.xsize * sizeof (T), s), "memset Lx") ;

@@ -4,8 +4,9 @@
 //   k_upd_simt    small descendant updates, one warp per 32x8 tile                  (SNW:769-930)
 //   k_upd_dmma    descendant / trailing updates on the FP64 tensor pipe (DMMA),
 //                 cp.async-staged shared-memory tiles, fused relative-map scatter    (SNW:769-930)
-//   k_potrf       dense Cholesky of one <=64-wide diagonal block per CTA             (SNW:1023)
-//   k_trsm        X <- X * L11^{-T} for 128 rows per CTA                             (SNW:1175)
+//   k_potrf       dense Cholesky (+ inverse) of <=64-wide diagonal blocks, row per thread (SNW:1023)
+//   k_trsm        X <- X * L11^{-T} by substitution, one thread per row                (SNW:1175)
+//   k_trsm_inv    X <- X * W', W = L11^{-1}, on the FP64 tensor pipe                   (SNW:1175)
 //   k_solve_*     supernodal forward / backward solve                               (SSOL:20-586)
 //
 // "SNW" = CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c, "SSOL" = t_cholmod_super_solve_worker.c.
@@ -182,25 +183,42 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
         for (int m = tid ; m < TN ; m += NT) smap_c [m] = (m < nB) ? (mapped ? map [j0 + m] : j0 + m) : 0 ;
     }
 
-    auto load_stage = [&] (int kt, int buf)
+    // Global -> shared staging.  Thread `tid` always copies the same tile row lm and the k columns
+    // lk, lk + KPP, ... of a stage, so its source pointer just advances by a constant number of
+    // columns; stages are requested in increasing k order.  A predicated-off copy has src-size 0
+    // (zero fill, nothing is read).
+    static_assert (NT % TM == 0 && NT % TN == 0, "thread count must be a multiple of the tile edges") ;
+    constexpr int KPP_A = NT / TM, KPP_B = NT / TN ;
+    const int lmA = tid % TM, lkA = tid / TM, lmB = tid % TN, lkB = tid / TN ;
+    const bool rokA = lmA < mA, rokB = lmB < nB ;
+    const double *gA = Arow + lmA + (int64_t) (kbeg + lkA) * lda ;
+    const double *gB = Brow + lmB + (int64_t) (kbeg + lkB) * lda ;
+    const int64_t stepA = (int64_t) KPP_A * lda, stepB = (int64_t) KPP_B * lda ;
+    const unsigned sA0 = (unsigned) __cvta_generic_to_shared (sA) + (unsigned) ((lkA * LDA_S + lmA) * 8) ;
+    const unsigned sB0 = (unsigned) __cvta_generic_to_shared (sB) + (unsigned) ((lkB * LDB_S + lmB) * 8) ;
+    int kleft = kend - kbeg ;           // columns not yet requested
+    auto load_stage = [&] (int buf)
     {
-        const int kb = kbeg + kt * DM_KC ;
-        double *dA = sA + buf * DM_KC * LDA_S ;
-        double *dB = sB + buf * DM_KC * LDB_S ;
+        const unsigned dA = sA0 + (unsigned) (buf * DM_KC * LDA_S * 8) ;
+        const unsigned dB = sB0 + (unsigned) (buf * DM_KC * LDB_S * 8) ;
+        const double *pa = gA, *pb = gB ;
         #pragma unroll
-        for (int e = tid ; e < DM_KC * TM ; e += NT)
+        for (int i = 0 ; i < DM_KC / KPP_A ; i++)
         {
-            int m = e % TM, k = e / TM ;
-            bool ok = (m < mA) && (kb + k < kend) ;
-            cp_async8 (dA + k * LDA_S + m, ok ? (const void *) (Arow + m + (int64_t) (kb + k) * lda) : (const void *) A, ok) ;
+            int sz = (rokA && (lkA + i * KPP_A < kleft)) ? 8 : 0 ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], 8, %2;\n"
+                :: "r" (dA + (unsigned) (i * KPP_A * LDA_S * 8)), "l" (pa), "r" (sz)) ;
+            pa += stepA ;
         }
         #pragma unroll
-        for (int e = tid ; e < DM_KC * TN ; e += NT)
+        for (int i = 0 ; i < DM_KC / KPP_B ; i++)
         {
-            int m = e % TN, k = e / TN ;
-            bool ok = (m < nB) && (kb + k < kend) ;
-            cp_async8 (dB + k * LDB_S + m, ok ? (const void *) (Brow + m + (int64_t) (kb + k) * lda) : (const void *) A, ok) ;
+            int sz = (rokB && (lkB + i * KPP_B < kleft)) ? 8 : 0 ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], 8, %2;\n"
+                :: "r" (dB + (unsigned) (i * KPP_B * LDB_S * 8)), "l" (pb), "r" (sz)) ;
+            pb += stepB ;
         }
+        gA = pa ; gB = pb ; kleft -= DM_KC ;
     } ;
 
     double acc [MT][NTL][2] ;
@@ -215,23 +233,24 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
     #pragma unroll
     for (int s = 0 ; s < DM_STAGES - 1 ; s++)
     {
-        if (s < nk) load_stage (s, s) ;
+        if (s < nk) load_stage (s) ;
         cp_async_commit () ;
     }
     const int fk = lane & 3, fm = lane >> 2 ;
+    int cbuf = 0, lbuf = DM_STAGES - 1 ;        // buffer being computed on / being filled
     for (int kt = 0 ; kt < nk ; kt++)
     {
         cp_async_wait<DM_STAGES - 2> () ;
         __syncthreads () ;
-        {
-            int nxt = kt + DM_STAGES - 1 ;
-            if (nxt < nk) load_stage (nxt, nxt % DM_STAGES) ;
-            cp_async_commit () ;
-        }
+        if (kt + DM_STAGES - 1 < nk) load_stage (lbuf) ;
+        cp_async_commit () ;
+        lbuf = (lbuf + 1 == DM_STAGES) ? 0 : lbuf + 1 ;
+        const int cur = cbuf ;
+        cbuf = (cbuf + 1 == DM_STAGES) ? 0 : cbuf + 1 ;
         if (warp_live)
         {
-            const double *cA = sA + (kt % DM_STAGES) * DM_KC * LDA_S + wm * WM + fm ;
-            const double *cB = sB + (kt % DM_STAGES) * DM_KC * LDB_S + wn * WN + fm ;
+            const double *cA = sA + cur * DM_KC * LDA_S + wm * WM + fm ;
+            const double *cB = sB + cur * DM_KC * LDB_S + wn * WN + fm ;
             #pragma unroll
             for (int kk = 0 ; kk < DM_KC ; kk += 4)
             {
@@ -295,51 +314,172 @@ __global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)
 }
 
 // ---------------------------------------------------------------------------------------------
-// dense Cholesky of one diagonal block (jb <= 64) per CTA, right-looking in shared memory
+// dense Cholesky of diagonal blocks (jb <= NB <= 64), one thread per row, the row in registers
 // ---------------------------------------------------------------------------------------------
 
 constexpr int PB_LD = POTRF_NB + 1 ;
+constexpr int WINV_LD = POTRF_NB ;              // an inverse slot is a 64 x 64 column-major array
 
-// On a pivot that is not > 0 (or NaN) the global column index is recorded in *minor (atomicMin): the
-// smallest failing column over the whole factorization is the reference's L->minor (SNW:1097).
-template <typename T>
-__global__ void __launch_bounds__ (256) k_potrf (const PotrfBlk *__restrict__ blks, T *Lx,
-    unsigned long long *minor)
+// A CTA of 64 threads factorizes 64/NB blocks, one NB-thread group each.  Thread r keeps row r of its
+// block in registers.  Right-looking: at step j every thread publishes its (still unscaled) entry of
+// column j through shared memory, then subtracts (a_rj / d) * a_cj from its row (d = the pivot), and
+// finally scales its own entry by 1/sqrt(d); one barrier per column.  On a pivot that is not > 0 (or
+// NaN) the global column index is recorded in *minor (atomicMin): the smallest failing column over the
+// whole factorization is the reference's L->minor (SNW:1097).
+// If the block has an inverse slot (slot >= 0), W = L^{-1} is also written to winv [slot] (identity
+// padded to NB x NB, leading dimension 64): the dtrsm on the rows below then becomes a product with W'
+// on the tensor pipe (k_trsm_inv).
+template <typename T, int NB>
+__global__ void __launch_bounds__ (64) k_potrf (const PotrfBlk *__restrict__ blks, int nblks, T *Lx,
+    T *__restrict__ winv, unsigned long long *minor)
 {
-    __shared__ T s [POTRF_NB * PB_LD] ;         // s [c * PB_LD + r], lower part used
-    const PotrfBlk b = blks [blockIdx.x] ;
+    constexpr int G = 64 / NB ;
+    __shared__ T colbuf [2][64] ;
+    __shared__ T rdiag [64] ;
+    __shared__ T sL [(NB > 16) ? G * NB * (NB + 1) : 1] ;
+    const int g = threadIdx.x / NB, r = threadIdx.x % NB ;
+    const int bi = blockIdx.x * G + g ;
+    const bool active = bi < nblks ;
+    PotrfBlk b ;
+    if (active) b = blks [bi] ; else { b.off = 0 ; b.col = 0 ; b.lda = 0 ; b.jb = 0 ; b.slot = -1 ; }
     const int jb = b.jb ;
     const int64_t lda = b.lda ;
     T *D = Lx + b.off ;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5 ;
-    for (int c = ty ; c < jb ; c += 8)
-        for (int r = c + tx ; r < jb ; r += 32)
-            s [c * PB_LD + r] = D [r + c * lda] ;
-    __syncthreads () ;
-    for (int j = 0 ; j < jb ; j++)
+    T a [NB] ;
+    #pragma unroll
+    for (int c = 0 ; c < NB ; c++)
+        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
+    #pragma unroll
+    for (int j = 0 ; j < NB ; j++)
     {
-        T d = s [j * PB_LD + j] ;
-        if (!(d > (T) 0))
-        {
-            if (threadIdx.x == 0) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-        }
-        T ljj = sqrt (d) ;
-        __syncthreads () ;                      // everyone has read the pivot
-        for (int r = j + threadIdx.x ; r < jb ; r += 256)
-            s [j * PB_LD + r] = (r == j) ? ljj : s [j * PB_LD + r] / ljj ;
+        T *cb = colbuf [j & 1] + g * NB ;
+        if (r >= j) cb [r] = a [j] ;
         __syncthreads () ;
-        const T *lj = s + j * PB_LD ;
-        for (int c = j + 1 + ty ; c < jb ; c += 8)
-        {
-            T ljc = lj [c] ;
-            for (int r = c + tx ; r < jb ; r += 32)
-                s [c * PB_LD + r] -= lj [r] * ljc ;
-        }
-        __syncthreads () ;
+        const T d = cb [j] ;
+        if (r == j && j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        const T t = a [j] * ((T) 1 / d) ;
+        #pragma unroll
+        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= t * cb [c] ;
+        const T ljj = sqrt (d) ;
+        if (r == j) { a [j] = ljj ; rdiag [g * NB + j] = (T) 1 / ljj ; }
+        else if (r > j) a [j] = a [j] / ljj ;
     }
-    for (int c = ty ; c < jb ; c += 8)
-        for (int r = c + tx ; r < jb ; r += 32)
-            D [r + c * lda] = s [c * PB_LD + r] ;
+    #pragma unroll
+    for (int c = 0 ; c < NB ; c++) if (r < jb && c <= r) D [r + c * lda] = a [c] ;
+
+    if (NB > 16)
+    {
+        // W = L^{-1}: thread c owns column c of W; row rr of W needs rows < rr only, so no barrier
+        // inside the loop.  L is read through shared memory (uniform address within a group).
+        T *Lg = sL + g * NB * (NB + 1) ;
+        #pragma unroll
+        for (int c = 0 ; c < NB ; c++) if (c <= r) Lg [r * (NB + 1) + c] = a [c] ;
+        __syncthreads () ;
+        if (b.slot < 0) return ;
+        const int c = r ;
+        T w [NB] ;
+        #pragma unroll
+        for (int rr = 0 ; rr < NB ; rr++)
+        {
+            T acc0 = (rr == c) ? (T) 1 : (T) 0, acc1 = 0, acc2 = 0, acc3 = 0 ;
+            const T *Lr = Lg + rr * (NB + 1) ;
+            #pragma unroll
+            for (int k = 0 ; k < rr ; k++)
+            {
+                // w [k] is zero for k < c, so the full-length dot product is right for every column
+                if ((k & 3) == 0) acc0 -= Lr [k] * w [k] ;
+                else if ((k & 3) == 1) acc1 -= Lr [k] * w [k] ;
+                else if ((k & 3) == 2) acc2 -= Lr [k] * w [k] ;
+                else acc3 -= Lr [k] * w [k] ;
+            }
+            w [rr] = (rr < c) ? (T) 0 : ((acc0 + acc1) + (acc2 + acc3)) * rdiag [g * NB + rr] ;
+        }
+        T *W = winv + (int64_t) b.slot * (WINV_LD * WINV_LD) + (int64_t) c * WINV_LD ;
+        #pragma unroll
+        for (int rr = 0 ; rr < NB ; rr++) W [rr] = w [rr] ;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rows below a factorized diagonal block through the explicit inverse:  X <- X * W',  W = L11^{-1}
+// ---------------------------------------------------------------------------------------------
+
+template <int NBK> constexpr size_t trsm_inv_smem_bytes ()
+{
+    return (size_t) NBK * ((TRSM_ROWS + 4) + (NBK + 4)) * sizeof (double) ;
+}
+
+// One CTA = 128 rows x NBK columns, 8 warps as 4 x 2, DMMA m8n8k4 with the same shared-memory layout
+// as k_upd_dmma.  The whole X tile is in shared memory before the first store, so the product is done
+// in place.  (W is lower triangular; its zero half is multiplied too -- K is only NBK.)
+template <int NBK>
+__global__ void __launch_bounds__ (256) k_trsm_inv (const TrsmTile *__restrict__ tiles, double *Lx,
+    const double *__restrict__ winv)
+{
+    constexpr int LDX = TRSM_ROWS + 4, LDW = NBK + 4 ;
+    constexpr int WN = NBK / 2, MT = 4, NTL = WN / 8 ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    double *sX = reinterpret_cast<double *> (smem_raw) ;        // [NBK][LDX]
+    double *sW = sX + NBK * LDX ;                               // [NBK][LDW]
+    const TrsmTile t = tiles [blockIdx.x] ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
+    const int wm = warp & 3, wn = warp >> 2 ;
+    const int jb = t.jb, nrows = t.nrows ;
+    const int64_t lda = t.lda ;
+    double *X = Lx + t.row_off ;
+    const double *W = winv + (int64_t) t.slot * (WINV_LD * WINV_LD) ;
+    #pragma unroll
+    for (int e = tid ; e < NBK * TRSM_ROWS ; e += 256)
+    {
+        int m = e % TRSM_ROWS, k = e / TRSM_ROWS ;
+        bool ok = (m < nrows) && (k < jb) ;
+        cp_async8 (sX + k * LDX + m, ok ? (const void *) (X + m + (int64_t) k * lda) : (const void *) W, ok) ;
+    }
+    #pragma unroll
+    for (int e = tid ; e < NBK * NBK ; e += 256)
+    {
+        int n = e % NBK, k = e / NBK ;
+        cp_async8 (sW + k * LDW + n, W + n + k * WINV_LD, true) ;
+    }
+    cp_async_commit () ;
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    double acc [MT][NTL][2] ;
+    #pragma unroll
+    for (int a = 0 ; a < MT ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) { acc [a][b][0] = 0.0 ; acc [a][b][1] = 0.0 ; }
+    const int fk = lane & 3, fm = lane >> 2 ;
+    const double *cA = sX + wm * 32 + fm ;
+    const double *cB = sW + wn * WN + fm ;
+    #pragma unroll
+    for (int kk = 0 ; kk < NBK ; kk += 4)
+    {
+        double fa [MT], fb [NTL] ;
+        #pragma unroll
+        for (int a = 0 ; a < MT ; a++) fa [a] = cA [(kk + fk) * LDX + a * 8] ;
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) fb [b] = cB [(kk + fk) * LDW + b * 8] ;
+        #pragma unroll
+        for (int a = 0 ; a < MT ; a++)
+            #pragma unroll
+            for (int b = 0 ; b < NTL ; b++)
+                dmma884 (acc [a][b][0], acc [a][b][1], fa [a], fb [b]) ;
+    }
+    #pragma unroll
+    for (int b = 0 ; b < NTL ; b++)
+        #pragma unroll
+        for (int e = 0 ; e < 2 ; e++)
+        {
+            const int jl = wn * WN + b * 8 + 2 * fk + e ;
+            if (jl >= jb) continue ;
+            #pragma unroll
+            for (int a = 0 ; a < MT ; a++)
+            {
+                const int il = wm * 32 + a * 8 + fm ;
+                if (il < nrows) X [il + (int64_t) jl * lda] = acc [a][b][e] ;
+            }
+        }
 }
 
 // ---------------------------------------------------------------------------------------------

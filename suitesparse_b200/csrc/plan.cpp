@@ -115,38 +115,44 @@ void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const in
 
 // blocked dpotrf + dtrsm of a set of independent supernodes, one POTRF_NB-wide block column per step.
 // ncol_eff [q] = number of leading columns of supernode S [q] to factorize (its nscol normally).
+// With use_dmma, blocks wider than 16 columns also produce their inverse and the rows below them are
+// multiplied by it on the tensor pipe (K_TRSM_INV*); narrower blocks use substitution (K_TRSM).
 void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma)
 {
     int64_t maxcol = 0 ;
     for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
+    std::vector<PotrfBlk> pb [3] ;      // jb <= 16, <= 32, <= 64
+    std::vector<TrsmTile> tt [3] ;      // substitution, inverse 32, inverse 64
     for (int64_t j0 = 0 ; j0 < maxcol ; j0 += POTRF_NB)
     {
-        Launch LP, LT ;
-        LP.kind = K_POTRF ; LP.first = (int64_t) out.potrf.size () ; LP.level = level ; LP.pad = 0 ;
-        LT.kind = K_TRSM ;  LT.first = (int64_t) out.trsm.size () ;  LT.level = level ; LT.pad = 0 ;
+        for (auto &v : pb) v.clear () ;
+        for (auto &v : tt) v.clear () ;
+        int32_t nslots = 0 ;
         for (int64_t q = 0 ; q < ns ; q++)
         {
             const int64_t s = S [q] ;
             const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
             if (nscol <= j0) continue ;
             const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
+            const int64_t r0 = j0 + jb ;
+            const int pcls = (jb <= 16) ? 0 : (jb <= 32) ? 1 : 2 ;
+            const bool inv = use_dmma && pcls > 0 && r0 < nsrow ;
             PotrfBlk b ;
             b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
             b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
-            out.potrf.push_back (b) ;
-            out.flops_kind [K_POTRF] += (double) jb * jb * jb / 3.0 ;
-            out.count_kind [K_POTRF]++ ;
-            const int64_t r0 = j0 + jb ;
+            b.slot = inv ? nslots++ : -1 ; b.pad = 0 ;
+            pb [pcls].push_back (b) ;
+            out.flops_kind [K_POTRF16 + pcls] += (double) jb * jb * jb / 3.0 ;
+            const int tcls = inv ? pcls : 0 ;
             for (int64_t r = r0 ; r < nsrow ; r += TRSM_ROWS)
             {
                 TrsmTile t ;
                 t.diag_off = b.off ; t.row_off = px [s] + r + j0 * nsrow ;
                 t.lda = (int32_t) nsrow ; t.jb = (int32_t) jb ;
-                t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.pad = 0 ;
-                out.trsm.push_back (t) ;
-                out.flops_kind [K_TRSM] += (double) t.nrows * jb * jb ;
-                out.count_kind [K_TRSM]++ ;
+                t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.slot = b.slot ;
+                tt [tcls].push_back (t) ;
+                out.flops_kind [K_TRSM + tcls] += (double) t.nrows * jb * jb ;
             }
             // trailing updates inside the supernode (two-level blocking)
             const int64_t J0 = (j0 / OUTER_NB) * OUTER_NB ;
@@ -173,10 +179,27 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
                 emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
             }
         }
-        LP.count = (int32_t) (out.potrf.size () - (size_t) LP.first) ;
-        LT.count = (int32_t) (out.trsm.size () - (size_t) LT.first) ;
-        if (LP.count > 0) out.launches.push_back (LP) ;
-        if (LT.count > 0) out.launches.push_back (LT) ;
+        out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
+        for (int c = 0 ; c < 3 ; c++)
+        {
+            if (pb [c].empty ()) continue ;
+            Launch L ;
+            L.kind = K_POTRF16 + c ; L.count = (int32_t) pb [c].size () ; L.first = (int64_t) out.potrf.size () ;
+            L.level = level ; L.pad = 0 ;
+            out.count_kind [L.kind] += L.count ;
+            out.potrf.insert (out.potrf.end (), pb [c].begin (), pb [c].end ()) ;
+            out.launches.push_back (L) ;
+        }
+        for (int c = 0 ; c < 3 ; c++)
+        {
+            if (tt [c].empty ()) continue ;
+            Launch L ;
+            L.kind = K_TRSM + c ; L.count = (int32_t) tt [c].size () ; L.first = (int64_t) out.trsm.size () ;
+            L.level = level ; L.pad = 0 ;
+            out.count_kind [L.kind] += L.count ;
+            out.trsm.insert (out.trsm.end (), tt [c].begin (), tt [c].end ()) ;
+            out.launches.push_back (L) ;
+        }
         flush_tiles (out, sink, level) ;
     }
 }

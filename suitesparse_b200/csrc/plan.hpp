@@ -40,6 +40,8 @@ struct PotrfBlk
     int64_t off ;       // Lx offset of the block's (0,0)
     int64_t col ;       // global column index of the block's first column (for L->minor)
     int32_t lda, jb ;
+    int32_t slot ;      // inverse slot in the winv scratch (k_trsm_inv follows), or -1
+    int32_t pad ;
 } ;
 
 // Rows below a factorized diagonal block:  X <- X * L11^{-T}   (the dtrsm of SNW:1175, R,L,C,N)
@@ -47,7 +49,8 @@ struct TrsmTile
 {
     int64_t diag_off ;  // Lx offset of L11 (0,0)
     int64_t row_off ;   // Lx offset of X (0,0)
-    int32_t lda, jb, nrows, pad ;
+    int32_t lda, jb, nrows ;
+    int32_t slot ;      // inverse slot of the diagonal block (K_TRSM_INV*), or -1
 } ;
 
 enum LaunchKind : int32_t
@@ -55,8 +58,13 @@ enum LaunchKind : int32_t
     K_UPD_SIMT = 0,     // UpdTile list, 32 x 8 tiles, one warp each
     K_UPD_D64  = 1,     // UpdTile list, 64 x 64 DMMA tiles
     K_UPD_D128 = 2,     // UpdTile list, 128 x 128 DMMA tiles
-    K_POTRF    = 3,     // PotrfBlk list
-    K_TRSM     = 4,     // TrsmTile list
+    K_POTRF16  = 3,     // PotrfBlk list, jb <= 16
+    K_POTRF32  = 4,     // PotrfBlk list, jb <= 32
+    K_POTRF64  = 5,     // PotrfBlk list, jb <= 64
+    K_TRSM     = 6,     // TrsmTile list, substitution
+    K_TRSM_INV32 = 7,   // TrsmTile list, product with the inverse of a <= 32-wide block
+    K_TRSM_INV64 = 8,   // TrsmTile list, product with the inverse of a <= 64-wide block
+    K_NKINDS   = 9,
 } ;
 
 struct Launch
@@ -82,8 +90,9 @@ struct Plan
     int32_t nlevels = 0 ;
     int64_t npairs = 0 ;
     double flops_update = 0, flops_potrf = 0, flops_trsm = 0 ;
-    double flops_kind [5] = {0, 0, 0, 0, 0} ;   // algorithmic flops executed by each launch kind
-    int64_t count_kind [5] = {0, 0, 0, 0, 0} ;  // list entries (tiles / blocks) per launch kind
+    double flops_kind [K_NKINDS] = {} ;     // algorithmic flops executed by each launch kind
+    int64_t count_kind [K_NKINDS] = {} ;    // list entries (tiles / blocks) per launch kind
+    int64_t winv_slots = 0 ;                // inverse slots (64 x 64 values each) the largest launch needs
 
     std::vector<int32_t> level ;        // [nsuper] height above the leaves in the supernodal etree
     std::vector<int64_t> parent ;       // [nsuper] etree parent or -1

@@ -79,9 +79,10 @@ def run_plan(F, Lx, tables=None):
                 pending.append((dst, Cpart[keep]))
             for dst, val in pending:
                 np.subtract.at(Lx, dst, val)
-        elif kind == b200.K_POTRF:
+        elif kind in b200.K_POTRF_KINDS:
             for b in potrf[first:first + cnt]:
                 jb, lda = int(b["jb"]), int(b["lda"])
+                assert jb <= (16, 32, 64)[kind - b200.K_POTRF16]
                 D = _view(Lx, int(b["off"]), jb, jb, lda)
                 Dl = np.tril(D)
                 Dsym = Dl + np.tril(Dl, -1).T
@@ -99,9 +100,10 @@ def run_plan(F, Lx, tables=None):
                         Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
                 r, c = np.tril_indices(jb)
                 D[r, c] = Lc[r, c]
-        elif kind == b200.K_TRSM:
+        elif kind in b200.K_TRSM_KINDS:
             for t in trsm[first:first + cnt]:
                 jb, lda, nr = int(t["jb"]), int(t["lda"]), int(t["nrows"])
+                assert (int(t["slot"]) >= 0) == (kind != b200.K_TRSM)
                 L11 = np.tril(_view(Lx, int(t["diag_off"]), jb, jb, lda))
                 X = _view(Lx, int(t["row_off"]), nr, jb, lda)
                 with np.errstate(all="ignore"):

@@ -77,7 +77,7 @@ def test_plan_structure():
     # a wide supernode exercises the two-level blocking and the DMMA tile classes
     assert np.diff(c.sym["super"]).max() > 256
     kinds = set(launches["kind"].tolist())
-    assert {b200.K_POTRF, b200.K_TRSM, b200.K_UPD_SIMT} <= kinds and (b200.K_UPD_D64 in kinds or b200.K_UPD_D128 in kinds)
+    assert {b200.K_POTRF16, b200.K_POTRF64, b200.K_TRSM, b200.K_TRSM_INV64, b200.K_UPD_SIMT} <= kinds and (b200.K_UPD_D64 in kinds or b200.K_UPD_D128 in kinds)
     F.close()
 
 
