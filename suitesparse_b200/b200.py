@@ -209,7 +209,9 @@ TILE_DT = np.dtype([("item", "<i4"), ("ti", "<u2"), ("tj", "<u2"), ("k0", "<i4")
 POTRF_DT = np.dtype([("off", "<i8"), ("col", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("slot", "<i4"), ("pad", "<i4")])
 TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("nrows", "<i4"),
                     ("slot", "<i4")])
-LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("pad", "<i4")])
+LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
+                      ("wait_ev", "<i4"), ("rec_ev", "<i4")])
+K_JOIN = 9
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)

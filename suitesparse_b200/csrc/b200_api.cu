@@ -46,7 +46,9 @@ struct b200_factor
     size_t esize = 8 ;
     std::vector<int64_t> h_super, h_pi, h_px ;
 
-    cudaStream_t stream = nullptr ;
+    cudaStream_t stream = nullptr ;         // main stream: everything except the look-ahead updates
+    cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
+    std::vector<cudaEvent_t> plan_ev ;      // events of the plan's look-ahead schedule
     cudaEvent_t ev [8] = {} ;
     // symbolic tables
     DevBuf<int64_t> d_super, d_pi, d_px ;
@@ -122,8 +124,14 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
 {
     T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
     T *winv = reinterpret_cast<T *> (f->d_winv.p) ;
-    cudaStream_t st = f->stream ;
+    const cudaStream_t streams [2] = { f->stream, f->stream2 } ;
     size_t nev = 0 ;
+    while ((int64_t) f->plan_ev.size () < (int64_t) P.nevents)
+    {
+        cudaEvent_t e ;
+        CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "plan event") ;
+        f->plan_ev.push_back (e) ;
+    }
     if ((size_t) P.winv_slots * WINV_LD * WINV_LD * sizeof (T) > f->d_winv.n) return B200_INVALID ;
     if (f->profile)
     {
@@ -136,7 +144,13 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     }
     for (const Launch &L : P.launches)
     {
-        if (L.count <= 0) continue ;
+        const cudaStream_t st = streams [L.stream ? 1 : 0] ;
+        if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
+        if (L.kind == K_JOIN || L.count <= 0)
+        {
+            if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
+            continue ;
+        }
         if (f->profile) cudaEventRecord (f->prof_ev [nev++], st) ;
         switch (L.kind)
         {
@@ -184,15 +198,17 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         }
         f->kernel_launches++ ;
         if (f->profile) cudaEventRecord (f->prof_ev [nev++], st) ;
+        if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
     }
     CK (cudaGetLastError (), "kernel launch") ;
     if (f->profile)
     {
-        CK (cudaStreamSynchronize (st), "profile sync") ;
+        CK (cudaStreamSynchronize (f->stream), "profile sync") ;
+        CK (cudaStreamSynchronize (f->stream2), "profile sync") ;
         size_t e = 0 ;
         for (const Launch &L : P.launches)
         {
-            if (L.count <= 0) continue ;
+            if (L.kind == K_JOIN || L.count <= 0) continue ;
             float ms = 0 ;
             cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
             e += 2 ;
@@ -324,7 +340,14 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     CK (cudaSetDevice (f->device), "cudaSetDevice") ;
     int st = kernel_attrs (f->device) ;
     if (st != B200_OK) return st ;
-    CK (cudaStreamCreateWithFlags (&f->stream, cudaStreamNonBlocking), "stream") ;
+    {
+        // the panel chain (main stream) gets the higher priority: its small kernels must be scheduled
+        // as soon as a slot frees up while a look-ahead update fills the machine
+        int lo = 0, hi = 0 ;
+        CK (cudaDeviceGetStreamPriorityRange (&lo, &hi), "priority range") ;
+        CK (cudaStreamCreateWithPriority (&f->stream, cudaStreamNonBlocking, hi), "stream") ;
+        CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
+    }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
     std::vector<int32_t> Ls32 ((size_t) P.ssize) ;
     for (int64_t k = 0 ; k < P.ssize ; k++) Ls32 [k] = (int32_t) Ls [k] ;
@@ -396,6 +419,9 @@ void b200_destroy (b200_factor *f)
         f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
+        for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
+        cudaStreamSynchronize (f->stream2) ;
+        cudaStreamDestroy (f->stream2) ;
         cudaStreamDestroy (f->stream) ;
         cudaGetLastError () ;
     }
@@ -418,6 +444,7 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "npotrf")) return (int64_t) P.potrf.size () ;
     if (!strcmp (name, "ntrsm")) return (int64_t) P.trsm.size () ;
     if (!strcmp (name, "nlaunches")) return (int64_t) P.launches.size () ;
+    if (!strcmp (name, "nevents")) return P.nevents ;
     if (!strcmp (name, "winv_slots")) return P.winv_slots ;
     if (!strcmp (name, "device_bytes")) return (int64_t) f->device_bytes ;
     if (!strcmp (name, "device")) return f->device ;

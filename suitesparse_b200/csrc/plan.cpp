@@ -75,20 +75,32 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     }
 }
 
-void flush_tiles (Plan &P, TileSink &sink, int level)
+Launch make_launch (int kind, int64_t first, int64_t count, int level, int stream)
 {
+    Launch L ;
+    L.kind = kind ; L.count = (int32_t) count ; L.first = first ; L.level = level ;
+    L.stream = stream ; L.wait_ev = -1 ; L.rec_ev = -1 ;
+    return L ;
+}
+
+// Append the gathered tiles as one launch per kernel class on `stream`.  The first launch waits for
+// wait_ev and the last records rec_ev; with nothing to launch the events are carried by a K_JOIN.
+void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_ev = -1, int rec_ev = -1)
+{
+    const size_t before = P.launches.size () ;
     for (int c = 0 ; c < 3 ; c++)
     {
         auto &v = sink.cls [c] ;
         if (v.empty ()) continue ;
-        Launch L ;
-        L.kind = c ; L.count = (int32_t) v.size () ; L.first = (int64_t) P.tiles.size () ;
-        L.level = level ; L.pad = 0 ;
-        P.count_kind [c] += L.count ;
+        P.launches.push_back (make_launch (c, (int64_t) P.tiles.size (), (int64_t) v.size (), level, stream)) ;
+        P.count_kind [c] += (int64_t) v.size () ;
         P.tiles.insert (P.tiles.end (), v.begin (), v.end ()) ;
-        P.launches.push_back (L) ;
     }
     sink.clear () ;
+    if (wait_ev < 0 && rec_ev < 0) return ;
+    if (P.launches.size () == before) P.launches.push_back (make_launch (K_JOIN, 0, 0, level, stream)) ;
+    P.launches [before].wait_ev = wait_ev ;
+    P.launches.back ().rec_ev = rec_ev ;
 }
 
 // the descendant updates into supernode s
@@ -113,10 +125,21 @@ void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const in
     }
 }
 
-// blocked dpotrf + dtrsm of a set of independent supernodes, one POTRF_NB-wide block column per step.
+// Blocked dpotrf + dtrsm of a set of independent supernodes (SNW:1023-1181), batched step by step.
 // ncol_eff [q] = number of leading columns of supernode S [q] to factorize (its nscol normally).
-// With use_dmma, blocks wider than 16 columns also produce their inverse and the rows below them are
-// multiplied by it on the tensor pipe (K_TRSM_INV*); narrower blocks use substitution (K_TRSM).
+//
+// Two-level blocking: an outer block is OUTER_NB columns, factorized in POTRF_NB-wide steps
+// (potrf of the diagonal block, trsm of the rows below, "inner" update of the rest of the outer block,
+// K = POTRF_NB); when an outer block T is done its "outer" update (K = OUTER_NB) goes to all later
+// columns.  With use_dmma, blocks wider than 16 columns also produce their inverse and the rows below
+// them are multiplied by it on the tensor pipe (K_TRSM_INV*); narrower blocks use substitution.
+//
+// Look-ahead: the outer update of block T is split into Ua (columns of outer block T+1, main stream) and
+// Ub (all later columns, look-ahead stream).  The panel chain F(T+1) = {potrf, trsm, inner updates} then
+// runs on the main stream while Ub(T) fills the machine:
+//     main:        F(T)  rec eF(T)   Ua(T)   [wait eB(T-1)]  F(T+1)  rec eF(T+1)  Ua(T+1) ...
+//     look-ahead:        [wait eF(T)]  Ub(T)  rec eB(T)       [wait eF(T+1)]  Ub(T+1) ...
+// Ub(T) and Ua(T+1) may touch the same columns concurrently; both only subtract with atomics.
 void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma)
 {
@@ -124,83 +147,136 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
     for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
     std::vector<PotrfBlk> pb [3] ;      // jb <= 16, <= 32, <= 64
     std::vector<TrsmTile> tt [3] ;      // substitution, inverse 32, inverse 64
-    for (int64_t j0 = 0 ; j0 < maxcol ; j0 += POTRF_NB)
+    int evB_prev = -1, evB_prev2 = -1 ; // eB(T-1), eB(T-2)
+    for (int64_t J0 = 0 ; J0 < maxcol ; J0 += OUTER_NB)
     {
-        for (auto &v : pb) v.clear () ;
-        for (auto &v : tt) v.clear () ;
-        int32_t nslots = 0 ;
+        // ---- F(T): the panel chain of outer block T -------------------------------------------------
+        // it reads columns that Ub(T-2) and earlier wrote; Ub(T-1) is only needed by F(T+1)
+        int pending_wait = evB_prev2 ;
+        evB_prev2 = -1 ;
+        for (int64_t j0 = J0 ; j0 < std::min (maxcol, J0 + OUTER_NB) ; j0 += POTRF_NB)
+        {
+            for (auto &v : pb) v.clear () ;
+            for (auto &v : tt) v.clear () ;
+            int32_t nslots = 0 ;
+            for (int64_t q = 0 ; q < ns ; q++)
+            {
+                const int64_t s = S [q] ;
+                const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
+                if (nscol <= j0) continue ;
+                const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
+                const int64_t r0 = j0 + jb ;
+                const int pcls = (jb <= 16) ? 0 : (jb <= 32) ? 1 : 2 ;
+                const bool inv = use_dmma && pcls > 0 && r0 < nsrow ;
+                PotrfBlk b ;
+                b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
+                b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
+                b.slot = inv ? nslots++ : -1 ; b.pad = 0 ;
+                pb [pcls].push_back (b) ;
+                out.flops_kind [K_POTRF16 + pcls] += (double) jb * jb * jb / 3.0 ;
+                const int tcls = inv ? pcls : 0 ;
+                for (int64_t r = r0 ; r < nsrow ; r += TRSM_ROWS)
+                {
+                    TrsmTile t ;
+                    t.diag_off = b.off ; t.row_off = px [s] + r + j0 * nsrow ;
+                    t.lda = (int32_t) nsrow ; t.jb = (int32_t) jb ;
+                    t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.slot = b.slot ;
+                    tt [tcls].push_back (t) ;
+                    out.flops_kind [K_TRSM + tcls] += (double) t.nrows * jb * jb ;
+                }
+                // inner update: columns [r0, Jend) of the current outer block, K = jb
+                const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
+                if (r0 < Jend)
+                {
+                    UpdItem it ;
+                    it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ;
+                    it.a_off = px [s] + r0 + j0 * nsrow ;
+                    it.c_off = px [s] + r0 + r0 * nsrow ;
+                    it.M = (int32_t) (nsrow - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
+                    out.items.push_back (it) ;
+                    emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+                }
+            }
+            out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
+            for (int c = 0 ; c < 3 ; c++)
+            {
+                if (pb [c].empty ()) continue ;
+                Launch L = make_launch (K_POTRF16 + c, (int64_t) out.potrf.size (), (int64_t) pb [c].size (), level, 0) ;
+                L.wait_ev = pending_wait ; pending_wait = -1 ;
+                out.count_kind [L.kind] += L.count ;
+                out.potrf.insert (out.potrf.end (), pb [c].begin (), pb [c].end ()) ;
+                out.launches.push_back (L) ;
+            }
+            for (int c = 0 ; c < 3 ; c++)
+            {
+                if (tt [c].empty ()) continue ;
+                Launch L = make_launch (K_TRSM + c, (int64_t) out.trsm.size (), (int64_t) tt [c].size (), level, 0) ;
+                out.count_kind [L.kind] += L.count ;
+                out.trsm.insert (out.trsm.end (), tt [c].begin (), tt [c].end ()) ;
+                out.launches.push_back (L) ;
+            }
+            flush_tiles (out, sink, level) ;
+        }
+
+        // ---- outer update of block T -------------------------------------------------------------------
+        const int64_t Jn = J0 + OUTER_NB ;      // first column of the next outer block
+        TileSink later ;
+        bool any_b = false ;
         for (int64_t q = 0 ; q < ns ; q++)
         {
             const int64_t s = S [q] ;
             const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
-            if (nscol <= j0) continue ;
-            const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
-            const int64_t r0 = j0 + jb ;
-            const int pcls = (jb <= 16) ? 0 : (jb <= 32) ? 1 : 2 ;
-            const bool inv = use_dmma && pcls > 0 && r0 < nsrow ;
-            PotrfBlk b ;
-            b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
-            b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
-            b.slot = inv ? nslots++ : -1 ; b.pad = 0 ;
-            pb [pcls].push_back (b) ;
-            out.flops_kind [K_POTRF16 + pcls] += (double) jb * jb * jb / 3.0 ;
-            const int tcls = inv ? pcls : 0 ;
-            for (int64_t r = r0 ; r < nsrow ; r += TRSM_ROWS)
-            {
-                TrsmTile t ;
-                t.diag_off = b.off ; t.row_off = px [s] + r + j0 * nsrow ;
-                t.lda = (int32_t) nsrow ; t.jb = (int32_t) jb ;
-                t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.slot = b.slot ;
-                tt [tcls].push_back (t) ;
-                out.flops_kind [K_TRSM + tcls] += (double) t.nrows * jb * jb ;
-            }
-            // trailing updates inside the supernode (two-level blocking)
-            const int64_t J0 = (j0 / OUTER_NB) * OUTER_NB ;
-            const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
+            if (nscol <= Jn) continue ;
             UpdItem it ;
-            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ;
-            if (r0 < Jend)
+            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ; it.K = (int32_t) OUTER_NB ;
+            // Ua: columns [Jn, Jn2) -- the next panel
+            const int64_t Jn2 = std::min<int64_t> (nscol, Jn + OUTER_NB) ;
+            it.a_off = px [s] + Jn + J0 * nsrow ;
+            it.c_off = px [s] + Jn + Jn * nsrow ;
+            it.M = (int32_t) (nsrow - Jn) ; it.N = (int32_t) (Jn2 - Jn) ;
+            out.items.push_back (it) ;
+            emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+            // Ub: columns [Jn2, nscol) -- everything after the next panel
+            if (Jn2 < nscol)
             {
-                // inner: columns [r0, Jend) of the current outer block, K = jb
-                it.a_off = px [s] + r0 + j0 * nsrow ;
-                it.c_off = px [s] + r0 + r0 * nsrow ;
-                it.M = (int32_t) (nsrow - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
+                it.a_off = px [s] + Jn2 + J0 * nsrow ;
+                it.c_off = px [s] + Jn2 + Jn2 * nsrow ;
+                it.M = (int32_t) (nsrow - Jn2) ; it.N = (int32_t) (nscol - Jn2) ;
                 out.items.push_back (it) ;
-                emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
-            }
-            else if (Jend < nscol)
-            {
-                // outer: all remaining columns [Jend, nscol), K = width of the finished outer block
-                it.a_off = px [s] + Jend + J0 * nsrow ;
-                it.c_off = px [s] + Jend + Jend * nsrow ;
-                it.M = (int32_t) (nsrow - Jend) ; it.N = (int32_t) (nscol - Jend) ;
-                it.K = (int32_t) (Jend - J0) ;
-                out.items.push_back (it) ;
-                emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+                emit_tiles (out, (int32_t) (out.items.size () - 1), it, later, use_dmma) ;
+                any_b = true ;
             }
         }
-        out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
-        for (int c = 0 ; c < 3 ; c++)
+        int evF = -1, evB = -1 ;
+        if (any_b)
         {
-            if (pb [c].empty ()) continue ;
-            Launch L ;
-            L.kind = K_POTRF16 + c ; L.count = (int32_t) pb [c].size () ; L.first = (int64_t) out.potrf.size () ;
-            L.level = level ; L.pad = 0 ;
-            out.count_kind [L.kind] += L.count ;
-            out.potrf.insert (out.potrf.end (), pb [c].begin (), pb [c].end ()) ;
-            out.launches.push_back (L) ;
+            // F(T) ends here on the main stream
+            evF = out.nevents++ ; evB = out.nevents++ ;
+            out.launches.back ().rec_ev = (out.launches.back ().rec_ev < 0) ? evF : out.launches.back ().rec_ev ;
+            if (out.launches.back ().rec_ev != evF)
+            {
+                Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evF ;
+                out.launches.push_back (J) ;
+            }
         }
-        for (int c = 0 ; c < 3 ; c++)
+        flush_tiles (out, sink, level, 0) ;                     // Ua(T), main stream
+        if (any_b) flush_tiles (out, later, level, 1, evF, evB) ;  // Ub(T), look-ahead stream
+        evB_prev2 = evB_prev ;
+        evB_prev = evB ;
+        // F(T+1) must see Ub(T-1); F(T+2) must see Ub(T): keep both pending events alive
+        if (pending_wait >= 0)
         {
-            if (tt [c].empty ()) continue ;
-            Launch L ;
-            L.kind = K_TRSM + c ; L.count = (int32_t) tt [c].size () ; L.first = (int64_t) out.trsm.size () ;
-            L.level = level ; L.pad = 0 ;
-            out.count_kind [L.kind] += L.count ;
-            out.trsm.insert (out.trsm.end (), tt [c].begin (), tt [c].end ()) ;
-            out.launches.push_back (L) ;
+            // no launch of F(T) consumed the wait (cannot happen: every outer block has a potrf)
+            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = pending_wait ;
+            out.launches.push_back (J) ;
         }
-        flush_tiles (out, sink, level) ;
+    }
+    // the main stream joins the look-ahead stream before anything else uses these supernodes
+    for (int ev : { evB_prev2, evB_prev })
+    {
+        if (ev < 0) continue ;
+        Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = ev ;
+        out.launches.push_back (J) ;
     }
 }
 

@@ -65,6 +65,7 @@ enum LaunchKind : int32_t
     K_TRSM_INV32 = 7,   // TrsmTile list, product with the inverse of a <= 32-wide block
     K_TRSM_INV64 = 8,   // TrsmTile list, product with the inverse of a <= 64-wide block
     K_NKINDS   = 9,
+    K_JOIN     = 9,     // no kernel: only the launch's wait_ev / rec_ev are honoured
 } ;
 
 struct Launch
@@ -73,7 +74,9 @@ struct Launch
     int32_t count ;     // number of list entries
     int64_t first ;     // first entry in the kind's list
     int32_t level ;     // etree level this launch belongs to
-    int32_t pad ;
+    int32_t stream ;    // 0 = main (panel) stream, 1 = look-ahead stream of the wide trailing updates
+    int32_t wait_ev ;   // event the stream waits for before this launch, or -1
+    int32_t rec_ev ;    // event recorded on the stream after this launch, or -1
 } ;
 
 constexpr int POTRF_NB   = 64 ;     // width of a block column factorized by one POTRF block
@@ -93,6 +96,7 @@ struct Plan
     double flops_kind [K_NKINDS] = {} ;     // algorithmic flops executed by each launch kind
     int64_t count_kind [K_NKINDS] = {} ;    // list entries (tiles / blocks) per launch kind
     int64_t winv_slots = 0 ;                // inverse slots (64 x 64 values each) the largest launch needs
+    int32_t nevents = 0 ;                   // events the look-ahead schedule uses
 
     std::vector<int32_t> level ;        // [nsuper] height above the leaves in the supernodal etree
     std::vector<int64_t> parent ;       // [nsuper] etree parent or -1

@@ -42,7 +42,39 @@ def _view(Lx, off, rows, cols, ld):
     return as_strided(Lx[off:], shape=(rows, cols), strides=(Lx.itemsize, ld * Lx.itemsize), writeable=True)
 
 
-def run_plan(F, Lx, tables=None):
+def _schedule(launches, prefer):
+    """Order the launches the way two CUDA streams could legally execute them: each stream in order, a
+    launch with wait_ev only after that event was recorded.  prefer = 0 runs the main stream as far as
+    it can before the look-ahead stream gets a turn; prefer = 1 the other way round."""
+    queues = {0: [i for i, L in enumerate(launches) if L["stream"] == 0],
+              1: [i for i, L in enumerate(launches) if L["stream"] == 1]}
+    pos, recorded, order = {0: 0, 1: 0}, set(), []
+    # cudaStreamWaitEvent on an event that the host has not recorded yet is a no-op: every wait must come
+    # after its record in issue (= list) order
+    rec_at = {int(L["rec_ev"]): i for i, L in enumerate(launches) if L["rec_ev"] >= 0}
+    for i, L in enumerate(launches):
+        if L["wait_ev"] >= 0:
+            assert int(L["wait_ev"]) in rec_at and rec_at[int(L["wait_ev"])] < i, "wait before record"
+
+    def ready(st):
+        if pos[st] >= len(queues[st]):
+            return False
+        w = int(launches[queues[st][pos[st]]]["wait_ev"])
+        return w < 0 or w in recorded
+
+    while pos[0] < len(queues[0]) or pos[1] < len(queues[1]):
+        st = prefer if ready(prefer) else 1 - prefer
+        assert ready(st), "dead-lock in the launch plan's event graph"
+        i = queues[st][pos[st]]
+        order.append(i)
+        pos[st] += 1
+        r = int(launches[i]["rec_ev"])
+        if r >= 0:
+            recorded.add(r)
+    return order
+
+
+def run_plan(F, Lx, tables=None, prefer=0):
     """Execute every launch of Factor F's plan on the flat factor array Lx.  Returns the smallest failing
     column (what the kernels record through atomicMin) or None."""
     if tables is None:
@@ -52,8 +84,14 @@ def run_plan(F, Lx, tables=None):
     items, tiles, potrf, trsm = tables["items"], tables["tiles"], tables["potrf"], tables["trsm"]
     relmap = tables["relmap"]
     minor = None
-    for L in tables["launches"]:
+    launches = tables["launches"]
+    for st1 in launches[launches["stream"] == 1]:
+        assert st1["wait_ev"] >= 0 or st1["kind"] != b200.K_JOIN
+    for idx in _schedule(launches, prefer):
+        L = launches[idx]
         kind, cnt, first = int(L["kind"]), int(L["count"]), int(L["first"])
+        if kind == b200.K_JOIN:
+            continue
         if kind in b200.TILE_SHAPE:
             TM, TN = b200.TILE_SHAPE[kind]
             # all tiles of a launch read operands that no tile of the same launch writes: gather the

@@ -47,6 +47,11 @@ def test_plan_reproduces_reference_factor(kind, size, ordering):
     minor = plan_interp.run_plan(F, Lx)
     assert minor is None
     assert c.rel_err(Lx) <= 1e-12
+    # the other legal interleaving of the main and the look-ahead stream gives the same factor
+    Lx2 = np.zeros(c.sym["xsize"])
+    plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx2)
+    assert plan_interp.run_plan(F, Lx2, prefer=1) is None
+    assert c.rel_err(Lx2) <= 1e-12
     # the plan's flop count is the supernodal formula of SURVEY.md 8d: never below Common->fl's leading terms
     assert F.getd("flops_executed") > 0
     F.close()
@@ -64,6 +69,7 @@ def test_plan_structure():
     assert np.all(parent[has_parent] > np.nonzero(has_parent)[0])          # postordered
     launches = F.plan_table("launches", b200.LAUNCH_DT)
     assert np.all(np.diff(launches["level"]) >= 0)                           # level by level
+    assert F.geti("nevents") > 0 and np.any(launches["stream"] == 1)        # look-ahead is in use
     items = F.plan_table("items", b200.ITEM_DT)
     tiles = F.plan_table("tiles", b200.TILE_DT)
     assert tiles["item"].max() < items.size
