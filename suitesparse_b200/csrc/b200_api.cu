@@ -109,6 +109,8 @@ int kernel_attrs (int device)
         (int) trsm_inv_smem_bytes<32> ()), "attr trsm_inv32") ;
     CK (cudaFuncSetAttribute (k_trsm_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) trsm_inv_smem_bytes<64> ()), "attr trsm_inv64") ;
+    CK (cudaFuncSetAttribute (k_potrf_tile<double>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) potrf_smem_bytes<double> ()), "attr potrf") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
@@ -172,13 +174,13 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                     (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
                 break ;
             case K_POTRF16:
-                k_potrf<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
+                k_potrf_reg<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
                 break ;
             case K_POTRF32:
-                k_potrf<T, 32><<<(unsigned) ((L.count + 1) / 2), 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
+                k_potrf_tile<T><<<(unsigned) L.count, 256, potrf_smem_bytes<T> (), st>>> (potrf + L.first, Lx, winv, 32, f->d_minor.p) ;
                 break ;
             case K_POTRF64:
-                k_potrf<T, 64><<<(unsigned) L.count, 64, 0, st>>> (potrf + L.first, L.count, Lx, winv, f->d_minor.p) ;
+                k_potrf_tile<T><<<(unsigned) L.count, 256, potrf_smem_bytes<T> (), st>>> (potrf + L.first, Lx, winv, 64, f->d_minor.p) ;
                 break ;
             case K_TRSM:
                 k_trsm<T><<<(unsigned) L.count, TRSM_ROWS, 0, st>>> (trsm + L.first, Lx) ;

@@ -320,23 +320,19 @@ __global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)
 constexpr int PB_LD = POTRF_NB + 1 ;
 constexpr int WINV_LD = POTRF_NB ;              // an inverse slot is a 64 x 64 column-major array
 
-// A CTA of 64 threads factorizes 64/NB blocks, one NB-thread group each.  Thread r keeps row r of its
-// block in registers.  Right-looking: at step j every thread publishes its (still unscaled) entry of
-// column j through shared memory, then subtracts (a_rj / d) * a_cj from its row (d = the pivot), and
-// finally scales its own entry by 1/sqrt(d); one barrier per column.  On a pivot that is not > 0 (or
-// NaN) the global column index is recorded in *minor (atomicMin): the smallest failing column over the
-// whole factorization is the reference's L->minor (SNW:1097).
-// If the block has an inverse slot (slot >= 0), W = L^{-1} is also written to winv [slot] (identity
-// padded to NB x NB, leading dimension 64): the dtrsm on the rows below then becomes a product with W'
-// on the tensor pipe (k_trsm_inv).
+// Narrow blocks (jb <= NB = 16, the leaves: 98 % of all supernodes): a CTA of 64 threads factorizes 4
+// blocks, one 16-thread group each.  Thread r keeps row r of its block in registers.  Right-looking: at
+// step j every thread publishes its (still unscaled) entry of column j through shared memory, then
+// subtracts (a_rj / d) * a_cj from its row (d = the pivot) and finally scales its own entry by
+// 1/sqrt(d); one barrier per column.  On a pivot that is not > 0 (or NaN) the global column index is
+// recorded in *minor (atomicMin): the smallest failing column over the whole factorization is the
+// reference's L->minor (SNW:1097).
 template <typename T, int NB>
-__global__ void __launch_bounds__ (64) k_potrf (const PotrfBlk *__restrict__ blks, int nblks, T *Lx,
-    T *__restrict__ winv, unsigned long long *minor)
+__global__ void __launch_bounds__ (64) k_potrf_reg (const PotrfBlk *__restrict__ blks, int nblks, T *Lx,
+    unsigned long long *minor)
 {
     constexpr int G = 64 / NB ;
     __shared__ T colbuf [2][64] ;
-    __shared__ T rdiag [64] ;
-    __shared__ T sL [(NB > 16) ? G * NB * (NB + 1) : 1] ;
     const int g = threadIdx.x / NB, r = threadIdx.x % NB ;
     const int bi = blockIdx.x * G + g ;
     const bool active = bi < nblks ;
@@ -361,42 +357,141 @@ __global__ void __launch_bounds__ (64) k_potrf (const PotrfBlk *__restrict__ blk
         #pragma unroll
         for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= t * cb [c] ;
         const T ljj = sqrt (d) ;
-        if (r == j) { a [j] = ljj ; rdiag [g * NB + j] = (T) 1 / ljj ; }
+        if (r == j) a [j] = ljj ;
         else if (r > j) a [j] = a [j] / ljj ;
     }
     #pragma unroll
     for (int c = 0 ; c < NB ; c++) if (r < jb && c <= r) D [r + c * lda] = a [c] ;
+}
 
-    if (NB > 16)
-    {
-        // W = L^{-1}: thread c owns column c of W; row rr of W needs rows < rr only, so no barrier
-        // inside the loop.  L is read through shared memory (uniform address within a group).
-        T *Lg = sL + g * NB * (NB + 1) ;
+template <typename T> constexpr size_t potrf_smem_bytes ()
+{
+    return (size_t) (2 * POTRF_NB * PB_LD + 5 * POTRF_NB) * sizeof (T) ;
+}
+
+// Wider blocks (16 < jb <= 64): one CTA of 256 threads per block.  The block lives in registers as a
+// 16 x 16 grid of 4 x 4 sub-tiles (thread (ti,tj) holds rows 4ti.., columns 4tj..); the loop over tile
+// columns is rolled, so the code stays small (a fully unrolled one-row-per-thread version is bound by
+// cold instruction fetch, a shared-memory version by read-modify-write latency).  Right-looking on the
+// UNSCALED columns: at step j the owners of column j publish it through shared memory, then every
+// thread subtracts a_rj * a_cj / d_j from its registers -- one barrier per column; afterwards every
+// column is scaled by 1/sqrt(d_j).
+// If the block has an inverse slot (slot >= 0), W = L^{-1} is also formed (4 lanes per column, row by
+// row, in shared memory) and written to winv [slot], identity-padded to nbk x nbk with leading
+// dimension 64: the dtrsm on the rows below then becomes a product with W' on the tensor pipe.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict__ blks, T *Lx,
+    T *__restrict__ winv, int nbk, unsigned long long *minor)
+{
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    T *s = reinterpret_cast<T *> (smem_raw) ;           // s [c * PB_LD + r] = L (r,c), lower part
+    T *w = s + POTRF_NB * PB_LD ;                       // w [r * PB_LD + c] = W (r,c), lower part
+    T *colbuf = w + POTRF_NB * PB_LD ;                  // [2][64] column j, double buffered
+    T *dvec = colbuf + 2 * POTRF_NB ;                   // [64] pivots d_j
+    T *sqv = dvec + POTRF_NB ;                          // [64] sqrt (d_j)
+    T *rsq = sqv + POTRF_NB ;                           // [64] 1 / sqrt (d_j)
+    const PotrfBlk b = blks [blockIdx.x] ;
+    const int jb = b.jb ;
+    const int64_t lda = b.lda ;
+    T *D = Lx + b.off ;
+    const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4 ;
+    T a [4][4] ;
+    #pragma unroll
+    for (int jc = 0 ; jc < 4 ; jc++)
         #pragma unroll
-        for (int c = 0 ; c < NB ; c++) if (c <= r) Lg [r * (NB + 1) + c] = a [c] ;
-        __syncthreads () ;
-        if (b.slot < 0) return ;
-        const int c = r ;
-        T w [NB] ;
-        #pragma unroll
-        for (int rr = 0 ; rr < NB ; rr++)
+        for (int i = 0 ; i < 4 ; i++)
         {
-            T acc0 = (rr == c) ? (T) 1 : (T) 0, acc1 = 0, acc2 = 0, acc3 = 0 ;
-            const T *Lr = Lg + rr * (NB + 1) ;
-            #pragma unroll
-            for (int k = 0 ; k < rr ; k++)
-            {
-                // w [k] is zero for k < c, so the full-length dot product is right for every column
-                if ((k & 3) == 0) acc0 -= Lr [k] * w [k] ;
-                else if ((k & 3) == 1) acc1 -= Lr [k] * w [k] ;
-                else if ((k & 3) == 2) acc2 -= Lr [k] * w [k] ;
-                else acc3 -= Lr [k] * w [k] ;
-            }
-            w [rr] = (rr < c) ? (T) 0 : ((acc0 + acc1) + (acc2 + acc3)) * rdiag [g * NB + rr] ;
+            const int r = 4 * ti + i, c = 4 * tj + jc ;
+            a [i][jc] = (r < jb && c < jb && r >= c) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
         }
-        T *W = winv + (int64_t) b.slot * (WINV_LD * WINV_LD) + (int64_t) c * WINV_LD ;
+    const int njt = (jb + 3) >> 2 ;
+    for (int jt = 0 ; jt < njt ; jt++)
+    {
         #pragma unroll
-        for (int rr = 0 ; rr < NB ; rr++) W [rr] = w [rr] ;
+        for (int jj = 0 ; jj < 4 ; jj++)
+        {
+            const int j = 4 * jt + jj ;
+            T *cb = colbuf + (jj & 1) * POTRF_NB ;
+            if (tj == jt)
+            {
+                #pragma unroll
+                for (int i = 0 ; i < 4 ; i++) cb [4 * ti + i] = a [i][jj] ;
+            }
+            __syncthreads () ;
+            const T d = cb [j] ;
+            if (threadIdx.x == 0)
+            {
+                dvec [j] = d ;
+                if (j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+            }
+            const T rd = (T) 1 / d ;
+            T ar [4], ac [4] ;
+            #pragma unroll
+            for (int i = 0 ; i < 4 ; i++) { ar [i] = cb [4 * ti + i] ; ac [i] = cb [4 * tj + i] * rd ; }
+            if (ti >= tj && tj >= jt)
+            {
+                #pragma unroll
+                for (int jc = 0 ; jc < 4 ; jc++)
+                {
+                    if (tj > jt || jc > jj)
+                    {
+                        #pragma unroll
+                        for (int i = 0 ; i < 4 ; i++) a [i][jc] -= ar [i] * ac [jc] ;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads () ;
+    if (threadIdx.x < POTRF_NB)
+    {
+        const T q = (threadIdx.x < 4 * njt) ? sqrt (dvec [threadIdx.x]) : (T) 1 ;
+        sqv [threadIdx.x] = q ;
+        rsq [threadIdx.x] = (T) 1 / q ;
+    }
+    __syncthreads () ;
+    #pragma unroll
+    for (int jc = 0 ; jc < 4 ; jc++)
+    {
+        const int c = 4 * tj + jc ;
+        const T ljj = sqv [c] ;
+        #pragma unroll
+        for (int i = 0 ; i < 4 ; i++)
+        {
+            const int r = 4 * ti + i ;
+            if (r < jb && c < jb && r >= c)
+            {
+                const T v = (r == c) ? ljj : a [i][jc] / ljj ;
+                s [c * PB_LD + r] = v ;
+                D [r + c * lda] = v ;
+            }
+        }
+    }
+    if (b.slot < 0) return ;
+    __syncthreads () ;
+    // W = L^{-1}, row by row: W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr).
+    // Column c is owned by the 4 consecutive lanes 4c..4c+3 (same warp), which split the sum.
+    {
+        const int c = threadIdx.x >> 2, part = threadIdx.x & 3 ;
+        for (int rr = 0 ; rr < jb ; rr++)
+        {
+            T acc = 0 ;
+            for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
+            acc += __shfl_xor_sync (0xffffffffu, acc, 1) ;
+            acc += __shfl_xor_sync (0xffffffffu, acc, 2) ;
+            if (part == 0 && c < jb && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? (T) 1 : (T) 0) - acc) * rsq [rr] ;
+            __syncwarp () ;
+        }
+    }
+    __syncthreads () ;
+    T *W = winv + (int64_t) b.slot * (WINV_LD * WINV_LD) ;
+    for (int e = threadIdx.x ; e < nbk * nbk ; e += 256)
+    {
+        const int r = e % nbk, c = e / nbk ;
+        T v ;
+        if (r < jb && c < jb) v = (r >= c) ? w [r * PB_LD + c] : (T) 0 ;
+        else v = (r == c) ? (T) 1 : (T) 0 ;
+        W [r + c * WINV_LD] = v ;
     }
 }
 
