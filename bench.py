@@ -10,7 +10,7 @@ reference's own host code as BASELINE.json's north_star prescribes).  Prints ONE
              library's stream: zero + scatter A + every update/potrf/trsm launch), aggregated over ranks.
   e2e        the same metric through the host-buffer C-ABI call b200_super_numeric_d: H2D of A, the
              factorization, D2H of all of L->x, timed on the host clock around the call.
-  roofline   the dominant kernel (128x128 DMMA update) against the FP64 tensor peak measured live on
+  roofline   the dominant kernel (128x64 DMMA update) against the FP64 tensor peak measured live on
              this device with a register-resident DMMA loop (MEASURED_PEAKS.json has no FP64 figure).
   cpu_baseline  the reference CPU supernodal path (oracle/_ref, all host cores) on a bounded sample.
 
@@ -253,7 +253,7 @@ def main():
     dom = max(("upd_dmma128", "upd_dmma64"), key=lambda nm: kinds[nm]["ms"])
     dk = kinds[dom]
     ach = (dk["gflop"] / 1e3) / (dk["ms"] * 1e-3) if dk["ms"] > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "k_upd_dmma<%s>" % ("128,128,32,64" if dom == "upd_dmma128" else "64,64,32,32"),
+    roofline = {"bound": "tensor", "kernel": "k_upd_dmma<%s>" % ("128,64,32,64" if dom == "upd_dmma128" else "64,64,32,32"),
                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak > 0 else None,
                 "traffic": None,
                 "peak_source": "FP64 DMMA peak measured live by b200_dmma_peak_tflops (not in MEASURED_PEAKS.json)",

@@ -217,4 +217,4 @@ K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)
 KIND_NAMES = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf16", "potrf32", "potrf64", "trsm_subst", "trsm_inv32",
               "trsm_inv64"]
-TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 128)}
+TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 64)}

@@ -101,8 +101,8 @@ bool g_attr_done [64] = {} ;
 int kernel_attrs (int device)
 {
     if (device < 64 && g_attr_done [device]) return B200_OK ;
-    CK (cudaFuncSetAttribute (k_upd_dmma<128, 128, 32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int) dmma_smem_bytes<128, 128> ()), "attr d128") ;
+    CK (cudaFuncSetAttribute (k_upd_dmma<BIG_TM, BIG_TN, 32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) dmma_smem_bytes<BIG_TM, BIG_TN> ()), "attr d128") ;
     CK (cudaFuncSetAttribute (k_upd_dmma<64, 64, 32, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) dmma_smem_bytes<64, 64> ()), "attr d64") ;
     CK (cudaFuncSetAttribute (k_trsm_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -170,7 +170,8 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                 break ;
             case K_UPD_D128:
                 if (sizeof (T) != 8) return B200_INVALID ;
-                k_upd_dmma<128, 128, 32, 64><<<(unsigned) L.count, 256, dmma_smem_bytes<128, 128> (), st>>>
+                k_upd_dmma<BIG_TM, BIG_TN, 32, 64><<<(unsigned) L.count, (BIG_TM / 32) * (BIG_TN / 64) * 32,
+                    dmma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
                     (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
                 break ;
             case K_POTRF16:

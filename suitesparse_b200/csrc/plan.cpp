@@ -34,11 +34,11 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     {
         // padded work of the two DMMA tilings; the 64-tile kernel re-reads operands twice as often
         double c64  = 1.25 * (double) (cdiv (M, 64) * 64) * (double) (cdiv (N, 64) * 64) ;
-        double c128 = (double) (cdiv (M, 128) * 128) * (double) (cdiv (N, 128) * 128) ;
+        double c128 = (double) (cdiv (M, BIG_TM) * BIG_TM) * (double) (cdiv (N, BIG_TN) * BIG_TN) ;
         cls = (c128 <= c64) ? K_UPD_D128 : K_UPD_D64 ;
     }
-    const int TM = (cls == K_UPD_SIMT) ? SIMT_TM : (cls == K_UPD_D64 ? 64 : 128) ;
-    const int TN = (cls == K_UPD_SIMT) ? SIMT_TN : (cls == K_UPD_D64 ? 64 : 128) ;
+    const int TM = (cls == K_UPD_SIMT) ? SIMT_TM : (cls == K_UPD_D64 ? 64 : BIG_TM) ;
+    const int TN = (cls == K_UPD_SIMT) ? SIMT_TN : (cls == K_UPD_D64 ? 64 : BIG_TN) ;
     const int64_t nti = cdiv (M, TM), ntj = cdiv (N, TN) ;
     // count the tiles that intersect the lower trapezoid
     int64_t ntiles = 0 ;

@@ -57,7 +57,7 @@ enum LaunchKind : int32_t
 {
     K_UPD_SIMT = 0,     // UpdTile list, 32 x 8 tiles, one warp each
     K_UPD_D64  = 1,     // UpdTile list, 64 x 64 DMMA tiles
-    K_UPD_D128 = 2,     // UpdTile list, 128 x 128 DMMA tiles
+    K_UPD_D128 = 2,     // UpdTile list, BIG_TM x BIG_TN DMMA tiles
     K_POTRF16  = 3,     // PotrfBlk list, jb <= 16
     K_POTRF32  = 4,     // PotrfBlk list, jb <= 32
     K_POTRF64  = 5,     // PotrfBlk list, jb <= 64
@@ -83,6 +83,9 @@ constexpr int POTRF_NB   = 64 ;     // width of a block column factorized by one
 constexpr int OUTER_NB   = 256 ;    // width of an outer block column (trailing updates with K = OUTER_NB)
 constexpr int TRSM_ROWS  = 128 ;    // rows per TRSM tile
 constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
+// the large DMMA tile: 128 x 64 with 4 warps of 32 x 64, two CTAs per SM so that one CTA's prologue,
+// barriers and epilogue overlap the other's tensor work
+constexpr int BIG_TM = 128, BIG_TN = 64 ;
 
 // One (descendant d, ancestor s) update: rows lpos.. of d; the first ndrow1 fall in the columns of s.
 struct Pair { int32_t d, s, lpos, ndrow1, ndrow2 ; } ;
