@@ -256,6 +256,7 @@ int refd_set_int (void *hv, const char *name, int64_t v)
     if (!strcmp (name, "nthreads_max")) { h->cm.nthreads_max = (int) v ; return 0 ; }
     if (!strcmp (name, "print")) { h->cm.print = (int) v ; return 0 ; }
     if (!strcmp (name, "try_catch")) { h->cm.try_catch = (int) v ; return 0 ; }
+    if (!strcmp (name, "useGPU")) { h->cm.useGPU = (int) v ; return 0 ; }
     return -1 ;
 }
 

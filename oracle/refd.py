@@ -32,6 +32,9 @@ _lib = None
 def _driver():
     global _lib
     if _lib is None:
+        # the reference goes into the global symbol scope, like a library an application links against,
+        # so that a preloaded libcholmod_b200_shim.so can call back into it (tests/test_gpu_dropin.py)
+        C.CDLL(os.path.join(_REF, "libcholmod_ref.so"), mode=C.RTLD_GLOBAL)
         lib = C.CDLL(os.path.join(_REF, "libref_driver.so"))
         lib.refd_open.restype = C.c_void_p
         lib.refd_open.argtypes = [C.c_int]
