@@ -119,6 +119,42 @@ int b200_upload_factor (b200_factor *f, const void *Lx) ;
  * (CHOLMOD/Supernodal/t_cholmod_super_solve_worker.c:20-303, :309-586). */
 int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
 
+/* --- one panel step without any allocation ---------------------------------------------------------
+ * This entry point has no counterpart in the reference.
+ *
+ * It exists for callers that are not allowed to reach cudaMalloc: solvers that run inside a time step or
+ * control loop and have banned allocation after start-up (cudaMalloc/cudaFree synchronize the device and
+ * have no latency bound), and applications that have given all of HBM to a pool of their own, so that an
+ * allocation made by a library fails or upsets a budget they track themselves.  Such a caller passes a
+ * device buffer it owns; the scratch the kernels need (inverse of the diagonal block, pivot flag, tile
+ * descriptors: about 49 KB) is a static __device__ array inside the library, resident on every GPU that
+ * loads the library from load time until the process exits.
+ *
+ * Work: one panel step of the blocked factorization, in place on the device.  d_panel is a column-major
+ * nrows-by-jb panel with leading dimension lda (device pointer, 8-byte aligned).  On entry its leading
+ * jb-by-jb block holds the lower triangle of a symmetric matrix A11 and the rows below hold A21; on return
+ * the leading block holds L11 with A11 = L11*L11' (strict upper triangle untouched) and the rows below hold
+ * A21 * L11^{-T} -- the dpotrf and dtrsm of t_cholmod_super_numeric_worker.c:1023 and :1175 for a supernode
+ * of jb columns.  `stream` is a cudaStream_t passed as a pointer (NULL = the default stream).  The call
+ * returns after the stream has finished the work.
+ *
+ * Limits: jb <= B200_NOALLOC_MAX_COLS and nrows <= B200_NOALLOC_MAX_ROWS; anything larger is refused with
+ * B200_TOO_LARGE and a message on stderr (the fixed scratch cannot hold it; use b200_create +
+ * b200_super_numeric_d).  B200_INVALID for a NULL panel or inconsistent sizes.
+ * Returns B200_OK, or B200_NOT_POSDEF with *info = the 1-based column of the first pivot that is not
+ * positive (LAPACK's convention; *info = 0 otherwise), or B200_GPU_PROBLEM.
+ *
+ * The device that owns d_panel must be current.  The first call on each device looks up the device address
+ * of the scratch and raises two kernel attributes; make that first call before starting any stream capture.
+ * No cudaMalloc, cudaFree or other allocating call is made, on the first call or later.
+ * All calls on a device share the one scratch array: each call rewrites every part of it that it reads
+ * (nothing is inherited from the previous call), but two calls that overlap on the GPU -- different streams,
+ * or different host threads -- race on it and corrupt each other.  Serialise them. */
+#define B200_NOALLOC_MAX_COLS 64
+#define B200_NOALLOC_MAX_ROWS 65536
+int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, int64_t jb, int64_t *info,
+    void *stream) ;
+
 /* --- diagnostics (the reference's counterparts are the BLAS_TIMER counters and cholmod_gpu_stats,
  * CHOLMOD/Check/cholmod_check.c:615-674) -------------------------------------------------------- */
 

@@ -23,7 +23,8 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_get_int", "b200_get_double", "b200_super_numeric_d", "b200_super_numeric_s",
            "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
-           "b200_dmma_peak_tflops"]
+           "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d"]
+NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
 class B200Error(RuntimeError):
@@ -63,6 +64,8 @@ def lib():
     L.b200_set_int.argtypes = [vp, C.c_char_p, i64]; L.b200_set_int.restype = cint
     L.b200_dmma_peak_tflops.argtypes = [cint, cint]; L.b200_dmma_peak_tflops.restype = dbl
     L.b200_plan_export.argtypes = [vp, C.c_char_p, vp, i64]; L.b200_plan_export.restype = i64
+    L.b200_panel_factor_noalloc_d.argtypes = [vp, i64, i64, i64, vp, vp]
+    L.b200_panel_factor_noalloc_d.restype = cint
     _lib = L
     return L
 
@@ -73,6 +76,18 @@ def device_count():
 
 def probe(device=0):
     return bool(lib().b200_probe(int(device)))
+
+
+def panel_factor_noalloc(d_panel, lda, nrows, jb, stream=0):
+    """b200_panel_factor_noalloc_d on a device pointer the caller owns (an int address).  The library
+    allocates nothing: for callers that have banned cudaMalloc after start-up or that keep all of HBM in
+    their own pool.  Returns (status, info); raises B200Error on a negative status."""
+    info = C.c_int64(0)
+    st = lib().b200_panel_factor_noalloc_d(C.c_void_p(int(d_panel)), int(lda), int(nrows), int(jb), C.byref(info),
+                                           C.c_void_p(int(stream)) if stream else None)
+    if st < 0:
+        raise B200Error(st, "b200_panel_factor_noalloc_d")
+    return int(st), int(info.value)
 
 
 def dmma_peak_tflops(device=0, iters=20000):

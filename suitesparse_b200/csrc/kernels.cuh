@@ -296,7 +296,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
 
 // Register-resident DMMA loop: the FP64 tensor peak this chip sustains (MEASURED_PEAKS.json has no FP64
 // figure, so bench.py measures the roofline denominator with this kernel on the box it runs on).
-__global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)
+static __global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)
 {
     double acc [16][2] ;
     #pragma unroll
