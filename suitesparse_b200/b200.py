@@ -226,7 +226,8 @@ TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("j
                     ("slot", "<i4")])
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
                       ("wait_ev", "<i4"), ("rec_ev", "<i4")])
-K_JOIN = 9
+K_JOIN, K_COPYOUT = 9, 10
+COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8")])
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)

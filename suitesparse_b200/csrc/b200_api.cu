@@ -48,6 +48,8 @@ struct b200_factor
 
     cudaStream_t stream = nullptr ;         // main stream: everything except the look-ahead updates
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
+    cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
+    void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
     std::vector<cudaEvent_t> plan_ev ;      // events of the plan's look-ahead schedule
     cudaEvent_t ev [8] = {} ;
     // symbolic tables
@@ -146,6 +148,19 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     }
     for (const Launch &L : P.launches)
     {
+        if (L.kind == K_COPYOUT)
+        {
+            // finished pieces of L->x leave for the caller's (pinned) buffer while later levels compute
+            if (!f->copy_dst) continue ;
+            if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (f->stream3, f->plan_ev [L.wait_ev], 0), "wait event") ;
+            for (int64_t c = L.first ; c < L.first + L.count ; c++)
+            {
+                const CopySeg &seg = P.copies [c] ;
+                CK (cudaMemcpyAsync ((char *) f->copy_dst + (size_t) seg.off * sizeof (T), Lx + seg.off,
+                    (size_t) seg.len * sizeof (T), cudaMemcpyDeviceToHost, f->stream3), "copy-out") ;
+            }
+            continue ;
+        }
         const cudaStream_t st = streams [L.stream ? 1 : 0] ;
         if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
         if (L.kind == K_JOIN || L.count <= 0)
@@ -211,7 +226,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         size_t e = 0 ;
         for (const Launch &L : P.launches)
         {
-            if (L.kind == K_JOIN || L.count <= 0) continue ;
+            if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.count <= 0) continue ;
             float ms = 0 ;
             cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
             e += 2 ;
@@ -350,6 +365,7 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         CK (cudaDeviceGetStreamPriorityRange (&lo, &hi), "priority range") ;
         CK (cudaStreamCreateWithPriority (&f->stream, cudaStreamNonBlocking, hi), "stream") ;
         CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
+        CK (cudaStreamCreateWithFlags (&f->stream3, cudaStreamNonBlocking), "stream3") ;
     }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
     std::vector<int32_t> Ls32 ((size_t) P.ssize) ;
@@ -425,6 +441,7 @@ void b200_destroy (b200_factor *f)
         for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
         cudaStreamSynchronize (f->stream2) ;
         cudaStreamDestroy (f->stream2) ;
+        if (f->stream3) { cudaStreamSynchronize (f->stream3) ; cudaStreamDestroy (f->stream3) ; }
         cudaStreamDestroy (f->stream) ;
         cudaGetLastError () ;
     }
@@ -502,6 +519,7 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
     else if (!strcmp (which, "potrf")) { src = P.potrf.data () ; bytes = P.potrf.size () * sizeof (PotrfBlk) ; }
     else if (!strcmp (which, "trsm")) { src = P.trsm.data () ; bytes = P.trsm.size () * sizeof (TrsmTile) ; }
     else if (!strcmp (which, "launches")) { src = P.launches.data () ; bytes = P.launches.size () * sizeof (Launch) ; }
+    else if (!strcmp (which, "copies")) { src = P.copies.data () ; bytes = P.copies.size () * sizeof (CopySeg) ; }
     else return -1 ;
     if (!out) return (int64_t) bytes ;
     if ((int64_t) bytes > out_bytes) return -1 ;
@@ -541,11 +559,27 @@ int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, co
 
 }   // extern "C"
 
+// pin the caller's L->x once: later factorizations into the same buffer then copy at PCIe speed
+static void ensure_registered (b200_factor *f, void *Lx, size_t bytes)
+{
+    if (f->reg_ptr == Lx && f->reg_bytes == bytes) return ;
+    if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
+    if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterDefault) == cudaSuccess)
+    {
+        f->reg_ptr = Lx ; f->reg_bytes = bytes ;
+    }
+    else cudaGetLastError () ;
+}
+
+// host_dst != NULL: finished parts of the factor are copied to host_dst [0..xsize) while the rest is still
+// being computed (the plan's K_COPYOUT schedule); on return the host copy is complete.
 template <typename T>
-static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *minor_out)
+static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *minor_out, void *host_dst = nullptr)
 {
     const Plan &P = f->plan ;
     cudaStream_t s = f->stream ;
+    f->copy_dst = host_dst ;
+    struct Reset { b200_factor *f ; ~Reset () { f->copy_dst = nullptr ; } } reset { f } ;
     const unsigned long long big = ~0ull ;
     f->kernel_launches = 0 ;
     for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
@@ -561,6 +595,7 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     CK (cudaMemcpyAsync (&minor, f->d_minor.p, sizeof (minor), cudaMemcpyDeviceToHost, s), "minor read") ;
     CK (cudaEventRecord (f->ev [4], s), "record") ;
     CK (cudaStreamSynchronize (s), "factorize") ;
+    if (host_dst) CK (cudaStreamSynchronize (f->stream3), "copy-out") ;
     cudaEventElapsedTime (&f->ms_scatter, f->ev [2], f->ev [3]) ;
     cudaEventElapsedTime (&f->ms_factor, f->ev [2], f->ev [4]) ;
     if (minor == big)
@@ -570,8 +605,11 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     }
     // not positive definite: reproduce SNW:1084-1146
     if (minor_out) *minor_out = (int64_t) minor ;
+    f->copy_dst = nullptr ;
     st = repair_not_posdef<T> (f, (int64_t) minor, beta, quick) ;
     if (st < 0) return st ;
+    if (host_dst && P.xsize > 0)     // rare path: send the repaired factor again, as a whole
+        CK (cudaMemcpyAsync (host_dst, f->d_Lx.p, (size_t) P.xsize * sizeof (T), cudaMemcpyDeviceToHost, s), "D2H repaired Lx") ;
     CK (cudaStreamSynchronize (s), "repair") ;
     return B200_NOT_POSDEF ;
 }
@@ -592,16 +630,7 @@ int b200_download_factor (b200_factor *f, void *Lx)
     if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
     size_t bytes = (size_t) f->plan.xsize * f->esize ;
     if (bytes == 0) return B200_OK ;
-    // pin the caller's buffer once: later factorizations into the same L->x then copy at PCIe speed
-    if (f->reg_ptr != Lx || f->reg_bytes != bytes)
-    {
-        if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
-        if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterDefault) == cudaSuccess)
-        {
-            f->reg_ptr = Lx ; f->reg_bytes = bytes ;
-        }
-        else cudaGetLastError () ;
-    }
+    ensure_registered (f, Lx, bytes) ;
     CK (cudaEventRecord (f->ev [5], f->stream), "record") ;
     CK (cudaMemcpyAsync (Lx, f->d_Lx.p, bytes, cudaMemcpyDeviceToHost, f->stream), "D2H Lx") ;
     CK (cudaEventRecord (f->ev [6], f->stream), "record") ;
@@ -629,10 +658,9 @@ int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
     if (!f || f->dtype != B200_DOUBLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
     int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
     if (st < 0) return st ;
-    int fst = b200_factor_device (f, beta, quick_return_if_not_posdef, minor) ;
-    if (fst < 0) return fst ;
-    st = b200_download_factor (f, Lx) ;
-    return st < 0 ? st : fst ;
+    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
+    ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (double)) ;
+    return factor_device_T<double> (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
 int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
@@ -641,10 +669,9 @@ int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
     if (!f || f->dtype != B200_SINGLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
     int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
     if (st < 0) return st ;
-    int fst = b200_factor_device (f, beta, quick_return_if_not_posdef, minor) ;
-    if (fst < 0) return fst ;
-    st = b200_download_factor (f, Lx) ;
-    return st < 0 ? st : fst ;
+    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
+    ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (float)) ;
+    return factor_device_T<float> (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
 }   // extern "C"

@@ -141,7 +141,8 @@ void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const in
 //     look-ahead:        [wait eF(T)]  Ub(T)  rec eB(T)       [wait eF(T+1)]  Ub(T+1) ...
 // Ub(T) and Ua(T+1) may touch the same columns concurrently; both only subtract with atomics.
 void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma)
+    const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma,
+    char *copied = nullptr)
 {
     int64_t maxcol = 0 ;
     for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
@@ -247,17 +248,39 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
                 any_b = true ;
             }
         }
+        // copy-out: the finished panel [J0, Jend) of every wide supernode can leave for the host now
+        const size_t copy_first = out.copies.size () ;
+        if (copied)
+        {
+            for (int64_t q = 0 ; q < ns ; q++)
+            {
+                const int64_t s = S [q] ;
+                const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
+                if (nscol <= OUTER_NB || nscol <= J0) continue ;
+                const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
+                CopySeg c ; c.off = px [s] + J0 * nsrow ; c.len = (Jend - J0) * nsrow ;
+                out.copies.push_back (c) ;
+                copied [s] = 1 ;
+            }
+        }
+        const bool any_copy = out.copies.size () > copy_first ;
         int evF = -1, evB = -1 ;
-        if (any_b)
+        if (any_b || any_copy)
         {
             // F(T) ends here on the main stream
-            evF = out.nevents++ ; evB = out.nevents++ ;
+            evF = out.nevents++ ; if (any_b) evB = out.nevents++ ;
             out.launches.back ().rec_ev = (out.launches.back ().rec_ev < 0) ? evF : out.launches.back ().rec_ev ;
             if (out.launches.back ().rec_ev != evF)
             {
                 Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evF ;
                 out.launches.push_back (J) ;
             }
+        }
+        if (any_copy)
+        {
+            Launch C = make_launch (K_COPYOUT, (int64_t) copy_first, (int64_t) (out.copies.size () - copy_first), level, 2) ;
+            C.wait_ev = evF ;
+            out.launches.push_back (C) ;
         }
         flush_tiles (out, sink, level, 0) ;                     // Ua(T), main stream
         if (any_b) flush_tiles (out, later, level, 1, evF, evB) ;  // Ub(T), look-ahead stream
@@ -418,6 +441,13 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
 
     // the launch plan, level by level: (1) every descendant update whose target lives on the level,
     // (2) the blocked factorization of the level's supernodes
+    // Copy-out schedule: from the first level above which at most 1024 supernodes remain, every level end
+    // is a checkpoint at which all maximal runs of finished, not yet copied supernodes (contiguous in L->x:
+    // the factor is postordered) are sent to the host; wide supernodes go panel by panel (plan_factor).
+    int first_ckpt = nlevels - 1 ;
+    for (int lev = 0 ; lev < nlevels ; lev++)
+        if (nsuper - P.level_ptr [lev+1] <= 1024) { first_ckpt = lev ; break ; }
+    std::vector<char> copied ((size_t) nsuper, 0) ;
     TileSink sink ;
     std::vector<int64_t> ncols ;
     for (int lev = 0 ; lev < nlevels ; lev++)
@@ -428,7 +458,30 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         flush_tiles (P, sink, lev) ;
         ncols.resize ((size_t) ns) ;
         for (int64_t q = 0 ; q < ns ; q++) ncols [q] = super [S [q] + 1] - super [S [q]] ;
-        plan_factor (P, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma) ;
+        const bool ckpt = lev >= first_ckpt ;
+        plan_factor (P, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr) ;
+        if (ckpt)
+        {
+            const size_t copy_first = P.copies.size () ;
+            for (int64_t s = 0 ; s < nsuper ; )
+            {
+                if (copied [s] || P.level [s] > lev) { s++ ; continue ; }
+                int64_t e = s ;
+                while (e < nsuper && !copied [e] && P.level [e] <= lev) copied [e++] = 1 ;
+                CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ;
+                P.copies.push_back (c) ;
+                s = e ;
+            }
+            if (P.copies.size () > copy_first)
+            {
+                const int evL = P.nevents++ ;
+                Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evL ;
+                P.launches.push_back (J) ;
+                Launch C = make_launch (K_COPYOUT, (int64_t) copy_first, (int64_t) (P.copies.size () - copy_first), lev, 2) ;
+                C.wait_ev = evL ;
+                P.launches.push_back (C) ;
+            }
+        }
     }
     if (P.items.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;
     return B200_OK ;

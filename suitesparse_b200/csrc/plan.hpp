@@ -66,6 +66,7 @@ enum LaunchKind : int32_t
     K_TRSM_INV64 = 8,   // TrsmTile list, product with the inverse of a <= 64-wide block
     K_NKINDS   = 9,
     K_JOIN     = 9,     // no kernel: only the launch's wait_ev / rec_ev are honoured
+    K_COPYOUT  = 10,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
 } ;
 
 struct Launch
@@ -74,7 +75,8 @@ struct Launch
     int32_t count ;     // number of list entries
     int64_t first ;     // first entry in the kind's list
     int32_t level ;     // etree level this launch belongs to
-    int32_t stream ;    // 0 = main (panel) stream, 1 = look-ahead stream of the wide trailing updates
+    int32_t stream ;    // 0 = main (panel) stream, 1 = look-ahead stream of the wide trailing updates,
+                        // 2 = copy stream (K_COPYOUT)
     int32_t wait_ev ;   // event the stream waits for before this launch, or -1
     int32_t rec_ev ;    // event recorded on the stream after this launch, or -1
 } ;
@@ -86,6 +88,9 @@ constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
 // the large DMMA tile: 128 x 64 with 4 warps of 32 x 64, two CTAs per SM so that one CTA's prologue,
 // barriers and epilogue overlap the other's tensor work
 constexpr int BIG_TM = 128, BIG_TN = 64 ;
+
+// A finished, contiguous piece of L->x (offset and length in values) that can go to the host early.
+struct CopySeg { int64_t off, len ; } ;
 
 // One (descendant d, ancestor s) update: rows lpos.. of d; the first ndrow1 fall in the columns of s.
 struct Pair { int32_t d, s, lpos, ndrow1, ndrow2 ; } ;
@@ -110,6 +115,7 @@ struct Plan
     std::vector<PotrfBlk> potrf ;
     std::vector<TrsmTile> trsm ;
     std::vector<Launch> launches ;
+    std::vector<CopySeg> copies ;       // K_COPYOUT segments; together they cover [0, xsize) exactly once
 
     std::vector<Pair> pairs ;           // all update pairs, in descendant order
     std::vector<int64_t> pair_map ;     // [npairs] offset of the pair's relative map in relmap

@@ -46,9 +46,10 @@ def _schedule(launches, prefer):
     """Order the launches the way two CUDA streams could legally execute them: each stream in order, a
     launch with wait_ev only after that event was recorded.  prefer = 0 runs the main stream as far as
     it can before the look-ahead stream gets a turn; prefer = 1 the other way round."""
-    queues = {0: [i for i, L in enumerate(launches) if L["stream"] == 0],
-              1: [i for i, L in enumerate(launches) if L["stream"] == 1]}
-    pos, recorded, order = {0: 0, 1: 0}, set(), []
+    queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in (0, 1, 2)}
+    pos, recorded, order = {0: 0, 1: 0, 2: 0}, set(), []
+    # stream 2 is the copy stream: prefer = 0 / 1 also make it the last / the first to run when it can
+    pref = {0: (0, 1, 2), 1: (2, 1, 0)}[prefer]
     # cudaStreamWaitEvent on an event that the host has not recorded yet is a no-op: every wait must come
     # after its record in issue (= list) order
     rec_at = {int(L["rec_ev"]): i for i, L in enumerate(launches) if L["rec_ev"] >= 0}
@@ -62,9 +63,10 @@ def _schedule(launches, prefer):
         w = int(launches[queues[st][pos[st]]]["wait_ev"])
         return w < 0 or w in recorded
 
-    while pos[0] < len(queues[0]) or pos[1] < len(queues[1]):
-        st = prefer if ready(prefer) else 1 - prefer
-        assert ready(st), "dead-lock in the launch plan's event graph"
+    while any(pos[st] < len(queues[st]) for st in (0, 1, 2)):
+        cand = [st for st in pref if ready(st)]
+        assert cand, "dead-lock in the launch plan's event graph"
+        st = cand[0]
         i = queues[st][pos[st]]
         order.append(i)
         pos[st] += 1
@@ -74,9 +76,10 @@ def _schedule(launches, prefer):
     return order
 
 
-def run_plan(F, Lx, tables=None, prefer=0):
+def run_plan(F, Lx, tables=None, prefer=0, host=None):
     """Execute every launch of Factor F's plan on the flat factor array Lx.  Returns the smallest failing
-    column (what the kernels record through atomicMin) or None."""
+    column (what the kernels record through atomicMin) or None.  With `host` (an array like Lx filled with
+    NaN) the K_COPYOUT launches copy their segments into it at the moment the schedule reaches them."""
     if tables is None:
         tables = dict(items=F.plan_table("items", b200.ITEM_DT), tiles=F.plan_table("tiles", b200.TILE_DT),
                       potrf=F.plan_table("potrf", b200.POTRF_DT), trsm=F.plan_table("trsm", b200.TRSM_DT),
@@ -91,6 +94,14 @@ def run_plan(F, Lx, tables=None, prefer=0):
         L = launches[idx]
         kind, cnt, first = int(L["kind"]), int(L["count"]), int(L["first"])
         if kind == b200.K_JOIN:
+            continue
+        if kind == b200.K_COPYOUT:
+            assert L["stream"] == 2
+            if host is not None:
+                for seg in F.plan_table("copies", b200.COPY_DT)[first:first + cnt]:
+                    o, ln = int(seg["off"]), int(seg["len"])
+                    assert np.all(np.isnan(host[o:o + ln])), "segment copied twice"
+                    host[o:o + ln] = Lx[o:o + ln]
             continue
         if kind in b200.TILE_SHAPE:
             TM, TN = b200.TILE_SHAPE[kind]

@@ -47,11 +47,16 @@ def test_plan_reproduces_reference_factor(kind, size, ordering):
     minor = plan_interp.run_plan(F, Lx)
     assert minor is None
     assert c.rel_err(Lx) <= 1e-12
-    # the other legal interleaving of the main and the look-ahead stream gives the same factor
+    # the other legal interleaving of the main, look-ahead and copy streams gives the same factor, and the
+    # copy-out schedule delivers every value of L->x exactly once and only after it is final
     Lx2 = np.zeros(c.sym["xsize"])
+    host = np.full(c.sym["xsize"], np.nan)
     plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx2)
-    assert plan_interp.run_plan(F, Lx2, prefer=1) is None
+    assert plan_interp.run_plan(F, Lx2, prefer=1, host=host) is None
     assert c.rel_err(Lx2) <= 1e-12
+    assert np.array_equal(host, Lx2)
+    copies = F.plan_table("copies", b200.COPY_DT)
+    assert copies["len"].sum() == c.sym["xsize"] and copies.size <= 1024 + 4 * F.geti("nlaunches")
     # the plan's flop count is the supernodal formula of SURVEY.md 8d: never below Common->fl's leading terms
     assert F.getd("flops_executed") > 0
     F.close()
