@@ -62,6 +62,22 @@ int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes) ;
 b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
     const int64_t *px, const int64_t *s, int dtype, int device, int *status) ;
 
+/* --- one factorization spread over the GPUs of one box (the reference has no counterpart: "this version
+ * of CHOLMOD can only utilize a single GPU", CHOLMOD/GPU/cholmod_gpu.c:138-143) ------------------------
+ * One process per GPU.  Every rank calls b200_create_dist with the same symbolic factor, its own
+ * device, the number of ranks and its rank, and gets its share of one common plan: the supernodal etree
+ * is cut into independent subtrees, each owned by one rank, and a top part (the big separators) whose
+ * supernodes are split over all ranks by 256-column blocks (1-D block cyclic).  Finished subtrees and
+ * finished panels of the top part are broadcast from their owner with ncclBroadcast, so at the end every
+ * rank holds the whole factor.  Rank 0 makes a NCCL unique id (b200_comm_unique_id, 128 bytes), the host
+ * program carries it to the other ranks by any means (torch.distributed, MPI, a file), and every rank
+ * calls b200_comm_init before the first factorization.  All ranks must then make the same sequence of
+ * b200_factor_device / b200_super_numeric_* calls.  nranks == 1 is b200_create. */
+b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
+    const int64_t *px, const int64_t *s, int dtype, int device, int nranks, int rank, int *status) ;
+int b200_comm_unique_id (void *id128) ;
+int b200_comm_init (b200_factor *f, const void *id128) ;
+
 /* Release everything.  Replaces cholmod_l_gpu_deallocate / gpu_end (cholmod_gpu.c:187-228, :319-420). */
 void b200_destroy (b200_factor *f) ;
 

@@ -23,7 +23,8 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_get_int", "b200_get_double", "b200_super_numeric_d", "b200_super_numeric_s",
            "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
-           "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d"]
+           "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
+           "b200_comm_init"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -66,6 +67,10 @@ def lib():
     L.b200_plan_export.argtypes = [vp, C.c_char_p, vp, i64]; L.b200_plan_export.restype = i64
     L.b200_panel_factor_noalloc_d.argtypes = [vp, i64, i64, i64, vp, vp]
     L.b200_panel_factor_noalloc_d.restype = cint
+    L.b200_create_dist.argtypes = [i64, i64, vp, vp, vp, vp, cint, cint, cint, cint, vp]
+    L.b200_create_dist.restype = vp
+    L.b200_comm_unique_id.argtypes = [vp]; L.b200_comm_unique_id.restype = cint
+    L.b200_comm_init.argtypes = [vp, vp]; L.b200_comm_init.restype = cint
     _lib = L
     return L
 
@@ -90,6 +95,15 @@ def panel_factor_noalloc(d_panel, lda, nrows, jb, stream=0):
     return int(st), int(info.value)
 
 
+def comm_unique_id():
+    """A fresh NCCL unique id (128 bytes) for b200_comm_init; made by rank 0, carried to the others."""
+    buf = (C.c_char * 128)()
+    st = lib().b200_comm_unique_id(buf)
+    if st < 0:
+        raise B200Error(st, "b200_comm_unique_id")
+    return bytes(buf)
+
+
 def dmma_peak_tflops(device=0, iters=20000):
     """Measured FP64 tensor (DMMA) peak of the device in TFLOP/s."""
     return float(lib().b200_dmma_peak_tflops(int(device), int(iters)))
@@ -106,7 +120,7 @@ class Factor:
     cholmod_analyze with a supernodal strategy).  device=-1 builds the host-side plan only.
     """
 
-    def __init__(self, sym, dtype=np.float64, device=0):
+    def __init__(self, sym, dtype=np.float64, device=0, nranks=1, rank=0):
         self.L = lib()
         self.n, self.nsuper = int(sym["n"]), int(sym["nsuper"])
         self.dtype = np.dtype(dtype)
@@ -114,9 +128,10 @@ class Factor:
             raise ValueError("dtype must be float64 or float32")
         sup, pi, px, s = _i64(sym["super"]), _i64(sym["pi"]), _i64(sym["px"]), _i64(sym["s"])
         st = C.c_int(0)
-        self.h = self.L.b200_create(self.n, self.nsuper, sup.ctypes.data, pi.ctypes.data, px.ctypes.data,
-                                    s.ctypes.data, DOUBLE if self.dtype == np.float64 else SINGLE,
-                                    int(device), C.byref(st))
+        self.nranks, self.rank = int(nranks), int(rank)
+        self.h = self.L.b200_create_dist(self.n, self.nsuper, sup.ctypes.data, pi.ctypes.data, px.ctypes.data,
+                                         s.ctypes.data, DOUBLE if self.dtype == np.float64 else SINGLE,
+                                         int(device), self.nranks, self.rank, C.byref(st))
         if not self.h:
             raise B200Error(st.value, "b200_create")
         self.xsize = self.geti("xsize")
@@ -138,6 +153,21 @@ class Factor:
 
     def getd(self, name):
         return float(self.L.b200_get_double(self.h, name.encode()))
+
+    def comm_init(self, unique_id):
+        """Join the NCCL communicator of a distributed plan (every rank, same 128-byte id)."""
+        buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
+        st = self.L.b200_comm_init(self.h, buf)
+        if st < 0:
+            raise B200Error(st, "b200_comm_init")
+
+    def comm_init_torch(self, group=None):
+        """Bootstrap the communicator through torch.distributed: rank 0 makes the id, everyone gets it."""
+        import torch
+        import torch.distributed as dist
+        ids = [comm_unique_id() if self.rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, group=group)
+        self.comm_init(ids[0])
 
     def seti(self, name, value):
         st = self.L.b200_set_int(self.h, name.encode(), int(value))
@@ -226,7 +256,8 @@ TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("j
                     ("slot", "<i4")])
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
                       ("wait_ev", "<i4"), ("rec_ev", "<i4")])
-K_JOIN, K_COPYOUT = 9, 10
+K_JOIN, K_COPYOUT, K_BCAST = 9, 10, 11
+BCAST_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("root", "<i4"), ("pad", "<i4")])
 COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8")])
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)

@@ -9,8 +9,54 @@
 #include <cstring>
 #include <new>
 #include <vector>
+#include <dlfcn.h>
+#include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
 
 using namespace b200 ;
+
+namespace {
+
+// NCCL entry points, resolved at run time from the libnccl.so.2 already in the process (torch's) or the
+// system one.  Only the multi-GPU path (b200_comm_*, K_BCAST) touches them.
+struct NcclApi
+{
+    void *handle = nullptr ;
+    ncclResult_t (*GetUniqueId) (ncclUniqueId *) = nullptr ;
+    ncclResult_t (*CommInitRank) (ncclComm_t *, int, ncclUniqueId, int) = nullptr ;
+    ncclResult_t (*CommDestroy) (ncclComm_t) = nullptr ;
+    ncclResult_t (*Broadcast) (const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr ;
+    ncclResult_t (*AllReduce) (const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr ;
+    ncclResult_t (*GroupStart) () = nullptr ;
+    ncclResult_t (*GroupEnd) () = nullptr ;
+    const char *(*GetErrorString) (ncclResult_t) = nullptr ;
+    bool ok = false ;
+} ;
+
+NcclApi *nccl_api ()
+{
+    static NcclApi api ;
+    static bool tried = false ;
+    if (tried) return api.ok ? &api : nullptr ;
+    tried = true ;
+    api.handle = dlopen ("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL) ;
+    if (!api.handle) api.handle = dlopen ("libnccl.so", RTLD_NOW | RTLD_GLOBAL) ;
+    if (!api.handle) { fprintf (stderr, "cholmod_b200: cannot load libnccl.so.2: %s\n", dlerror ()) ; return nullptr ; }
+    #define B200_NCCL_SYM(field, name) *(void **) (&api.field) = dlsym (api.handle, name)
+    B200_NCCL_SYM (GetUniqueId, "ncclGetUniqueId") ;
+    B200_NCCL_SYM (CommInitRank, "ncclCommInitRank") ;
+    B200_NCCL_SYM (CommDestroy, "ncclCommDestroy") ;
+    B200_NCCL_SYM (Broadcast, "ncclBroadcast") ;
+    B200_NCCL_SYM (AllReduce, "ncclAllReduce") ;
+    B200_NCCL_SYM (GroupStart, "ncclGroupStart") ;
+    B200_NCCL_SYM (GroupEnd, "ncclGroupEnd") ;
+    B200_NCCL_SYM (GetErrorString, "ncclGetErrorString") ;
+    #undef B200_NCCL_SYM
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.AllReduce
+        && api.GroupStart && api.GroupEnd && api.GetErrorString ;
+    return api.ok ? &api : nullptr ;
+}
+
+}   // namespace
 
 namespace {
 
@@ -50,6 +96,7 @@ struct b200_factor
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
     cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
     void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
+    ncclComm_t comm = nullptr ;             // multi-GPU: communicator over the ranks of the plan (b200_comm_init)
     std::vector<cudaEvent_t> plan_ev ;      // events of the plan's look-ahead schedule
     cudaEvent_t ev [8] = {} ;
     // symbolic tables
@@ -72,6 +119,7 @@ struct b200_factor
     void *reg_ptr = nullptr ; size_t reg_bytes = 0 ;
 
     int64_t kernel_launches = 0 ;
+    int64_t nccl_calls = 0 ;
     int profile = 0 ;                       // 1: bracket every launch with events (diagnostic runs only)
     std::vector<cudaEvent_t> prof_ev ;
     double ms_kind [K_NKINDS] = {} ;
@@ -163,6 +211,24 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         }
         const cudaStream_t st = streams [L.stream ? 1 : 0] ;
         if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
+        if (L.kind == K_BCAST)
+        {
+            // finished panels / subtrees travel from their owner to every other rank over NVLink
+            NcclApi *nc = nccl_api () ;
+            if (!nc || !f->comm) { fprintf (stderr, "cholmod_b200: distributed plan without b200_comm_init\n") ; return B200_INVALID ; }
+            const ncclDataType_t dt = (sizeof (T) == 8) ? ncclDouble : ncclFloat ;
+            nc->GroupStart () ;
+            for (int64_t c = L.first ; c < L.first + L.count ; c++)
+            {
+                const BcastSeg &seg = P.bcasts [c] ;
+                ncclResult_t r = nc->Broadcast (Lx + seg.off, Lx + seg.off, (size_t) seg.len, dt, seg.root, f->comm, st) ;
+                if (r != ncclSuccess) { nc->GroupEnd () ; fprintf (stderr, "cholmod_b200: ncclBroadcast: %s\n", nc->GetErrorString (r)) ; return B200_GPU_PROBLEM ; }
+            }
+            if (nc->GroupEnd () != ncclSuccess) return B200_GPU_PROBLEM ;
+            f->nccl_calls += L.count ;
+            if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
+            continue ;
+        }
         if (L.kind == K_JOIN || L.count <= 0)
         {
             if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
@@ -226,7 +292,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         size_t e = 0 ;
         for (const Launch &L : P.launches)
         {
-            if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.count <= 0) continue ;
+            if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.kind == K_BCAST || L.count <= 0) continue ;
             float ms = 0 ;
             cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
             e += 2 ;
@@ -397,6 +463,12 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
 b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
     const int64_t *px, const int64_t *s, int dtype, int device, int *status)
 {
+    return b200_create_dist (n, nsuper, super, pi, px, s, dtype, device, 1, 0, status) ;
+}
+
+b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
+    const int64_t *px, const int64_t *s, int dtype, int device, int nranks, int rank, int *status)
+{
     int dummy ; if (!status) status = &dummy ;
     *status = B200_OK ;
     if (dtype != B200_DOUBLE && dtype != B200_SINGLE) { *status = B200_INVALID ; return nullptr ; }
@@ -405,7 +477,7 @@ b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const
     f->dtype = dtype ; f->esize = (dtype == B200_DOUBLE) ? 8 : 4 ; f->device = device ;
     try
     {
-        *status = build_plan (n, nsuper, super, pi, px, s, dtype == B200_DOUBLE, f->plan) ;
+        *status = build_plan (n, nsuper, super, pi, px, s, dtype == B200_DOUBLE, f->plan, nranks, rank) ;
         if (*status == B200_OK)
         {
             f->h_super.assign (super, super + nsuper + 1) ;
@@ -439,6 +511,7 @@ void b200_destroy (b200_factor *f)
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
         for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
+        if (f->comm) { NcclApi *nc = nccl_api () ; if (nc) nc->CommDestroy (f->comm) ; f->comm = nullptr ; }
         cudaStreamSynchronize (f->stream2) ;
         cudaStreamDestroy (f->stream2) ;
         if (f->stream3) { cudaStreamSynchronize (f->stream3) ; cudaStreamDestroy (f->stream3) ; }
@@ -470,7 +543,11 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "device")) return f->device ;
     if (!strcmp (name, "dtype")) return f->dtype ;
     if (!strcmp (name, "kernel_launches")) return f->kernel_launches ;
-    if (!strcmp (name, "ngpus")) return f->device >= 0 ? 1 : 0 ;
+    if (!strcmp (name, "ngpus")) return P.nranks ;
+    if (!strcmp (name, "rank")) return P.rank ;
+    if (!strcmp (name, "nccl_calls")) return f->nccl_calls ;
+    if (!strcmp (name, "nbcasts")) return (int64_t) P.bcasts.size () ;
+    if (!strcmp (name, "ntop")) { int64_t c = 0 ; for (char t : P.top) c += t ; return c ; }
     if (!strcmp (name, "profile")) return f->profile ;
     if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] < '0' + K_NKINDS) return f->launches_kind [name [13] - '0'] ;
     if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.count_kind [name [10] - '0'] ;
@@ -520,11 +597,45 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
     else if (!strcmp (which, "trsm")) { src = P.trsm.data () ; bytes = P.trsm.size () * sizeof (TrsmTile) ; }
     else if (!strcmp (which, "launches")) { src = P.launches.data () ; bytes = P.launches.size () * sizeof (Launch) ; }
     else if (!strcmp (which, "copies")) { src = P.copies.data () ; bytes = P.copies.size () * sizeof (CopySeg) ; }
+    else if (!strcmp (which, "bcasts")) { src = P.bcasts.data () ; bytes = P.bcasts.size () * sizeof (BcastSeg) ; }
+    else if (!strcmp (which, "owner")) { src = P.owner.data () ; bytes = P.owner.size () * sizeof (int32_t) ; }
+    else if (!strcmp (which, "top")) { src = P.top.data () ; bytes = P.top.size () ; }
     else return -1 ;
     if (!out) return (int64_t) bytes ;
     if ((int64_t) bytes > out_bytes) return -1 ;
     if (bytes) memcpy (out, src, bytes) ;
     return (int64_t) bytes ;
+}
+
+int b200_comm_unique_id (void *id128)
+{
+    NcclApi *nc = nccl_api () ;
+    if (!nc || !id128) return B200_GPU_PROBLEM ;
+    static_assert (sizeof (ncclUniqueId) == 128, "ncclUniqueId is 128 bytes") ;
+    ncclUniqueId id ;
+    if (nc->GetUniqueId (&id) != ncclSuccess) return B200_GPU_PROBLEM ;
+    memcpy (id128, &id, sizeof (id)) ;
+    return B200_OK ;
+}
+
+int b200_comm_init (b200_factor *f, const void *id128)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!id128) return B200_INVALID ;
+    if (f->plan.nranks <= 1) return B200_OK ;
+    NcclApi *nc = nccl_api () ;
+    if (!nc) return B200_GPU_PROBLEM ;
+    if (f->comm) { nc->CommDestroy (f->comm) ; f->comm = nullptr ; }
+    ncclUniqueId id ;
+    memcpy (&id, id128, sizeof (id)) ;
+    ncclResult_t r = nc->CommInitRank (&f->comm, f->plan.nranks, id, f->plan.rank) ;
+    if (r != ncclSuccess)
+    {
+        fprintf (stderr, "cholmod_b200: ncclCommInitRank: %s\n", nc->GetErrorString (r)) ;
+        f->comm = nullptr ;
+        return B200_GPU_PROBLEM ;
+    }
+    return B200_OK ;
 }
 
 int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
@@ -581,7 +692,7 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     f->copy_dst = host_dst ;
     struct Reset { b200_factor *f ; ~Reset () { f->copy_dst = nullptr ; } } reset { f } ;
     const unsigned long long big = ~0ull ;
-    f->kernel_launches = 0 ;
+    f->kernel_launches = 0 ; f->nccl_calls = 0 ;
     for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
     CK (cudaEventRecord (f->ev [2], s), "record") ;
     CK (cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, s), "minor init") ;
@@ -591,6 +702,13 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     CK (cudaEventRecord (f->ev [3], s), "record") ;
     st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p) ;
     if (st) return st ;
+    if (P.nranks > 1)
+    {
+        // the smallest failing column over all ranks is L->minor
+        NcclApi *nc = nccl_api () ;
+        if (!nc || !f->comm) return B200_INVALID ;
+        if (nc->AllReduce (f->d_minor.p, f->d_minor.p, 1, ncclUint64, ncclMin, f->comm, s) != ncclSuccess) return B200_GPU_PROBLEM ;
+    }
     unsigned long long minor = big ;
     CK (cudaMemcpyAsync (&minor, f->d_minor.p, sizeof (minor), cudaMemcpyDeviceToHost, s), "minor read") ;
     CK (cudaEventRecord (f->ev [4], s), "record") ;

@@ -8,6 +8,7 @@
 #include "../../include/cholmod_b200.h"
 #include <algorithm>
 #include <cstring>
+#include <numeric>
 
 namespace b200 {
 
@@ -20,6 +21,22 @@ struct TileSink
 } ;
 
 inline int64_t cdiv (int64_t a, int64_t b) { return (a + b - 1) / b ; }
+
+// Who does what.  `D` carries the distribution (Plan::nranks/rank/top/owner); a repair plan is built
+// with local == true: every rank then does everything itself on its own complete copy of the factor.
+struct Own
+{
+    const Plan *D ;
+    bool local ;
+    bool dist () const { return !local && D->nranks > 1 ; }
+    bool is_top (int64_t s) const { return dist () && D->top [s] ; }
+    int block_owner (int64_t s, int64_t T) const
+    {
+        if (!dist ()) return D->rank ;
+        return D->top [s] ? (int) ((D->owner [s] + T) % D->nranks) : D->owner [s] ;
+    }
+    bool mine (int64_t s, int64_t T) const { return block_owner (s, T) == D->rank ; }
+} ;
 
 // choose the kernel class of an item and emit its tiles
 void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bool use_dmma)
@@ -75,6 +92,12 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     }
 }
 
+void add_item (Plan &P, const UpdItem &it, TileSink &sink, bool use_dmma)
+{
+    P.items.push_back (it) ;
+    emit_tiles (P, (int32_t) (P.items.size () - 1), it, sink, use_dmma) ;
+}
+
 Launch make_launch (int kind, int64_t first, int64_t count, int level, int stream)
 {
     Launch L ;
@@ -103,10 +126,15 @@ void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_e
     P.launches.back ().rec_ev = rec_ev ;
 }
 
-// the descendant updates into supernode s
-void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const int64_t *pi,
+// The descendant updates into supernode s.  A target that is split over the ranks (top) gets each update
+// as slabs of target columns, one slab per outer block, and this rank keeps the slabs of the blocks it
+// owns: a slab [ja, jb) of an item is the item of the panel rows ja.. (B = its first jb-ja rows), so the
+// same kernels apply.
+void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t *super, const int64_t *pi,
     const int64_t *px, int64_t s, TileSink &sink, bool use_dmma)
 {
+    const bool split = own.is_top (s) ;
+    if (!split && !own.mine (s, 0)) return ;
     for (int64_t t = P.target_ptr [s] ; t < P.target_ptr [s+1] ; t++)
     {
         const int32_t pid = P.target_list [t] ;
@@ -120,8 +148,22 @@ void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const in
         it.map_off = P.pair_map [pid] ;
         it.M = pr.ndrow2 ; it.N = pr.ndrow1 ; it.K = (int32_t) (super [d+1] - super [d]) ;
         it.pad = 0 ;
-        out.items.push_back (it) ;
-        emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+        if (!split) { add_item (out, it, sink, use_dmma) ; continue ; }
+        const int32_t *map = P.relmap.data () + it.map_off ;    // map [j] < nscol (s) for j < N
+        for (int64_t ja = 0 ; ja < it.N ; )
+        {
+            const int64_t T = map [ja] / OUTER_NB ;
+            int64_t jb = ja + 1 ;
+            while (jb < it.N && map [jb] / OUTER_NB == T) jb++ ;
+            if (own.mine (s, T))
+            {
+                UpdItem sl = it ;
+                sl.a_off = it.a_off + ja ; sl.map_off = it.map_off + ja ;
+                sl.M = (int32_t) (it.M - ja) ; sl.N = (int32_t) (jb - ja) ;
+                add_item (out, sl, sink, use_dmma) ;
+            }
+            ja = jb ;
+        }
     }
 }
 
@@ -137,10 +179,14 @@ void plan_updates_into (Plan &out, const Plan &P, const int64_t *super, const in
 // Look-ahead: the outer update of block T is split into Ua (columns of outer block T+1, main stream) and
 // Ub (all later columns, look-ahead stream).  The panel chain F(T+1) = {potrf, trsm, inner updates} then
 // runs on the main stream while Ub(T) fills the machine:
-//     main:        F(T)  rec eF(T)   Ua(T)   [wait eB(T-1)]  F(T+1)  rec eF(T+1)  Ua(T+1) ...
-//     look-ahead:        [wait eF(T)]  Ub(T)  rec eB(T)       [wait eF(T+1)]  Ub(T+1) ...
+//     main:        F(T)  [bcast T]  rec eF(T)   Ua(T)   [wait eB(T-1)]  F(T+1)  rec eF(T+1)  Ua(T+1) ...
+//     look-ahead:                   [wait eF(T)]  Ub(T)  rec eB(T)       [wait eF(T+1)]  Ub(T+1) ...
 // Ub(T) and Ua(T+1) may touch the same columns concurrently; both only subtract with atomics.
-void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int64_t *px,
+//
+// Distributed (top) supernodes: block T is factorized by its owner and then broadcast (K_BCAST, issued
+// by every rank in the same order); Ua(T) is done by the owner of block T+1 and Ub(T) as one slab per
+// later block by that block's owner -- a 1-D block-cyclic right-looking Cholesky.
+void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma,
     char *copied = nullptr)
 {
@@ -151,6 +197,7 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
     int evB_prev = -1, evB_prev2 = -1 ; // eB(T-1), eB(T-2)
     for (int64_t J0 = 0 ; J0 < maxcol ; J0 += OUTER_NB)
     {
+        const int64_t T = J0 / OUTER_NB ;
         // ---- F(T): the panel chain of outer block T -------------------------------------------------
         // it reads columns that Ub(T-2) and earlier wrote; Ub(T-1) is only needed by F(T+1)
         int pending_wait = evB_prev2 ;
@@ -164,7 +211,7 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
             {
                 const int64_t s = S [q] ;
                 const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
-                if (nscol <= j0) continue ;
+                if (nscol <= j0 || !own.mine (s, T)) continue ;
                 const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
                 const int64_t r0 = j0 + jb ;
                 const int pcls = (jb <= 16) ? 0 : (jb <= 32) ? 1 : 2 ;
@@ -194,8 +241,7 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
                     it.a_off = px [s] + r0 + j0 * nsrow ;
                     it.c_off = px [s] + r0 + r0 * nsrow ;
                     it.M = (int32_t) (nsrow - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
-                    out.items.push_back (it) ;
-                    emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
+                    add_item (out, it, sink, use_dmma) ;
                 }
             }
             out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
@@ -218,6 +264,32 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
             }
             flush_tiles (out, sink, level) ;
         }
+        if (pending_wait >= 0)
+        {
+            // this rank had no panel work in block T: the wait still has to be honoured before the
+            // broadcast / updates below may overwrite or read what Ub(T-2) touched
+            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = pending_wait ;
+            out.launches.push_back (J) ;
+            pending_wait = -1 ;
+        }
+
+        // ---- distributed supernodes: the owner of block T sends the finished panel to everyone -----------
+        {
+            const size_t first = out.bcasts.size () ;
+            for (int64_t q = 0 ; q < ns ; q++)
+            {
+                const int64_t s = S [q] ;
+                const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
+                if (nscol <= J0 || !own.is_top (s)) continue ;
+                const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
+                BcastSeg b ;
+                b.off = px [s] + J0 * nsrow ; b.len = (Jend - J0) * nsrow ;
+                b.root = own.block_owner (s, T) ; b.pad = 0 ;
+                out.bcasts.push_back (b) ;
+            }
+            if (out.bcasts.size () > first)
+                out.launches.push_back (make_launch (K_BCAST, (int64_t) first, (int64_t) (out.bcasts.size () - first), level, 0)) ;
+        }
 
         // ---- outer update of block T -------------------------------------------------------------------
         const int64_t Jn = J0 + OUTER_NB ;      // first column of the next outer block
@@ -232,23 +304,40 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
             it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ; it.K = (int32_t) OUTER_NB ;
             // Ua: columns [Jn, Jn2) -- the next panel
             const int64_t Jn2 = std::min<int64_t> (nscol, Jn + OUTER_NB) ;
-            it.a_off = px [s] + Jn + J0 * nsrow ;
-            it.c_off = px [s] + Jn + Jn * nsrow ;
-            it.M = (int32_t) (nsrow - Jn) ; it.N = (int32_t) (Jn2 - Jn) ;
-            out.items.push_back (it) ;
-            emit_tiles (out, (int32_t) (out.items.size () - 1), it, sink, use_dmma) ;
-            // Ub: columns [Jn2, nscol) -- everything after the next panel
-            if (Jn2 < nscol)
+            if (own.mine (s, T + 1))
             {
+                it.a_off = px [s] + Jn + J0 * nsrow ;
+                it.c_off = px [s] + Jn + Jn * nsrow ;
+                it.M = (int32_t) (nsrow - Jn) ; it.N = (int32_t) (Jn2 - Jn) ;
+                add_item (out, it, sink, use_dmma) ;
+            }
+            if (Jn2 >= nscol) continue ;
+            // Ub: columns [Jn2, nscol) -- everything after the next panel
+            if (!own.is_top (s))
+            {
+                if (!own.mine (s, 0)) continue ;
                 it.a_off = px [s] + Jn2 + J0 * nsrow ;
                 it.c_off = px [s] + Jn2 + Jn2 * nsrow ;
                 it.M = (int32_t) (nsrow - Jn2) ; it.N = (int32_t) (nscol - Jn2) ;
-                out.items.push_back (it) ;
-                emit_tiles (out, (int32_t) (out.items.size () - 1), it, later, use_dmma) ;
+                add_item (out, it, later, use_dmma) ;
                 any_b = true ;
             }
+            else
+            {
+                // one slab per later outer block, done by the rank that owns the block
+                for (int64_t Jc = Jn2 ; Jc < nscol ; Jc += OUTER_NB)
+                {
+                    if (!own.mine (s, Jc / OUTER_NB)) continue ;
+                    const int64_t Je = std::min<int64_t> (nscol, Jc + OUTER_NB) ;
+                    it.a_off = px [s] + Jc + J0 * nsrow ;
+                    it.c_off = px [s] + Jc + Jc * nsrow ;
+                    it.M = (int32_t) (nsrow - Jc) ; it.N = (int32_t) (Je - Jc) ;
+                    add_item (out, it, later, use_dmma) ;
+                    any_b = true ;
+                }
+            }
         }
-        // copy-out: the finished panel [J0, Jend) of every wide supernode can leave for the host now
+        // copy-out: the finished panel [J0, Jend) of every wide supernode this rank holds can go to the host
         const size_t copy_first = out.copies.size () ;
         if (copied)
         {
@@ -257,6 +346,7 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
                 const int64_t s = S [q] ;
                 const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
                 if (nscol <= OUTER_NB || nscol <= J0) continue ;
+                if (!own.is_top (s) && !own.mine (s, 0)) continue ;     // arrives later, with its subtree
                 const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
                 CopySeg c ; c.off = px [s] + J0 * nsrow ; c.len = (Jend - J0) * nsrow ;
                 out.copies.push_back (c) ;
@@ -267,10 +357,11 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
         int evF = -1, evB = -1 ;
         if (any_b || any_copy)
         {
-            // F(T) ends here on the main stream
+            // F(T) (and its broadcast) end here on the main stream
             evF = out.nevents++ ; if (any_b) evB = out.nevents++ ;
-            out.launches.back ().rec_ev = (out.launches.back ().rec_ev < 0) ? evF : out.launches.back ().rec_ev ;
-            if (out.launches.back ().rec_ev != evF)
+            if (!out.launches.empty () && out.launches.back ().stream == 0 && out.launches.back ().rec_ev < 0)
+                out.launches.back ().rec_ev = evF ;
+            else
             {
                 Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evF ;
                 out.launches.push_back (J) ;
@@ -286,13 +377,6 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
         if (any_b) flush_tiles (out, later, level, 1, evF, evB) ;  // Ub(T), look-ahead stream
         evB_prev2 = evB_prev ;
         evB_prev = evB ;
-        // F(T+1) must see Ub(T-1); F(T+2) must see Ub(T): keep both pending events alive
-        if (pending_wait >= 0)
-        {
-            // no launch of F(T) consumed the wait (cannot happen: every outer block has a potrf)
-            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = pending_wait ;
-            out.launches.push_back (J) ;
-        }
     }
     // the main stream joins the look-ahead stream before anything else uses these supernodes
     for (int ev : { evB_prev2, evB_prev })
@@ -303,15 +387,78 @@ void plan_factor (Plan &out, const int64_t *super, const int64_t *pi, const int6
     }
 }
 
+// Split the supernodal etree among the ranks: "top" = supernodes whose subtree holds more than
+// 1/(4 nranks) of all work (closed under taking ancestors); every maximal subtree below them goes, whole,
+// to the currently least loaded rank (largest first).
+int partition (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *px)
+{
+    const int64_t nsuper = P.nsuper ;
+    const int R = P.nranks ;
+    P.top.assign ((size_t) nsuper, 0) ;
+    P.owner.assign ((size_t) nsuper, 0) ;
+    P.sroot.resize ((size_t) nsuper) ;
+    std::iota (P.sroot.begin (), P.sroot.end (), 0) ;
+    if (R <= 1) return B200_OK ;
+    std::vector<double> work ((size_t) nsuper, 0.0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        double nscol = (double) (super [s+1] - super [s]), nsrow = (double) (pi [s+1] - pi [s]) ;
+        work [s] = nscol * nscol * nscol / 3.0 + nscol * nscol * (nsrow - nscol) + nsrow * nscol ;
+    }
+    for (const Pair &pr : P.pairs)
+    {
+        double K = (double) (super [pr.d+1] - super [pr.d]) ;
+        work [pr.s] += K * pr.ndrow1 * (2.0 * pr.ndrow2 - pr.ndrow1) ;
+    }
+    std::vector<double> sub (work) ;                // subtree work; children precede parents
+    std::vector<int64_t> first ((size_t) nsuper) ;
+    std::iota (first.begin (), first.end (), 0) ;
+    double total = 0 ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        int64_t p = P.parent [s] ;
+        if (p >= 0) { sub [p] += sub [s] ; first [p] = std::min (first [p], first [s]) ; }
+        else total += sub [s] ;
+    }
+    const double thresh = total / (4.0 * R) ;
+    for (int64_t s = 0 ; s < nsuper ; s++) P.top [s] = (sub [s] > thresh) ? 1 : 0 ;
+    // local subtree roots, largest first, to the least loaded rank
+    std::vector<int64_t> roots ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+        if (!P.top [s] && (P.parent [s] < 0 || P.top [P.parent [s]])) roots.push_back (s) ;
+    std::sort (roots.begin (), roots.end (), [&] (int64_t a, int64_t b) { return sub [a] != sub [b] ? sub [a] > sub [b] : a < b ; }) ;
+    std::vector<double> load ((size_t) R, 0.0) ;
+    for (int64_t r : roots)
+    {
+        int g = (int) (std::min_element (load.begin (), load.end ()) - load.begin ()) ;
+        load [g] += sub [r] ;
+        P.owner [r] = g ;
+    }
+    int ntop = 0 ;
+    for (int64_t s = nsuper - 1 ; s >= 0 ; s--)
+    {
+        if (P.top [s]) { P.owner [s] = (ntop++) % R ; continue ; }
+        int64_t p = P.parent [s] ;
+        if (p >= 0 && !P.top [p]) { P.sroot [s] = P.sroot [p] ; P.owner [s] = P.owner [p] ; }
+    }
+    // a local subtree must be one contiguous range of supernodes (the factor is postordered)
+    for (int64_t r : roots)
+        for (int64_t s = first [r] ; s <= r ; s++)
+            if (P.top [s] || P.sroot [s] != r) return B200_INVALID ;
+    (void) px ;
+    return B200_OK ;
+}
+
 }   // namespace
 
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int64_t *Ls, bool use_dmma, Plan &P)
+    const int64_t *Ls, bool use_dmma, Plan &P, int nranks, int rank)
 {
     if (n < 0 || nsuper < 0 || !super || !pi || !px || (!Ls && nsuper > 0)) return B200_INVALID ;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return B200_INVALID ;
     if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
     P = Plan () ;
-    P.n = n ; P.nsuper = nsuper ;
+    P.n = n ; P.nsuper = nsuper ; P.nranks = nranks ; P.rank = rank ;
     if (nsuper == 0)
     {
         if (n != 0) return B200_INVALID ;
@@ -439,8 +586,22 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         P.flops_trsm += nscol * nscol * (nsrow - nscol) ;
     }
 
-    // the launch plan, level by level: (1) every descendant update whose target lives on the level,
-    // (2) the blocked factorization of the level's supernodes
+    // who owns what
+    int st = partition (P, super, pi, px) ;
+    if (st != B200_OK) return st ;
+    const Own own { &P, false } ;
+    // a supernode's values are on this rank once it (top: panel by panel) or, for another rank's subtree,
+    // the root of that subtree is done
+    auto avail_level = [&] (int64_t s) -> int
+    {
+        if (nranks == 1 || P.top [s] || P.owner [s] == rank) return P.level [s] ;
+        return P.level [P.sroot [s]] ;
+    } ;
+    std::vector<int64_t> first_of ((size_t) nsuper) ;
+    std::iota (first_of.begin (), first_of.end (), 0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+        if (P.parent [s] >= 0) first_of [P.parent [s]] = std::min (first_of [P.parent [s]], first_of [s]) ;
+
     // Copy-out schedule: from the first level above which at most 1024 supernodes remain, every level end
     // is a checkpoint at which all maximal runs of finished, not yet copied supernodes (contiguous in L->x:
     // the factor is postordered) are sent to the host; wide supernodes go panel by panel (plan_factor).
@@ -448,26 +609,45 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     for (int lev = 0 ; lev < nlevels ; lev++)
         if (nsuper - P.level_ptr [lev+1] <= 1024) { first_ckpt = lev ; break ; }
     std::vector<char> copied ((size_t) nsuper, 0) ;
+
+    // the launch plan, level by level: (1) every descendant update whose target lives on the level,
+    // (2) the blocked factorization of the level's supernodes, (3) broadcasts of finished local subtrees
     TileSink sink ;
     std::vector<int64_t> ncols ;
     for (int lev = 0 ; lev < nlevels ; lev++)
     {
         const int32_t *S = P.level_list.data () + P.level_ptr [lev] ;
         const int64_t ns = P.level_ptr [lev+1] - P.level_ptr [lev] ;
-        for (int64_t q = 0 ; q < ns ; q++) plan_updates_into (P, P, super, pi, px, S [q], sink, use_dmma) ;
+        for (int64_t q = 0 ; q < ns ; q++) plan_updates_into (P, P, own, super, pi, px, S [q], sink, use_dmma) ;
         flush_tiles (P, sink, lev) ;
         ncols.resize ((size_t) ns) ;
         for (int64_t q = 0 ; q < ns ; q++) ncols [q] = super [S [q] + 1] - super [S [q]] ;
         const bool ckpt = lev >= first_ckpt ;
-        plan_factor (P, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr) ;
+        plan_factor (P, own, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr) ;
+        if (nranks > 1)
+        {
+            // every local subtree whose root was finished on this level goes to all ranks, as one range
+            const size_t first = P.bcasts.size () ;
+            for (int64_t q = 0 ; q < ns ; q++)
+            {
+                const int64_t r = S [q] ;
+                if (P.top [r] || P.sroot [r] != r) continue ;
+                BcastSeg b ;
+                b.off = px [first_of [r]] ; b.len = px [r+1] - px [first_of [r]] ;
+                b.root = P.owner [r] ; b.pad = 0 ;
+                P.bcasts.push_back (b) ;
+            }
+            if (P.bcasts.size () > first)
+                P.launches.push_back (make_launch (K_BCAST, (int64_t) first, (int64_t) (P.bcasts.size () - first), lev, 0)) ;
+        }
         if (ckpt)
         {
             const size_t copy_first = P.copies.size () ;
             for (int64_t s = 0 ; s < nsuper ; )
             {
-                if (copied [s] || P.level [s] > lev) { s++ ; continue ; }
+                if (copied [s] || avail_level (s) > lev) { s++ ; continue ; }
                 int64_t e = s ;
-                while (e < nsuper && !copied [e] && P.level [e] <= lev) copied [e++] = 1 ;
+                while (e < nsuper && !copied [e] && avail_level (e) <= lev) copied [e++] = 1 ;
                 CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ;
                 P.copies.push_back (c) ;
                 s = e ;
@@ -493,12 +673,14 @@ int build_repair_plan (const Plan &P, const int64_t *super, const int64_t *pi, c
     R = Plan () ;
     R.n = P.n ; R.nsuper = P.nsuper ; R.xsize = P.xsize ; R.ssize = P.ssize ;
     if (s < 0 || s >= P.nsuper || nscol_new < 0 || nscol_new > super [s+1] - super [s]) return B200_INVALID ;
+    // every rank repairs its own (complete) copy of the factor by itself
+    const Own own { &P, true } ;
     TileSink sink ;
-    plan_updates_into (R, P, super, pi, px, s, sink, use_dmma) ;
+    plan_updates_into (R, P, own, super, pi, px, s, sink, use_dmma) ;
     flush_tiles (R, sink, P.level [s]) ;
     const int32_t S [1] = { (int32_t) s } ;
     const int64_t nc [1] = { nscol_new } ;
-    if (nscol_new > 0) plan_factor (R, super, pi, px, S, nc, 1, P.level [s], sink, use_dmma) ;
+    if (nscol_new > 0) plan_factor (R, own, super, pi, px, S, nc, 1, P.level [s], sink, use_dmma) ;
     return B200_OK ;
 }
 

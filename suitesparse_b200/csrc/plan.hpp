@@ -67,6 +67,7 @@ enum LaunchKind : int32_t
     K_NKINDS   = 9,
     K_JOIN     = 9,     // no kernel: only the launch's wait_ev / rec_ev are honoured
     K_COPYOUT  = 10,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
+    K_BCAST    = 11,    // no kernel: BcastSeg list, ncclBroadcast of finished panels / subtrees (main stream)
 } ;
 
 struct Launch
@@ -92,6 +93,9 @@ constexpr int BIG_TM = 128, BIG_TN = 64 ;
 // A finished, contiguous piece of L->x (offset and length in values) that can go to the host early.
 struct CopySeg { int64_t off, len ; } ;
 
+// A finished, contiguous piece of L->x that its owner rank broadcasts to all other ranks.
+struct BcastSeg { int64_t off, len ; int32_t root, pad ; } ;
+
 // One (descendant d, ancestor s) update: rows lpos.. of d; the first ndrow1 fall in the columns of s.
 struct Pair { int32_t d, s, lpos, ndrow1, ndrow2 ; } ;
 
@@ -116,6 +120,16 @@ struct Plan
     std::vector<TrsmTile> trsm ;
     std::vector<Launch> launches ;
     std::vector<CopySeg> copies ;       // K_COPYOUT segments; together they cover [0, xsize) exactly once
+    std::vector<BcastSeg> bcasts ;      // K_BCAST segments (identical on every rank)
+
+    // Distribution over the GPUs of one box.  nranks == 1: everything belongs to rank 0.
+    // "top" supernodes (the separators whose subtree carries more than 1/(4 nranks) of the work) are split
+    // by outer block columns, block T of s belonging to rank (owner [s] + T) % nranks (1-D block cyclic);
+    // every other supernode belongs, with its whole subtree, to one rank.
+    int32_t nranks = 1, rank = 0 ;
+    std::vector<char> top ;             // [nsuper]
+    std::vector<int32_t> owner ;        // [nsuper] owning rank (top: the rank of outer block 0)
+    std::vector<int32_t> sroot ;        // [nsuper] root of the local subtree of a non-top supernode
 
     std::vector<Pair> pairs ;           // all update pairs, in descendant order
     std::vector<int64_t> pair_map ;     // [npairs] offset of the pair's relative map in relmap
@@ -129,8 +143,10 @@ struct Plan
 
 // Builds the plan.  Returns 0, or a negative B200_* status (invalid input / too large).
 // use_dmma = false (single precision) routes every update through the SIMT kernel class.
+// nranks > 1 builds rank `rank`'s share of the distributed plan: the same launch structure on every rank,
+// each launch holding only the blocks / tiles that rank owns, plus the K_BCAST launches all ranks share.
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int64_t *Ls, bool use_dmma, Plan &plan) ;
+    const int64_t *Ls, bool use_dmma, Plan &plan, int nranks = 1, int rank = 0) ;
 
 // SNW:1084-1146: a one-supernode plan that re-applies every descendant update to supernode s and then
 // factorizes only its first nscol_new columns (dtrsm on all rows below them).  Reuses P.relmap.

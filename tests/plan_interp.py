@@ -76,7 +76,7 @@ def _schedule(launches, prefer):
     return order
 
 
-def run_plan(F, Lx, tables=None, prefer=0, host=None):
+def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
     """Execute every launch of Factor F's plan on the flat factor array Lx.  Returns the smallest failing
     column (what the kernels record through atomicMin) or None.  With `host` (an array like Lx filled with
     NaN) the K_COPYOUT launches copy their segments into it at the moment the schedule reaches them."""
@@ -94,6 +94,12 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None):
         L = launches[idx]
         kind, cnt, first = int(L["kind"]), int(L["count"]), int(L["first"])
         if kind == b200.K_JOIN:
+            continue
+        if kind == b200.K_BCAST:
+            # bcast (off, len, root): the collective; every rank calls it in the same order
+            assert L["stream"] == 0 and bcast is not None
+            for seg in F.plan_table("bcasts", b200.BCAST_DT)[first:first + cnt]:
+                bcast(int(seg["off"]), int(seg["len"]), int(seg["root"]))
             continue
         if kind == b200.K_COPYOUT:
             assert L["stream"] == 2
