@@ -113,6 +113,11 @@ int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
 int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const void *Ax) ;
 
+/* Re-factorization fast path (cholmod_factorize.c:67-70: one analysis, many numeric factorizations): the
+ * pattern uploaded by the last b200_upload_matrix is kept on the device and only the values Ax (same
+ * order, same count) are replaced -- 8 bytes per entry instead of 24. */
+int b200_upload_values (b200_factor *f, const void *Ax) ;
+
 /* Factorize the device-resident A into the device-resident L: zero + scatter A (:361-520), then level by
  * level the batched descendant updates (dsyrk/dgemm/assemble, :769-930) and the per-supernode
  * dpotrf/dtrsm (:1023-1181).  Blocks until the device is done.  Returns status and *minor as above. */

@@ -24,7 +24,7 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
-           "b200_comm_init"]
+           "b200_comm_init", "b200_upload_values"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -71,6 +71,7 @@ def lib():
     L.b200_create_dist.restype = vp
     L.b200_comm_unique_id.argtypes = [vp]; L.b200_comm_unique_id.restype = cint
     L.b200_comm_init.argtypes = [vp, vp]; L.b200_comm_init.restype = cint
+    L.b200_upload_values.argtypes = [vp, vp]; L.b200_upload_values.restype = cint
     _lib = L
     return L
 
@@ -202,6 +203,13 @@ class Factor:
         if st < 0:
             raise B200Error(st, "b200_upload_matrix")
 
+    def upload_values(self, Ax):
+        """New values for the pattern of the last upload_matrix (re-factorization fast path)."""
+        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+        st = self.L.b200_upload_values(self.h, Ax.ctypes.data)
+        if st < 0:
+            raise B200Error(st, "b200_upload_values")
+
     def factor_device(self, beta=0.0, quick_return=False):
         minor = C.c_int64(-1)
         st = self.L.b200_factor_device(self.h, float(beta), int(quick_return), C.byref(minor))
@@ -256,12 +264,13 @@ TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("j
                     ("slot", "<i4")])
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
                       ("wait_ev", "<i4"), ("rec_ev", "<i4")])
-K_JOIN, K_COPYOUT, K_BCAST = 9, 10, 11
+K_FACTOR_SMALL = 9
+K_JOIN, K_COPYOUT, K_BCAST = 10, 11, 12
 BCAST_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("root", "<i4"), ("pad", "<i4")])
 COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8")])
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)
 KIND_NAMES = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf16", "potrf32", "potrf64", "trsm_subst", "trsm_inv32",
-              "trsm_inv64"]
+              "trsm_inv64", "factor_small"]
 TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 64)}

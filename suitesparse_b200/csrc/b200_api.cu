@@ -258,6 +258,9 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             case K_POTRF16:
                 k_potrf_reg<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
                 break ;
+            case K_FACTOR_SMALL:
+                k_factor_small<T><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
+                break ;
             case K_POTRF32:
                 k_potrf_tile<T><<<(unsigned) L.count, 256, potrf_smem_bytes<T> (), st>>> (potrf + L.first, Lx, winv, 32, f->d_minor.p) ;
                 break ;
@@ -665,6 +668,20 @@ int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, co
     CK (cudaStreamSynchronize (s), "H2D A") ;
     cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
     f->have_A = true ; f->A_unpacked = (Anz != nullptr) ; f->A_nz = nz ;
+    return B200_OK ;
+}
+
+int b200_upload_values (b200_factor *f, const void *Ax)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!f->have_A) return B200_INVALID ;       // the pattern must have been uploaded once
+    if (f->A_nz == 0) return B200_OK ;
+    if (!Ax) return B200_INVALID ;
+    CK (cudaEventRecord (f->ev [0], f->stream), "record") ;
+    CK (cudaMemcpyAsync (f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, cudaMemcpyHostToDevice, f->stream), "H2D Ax") ;
+    CK (cudaEventRecord (f->ev [1], f->stream), "record") ;
+    CK (cudaStreamSynchronize (f->stream), "H2D Ax") ;
+    cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
     return B200_OK ;
 }
 

@@ -364,9 +364,79 @@ __global__ void __launch_bounds__ (64) k_potrf_reg (const PotrfBlk *__restrict__
     for (int c = 0 ; c < NB ; c++) if (r < jb && c <= r) D [r + c * lda] = a [c] ;
 }
 
+// Whole small supernodes (nscol <= 16, at most SMALL_ROWS rows below the diagonal block; the bulk of the
+// leaves): the same register Cholesky as k_potrf_reg, and then the same 16-thread group solves the rows
+// below, 16 at a time, by substitution against the factor it has just put in shared memory -- dpotrf and
+// dtrsm of SNW:1023 and :1175 in one launch, no second kernel, no 128-thread tile for a handful of rows.
+template <typename T>
+__global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restrict__ blks, int nblks, T *Lx,
+    unsigned long long *minor)
+{
+    constexpr int NB = 16, G = 4 ;
+    __shared__ T colbuf [2][64] ;
+    __shared__ T sL [G][NB][NB + 1] ;
+    const int g = threadIdx.x / NB, r = threadIdx.x % NB ;
+    const int bi = blockIdx.x * G + g ;
+    const bool active = bi < nblks ;
+    PotrfBlk b ;
+    if (active) b = blks [bi] ; else { b.off = 0 ; b.col = 0 ; b.lda = 0 ; b.jb = 0 ; b.slot = -1 ; }
+    const int jb = b.jb ;
+    const int64_t lda = b.lda ;
+    T *D = Lx + b.off ;
+    T a [NB] ;
+    #pragma unroll
+    for (int c = 0 ; c < NB ; c++)
+        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
+    #pragma unroll
+    for (int j = 0 ; j < NB ; j++)
+    {
+        T *cb = colbuf [j & 1] + g * NB ;
+        if (r >= j) cb [r] = a [j] ;
+        __syncthreads () ;
+        const T d = cb [j] ;
+        if (r == j && j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        const T t = a [j] * ((T) 1 / d) ;
+        #pragma unroll
+        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= t * cb [c] ;
+        const T ljj = sqrt (d) ;
+        if (r == j) a [j] = ljj ;
+        else if (r > j) a [j] = a [j] / ljj ;
+    }
+    #pragma unroll
+    for (int c = 0 ; c < NB ; c++)
+    {
+        if (r < jb && c <= r) D [r + c * lda] = a [c] ;
+        sL [g][r][c] = (c <= r) ? a [c] : (T) 0 ;       // identity padded: rows / columns >= jb are e_r
+    }
+    __syncthreads () ;
+    // rows below the diagonal block: x <- x * L11^{-T}, one row per thread
+    const int below = (int) lda - jb ;
+    for (int r0 = 0 ; r0 < below ; r0 += NB)
+    {
+        const int row = r0 + r ;
+        if (row < below)
+        {
+            T *X = D + jb + row ;
+            T x [NB] ;
+            #pragma unroll
+            for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : (T) 0 ;
+            #pragma unroll
+            for (int j = 0 ; j < NB ; j++)
+            {
+                const T xj = x [j] / sL [g][j][j] ;
+                x [j] = xj ;
+                #pragma unroll
+                for (int k = j + 1 ; k < NB ; k++) x [k] -= xj * sL [g][k][j] ;
+            }
+            #pragma unroll
+            for (int j = 0 ; j < NB ; j++) if (j < jb) X [j * lda] = x [j] ;
+        }
+    }
+}
+
 template <typename T> constexpr size_t potrf_smem_bytes ()
 {
-    return (size_t) (2 * POTRF_NB * PB_LD + 5 * POTRF_NB) * sizeof (T) ;
+    return (size_t) (2 * POTRF_NB * PB_LD + 5 * POTRF_NB + 32 * 33) * sizeof (T) ;
 }
 
 // Wider blocks (16 < jb <= 64): one CTA of 256 threads per block.  The block lives in registers as a
@@ -459,31 +529,69 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
         for (int i = 0 ; i < 4 ; i++)
         {
             const int r = 4 * ti + i ;
-            if (r < jb && c < jb && r >= c)
+            if (r < c) continue ;
+            if (r < jb && c < jb)
             {
                 const T v = (r == c) ? ljj : a [i][jc] / ljj ;
                 s [c * PB_LD + r] = v ;
                 D [r + c * lda] = v ;
             }
+            else s [c * PB_LD + r] = (r == c) ? (T) 1 : (T) 0 ;     // identity padding up to 64 x 64
         }
     }
     if (b.slot < 0) return ;
     __syncthreads () ;
-    // W = L^{-1}, row by row: W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr).
-    // Column c is owned by the 4 consecutive lanes 4c..4c+3 (same warp), which split the sum.
+    // W = L^{-1} of the (padded) 64 x 64 block, block-recursively, so that the serial chain is 16 rows
+    // instead of 64:  (A) the four 16 x 16 diagonal blocks are inverted side by side, row by row --
+    // W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr), column c owned by the 4
+    // consecutive lanes 4c..4c+3 which split the sum;  (B), (C) the off-diagonal blocks follow from
+    // W21 = -W22 * L21 * W11, first for the two 16-blocks inside each 32-block, then for the 32-block.
     {
         const int c = threadIdx.x >> 2, part = threadIdx.x & 3 ;
-        for (int rr = 0 ; rr < jb ; rr++)
+        const int b0 = c & ~15 ;
+        for (int rl = 0 ; rl < 16 ; rl++)
         {
+            const int rr = b0 + rl ;
             T acc = 0 ;
             for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
             acc += __shfl_xor_sync (0xffffffffu, acc, 1) ;
             acc += __shfl_xor_sync (0xffffffffu, acc, 2) ;
-            if (part == 0 && c < jb && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? (T) 1 : (T) 0) - acc) * rsq [rr] ;
+            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? (T) 1 : (T) 0) - acc) * rsq [rr] ;
             __syncwarp () ;
         }
     }
     __syncthreads () ;
+    T *tmp = rsq + POTRF_NB ;                   // [32][33] scratch of the off-diagonal products
+    #pragma unroll 1
+    for (int pass = 0 ; pass < 2 ; pass++)
+    {
+        const int nb = pass ? 32 : 16 ;
+        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31)
+        // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
+        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        {
+            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
+            const int i = el % nb, j = el / nb ;
+            if (j >= nb) continue ;
+            const int c0 = half * 32, r0 = c0 + nb ;
+            T acc = 0 ;
+            for (int k = j ; k < nb ; k++) acc += s [(c0 + k) * PB_LD + r0 + i] * w [(c0 + k) * PB_LD + c0 + j] ;
+            tmp [(half * 16 + i) * 33 + j] = acc ;
+        }
+        __syncthreads () ;
+        // step 2: W (r0+i, c0+j) = - sum_{k <= i} W (r0+i, r0+k) tmp (k,j)
+        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        {
+            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
+            const int i = el % nb, j = el / nb ;
+            if (j >= nb) continue ;
+            const int c0 = half * 32, r0 = c0 + nb ;
+            T acc = 0 ;
+            for (int k = 0 ; k <= i ; k++) acc += w [(r0 + i) * PB_LD + r0 + k] * tmp [(half * 16 + k) * 33 + j] ;
+            w [(r0 + i) * PB_LD + c0 + j] = -acc ;
+        }
+        __syncthreads () ;
+    }
     T *W = winv + (int64_t) b.slot * (WINV_LD * WINV_LD) ;
     for (int e = threadIdx.x ; e < nbk * nbk ; e += 256)
     {

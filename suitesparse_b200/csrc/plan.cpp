@@ -206,6 +206,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         {
             for (auto &v : pb) v.clear () ;
             for (auto &v : tt) v.clear () ;
+            std::vector<PotrfBlk> small ;
             int32_t nslots = 0 ;
             for (int64_t q = 0 ; q < ns ; q++)
             {
@@ -219,6 +220,14 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 PotrfBlk b ;
                 b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
                 b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
+                if (j0 == 0 && nscol <= 16 && nsrow - nscol <= SMALL_ROWS)
+                {
+                    // a whole small supernode: potrf and the trsm of its few rows in one kernel
+                    b.slot = -1 ; b.pad = 0 ;
+                    small.push_back (b) ;
+                    out.flops_kind [K_FACTOR_SMALL] += (double) jb * jb * jb / 3.0 + (double) (nsrow - nscol) * jb * jb ;
+                    continue ;
+                }
                 b.slot = inv ? nslots++ : -1 ; b.pad = 0 ;
                 pb [pcls].push_back (b) ;
                 out.flops_kind [K_POTRF16 + pcls] += (double) jb * jb * jb / 3.0 ;
@@ -245,6 +254,14 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 }
             }
             out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
+            if (!small.empty ())
+            {
+                Launch L = make_launch (K_FACTOR_SMALL, (int64_t) out.potrf.size (), (int64_t) small.size (), level, 0) ;
+                L.wait_ev = pending_wait ; pending_wait = -1 ;
+                out.count_kind [L.kind] += L.count ;
+                out.potrf.insert (out.potrf.end (), small.begin (), small.end ()) ;
+                out.launches.push_back (L) ;
+            }
             for (int c = 0 ; c < 3 ; c++)
             {
                 if (pb [c].empty ()) continue ;

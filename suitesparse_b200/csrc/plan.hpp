@@ -64,10 +64,11 @@ enum LaunchKind : int32_t
     K_TRSM     = 6,     // TrsmTile list, substitution
     K_TRSM_INV32 = 7,   // TrsmTile list, product with the inverse of a <= 32-wide block
     K_TRSM_INV64 = 8,   // TrsmTile list, product with the inverse of a <= 64-wide block
-    K_NKINDS   = 9,
-    K_JOIN     = 9,     // no kernel: only the launch's wait_ev / rec_ev are honoured
-    K_COPYOUT  = 10,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
-    K_BCAST    = 11,    // no kernel: BcastSeg list, ncclBroadcast of finished panels / subtrees (main stream)
+    K_FACTOR_SMALL = 9, // PotrfBlk list: whole supernodes of <= 16 columns and few rows, potrf + trsm fused
+    K_NKINDS   = 10,
+    K_JOIN     = 10,    // no kernel: only the launch's wait_ev / rec_ev are honoured
+    K_COPYOUT  = 11,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
+    K_BCAST    = 12,    // no kernel: BcastSeg list, ncclBroadcast of finished panels / subtrees (main stream)
 } ;
 
 struct Launch
@@ -85,6 +86,8 @@ struct Launch
 constexpr int POTRF_NB   = 64 ;     // width of a block column factorized by one POTRF block
 constexpr int OUTER_NB   = 256 ;    // width of an outer block column (trailing updates with K = OUTER_NB)
 constexpr int TRSM_ROWS  = 128 ;    // rows per TRSM tile
+constexpr int SMALL_ROWS = 256 ;    // a supernode of <= 16 columns with at most this many rows below its
+                                    // diagonal block is factorized by one 16-thread group (K_FACTOR_SMALL)
 constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
 // the large DMMA tile: 128 x 64 with 4 warps of 32 x 64, two CTAs per SM so that one CTA's prologue,
 // barriers and epilogue overlap the other's tensor work

@@ -155,6 +155,30 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                         Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
                 r, c = np.tril_indices(jb)
                 D[r, c] = Lc[r, c]
+        elif kind == b200.K_FACTOR_SMALL:
+            for b in potrf[first:first + cnt]:
+                jb, lda = int(b["jb"]), int(b["lda"])
+                assert jb <= 16 and lda - jb <= 256
+                P = _view(Lx, int(b["off"]), lda, jb, lda)      # the whole supernode: b.off is its origin
+                Dl = np.tril(P[:jb, :])
+                Lc = Dl + np.tril(Dl, -1).T
+                for j in range(jb):
+                    d = Lc[j, j]
+                    if not d > 0:
+                        col = int(b["col"]) + j
+                        minor = col if minor is None else min(minor, col)
+                    with np.errstate(all="ignore"):
+                        ljj = np.sqrt(d)
+                        Lc[j:, j] = Lc[j:, j] / ljj
+                        Lc[j, j] = ljj
+                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
+                r, c = np.tril_indices(jb)
+                P[r, c] = Lc[r, c]
+                if lda > jb:
+                    L11 = np.tril(P[:jb, :])
+                    with np.errstate(all="ignore"):
+                        P[jb:, :] = np.linalg.solve(L11, P[jb:, :].T).T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
+                            else np.nan
         elif kind in b200.K_TRSM_KINDS:
             for t in trsm[first:first + cnt]:
                 jb, lda, nr = int(t["jb"]), int(t["lda"]), int(t["nrows"])

@@ -80,6 +80,12 @@ def test_beta_and_refactorization():
         stp, _, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx * scale, beta=beta)
         assert st == stp == 0
         assert np.max(np.abs(Lx - Lp)) <= TOL_L * np.max(np.abs(Lp))
+    # values-only path: the pattern stays on the device
+    F.upload_matrix(c.Sp, c.Si, c.Sx)
+    F.upload_values(c.Sx * 3.0)
+    assert F.factor_device() == b200.OK
+    stp, _, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx * 3.0)
+    assert np.max(np.abs(F.download_factor() - Lp)) <= TOL_L * np.max(np.abs(Lp))
     F.close()
 
 

@@ -73,7 +73,7 @@ def test_distributed_plan_every_rank_ends_with_the_reference_factor(kind, size, 
         assert np.array_equal(F.plan_table("top", np.int8), top0)
     assert b0.size > 0 and set(b0["root"].tolist()) <= set(range(nranks))
     # work is really divided: every rank has update tiles, and no rank does more than ~60 % of the flops
-    flops = np.array([sum(F.getd("flops_kind%d" % k) for k in range(9)) for F in Fs])
+    flops = np.array([sum(F.getd("flops_kind%d" % k) for k in range(len(b200.KIND_NAMES))) for F in Fs])
     assert np.all(flops > 0)
     if nranks >= 2 and kind == "lap3d7":
         assert flops.max() <= 0.75 * flops.sum()
