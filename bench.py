@@ -37,6 +37,7 @@ WORKLOADS = {
     "cfg1": ("lap2d5", 100, 2, "2-D 5-point Laplacian 100x100 (n=10k), double, AMD"),
     "cfg5": ("lap2d9", 2000, 3, "2-D 9-point Laplacian 2000x2000 (n=4M), double, METIS"),
     "cfg3": ("el27", 80, 3, "3-D 27-point 3-dof elasticity-style 80^3 (n=1.5M), double, METIS"),
+    "cfg4": ("lap3d7", 160, 3, "3-D 7-point Laplacian 160^3 (n=4.1M), double, METIS"),
     "lap3d7_64": ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262k), double, METIS"),
     "lap3d7_40": ("lap3d7", 40, 3, "3-D 7-point Laplacian 40^3 (n=64k), double, METIS"),
 }
@@ -105,6 +106,18 @@ class ClockSampler:
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/r01_ncu_full_k_upd_dmma.json: mean of dram__bytes_read.sum + dram__bytes_write.sum over the
+    captured launches).  A number taken under a profiler, reported only as the traffic figure."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_full_k_upd_dmma.json")))
+        vals = [(float(r["dram__bytes_read.sum"]) + float(r["dram__bytes_write.sum"])) * 1e6 for r in d["launches"]]
+        return float(np.mean(vals)) if vals else None
+    except Exception:
+        return None
 
 
 def cpu_reference_steps(steps, warmup, nthreads):
@@ -275,7 +288,7 @@ def main():
     ach = (dk["gflop"] / 1e3) / (dk["ms"] * 1e-3) if dk["ms"] > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "k_upd_dmma<%s>" % ("128,64,32,64" if dom == "upd_dmma128" else "64,64,32,32"),
                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak > 0 else None,
-                "traffic": None,
+                "traffic": ncu_traffic(),
                 "peak_burst": peak_burst, "peak_sustained": peak_sustained,
                 "frac_of_sustained": ach / peak_sustained if peak_sustained > 0 else None,
                 "peak_source": "FP64 DMMA peak measured live by b200_dmma_peak_tflops (MEASURED_PEAKS.json has no FP64 "
