@@ -45,14 +45,14 @@ CPU_SAMPLE = ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262144), METIS: sa
               "workload, reduced so one CPU factorization takes ~10 s")
 
 
-def analyze(kind, size, ordering, nthreads=0):
+def analyze(kind, size, ordering, nthreads=0, single=False):
     """Reference host analysis (ordering, etree, supernodes) + the seam matrix."""
     from oracle import refd
     from suitesparse_b200 import matrices
     gen = getattr(matrices, kind)
     n, Ap, Ai, Ax = gen(size)
     ref = refd.Ref(nthreads)
-    ref.set_matrix(n, Ap, Ai, Ax, -1)
+    ref.set_matrix(n, Ap, Ai, Ax, -1, single=single)
     t = time.time()
     ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
     t_an = time.time() - t
@@ -166,6 +166,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--single", action="store_true", help="single precision (config 5b); the roofline stays FP64-tensor "
+                    "and is then only informative: single precision runs on the FP32 FMA pipe")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -189,18 +191,21 @@ def main():
     peak_burst = max(b200.dmma_peak_tflops(local, 40000) for _ in range(3)) if rank == 0 else 0.0
 
     kind, size, ordering, desc = WORKLOADS[args.workload]
-    ref, t_an = analyze(kind, size, ordering)
+    fdtype = np.float32 if args.single else np.float64
+    if args.single:
+        desc = desc.replace("double", "single")
+    ref, t_an = analyze(kind, size, ordering, single=args.single)
     sym = ref.symbolic()
     Sp, Si, Sx = ref.seam()
     fl = sym["fl"]
     t0 = time.time()
     # N > 1: ONE factorization partitioned over the N GPUs (etree subtrees + block-cyclic top separators,
     # panels broadcast with NCCL); every rank ends with the whole factor.  Strong scaling: value = fl / t.
-    F = b200.Factor(sym, device=local, nranks=world, rank=rank)
+    F = b200.Factor(sym, dtype=fdtype, device=local, nranks=world, rank=rank)
     if world > 1:
         F.comm_init_torch()
     t_plan = time.time() - t0
-    Lx_host = np.empty(sym["xsize"], dtype=np.float64) if rank == 0 else None
+    Lx_host = np.empty(sym["xsize"], dtype=fdtype) if rank == 0 else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -260,7 +265,7 @@ def main():
             t_e2e = float(tt.item())
         e2e = {"value": fl / t_e2e / 1e9, "unit": UNIT, "ms_per_step": 1e3 * t_e2e,
                "h2d_bytes_per_step": int(Sp.nbytes + Si.nbytes + Sx.nbytes),
-               "d2h_bytes_per_step": int(sym["xsize"] * 8),
+               "d2h_bytes_per_step": int(sym["xsize"] * np.dtype(fdtype).itemsize),
                "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h")}
 
     # one profiled (untimed) factorization for the per-kernel breakdown; collective, so every rank runs it
@@ -298,6 +303,13 @@ def main():
     whole = {"achieved_tflops": fl / (ms_step * 1e-3) / 1e12, "frac_of_fp64_peak": fl / (ms_step * 1e-3) / 1e12 / peak if peak > 0 else None,
              "executed_tflops": F.getd("flops_executed") / (ms_step * 1e-3) / 1e12}
 
+    # ---- full-size sanity of the factor just computed: device solve + the demo's scaled residual ----------
+    from suitesparse_b200 import matrices
+    bvec = matrices.rhs(sym["n"])
+    xs = np.empty(sym["n"])
+    xs[sym["Perm"]] = F.solve(bvec[sym["Perm"]])
+    check = {"solve_ms": F.getd("ms_solve"), "scaled_residual": ref.resid(xs, bvec), "tolerance": 1e-5 if args.single else 1e-12}
+
     # ---- CPU baseline: the reference on a bounded sample, rank 0, N = 1 only ----------------------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -309,15 +321,17 @@ def main():
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
+        "dtype": "f32" if args.single else "f64", "data": "synthetic",
         "config": {"workload": desc, "n": int(sym["n"]), "nsuper": int(sym["nsuper"]), "fl": fl, "lnz": sym["lnz"],
                    "xsize": int(sym["xsize"]), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
+                   "relmap_len": F.geti("relmap_len"), "device_bytes": F.geti("device_bytes"),
                    "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * 8 / 1e9),
                    "parallelism": ("one factorization over %d GPUs: etree subtrees per GPU + block-cyclic top separators, "
                                    "%d NCCL broadcasts per step, %d top supernodes" % (world, nccl_calls, F.geti("ntop")))
                    if world > 1 else "1 GPU",
                    "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
+        "check": check,
         "kernels": kinds, "cpu_baseline": cpu,
     }
     print(json.dumps(out))

@@ -161,6 +161,8 @@ int kernel_attrs (int device)
         (int) trsm_inv_smem_bytes<64> ()), "attr trsm_inv64") ;
     CK (cudaFuncSetAttribute (k_potrf_tile<double>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) potrf_smem_bytes<double> ()), "attr potrf") ;
+    CK (cudaFuncSetAttribute (k_potrf_tile<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) potrf_smem_bytes<float> ()), "attr potrf") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
@@ -245,15 +247,22 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                 break ;
             }
             case K_UPD_D64:
-                if (sizeof (T) != 8) return B200_INVALID ;
-                k_upd_dmma<64, 64, 32, 32><<<(unsigned) L.count, 128, dmma_smem_bytes<64, 64> (), st>>>
-                    (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                if (sizeof (T) == 8)
+                    k_upd_dmma<64, 64, 32, 32><<<(unsigned) L.count, 128, dmma_smem_bytes<64, 64> (), st>>>
+                        (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                else
+                    k_upd_ffma<64, 64><<<(unsigned) L.count, 64, ffma_smem_bytes<64, 64> (), st>>>
+                        (tiles + L.first, items, relmap, reinterpret_cast<float *> (Lx)) ;
                 break ;
             case K_UPD_D128:
-                if (sizeof (T) != 8) return B200_INVALID ;
-                k_upd_dmma<BIG_TM, BIG_TN, 32, 64><<<(unsigned) L.count, (BIG_TM / 32) * (BIG_TN / 64) * 32,
-                    dmma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
-                    (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                if (sizeof (T) == 8)
+                    k_upd_dmma<BIG_TM, BIG_TN, 32, 64><<<(unsigned) L.count, (BIG_TM / 32) * (BIG_TN / 64) * 32,
+                        dmma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
+                        (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
+                else
+                    k_upd_ffma<BIG_TM, BIG_TN><<<(unsigned) L.count, (BIG_TM / 8) * (BIG_TN / 8),
+                        ffma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
+                        (tiles + L.first, items, relmap, reinterpret_cast<float *> (Lx)) ;
                 break ;
             case K_POTRF16:
                 k_potrf_reg<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;

@@ -294,6 +294,126 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// single precision: the same tiles on the FP32 FMA pipe
+// ---------------------------------------------------------------------------------------------
+
+// FP32 has no tensor path of FP32 accuracy (tf32 keeps 10 mantissa bits), so the single-precision
+// factorization (config 5b) runs the update tiles as a classic register-blocked SGEMM: TM x TN tile,
+// (TM/8) x (TN/8) threads with an 8 x 8 micro-tile each, operands staged [k][m] by a 3-stage cp.async
+// ring exactly like k_upd_dmma, epilogue = red.global.add.f32 of -C through the relative map.
+template <int TM, int TN> constexpr size_t ffma_smem_bytes ()
+{
+    return (size_t) DM_STAGES * DM_KC * (TM + TN) * sizeof (float) + (TM + TN) * sizeof (int32_t) ;
+}
+
+template <int TM, int TN>
+__global__ void __launch_bounds__ ((TM / 8) * (TN / 8)) k_upd_ffma (const UpdTile *__restrict__ tiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, float *Lx)
+{
+    constexpr int NTX = TM / 8, NTY = TN / 8, NT = NTX * NTY ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    float *sA = reinterpret_cast<float *> (smem_raw) ;                   // [STAGES][KC][TM]
+    float *sB = sA + DM_STAGES * DM_KC * TM ;                            // [STAGES][KC][TN]
+    int32_t *smap_r = reinterpret_cast<int32_t *> (sB + DM_STAGES * DM_KC * TN) ;
+    int32_t *smap_c = smap_r + TM ;
+    const UpdTile t = tiles [blockIdx.x] ;
+    const UpdItem it = items [t.item] ;
+    const int tid = threadIdx.x, tx = tid % NTX, ty = tid / NTX ;
+    const int i0 = (int) t.ti * TM, j0 = (int) t.tj * TN ;
+    const int mA = min (TM, it.M - i0), nB = min (TN, it.N - j0) ;
+    const int64_t lda = it.lda ;
+    const float *A = Lx + it.a_off ;
+    const int kbeg = t.k0, kend = t.k1 ;
+    const int nk = (kend - kbeg + DM_KC - 1) / DM_KC ;
+    {
+        const bool mapped = it.map_off >= 0 ;
+        const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+        for (int m = tid ; m < TM ; m += NT) smap_r [m] = (m < mA) ? (mapped ? map [i0 + m] : i0 + m) : 0 ;
+        for (int m = tid ; m < TN ; m += NT) smap_c [m] = (m < nB) ? (mapped ? map [j0 + m] : j0 + m) : 0 ;
+    }
+    auto load_stage = [&] (int kt, int buf)
+    {
+        const int kb = kbeg + kt * DM_KC ;
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TM ; e += NT)
+        {
+            const int m = e % TM, k = e / TM ;
+            const int sz = (m < mA && kb + k < kend) ? 4 : 0 ;
+            const unsigned d = (unsigned) __cvta_generic_to_shared (sA + (buf * DM_KC + k) * TM + m) ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], 4, %2;\n"
+                :: "r" (d), "l" (A + i0 + m + (int64_t) (kb + k) * lda), "r" (sz)) ;
+        }
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TN ; e += NT)
+        {
+            const int m = e % TN, k = e / TN ;
+            const int sz = (m < nB && kb + k < kend) ? 4 : 0 ;
+            const unsigned d = (unsigned) __cvta_generic_to_shared (sB + (buf * DM_KC + k) * TN + m) ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], 4, %2;\n"
+                :: "r" (d), "l" (A + j0 + m + (int64_t) (kb + k) * lda), "r" (sz)) ;
+        }
+    } ;
+    float acc [8][8] ;
+    #pragma unroll
+    for (int a = 0 ; a < 8 ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < 8 ; b++) acc [a][b] = 0.f ;
+    // a thread whose whole micro-tile lies strictly above the diagonal has nothing to compute
+    const bool live = (i0 + tx * 8 + 7) >= (j0 + ty * 8) ;
+    #pragma unroll
+    for (int s = 0 ; s < DM_STAGES - 1 ; s++)
+    {
+        if (s < nk) load_stage (s, s) ;
+        cp_async_commit () ;
+    }
+    for (int kt = 0 ; kt < nk ; kt++)
+    {
+        cp_async_wait<DM_STAGES - 2> () ;
+        __syncthreads () ;
+        if (kt + DM_STAGES - 1 < nk) load_stage (kt + DM_STAGES - 1, (kt + DM_STAGES - 1) % DM_STAGES) ;
+        cp_async_commit () ;
+        if (live)
+        {
+            const float *cA = sA + (kt % DM_STAGES) * DM_KC * TM + tx * 8 ;
+            const float *cB = sB + (kt % DM_STAGES) * DM_KC * TN + ty * 8 ;
+            #pragma unroll
+            for (int k = 0 ; k < DM_KC ; k++)
+            {
+                const float4 a0 = *reinterpret_cast<const float4 *> (cA + k * TM) ;
+                const float4 a1 = *reinterpret_cast<const float4 *> (cA + k * TM + 4) ;
+                const float4 b0 = *reinterpret_cast<const float4 *> (cB + k * TN) ;
+                const float4 b1 = *reinterpret_cast<const float4 *> (cB + k * TN + 4) ;
+                const float fa [8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w } ;
+                const float fb [8] = { b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w } ;
+                #pragma unroll
+                for (int a = 0 ; a < 8 ; a++)
+                    #pragma unroll
+                    for (int b = 0 ; b < 8 ; b++) acc [a][b] += fa [a] * fb [b] ;
+            }
+        }
+    }
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    if (!live) return ;
+    float *C = Lx + it.c_off ;
+    const int64_t ldc = it.ldc ;
+    #pragma unroll
+    for (int b = 0 ; b < 8 ; b++)
+    {
+        const int jl = ty * 8 + b ;
+        if (jl >= nB) continue ;
+        const int j = j0 + jl ;
+        float *Cj = C + (int64_t) smap_c [jl] * ldc ;
+        #pragma unroll
+        for (int a = 0 ; a < 8 ; a++)
+        {
+            const int il = tx * 8 + a ;
+            if (il < mA && i0 + il >= j) atomicAdd (Cj + smap_r [il], -acc [a][b]) ;
+        }
+    }
+}
+
 // Register-resident DMMA loop: the FP64 tensor peak this chip sustains (MEASURED_PEAKS.json has no FP64
 // figure, so bench.py measures the roofline denominator with this kernel on the box it runs on).
 static __global__ void __launch_bounds__ (256) k_dmma_peak (double *out, int iters)

@@ -43,7 +43,8 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
 {
     const int64_t M = it.M, N = it.N, K = it.K ;
     int cls ;
-    if (!use_dmma || N < 16 || K < 8 || M * N < 2048)
+    (void) use_dmma ;       // both precisions use the tile classes (double: DMMA, single: FFMA kernels)
+    if (N < 16 || K < 8 || M * N < 2048)
     {
         cls = K_UPD_SIMT ;
     }
@@ -115,6 +116,8 @@ void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_e
     {
         auto &v = sink.cls [c] ;
         if (v.empty ()) continue ;
+        // longest tiles first: the CTAs still running when the launch drains are then the short ones
+        std::stable_sort (v.begin (), v.end (), [] (const UpdTile &a, const UpdTile &b) { return (a.k1 - a.k0) > (b.k1 - b.k0) ; }) ;
         P.launches.push_back (make_launch (c, (int64_t) P.tiles.size (), (int64_t) v.size (), level, stream)) ;
         P.count_kind [c] += (int64_t) v.size () ;
         P.tiles.insert (P.tiles.end (), v.begin (), v.end ()) ;
