@@ -302,6 +302,22 @@ def main():
                 "avg_launch_ms": dk["ms"] / max(1, dk["launches"]), "share_of_step": dk["ms"] / max(1e-9, sum(v["ms"] for v in kinds.values()))}
     whole = {"achieved_tflops": fl / (ms_step * 1e-3) / 1e12, "frac_of_fp64_peak": fl / (ms_step * 1e-3) / 1e12 / peak if peak > 0 else None,
              "executed_tflops": F.getd("flops_executed") / (ms_step * 1e-3) / 1e12}
+    # the HBM-bound part: zero all of L->x, then scatter A into it.  Algorithmic bytes =
+    # 8 per value of L written by the memset + (8 value + 8 row index read, 8 written) per entry of A.
+    esz = np.dtype(fdtype).itemsize
+    ms_scatter = F.getd("ms_scatter")
+    hbm_peak = None
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        pass
+    zs_bytes = esz * sym["xsize"] + (esz + 8 + esz) * len(Si)
+    hbm_phase = {"kernel": "cudaMemsetAsync + k_scatter_A", "bound": "hbm", "bytes": int(zs_bytes), "ms": ms_scatter,
+                 "achieved": zs_bytes / (ms_scatter * 1e-3) / 1e9 if ms_scatter > 0 else None,
+                 "peak": hbm_peak if hbm_peak else 6650.0, "unit": "GB/s",
+                 "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "fallback 6.65 TB/s (B200_PROFILING.md)"}
+    if hbm_phase["achieved"]:
+        hbm_phase["frac"] = hbm_phase["achieved"] / hbm_phase["peak"]
 
     # ---- full-size sanity of the factor just computed: device solve + the demo's scaled residual ----------
     from suitesparse_b200 import matrices
@@ -331,7 +347,7 @@ def main():
                    if world > 1 else "1 GPU",
                    "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
-        "check": check,
+        "check": check, "hbm_phase": hbm_phase,
         "kernels": kinds, "cpu_baseline": cpu,
     }
     print(json.dumps(out))

@@ -113,6 +113,13 @@ struct b200_factor
     DevBuf<unsigned long long> d_minor ;
     DevBuf<unsigned char> d_winv ;          // scratch: inverses of the diagonal blocks of one launch
     DevBuf<double> d_X ;
+    // solve schedule (built at the first solve)
+    struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;  // kind 0: one CTA per supernode, 1: diag, 2: gemv
+    std::vector<SolveLaunch> solve_launches ;
+    bool solve_ready = false ;
+    DevBuf<int32_t> d_ssmall ;
+    DevBuf<SolveBlk> d_sblk ;
+    DevBuf<SolveTile> d_stile ;
     bool have_A = false, A_unpacked = false ;
     int64_t A_nz = 0 ;
     // host-registered output buffer (pinned once, reused by later factorizations)
@@ -520,6 +527,7 @@ void b200_destroy (b200_factor *f)
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
         f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
+        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
         for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
@@ -827,33 +835,91 @@ static int solve_T (b200_factor *f, int nrhs)
     cudaStream_t s = f->stream ;
     const int64_t cap = (200 * 1024) / 8 ;
     const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
-    for (int lev = 0 ; lev < P.nlevels ; lev++)
+    if (!f->solve_ready)
     {
-        int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
-        if (cnt <= 0) continue ;
-        int64_t maxcol = 0 ;
-        for (int64_t q = 0 ; q < cnt ; q++)
+        // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_BIG columns
+        // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
+        // over the level: diagonal block (k_solve_diag), then the rows below it spread over 256-row tiles
+        // (k_solve_gemv).  The backward sweep is the same list read in reverse with the transposed kernels.
+        constexpr int64_t SOLVE_BIG = 256, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
+        std::vector<int32_t> small ;
+        std::vector<SolveBlk> blks ;
+        std::vector<SolveTile> tiles ;
+        f->solve_launches.clear () ;
+        for (int lev = 0 ; lev < P.nlevels ; lev++)
         {
-            int32_t sn = P.level_list [first + q] ;
-            maxcol = std::max (maxcol, f->h_super [sn+1] - f->h_super [sn]) ;
+            const int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
+            const size_t s0 = small.size () ;
+            std::vector<int32_t> big ;
+            int64_t maxcol = 0, maxbig = 0 ;
+            for (int64_t q = 0 ; q < cnt ; q++)
+            {
+                const int32_t sn = P.level_list [first + q] ;
+                const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
+                if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; }
+                else { big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ; }
+            }
+            if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
+            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
+            {
+                const size_t b0 = blks.size (), t0 = tiles.size () ;
+                for (int32_t sn : big)
+                {
+                    const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
+                    if (nscol <= c0) continue ;
+                    const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
+                    blks.push_back ({ sn, (int32_t) c0, jb, 0 }) ;
+                    for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
+                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, 0 }) ;
+                }
+                f->solve_launches.push_back ({ 1, (int64_t) b0, (int64_t) (blks.size () - b0), 0 }) ;
+                if (tiles.size () > t0) f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
+            }
         }
-        size_t sm = (size_t) std::min (maxcol, cap) * 8 ;
-        k_solve_fwd<T><<<(unsigned) cnt, 256, sm, s>>> (f->d_level_list.p + first, f->d_super.p, f->d_pi.p,
-            f->d_px.p, f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+        bool ok = f->d_ssmall.upload (small, s) == cudaSuccess ;
+        ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
+        ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
+        if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
+        CK (cudaStreamSynchronize (s), "solve plan upload") ;
+        f->solve_ready = true ;
     }
-    for (int lev = P.nlevels - 1 ; lev >= 0 ; lev--)
+    const size_t nl = f->solve_launches.size () ;
+    for (size_t pass = 0 ; pass < 2 ; pass++)
     {
-        int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
-        if (cnt <= 0) continue ;
-        int64_t maxcol = 0 ;
-        for (int64_t q = 0 ; q < cnt ; q++)
+        for (size_t q = 0 ; q < nl ; q++)
         {
-            int32_t sn = P.level_list [first + q] ;
-            maxcol = std::max (maxcol, f->h_super [sn+1] - f->h_super [sn]) ;
+            const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
+            if (L.count <= 0) continue ;
+            const unsigned grid = (unsigned) L.count ;
+            if (L.kind == 0)
+            {
+                const size_t sm = (size_t) std::min (L.maxcol, cap) * 8 ;
+                if (pass == 0)
+                    k_solve_fwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+                else
+                    k_solve_bwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+            }
+            else if (L.kind == 1)
+            {
+                if (pass == 0)
+                    k_solve_diag<T, false><<<grid, 64, 0, s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        Lx, f->d_X.p, P.n, nrhs) ;
+                else
+                    k_solve_diag<T, true><<<grid, 64, 0, s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        Lx, f->d_X.p, P.n, nrhs) ;
+            }
+            else
+            {
+                if (pass == 0)
+                    k_solve_gemv<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs) ;
+                else
+                    k_solve_gemvt<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs) ;
+            }
         }
-        size_t sm = (size_t) std::min (maxcol, cap) * 8 ;
-        k_solve_bwd<T><<<(unsigned) cnt, 256, sm, s>>> (f->d_level_list.p + first, f->d_super.p, f->d_pi.p,
-            f->d_px.p, f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
     }
     CK (cudaGetLastError (), "solve kernels") ;
     return B200_OK ;

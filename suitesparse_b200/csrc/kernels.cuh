@@ -946,4 +946,119 @@ __global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// wide supernodes (nscol > 256) in the solve: 64 columns at a time, the rows below them spread over
+// many CTAs, instead of one CTA walking thousands of columns one by one
+// ---------------------------------------------------------------------------------------------
+
+struct SolveBlk  { int32_t s, c0, jb, pad ; } ;                     // 64-wide diagonal block of supernode s
+struct SolveTile { int32_t s, c0, jb, r0, nrows, p0, p1, p2 ; } ;   // rows [r0, r0+nrows) of s below that block
+
+// forward, diagonal block:  x_blk <- L_blk \ x_blk     (the dtrsv / dtrsm of SSOL:93, :204)
+// backward (TRANS):         x_blk <- L_blk' \ x_blk    (SSOL:386-402)
+template <typename T, bool TRANS>
+__global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict__ blks,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+{
+    __shared__ double sL [64 * 65] ;            // sL [c * 65 + r] = L (r,c), lower
+    __shared__ double sx [64] ;
+    const SolveBlk b = blks [blockIdx.x] ;
+    const int64_t k1 = super [b.s], nsrow = pi [b.s+1] - pi [b.s] ;
+    const T *L = Lx + px [b.s] + b.c0 + (int64_t) b.c0 * nsrow ;
+    const int jb = b.jb, tid = threadIdx.x ;
+    for (int e = tid ; e < jb * jb ; e += 64)
+    {
+        const int r = e % jb, c = e / jb ;
+        if (r >= c) sL [c * 65 + r] = (double) L [r + (int64_t) c * nsrow] ;
+    }
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        double *x = X + (int64_t) rhs * n + k1 + b.c0 ;
+        if (tid < jb) sx [tid] = x [tid] ;
+        __syncthreads () ;
+        if (!TRANS)
+        {
+            for (int j = 0 ; j < jb ; j++)
+            {
+                if (tid == j) sx [j] = sx [j] / sL [j * 65 + j] ;
+                __syncthreads () ;
+                if (tid > j && tid < jb) sx [tid] -= sL [j * 65 + tid] * sx [j] ;
+                __syncthreads () ;
+            }
+        }
+        else
+        {
+            for (int j = jb - 1 ; j >= 0 ; j--)
+            {
+                if (tid == j) sx [j] = sx [j] / sL [j * 65 + j] ;
+                __syncthreads () ;
+                if (tid < j) sx [tid] -= sL [tid * 65 + j] * sx [j] ;
+                __syncthreads () ;
+            }
+        }
+        if (tid < jb) x [tid] = sx [tid] ;
+        __syncthreads () ;
+    }
+}
+
+// forward, rows below the block:  x [rows] -= L (rows, blk) * x_blk     (the dgemv / dgemm of SSOL:100, :212);
+// rows inside the supernode are its own unknowns, rows below it belong to ancestors and are shared with
+// the siblings of the level, hence the atomics
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_gemv (const SolveTile *__restrict__ tiles,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+{
+    __shared__ double xb [64] ;
+    const SolveTile t = tiles [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
+    const T *L = Lx + px [t.s] + (int64_t) t.c0 * nsrow ;
+    const int row = t.r0 + threadIdx.x ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        double *x = X + (int64_t) rhs * n ;
+        if (threadIdx.x < t.jb) xb [threadIdx.x] = x [k1 + t.c0 + threadIdx.x] ;
+        __syncthreads () ;
+        if ((int) threadIdx.x < t.nrows)
+        {
+            double acc = 0 ;
+            for (int j = 0 ; j < t.jb ; j++) acc += (double) L [row + (int64_t) j * nsrow] * xb [j] ;
+            const int64_t dst = (row < nscol) ? k1 + row : (int64_t) Ls [psi + row] ;
+            atomicAdd (x + dst, -acc) ;
+        }
+        __syncthreads () ;
+    }
+}
+
+// backward, rows below the block:  x_blk -= L (rows, blk)' * x [rows]     (SSOL:386: dgemv "C");
+// thread (j, part) walks down column j of the tile, 4 threads per column
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_gemvt (const SolveTile *__restrict__ tiles,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+{
+    __shared__ double xr [256] ;
+    const SolveTile t = tiles [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
+    const int j = threadIdx.x >> 2, part = threadIdx.x & 3 ;
+    const T *Lc = Lx + px [t.s] + (int64_t) (t.c0 + j) * nsrow + t.r0 ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        double *x = X + (int64_t) rhs * n ;
+        if ((int) threadIdx.x < t.nrows)
+        {
+            const int row = t.r0 + threadIdx.x ;
+            xr [threadIdx.x] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
+        }
+        __syncthreads () ;
+        double acc = 0 ;
+        if (j < t.jb) for (int r = part ; r < t.nrows ; r += 4) acc += (double) Lc [r] * xr [r] ;
+        acc += __shfl_xor_sync (0xffffffffu, acc, 1) ;
+        acc += __shfl_xor_sync (0xffffffffu, acc, 2) ;
+        if (part == 0 && j < t.jb) atomicAdd (x + k1 + t.c0 + j, -acc) ;
+        __syncthreads () ;
+    }
+}
+
 }   // namespace b200
