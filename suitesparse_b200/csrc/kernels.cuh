@@ -556,7 +556,7 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
 
 template <typename T> constexpr size_t potrf_smem_bytes ()
 {
-    return (size_t) (2 * POTRF_NB * PB_LD + 5 * POTRF_NB + 32 * 33) * sizeof (T) ;
+    return (size_t) (2 * POTRF_NB * PB_LD + 2 * (4 * POTRF_NB + 4) + 3 * POTRF_NB + 32 * 33) * sizeof (T) ;
 }
 
 // Wider blocks (16 < jb <= 64): one CTA of 256 threads per block.  The block lives in registers as a
@@ -576,8 +576,9 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     extern __shared__ __align__ (16) unsigned char smem_raw [] ;
     T *s = reinterpret_cast<T *> (smem_raw) ;           // s [c * PB_LD + r] = L (r,c), lower part
     T *w = s + POTRF_NB * PB_LD ;                       // w [r * PB_LD + c] = W (r,c), lower part
-    T *colbuf = w + POTRF_NB * PB_LD ;                  // [2][64] column j, double buffered
-    T *dvec = colbuf + 2 * POTRF_NB ;                   // [64] pivots d_j
+    constexpr int CB = 4 * POTRF_NB + 4 ;               // one buffer: 4 columns of 64 + their 4 pivots
+    T *colbuf = w + POTRF_NB * PB_LD ;                  // [2][CB] the 4 columns of a panel, double buffered
+    T *dvec = colbuf + 2 * CB ;                         // [64] pivots d_j
     T *sqv = dvec + POTRF_NB ;                          // [64] sqrt (d_j)
     T *rsq = sqv + POTRF_NB ;                           // [64] 1 / sqrt (d_j)
     const PotrfBlk b = blks [blockIdx.x] ;
@@ -595,40 +596,69 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             a [i][jc] = (r < jb && c < jb && r >= c) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
         }
     const int njt = (jb + 3) >> 2 ;
+    // One barrier per PANEL of 4 columns: the 16 owners of tile column jt (one half-warp: threadIdx =
+    // 16 tj + ti) first factorize their 4 columns among themselves, getting the pivot and the pivot-row
+    // entries from the diagonal-tile thread by shuffles; then the panel is published and every later
+    // tile column takes a rank-4 update.
+    const unsigned lane = threadIdx.x & 31 ;
     for (int jt = 0 ; jt < njt ; jt++)
     {
-        #pragma unroll
-        for (int jj = 0 ; jj < 4 ; jj++)
+        T *cb = colbuf + (jt & 1) * CB ;
+        if (tj == jt)
         {
-            const int j = 4 * jt + jj ;
-            T *cb = colbuf + (jj & 1) * POTRF_NB ;
-            if (tj == jt)
+            const unsigned mask = 0xFFFFu << (lane & 16) ;
+            const int src = (int) (lane & 16) | jt ;           // the lane with ti == jt in this half-warp
+            #pragma unroll
+            for (int jj = 0 ; jj < 4 ; jj++)
+            {
+                const T d = __shfl_sync (mask, a [jj][jj], src) ;
+                const T rd = (T) 1 / d ;
+                #pragma unroll
+                for (int cc = jj + 1 ; cc < 4 ; cc++)
+                {
+                    const T f = __shfl_sync (mask, a [cc][jj], src) * rd ;     // A (4jt+cc, j) / d_j
+                    #pragma unroll
+                    for (int i = 0 ; i < 4 ; i++) a [i][cc] -= a [i][jj] * f ;
+                }
+            }
+            #pragma unroll
+            for (int q = 0 ; q < 4 ; q++)
             {
                 #pragma unroll
-                for (int i = 0 ; i < 4 ; i++) cb [4 * ti + i] = a [i][jj] ;
+                for (int i = 0 ; i < 4 ; i++) cb [q * POTRF_NB + 4 * ti + i] = a [i][q] ;
+                if (ti == jt) cb [4 * POTRF_NB + q] = a [q][q] ;
             }
-            __syncthreads () ;
-            const T d = cb [j] ;
-            if (threadIdx.x == 0)
-            {
-                dvec [j] = d ;
-                if (j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-            }
-            const T rd = (T) 1 / d ;
-            T ar [4], ac [4] ;
+        }
+        __syncthreads () ;
+        T rd [4] ;
+        #pragma unroll
+        for (int q = 0 ; q < 4 ; q++) rd [q] = (T) 1 / cb [4 * POTRF_NB + q] ;
+        if (threadIdx.x == 0)
+        {
             #pragma unroll
-            for (int i = 0 ; i < 4 ; i++) { ar [i] = cb [4 * ti + i] ; ac [i] = cb [4 * tj + i] * rd ; }
-            if (ti >= tj && tj >= jt)
+            for (int q = 0 ; q < 4 ; q++)
             {
+                const T d = cb [4 * POTRF_NB + q] ;
+                dvec [4 * jt + q] = d ;
+                if (4 * jt + q < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + 4 * jt + q)) ;
+            }
+        }
+        if (ti >= tj && tj > jt)
+        {
+            #pragma unroll
+            for (int q = 0 ; q < 4 ; q++)
+            {
+                T ar [4], ac [4] ;
+                #pragma unroll
+                for (int i = 0 ; i < 4 ; i++)
+                {
+                    ar [i] = cb [q * POTRF_NB + 4 * ti + i] ;
+                    ac [i] = cb [q * POTRF_NB + 4 * tj + i] * rd [q] ;
+                }
                 #pragma unroll
                 for (int jc = 0 ; jc < 4 ; jc++)
-                {
-                    if (tj > jt || jc > jj)
-                    {
-                        #pragma unroll
-                        for (int i = 0 ; i < 4 ; i++) a [i][jc] -= ar [i] * ac [jc] ;
-                    }
-                }
+                    #pragma unroll
+                    for (int i = 0 ; i < 4 ; i++) a [i][jc] -= ar [i] * ac [jc] ;
             }
         }
     }

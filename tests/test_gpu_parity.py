@@ -139,6 +139,47 @@ def test_not_posdef_semantics(col, quick):
     F.close()
 
 
+def test_edge_cases_empty_scalar_diagonal_dense():
+    """Degenerate shapes: n = 0, n = 1, a diagonal matrix (every supernode one column, no update pair),
+    one dense supernode wider than an outer block (all of the two-level blocking, no pair)."""
+    sym0 = dict(n=0, nsuper=0, super=np.array([0]), pi=np.array([0]), px=np.array([0]), s=np.zeros(0, dtype=np.int64))
+    F = b200.Factor(sym0, device=0)
+    st, Lx = F.super_numeric(np.array([0]), np.zeros(0, dtype=np.int64), np.zeros(0))
+    assert st == b200.OK and Lx.size == 0 and F.minor == 0
+    F.close()
+    sym1 = dict(n=1, nsuper=1, super=np.array([0, 1]), pi=np.array([0, 1]), px=np.array([0, 1]), s=np.array([0]))
+    F = b200.Factor(sym1, device=0)
+    st, Lx = F.super_numeric(np.array([0, 1]), np.array([0]), np.array([9.0]))
+    assert st == b200.OK and Lx[0] == 3.0
+    st, Lx = F.super_numeric(np.array([0, 1]), np.array([0]), np.array([-4.0]))
+    assert st == b200.NOT_POSDEF and F.minor == 0 and Lx[0] == 0.0
+    F.close()
+    n = 50
+    symd = dict(n=n, nsuper=n, super=np.arange(n + 1), pi=np.arange(n + 1), px=np.arange(n + 1), s=np.arange(n))
+    F = b200.Factor(symd, device=0)
+    d = np.arange(1.0, n + 1)
+    st, Lx = F.super_numeric(np.arange(n + 1), np.arange(n), d)
+    assert st == b200.OK and np.allclose(Lx, np.sqrt(d), rtol=1e-15) and F.geti("npairs") == 0
+    assert np.allclose(F.solve(d), np.ones(n), rtol=1e-14)
+    F.close()
+    n = 700                                                   # one dense supernode, 3 outer blocks
+    rng = np.random.default_rng(3)
+    B = rng.standard_normal((n, n))
+    A = B @ B.T / n + 2.0 * np.eye(n)
+    symn = dict(n=n, nsuper=1, super=np.array([0, n]), pi=np.array([0, n]), px=np.array([0, n * n]), s=np.arange(n))
+    Ap = np.zeros(n + 1, dtype=np.int64); Ap[1:] = np.cumsum(n - np.arange(n))
+    Ai = np.concatenate([np.arange(k, n) for k in range(n)])
+    Ax = np.concatenate([A[k:, k] for k in range(n)])
+    F = b200.Factor(symn, device=0)
+    st, Lx = F.super_numeric(Ap, Ai, Ax)
+    L = np.tril(Lx.reshape(n, n).T)
+    assert st == b200.OK and np.max(np.abs(L - np.linalg.cholesky(A))) <= TOL_L * np.max(np.abs(L))
+    assert np.all(np.triu(Lx.reshape(n, n).T, 1) == 0)
+    x = F.solve(A @ np.ones(n))
+    assert np.max(np.abs(x - 1.0)) <= 1e-10
+    F.close()
+
+
 def test_single_precision():
     c = Case("lap3d7", 14, refd.CHOLMOD_METIS, single=True)
     F = b200.Factor(c.sym, dtype=np.float32, device=0)
