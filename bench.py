@@ -288,6 +288,8 @@ def main():
     for k, nm in enumerate(b200.KIND_NAMES):
         kinds[nm] = {"ms": F.getd("ms_kind%d" % k), "launches": F.geti("launches_kind%d" % k),
                      "gflop": F.getd("flops_kind%d" % k) / 1e9}
+    # device timeline of the profiled pass: when (ms after the first launch) each etree level was finished
+    timeline = [round(F.getd("ms_level_end%d" % k), 3) for k in range(F.geti("nlevels"))]
     dom = max(("upd_dmma128", "upd_dmma64"), key=lambda nm: kinds[nm]["ms"])
     dk = kinds[dom]
     ach = (dk["gflop"] / 1e3) / (dk["ms"] * 1e-3) if dk["ms"] > 0 else 0.0
@@ -348,7 +350,7 @@ def main():
                    "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
         "check": check, "hbm_phase": hbm_phase,
-        "kernels": kinds, "cpu_baseline": cpu,
+        "kernels": kinds, "level_end_ms": timeline, "cpu_baseline": cpu,
     }
     print(json.dumps(out))
     F.close()

@@ -131,6 +131,7 @@ struct b200_factor
     std::vector<cudaEvent_t> prof_ev ;
     double ms_kind [K_NKINDS] = {} ;
     int64_t launches_kind [K_NKINDS] = {} ;
+    float ms_level_end [64] = {} ;          // profile mode: end time of each etree level on the device timeline
     float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
     size_t device_bytes = 0 ;
 } ;
@@ -317,6 +318,13 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             e += 2 ;
             f->ms_kind [L.kind] += ms ;
             f->launches_kind [L.kind]++ ;
+            // timeline: when (after the first launch of the plan) the last launch of each level ended
+            if (L.level >= 0 && L.level < 64)
+            {
+                float t_end = 0 ;
+                cudaEventElapsedTime (&t_end, f->prof_ev [0], f->prof_ev [e-1]) ;
+                if (t_end > f->ms_level_end [L.level]) f->ms_level_end [L.level] = t_end ;
+            }
         }
     }
     return B200_OK ;
@@ -595,6 +603,7 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "ms_level_end", 12)) { int k = atoi (name + 12) ; return (k >= 0 && k < 64) ? f->ms_level_end [k] : -1 ; }
     if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.flops_kind [name [10] - '0'] ;
     return -1 ;
 }
@@ -728,6 +737,7 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     const unsigned long long big = ~0ull ;
     f->kernel_launches = 0 ; f->nccl_calls = 0 ;
     for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
+    for (int k = 0 ; k < 64 ; k++) f->ms_level_end [k] = 0 ;
     CK (cudaEventRecord (f->ev [2], s), "record") ;
     CK (cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, s), "minor init") ;
     if (P.xsize > 0) CK (cudaMemsetAsync (f->d_Lx.p, 0, (size_t) P.xsize * sizeof (T), s), "memset Lx") ;
