@@ -95,6 +95,8 @@ struct b200_factor
     cudaStream_t stream = nullptr ;         // main stream: everything except the look-ahead updates
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
     cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
+    cudaStream_t stream4 = nullptr ;        // communication stream: every NCCL call of this context
+    cudaEvent_t ev_comm [2] = {} ;
     void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
     ncclComm_t comm = nullptr ;             // multi-GPU: communicator over the ranks of the plan (b200_comm_init)
     std::vector<cudaEvent_t> plan_ev ;      // events of the plan's look-ahead schedule
@@ -219,7 +221,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             }
             continue ;
         }
-        const cudaStream_t st = streams [L.stream ? 1 : 0] ;
+        const cudaStream_t st = (L.stream == 3) ? f->stream4 : streams [L.stream ? 1 : 0] ;
         if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
         if (L.kind == K_BCAST)
         {
@@ -309,6 +311,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     {
         CK (cudaStreamSynchronize (f->stream), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream2), "profile sync") ;
+        CK (cudaStreamSynchronize (f->stream4), "profile sync") ;
         size_t e = 0 ;
         for (const Launch &L : P.launches)
         {
@@ -459,6 +462,8 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         CK (cudaStreamCreateWithPriority (&f->stream, cudaStreamNonBlocking, hi), "stream") ;
         CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
         CK (cudaStreamCreateWithFlags (&f->stream3, cudaStreamNonBlocking), "stream3") ;
+        CK (cudaStreamCreateWithPriority (&f->stream4, cudaStreamNonBlocking, hi), "stream4") ;
+        for (auto &e : f->ev_comm) CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "event") ;
     }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
     std::vector<int32_t> Ls32 ((size_t) P.ssize) ;
@@ -543,6 +548,8 @@ void b200_destroy (b200_factor *f)
         cudaStreamSynchronize (f->stream2) ;
         cudaStreamDestroy (f->stream2) ;
         if (f->stream3) { cudaStreamSynchronize (f->stream3) ; cudaStreamDestroy (f->stream3) ; }
+        if (f->stream4) { cudaStreamSynchronize (f->stream4) ; cudaStreamDestroy (f->stream4) ; }
+        for (auto &e : f->ev_comm) if (e) cudaEventDestroy (e) ;
         cudaStreamDestroy (f->stream) ;
         cudaGetLastError () ;
     }
@@ -751,7 +758,11 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
         // the smallest failing column over all ranks is L->minor
         NcclApi *nc = nccl_api () ;
         if (!nc || !f->comm) return B200_INVALID ;
-        if (nc->AllReduce (f->d_minor.p, f->d_minor.p, 1, ncclUint64, ncclMin, f->comm, s) != ncclSuccess) return B200_GPU_PROBLEM ;
+        CK (cudaEventRecord (f->ev_comm [0], s), "record") ;
+        CK (cudaStreamWaitEvent (f->stream4, f->ev_comm [0], 0), "wait") ;
+        if (nc->AllReduce (f->d_minor.p, f->d_minor.p, 1, ncclUint64, ncclMin, f->comm, f->stream4) != ncclSuccess) return B200_GPU_PROBLEM ;
+        CK (cudaEventRecord (f->ev_comm [1], f->stream4), "record") ;
+        CK (cudaStreamWaitEvent (s, f->ev_comm [1], 0), "wait") ;
     }
     unsigned long long minor = big ;
     CK (cudaMemcpyAsync (&minor, f->d_minor.p, sizeof (minor), cudaMemcpyDeviceToHost, s), "minor read") ;

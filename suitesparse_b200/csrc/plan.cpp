@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstring>
 #include <numeric>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -33,7 +34,7 @@ struct Own
     int block_owner (int64_t s, int64_t T) const
     {
         if (!dist ()) return D->rank ;
-        return D->top [s] ? (int) ((D->owner [s] + T) % D->nranks) : D->owner [s] ;
+        return D->top [s] ? (int) ((D->owner [s] + T / D->dist_run) % D->nranks) : D->owner [s] ;
     }
     bool mine (int64_t s, int64_t T) const { return block_owner (s, T) == D->rank ; }
 } ;
@@ -198,6 +199,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
     std::vector<PotrfBlk> pb [3] ;      // jb <= 16, <= 32, <= 64
     std::vector<TrsmTile> tt [3] ;      // substitution, inverse 32, inverse 64
     int evB_prev = -1, evB_prev2 = -1 ; // eB(T-1), eB(T-2)
+    int last_bcast_ev = -1 ;
     for (int64_t J0 = 0 ; J0 < maxcol ; J0 += OUTER_NB)
     {
         const int64_t T = J0 / OUTER_NB ;
@@ -294,6 +296,8 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         }
 
         // ---- distributed supernodes: the owner of block T sends the finished panel to everyone -----------
+        size_t bcast_first = 0, bcast_count = 0 ;
+        bool foreign_ua = false ;       // this rank applies Ua(T) from a panel it has to receive first
         {
             const size_t first = out.bcasts.size () ;
             for (int64_t q = 0 ; q < ns ; q++)
@@ -307,8 +311,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 b.root = own.block_owner (s, T) ; b.pad = 0 ;
                 out.bcasts.push_back (b) ;
             }
-            if (out.bcasts.size () > first)
-                out.launches.push_back (make_launch (K_BCAST, (int64_t) first, (int64_t) (out.bcasts.size () - first), level, 0)) ;
+            bcast_first = first ; bcast_count = out.bcasts.size () - first ;
         }
 
         // ---- outer update of block T -------------------------------------------------------------------
@@ -326,6 +329,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             const int64_t Jn2 = std::min<int64_t> (nscol, Jn + OUTER_NB) ;
             if (own.mine (s, T + 1))
             {
+                if (own.is_top (s) && !own.mine (s, T)) foreign_ua = true ;
                 it.a_off = px [s] + Jn + J0 * nsrow ;
                 it.c_off = px [s] + Jn + Jn * nsrow ;
                 it.M = (int32_t) (nsrow - Jn) ; it.N = (int32_t) (Jn2 - Jn) ;
@@ -375,9 +379,23 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         }
         const bool any_copy = out.copies.size () > copy_first ;
         int evF = -1, evB = -1 ;
-        if (any_b || any_copy)
+        if (bcast_count > 0)
         {
-            // F(T) (and its broadcast) end here on the main stream
+            // F(T) ends here on the main stream (evP); the panels then travel on the communication stream,
+            // off the owner's critical path, and evF says "panel T is on this rank"
+            const int evP = out.nevents++ ;
+            evF = out.nevents++ ;
+            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evP ;
+            out.launches.push_back (J) ;
+            Launch Bc = make_launch (K_BCAST, (int64_t) bcast_first, (int64_t) bcast_count, level, 3) ;
+            Bc.wait_ev = evP ; Bc.rec_ev = evF ;
+            out.launches.push_back (Bc) ;
+            last_bcast_ev = evF ;
+            if (any_b) evB = out.nevents++ ;
+        }
+        else if (any_b || any_copy)
+        {
+            // F(T) ends here on the main stream
             evF = out.nevents++ ; if (any_b) evB = out.nevents++ ;
             if (!out.launches.empty () && out.launches.back ().stream == 0 && out.launches.back ().rec_ev < 0)
                 out.launches.back ().rec_ev = evF ;
@@ -393,13 +411,14 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             C.wait_ev = evF ;
             out.launches.push_back (C) ;
         }
-        flush_tiles (out, sink, level, 0) ;                     // Ua(T), main stream
+        flush_tiles (out, sink, level, 0, foreign_ua ? evF : -1, -1) ;  // Ua(T), main stream
         if (any_b) flush_tiles (out, later, level, 1, evF, evB) ;  // Ub(T), look-ahead stream
         evB_prev2 = evB_prev ;
         evB_prev = evB ;
     }
-    // the main stream joins the look-ahead stream before anything else uses these supernodes
-    for (int ev : { evB_prev2, evB_prev })
+    // the main stream joins the look-ahead and the communication stream before anything else uses these
+    // supernodes
+    for (int ev : { evB_prev2, evB_prev, last_bcast_ev })
     {
         if (ev < 0) continue ;
         Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = ev ;
@@ -479,6 +498,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
     P = Plan () ;
     P.n = n ; P.nsuper = nsuper ; P.nranks = nranks ; P.rank = rank ;
+    if (const char *e = getenv ("CHOLMOD_B200_DIST_RUN")) P.dist_run = std::max (1, atoi (e)) ;
     if (nsuper == 0)
     {
         if (n != 0) return B200_INVALID ;
@@ -658,7 +678,17 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 P.bcasts.push_back (b) ;
             }
             if (P.bcasts.size () > first)
-                P.launches.push_back (make_launch (K_BCAST, (int64_t) first, (int64_t) (P.bcasts.size () - first), lev, 0)) ;
+            {
+                // all NCCL traffic is issued on the communication stream, in the same order on every rank
+                const int evS = P.nevents++, evR = P.nevents++ ;
+                Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evS ;
+                P.launches.push_back (J) ;
+                Launch Bc = make_launch (K_BCAST, (int64_t) first, (int64_t) (P.bcasts.size () - first), lev, 3) ;
+                Bc.wait_ev = evS ; Bc.rec_ev = evR ;
+                P.launches.push_back (Bc) ;
+                Launch W = make_launch (K_JOIN, 0, 0, lev, 0) ; W.wait_ev = evR ;
+                P.launches.push_back (W) ;
+            }
         }
         if (ckpt)
         {

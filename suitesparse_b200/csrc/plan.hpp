@@ -78,7 +78,7 @@ struct Launch
     int64_t first ;     // first entry in the kind's list
     int32_t level ;     // etree level this launch belongs to
     int32_t stream ;    // 0 = main (panel) stream, 1 = look-ahead stream of the wide trailing updates,
-                        // 2 = copy stream (K_COPYOUT)
+                        // 2 = copy stream (K_COPYOUT), 3 = communication stream (K_BCAST)
     int32_t wait_ev ;   // event the stream waits for before this launch, or -1
     int32_t rec_ev ;    // event recorded on the stream after this launch, or -1
 } ;
@@ -92,6 +92,9 @@ constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
 // the large DMMA tile: 128 x 64 with 4 warps of 32 x 64, two CTAs per SM so that one CTA's prologue,
 // barriers and epilogue overlap the other's tensor work
 constexpr int BIG_TM = 128, BIG_TN = 64 ;
+// multi-GPU: consecutive outer blocks of a distributed supernode that stay on one rank (block-cyclic with
+// blocks of DIST_RUN * OUTER_NB columns): inside a run the panel chain never waits for a broadcast
+constexpr int DIST_RUN = 4 ;
 
 // A finished, contiguous piece of L->x (offset and length in values) that can go to the host early.
 struct CopySeg { int64_t off, len ; } ;
@@ -130,6 +133,7 @@ struct Plan
     // by outer block columns, block T of s belonging to rank (owner [s] + T) % nranks (1-D block cyclic);
     // every other supernode belongs, with its whole subtree, to one rank.
     int32_t nranks = 1, rank = 0 ;
+    int32_t dist_run = DIST_RUN ;       // outer blocks per block-cyclic unit (env CHOLMOD_B200_DIST_RUN overrides)
     std::vector<char> top ;             // [nsuper]
     std::vector<int32_t> owner ;        // [nsuper] owning rank (top: the rank of outer block 0)
     std::vector<int32_t> sroot ;        // [nsuper] root of the local subtree of a non-top supernode

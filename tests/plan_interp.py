@@ -46,10 +46,11 @@ def _schedule(launches, prefer):
     """Order the launches the way two CUDA streams could legally execute them: each stream in order, a
     launch with wait_ev only after that event was recorded.  prefer = 0 runs the main stream as far as
     it can before the look-ahead stream gets a turn; prefer = 1 the other way round."""
-    queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in (0, 1, 2)}
-    pos, recorded, order = {0: 0, 1: 0, 2: 0}, set(), []
-    # stream 2 is the copy stream: prefer = 0 / 1 also make it the last / the first to run when it can
-    pref = {0: (0, 1, 2), 1: (2, 1, 0)}[prefer]
+    queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in (0, 1, 2, 3)}
+    pos, recorded, order = {0: 0, 1: 0, 2: 0, 3: 0}, set(), []
+    # stream 2 is the copy stream, 3 the communication stream: prefer = 0 / 1 also make them the last / the
+    # first to run when they can
+    pref = {0: (0, 1, 3, 2), 1: (2, 3, 1, 0)}[prefer]
     # cudaStreamWaitEvent on an event that the host has not recorded yet is a no-op: every wait must come
     # after its record in issue (= list) order
     rec_at = {int(L["rec_ev"]): i for i, L in enumerate(launches) if L["rec_ev"] >= 0}
@@ -63,7 +64,7 @@ def _schedule(launches, prefer):
         w = int(launches[queues[st][pos[st]]]["wait_ev"])
         return w < 0 or w in recorded
 
-    while any(pos[st] < len(queues[st]) for st in (0, 1, 2)):
+    while any(pos[st] < len(queues[st]) for st in (0, 1, 2, 3)):
         cand = [st for st in pref if ready(st)]
         assert cand, "dead-lock in the launch plan's event graph"
         st = cand[0]
@@ -97,7 +98,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
             continue
         if kind == b200.K_BCAST:
             # bcast (off, len, root): the collective; every rank calls it in the same order
-            assert L["stream"] == 0 and bcast is not None
+            assert L["stream"] == 3 and bcast is not None
             for seg in F.plan_table("bcasts", b200.BCAST_DT)[first:first + cnt]:
                 bcast(int(seg["off"]), int(seg["len"]), int(seg["root"]))
             continue

@@ -20,8 +20,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 needs_ref = pytest.mark.skipif(not refd.have_ref(), reason="oracle/_ref/libref_driver.so not built")
 
 
-def run_ranks_as_threads(c, nranks, prefer=0):
+def run_ranks_as_threads(c, nranks, prefer=0, dist_run=None):
     """All ranks in one process; a broadcast is two barriers around a copy from the root's array."""
+    if dist_run is None:
+        os.environ.pop("CHOLMOD_B200_DIST_RUN", None)
+    else:
+        os.environ["CHOLMOD_B200_DIST_RUN"] = str(dist_run)     # read when the plans are built
     Fs = [b200.Factor(c.sym, device=-1, nranks=nranks, rank=r) for r in range(nranks)]
     Lxs = [np.zeros(c.sym["xsize"]) for _ in range(nranks)]
     hosts = [np.full(c.sym["xsize"], np.nan) for _ in range(nranks)]
@@ -52,13 +56,15 @@ def run_ranks_as_threads(c, nranks, prefer=0):
 
 
 @needs_ref
-@pytest.mark.parametrize("kind,size,ordering,nranks", [("lap3d7", 22, refd.CHOLMOD_METIS, 2),
-                                                       ("lap3d7", 22, refd.CHOLMOD_METIS, 4),
-                                                       ("lap2d9", 60, refd.CHOLMOD_METIS, 3),
-                                                       ("lap2d5", 40, refd.CHOLMOD_AMD, 8)])
-def test_distributed_plan_every_rank_ends_with_the_reference_factor(kind, size, ordering, nranks):
+@pytest.mark.parametrize("kind,size,ordering,nranks,dist_run", [("lap3d7", 22, refd.CHOLMOD_METIS, 2, 1),
+                                                                ("lap3d7", 22, refd.CHOLMOD_METIS, 4, None),
+                                                                ("lap3d7", 26, refd.CHOLMOD_METIS, 3, 1),
+                                                                ("lap2d9", 60, refd.CHOLMOD_METIS, 3, 1),
+                                                                ("lap2d5", 40, refd.CHOLMOD_AMD, 8, 2)])
+def test_distributed_plan_every_rank_ends_with_the_reference_factor(kind, size, ordering, nranks, dist_run):
     c = get_case(kind, size, ordering)
-    Fs, Lxs, hosts, minors = run_ranks_as_threads(c, nranks, prefer=1)
+    Fs, Lxs, hosts, minors = run_ranks_as_threads(c, nranks, prefer=1, dist_run=dist_run)
+    os.environ.pop("CHOLMOD_B200_DIST_RUN", None)
     for r in range(nranks):
         assert minors[r] is None
         assert c.rel_err(Lxs[r]) <= 1e-12, r
