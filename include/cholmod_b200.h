@@ -127,6 +127,12 @@ int b200_factor_device (b200_factor *f, double beta, int quick_return_if_not_pos
  * Replaces the per-supernode D2H of t_cholmod_gpu.c:1263-1273, :1403-1443. */
 int b200_download_factor (b200_factor *f, void *Lx) ;
 
+/* The host L->x passed to b200_super_numeric_* / b200_download_factor is page-locked (cudaHostRegister) the
+ * first time it is seen and stays so for later factorizations.  Call this before that memory is freed
+ * (cholmod_free_factor): Lx = the buffer, or NULL for "whatever is registered".  Always B200_OK unless the
+ * device cannot be selected. */
+int b200_forget_host_buffer (b200_factor *f, const void *Lx) ;
+
 /* Device address of the L->x arena (xsize values of the context's dtype), or NULL. */
 void *b200_device_Lx (b200_factor *f) ;
 

@@ -24,7 +24,7 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
-           "b200_comm_init", "b200_upload_values"]
+           "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -72,6 +72,7 @@ def lib():
     L.b200_comm_unique_id.argtypes = [vp]; L.b200_comm_unique_id.restype = cint
     L.b200_comm_init.argtypes = [vp, vp]; L.b200_comm_init.restype = cint
     L.b200_upload_values.argtypes = [vp, vp]; L.b200_upload_values.restype = cint
+    L.b200_forget_host_buffer.argtypes = [vp, vp]; L.b200_forget_host_buffer.restype = cint
     _lib = L
     return L
 
@@ -191,6 +192,7 @@ class Factor:
         if st < 0:
             raise B200Error(st, "b200_super_numeric")
         self.minor = int(minor.value)
+        self._pinned_Lx = Lx       # the library page-locked this buffer: keep it alive until close()
         return st, Lx
 
     # -- the same in three steps ---------------------------------------------------------------------

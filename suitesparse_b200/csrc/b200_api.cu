@@ -825,6 +825,20 @@ int b200_upload_factor (b200_factor *f, const void *Lx)
 
 void *b200_device_Lx (b200_factor *f) { return (f && f->device >= 0) ? (void *) f->d_Lx.p : nullptr ; }
 
+int b200_forget_host_buffer (b200_factor *f, const void *Lx)
+{
+    if (!f || f->device < 0) return B200_OK ;
+    if (f->reg_ptr && (Lx == nullptr || Lx == f->reg_ptr))
+    {
+        if (set_device (f)) return B200_GPU_PROBLEM ;
+        cudaStreamSynchronize (f->stream3) ;
+        cudaHostUnregister (f->reg_ptr) ;
+        cudaGetLastError () ;
+        f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+    }
+    return B200_OK ;
+}
+
 int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const double *Ax, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor)
 {

@@ -137,6 +137,23 @@ int cholmod_l_b200_deallocate (cholmod_common *Common)
     return 1 ;
 }
 
+// cholmod_l_free_factor (CHOLMOD/Utility/t_cholmod_free_factor.c): the numeric phase page-locks host L->x
+// the first time it writes into it; release that before the reference frees the memory.
+typedef int (*free_factor_fn) (cholmod_factor **, cholmod_common *) ;
+
+int cholmod_l_free_factor (cholmod_factor **L, cholmod_common *Common)
+{
+    if (L && *L && (*L)->x)
+    {
+        pthread_mutex_lock (&g_lock) ;
+        for (int k = 0 ; k < B200_SHIM_SLOTS ; k++)
+            if (g_slots [k].ctx) b200_forget_host_buffer (g_slots [k].ctx, (*L)->x) ;
+        pthread_mutex_unlock (&g_lock) ;
+    }
+    free_factor_fn next = (free_factor_fn) dlsym (RTLD_NEXT, "cholmod_l_free_factor") ;
+    return next ? next (L, Common) : 0 ;
+}
+
 // ---------------------------------------------------------------------------------------------
 // the worker entry: same contract as rd_/rs_cholmod_super_numeric_worker for stype < 0
 // ---------------------------------------------------------------------------------------------
