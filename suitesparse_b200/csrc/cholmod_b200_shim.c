@@ -140,18 +140,32 @@ int cholmod_l_b200_deallocate (cholmod_common *Common)
 // cholmod_l_free_factor (CHOLMOD/Utility/t_cholmod_free_factor.c): the numeric phase page-locks host L->x
 // the first time it writes into it; release that before the reference frees the memory.
 typedef int (*free_factor_fn) (cholmod_factor **, cholmod_common *) ;
+typedef int (*change_factor_fn) (int, int, int, int, int, cholmod_factor *, cholmod_common *) ;
+
+static void shim_forget (const void *Lx)
+{
+    if (!Lx) return ;
+    pthread_mutex_lock (&g_lock) ;
+    for (int k = 0 ; k < B200_SHIM_SLOTS ; k++)
+        if (g_slots [k].ctx) b200_forget_host_buffer (g_slots [k].ctx, Lx) ;
+    pthread_mutex_unlock (&g_lock) ;
+}
 
 int cholmod_l_free_factor (cholmod_factor **L, cholmod_common *Common)
 {
-    if (L && *L && (*L)->x)
-    {
-        pthread_mutex_lock (&g_lock) ;
-        for (int k = 0 ; k < B200_SHIM_SLOTS ; k++)
-            if (g_slots [k].ctx) b200_forget_host_buffer (g_slots [k].ctx, (*L)->x) ;
-        pthread_mutex_unlock (&g_lock) ;
-    }
+    if (L && *L) shim_forget ((*L)->x) ;
     free_factor_fn next = (free_factor_fn) dlsym (RTLD_NEXT, "cholmod_l_free_factor") ;
     return next ? next (L, Common) : 0 ;
+}
+
+// cholmod_l_change_factor (CHOLMOD/Cholesky/cholmod_change_factor.c) frees or reallocates L->x when a
+// supernodal numeric factor is converted (to simplicial, to symbolic): same release first.
+int cholmod_l_change_factor (int to_xtype, int to_ll, int to_super, int to_packed, int to_monotonic,
+    cholmod_factor *L, cholmod_common *Common)
+{
+    if (L && L->is_super && L->xtype != CHOLMOD_PATTERN) shim_forget (L->x) ;
+    change_factor_fn next = (change_factor_fn) dlsym (RTLD_NEXT, "cholmod_l_change_factor") ;
+    return next ? next (to_xtype, to_ll, to_super, to_packed, to_monotonic, L, Common) : 0 ;
 }
 
 // ---------------------------------------------------------------------------------------------
