@@ -31,6 +31,8 @@ extern "C" {
 
 #define B200_DOUBLE 0               /* CHOLMOD_DOUBLE */
 #define B200_SINGLE 4               /* CHOLMOD_SINGLE */
+#define B200_COMPLEX_DOUBLE 2       /* CHOLMOD_COMPLEX + CHOLMOD_DOUBLE: entries are (re,im) pairs of doubles */
+#define B200_COMPLEX_SINGLE 6       /* CHOLMOD_COMPLEX + CHOLMOD_SINGLE: (re,im) pairs of floats */
 
 /* Opaque factorization context: device-resident symbolic tables, the launch plan derived from them,
  * the L->x arena in HBM, streams and events.  One per (analysis, device); it is reused by every
@@ -58,7 +60,8 @@ int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes) ;
  * Replaces gpu_init (CHOLMOD/GPU/t_cholmod_gpu.c:84-160) and cholmod_l_gpu_allocate
  * (cholmod_gpu.c:426-543).  device < 0 builds the host-side plan only (no CUDA call is made; used by
  * the CPU tests of the planner) -- such a context cannot factorize.
- * dtype is B200_DOUBLE or B200_SINGLE.  On failure returns NULL and sets *status. */
+ * dtype is B200_DOUBLE, B200_SINGLE, B200_COMPLEX_DOUBLE or B200_COMPLEX_SINGLE (the factor is then
+ * Hermitian: A = L*L^H).  On failure returns NULL and sets *status. */
 b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
     const int64_t *px, const int64_t *s, int dtype, int device, int *status) ;
 
@@ -106,6 +109,19 @@ int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
 int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const float *Ax, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor) ;
 
+/* The Hermitian case: cd_/zd_ and cs_/zs_cholmod_super_numeric_worker (the COMPLEX and ZOMPLEX variants of
+ * t_cholmod_super_numeric_worker.c, selected at cholmod_super_numeric.c:262-322; zherk/zgemm/zpotrf/ztrsm at
+ * :786-803, :850-876, :1030-1048, :1184-1208).  A = tril of a Hermitian matrix.  Az == NULL: Ax holds nnz
+ * (re,im) pairs (CHOLMOD_COMPLEX); Az != NULL: Ax holds the real and Az the imaginary parts
+ * (CHOLMOD_ZOMPLEX).  Lx [2*xsize] receives (re,im) pairs whatever the input was, as in the reference
+ * (a supernodal L is never zomplex).  Only the real part of beta exists (:510-520); the imaginary part of
+ * the diagonal of A is ignored and the diagonal of L is real, as zpotrf does.  The context must have been
+ * created with B200_COMPLEX_DOUBLE (_z) or B200_COMPLEX_SINGLE (_c). */
+int b200_super_numeric_z (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const double *Ax, const double *Az, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor) ;
+int b200_super_numeric_c (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const float *Ax, const float *Az, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor) ;
+
 /* --- the same phase in three steps, for callers that keep A and L resident in HBM ---------------- */
 
 /* Copy A (host CSC as above, values of the context's dtype) to the device.  The pattern may change from
@@ -145,6 +161,10 @@ int b200_upload_factor (b200_factor *f, const void *Lx) ;
  * alias B).  Device counterpart of cholmod_super_lsolve / cholmod_super_ltsolve
  * (CHOLMOD/Supernodal/t_cholmod_super_solve_worker.c:20-303, :309-586). */
 int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
+
+/* The same with a complex factor: X = L^H\(L\B), B and X n-by-nrhs column-major (re,im) pairs of doubles
+ * (the "C" variants of the same file). */
+int b200_solve_z (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
 
 /* --- one panel step without any allocation ---------------------------------------------------------
  * This entry point has no counterpart in the reference.

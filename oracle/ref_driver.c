@@ -13,7 +13,7 @@
 //     (CHOLMOD/Demo/cholmod_dl_demo.c:609-617) applied to ANY factor values, so the factor the
 //     CUDA path produced can be pushed through the reference's own cholmod_l_solve.
 //
-// Everything is int64 ("cholmod_l_") and real; dtype is double or single.
+// Everything is int64 ("cholmod_l_"); real, complex or zomplex; dtype is double or single.
 
 #include "cholmod.h"
 #include <stdio.h>
@@ -81,6 +81,37 @@ int refd_set_matrix (void *hv, int64_t n, const int64_t *Ap, const int64_t *Ai,
     else
     {
         memcpy (h->A->x, Ax, (size_t) nz * sizeof (double)) ;
+    }
+    return 0 ;
+}
+
+// The same with an xtype: CHOLMOD_REAL (1; Ax real), CHOLMOD_COMPLEX (2; Ax = nz (re,im) pairs) or
+// CHOLMOD_ZOMPLEX (3; Ax real parts, Az imaginary parts).  A is Hermitian, one triangle stored.
+int refd_set_matrix_x (void *hv, int64_t n, const int64_t *Ap, const int64_t *Ai,
+    const double *Ax, const double *Az, int stype, int single, int xtype)
+{
+    refd *h = (refd *) hv ;
+    if (xtype == CHOLMOD_REAL) return refd_set_matrix (hv, n, Ap, Ai, Ax, stype, single) ;
+    cholmod_l_free_sparse (&h->A, &h->cm) ;
+    cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_factor (&h->L, &h->cm) ;
+    int64_t nz = Ap [n] ;
+    int xdtype = xtype + (single ? CHOLMOD_SINGLE : CHOLMOD_DOUBLE) ;
+    h->A = cholmod_l_allocate_sparse ((size_t) n, (size_t) n, (size_t) nz, 1, 1, stype, xdtype, &h->cm) ;
+    if (!h->A) return -1 ;
+    memcpy (h->A->p, Ap, (size_t) (n+1) * sizeof (int64_t)) ;
+    memcpy (h->A->i, Ai, (size_t) nz * sizeof (int64_t)) ;
+    int64_t nx = (xtype == CHOLMOD_COMPLEX) ? 2*nz : nz ;
+    if (single)
+    {
+        float *x = (float *) h->A->x ;
+        for (int64_t p = 0 ; p < nx ; p++) x [p] = (float) Ax [p] ;
+        if (xtype == CHOLMOD_ZOMPLEX) { float *z = (float *) h->A->z ; for (int64_t p = 0 ; p < nz ; p++) z [p] = (float) Az [p] ; }
+    }
+    else
+    {
+        memcpy (h->A->x, Ax, (size_t) nx * sizeof (double)) ;
+        if (xtype == CHOLMOD_ZOMPLEX) memcpy (h->A->z, Az, (size_t) nz * sizeof (double)) ;
     }
     return 0 ;
 }
@@ -180,7 +211,9 @@ void *refd_numeric_Lx (void *hv, int single)
     if (h->L->xtype == CHOLMOD_PATTERN)
     {
         h->L->dtype = single ? CHOLMOD_SINGLE : CHOLMOD_DOUBLE ;
-        cholmod_l_change_factor (CHOLMOD_REAL, 1, 1, 1, 1, h->L, &h->cm) ;
+        // a complex or zomplex A gives a complex supernodal L (cholmod_super_numeric.c:219-231)
+        int xt = (h->A && h->A->xtype != CHOLMOD_REAL) ? CHOLMOD_COMPLEX : CHOLMOD_REAL ;
+        cholmod_l_change_factor (xt, 1, 1, 1, 1, h->L, &h->cm) ;
         if (h->cm.status < CHOLMOD_OK) return NULL ;
     }
     h->L->is_ll = 1 ;
@@ -191,15 +224,18 @@ void *refd_numeric_Lx (void *hv, int single)
 void refd_set_minor (void *hv, int64_t minor) { ((refd *) hv)->L->minor = (size_t) minor ; }
 
 // x = A\b with the reference's cholmod_l_solve (CHOLMOD_A); b, x are n-by-nrhs column-major doubles
+// ((re,im) pairs of doubles when the factor is complex)
 int refd_solve (void *hv, const double *b, double *x, int64_t nrhs)
 {
     refd *h = (refd *) hv ;
     if (!h->L || !h->A) return -1 ;
     int64_t n = (int64_t) h->L->n ;
     int single = (h->L->dtype == CHOLMOD_SINGLE) ;
+    int cplx = (h->L->xtype == CHOLMOD_COMPLEX) ;
     cholmod_dense *B = cholmod_l_allocate_dense ((size_t) n, (size_t) nrhs, (size_t) n,
-        CHOLMOD_REAL + h->L->dtype, &h->cm) ;
+        (cplx ? CHOLMOD_COMPLEX : CHOLMOD_REAL) + h->L->dtype, &h->cm) ;
     if (!B) return -2 ;
+    if (cplx) n *= 2 ;      // from here on n counts doubles per column
     if (single) { float *bx = (float *) B->x ; for (int64_t i = 0 ; i < n*nrhs ; i++) bx [i] = (float) b [i] ; }
     else memcpy (B->x, b, (size_t) (n*nrhs) * sizeof (double)) ;
     double t = SUITESPARSE_TIME ;
@@ -304,9 +340,11 @@ const void *refd_get_ptr (void *hv, const char *name)
     if (h->A && !strcmp (name, "Ap")) return h->A->p ;
     if (h->A && !strcmp (name, "Ai")) return h->A->i ;
     if (h->A && !strcmp (name, "Ax")) return h->A->x ;
+    if (h->A && !strcmp (name, "Az")) return h->A->z ;
     if (h->S && !strcmp (name, "Sp")) return h->S->p ;
     if (h->S && !strcmp (name, "Si")) return h->S->i ;
     if (h->S && !strcmp (name, "Sx")) return h->S->x ;
+    if (h->S && !strcmp (name, "Sz")) return h->S->z ;
     if (!L) return NULL ;
     if (!strcmp (name, "Perm")) return L->Perm ;
     if (!strcmp (name, "ColCount")) return L->ColCount ;

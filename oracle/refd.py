@@ -40,6 +40,8 @@ def _driver():
         lib.refd_open.argtypes = [C.c_int]
         lib.refd_close.argtypes = [C.c_void_p]
         lib.refd_set_matrix.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        lib.refd_set_matrix_x.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_int, C.c_int, C.c_int]
         lib.refd_read_matrix.argtypes = [C.c_void_p, C.c_char_p]
         lib.refd_analyze.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.refd_seam.argtypes = [C.c_void_p]
@@ -76,6 +78,13 @@ class Ref:
         self.lib = _driver()
         self.h = self.lib.refd_open(int(nthreads))
         self.single = False
+        self.xtype = 1          # CHOLMOD_REAL 1, CHOLMOD_COMPLEX 2, CHOLMOD_ZOMPLEX 3
+
+    def _xd(self):
+        """numpy dtype of the entries of a complex-or-real array of this session (S, L)."""
+        if self.xtype == 1:
+            return np.float32 if self.single else np.float64
+        return np.complex64 if self.single else np.complex128
 
     def close(self):
         if self.h:
@@ -101,12 +110,28 @@ class Ref:
     def _ptr(self, name):
         return self.lib.refd_get_ptr(self.h, name.encode())
 
-    def set_matrix(self, n, Ap, Ai, Ax, stype=-1, single=False):
+    def set_matrix(self, n, Ap, Ai, Ax, stype=-1, single=False, zomplex=False):
+        """Real Ax: a symmetric matrix.  Complex Ax: a Hermitian one, stored as CHOLMOD_COMPLEX, or as
+        CHOLMOD_ZOMPLEX (split real / imaginary arrays) with zomplex=True."""
         Ap = np.ascontiguousarray(Ap, dtype=np.int64)
         Ai = np.ascontiguousarray(Ai, dtype=np.int64)
-        Ax = np.ascontiguousarray(Ax, dtype=np.float64)
         self.single = bool(single)
-        rc = self.lib.refd_set_matrix(self.h, n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, stype, int(single))
+        if np.iscomplexobj(Ax):
+            Ax = np.ascontiguousarray(Ax, dtype=np.complex128)
+            if zomplex:
+                self.xtype = 3
+                re, im = np.ascontiguousarray(Ax.real), np.ascontiguousarray(Ax.imag)
+                rc = self.lib.refd_set_matrix_x(self.h, n, Ap.ctypes.data, Ai.ctypes.data, re.ctypes.data,
+                                                im.ctypes.data, stype, int(single), 3)
+            else:
+                self.xtype = 2
+                rc = self.lib.refd_set_matrix_x(self.h, n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, None,
+                                                stype, int(single), 2)
+        else:
+            self.xtype = 1
+            Ax = np.ascontiguousarray(Ax, dtype=np.float64)
+            rc = self.lib.refd_set_matrix(self.h, n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, stype,
+                                          int(single))
         if rc:
             raise RuntimeError("refd_set_matrix failed")
 
@@ -145,9 +170,12 @@ class Ref:
         if rc:
             raise RuntimeError("refd_seam failed")
         n, nz = self.geti("n"), self.geti("nnzS")
-        xd = np.float32 if self.single else np.float64
-        return (_view(self._ptr("Sp"), n + 1, np.int64).copy(), _view(self._ptr("Si"), nz, np.int64).copy(),
-                _view(self._ptr("Sx"), nz, xd).copy())
+        Sp, Si = _view(self._ptr("Sp"), n + 1, np.int64).copy(), _view(self._ptr("Si"), nz, np.int64).copy()
+        if self.xtype == 3:     # zomplex: returned as one complex array
+            rd = np.float32 if self.single else np.float64
+            Sx = _view(self._ptr("Sx"), nz, rd) + 1j * _view(self._ptr("Sz"), nz, rd)
+            return Sp, Si, Sx.astype(self._xd())
+        return Sp, Si, _view(self._ptr("Sx"), nz, self._xd()).copy()
 
     def super_numeric(self, beta=0.0):
         """Reference CPU numeric phase at the seam; returns Common->status."""
@@ -158,7 +186,11 @@ class Ref:
         return int(self.lib.refd_factorize(self.h, float(beta)))
 
     def Lx(self):
-        xd = np.float32 if self.geti("dtype") == 4 else np.float64
+        single = self.geti("dtype") == 4
+        if self.geti("xtype") == 2:
+            xd = np.complex64 if single else np.complex128
+        else:
+            xd = np.float32 if single else np.float64
         return _view(self._ptr("Lx"), self.geti("xsize"), xd)
 
     def numeric_Lx(self):
@@ -166,13 +198,13 @@ class Ref:
         p = self.lib.refd_numeric_Lx(self.h, int(self.single))
         if not p:
             raise RuntimeError("refd_numeric_Lx failed")
-        return _view(p, self.geti("xsize"), np.float32 if self.single else np.float64)
+        return _view(p, self.geti("xsize"), self._xd())
 
     def set_minor(self, minor):
         self.lib.refd_set_minor(self.h, int(minor))
 
     def solve(self, b):
-        b = np.asfortranarray(b, dtype=np.float64)
+        b = np.asfortranarray(b, dtype=np.float64 if self.xtype == 1 else np.complex128)
         n = self.geti("n")
         nrhs = 1 if b.ndim == 1 else b.shape[1]
         x = np.zeros_like(b, order="F")
@@ -183,9 +215,35 @@ class Ref:
         return x
 
     def resid(self, x, b):
+        if self.xtype != 1:
+            return self._resid_complex(x, b)
         x = np.ascontiguousarray(x, dtype=np.float64)
         b = np.ascontiguousarray(b, dtype=np.float64)
         return float(self.lib.refd_resid(self.h, x.ctypes.data, b.ctypes.data))
+
+    def _resid_complex(self, x, b):
+        """The same scaled residual for a Hermitian A (one triangle stored), in numpy."""
+        n, nz = self.geti("n"), self.geti("nnzA")
+        Ap, Ai = _view(self._ptr("Ap"), n + 1, np.int64), _view(self._ptr("Ai"), nz, np.int64)
+        rd = np.float32 if self.single else np.float64
+        if self.xtype == 3:
+            Ax = _view(self._ptr("Ax"), nz, rd).astype(np.float64) + 1j * _view(self._ptr("Az"), nz, rd)
+        else:
+            Ax = _view(self._ptr("Ax"), nz, np.complex64 if self.single else np.complex128).astype(np.complex128)
+        col = np.repeat(np.arange(n), np.diff(Ap))
+        stype = self.geti("stypeA")
+        keep = (Ai >= col) if stype < 0 else (Ai <= col)
+        i, j, a = Ai[keep], col[keep], Ax[keep]
+        x = np.asarray(x, dtype=np.complex128).ravel()
+        b = np.asarray(b, dtype=np.complex128).ravel()
+        r = -b.copy()
+        rowsum = np.zeros(n)
+        np.add.at(r, i, a * x[j])
+        np.add.at(rowsum, i, np.abs(a))
+        off = i != j
+        np.add.at(r, j[off], np.conj(a[off]) * x[i[off]])
+        np.add.at(rowsum, j[off], np.abs(a[off]))
+        return float(np.abs(r).max() / (rowsum.max() * np.abs(x).max() + np.abs(b).max()))
 
 
 _port = None
@@ -195,11 +253,12 @@ def _portlib():
     global _port
     if _port is None:
         lib = C.CDLL(os.path.join(_REF, "libsnport.so"))
-        for f in (lib.sn_port_d, lib.sn_port_s):
+        for f in (lib.sn_port_d, lib.sn_port_s, lib.sn_port_z, lib.sn_port_c):
             f.restype = C.c_int
             f.argtypes = [C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
         lib.sn_port_solve_d.argtypes = [C.c_int64] + [C.c_void_p] * 6
+        lib.sn_port_solve_z.argtypes = [C.c_int64] + [C.c_void_p] * 6
         _port = lib
     return _port
 
@@ -207,15 +266,17 @@ def _portlib():
 def port_factor(sym, Sp, Si, Sx, beta=0.0, quick_return=False, Snz=None):
     """Run the plain-C restatement.  Returns (status, minor, Lx)."""
     lib = _portlib()
-    single = (np.asarray(Sx).dtype == np.float32)
-    xd = np.float32 if single else np.float64
+    xd = np.asarray(Sx).dtype
+    if xd not in (np.float32, np.float64, np.complex64, np.complex128):
+        xd = np.dtype(np.float64)
     Sp = np.ascontiguousarray(Sp, dtype=np.int64)
     Si = np.ascontiguousarray(Si, dtype=np.int64)
     Sx = np.ascontiguousarray(Sx, dtype=xd)
     Lx = np.full(sym["xsize"], np.nan, dtype=xd)
     minor = C.c_int64(-1)
     sup, pi, px, s = (np.ascontiguousarray(sym[k], dtype=np.int64) for k in ("super", "pi", "px", "s"))
-    fn = lib.sn_port_s if single else lib.sn_port_d
+    fn = {np.dtype(np.float64): lib.sn_port_d, np.dtype(np.float32): lib.sn_port_s,
+          np.dtype(np.complex128): lib.sn_port_z, np.dtype(np.complex64): lib.sn_port_c}[np.dtype(xd)]
     nzp = None if Snz is None else np.ascontiguousarray(Snz, dtype=np.int64).ctypes.data
     st = fn(sym["n"], sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
             sym["xsize"], Sp.ctypes.data, Si.ctypes.data, nzp, Sx.ctypes.data, float(beta), int(quick_return),
@@ -227,8 +288,9 @@ def port_solve(sym, Lx, b_perm):
     """Solve L L' x = b in the permuted ordering with the plain-C restatement."""
     lib = _portlib()
     sup, pi, px, s = (np.ascontiguousarray(sym[k], dtype=np.int64) for k in ("super", "pi", "px", "s"))
-    Lx = np.ascontiguousarray(Lx, dtype=np.float64)
-    x = np.array(b_perm, dtype=np.float64, copy=True)
-    lib.sn_port_solve_d(sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
+    cplx = np.iscomplexobj(Lx)
+    Lx = np.ascontiguousarray(Lx, dtype=np.complex128 if cplx else np.float64)
+    x = np.array(b_perm, dtype=np.complex128 if cplx else np.float64, copy=True)
+    (lib.sn_port_solve_z if cplx else lib.sn_port_solve_d)(sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
                         Lx.ctypes.data, x.ctypes.data)
     return x

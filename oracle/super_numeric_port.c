@@ -1,8 +1,9 @@
 // oracle/super_numeric_port.c -- TEST INFRASTRUCTURE (the oracle), not product code.
 //
 // A plain-C restatement of the reference's left-looking supernodal numeric Cholesky,
-// CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c ("SNW" below), real case, int64
-// indices, for double (sn_port_d) and float (sn_port_s).  It takes the arrays of the
+// CHOLMOD/Supernodal/t_cholmod_super_numeric_worker.c ("SNW" below), int64 indices, for
+// double (sn_port_d), float (sn_port_s) and the Hermitian case in complex double (sn_port_z)
+// and complex float (sn_port_c; entries are (re,im) pairs, the CHOLMOD_COMPLEX layout).  It takes the arrays of the
 // supernodal symbolic factor (L->super, pi, px, s) and the seam matrix S = tril(P A P')
 // as plain pointers; it does not include cholmod.h and calls no BLAS: the four dense
 // kernels are written out as loops, so it is slow and meant for small cases.
@@ -17,16 +18,17 @@
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
+#include <complex.h>
 
 #define SNP_OK 0
 #define SNP_NOT_POSDEF 1
 #define SNP_OUT_OF_MEMORY (-2)
 
-#define SNP_TEMPLATE(NAME, REAL)                                                                  \
+#define SNP_TEMPLATE(NAME, REAL, SCALAR, CONJ, REPART)                                                                \
 int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,                    \
     const int64_t *Lpx, const int64_t *Ls, int64_t xsize,                                         \
-    const int64_t *Ap, const int64_t *Ai, const int64_t *Anz, const REAL *Ax,                     \
-    double beta, int quick_return_if_not_posdef, REAL *Lx, int64_t *minor_out)                    \
+    const int64_t *Ap, const int64_t *Ai, const int64_t *Anz, const SCALAR *Ax,                    \
+    double beta, int quick_return_if_not_posdef, SCALAR *Lx, int64_t *minor_out)                  \
 {                                                                                                 \
     /* workspace, SNW:211-221 */                                                                  \
     int64_t *SuperMap = malloc ((size_t) (n+1) * sizeof (int64_t)) ;                              \
@@ -37,7 +39,7 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
     int64_t *Next_save = malloc ((size_t) (nsuper+1) * sizeof (int64_t)) ;                        \
     int64_t *Lpos_save = malloc ((size_t) (nsuper+1) * sizeof (int64_t)) ;                        \
     int64_t maxc = 1 ;                                                                            \
-    REAL *C = NULL ;                                                                              \
+    SCALAR *C = NULL ;                                                                            \
     int status = SNP_OK ;                                                                         \
     if (!SuperMap || !Map || !Head || !Next || !Lpos || !Next_save || !Lpos_save)                 \
     { status = SNP_OUT_OF_MEMORY ; goto done ; }                                                  \
@@ -94,7 +96,7 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
             if (ndrow1*ndrow2 > maxc || !C)                                                       \
             {                                                                                     \
                 if (ndrow1*ndrow2 > maxc) maxc = ndrow1*ndrow2 ;                                  \
-                free (C) ; C = malloc ((size_t) maxc * sizeof (REAL)) ;                           \
+                free (C) ; C = malloc ((size_t) maxc * sizeof (SCALAR)) ;                         \
                 if (!C) { status = SNP_OUT_OF_MEMORY ; goto done ; }                              \
             }                                                                                     \
             /* C = [L1;L2] * L1', lower part of the top block only: the dsyrk of SNW:769 */       \
@@ -102,9 +104,9 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
             for (int64_t j = 0 ; j < ndrow1 ; j++)                                                \
                 for (int64_t i = j ; i < ndrow2 ; i++)                                            \
                 {                                                                                 \
-                    REAL acc = 0 ;                                                                \
+                    SCALAR acc = 0 ;                                                              \
                     for (int64_t k = 0 ; k < ndcol ; k++)                                         \
-                        acc += Lx [pdx1 + i + k*ndrow] * Lx [pdx1 + j + k*ndrow] ;                \
+                        acc += Lx [pdx1 + i + k*ndrow] * CONJ (Lx [pdx1 + j + k*ndrow]) ;         \
                     C [i + j*ndrow2] = acc ;                                                      \
                 }                                                                                 \
             /* relative map + assembly, SNW:897-930 */                                            \
@@ -131,15 +133,17 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
         int64_t info = 0 ;                                                                        \
         for (int64_t j = 0 ; j < nscol2 && !info ; j++)                                           \
         {                                                                                         \
-            REAL ajj = Lx [psx + j + j*nsrow] ;                                                   \
-            for (int64_t k = 0 ; k < j ; k++) ajj -= Lx [psx + j + k*nsrow] * Lx [psx + j + k*nsrow] ; \
+            REAL ajj = REPART (Lx [psx + j + j*nsrow]) ;      /* zpotrf: the real part only */    \
+            for (int64_t k = 0 ; k < j ; k++)                                                     \
+                ajj -= REPART (Lx [psx + j + k*nsrow] * CONJ (Lx [psx + j + k*nsrow])) ;          \
             if (!(ajj > 0)) { Lx [psx + j + j*nsrow] = ajj ; info = j+1 ; break ; }               \
             ajj = (REAL) sqrt ((double) ajj) ;                                                    \
             Lx [psx + j + j*nsrow] = ajj ;                                                        \
             for (int64_t i = j+1 ; i < nscol2 ; i++)                                              \
             {                                                                                     \
-                REAL v = Lx [psx + i + j*nsrow] ;                                                 \
-                for (int64_t k = 0 ; k < j ; k++) v -= Lx [psx + i + k*nsrow] * Lx [psx + j + k*nsrow] ; \
+                SCALAR v = Lx [psx + i + j*nsrow] ;                                               \
+                for (int64_t k = 0 ; k < j ; k++)                                                 \
+                    v -= Lx [psx + i + k*nsrow] * CONJ (Lx [psx + j + k*nsrow]) ;                 \
                 Lx [psx + i + j*nsrow] = v / ajj ;                                                \
             }                                                                                     \
         }                                                                                         \
@@ -165,11 +169,12 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
         {                                                                                         \
             for (int64_t j = 0 ; j < nscol2 ; j++)                                                \
             {                                                                                     \
-                REAL ljj = Lx [psx + j + j*nsrow] ;                                               \
+                REAL ljj = REPART (Lx [psx + j + j*nsrow]) ;                                      \
                 for (int64_t i = nscol2 ; i < nsrow ; i++)                                        \
                 {                                                                                 \
-                    REAL v = Lx [psx + i + j*nsrow] ;                                             \
-                    for (int64_t k = 0 ; k < j ; k++) v -= Lx [psx + i + k*nsrow] * Lx [psx + j + k*nsrow] ; \
+                    SCALAR v = Lx [psx + i + j*nsrow] ;                                           \
+                    for (int64_t k = 0 ; k < j ; k++)                                             \
+                        v -= Lx [psx + i + k*nsrow] * CONJ (Lx [psx + j + k*nsrow]) ;             \
                     Lx [psx + i + j*nsrow] = v / ljj ;                                            \
                 }                                                                                 \
             }                                                                                     \
@@ -190,8 +195,12 @@ done:                                                                           
     return status ;                                                                               \
 }
 
-SNP_TEMPLATE (sn_port_d, double)
-SNP_TEMPLATE (sn_port_s, float)
+#define SNP_ID(x) (x)
+SNP_TEMPLATE (sn_port_d, double, double, SNP_ID, SNP_ID)
+SNP_TEMPLATE (sn_port_s, float, float, SNP_ID, SNP_ID)
+/* the COMPLEX variants: zherk/zgemm "C" (SNW:786-803, :850-876), zpotrf (:1030-1048), ztrsm "C" (:1184-1208) */
+SNP_TEMPLATE (sn_port_z, double, double _Complex, conj, creal)
+SNP_TEMPLATE (sn_port_c, float, float _Complex, conjf, crealf)
 
 // Supernodal forward/back solve L L' x = b for one right-hand side, double, following
 // CHOLMOD/Supernodal/t_cholmod_super_solve_worker.c:20-303 (lsolve) and :309-586 (ltsolve),
@@ -219,6 +228,35 @@ int sn_port_solve_d (int64_t nsuper, const int64_t *Super, const int64_t *Lpi, c
             double v = x [k1+j] ;
             for (int64_t i = j+1 ; i < nsrow ; i++) v -= Lx [psx + i + j*nsrow] * x [Ls [psi+i]] ;
             x [k1+j] = v / Lx [psx + j + j*nsrow] ;
+        }
+    }
+    return 0 ;
+}
+
+// The same for a complex factor: L L^H x = b (the "C" variants of the same file).
+int sn_port_solve_z (int64_t nsuper, const int64_t *Super, const int64_t *Lpi, const int64_t *Lpx,
+    const int64_t *Ls, const double _Complex *Lx, double _Complex *x)
+{
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        int64_t k1 = Super [s], nscol = Super [s+1] - k1, psi = Lpi [s], psx = Lpx [s] ;
+        int64_t nsrow = Lpi [s+1] - psi ;
+        for (int64_t j = 0 ; j < nscol ; j++)
+        {
+            double _Complex xj = x [k1+j] / creal (Lx [psx + j + j*nsrow]) ;
+            x [k1+j] = xj ;
+            for (int64_t i = j+1 ; i < nsrow ; i++) x [Ls [psi+i]] -= Lx [psx + i + j*nsrow] * xj ;
+        }
+    }
+    for (int64_t s = nsuper-1 ; s >= 0 ; s--)
+    {
+        int64_t k1 = Super [s], nscol = Super [s+1] - k1, psi = Lpi [s], psx = Lpx [s] ;
+        int64_t nsrow = Lpi [s+1] - psi ;
+        for (int64_t j = nscol-1 ; j >= 0 ; j--)
+        {
+            double _Complex v = x [k1+j] ;
+            for (int64_t i = j+1 ; i < nsrow ; i++) v -= conj (Lx [psx + i + j*nsrow]) * x [Ls [psi+i]] ;
+            x [k1+j] = v / creal (Lx [psx + j + j*nsrow]) ;
         }
     }
     return 0 ;

@@ -13,7 +13,9 @@ import os
 import numpy as np
 
 OK, NOT_POSDEF, OUT_OF_MEMORY, TOO_LARGE, INVALID, GPU_PROBLEM = 0, 1, -2, -3, -4, -5
-DOUBLE, SINGLE = 0, 4
+DOUBLE, SINGLE, COMPLEX_DOUBLE, COMPLEX_SINGLE = 0, 4, 2, 6
+_DTYPE_CODE = {np.dtype(np.float64): DOUBLE, np.dtype(np.float32): SINGLE,
+               np.dtype(np.complex128): COMPLEX_DOUBLE, np.dtype(np.complex64): COMPLEX_SINGLE}
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libcholmod_b200.so")
@@ -24,7 +26,8 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_upload_matrix", "b200_factor_device", "b200_download_factor", "b200_device_Lx",
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
-           "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer"]
+           "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer", "b200_super_numeric_z",
+           "b200_super_numeric_c", "b200_solve_z"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -55,6 +58,9 @@ def lib():
     L.b200_get_double.argtypes = [vp, C.c_char_p]; L.b200_get_double.restype = dbl
     for fn in (L.b200_super_numeric_d, L.b200_super_numeric_s):
         fn.argtypes = [vp, vp, vp, vp, vp, dbl, cint, vp, vp]; fn.restype = cint
+    for fn in (L.b200_super_numeric_z, L.b200_super_numeric_c):
+        fn.argtypes = [vp, vp, vp, vp, vp, vp, dbl, cint, vp, vp]; fn.restype = cint
+    L.b200_solve_z.argtypes = [vp, vp, vp, i64]; L.b200_solve_z.restype = cint
     L.b200_upload_matrix.argtypes = [vp, vp, vp, vp, vp]; L.b200_upload_matrix.restype = cint
     L.b200_factor_device.argtypes = [vp, dbl, cint, vp]; L.b200_factor_device.restype = cint
     L.b200_download_factor.argtypes = [vp, vp]; L.b200_download_factor.restype = cint
@@ -126,13 +132,14 @@ class Factor:
         self.L = lib()
         self.n, self.nsuper = int(sym["n"]), int(sym["nsuper"])
         self.dtype = np.dtype(dtype)
-        if self.dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
-            raise ValueError("dtype must be float64 or float32")
+        if self.dtype not in _DTYPE_CODE:
+            raise ValueError("dtype must be float64, float32, complex128 or complex64")
+        self.is_complex = self.dtype.kind == "c"
         sup, pi, px, s = _i64(sym["super"]), _i64(sym["pi"]), _i64(sym["px"]), _i64(sym["s"])
         st = C.c_int(0)
         self.nranks, self.rank = int(nranks), int(rank)
         self.h = self.L.b200_create_dist(self.n, self.nsuper, sup.ctypes.data, pi.ctypes.data, px.ctypes.data,
-                                         s.ctypes.data, DOUBLE if self.dtype == np.float64 else SINGLE,
+                                         s.ctypes.data, _DTYPE_CODE[self.dtype],
                                          int(device), self.nranks, self.rank, C.byref(st))
         if not self.h:
             raise B200Error(st.value, "b200_create")
@@ -177,18 +184,34 @@ class Factor:
             raise B200Error(st, "b200_set_int(%s)" % name)
 
     # -- the drop-in call: host A in, host L->x out ------------------------------------------------
-    def super_numeric(self, Ap, Ai, Ax, beta=0.0, quick_return=False, Lx=None, Anz=None):
-        """Returns (status, Lx); status is OK or NOT_POSDEF (self.minor then holds L->minor)."""
+    def super_numeric(self, Ap, Ai, Ax, beta=0.0, quick_return=False, Lx=None, Anz=None, Az=None):
+        """Returns (status, Lx); status is OK or NOT_POSDEF (self.minor then holds L->minor).
+        Complex contexts: Ax is complex (CHOLMOD_COMPLEX), or Ax and Az are the real and imaginary parts
+        (CHOLMOD_ZOMPLEX); Lx is complex either way."""
         Ap, Ai = _i64(Ap), _i64(Ai)
-        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
         if Lx is None:
             Lx = np.empty(self.xsize, dtype=self.dtype)
         assert Lx.dtype == self.dtype and Lx.size == self.xsize and Lx.flags.c_contiguous
         nzp = None if Anz is None else _i64(Anz)
         minor = C.c_int64(-1)
-        fn = self.L.b200_super_numeric_d if self.dtype == np.float64 else self.L.b200_super_numeric_s
-        st = fn(self.h, Ap.ctypes.data, Ai.ctypes.data, None if nzp is None else nzp.ctypes.data,
-                Ax.ctypes.data, float(beta), int(quick_return), Lx.ctypes.data, C.byref(minor))
+        nzptr = None if nzp is None else nzp.ctypes.data
+        if self.is_complex:
+            real_dt = np.float64 if self.dtype == np.complex128 else np.float32
+            fn = self.L.b200_super_numeric_z if self.dtype == np.complex128 else self.L.b200_super_numeric_c
+            if Az is None:
+                Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+                azptr = None
+            else:
+                Ax = np.ascontiguousarray(Ax, dtype=real_dt)
+                Az = np.ascontiguousarray(Az, dtype=real_dt)
+                azptr = Az.ctypes.data
+            st = fn(self.h, Ap.ctypes.data, Ai.ctypes.data, nzptr, Ax.ctypes.data, azptr, float(beta),
+                    int(quick_return), Lx.ctypes.data, C.byref(minor))
+        else:
+            Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+            fn = self.L.b200_super_numeric_d if self.dtype == np.float64 else self.L.b200_super_numeric_s
+            st = fn(self.h, Ap.ctypes.data, Ai.ctypes.data, nzptr, Ax.ctypes.data, float(beta), int(quick_return),
+                    Lx.ctypes.data, C.byref(minor))
         if st < 0:
             raise B200Error(st, "b200_super_numeric")
         self.minor = int(minor.value)
@@ -238,11 +261,12 @@ class Factor:
         return self.L.b200_device_Lx(self.h)
 
     def solve(self, B):
-        """X = L'\\(L\\B) in the permuted ordering; B is n or n-by-nrhs."""
-        B = np.asfortranarray(B, dtype=np.float64)
+        """X = L'\\(L\\B) in the permuted ordering (L^H for a complex factor); B is n or n-by-nrhs."""
+        B = np.asfortranarray(B, dtype=np.complex128 if self.is_complex else np.float64)
         nrhs = 1 if B.ndim == 1 else B.shape[1]
         X = np.empty_like(B, order="F")
-        st = self.L.b200_solve_d(self.h, B.ctypes.data, X.ctypes.data, nrhs)
+        fn = self.L.b200_solve_z if self.is_complex else self.L.b200_solve_d
+        st = fn(self.h, B.ctypes.data, X.ctypes.data, nrhs)
         if st < 0:
             raise B200Error(st, "b200_solve_d")
         return X

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <new>
 #include <vector>
+#include <type_traits>
 #include <dlfcn.h>
 #include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
 
@@ -122,6 +123,7 @@ struct b200_factor
     DevBuf<int32_t> d_ssmall ;
     DevBuf<SolveBlk> d_sblk ;
     DevBuf<SolveTile> d_stile ;
+    std::vector<unsigned char> h_Ax ;       // zomplex input (Ax, Az) interleaved before the upload
     bool have_A = false, A_unpacked = false ;
     int64_t A_nz = 0 ;
     // host-registered output buffer (pinned once, reused by later factorizations)
@@ -149,6 +151,23 @@ bool cuda_ok (cudaError_t e, const char *what)
 
 #define CK(call, what) do { if (!cuda_ok ((call), what)) return B200_GPU_PROBLEM ; } while (0)
 
+bool dtype_ok (int dtype)
+{
+    return dtype == B200_DOUBLE || dtype == B200_SINGLE || dtype == B200_COMPLEX_DOUBLE || dtype == B200_COMPLEX_SINGLE ;
+}
+bool dtype_complex (int dtype) { return dtype == B200_COMPLEX_DOUBLE || dtype == B200_COMPLEX_SINGLE ; }
+// double and complex double have the FP64 tensor pipe (and with it the inverse-based panel solves)
+bool dtype_dmma (int dtype) { return dtype == B200_DOUBLE || dtype == B200_COMPLEX_DOUBLE ; }
+size_t dtype_esize (int dtype)
+{
+    return (dtype == B200_DOUBLE) ? 8 : (dtype == B200_SINGLE) ? 4 : (dtype == B200_COMPLEX_DOUBLE) ? 16 : 8 ;
+}
+
+// run `call` with T = the entry type of the context
+#define B200_DISPATCH(dtype, call) \
+    ((dtype) == B200_DOUBLE ? call<double> : (dtype) == B200_SINGLE ? call<float> : \
+     (dtype) == B200_COMPLEX_DOUBLE ? call<zdouble> : call<cfloat>)
+
 int set_device (const b200_factor *f)
 {
     if (!f || f->device < 0) return B200_GPU_PROBLEM ;
@@ -173,10 +192,38 @@ int kernel_attrs (int device)
         (int) potrf_smem_bytes<double> ()), "attr potrf") ;
     CK (cudaFuncSetAttribute (k_potrf_tile<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) potrf_smem_bytes<float> ()), "attr potrf") ;
+    CK (cudaFuncSetAttribute (k_potrf_tile<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) potrf_smem_bytes<zdouble> ()), "attr potrf") ;
+    CK (cudaFuncSetAttribute (k_potrf_tile<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) potrf_smem_bytes<cfloat> ()), "attr potrf") ;
+    CK (cudaFuncSetAttribute (k_upd_zmma<BIG_TM, BIG_TN, 32, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) zmma_smem_bytes<BIG_TM, BIG_TN> ()), "attr z128") ;
+    CK (cudaFuncSetAttribute (k_upd_zmma<64, 64, 32, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) zmma_smem_bytes<64, 64> ()), "attr z64") ;
+    CK (cudaFuncSetAttribute (k_trsm_zinv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) trsm_zinv_smem_bytes<32> ()), "attr trsm_zinv32") ;
+    CK (cudaFuncSetAttribute (k_trsm_zinv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) trsm_zinv_smem_bytes<64> ()), "attr trsm_zinv64") ;
+    CK (cudaFuncSetAttribute (k_upd_cfma<cfloat, BIG_TM, BIG_TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) cfma_smem_bytes<cfloat, BIG_TM, BIG_TN> ()), "attr c128") ;
+    CK (cudaFuncSetAttribute (k_upd_cfma<cfloat, 64, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) cfma_smem_bytes<cfloat, 64, 64> ()), "attr c64") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
+    CK (cudaFuncSetAttribute (k_solve_fwd<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
+    CK (cudaFuncSetAttribute (k_solve_bwd<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
+    CK (cudaFuncSetAttribute (k_solve_fwd<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
+    CK (cudaFuncSetAttribute (k_solve_bwd<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
+    CK (cudaFuncSetAttribute (k_solve_diag<zdouble, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) solve_diag_smem_bytes<zdouble> ()), "attr diag") ;
+    CK (cudaFuncSetAttribute (k_solve_diag<zdouble, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) solve_diag_smem_bytes<zdouble> ()), "attr diag") ;
+    CK (cudaFuncSetAttribute (k_solve_diag<cfloat, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) solve_diag_smem_bytes<cfloat> ()), "attr diag") ;
+    CK (cudaFuncSetAttribute (k_solve_diag<cfloat, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) solve_diag_smem_bytes<cfloat> ()), "attr diag") ;
     if (device < 64) g_attr_done [device] = true ;
     return B200_OK ;
 }
@@ -228,12 +275,14 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             // finished panels / subtrees travel from their owner to every other rank over NVLink
             NcclApi *nc = nccl_api () ;
             if (!nc || !f->comm) { fprintf (stderr, "cholmod_b200: distributed plan without b200_comm_init\n") ; return B200_INVALID ; }
-            const ncclDataType_t dt = (sizeof (T) == 8) ? ncclDouble : ncclFloat ;
+            typedef typename num<T>::real R ;
+            const ncclDataType_t dt = (sizeof (R) == 8) ? ncclDouble : ncclFloat ;
+            constexpr size_t per = sizeof (T) / sizeof (R) ;       // 2 for (re,im) entries
             nc->GroupStart () ;
             for (int64_t c = L.first ; c < L.first + L.count ; c++)
             {
                 const BcastSeg &seg = P.bcasts [c] ;
-                ncclResult_t r = nc->Broadcast (Lx + seg.off, Lx + seg.off, (size_t) seg.len, dt, seg.root, f->comm, st) ;
+                ncclResult_t r = nc->Broadcast (Lx + seg.off, Lx + seg.off, (size_t) seg.len * per, dt, seg.root, f->comm, st) ;
                 if (r != ncclSuccess) { nc->GroupEnd () ; fprintf (stderr, "cholmod_b200: ncclBroadcast: %s\n", nc->GetErrorString (r)) ; return B200_GPU_PROBLEM ; }
             }
             if (nc->GroupEnd () != ncclSuccess) return B200_GPU_PROBLEM ;
@@ -257,22 +306,36 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                 break ;
             }
             case K_UPD_D64:
-                if (sizeof (T) == 8)
+                if constexpr (std::is_same<T, double>::value)
                     k_upd_dmma<64, 64, 32, 32><<<(unsigned) L.count, 128, dmma_smem_bytes<64, 64> (), st>>>
-                        (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
-                else
+                        (tiles + L.first, items, relmap, Lx) ;
+                else if constexpr (std::is_same<T, float>::value)
                     k_upd_ffma<64, 64><<<(unsigned) L.count, 64, ffma_smem_bytes<64, 64> (), st>>>
-                        (tiles + L.first, items, relmap, reinterpret_cast<float *> (Lx)) ;
+                        (tiles + L.first, items, relmap, Lx) ;
+                else if constexpr (std::is_same<T, zdouble>::value)
+                    k_upd_zmma<64, 64, 32, 16><<<(unsigned) L.count, 256, zmma_smem_bytes<64, 64> (), st>>>
+                        (tiles + L.first, items, relmap, Lx) ;
+                else
+                    k_upd_cfma<T, 64, 64><<<(unsigned) L.count, 256, cfma_smem_bytes<T, 64, 64> (), st>>>
+                        (tiles + L.first, items, relmap, Lx) ;
                 break ;
             case K_UPD_D128:
-                if (sizeof (T) == 8)
+                if constexpr (std::is_same<T, double>::value)
                     k_upd_dmma<BIG_TM, BIG_TN, 32, 64><<<(unsigned) L.count, (BIG_TM / 32) * (BIG_TN / 64) * 32,
                         dmma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
-                        (tiles + L.first, items, relmap, reinterpret_cast<double *> (Lx)) ;
-                else
+                        (tiles + L.first, items, relmap, Lx) ;
+                else if constexpr (std::is_same<T, float>::value)
                     k_upd_ffma<BIG_TM, BIG_TN><<<(unsigned) L.count, (BIG_TM / 8) * (BIG_TN / 8),
                         ffma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
-                        (tiles + L.first, items, relmap, reinterpret_cast<float *> (Lx)) ;
+                        (tiles + L.first, items, relmap, Lx) ;
+                else if constexpr (std::is_same<T, zdouble>::value)
+                    k_upd_zmma<BIG_TM, BIG_TN, 32, 32><<<(unsigned) L.count, (BIG_TM / 32) * (BIG_TN / 32) * 32,
+                        zmma_smem_bytes<BIG_TM, BIG_TN> (), st>>>
+                        (tiles + L.first, items, relmap, Lx) ;
+                else
+                    k_upd_cfma<T, BIG_TM, BIG_TN><<<(unsigned) L.count, (BIG_TM / 4) * (BIG_TN / 4),
+                        cfma_smem_bytes<T, BIG_TM, BIG_TN> (), st>>>
+                        (tiles + L.first, items, relmap, Lx) ;
                 break ;
             case K_POTRF16:
                 k_potrf_reg<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
@@ -290,14 +353,18 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                 k_trsm<T><<<(unsigned) L.count, TRSM_ROWS, 0, st>>> (trsm + L.first, Lx) ;
                 break ;
             case K_TRSM_INV32:
-                if (sizeof (T) != 8) return B200_INVALID ;
-                k_trsm_inv<32><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<32> (), st>>>
-                    (trsm + L.first, reinterpret_cast<double *> (Lx), reinterpret_cast<const double *> (winv)) ;
+                if constexpr (std::is_same<T, double>::value)
+                    k_trsm_inv<32><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<32> (), st>>> (trsm + L.first, Lx, winv) ;
+                else if constexpr (std::is_same<T, zdouble>::value)
+                    k_trsm_zinv<32><<<(unsigned) L.count, 256, trsm_zinv_smem_bytes<32> (), st>>> (trsm + L.first, Lx, winv) ;
+                else return B200_INVALID ;
                 break ;
             case K_TRSM_INV64:
-                if (sizeof (T) != 8) return B200_INVALID ;
-                k_trsm_inv<64><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<64> (), st>>>
-                    (trsm + L.first, reinterpret_cast<double *> (Lx), reinterpret_cast<const double *> (winv)) ;
+                if constexpr (std::is_same<T, double>::value)
+                    k_trsm_inv<64><<<(unsigned) L.count, 256, trsm_inv_smem_bytes<64> (), st>>> (trsm + L.first, Lx, winv) ;
+                else if constexpr (std::is_same<T, zdouble>::value)
+                    k_trsm_zinv<64><<<(unsigned) L.count, 256, trsm_zinv_smem_bytes<64> (), st>>> (trsm + L.first, Lx, winv) ;
+                else return B200_INVALID ;
                 break ;
             default:
                 return B200_INVALID ;
@@ -340,7 +407,7 @@ int scatter_A (b200_factor *f, int64_t kfirst, int64_t klast, double beta)
     unsigned grid = (unsigned) ((klast - kfirst + 255) / 256) ;
     k_scatter_A<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
         f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_supermap.p,
-        f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (T) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
+        f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
     f->kernel_launches++ ;
     CK (cudaGetLastError (), "k_scatter_A") ;
     return B200_OK ;
@@ -363,7 +430,7 @@ int repair_not_posdef (b200_factor *f, int64_t minor, double beta, int quick)
     const int64_t nscol_new = info - 1 ;
     Plan R ;
     int st = build_repair_plan (P, f->h_super.data (), f->h_pi.data (), f->h_px.data (), s, nscol_new,
-        f->dtype == B200_DOUBLE, R) ;
+        dtype_dmma (f->dtype), R) ;
     if (st) return st ;
     DevBuf<UpdItem> items ; DevBuf<UpdTile> tiles ; DevBuf<PotrfBlk> potrf ; DevBuf<TrsmTile> trsm ;
     bool ok = items.upload (R.items, f->stream) == cudaSuccess && tiles.upload (R.tiles, f->stream) == cudaSuccess
@@ -503,13 +570,13 @@ b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, 
 {
     int dummy ; if (!status) status = &dummy ;
     *status = B200_OK ;
-    if (dtype != B200_DOUBLE && dtype != B200_SINGLE) { *status = B200_INVALID ; return nullptr ; }
+    if (!dtype_ok (dtype)) { *status = B200_INVALID ; return nullptr ; }
     b200_factor *f = new (std::nothrow) b200_factor ;
     if (!f) { *status = B200_OUT_OF_MEMORY ; return nullptr ; }
-    f->dtype = dtype ; f->esize = (dtype == B200_DOUBLE) ? 8 : 4 ; f->device = device ;
+    f->dtype = dtype ; f->esize = dtype_esize (dtype) ; f->device = device ;
     try
     {
-        *status = build_plan (n, nsuper, super, pi, px, s, dtype == B200_DOUBLE, f->plan, nranks, rank) ;
+        *status = build_plan (n, nsuper, super, pi, px, s, dtype_dmma (dtype), f->plan, nranks, rank) ;
         if (*status == B200_OK)
         {
             f->h_super.assign (super, super + nsuper + 1) ;
@@ -793,8 +860,7 @@ int b200_factor_device (b200_factor *f, double beta, int quick_return_if_not_pos
 {
     int st = set_device (f) ; if (st) return st ;
     if (!f->have_A) return B200_INVALID ;
-    return (f->dtype == B200_DOUBLE) ? factor_device_T<double> (f, beta, quick_return_if_not_posdef, minor)
-                                     : factor_device_T<float> (f, beta, quick_return_if_not_posdef, minor) ;
+    return B200_DISPATCH (f->dtype, factor_device_T) (f, beta, quick_return_if_not_posdef, minor, nullptr) ;
 }
 
 int b200_download_factor (b200_factor *f, void *Lx)
@@ -863,13 +929,61 @@ int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
 
 }   // extern "C"
 
+// complex: Ax holds (re,im) pairs when Az == NULL (CHOLMOD_COMPLEX), else Ax = real parts and Az =
+// imaginary parts (CHOLMOD_ZOMPLEX; interleaved here on the host, O(nnz(A))).  L is always (re,im) pairs,
+// as in the reference (a zomplex A gives a complex L, SNW:42-84).
+template <typename R>
+static int super_numeric_complex (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const R *Ax, const R *Az, double beta, int quick, R *Lx, int64_t *minor)
+{
+    if (!f) return B200_GPU_PROBLEM ;
+    if (f->dtype != ((sizeof (R) == 8) ? B200_COMPLEX_DOUBLE : B200_COMPLEX_SINGLE)) return B200_INVALID ;
+    const void *vals = Ax ;
+    if (Az)
+    {
+        if (!Ap) return B200_INVALID ;
+        const int64_t n = f->plan.n ;
+        int64_t nz = Ap [n] ;
+        if (Anz) for (int64_t k = 0 ; k < n ; k++) nz = (Ap [k] + Anz [k] > nz) ? Ap [k] + Anz [k] : nz ;
+        if (nz < 0 || (nz > 0 && !Ax)) return B200_INVALID ;
+        try { f->h_Ax.resize ((size_t) nz * 2 * sizeof (R)) ; }
+        catch (const std::bad_alloc &) { return B200_OUT_OF_MEMORY ; }
+        R *dst = reinterpret_cast<R *> (f->h_Ax.data ()) ;
+        for (int64_t p = 0 ; p < nz ; p++) { dst [2*p] = Ax [p] ; dst [2*p+1] = Az [p] ; }
+        vals = dst ;
+    }
+    int st = b200_upload_matrix (f, Ap, Ai, Anz, vals) ;
+    if (st < 0) return st ;
+    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
+    ensure_registered (f, Lx, (size_t) f->plan.xsize * 2 * sizeof (R)) ;
+    return factor_device_T<cx<R>> (f, beta, quick, minor, Lx) ;
+}
+
+extern "C" {
+
+int b200_super_numeric_z (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const double *Ax, const double *Az, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor)
+{
+    return super_numeric_complex<double> (f, Ap, Ai, Anz, Ax, Az, beta, quick_return_if_not_posdef, Lx, minor) ;
+}
+
+int b200_super_numeric_c (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const float *Ax, const float *Az, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor)
+{
+    return super_numeric_complex<float> (f, Ap, Ai, Anz, Ax, Az, beta, quick_return_if_not_posdef, Lx, minor) ;
+}
+
+}   // extern "C"
+
 template <typename T>
 static int solve_T (b200_factor *f, int nrhs)
 {
     const Plan &P = f->plan ;
     cudaStream_t s = f->stream ;
-    const int64_t cap = (200 * 1024) / 8 ;
+    typedef typename solve_x<T>::type XT ;
+    const int64_t cap = (200 * 1024) / (int64_t) sizeof (XT) ;
     const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
+    XT *X = reinterpret_cast<XT *> (f->d_X.p) ;
     if (!f->solve_ready)
     {
         // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_BIG columns
@@ -928,31 +1042,31 @@ static int solve_T (b200_factor *f, int nrhs)
             const unsigned grid = (unsigned) L.count ;
             if (L.kind == 0)
             {
-                const size_t sm = (size_t) std::min (L.maxcol, cap) * 8 ;
+                const size_t sm = (size_t) std::min (L.maxcol, cap) * sizeof (XT) ;
                 if (pass == 0)
                     k_solve_fwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+                        f->d_Ls.p, Lx, X, P.n, nrhs, cap) ;
                 else
                     k_solve_bwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs, cap) ;
+                        f->d_Ls.p, Lx, X, P.n, nrhs, cap) ;
             }
             else if (L.kind == 1)
             {
                 if (pass == 0)
-                    k_solve_diag<T, false><<<grid, 64, 0, s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        Lx, f->d_X.p, P.n, nrhs) ;
+                    k_solve_diag<T, false><<<grid, 64, solve_diag_smem_bytes<T> (), s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        Lx, X, P.n, nrhs) ;
                 else
-                    k_solve_diag<T, true><<<grid, 64, 0, s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        Lx, f->d_X.p, P.n, nrhs) ;
+                    k_solve_diag<T, true><<<grid, 64, solve_diag_smem_bytes<T> (), s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        Lx, X, P.n, nrhs) ;
             }
             else
             {
                 if (pass == 0)
                     k_solve_gemv<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs) ;
+                        f->d_Ls.p, Lx, X, P.n, nrhs) ;
                 else
                     k_solve_gemvt<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, f->d_X.p, P.n, nrhs) ;
+                        f->d_Ls.p, Lx, X, P.n, nrhs) ;
             }
         }
     }
@@ -962,24 +1076,35 @@ static int solve_T (b200_factor *f, int nrhs)
 
 extern "C" {
 
-int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs)
+static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs, bool want_complex)
 {
     int st = set_device (f) ; if (st) return st ;
+    if (dtype_complex (f->dtype) != want_complex) return B200_INVALID ;
     const int64_t n = f->plan.n ;
     if (nrhs < 0 || (!B && n * nrhs > 0) || (!X && n * nrhs > 0)) return B200_INVALID ;
     if (n == 0 || nrhs == 0) return B200_OK ;
-    size_t cnt = (size_t) n * (size_t) nrhs ;
+    size_t cnt = (size_t) n * (size_t) nrhs * (want_complex ? 2 : 1) ;      // doubles
     if (f->d_X.n < cnt && f->d_X.alloc (cnt) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     cudaStream_t s = f->stream ;
     CK (cudaMemcpyAsync (f->d_X.p, B, cnt * 8, cudaMemcpyHostToDevice, s), "H2D B") ;
     CK (cudaEventRecord (f->ev [0], s), "record") ;
-    st = (f->dtype == B200_DOUBLE) ? solve_T<double> (f, (int) nrhs) : solve_T<float> (f, (int) nrhs) ;
+    st = B200_DISPATCH (f->dtype, solve_T) (f, (int) nrhs) ;
     if (st) return st ;
     CK (cudaEventRecord (f->ev [1], s), "record") ;
     CK (cudaMemcpyAsync (X, f->d_X.p, cnt * 8, cudaMemcpyDeviceToHost, s), "D2H X") ;
     CK (cudaStreamSynchronize (s), "solve") ;
     cudaEventElapsedTime (&f->ms_solve, f->ev [0], f->ev [1]) ;
     return B200_OK ;
+}
+
+int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs)
+{
+    return solve_host (f, B, X, nrhs, false) ;
+}
+
+int b200_solve_z (b200_factor *f, const double *B, double *X, int64_t nrhs)
+{
+    return solve_host (f, B, X, nrhs, true) ;
 }
 
 }   // extern "C"

@@ -7,12 +7,14 @@
 //   cholmod_l_b200_probe            <->  cholmod_l_gpu_probe            (CHOLMOD/GPU/cholmod_gpu.c:148)
 //   cholmod_l_b200_symbolic         <->  gpu_init + cholmod_l_gpu_allocate (t_cholmod_gpu.c:84, cholmod_gpu.c:426)
 //   cholmod_l_b200_deallocate       <->  cholmod_l_gpu_deallocate       (cholmod_gpu.c:187)
-//   rd_/rs_cholmod_l_b200_super_numeric <-> the useGPU branch of rd_cholmod_super_numeric_worker
-//                                        (t_cholmod_super_numeric_worker.c:133-1279)
+//   rd_/rs_/cd_/cs_/zd_/zs_cholmod_l_b200_super_numeric <-> the useGPU branch of the six instances of
+//                                        TEMPLATE (cholmod_super_numeric_worker)
+//                                        (t_cholmod_super_numeric_worker.c:133-1279; the reference's GPU
+//                                        branch exists for rd_ and cd_ only)
 //   cholmod_l_super_numeric         the public entry (cholmod_super_numeric.c:100) re-implemented so that,
 //                                   when this library precedes libcholmod in symbol resolution (link
 //                                   order or LD_PRELOAD), an UNMODIFIED cholmod_l_factorize lands in the
-//                                   B200 numeric phase.  Inputs outside the module's scope (complex, the
+//                                   B200 numeric phase.  Inputs outside the module's scope (the
 //                                   unsymmetric A*F case, int32) are handed to the next definition of
 //                                   cholmod_l_super_numeric (the reference's), exactly as the reference's
 //                                   GPU branch only ever covered real/complex double int64.
@@ -118,10 +120,20 @@ static b200_factor *shim_context (cholmod_factor *L, int dtype, cholmod_common *
     return ctx ;
 }
 
+// B200 entry type of a factor: CHOLMOD's xtype + dtype for complex, dtype alone for real
+static int shim_dtype (int xtype, int dtype)
+{
+    if (xtype == CHOLMOD_COMPLEX || xtype == CHOLMOD_ZOMPLEX)
+        return (dtype == CHOLMOD_SINGLE) ? B200_COMPLEX_SINGLE : B200_COMPLEX_DOUBLE ;
+    return (dtype == CHOLMOD_SINGLE) ? B200_SINGLE : B200_DOUBLE ;
+}
+
 int cholmod_l_b200_symbolic (cholmod_factor *L, cholmod_common *Common)
 {
     if (!L || !Common || !L->is_super) return 0 ;
-    return shim_context (L, (L->dtype == CHOLMOD_SINGLE) ? B200_SINGLE : B200_DOUBLE, Common) != NULL ;
+    // a symbolic factor does not know yet whether it will hold real or complex values: real is assumed,
+    // the numeric phase builds the context of the other kind when it turns out to be needed
+    return shim_context (L, shim_dtype (L->xtype, L->dtype), Common) != NULL ;
 }
 
 int cholmod_l_b200_deallocate (cholmod_common *Common)
@@ -179,12 +191,22 @@ static int shim_worker (cholmod_sparse *A, double beta [2], cholmod_factor *L, c
     int64_t minor = (int64_t) L->n ;
     const int64_t *Anz = A->packed ? NULL : (const int64_t *) A->nz ;
     int st ;
+    // zomplex A: real parts in A->x, imaginary parts in A->z (L is complex either way)
+    const void *Az = (A->xtype == CHOLMOD_ZOMPLEX) ? A->z : NULL ;
     if (dtype == B200_DOUBLE)
         st = b200_super_numeric_d (ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
             (const double *) A->x, beta [0], Common->quick_return_if_not_posdef, (double *) L->x, &minor) ;
-    else
+    else if (dtype == B200_SINGLE)
         st = b200_super_numeric_s (ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
             (const float *) A->x, beta [0], Common->quick_return_if_not_posdef, (float *) L->x, &minor) ;
+    else if (dtype == B200_COMPLEX_DOUBLE)
+        st = b200_super_numeric_z (ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
+            (const double *) A->x, (const double *) Az, beta [0], Common->quick_return_if_not_posdef,
+            (double *) L->x, &minor) ;
+    else
+        st = b200_super_numeric_c (ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
+            (const float *) A->x, (const float *) Az, beta [0], Common->quick_return_if_not_posdef,
+            (float *) L->x, &minor) ;
     if (st < 0)
     {
         cholmod_l_error (st, __FILE__, __LINE__, "CHOLMOD/B200 numeric factorization failed", Common) ;
@@ -210,6 +232,35 @@ int rs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, doubl
     return shim_worker (A, beta, L, Common, B200_SINGLE) ;
 }
 
+// cd_/zd_ (complex double L; A complex or zomplex) and cs_/zs_ (complex single)
+int cd_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
+    cholmod_factor *L, cholmod_common *Common)
+{
+    (void) F ;
+    return shim_worker (A, beta, L, Common, B200_COMPLEX_DOUBLE) ;
+}
+
+int zd_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
+    cholmod_factor *L, cholmod_common *Common)
+{
+    (void) F ;
+    return shim_worker (A, beta, L, Common, B200_COMPLEX_DOUBLE) ;
+}
+
+int cs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
+    cholmod_factor *L, cholmod_common *Common)
+{
+    (void) F ;
+    return shim_worker (A, beta, L, Common, B200_COMPLEX_SINGLE) ;
+}
+
+int zs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
+    cholmod_factor *L, cholmod_common *Common)
+{
+    (void) F ;
+    return shim_worker (A, beta, L, Common, B200_COMPLEX_SINGLE) ;
+}
+
 // ---------------------------------------------------------------------------------------------
 // cholmod_l_super_numeric: the public seam (cholmod_super_numeric.c:100-335)
 // ---------------------------------------------------------------------------------------------
@@ -225,10 +276,12 @@ int cholmod_l_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [
     // libcholmod the environment variable is the switch.
     const char *env = getenv ("CHOLMOD_USE_GPU") ;
     int want = Common && (Common->useGPU == 1 || (env && atoi (env) == 1)) ;
-    // scope of the module: int64, real, symmetric with the lower triangle stored, double or single
-    int ours = want && A && L && L->is_super && A->stype < 0 && A->xtype == CHOLMOD_REAL
+    // scope of the module: int64, symmetric / Hermitian with the lower triangle stored, real, complex or
+    // zomplex, double or single (the type checks are the reference's, cholmod_super_numeric.c:166-180)
+    int cplx = A && (A->xtype == CHOLMOD_COMPLEX || A->xtype == CHOLMOD_ZOMPLEX) ;
+    int ours = want && A && L && L->is_super && A->stype < 0 && (A->xtype == CHOLMOD_REAL || cplx)
         && A->itype == CHOLMOD_LONG && L->itype == CHOLMOD_LONG
-        && (L->xtype == CHOLMOD_PATTERN || L->xtype == CHOLMOD_REAL)
+        && (L->xtype == CHOLMOD_PATTERN || L->xtype == (cplx ? CHOLMOD_COMPLEX : CHOLMOD_REAL))
         && A->nrow == A->ncol && A->nrow == L->n ;
     if (!ours)
     {
@@ -247,10 +300,18 @@ int cholmod_l_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [
     {
         // allocate L->x on the host, as cholmod_super_numeric.c:219-231 does
         L->dtype = A->dtype ;
-        cholmod_l_change_factor (CHOLMOD_REAL, 1, 1, 1, 1, L, Common) ;
+        cholmod_l_change_factor (cplx ? CHOLMOD_COMPLEX : CHOLMOD_REAL, 1, 1, 1, 1, L, Common) ;
         if (Common->status < CHOLMOD_OK) return 0 ;
     }
     L->is_ll = 1 ;
-    if (A->dtype == CHOLMOD_SINGLE) return rs_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+    switch ((A->xtype + A->dtype) % 8)      // the dispatch of cholmod_super_numeric.c:293-322
+    {
+        case CHOLMOD_REAL    + CHOLMOD_SINGLE: return rs_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+        case CHOLMOD_COMPLEX + CHOLMOD_SINGLE: return cs_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+        case CHOLMOD_ZOMPLEX + CHOLMOD_SINGLE: return zs_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+        case CHOLMOD_COMPLEX + CHOLMOD_DOUBLE: return cd_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+        case CHOLMOD_ZOMPLEX + CHOLMOD_DOUBLE: return zd_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
+        default: break ;
+    }
     return rd_cholmod_l_b200_super_numeric (A, F, beta, L, Common) ;
 }

@@ -21,6 +21,80 @@
 namespace b200 {
 
 // ---------------------------------------------------------------------------------------------
+// scalars: real (float, double) and complex (re,im interleaved, the layout of CHOLMOD_COMPLEX)
+// ---------------------------------------------------------------------------------------------
+
+// The kernels below are written once over T.  For a real T every helper is the identity / the plain
+// operator, so the real instantiations compile to what they were before the complex types existed; for
+// cx<R> they spell out the Hermitian case of the reference (zherk/zgemm "C", zpotrf, ztrsm "C":
+// SNW:786-803, :850-876, :1030-1048, :1184-1208): A = L*L^H, the diagonal of L real and positive.
+template <typename R> struct __align__ (2 * sizeof (R)) cx { R re, im ; } ;
+typedef cx<double> zdouble ;
+typedef cx<float> cfloat ;
+
+template <typename T> struct num { typedef T real ; static constexpr bool is_complex = false ; } ;
+template <typename R> struct num<cx<R>> { typedef R real ; static constexpr bool is_complex = true ; } ;
+
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator+ (cx<R> a, cx<R> b) { return { a.re + b.re, a.im + b.im } ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator- (cx<R> a, cx<R> b) { return { a.re - b.re, a.im - b.im } ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator- (cx<R> a) { return { -a.re, -a.im } ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator* (cx<R> a, cx<R> b)
+{
+    return { a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re } ;
+}
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator* (cx<R> a, R b) { return { a.re * b, a.im * b } ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> operator/ (cx<R> a, R b) { return { a.re / b, a.im / b } ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> &operator+= (cx<R> &a, cx<R> b) { a.re += b.re ; a.im += b.im ; return a ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> &operator-= (cx<R> &a, cx<R> b) { a.re -= b.re ; a.im -= b.im ; return a ; }
+
+__host__ __device__ __forceinline__ float conj_ (float a) { return a ; }
+__host__ __device__ __forceinline__ double conj_ (double a) { return a ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> conj_ (cx<R> a) { return { a.re, -a.im } ; }
+__host__ __device__ __forceinline__ float real_ (float a) { return a ; }
+__host__ __device__ __forceinline__ double real_ (double a) { return a ; }
+template <typename R> __host__ __device__ __forceinline__ R real_ (cx<R> a) { return a.re ; }
+
+// a * conj (b)
+__host__ __device__ __forceinline__ float mulc (float a, float b) { return a * b ; }
+__host__ __device__ __forceinline__ double mulc (double a, double b) { return a * b ; }
+template <typename R> __host__ __device__ __forceinline__ cx<R> mulc (cx<R> a, cx<R> b)
+{
+    return { a.re * b.re + a.im * b.im, a.im * b.re - a.re * b.im } ;
+}
+
+// the scalar r (a real number) as a T
+template <typename T> struct from_real_t { static __host__ __device__ __forceinline__ T make (T r) { return r ; } } ;
+template <typename R> struct from_real_t<cx<R>> { static __host__ __device__ __forceinline__ cx<R> make (R r) { return { r, (R) 0 } ; } } ;
+template <typename T> __host__ __device__ __forceinline__ T from_real (typename num<T>::real r) { return from_real_t<T>::make (r) ; }
+
+// conversion between precisions (the solve works in double whatever the factor's precision is)
+template <typename X, typename T> struct cvt_t { static __device__ __forceinline__ X make (T a) { return (X) a ; } } ;
+template <typename RX, typename R> struct cvt_t<cx<RX>, cx<R>> { static __device__ __forceinline__ cx<RX> make (cx<R> a) { return { (RX) a.re, (RX) a.im } ; } } ;
+template <typename X, typename T> __device__ __forceinline__ X cvt (T a) { return cvt_t<X, T>::make (a) ; }
+
+// *p -= v, atomically (per component for a complex entry: the components are independent sums)
+__device__ __forceinline__ void atomic_sub (float *p, float v) { atomicAdd (p, -v) ; }
+__device__ __forceinline__ void atomic_sub (double *p, double v) { atomicAdd (p, -v) ; }
+template <typename R> __device__ __forceinline__ void atomic_sub (cx<R> *p, cx<R> v)
+{
+    atomicAdd (&p->re, -v.re) ;
+    atomicAdd (&p->im, -v.im) ;
+}
+
+__device__ __forceinline__ float shfl_ (unsigned mask, float v, int src) { return __shfl_sync (mask, v, src) ; }
+__device__ __forceinline__ double shfl_ (unsigned mask, double v, int src) { return __shfl_sync (mask, v, src) ; }
+template <typename R> __device__ __forceinline__ cx<R> shfl_ (unsigned mask, cx<R> v, int src)
+{
+    return { __shfl_sync (mask, v.re, src), __shfl_sync (mask, v.im, src) } ;
+}
+__device__ __forceinline__ float shfl_xor_ (unsigned mask, float v, int o) { return __shfl_xor_sync (mask, v, o) ; }
+__device__ __forceinline__ double shfl_xor_ (unsigned mask, double v, int o) { return __shfl_xor_sync (mask, v, o) ; }
+template <typename R> __device__ __forceinline__ cx<R> shfl_xor_ (unsigned mask, cx<R> v, int o)
+{
+    return { __shfl_xor_sync (mask, v.re, o), __shfl_xor_sync (mask, v.im, o) } ;
+}
+
+// ---------------------------------------------------------------------------------------------
 // scatter A
 // ---------------------------------------------------------------------------------------------
 
@@ -34,7 +108,7 @@ __global__ void __launch_bounds__ (256) k_scatter_A (int64_t kfirst, int64_t kla
     const int64_t *__restrict__ Ap, const int64_t *__restrict__ Ai, const int64_t *__restrict__ Anz,
     const T *__restrict__ Ax, const int32_t *__restrict__ supermap, const int64_t *__restrict__ super,
     const int64_t *__restrict__ pi, const int64_t *__restrict__ px, const int32_t *__restrict__ Ls,
-    T beta, T *__restrict__ Lx)
+    typename num<T>::real beta, T *__restrict__ Lx)
 {
     int64_t k = kfirst + (int64_t) blockIdx.x * blockDim.x + threadIdx.x ;
     if (k >= klast) return ;
@@ -65,7 +139,8 @@ __global__ void __launch_bounds__ (256) k_scatter_A (int64_t kfirst, int64_t kla
         }
         col [pos] = Ax [p] ;
     }
-    if (beta != (T) 0) col [k - k1] += beta ;
+    // only the real part of beta exists (SNW:510-520)
+    if (beta != (typename num<T>::real) 0) col [k - k1] += from_real<T> (beta) ;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -87,18 +162,19 @@ __global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ 
     const bool rowok = i < it.M ;
     const T *A = Lx + it.a_off ;
     const int64_t lda = it.lda ;
+    const T zero = from_real<T> (0) ;
     T acc [SIMT_TN] ;
     #pragma unroll
-    for (int jj = 0 ; jj < SIMT_TN ; jj++) acc [jj] = 0 ;
+    for (int jj = 0 ; jj < SIMT_TN ; jj++) acc [jj] = zero ;
     for (int k = t.k0 ; k < t.k1 ; k++)
     {
         const T *Ak = A + (int64_t) k * lda ;
-        T a = rowok ? Ak [i] : (T) 0 ;
+        T a = rowok ? Ak [i] : zero ;
         #pragma unroll
         for (int jj = 0 ; jj < SIMT_TN ; jj++)
         {
-            T b = (jj < nj) ? Ak [j0 + jj] : (T) 0 ;
-            acc [jj] += a * b ;
+            T b = (jj < nj) ? Ak [j0 + jj] : zero ;
+            acc [jj] += mulc (a, b) ;
         }
     }
     if (!rowok) return ;
@@ -113,7 +189,7 @@ __global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ 
         if (jj < nj && i >= j)
         {
             int64_t cj = mapped ? (int64_t) map [j] : (int64_t) j ;
-            atomicAdd (C + cj * it.ldc, -acc [jj]) ;
+            atomic_sub (C + cj * it.ldc, acc [jj]) ;
         }
     }
 }
@@ -295,6 +371,296 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
 }
 
 // ---------------------------------------------------------------------------------------------
+// complex double: the same tiles, four real DMMAs per complex product
+// ---------------------------------------------------------------------------------------------
+
+// C = A * B^H on (re,im)-interleaved operands (zherk / zgemm "N","C" of SNW:786-803, :850-876):
+//     Cre += Are Bre' + Aim Bim'          Cim += Aim Bre' - Are Bim'
+// One m8n8k4 fragment element is a 16-byte (re,im) pair fetched with one LDS.128; the shared tiles are
+// [k][m] with the row pitch padded to TM+2 pairs, so the 8 lanes of a quarter-warp (k = lane%4, m = lane/4)
+// hit 8 distinct 16-byte bank groups.  Twice the bytes but four times the flops of the real kernel per
+// element staged, so a stage is 8 columns deep instead of 16.
+constexpr int ZM_KC = 8 ;
+
+template <int TM, int TN> constexpr size_t zmma_smem_bytes ()
+{
+    return (size_t) DM_STAGES * ZM_KC * ((TM + 2) + (TN + 2)) * sizeof (double2) + (TM + TN) * sizeof (int32_t) ;
+}
+
+__device__ __forceinline__ double neg_ (double x)
+{
+    // sign flip on the integer pipe: the FP64 pipe is the one this kernel saturates
+    return __hiloint2double (__double2hiint (x) ^ (int) 0x80000000, __double2loint (x)) ;
+}
+
+// acc (re,im) [MT][NTL][2] += A-fragments * B-fragments^H over one shared-memory stage of KC columns
+template <int MT, int NTL, int KC, int LDA_S, int LDB_S>
+__device__ __forceinline__ void zmma_stage (const double2 *cA, const double2 *cB, int fk,
+    double (&cre) [MT][NTL][2], double (&cim) [MT][NTL][2])
+{
+    #pragma unroll
+    for (int kk = 0 ; kk < KC ; kk += 4)
+    {
+        double2 fa [MT], fb [NTL] ;
+        double nre [MT] ;
+        #pragma unroll
+        for (int a = 0 ; a < MT ; a++) { fa [a] = cA [(kk + fk) * LDA_S + a * 8] ; nre [a] = neg_ (fa [a].x) ; }
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) fb [b] = cB [(kk + fk) * LDB_S + b * 8] ;
+        #pragma unroll
+        for (int a = 0 ; a < MT ; a++)
+            #pragma unroll
+            for (int b = 0 ; b < NTL ; b++)
+            {
+                dmma884 (cre [a][b][0], cre [a][b][1], fa [a].x, fb [b].x) ;
+                dmma884 (cre [a][b][0], cre [a][b][1], fa [a].y, fb [b].y) ;
+                dmma884 (cim [a][b][0], cim [a][b][1], fa [a].y, fb [b].x) ;
+                dmma884 (cim [a][b][0], cim [a][b][1], nre [a], fb [b].y) ;
+            }
+    }
+}
+
+template <int TM, int TN, int WM, int WN>
+__global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_zmma (const UpdTile *__restrict__ tiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, zdouble *Lx)
+{
+    constexpr int NW_M = TM / WM, NW_N = TN / WN ;
+    constexpr int NT = NW_M * NW_N * 32 ;
+    constexpr int LDA_S = TM + 2, LDB_S = TN + 2 ;
+    constexpr int MT = WM / 8, NTL = WN / 8 ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    double2 *sA = reinterpret_cast<double2 *> (smem_raw) ;              // [STAGES][KC][LDA_S]
+    double2 *sB = sA + DM_STAGES * ZM_KC * LDA_S ;                      // [STAGES][KC][LDB_S]
+    int32_t *smap_r = reinterpret_cast<int32_t *> (sB + DM_STAGES * ZM_KC * LDB_S) ;
+    int32_t *smap_c = smap_r + TM ;
+
+    const UpdTile t = tiles [blockIdx.x] ;
+    const UpdItem it = items [t.item] ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
+    const int wm = warp % NW_M, wn = warp / NW_M ;
+    const int i0 = (int) t.ti * TM, j0 = (int) t.tj * TN ;
+    const int mA = min (TM, it.M - i0), nB = min (TN, it.N - j0) ;
+    const int64_t lda = it.lda ;
+    const zdouble *A = Lx + it.a_off ;
+    const int kbeg = t.k0, kend = t.k1 ;
+    const int nk = (kend - kbeg + ZM_KC - 1) / ZM_KC ;
+    {
+        const bool mapped = it.map_off >= 0 ;
+        const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+        for (int m = tid ; m < TM ; m += NT) smap_r [m] = (m < mA) ? (mapped ? map [i0 + m] : i0 + m) : 0 ;
+        for (int m = tid ; m < TN ; m += NT) smap_c [m] = (m < nB) ? (mapped ? map [j0 + m] : j0 + m) : 0 ;
+    }
+    static_assert (NT % TM == 0 && NT % TN == 0, "thread count must be a multiple of the tile edges") ;
+    constexpr int KPP_A = NT / TM, KPP_B = NT / TN ;
+    static_assert (ZM_KC % KPP_A == 0 && ZM_KC % KPP_B == 0, "a stage must be a whole number of passes") ;
+    const int lmA = tid % TM, lkA = tid / TM, lmB = tid % TN, lkB = tid / TN ;
+    const bool rokA = lmA < mA, rokB = lmB < nB ;
+    const zdouble *gA = A + i0 + lmA + (int64_t) (kbeg + lkA) * lda ;
+    const zdouble *gB = A + j0 + lmB + (int64_t) (kbeg + lkB) * lda ;
+    const int64_t stepA = (int64_t) KPP_A * lda, stepB = (int64_t) KPP_B * lda ;
+    const unsigned sA0 = (unsigned) __cvta_generic_to_shared (sA) + (unsigned) ((lkA * LDA_S + lmA) * 16) ;
+    const unsigned sB0 = (unsigned) __cvta_generic_to_shared (sB) + (unsigned) ((lkB * LDB_S + lmB) * 16) ;
+    int kleft = kend - kbeg ;
+    auto load_stage = [&] (int buf)
+    {
+        const unsigned dA = sA0 + (unsigned) (buf * ZM_KC * LDA_S * 16) ;
+        const unsigned dB = sB0 + (unsigned) (buf * ZM_KC * LDB_S * 16) ;
+        const zdouble *pa = gA, *pb = gB ;
+        #pragma unroll
+        for (int i = 0 ; i < ZM_KC / KPP_A ; i++)
+        {
+            int sz = (rokA && (lkA + i * KPP_A < kleft)) ? 16 : 0 ;
+            asm volatile ("cp.async.cg.shared.global [%0], [%1], 16, %2;\n"
+                :: "r" (dA + (unsigned) (i * KPP_A * LDA_S * 16)), "l" (pa), "r" (sz)) ;
+            pa += stepA ;
+        }
+        #pragma unroll
+        for (int i = 0 ; i < ZM_KC / KPP_B ; i++)
+        {
+            int sz = (rokB && (lkB + i * KPP_B < kleft)) ? 16 : 0 ;
+            asm volatile ("cp.async.cg.shared.global [%0], [%1], 16, %2;\n"
+                :: "r" (dB + (unsigned) (i * KPP_B * LDB_S * 16)), "l" (pb), "r" (sz)) ;
+            pb += stepB ;
+        }
+        gA = pa ; gB = pb ; kleft -= ZM_KC ;
+    } ;
+
+    double cre [MT][NTL][2], cim [MT][NTL][2] ;
+    #pragma unroll
+    for (int a = 0 ; a < MT ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) { cre [a][b][0] = 0.0 ; cre [a][b][1] = 0.0 ; cim [a][b][0] = 0.0 ; cim [a][b][1] = 0.0 ; }
+    const bool warp_live = (i0 + wm * WM + WM - 1) >= (j0 + wn * WN) ;
+
+    #pragma unroll
+    for (int s = 0 ; s < DM_STAGES - 1 ; s++)
+    {
+        if (s < nk) load_stage (s) ;
+        cp_async_commit () ;
+    }
+    const int fk = lane & 3, fm = lane >> 2 ;
+    int cbuf = 0, lbuf = DM_STAGES - 1 ;
+    for (int kt = 0 ; kt < nk ; kt++)
+    {
+        cp_async_wait<DM_STAGES - 2> () ;
+        __syncthreads () ;
+        if (kt + DM_STAGES - 1 < nk) load_stage (lbuf) ;
+        cp_async_commit () ;
+        lbuf = (lbuf + 1 == DM_STAGES) ? 0 : lbuf + 1 ;
+        const int cur = cbuf ;
+        cbuf = (cbuf + 1 == DM_STAGES) ? 0 : cbuf + 1 ;
+        if (warp_live)
+            zmma_stage<MT, NTL, ZM_KC, LDA_S, LDB_S> (sA + cur * ZM_KC * LDA_S + wm * WM + fm,
+                sB + cur * ZM_KC * LDB_S + wn * WN + fm, fk, cre, cim) ;
+    }
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    if (!warp_live) return ;
+
+    zdouble *C = Lx + it.c_off ;
+    const int64_t ldc = it.ldc ;
+    #pragma unroll
+    for (int b = 0 ; b < NTL ; b++)
+    {
+        #pragma unroll
+        for (int e = 0 ; e < 2 ; e++)
+        {
+            const int jl = wn * WN + b * 8 + 2 * fk + e ;
+            if (jl >= nB) continue ;
+            const int j = j0 + jl ;
+            zdouble *Cj = C + (int64_t) smap_c [jl] * ldc ;
+            #pragma unroll
+            for (int a = 0 ; a < MT ; a++)
+            {
+                const int il = wm * WM + a * 8 + fm ;
+                if (il < mA && i0 + il >= j)
+                {
+                    zdouble *dst = Cj + smap_r [il] ;
+                    atomicAdd (&dst->re, -cre [a][b][e]) ;
+                    // the diagonal of L1*L1^H is real (zherk leaves its imaginary part exactly zero)
+                    if (i0 + il > j) atomicAdd (&dst->im, -cim [a][b][e]) ;
+                }
+            }
+        }
+    }
+}
+
+// complex single (and any T without a tensor path): register-blocked tiles on the FMA pipe, a 4 x 4
+// micro-tile per thread, the same 3-stage cp.async ring and relative-map epilogue
+template <typename T, int TM, int TN> constexpr size_t cfma_smem_bytes ()
+{
+    return (size_t) DM_STAGES * DM_KC * (TM + TN) * sizeof (T) + (TM + TN) * sizeof (int32_t) ;
+}
+
+template <typename T, int TM, int TN>
+__global__ void __launch_bounds__ ((TM / 4) * (TN / 4)) k_upd_cfma (const UpdTile *__restrict__ tiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, T *Lx)
+{
+    constexpr int NTX = TM / 4, NTY = TN / 4, NT = NTX * NTY ;
+    constexpr int ES = (int) sizeof (T) ;
+    static_assert (ES == 4 || ES == 8 || ES == 16, "cp.async moves 4, 8 or 16 bytes") ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    T *sA = reinterpret_cast<T *> (smem_raw) ;                          // [STAGES][KC][TM]
+    T *sB = sA + DM_STAGES * DM_KC * TM ;                               // [STAGES][KC][TN]
+    int32_t *smap_r = reinterpret_cast<int32_t *> (sB + DM_STAGES * DM_KC * TN) ;
+    int32_t *smap_c = smap_r + TM ;
+    const UpdTile t = tiles [blockIdx.x] ;
+    const UpdItem it = items [t.item] ;
+    const int tid = threadIdx.x, tx = tid % NTX, ty = tid / NTX ;
+    const int i0 = (int) t.ti * TM, j0 = (int) t.tj * TN ;
+    const int mA = min (TM, it.M - i0), nB = min (TN, it.N - j0) ;
+    const int64_t lda = it.lda ;
+    const T *A = Lx + it.a_off ;
+    const int kbeg = t.k0, kend = t.k1 ;
+    const int nk = (kend - kbeg + DM_KC - 1) / DM_KC ;
+    {
+        const bool mapped = it.map_off >= 0 ;
+        const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+        for (int m = tid ; m < TM ; m += NT) smap_r [m] = (m < mA) ? (mapped ? map [i0 + m] : i0 + m) : 0 ;
+        for (int m = tid ; m < TN ; m += NT) smap_c [m] = (m < nB) ? (mapped ? map [j0 + m] : j0 + m) : 0 ;
+    }
+    auto load_stage = [&] (int kt, int buf)
+    {
+        const int kb = kbeg + kt * DM_KC ;
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TM ; e += NT)
+        {
+            const int m = e % TM, k = e / TM ;
+            const int sz = (m < mA && kb + k < kend) ? ES : 0 ;
+            const unsigned d = (unsigned) __cvta_generic_to_shared (sA + (buf * DM_KC + k) * TM + m) ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], %2, %3;\n"
+                :: "r" (d), "l" (A + i0 + m + (int64_t) (kb + k) * lda), "n" (ES), "r" (sz)) ;
+        }
+        #pragma unroll
+        for (int e = tid ; e < DM_KC * TN ; e += NT)
+        {
+            const int m = e % TN, k = e / TN ;
+            const int sz = (m < nB && kb + k < kend) ? ES : 0 ;
+            const unsigned d = (unsigned) __cvta_generic_to_shared (sB + (buf * DM_KC + k) * TN + m) ;
+            asm volatile ("cp.async.ca.shared.global [%0], [%1], %2, %3;\n"
+                :: "r" (d), "l" (A + j0 + m + (int64_t) (kb + k) * lda), "n" (ES), "r" (sz)) ;
+        }
+    } ;
+    const T zero = from_real<T> (0) ;
+    T acc [4][4] ;
+    #pragma unroll
+    for (int a = 0 ; a < 4 ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < 4 ; b++) acc [a][b] = zero ;
+    const bool live = (i0 + tx * 4 + 3) >= (j0 + ty * 4) ;
+    #pragma unroll
+    for (int s = 0 ; s < DM_STAGES - 1 ; s++)
+    {
+        if (s < nk) load_stage (s, s) ;
+        cp_async_commit () ;
+    }
+    for (int kt = 0 ; kt < nk ; kt++)
+    {
+        cp_async_wait<DM_STAGES - 2> () ;
+        __syncthreads () ;
+        if (kt + DM_STAGES - 1 < nk) load_stage (kt + DM_STAGES - 1, (kt + DM_STAGES - 1) % DM_STAGES) ;
+        cp_async_commit () ;
+        if (live)
+        {
+            const T *cA = sA + (kt % DM_STAGES) * DM_KC * TM + tx * 4 ;
+            const T *cB = sB + (kt % DM_STAGES) * DM_KC * TN + ty * 4 ;
+            #pragma unroll
+            for (int k = 0 ; k < DM_KC ; k++)
+            {
+                T fa [4], fb [4] ;
+                #pragma unroll
+                for (int a = 0 ; a < 4 ; a++) fa [a] = cA [k * TM + a] ;
+                #pragma unroll
+                for (int b = 0 ; b < 4 ; b++) fb [b] = cB [k * TN + b] ;
+                #pragma unroll
+                for (int a = 0 ; a < 4 ; a++)
+                    #pragma unroll
+                    for (int b = 0 ; b < 4 ; b++) acc [a][b] += mulc (fa [a], fb [b]) ;
+            }
+        }
+    }
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    if (!live) return ;
+    T *C = Lx + it.c_off ;
+    const int64_t ldc = it.ldc ;
+    #pragma unroll
+    for (int b = 0 ; b < 4 ; b++)
+    {
+        const int jl = ty * 4 + b ;
+        if (jl >= nB) continue ;
+        const int j = j0 + jl ;
+        T *Cj = C + (int64_t) smap_c [jl] * ldc ;
+        #pragma unroll
+        for (int a = 0 ; a < 4 ; a++)
+        {
+            const int il = tx * 4 + a ;
+            if (il < mA && i0 + il >= j) atomic_sub (Cj + smap_r [il], acc [a][b]) ;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // single precision: the same tiles on the FP32 FMA pipe
 // ---------------------------------------------------------------------------------------------
 
@@ -461,23 +827,25 @@ __global__ void __launch_bounds__ (64) k_potrf_reg (const PotrfBlk *__restrict__
     const int jb = b.jb ;
     const int64_t lda = b.lda ;
     T *D = Lx + b.off ;
+    typedef typename num<T>::real R ;
+    const T one = from_real<T> (1), zero = from_real<T> (0) ;
     T a [NB] ;
     #pragma unroll
     for (int c = 0 ; c < NB ; c++)
-        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
+        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? one : zero) ;
     #pragma unroll
     for (int j = 0 ; j < NB ; j++)
     {
         T *cb = colbuf [j & 1] + g * NB ;
         if (r >= j) cb [r] = a [j] ;
         __syncthreads () ;
-        const T d = cb [j] ;
-        if (r == j && j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-        const T t = a [j] * ((T) 1 / d) ;
+        const R d = real_ (cb [j]) ;            // the pivot: only its real part exists (zpotrf)
+        if (r == j && j < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        const T t = a [j] * ((R) 1 / d) ;
         #pragma unroll
-        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= t * cb [c] ;
-        const T ljj = sqrt (d) ;
-        if (r == j) a [j] = ljj ;
+        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= mulc (t, cb [c]) ;
+        const R ljj = sqrt (d) ;
+        if (r == j) a [j] = from_real<T> (ljj) ;
         else if (r > j) a [j] = a [j] / ljj ;
     }
     #pragma unroll
@@ -503,30 +871,32 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
     const int jb = b.jb ;
     const int64_t lda = b.lda ;
     T *D = Lx + b.off ;
+    typedef typename num<T>::real R ;
+    const T one = from_real<T> (1), zero = from_real<T> (0) ;
     T a [NB] ;
     #pragma unroll
     for (int c = 0 ; c < NB ; c++)
-        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
+        a [c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? one : zero) ;
     #pragma unroll
     for (int j = 0 ; j < NB ; j++)
     {
         T *cb = colbuf [j & 1] + g * NB ;
         if (r >= j) cb [r] = a [j] ;
         __syncthreads () ;
-        const T d = cb [j] ;
-        if (r == j && j < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-        const T t = a [j] * ((T) 1 / d) ;
+        const R d = real_ (cb [j]) ;            // the pivot: only its real part exists (zpotrf)
+        if (r == j && j < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        const T t = a [j] * ((R) 1 / d) ;
         #pragma unroll
-        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= t * cb [c] ;
-        const T ljj = sqrt (d) ;
-        if (r == j) a [j] = ljj ;
+        for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= mulc (t, cb [c]) ;
+        const R ljj = sqrt (d) ;
+        if (r == j) a [j] = from_real<T> (ljj) ;
         else if (r > j) a [j] = a [j] / ljj ;
     }
     #pragma unroll
     for (int c = 0 ; c < NB ; c++)
     {
         if (r < jb && c <= r) D [r + c * lda] = a [c] ;
-        sL [g][r][c] = (c <= r) ? a [c] : (T) 0 ;       // identity padded: rows / columns >= jb are e_r
+        sL [g][r][c] = (c <= r) ? a [c] : zero ;        // identity padded: rows / columns >= jb are e_r
     }
     __syncthreads () ;
     // rows below the diagonal block: x <- x * L11^{-T}, one row per thread
@@ -539,14 +909,14 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
             T *X = D + jb + row ;
             T x [NB] ;
             #pragma unroll
-            for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : (T) 0 ;
+            for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : zero ;
             #pragma unroll
             for (int j = 0 ; j < NB ; j++)
             {
-                const T xj = x [j] / sL [g][j][j] ;
+                const T xj = x [j] / real_ (sL [g][j][j]) ;
                 x [j] = xj ;
                 #pragma unroll
-                for (int k = j + 1 ; k < NB ; k++) x [k] -= xj * sL [g][k][j] ;
+                for (int k = j + 1 ; k < NB ; k++) x [k] -= mulc (xj, sL [g][k][j]) ;
             }
             #pragma unroll
             for (int j = 0 ; j < NB ; j++) if (j < jb) X [j * lda] = x [j] ;
@@ -586,6 +956,8 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     const int64_t lda = b.lda ;
     T *D = Lx + b.off ;
     const int ti = threadIdx.x & 15, tj = threadIdx.x >> 4 ;
+    typedef typename num<T>::real R ;
+    const T one = from_real<T> (1), zero = from_real<T> (0) ;
     T a [4][4] ;
     #pragma unroll
     for (int jc = 0 ; jc < 4 ; jc++)
@@ -593,7 +965,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
         for (int i = 0 ; i < 4 ; i++)
         {
             const int r = 4 * ti + i, c = 4 * tj + jc ;
-            a [i][jc] = (r < jb && c < jb && r >= c) ? D [r + c * lda] : ((r == c) ? (T) 1 : (T) 0) ;
+            a [i][jc] = (r < jb && c < jb && r >= c) ? D [r + c * lda] : ((r == c) ? one : zero) ;
         }
     const int njt = (jb + 3) >> 2 ;
     // One barrier per PANEL of 4 columns: the 16 owners of tile column jt (one half-warp: threadIdx =
@@ -611,12 +983,12 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             #pragma unroll
             for (int jj = 0 ; jj < 4 ; jj++)
             {
-                const T d = __shfl_sync (mask, a [jj][jj], src) ;
-                const T rd = (T) 1 / d ;
+                const R d = __shfl_sync (mask, real_ (a [jj][jj]), src) ;
+                const R rd = (R) 1 / d ;
                 #pragma unroll
                 for (int cc = jj + 1 ; cc < 4 ; cc++)
                 {
-                    const T f = __shfl_sync (mask, a [cc][jj], src) * rd ;     // A (4jt+cc, j) / d_j
+                    const T f = conj_ (shfl_ (mask, a [cc][jj], src)) * rd ;   // conj (A (4jt+cc, j)) / d_j
                     #pragma unroll
                     for (int i = 0 ; i < 4 ; i++) a [i][cc] -= a [i][jj] * f ;
                 }
@@ -630,17 +1002,17 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             }
         }
         __syncthreads () ;
-        T rd [4] ;
+        R rd [4] ;
         #pragma unroll
-        for (int q = 0 ; q < 4 ; q++) rd [q] = (T) 1 / cb [4 * POTRF_NB + q] ;
+        for (int q = 0 ; q < 4 ; q++) rd [q] = (R) 1 / real_ (cb [4 * POTRF_NB + q]) ;
         if (threadIdx.x == 0)
         {
             #pragma unroll
             for (int q = 0 ; q < 4 ; q++)
             {
-                const T d = cb [4 * POTRF_NB + q] ;
-                dvec [4 * jt + q] = d ;
-                if (4 * jt + q < jb && !(d > (T) 0)) atomicMin (minor, (unsigned long long) (b.col + 4 * jt + q)) ;
+                const R d = real_ (cb [4 * POTRF_NB + q]) ;
+                dvec [4 * jt + q] = from_real<T> (d) ;
+                if (4 * jt + q < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + 4 * jt + q)) ;
             }
         }
         if (ti >= tj && tj > jt)
@@ -653,7 +1025,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
                 for (int i = 0 ; i < 4 ; i++)
                 {
                     ar [i] = cb [q * POTRF_NB + 4 * ti + i] ;
-                    ac [i] = cb [q * POTRF_NB + 4 * tj + i] * rd [q] ;
+                    ac [i] = conj_ (cb [q * POTRF_NB + 4 * tj + i]) * rd [q] ;
                 }
                 #pragma unroll
                 for (int jc = 0 ; jc < 4 ; jc++)
@@ -665,16 +1037,16 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     __syncthreads () ;
     if (threadIdx.x < POTRF_NB)
     {
-        const T q = (threadIdx.x < 4 * njt) ? sqrt (dvec [threadIdx.x]) : (T) 1 ;
-        sqv [threadIdx.x] = q ;
-        rsq [threadIdx.x] = (T) 1 / q ;
+        const R q = (threadIdx.x < 4 * njt) ? sqrt (real_ (dvec [threadIdx.x])) : (R) 1 ;
+        sqv [threadIdx.x] = from_real<T> (q) ;
+        rsq [threadIdx.x] = from_real<T> ((R) 1 / q) ;
     }
     __syncthreads () ;
     #pragma unroll
     for (int jc = 0 ; jc < 4 ; jc++)
     {
         const int c = 4 * tj + jc ;
-        const T ljj = sqv [c] ;
+        const R ljj = real_ (sqv [c]) ;
         #pragma unroll
         for (int i = 0 ; i < 4 ; i++)
         {
@@ -682,11 +1054,11 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             if (r < c) continue ;
             if (r < jb && c < jb)
             {
-                const T v = (r == c) ? ljj : a [i][jc] / ljj ;
+                const T v = (r == c) ? from_real<T> (ljj) : a [i][jc] / ljj ;
                 s [c * PB_LD + r] = v ;
                 D [r + c * lda] = v ;
             }
-            else s [c * PB_LD + r] = (r == c) ? (T) 1 : (T) 0 ;     // identity padding up to 64 x 64
+            else s [c * PB_LD + r] = (r == c) ? one : zero ;        // identity padding up to 64 x 64
         }
     }
     if (b.slot < 0) return ;
@@ -702,11 +1074,11 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
         for (int rl = 0 ; rl < 16 ; rl++)
         {
             const int rr = b0 + rl ;
-            T acc = 0 ;
+            T acc = zero ;
             for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
-            acc += __shfl_xor_sync (0xffffffffu, acc, 1) ;
-            acc += __shfl_xor_sync (0xffffffffu, acc, 2) ;
-            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? (T) 1 : (T) 0) - acc) * rsq [rr] ;
+            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? one : zero) - acc) * real_ (rsq [rr]) ;
             __syncwarp () ;
         }
     }
@@ -724,7 +1096,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             const int i = el % nb, j = el / nb ;
             if (j >= nb) continue ;
             const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = 0 ;
+            T acc = zero ;
             for (int k = j ; k < nb ; k++) acc += s [(c0 + k) * PB_LD + r0 + i] * w [(c0 + k) * PB_LD + c0 + j] ;
             tmp [(half * 16 + i) * 33 + j] = acc ;
         }
@@ -736,7 +1108,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             const int i = el % nb, j = el / nb ;
             if (j >= nb) continue ;
             const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = 0 ;
+            T acc = zero ;
             for (int k = 0 ; k <= i ; k++) acc += w [(r0 + i) * PB_LD + r0 + k] * tmp [(half * 16 + k) * 33 + j] ;
             w [(r0 + i) * PB_LD + c0 + j] = -acc ;
         }
@@ -747,8 +1119,8 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     {
         const int r = e % nbk, c = e / nbk ;
         T v ;
-        if (r < jb && c < jb) v = (r >= c) ? w [r * PB_LD + c] : (T) 0 ;
-        else v = (r == c) ? (T) 1 : (T) 0 ;
+        if (r < jb && c < jb) v = (r >= c) ? w [r * PB_LD + c] : zero ;
+        else v = (r == c) ? one : zero ;
         W [r + c * WINV_LD] = v ;
     }
 }
@@ -835,6 +1207,71 @@ __global__ void __launch_bounds__ (256) k_trsm_inv (const TrsmTile *__restrict__
         }
 }
 
+// complex double:  X <- X * W^H  (ztrsm "R","L","C","N" of SNW:1198 through the inverse), the same
+// A * B^H product as k_upd_zmma with A = the X tile and B = W
+template <int NBK> constexpr size_t trsm_zinv_smem_bytes ()
+{
+    return (size_t) NBK * ((TRSM_ROWS + 2) + (NBK + 2)) * sizeof (double2) ;
+}
+
+template <int NBK>
+__global__ void __launch_bounds__ (256) k_trsm_zinv (const TrsmTile *__restrict__ tiles, zdouble *Lx,
+    const zdouble *__restrict__ winv)
+{
+    constexpr int LDX = TRSM_ROWS + 2, LDW = NBK + 2 ;
+    constexpr int WN = NBK / 2, MT = 4, NTL = WN / 8 ;
+    extern __shared__ __align__ (16) unsigned char smem_raw [] ;
+    double2 *sX = reinterpret_cast<double2 *> (smem_raw) ;      // [NBK][LDX]
+    double2 *sW = sX + NBK * LDX ;                              // [NBK][LDW]
+    const TrsmTile t = tiles [blockIdx.x] ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
+    const int wm = warp & 3, wn = warp >> 2 ;
+    const int jb = t.jb, nrows = t.nrows ;
+    const int64_t lda = t.lda ;
+    zdouble *X = Lx + t.row_off ;
+    const zdouble *W = winv + (int64_t) t.slot * (WINV_LD * WINV_LD) ;
+    #pragma unroll
+    for (int e = tid ; e < NBK * TRSM_ROWS ; e += 256)
+    {
+        int m = e % TRSM_ROWS, k = e / TRSM_ROWS ;
+        bool ok = (m < nrows) && (k < jb) ;
+        const void *src = ok ? (const void *) (X + m + (int64_t) k * lda) : (const void *) W ;
+        unsigned d = (unsigned) __cvta_generic_to_shared (sX + k * LDX + m) ;
+        asm volatile ("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r" (d), "l" (src), "r" (ok ? 16 : 0)) ;
+    }
+    #pragma unroll
+    for (int e = tid ; e < NBK * NBK ; e += 256)
+    {
+        int n = e % NBK, k = e / NBK ;
+        unsigned d = (unsigned) __cvta_generic_to_shared (sW + k * LDW + n) ;
+        asm volatile ("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r" (d), "l" (W + n + k * WINV_LD), "r" (16)) ;
+    }
+    cp_async_commit () ;
+    cp_async_wait<0> () ;
+    __syncthreads () ;
+    double cre [MT][NTL][2], cim [MT][NTL][2] ;
+    #pragma unroll
+    for (int a = 0 ; a < MT ; a++)
+        #pragma unroll
+        for (int b = 0 ; b < NTL ; b++) { cre [a][b][0] = 0.0 ; cre [a][b][1] = 0.0 ; cim [a][b][0] = 0.0 ; cim [a][b][1] = 0.0 ; }
+    const int fk = lane & 3, fm = lane >> 2 ;
+    zmma_stage<MT, NTL, NBK, LDX, LDW> (sX + wm * 32 + fm, sW + wn * WN + fm, fk, cre, cim) ;
+    #pragma unroll
+    for (int b = 0 ; b < NTL ; b++)
+        #pragma unroll
+        for (int e = 0 ; e < 2 ; e++)
+        {
+            const int jl = wn * WN + b * 8 + 2 * fk + e ;
+            if (jl >= jb) continue ;
+            #pragma unroll
+            for (int a = 0 ; a < MT ; a++)
+            {
+                const int il = wm * 32 + a * 8 + fm ;
+                if (il < nrows) X [il + (int64_t) jl * lda] = { cre [a][b][e], cim [a][b][e] } ;
+            }
+        }
+}
+
 // ---------------------------------------------------------------------------------------------
 // triangular solve of the rows below a factorized diagonal block: one thread per row
 // ---------------------------------------------------------------------------------------------
@@ -844,15 +1281,15 @@ __device__ __forceinline__ void trsm_row (const T *sL, T *X, int64_t lda, int jb
 {
     T x [NB] ;
     #pragma unroll
-    for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : (T) 0 ;
+    for (int j = 0 ; j < NB ; j++) x [j] = (j < jb) ? X [j * lda] : from_real<T> (0) ;
     #pragma unroll
     for (int j = 0 ; j < NB ; j++)
     {
         // columns >= jb of sL hold the identity, so the padded part is a no-op
-        T xj = x [j] / sL [j * PB_LD + j] ;
+        T xj = x [j] / real_ (sL [j * PB_LD + j]) ;
         x [j] = xj ;
         #pragma unroll
-        for (int k = j + 1 ; k < NB ; k++) x [k] -= xj * sL [j * PB_LD + k] ;
+        for (int k = j + 1 ; k < NB ; k++) x [k] -= mulc (xj, sL [j * PB_LD + k]) ;
     }
     #pragma unroll
     for (int j = 0 ; j < NB ; j++) if (j < jb) X [j * lda] = x [j] ;
@@ -861,18 +1298,22 @@ __device__ __forceinline__ void trsm_row (const T *sL, T *X, int64_t lda, int jb
 template <typename T>
 __global__ void __launch_bounds__ (TRSM_ROWS) k_trsm (const TrsmTile *__restrict__ tiles, T *Lx)
 {
-    __shared__ T sL [POTRF_NB * PB_LD] ;
+    // 16-byte entries: blocks wider than 16 columns always take the inverse path (k_trsm_zinv), and a
+    // 64 x 65 tile of them would not fit the 48 KB of static shared memory
+    constexpr int MAXNB = (sizeof (T) == 16) ? 32 : POTRF_NB ;
+    __shared__ T sL [(MAXNB - 1) * PB_LD + MAXNB] ;
     const TrsmTile t = tiles [blockIdx.x] ;
     const int jb = t.jb ;
     const int64_t lda = t.lda ;
     const int nbp = (jb <= 8) ? 8 : (jb <= 16) ? 16 : (jb <= 32) ? 32 : 64 ;
+    if (nbp > MAXNB) { __trap () ; }
     const T *D = Lx + t.diag_off ;
     for (int e = threadIdx.x ; e < nbp * nbp ; e += TRSM_ROWS)
     {
         int r = e % nbp, c = e / nbp ;
         T v ;
-        if (r < jb && c < jb) v = (r >= c) ? D [r + c * lda] : (T) 0 ;
-        else v = (r == c) ? (T) 1 : (T) 0 ;
+        if (r < jb && c < jb) v = (r >= c) ? D [r + c * lda] : from_real<T> (0) ;
+        else v = from_real<T> ((r == c) ? 1 : 0) ;
         sL [c * PB_LD + r] = v ;
     }
     __syncthreads () ;
@@ -881,93 +1322,105 @@ __global__ void __launch_bounds__ (TRSM_ROWS) k_trsm (const TrsmTile *__restrict
     if (nbp == 8) trsm_row<T, 8> (sL, X, lda, jb) ;
     else if (nbp == 16) trsm_row<T, 16> (sL, X, lda, jb) ;
     else if (nbp == 32) trsm_row<T, 32> (sL, X, lda, jb) ;
-    else trsm_row<T, 64> (sL, X, lda, jb) ;
+    else if constexpr (MAXNB >= 64) trsm_row<T, 64> (sL, X, lda, jb) ;
 }
 
 // ---------------------------------------------------------------------------------------------
 // supernodal solve, one CTA per supernode of a level (forward: leaves first; backward: root first)
 // ---------------------------------------------------------------------------------------------
 
+// The right-hand sides are double (real factor) or complex double (complex factor) whatever the factor's
+// own precision; the backward sweep uses L^H (SSOL:309-586, the "C" variants for complex).
+template <typename T> struct solve_x { typedef double type ; } ;
+template <typename R> struct solve_x<cx<R>> { typedef cx<double> type ; } ;
+
 // forward:  x1 <- L11 \ x1 ;  x [rows below] -= L21 * x1      (SSOL:20-303; atomics because siblings of
 // one level update common ancestor rows concurrently)
 template <typename T>
 __global__ void __launch_bounds__ (256) k_solve_fwd (const int32_t *__restrict__ list,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs, int64_t smem_cap)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs,
+    int64_t smem_cap)
 {
-    extern __shared__ double sx_smem [] ;       // [min (nscol, smem_cap)]
+    typedef typename solve_x<T>::type XT ;
+    extern __shared__ __align__ (16) unsigned char solve_smem [] ;
+    XT *sx_smem = reinterpret_cast<XT *> (solve_smem) ;      // [min (nscol, smem_cap)]
     const int s = list [blockIdx.x] ;
     const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
     const T *L = Lx + px [s] ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        double *x = X + (int64_t) rhs * n ;
+        XT *x = X + (int64_t) rhs * n ;
         // work in shared memory when the supernode's columns fit, else in place in global memory
         const bool in_smem = nscol <= smem_cap ;
-        double *sx = in_smem ? sx_smem : x + k1 ;
+        XT *sx = in_smem ? sx_smem : x + k1 ;
         if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) sx [j] = x [k1 + j] ;
         __syncthreads () ;
         for (int64_t j = 0 ; j < nscol ; j++)
         {
-            double xj = sx [j] / (double) L [j + j * nsrow] ;
+            XT xj = sx [j] / (double) real_ (L [j + j * nsrow]) ;
             __syncthreads () ;
             if (threadIdx.x == 0) sx [j] = xj ;
             for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
-                sx [i] -= (double) L [i + j * nsrow] * xj ;
+                sx [i] -= cvt<XT> (L [i + j * nsrow]) * xj ;
             __syncthreads () ;
         }
         if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) x [k1 + j] = sx [j] ;
         for (int64_t i = nscol + threadIdx.x ; i < nsrow ; i += blockDim.x)
         {
-            double acc = 0 ;
-            for (int64_t j = 0 ; j < nscol ; j++) acc += (double) L [i + j * nsrow] * sx [j] ;
-            atomicAdd (x + Ls [psi + i], -acc) ;
+            XT acc = from_real<XT> (0) ;
+            for (int64_t j = 0 ; j < nscol ; j++) acc += cvt<XT> (L [i + j * nsrow]) * sx [j] ;
+            atomic_sub (x + Ls [psi + i], acc) ;
         }
         __syncthreads () ;
     }
 }
 
-// backward:  x1 <- L11' \ (x1 - L21' * x [rows below])        (SSOL:309-586)
+// backward:  x1 <- L11^H \ (x1 - L21^H * x [rows below])        (SSOL:309-586)
 template <typename T>
 __global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__ list,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs, int64_t smem_cap)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs,
+    int64_t smem_cap)
 {
-    extern __shared__ double sx_smem [] ;       // [min (nscol, smem_cap)]
-    __shared__ double red [8] ;
+    typedef typename solve_x<T>::type XT ;
+    extern __shared__ __align__ (16) unsigned char solve_smem [] ;
+    XT *sx_smem = reinterpret_cast<XT *> (solve_smem) ;      // [min (nscol, smem_cap)]
+    __shared__ XT red [8] ;
     const int s = list [blockIdx.x] ;
     const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
     const T *L = Lx + px [s] ;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5 ;
+    const XT zero = from_real<XT> (0) ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        double *x = X + (int64_t) rhs * n ;
+        XT *x = X + (int64_t) rhs * n ;
         const bool in_smem = nscol <= smem_cap ;
-        double *sx = in_smem ? sx_smem : x + k1 ;
-        // sx [j] = x [k1+j] - sum_{i >= nscol} L (i,j) * x [Ls [i]] : one warp per column
+        XT *sx = in_smem ? sx_smem : x + k1 ;
+        // sx [j] = x [k1+j] - sum_{i >= nscol} conj (L (i,j)) * x [Ls [i]] : one warp per column
         for (int64_t j = warp ; j < nscol ; j += nwarps)
         {
-            double acc = 0 ;
+            XT acc = zero ;
             for (int64_t i = nscol + lane ; i < nsrow ; i += 32)
-                acc += (double) L [i + j * nsrow] * x [Ls [psi + i]] ;
-            for (int o = 16 ; o > 0 ; o >>= 1) acc += __shfl_xor_sync (0xffffffffu, acc, o) ;
+                acc += mulc (x [Ls [psi + i]], cvt<XT> (L [i + j * nsrow])) ;
+            for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
             if (lane == 0) sx [j] = x [k1 + j] - acc ;
         }
         __syncthreads () ;
         for (int64_t j = nscol - 1 ; j >= 0 ; j--)
         {
-            // xj = (sx [j] - sum_{i > j, i < nscol} L (i,j) * sx [i]) / L (j,j)
-            double acc = 0 ;
+            // xj = (sx [j] - sum_{i > j, i < nscol} conj (L (i,j)) * sx [i]) / L (j,j)
+            XT acc = zero ;
             for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
-                acc += (double) L [i + j * nsrow] * sx [i] ;
-            for (int o = 16 ; o > 0 ; o >>= 1) acc += __shfl_xor_sync (0xffffffffu, acc, o) ;
+                acc += mulc (sx [i], cvt<XT> (L [i + j * nsrow])) ;
+            for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
             if (lane == 0) red [warp] = acc ;
             __syncthreads () ;
             if (threadIdx.x == 0)
             {
-                double tot = 0 ;
+                XT tot = zero ;
                 for (int w = 0 ; w < nwarps ; w++) tot += red [w] ;
-                sx [j] = (sx [j] - tot) / (double) L [j + j * nsrow] ;
+                sx [j] = (sx [j] - tot) / (double) real_ (L [j + j * nsrow]) ;
             }
             __syncthreads () ;
         }
@@ -984,15 +1437,22 @@ __global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__
 struct SolveBlk  { int32_t s, c0, jb, pad ; } ;                     // 64-wide diagonal block of supernode s
 struct SolveTile { int32_t s, c0, jb, r0, nrows, p0, p1, p2 ; } ;   // rows [r0, r0+nrows) of s below that block
 
+template <typename T> constexpr size_t solve_diag_smem_bytes ()
+{
+    return (size_t) (64 * 65 + 64) * sizeof (typename solve_x<T>::type) ;
+}
+
 // forward, diagonal block:  x_blk <- L_blk \ x_blk     (the dtrsv / dtrsm of SSOL:93, :204)
-// backward (TRANS):         x_blk <- L_blk' \ x_blk    (SSOL:386-402)
+// backward (TRANS):         x_blk <- L_blk^H \ x_blk   (SSOL:386-402)
 template <typename T, bool TRANS>
 __global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict__ blks,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+    const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
 {
-    __shared__ double sL [64 * 65] ;            // sL [c * 65 + r] = L (r,c), lower
-    __shared__ double sx [64] ;
+    typedef typename solve_x<T>::type XT ;
+    extern __shared__ __align__ (16) unsigned char solve_smem [] ;
+    XT *sL = reinterpret_cast<XT *> (solve_smem) ;          // sL [c * 65 + r] = L (r,c), lower
+    XT *sx = sL + 64 * 65 ;                                 // [64]
     const SolveBlk b = blks [blockIdx.x] ;
     const int64_t k1 = super [b.s], nsrow = pi [b.s+1] - pi [b.s] ;
     const T *L = Lx + px [b.s] + b.c0 + (int64_t) b.c0 * nsrow ;
@@ -1000,18 +1460,18 @@ __global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict_
     for (int e = tid ; e < jb * jb ; e += 64)
     {
         const int r = e % jb, c = e / jb ;
-        if (r >= c) sL [c * 65 + r] = (double) L [r + (int64_t) c * nsrow] ;
+        if (r >= c) sL [c * 65 + r] = cvt<XT> (L [r + (int64_t) c * nsrow]) ;
     }
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        double *x = X + (int64_t) rhs * n + k1 + b.c0 ;
+        XT *x = X + (int64_t) rhs * n + k1 + b.c0 ;
         if (tid < jb) sx [tid] = x [tid] ;
         __syncthreads () ;
         if (!TRANS)
         {
             for (int j = 0 ; j < jb ; j++)
             {
-                if (tid == j) sx [j] = sx [j] / sL [j * 65 + j] ;
+                if (tid == j) sx [j] = sx [j] / real_ (sL [j * 65 + j]) ;
                 __syncthreads () ;
                 if (tid > j && tid < jb) sx [tid] -= sL [j * 65 + tid] * sx [j] ;
                 __syncthreads () ;
@@ -1021,9 +1481,9 @@ __global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict_
         {
             for (int j = jb - 1 ; j >= 0 ; j--)
             {
-                if (tid == j) sx [j] = sx [j] / sL [j * 65 + j] ;
+                if (tid == j) sx [j] = sx [j] / real_ (sL [j * 65 + j]) ;
                 __syncthreads () ;
-                if (tid < j) sx [tid] -= sL [tid * 65 + j] * sx [j] ;
+                if (tid < j) sx [tid] -= mulc (sx [j], sL [tid * 65 + j]) ;
                 __syncthreads () ;
             }
         }
@@ -1038,55 +1498,57 @@ __global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict_
 template <typename T>
 __global__ void __launch_bounds__ (256) k_solve_gemv (const SolveTile *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
 {
-    __shared__ double xb [64] ;
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT xb [64] ;
     const SolveTile t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
     const T *L = Lx + px [t.s] + (int64_t) t.c0 * nsrow ;
     const int row = t.r0 + threadIdx.x ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        double *x = X + (int64_t) rhs * n ;
+        XT *x = X + (int64_t) rhs * n ;
         if (threadIdx.x < t.jb) xb [threadIdx.x] = x [k1 + t.c0 + threadIdx.x] ;
         __syncthreads () ;
         if ((int) threadIdx.x < t.nrows)
         {
-            double acc = 0 ;
-            for (int j = 0 ; j < t.jb ; j++) acc += (double) L [row + (int64_t) j * nsrow] * xb [j] ;
+            XT acc = from_real<XT> (0) ;
+            for (int j = 0 ; j < t.jb ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * xb [j] ;
             const int64_t dst = (row < nscol) ? k1 + row : (int64_t) Ls [psi + row] ;
-            atomicAdd (x + dst, -acc) ;
+            atomic_sub (x + dst, acc) ;
         }
         __syncthreads () ;
     }
 }
 
-// backward, rows below the block:  x_blk -= L (rows, blk)' * x [rows]     (SSOL:386: dgemv "C");
+// backward, rows below the block:  x_blk -= L (rows, blk)^H * x [rows]     (SSOL:386: dgemv "C");
 // thread (j, part) walks down column j of the tile, 4 threads per column
 template <typename T>
 __global__ void __launch_bounds__ (256) k_solve_gemvt (const SolveTile *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, double *X, int64_t n, int nrhs)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
 {
-    __shared__ double xr [256] ;
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT xr [256] ;
     const SolveTile t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
     const int j = threadIdx.x >> 2, part = threadIdx.x & 3 ;
     const T *Lc = Lx + px [t.s] + (int64_t) (t.c0 + j) * nsrow + t.r0 ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        double *x = X + (int64_t) rhs * n ;
+        XT *x = X + (int64_t) rhs * n ;
         if ((int) threadIdx.x < t.nrows)
         {
             const int row = t.r0 + threadIdx.x ;
             xr [threadIdx.x] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
         }
         __syncthreads () ;
-        double acc = 0 ;
-        if (j < t.jb) for (int r = part ; r < t.nrows ; r += 4) acc += (double) Lc [r] * xr [r] ;
-        acc += __shfl_xor_sync (0xffffffffu, acc, 1) ;
-        acc += __shfl_xor_sync (0xffffffffu, acc, 2) ;
-        if (part == 0 && j < t.jb) atomicAdd (x + k1 + t.c0 + j, -acc) ;
+        XT acc = from_real<XT> (0) ;
+        if (j < t.jb) for (int r = part ; r < t.nrows ; r += 4) acc += mulc (xr [r], cvt<XT> (Lc [r])) ;
+        acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+        acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+        if (part == 0 && j < t.jb) atomic_sub (x + k1 + t.c0 + j, acc) ;
         __syncthreads () ;
     }
 }

@@ -95,6 +95,18 @@ def el27(nx, ny=None, nz=None, dof=3):
     return _lower_csc(np.concatenate(rows), np.concatenate(cols), np.concatenate(vals), n)
 
 
+def hermitian(n, Ap, Ai, Ax):
+    """A Hermitian positive definite matrix with the pattern and the moduli of a real symmetric one: every
+    stored off-diagonal entry a_ij (i > j) gets the deterministic phase exp(i*theta_ij); the diagonal stays
+    real.  (Irreducible diagonal dominance does not see phases, so the result is positive definite whenever
+    the real matrix is diagonally dominant.)  Returns (n, Ap, Ai, Ax) with complex128 Ax."""
+    col = np.repeat(np.arange(n, dtype=np.int64), np.diff(Ap))
+    theta = 0.37 * ((7 * Ai + 13 * col) % 11) + 0.11
+    z = np.asarray(Ax, dtype=np.float64) * np.exp(1j * theta)
+    z[Ai == col] = np.asarray(Ax, dtype=np.float64)[Ai == col]
+    return n, Ap, Ai, z.astype(np.complex128)
+
+
 def rhs(n):
     """The demo's right-hand side b_i = 1 + i/n (CHOLMOD/Demo/cholmod_dl_demo.c:243-249)."""
     return 1.0 + np.arange(n, dtype=np.float64) / n

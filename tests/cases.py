@@ -9,8 +9,10 @@ from suitesparse_b200 import matrices as M
 GEN = {"lap2d5": M.lap2d5, "lap2d9": M.lap2d9, "lap3d7": M.lap3d7, "el27": M.el27}
 
 
-def make_matrix(kind, size, shift_diag=None):
+def make_matrix(kind, size, shift_diag=None, hermitian=False):
     n, Ap, Ai, Ax = GEN[kind](size)
+    if hermitian:
+        n, Ap, Ai, Ax = M.hermitian(n, Ap, Ai, Ax)
     if shift_diag is not None:
         # make the matrix indefinite: overwrite one diagonal entry (column k's first stored entry is the diagonal)
         k, val = shift_diag
@@ -23,11 +25,12 @@ def make_matrix(kind, size, shift_diag=None):
 class Case:
     """Reference analysis + seam matrix + reference CPU factor for one matrix."""
 
-    def __init__(self, kind, size, ordering, single=False, shift_diag=None, beta=0.0, factor=True):
+    def __init__(self, kind, size, ordering, single=False, shift_diag=None, beta=0.0, factor=True,
+                 hermitian=False, zomplex=False):
         self.kind, self.size, self.single, self.beta = kind, size, single, beta
-        self.n, self.Ap, self.Ai, self.Ax = make_matrix(kind, size, shift_diag)
+        self.n, self.Ap, self.Ai, self.Ax = make_matrix(kind, size, shift_diag, hermitian)
         self.ref = refd.Ref()
-        self.ref.set_matrix(self.n, self.Ap, self.Ai, self.Ax, -1, single=single)
+        self.ref.set_matrix(self.n, self.Ap, self.Ai, self.Ax, -1, single=single, zomplex=zomplex)
         self.ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
         self.sym = self.ref.symbolic()
         self.Sp, self.Si, self.Sx = self.ref.seam()
@@ -38,8 +41,9 @@ class Case:
 
     def rel_err(self, Lx):
         """max |dL| / max |L| over the supernodal storage."""
-        Lx = np.asarray(Lx, dtype=np.float64)
-        Lr = self.Lref.astype(np.float64)
+        wide = np.complex128 if np.iscomplexobj(self.Lref) else np.float64
+        Lx = np.asarray(Lx, dtype=wide)
+        Lr = self.Lref.astype(wide)
         scale = np.max(np.abs(Lr))
         return float(np.max(np.abs(Lx - Lr)) / (scale if scale > 0 else 1.0))
 
@@ -53,5 +57,6 @@ class Case:
 
 
 @functools.lru_cache(maxsize=None)
-def get_case(kind, size, ordering, single=False, shift_diag=None, beta=0.0):
-    return Case(kind, size, ordering, single=single, shift_diag=shift_diag, beta=beta)
+def get_case(kind, size, ordering, single=False, shift_diag=None, beta=0.0, hermitian=False, zomplex=False):
+    return Case(kind, size, ordering, single=single, shift_diag=shift_diag, beta=beta, hermitian=hermitian,
+                zomplex=zomplex)

@@ -32,8 +32,10 @@ def dump(name, ref, beta=0.0):
           "minor", ref.geti("minor"))
 
 
-def synthetic(name, gen, size, ordering, beta=0.0, neg=None):
+def synthetic(name, gen, size, ordering, beta=0.0, neg=None, hermitian=False):
     n, Ap, Ai, Ax = gen(size)
+    if hermitian:
+        n, Ap, Ai, Ax = M.hermitian(n, Ap, Ai, Ax)
     if neg is not None:
         Ax = Ax.copy(); Ax[Ap[neg]] = -1.0
     r = refd.Ref(); r.set_matrix(n, Ap, Ai, Ax, -1); r.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
@@ -47,11 +49,19 @@ def demo(name, fname):
 
 
 if __name__ == "__main__":
+    only = sys.argv[1:]         # optional: names of the fixtures to (re)generate
+    if only:
+        _syn, _demo = synthetic, demo
+        synthetic = lambda name, *a, **k: _syn(name, *a, **k) if name in only else None     # noqa: E731
+        demo = lambda name, *a, **k: _demo(name, *a, **k) if name in only else None         # noqa: E731
     synthetic("lap2d5_24_amd", M.lap2d5, 24, refd.CHOLMOD_AMD)
     synthetic("lap3d7_9_metis", M.lap3d7, 9, refd.CHOLMOD_METIS)
     synthetic("lap2d9_20_metis_beta", M.lap2d9, 20, refd.CHOLMOD_METIS, beta=0.25)
     synthetic("el27_4_metis", M.el27, 4, refd.CHOLMOD_METIS)
     synthetic("lap2d5_16_notposdef", M.lap2d5, 16, refd.CHOLMOD_AMD, neg=100)
+    # Hermitian (cd_cholmod_super_numeric_worker): complex entries, complex L
+    synthetic("herm_lap3d7_8_metis", M.lap3d7, 8, refd.CHOLMOD_METIS, hermitian=True)
+    synthetic("herm_lap2d5_14_notposdef", M.lap2d5, 14, refd.CHOLMOD_AMD, neg=90, hermitian=True)
     # the reference's own ctest matrices (CHOLMOD/CMakeLists.txt:835-878); bcsstk02 is its "supernodal" test
     demo("bcsstk01", "bcsstk01.tri")
     demo("bcsstk02", "bcsstk02.tri")

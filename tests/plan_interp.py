@@ -124,7 +124,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                 k0, k1 = int(t["k0"]), int(t["k1"])
                 assert 0 <= k0 < k1 <= it["K"]
                 A = _view(Lx, int(it["a_off"]), M, int(it["K"]), lda)
-                Cpart = A[i0:i1, k0:k1] @ A[j0:j1, k0:k1].T
+                Cpart = A[i0:i1, k0:k1] @ A[j0:j1, k0:k1].conj().T    # A * B^H (B' for real data)
                 ii, jj = np.meshgrid(np.arange(i0, i1), np.arange(j0, j1), indexing="ij")
                 keep = ii >= jj
                 if it["map_off"] >= 0:
@@ -141,11 +141,11 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                 assert jb <= (16, 32, 64)[kind - b200.K_POTRF16]
                 D = _view(Lx, int(b["off"]), jb, jb, lda)
                 Dl = np.tril(D)
-                Dsym = Dl + np.tril(Dl, -1).T
+                Dsym = Dl + np.tril(Dl, -1).conj().T
                 # unblocked right-looking Cholesky with the kernel's failure rule
                 Lc = Dsym.copy()
                 for j in range(jb):
-                    d = Lc[j, j]
+                    d = Lc[j, j].real
                     if not d > 0:
                         col = int(b["col"]) + j
                         minor = col if minor is None else min(minor, col)
@@ -153,7 +153,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                         ljj = np.sqrt(d)
                         Lc[j:, j] = Lc[j:, j] / ljj
                         Lc[j, j] = ljj
-                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
+                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j].conj())
                 r, c = np.tril_indices(jb)
                 D[r, c] = Lc[r, c]
         elif kind == b200.K_FACTOR_SMALL:
@@ -162,9 +162,9 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                 assert jb <= 16 and lda - jb <= 256
                 P = _view(Lx, int(b["off"]), lda, jb, lda)      # the whole supernode: b.off is its origin
                 Dl = np.tril(P[:jb, :])
-                Lc = Dl + np.tril(Dl, -1).T
+                Lc = Dl + np.tril(Dl, -1).conj().T
                 for j in range(jb):
-                    d = Lc[j, j]
+                    d = Lc[j, j].real
                     if not d > 0:
                         col = int(b["col"]) + j
                         minor = col if minor is None else min(minor, col)
@@ -172,13 +172,13 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                         ljj = np.sqrt(d)
                         Lc[j:, j] = Lc[j:, j] / ljj
                         Lc[j, j] = ljj
-                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j])
+                        Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j].conj())
                 r, c = np.tril_indices(jb)
                 P[r, c] = Lc[r, c]
                 if lda > jb:
                     L11 = np.tril(P[:jb, :])
                     with np.errstate(all="ignore"):
-                        P[jb:, :] = np.linalg.solve(L11, P[jb:, :].T).T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
+                        P[jb:, :] = np.linalg.solve(L11, P[jb:, :].conj().T).conj().T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
                             else np.nan
         elif kind in b200.K_TRSM_KINDS:
             for t in trsm[first:first + cnt]:
@@ -187,7 +187,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
                 L11 = np.tril(_view(Lx, int(t["diag_off"]), jb, jb, lda))
                 X = _view(Lx, int(t["row_off"]), nr, jb, lda)
                 with np.errstate(all="ignore"):
-                    X[:, :] = np.linalg.solve(L11, X.T).T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
+                    X[:, :] = np.linalg.solve(L11, X.conj().T).conj().T if np.all(np.isfinite(L11)) and np.all(np.diag(L11) != 0) \
                         else np.full_like(X, np.nan)
         else:
             raise AssertionError("unknown launch kind %d" % kind)

@@ -37,6 +37,14 @@ for use_gpu in (0, 1):
     out[use_gpu]["np_status"] = r2.factorize(0.0)
     out[use_gpu]["np_minor"] = r2.geti("minor")
     out[use_gpu]["np_Lx"] = r2.Lx().copy()
+    # Hermitian, stored zomplex: zd_cholmod_super_numeric_worker's seat (complex L from a zomplex A)
+    nz_, Zp, Zi, Zx = M.hermitian(*M.lap3d7(14))
+    r3 = refd.Ref(); r3.seti("useGPU", use_gpu); r3.set_matrix(nz_, Zp, Zi, Zx, -1, zomplex=True)
+    r3.analyze(refd.CHOLMOD_METIS, refd.CHOLMOD_SUPERNODAL)
+    out[use_gpu]["z_status"] = r3.factorize(0.0)
+    bz = M.rhs(nz_) * (1 + 0.5j)
+    out[use_gpu]["z_resid"] = r3.resid(r3.solve(bz), bz)
+    out[use_gpu]["z_Lx"] = r3.Lx().copy()
 import ctypes
 shim = ctypes.CDLL(%(shim)r)
 res = dict(
@@ -47,6 +55,9 @@ res = dict(
     np_status=[out[0]["np_status"], out[1]["np_status"]], np_minor=[out[0]["np_minor"], out[1]["np_minor"]],
     np_err=float(np.max(np.abs(out[0]["np_Lx"] - out[1]["np_Lx"]))),
     np_zero_same=bool(np.array_equal(out[0]["np_Lx"] == 0, out[1]["np_Lx"] == 0)),
+    z_status=[out[0]["z_status"], out[1]["z_status"]], z_resid=[out[0]["z_resid"], out[1]["z_resid"]],
+    z_err=float(np.max(np.abs(out[0]["z_Lx"] - out[1]["z_Lx"])) / np.max(np.abs(out[0]["z_Lx"]))),
+    z_identical=bool(np.array_equal(out[0]["z_Lx"], out[1]["z_Lx"])), z_dtype=str(out[1]["z_Lx"].dtype),
     dealloc=int(shim.cholmod_l_b200_deallocate(None)))
 print("RESULT " + json.dumps(res))
 """
@@ -68,4 +79,7 @@ def test_unmodified_cholmod_factorize_runs_on_the_gpu():
     assert not res["identical"]
     assert res["np_status"] == [1, 1] and res["np_minor"][0] == res["np_minor"][1]
     assert res["np_zero_same"] and res["np_err"] <= 1e-10 * 10
+    # the Hermitian (zomplex in, complex out) factorization went through the same door
+    assert res["z_status"] == [0, 0] and res["z_dtype"] == "complex128"
+    assert res["z_err"] <= 1e-10 and res["z_resid"][1] <= 1e-12 and not res["z_identical"]
     assert res["dealloc"] == 1

@@ -53,7 +53,7 @@ def test_golden_fixtures_on_gpu():
         g = np.load(f)
         sym = dict(n=int(g["n"]), nsuper=int(g["nsuper"]), xsize=int(g["xsize"]), super=g["super"], pi=g["pi"],
                    px=g["px"], s=g["s"])
-        F = b200.Factor(sym, device=0)
+        F = b200.Factor(sym, dtype=g["Sx"].dtype, device=0)      # the Hermitian fixtures are complex128
         st, Lx = F.super_numeric(g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]))
         assert st == int(g["status"]) and F.minor == int(g["minor"]), f
         Lref = g["Lx"]

@@ -46,6 +46,40 @@ def test_port_single_precision():
 
 
 @needs_ref
+@pytest.mark.parametrize("zomplex", [False, True])
+@pytest.mark.parametrize("single", [False, True])
+def test_port_hermitian(zomplex, single):
+    """cd_/zd_/cs_/zs_cholmod_super_numeric_worker: Hermitian A stored complex or zomplex, L complex."""
+    c = Case("lap3d7", 10, refd.CHOLMOD_METIS, hermitian=True, zomplex=zomplex, single=single)
+    want = np.complex64 if single else np.complex128
+    assert c.status == refd.CHOLMOD_OK and c.Lref.dtype == want and c.Sx.dtype == want
+    st, minor, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx)
+    assert st == 0 and minor == c.n and Lp.dtype == want
+    assert c.rel_err(Lp) <= (1e-5 if single else 1e-13)
+    if not single:
+        assert c.residual_with(Lp) <= 1e-12
+        b = M.rhs(c.n) * (1 + 0.5j)
+        x = refd.port_solve(c.sym, Lp, b[c.sym["Perm"]])
+        xx = np.empty(c.n, dtype=np.complex128); xx[c.sym["Perm"]] = x
+        xr = c.ref.solve(b)
+        assert np.max(np.abs(xx - xr)) <= 1e-12 * np.max(np.abs(xr))
+
+
+@needs_ref
+@pytest.mark.parametrize("col,quick", [(37, False), (37, True), (0, False)])
+def test_port_hermitian_not_posdef(col, quick):
+    c = Case("lap2d5", 20, refd.CHOLMOD_AMD, shift_diag=(col, -1.0), factor=False, hermitian=True)
+    c.ref.seti("quick_return_if_not_posdef", int(quick))
+    c.ref.super_numeric(0.0)
+    assert c.ref.geti("status") == refd.CHOLMOD_NOT_POSDEF
+    Lref, minor_ref = c.ref.Lx().copy(), c.ref.geti("minor")
+    st, minor, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx, quick_return=quick)
+    assert st == 1 and minor == minor_ref
+    assert np.array_equal(Lp == 0, Lref == 0)
+    assert np.max(np.abs(Lp - Lref)) <= 1e-13 * max(1.0, np.max(np.abs(Lref)))
+
+
+@needs_ref
 @pytest.mark.parametrize("col,quick", [(0, False), (37, False), (37, True), (399, False), (250, False)])
 def test_port_not_posdef_semantics(col, quick):
     """L->minor, zero fill and the repeated supernode of SNW:1084-1146."""

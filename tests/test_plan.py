@@ -63,6 +63,28 @@ def test_plan_reproduces_reference_factor(kind, size, ordering):
 
 
 @needs_ref
+@needs_ref
+@pytest.mark.parametrize("kind,size,ordering,dtype", [("lap3d7", 12, refd.CHOLMOD_METIS, np.complex128),
+                                                      ("lap2d9", 30, refd.CHOLMOD_METIS, np.complex128),
+                                                      ("lap3d7", 16, refd.CHOLMOD_METIS, np.complex64)])
+def test_plan_reproduces_reference_factor_hermitian(kind, size, ordering, dtype):
+    """The same plan run with Hermitian kernel semantics (A*B^H updates, zpotrf, X*L^-H) gives the factor of
+    the reference's cd_/cs_ workers; complex128 plans use the inverse-based panel solves, complex64 ones the
+    substitution kernels, like their real counterparts."""
+    single = dtype == np.complex64
+    c = get_case(kind, size, ordering, hermitian=True, single=single)
+    assert c.status == refd.CHOLMOD_OK and c.Lref.dtype == dtype
+    F = b200.Factor(c.sym, dtype=dtype, device=-1)
+    for prefer in (0, 1):
+        Lx = np.zeros(c.sym["xsize"], dtype=np.complex128)
+        plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
+        assert plan_interp.run_plan(F, Lx, prefer=prefer) is None
+        assert c.rel_err(Lx) <= (1e-5 if single else 1e-12)
+    launches = F.plan_table("launches", b200.LAUNCH_DT)
+    has_inv = np.isin(launches["kind"], (b200.K_TRSM_INV32, b200.K_TRSM_INV64)).any()
+    assert has_inv == (not single) or not np.isin(launches["kind"], b200.K_TRSM_KINDS).any()
+
+
 def test_plan_structure():
     c = get_case("lap3d7", 22, refd.CHOLMOD_METIS)
     F = b200.Factor(c.sym, device=-1)
