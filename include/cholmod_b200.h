@@ -122,12 +122,28 @@ int b200_super_numeric_z (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
 int b200_super_numeric_c (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const float *Ax, const float *Az, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor) ;
 
+/* The unsymmetric case, A->stype == 0 (cholmod_super_numeric.c:136-154, t_cholmod_super_numeric_worker.c:471-506):
+ * the matrix that is factorized is A*F + beta*I, where A is n-by-ncol (rows already permuted:
+ * A(p,f) of cholmod_factorize.c:236-247) and F = A(p,f)^H is ncol-by-n, both CSC, packed or not (Anz / Fnz),
+ * values of the context's type (any of the four); A*F is never formed: each column of L gathers its part of
+ * it.  Az and Fz are both NULL, or both non-NULL for zomplex input to a complex context (real parts in Ax /
+ * Fx, imaginary parts in Az / Fz).  Lx [xsize] of the context's type.  Status and *minor as above. */
+int b200_super_numeric_aat (b200_factor *f, int64_t ncol, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax, const void *Az, const int64_t *Fp, const int64_t *Fi, const int64_t *Fnz, const void *Fx,
+    const void *Fz, double beta, int quick_return_if_not_posdef, void *Lx, int64_t *minor) ;
+
 /* --- the same phase in three steps, for callers that keep A and L resident in HBM ---------------- */
 
 /* Copy A (host CSC as above, values of the context's dtype) to the device.  The pattern may change from
  * call to call.  Replaces the per-supernode host scatter + H2D of t_cholmod_gpu.c:669-700. */
 int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const void *Ax) ;
+
+/* The same for the unsymmetric case: A (n-by-ncol) and F (ncol-by-n) as for b200_super_numeric_aat, values
+ * of the context's type ((re,im) pairs for a complex context).  The next b200_factor_device factorizes
+ * A*F + beta*I. */
+int b200_upload_matrix_aat (b200_factor *f, int64_t ncol, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax, const int64_t *Fp, const int64_t *Fi, const int64_t *Fnz, const void *Fx) ;
 
 /* Re-factorization fast path (cholmod_factorize.c:67-70: one analysis, many numeric factorizations): the
  * pattern uploaded by the last b200_upload_matrix is kept on the device and only the values Ax (same

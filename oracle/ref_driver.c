@@ -25,7 +25,8 @@ typedef struct
 {
     cholmod_common cm ;
     cholmod_sparse *A ;     // user matrix (symmetric, one triangle stored)
-    cholmod_sparse *S ;     // seam matrix: tril (P A P'), stype -1
+    cholmod_sparse *S ;     // seam matrix: tril (P A P'), stype -1 (or A(p,:), stype 0, when A is unsymmetric)
+    cholmod_sparse *F ;     // unsymmetric case only: F = A(p,:)^H, so that S*F is what gets factorized
     cholmod_factor *L ;
     double t_analyze, t_factor, t_solve ;
 } refd ;
@@ -53,6 +54,7 @@ void refd_close (void *hv)
     if (!h) return ;
     cholmod_l_free_factor (&h->L, &h->cm) ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     cholmod_l_free_sparse (&h->A, &h->cm) ;
     cholmod_l_finish (&h->cm) ;
     free (h) ;
@@ -66,6 +68,7 @@ int refd_set_matrix (void *hv, int64_t n, const int64_t *Ap, const int64_t *Ai,
     refd *h = (refd *) hv ;
     cholmod_l_free_sparse (&h->A, &h->cm) ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     cholmod_l_free_factor (&h->L, &h->cm) ;
     int64_t nz = Ap [n] ;
     int xdtype = CHOLMOD_REAL + (single ? CHOLMOD_SINGLE : CHOLMOD_DOUBLE) ;
@@ -94,12 +97,44 @@ int refd_set_matrix_x (void *hv, int64_t n, const int64_t *Ap, const int64_t *Ai
     if (xtype == CHOLMOD_REAL) return refd_set_matrix (hv, n, Ap, Ai, Ax, stype, single) ;
     cholmod_l_free_sparse (&h->A, &h->cm) ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     cholmod_l_free_factor (&h->L, &h->cm) ;
     int64_t nz = Ap [n] ;
     int xdtype = xtype + (single ? CHOLMOD_SINGLE : CHOLMOD_DOUBLE) ;
     h->A = cholmod_l_allocate_sparse ((size_t) n, (size_t) n, (size_t) nz, 1, 1, stype, xdtype, &h->cm) ;
     if (!h->A) return -1 ;
     memcpy (h->A->p, Ap, (size_t) (n+1) * sizeof (int64_t)) ;
+    memcpy (h->A->i, Ai, (size_t) nz * sizeof (int64_t)) ;
+    int64_t nx = (xtype == CHOLMOD_COMPLEX) ? 2*nz : nz ;
+    if (single)
+    {
+        float *x = (float *) h->A->x ;
+        for (int64_t p = 0 ; p < nx ; p++) x [p] = (float) Ax [p] ;
+        if (xtype == CHOLMOD_ZOMPLEX) { float *z = (float *) h->A->z ; for (int64_t p = 0 ; p < nz ; p++) z [p] = (float) Az [p] ; }
+    }
+    else
+    {
+        memcpy (h->A->x, Ax, (size_t) nx * sizeof (double)) ;
+        if (xtype == CHOLMOD_ZOMPLEX) memcpy (h->A->z, Az, (size_t) nz * sizeof (double)) ;
+    }
+    return 0 ;
+}
+
+// An unsymmetric (stype 0) nrow-by-ncol matrix: cholmod_l_analyze / factorize then work on A*A^H
+// (cholmod_factorize.c:211-247).  xtype as for refd_set_matrix_x.
+int refd_set_matrix_rect (void *hv, int64_t nrow, int64_t ncol, const int64_t *Ap, const int64_t *Ai,
+    const double *Ax, const double *Az, int single, int xtype)
+{
+    refd *h = (refd *) hv ;
+    cholmod_l_free_sparse (&h->A, &h->cm) ;
+    cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
+    cholmod_l_free_factor (&h->L, &h->cm) ;
+    int64_t nz = Ap [ncol] ;
+    int xdtype = xtype + (single ? CHOLMOD_SINGLE : CHOLMOD_DOUBLE) ;
+    h->A = cholmod_l_allocate_sparse ((size_t) nrow, (size_t) ncol, (size_t) nz, 1, 1, 0, xdtype, &h->cm) ;
+    if (!h->A) return -1 ;
+    memcpy (h->A->p, Ap, (size_t) (ncol+1) * sizeof (int64_t)) ;
     memcpy (h->A->i, Ai, (size_t) nz * sizeof (int64_t)) ;
     int64_t nx = (xtype == CHOLMOD_COMPLEX) ? 2*nz : nz ;
     if (single)
@@ -124,6 +159,7 @@ int refd_read_matrix (void *hv, const char *path)
     if (!f) return -1 ;
     cholmod_l_free_sparse (&h->A, &h->cm) ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     cholmod_l_free_factor (&h->L, &h->cm) ;
     h->A = cholmod_l_read_sparse2 (f, CHOLMOD_DOUBLE, &h->cm) ;
     fclose (f) ;
@@ -138,6 +174,7 @@ int refd_analyze (void *hv, int ordering, int supernodal)
     if (!h->A) return -1 ;
     cholmod_l_free_factor (&h->L, &h->cm) ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     h->cm.supernodal = supernodal ;
     if (ordering >= 0)
     {
@@ -158,8 +195,17 @@ int refd_seam (void *hv)
     refd *h = (refd *) hv ;
     if (!h->A || !h->L) return -1 ;
     cholmod_l_free_sparse (&h->S, &h->cm) ;
+    cholmod_l_free_sparse (&h->F, &h->cm) ;
     cholmod_sparse *A = h->A, *A1 = NULL, *A2 = NULL ;
     int64_t *Perm = (h->L->ordering == CHOLMOD_NATURAL) ? NULL : (int64_t *) h->L->Perm ;
+    if (A->stype == 0)
+    {
+        // F = A(p,:)^H, S = F^H = A(p,:)   (cholmod_factorize.c:201-209, :236-247)
+        h->F = cholmod_l_ptranspose (A, 2, Perm, NULL, 0, &h->cm) ;
+        if (!h->F) return -2 ;
+        h->S = cholmod_l_ptranspose (h->F, 2, NULL, NULL, 0, &h->cm) ;
+        return h->S ? 0 : -2 ;
+    }
     if (A->stype > 0)
     {
         A1 = cholmod_l_ptranspose (A, 2, Perm, NULL, 0, &h->cm) ;
@@ -185,7 +231,7 @@ int refd_super_numeric (void *hv, double beta)
     if (!h->S || !h->L) return -1 ;
     double b [2] = { beta, 0 } ;
     double t = SUITESPARSE_TIME ;
-    int ok = cholmod_l_super_numeric (h->S, NULL, b, h->L, &h->cm) ;
+    int ok = cholmod_l_super_numeric (h->S, h->F, b, h->L, &h->cm) ;
     h->t_factor = SUITESPARSE_TIME - t ;
     return ok ? h->cm.status : -100 + h->cm.status ;
 }
@@ -303,6 +349,8 @@ int64_t refd_get_int (void *hv, const char *name)
     if (!strcmp (name, "status")) return h->cm.status ;
     if (!strcmp (name, "nthreads_max")) return h->cm.nthreads_max ;
     if (h->A && !strcmp (name, "n")) return (int64_t) h->A->nrow ;
+    if (h->A && !strcmp (name, "ncol")) return (int64_t) h->A->ncol ;
+    if (h->F && !strcmp (name, "nnzF")) return ((int64_t *) h->F->p) [h->F->ncol] ;
     if (h->A && !strcmp (name, "nnzA")) return ((int64_t *) h->A->p) [h->A->ncol] ;
     if (h->A && !strcmp (name, "stypeA")) return h->A->stype ;
     if (h->S && !strcmp (name, "nnzS")) return ((int64_t *) h->S->p) [h->S->ncol] ;
@@ -345,6 +393,10 @@ const void *refd_get_ptr (void *hv, const char *name)
     if (h->S && !strcmp (name, "Si")) return h->S->i ;
     if (h->S && !strcmp (name, "Sx")) return h->S->x ;
     if (h->S && !strcmp (name, "Sz")) return h->S->z ;
+    if (h->F && !strcmp (name, "Fp")) return h->F->p ;
+    if (h->F && !strcmp (name, "Fi")) return h->F->i ;
+    if (h->F && !strcmp (name, "Fx")) return h->F->x ;
+    if (h->F && !strcmp (name, "Fz")) return h->F->z ;
     if (!L) return NULL ;
     if (!strcmp (name, "Perm")) return L->Perm ;
     if (!strcmp (name, "ColCount")) return L->ColCount ;

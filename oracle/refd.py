@@ -42,6 +42,8 @@ def _driver():
         lib.refd_set_matrix.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         lib.refd_set_matrix_x.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_int, C.c_int, C.c_int]
+        lib.refd_set_matrix_rect.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_int, C.c_int]
         lib.refd_read_matrix.argtypes = [C.c_void_p, C.c_char_p]
         lib.refd_analyze.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.refd_seam.argtypes = [C.c_void_p]
@@ -135,6 +137,29 @@ class Ref:
         if rc:
             raise RuntimeError("refd_set_matrix failed")
 
+    def set_matrix_rect(self, nrow, ncol, Ap, Ai, Ax, single=False, zomplex=False):
+        """An unsymmetric nrow-by-ncol A (stype 0): analysis and factorization are those of A*A^H."""
+        Ap = np.ascontiguousarray(Ap, dtype=np.int64)
+        Ai = np.ascontiguousarray(Ai, dtype=np.int64)
+        self.single = bool(single)
+        if np.iscomplexobj(Ax):
+            Ax = np.ascontiguousarray(Ax, dtype=np.complex128)
+            self.xtype = 3 if zomplex else 2
+            if zomplex:
+                re, im = np.ascontiguousarray(Ax.real), np.ascontiguousarray(Ax.imag)
+                rc = self.lib.refd_set_matrix_rect(self.h, nrow, ncol, Ap.ctypes.data, Ai.ctypes.data, re.ctypes.data,
+                                                   im.ctypes.data, int(single), 3)
+            else:
+                rc = self.lib.refd_set_matrix_rect(self.h, nrow, ncol, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data,
+                                                   None, int(single), 2)
+        else:
+            self.xtype = 1
+            Ax = np.ascontiguousarray(Ax, dtype=np.float64)
+            rc = self.lib.refd_set_matrix_rect(self.h, nrow, ncol, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data,
+                                               None, int(single), 1)
+        if rc:
+            raise RuntimeError("refd_set_matrix_rect failed")
+
     def read_matrix(self, path):
         rc = self.lib.refd_read_matrix(self.h, path.encode())
         if rc:
@@ -169,13 +194,19 @@ class Ref:
         rc = self.lib.refd_seam(self.h)
         if rc:
             raise RuntimeError("refd_seam failed")
-        n, nz = self.geti("n"), self.geti("nnzS")
-        Sp, Si = _view(self._ptr("Sp"), n + 1, np.int64).copy(), _view(self._ptr("Si"), nz, np.int64).copy()
+        return self._csc("S", self.geti("ncol"), self.geti("nnzS"))
+
+    def _csc(self, which, ncols, nz):
+        p, i = _view(self._ptr(which + "p"), ncols + 1, np.int64).copy(), _view(self._ptr(which + "i"), nz, np.int64).copy()
         if self.xtype == 3:     # zomplex: returned as one complex array
             rd = np.float32 if self.single else np.float64
-            Sx = _view(self._ptr("Sx"), nz, rd) + 1j * _view(self._ptr("Sz"), nz, rd)
-            return Sp, Si, Sx.astype(self._xd())
-        return Sp, Si, _view(self._ptr("Sx"), nz, self._xd()).copy()
+            x = _view(self._ptr(which + "x"), nz, rd) + 1j * _view(self._ptr(which + "z"), nz, rd)
+            return p, i, x.astype(self._xd())
+        return p, i, _view(self._ptr(which + "x"), nz, self._xd()).copy()
+
+    def seam_F(self):
+        """Unsymmetric case, after seam(): F = A(p,:)^H (ncol-by-n), the second operand of cholmod_super_numeric."""
+        return self._csc("F", self.geti("n"), self.geti("nnzF"))
 
     def super_numeric(self, beta=0.0):
         """Reference CPU numeric phase at the seam; returns Common->status."""
@@ -256,15 +287,17 @@ def _portlib():
         for f in (lib.sn_port_d, lib.sn_port_s, lib.sn_port_z, lib.sn_port_c):
             f.restype = C.c_int
             f.argtypes = [C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
+                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                          C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
         lib.sn_port_solve_d.argtypes = [C.c_int64] + [C.c_void_p] * 6
         lib.sn_port_solve_z.argtypes = [C.c_int64] + [C.c_void_p] * 6
         _port = lib
     return _port
 
 
-def port_factor(sym, Sp, Si, Sx, beta=0.0, quick_return=False, Snz=None):
-    """Run the plain-C restatement.  Returns (status, minor, Lx)."""
+def port_factor(sym, Sp, Si, Sx, beta=0.0, quick_return=False, Snz=None, F=None):
+    """Run the plain-C restatement.  Returns (status, minor, Lx).  F = (Fp, Fi, Fx) selects the unsymmetric
+    case: S is then A(p,:) and S*F is factorized."""
     lib = _portlib()
     xd = np.asarray(Sx).dtype
     if xd not in (np.float32, np.float64, np.complex64, np.complex128):
@@ -278,9 +311,14 @@ def port_factor(sym, Sp, Si, Sx, beta=0.0, quick_return=False, Snz=None):
     fn = {np.dtype(np.float64): lib.sn_port_d, np.dtype(np.float32): lib.sn_port_s,
           np.dtype(np.complex128): lib.sn_port_z, np.dtype(np.complex64): lib.sn_port_c}[np.dtype(xd)]
     nzp = None if Snz is None else np.ascontiguousarray(Snz, dtype=np.int64).ctypes.data
+    fp = fi = fx = None
+    if F is not None:
+        Fp, Fi = (np.ascontiguousarray(a, dtype=np.int64) for a in F[:2])
+        Fx = np.ascontiguousarray(F[2], dtype=xd)
+        fp, fi, fx = Fp.ctypes.data, Fi.ctypes.data, Fx.ctypes.data
     st = fn(sym["n"], sym["nsuper"], sup.ctypes.data, pi.ctypes.data, px.ctypes.data, s.ctypes.data,
-            sym["xsize"], Sp.ctypes.data, Si.ctypes.data, nzp, Sx.ctypes.data, float(beta), int(quick_return),
-            Lx.ctypes.data, C.byref(minor))
+            sym["xsize"], Sp.ctypes.data, Si.ctypes.data, nzp, Sx.ctypes.data, fp, fi, None, fx, float(beta),
+            int(quick_return), Lx.ctypes.data, C.byref(minor))
     return int(st), int(minor.value), Lx
 
 

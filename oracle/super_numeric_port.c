@@ -5,6 +5,7 @@
 // double (sn_port_d), float (sn_port_s) and the Hermitian case in complex double (sn_port_z)
 // and complex float (sn_port_c; entries are (re,im) pairs, the CHOLMOD_COMPLEX layout).  It takes the arrays of the
 // supernodal symbolic factor (L->super, pi, px, s) and the seam matrix S = tril(P A P')
+// (or, for the unsymmetric case, S = A(p,:) and F = S^H: then S*F is what gets factorized)
 // as plain pointers; it does not include cholmod.h and calls no BLAS: the four dense
 // kernels are written out as loops, so it is slow and meant for small cases.
 //
@@ -27,7 +28,8 @@
 #define SNP_TEMPLATE(NAME, REAL, SCALAR, CONJ, REPART)                                                                \
 int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,                    \
     const int64_t *Lpx, const int64_t *Ls, int64_t xsize,                                         \
-    const int64_t *Ap, const int64_t *Ai, const int64_t *Anz, const SCALAR *Ax,                    \
+    const int64_t *Ap, const int64_t *Ai, const int64_t *Anz, const SCALAR *Ax,                   \
+    const int64_t *Fp, const int64_t *Fi, const int64_t *Fnz, const SCALAR *Fx,                   \
     double beta, int quick_return_if_not_posdef, SCALAR *Lx, int64_t *minor_out)                  \
 {                                                                                                 \
     /* workspace, SNW:211-221 */                                                                  \
@@ -60,8 +62,28 @@ int NAME (int64_t n, int64_t nsuper, const int64_t *Super, const int64_t *Lpi,  
         for (int64_t p = psx ; p < psx + nsrow*nscol ; p++) Lx [p] = 0 ;                          \
         /* Map: global row -> local row of s, SNW:388-399 */                                      \
         for (int64_t k = 0 ; k < nsrow ; k++) Map [Ls [psi+k]] = k ;                              \
+        /* unsymmetric case (Fp != NULL): columns k1..k2-1 of A*F, SNW:471-506 */                 \
+        for (int64_t k = k1 ; Fp && k < k2 ; k++)                                                 \
+        {                                                                                         \
+            int64_t pf = Fp [k], pfend = Fnz ? pf + Fnz [k] : Fp [k+1] ;                          \
+            for ( ; pf < pfend ; pf++)                                                            \
+            {                                                                                     \
+                int64_t j = Fi [pf] ;                                                             \
+                SCALAR fjk = Fx [pf] ;                                                            \
+                int64_t p = Ap [j], pend = Anz ? p + Anz [j] : Ap [j+1] ;                         \
+                for ( ; p < pend ; p++)                                                           \
+                {                                                                                 \
+                    int64_t i = Ai [p] ;                                                          \
+                    if (i >= k)                                                                   \
+                    {                                                                             \
+                        int64_t im = Map [i] ;                                                    \
+                        if (im >= 0 && im < nsrow) Lx [psx + im + (k-k1)*nsrow] += Ax [p] * fjk ; \
+                    }                                                                             \
+                }                                                                                 \
+            }                                                                                     \
+        }                                                                                         \
         /* scatter the lower part of columns k1..k2-1 of A, SNW:437-468 */                        \
-        for (int64_t k = k1 ; k < k2 ; k++)                                                       \
+        for (int64_t k = k1 ; !Fp && k < k2 ; k++)                                                \
         {                                                                                         \
             int64_t p = Ap [k], pend = Anz ? p + Anz [k] : Ap [k+1] ;                             \
             for ( ; p < pend ; p++)                                                               \

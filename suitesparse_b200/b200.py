@@ -27,7 +27,7 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
            "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer", "b200_super_numeric_z",
-           "b200_super_numeric_c", "b200_solve_z"]
+           "b200_super_numeric_c", "b200_solve_z", "b200_super_numeric_aat", "b200_upload_matrix_aat"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -61,6 +61,9 @@ def lib():
     for fn in (L.b200_super_numeric_z, L.b200_super_numeric_c):
         fn.argtypes = [vp, vp, vp, vp, vp, vp, dbl, cint, vp, vp]; fn.restype = cint
     L.b200_solve_z.argtypes = [vp, vp, vp, i64]; L.b200_solve_z.restype = cint
+    L.b200_super_numeric_aat.argtypes = [vp, i64] + [vp] * 10 + [dbl, cint, vp, vp]
+    L.b200_super_numeric_aat.restype = cint
+    L.b200_upload_matrix_aat.argtypes = [vp, i64] + [vp] * 8; L.b200_upload_matrix_aat.restype = cint
     L.b200_upload_matrix.argtypes = [vp, vp, vp, vp, vp]; L.b200_upload_matrix.restype = cint
     L.b200_factor_device.argtypes = [vp, dbl, cint, vp]; L.b200_factor_device.restype = cint
     L.b200_download_factor.argtypes = [vp, vp]; L.b200_download_factor.restype = cint
@@ -217,6 +220,43 @@ class Factor:
         self.minor = int(minor.value)
         self._pinned_Lx = Lx       # the library page-locked this buffer: keep it alive until close()
         return st, Lx
+
+    def super_numeric_aat(self, ncol, Ap, Ai, Ax, Fp, Fi, Fx, beta=0.0, quick_return=False, Lx=None, Anz=None,
+                          Fnz=None, zomplex=False):
+        """The unsymmetric case of cholmod_super_numeric: factorize A*F + beta*I, A n-by-ncol (row-permuted),
+        F = A^H ncol-by-n.  zomplex=True passes the values of a complex context as split arrays."""
+        Ap, Ai, Fp, Fi = _i64(Ap), _i64(Ai), _i64(Fp), _i64(Fi)
+        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+        Fx = np.ascontiguousarray(Fx, dtype=self.dtype)
+        if Lx is None:
+            Lx = np.empty(self.xsize, dtype=self.dtype)
+        assert Lx.dtype == self.dtype and Lx.size == self.xsize and Lx.flags.c_contiguous
+        keep = [None if a is None else _i64(a) for a in (Anz, Fnz)]
+        ptr = [None if a is None else a.ctypes.data for a in keep]
+        if zomplex:
+            assert self.is_complex
+            parts = [np.ascontiguousarray(v) for v in (Ax.real, Ax.imag, Fx.real, Fx.imag)]
+            ax, az, fx, fz = (v.ctypes.data for v in parts)
+        else:
+            ax, az, fx, fz = Ax.ctypes.data, None, Fx.ctypes.data, None
+        minor = C.c_int64(-1)
+        st = self.L.b200_super_numeric_aat(self.h, int(ncol), Ap.ctypes.data, Ai.ctypes.data, ptr[0], ax, az,
+                                           Fp.ctypes.data, Fi.ctypes.data, ptr[1], fx, fz, float(beta),
+                                           int(quick_return), Lx.ctypes.data, C.byref(minor))
+        if st < 0:
+            raise B200Error(st, "b200_super_numeric_aat")
+        self.minor = int(minor.value)
+        self._pinned_Lx = Lx
+        return st, Lx
+
+    def upload_matrix_aat(self, ncol, Ap, Ai, Ax, Fp, Fi, Fx):
+        Ap, Ai, Fp, Fi = _i64(Ap), _i64(Ai), _i64(Fp), _i64(Fi)
+        Ax = np.ascontiguousarray(Ax, dtype=self.dtype)
+        Fx = np.ascontiguousarray(Fx, dtype=self.dtype)
+        st = self.L.b200_upload_matrix_aat(self.h, int(ncol), Ap.ctypes.data, Ai.ctypes.data, None, Ax.ctypes.data,
+                                           Fp.ctypes.data, Fi.ctypes.data, None, Fx.ctypes.data)
+        if st < 0:
+            raise B200Error(st, "b200_upload_matrix_aat")
 
     # -- the same in three steps ---------------------------------------------------------------------
     def upload_matrix(self, Ap, Ai, Ax, Anz=None):

@@ -113,6 +113,8 @@ struct b200_factor
     DevBuf<unsigned char> d_Lx ;
     DevBuf<int64_t> d_Ap, d_Ai, d_Anz ;
     DevBuf<unsigned char> d_Ax ;
+    DevBuf<int64_t> d_Fp, d_Fi, d_Fnz ;     // F = A(:,f)^H of the unsymmetric case (A*F is factorized)
+    DevBuf<unsigned char> d_Fx ;
     DevBuf<unsigned long long> d_minor ;
     DevBuf<unsigned char> d_winv ;          // scratch: inverses of the diagonal blocks of one launch
     DevBuf<double> d_X ;
@@ -124,7 +126,9 @@ struct b200_factor
     DevBuf<SolveBlk> d_sblk ;
     DevBuf<SolveTile> d_stile ;
     std::vector<unsigned char> h_Ax ;       // zomplex input (Ax, Az) interleaved before the upload
+    std::vector<unsigned char> h_Fx ;
     bool have_A = false, A_unpacked = false ;
+    bool have_F = false, F_unpacked = false ;
     int64_t A_nz = 0 ;
     // host-registered output buffer (pinned once, reused by later factorizations)
     void *reg_ptr = nullptr ; size_t reg_bytes = 0 ;
@@ -405,6 +409,12 @@ int scatter_A (b200_factor *f, int64_t kfirst, int64_t klast, double beta)
 {
     if (klast <= kfirst) return B200_OK ;
     unsigned grid = (unsigned) ((klast - kfirst + 255) / 256) ;
+    if (f->have_F)
+        k_scatter_AF<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
+            f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_Fp.p, f->d_Fi.p,
+            f->F_unpacked ? f->d_Fnz.p : nullptr, reinterpret_cast<const T *> (f->d_Fx.p), f->d_supermap.p,
+            f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
+    else
     k_scatter_A<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
         f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_supermap.p,
         f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
@@ -606,7 +616,8 @@ void b200_destroy (b200_factor *f)
         f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
-        f->d_Ax.release () ; f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
+        f->d_Ax.release () ; f->d_Fp.release () ; f->d_Fi.release () ; f->d_Fnz.release () ; f->d_Fx.release () ;
+        f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
         f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
@@ -741,40 +752,73 @@ int b200_comm_init (b200_factor *f, const void *id128)
     return B200_OK ;
 }
 
+// one CSC matrix (ncols columns) to the device; returns its entry count through *nz_out
+static int upload_csc (b200_factor *f, int64_t ncols, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax, DevBuf<int64_t> &dp, DevBuf<int64_t> &di, DevBuf<int64_t> &dnz, DevBuf<unsigned char> &dx,
+    int64_t *nz_out)
+{
+    if (!Ap || ncols < 0) return B200_INVALID ;
+    // unpacked matrices: entries of column k live at Ap [k] .. Ap [k] + Anz [k]; copy up to max end
+    int64_t nz = Ap [ncols] ;
+    if (Anz) for (int64_t k = 0 ; k < ncols ; k++) nz = (Ap [k] + Anz [k] > nz) ? Ap [k] + Anz [k] : nz ;
+    if (nz < 0 || (nz > 0 && (!Ai || !Ax))) return B200_INVALID ;
+    cudaStream_t s = f->stream ;
+    if (dp.n < (size_t) ncols + 1 && dp.alloc ((size_t) ncols + 1) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (di.n < (size_t) nz && di.alloc ((size_t) nz) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (dx.n < (size_t) nz * f->esize && dx.alloc ((size_t) nz * f->esize) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (Anz && dnz.n < (size_t) ncols && dnz.alloc ((size_t) ncols) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    CK (cudaMemcpyAsync (dp.p, Ap, (size_t) (ncols + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
+    if (nz > 0)
+    {
+        CK (cudaMemcpyAsync (di.p, Ai, (size_t) nz * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ai") ;
+        CK (cudaMemcpyAsync (dx.p, Ax, (size_t) nz * f->esize, cudaMemcpyHostToDevice, s), "H2D Ax") ;
+    }
+    if (Anz && ncols > 0) CK (cudaMemcpyAsync (dnz.p, Anz, (size_t) ncols * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
+    *nz_out = nz ;
+    return B200_OK ;
+}
+
 int b200_upload_matrix (b200_factor *f, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const void *Ax)
 {
     int st = set_device (f) ; if (st) return st ;
-    if (!Ap || (!Ai && f->plan.n > 0)) return B200_INVALID ;
-    const int64_t n = f->plan.n ;
-    // unpacked matrices: entries of column k live at Ap [k] .. Ap [k] + Anz [k]; copy up to max end
-    int64_t nz = Ap [n] ;
-    if (Anz) for (int64_t k = 0 ; k < n ; k++) nz = (Ap [k] + Anz [k] > nz) ? Ap [k] + Anz [k] : nz ;
-    if (nz < 0) return B200_INVALID ;
     cudaStream_t s = f->stream ;
-    if (f->d_Ap.n < (size_t) n + 1 && f->d_Ap.alloc ((size_t) n + 1) != cudaSuccess) return B200_OUT_OF_MEMORY ;
-    if (f->d_Ai.n < (size_t) nz && f->d_Ai.alloc ((size_t) nz) != cudaSuccess) return B200_OUT_OF_MEMORY ;
-    if (f->d_Ax.n < (size_t) nz * f->esize && f->d_Ax.alloc ((size_t) nz * f->esize) != cudaSuccess) return B200_OUT_OF_MEMORY ;
-    if (Anz && f->d_Anz.n < (size_t) n && f->d_Anz.alloc ((size_t) n) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    int64_t nz = 0 ;
     CK (cudaEventRecord (f->ev [0], s), "record") ;
-    CK (cudaMemcpyAsync (f->d_Ap.p, Ap, (size_t) (n + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
-    if (nz > 0)
-    {
-        CK (cudaMemcpyAsync (f->d_Ai.p, Ai, (size_t) nz * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ai") ;
-        CK (cudaMemcpyAsync (f->d_Ax.p, Ax, (size_t) nz * f->esize, cudaMemcpyHostToDevice, s), "H2D Ax") ;
-    }
-    if (Anz && n > 0) CK (cudaMemcpyAsync (f->d_Anz.p, Anz, (size_t) n * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
+    st = upload_csc (f, f->plan.n, Ap, Ai, Anz, Ax, f->d_Ap, f->d_Ai, f->d_Anz, f->d_Ax, &nz) ;
+    if (st) return st ;
     CK (cudaEventRecord (f->ev [1], s), "record") ;
     CK (cudaStreamSynchronize (s), "H2D A") ;
     cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
     f->have_A = true ; f->A_unpacked = (Anz != nullptr) ; f->A_nz = nz ;
+    f->have_F = false ;
+    return B200_OK ;
+}
+
+int b200_upload_matrix_aat (b200_factor *f, int64_t ncol, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax, const int64_t *Fp, const int64_t *Fi, const int64_t *Fnz, const void *Fx)
+{
+    int st = set_device (f) ; if (st) return st ;
+    cudaStream_t s = f->stream ;
+    int64_t nz = 0, fnz = 0 ;
+    f->have_A = false ; f->have_F = false ;
+    CK (cudaEventRecord (f->ev [0], s), "record") ;
+    st = upload_csc (f, ncol, Ap, Ai, Anz, Ax, f->d_Ap, f->d_Ai, f->d_Anz, f->d_Ax, &nz) ;
+    if (st) return st ;
+    st = upload_csc (f, f->plan.n, Fp, Fi, Fnz, Fx, f->d_Fp, f->d_Fi, f->d_Fnz, f->d_Fx, &fnz) ;
+    if (st) return st ;
+    CK (cudaEventRecord (f->ev [1], s), "record") ;
+    CK (cudaStreamSynchronize (s), "H2D A, F") ;
+    cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
+    f->have_A = true ; f->A_unpacked = (Anz != nullptr) ; f->A_nz = nz ;
+    f->have_F = true ; f->F_unpacked = (Fnz != nullptr) ;
     return B200_OK ;
 }
 
 int b200_upload_values (b200_factor *f, const void *Ax)
 {
     int st = set_device (f) ; if (st) return st ;
-    if (!f->have_A) return B200_INVALID ;       // the pattern must have been uploaded once
+    if (!f->have_A || f->have_F) return B200_INVALID ;      // the pattern of a symmetric A must be on the device
     if (f->A_nz == 0) return B200_OK ;
     if (!Ax) return B200_INVALID ;
     CK (cudaEventRecord (f->ev [0], f->stream), "record") ;
@@ -971,6 +1015,48 @@ int b200_super_numeric_c (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
     const float *Ax, const float *Az, double beta, int quick_return_if_not_posdef, float *Lx, int64_t *minor)
 {
     return super_numeric_complex<float> (f, Ap, Ai, Anz, Ax, Az, beta, quick_return_if_not_posdef, Lx, minor) ;
+}
+
+// (re,im) pairs from split real / imaginary arrays of nz entries of the context's precision
+static const void *interleave_zomplex (b200_factor *f, std::vector<unsigned char> &buf, int64_t ncols,
+    const int64_t *Ap, const int64_t *Anz, const void *Ax, const void *Az)
+{
+    if (!Az) return Ax ;
+    if (!Ap || !dtype_complex (f->dtype)) return nullptr ;
+    int64_t nz = Ap [ncols] ;
+    if (Anz) for (int64_t k = 0 ; k < ncols ; k++) nz = (Ap [k] + Anz [k] > nz) ? Ap [k] + Anz [k] : nz ;
+    if (nz < 0 || (nz > 0 && !Ax)) return nullptr ;
+    const size_t rs = f->esize / 2 ;
+    buf.resize ((size_t) nz * f->esize + 1) ;
+    unsigned char *dst = buf.data () ;
+    const unsigned char *re = (const unsigned char *) Ax, *im = (const unsigned char *) Az ;
+    for (int64_t p = 0 ; p < nz ; p++)
+    {
+        memcpy (dst + (size_t) p * 2 * rs, re + (size_t) p * rs, rs) ;
+        memcpy (dst + (size_t) p * 2 * rs + rs, im + (size_t) p * rs, rs) ;
+    }
+    return dst ;
+}
+
+int b200_super_numeric_aat (b200_factor *f, int64_t ncol, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const void *Ax, const void *Az, const int64_t *Fp, const int64_t *Fi, const int64_t *Fnz, const void *Fx,
+    const void *Fz, double beta, int quick_return_if_not_posdef, void *Lx, int64_t *minor)
+{
+    if (!f) return B200_GPU_PROBLEM ;
+    if ((Az != nullptr) != (Fz != nullptr)) return B200_INVALID ;      // A and F have the same xtype (SNUM:151)
+    const void *av, *fv ;
+    try
+    {
+        av = interleave_zomplex (f, f->h_Ax, ncol, Ap, Anz, Ax, Az) ;
+        fv = interleave_zomplex (f, f->h_Fx, f->plan.n, Fp, Fnz, Fx, Fz) ;
+    }
+    catch (const std::bad_alloc &) { return B200_OUT_OF_MEMORY ; }
+    if ((Az && !av) || (Fz && !fv)) return B200_INVALID ;
+    int st = b200_upload_matrix_aat (f, ncol, Ap, Ai, Anz, av, Fp, Fi, Fnz, fv) ;
+    if (st < 0) return st ;
+    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
+    ensure_registered (f, Lx, (size_t) f->plan.xsize * f->esize) ;
+    return B200_DISPATCH (f->dtype, factor_device_T) (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
 }   // extern "C"

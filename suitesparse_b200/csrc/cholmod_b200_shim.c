@@ -14,8 +14,8 @@
 //   cholmod_l_super_numeric         the public entry (cholmod_super_numeric.c:100) re-implemented so that,
 //                                   when this library precedes libcholmod in symbol resolution (link
 //                                   order or LD_PRELOAD), an UNMODIFIED cholmod_l_factorize lands in the
-//                                   B200 numeric phase.  Inputs outside the module's scope (the
-//                                   unsymmetric A*F case, int32) are handed to the next definition of
+//                                   B200 numeric phase.  Inputs outside the module's scope (int32
+//                                   indices, malformed arguments) are handed to the next definition of
 //                                   cholmod_l_super_numeric (the reference's), exactly as the reference's
 //                                   GPU branch only ever covered real/complex double int64.
 //
@@ -184,7 +184,8 @@ int cholmod_l_change_factor (int to_xtype, int to_ll, int to_super, int to_packe
 // the worker entry: same contract as rd_/rs_cholmod_super_numeric_worker for stype < 0
 // ---------------------------------------------------------------------------------------------
 
-static int shim_worker (cholmod_sparse *A, double beta [2], cholmod_factor *L, cholmod_common *Common, int dtype)
+static int shim_worker (cholmod_sparse *A, cholmod_sparse *F, double beta [2], cholmod_factor *L,
+    cholmod_common *Common, int dtype)
 {
     b200_factor *ctx = shim_context (L, dtype, Common) ;
     if (!ctx) return 0 ;
@@ -193,7 +194,15 @@ static int shim_worker (cholmod_sparse *A, double beta [2], cholmod_factor *L, c
     int st ;
     // zomplex A: real parts in A->x, imaginary parts in A->z (L is complex either way)
     const void *Az = (A->xtype == CHOLMOD_ZOMPLEX) ? A->z : NULL ;
-    if (dtype == B200_DOUBLE)
+    if (A->stype == 0)
+    {
+        // the unsymmetric case: A*F is factorized (t_cholmod_super_numeric_worker.c:471-506)
+        const int64_t *Fnz = F->packed ? NULL : (const int64_t *) F->nz ;
+        st = b200_super_numeric_aat (ctx, (int64_t) A->ncol, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
+            A->x, Az, (const int64_t *) F->p, (const int64_t *) F->i, Fnz, F->x,
+            (F->xtype == CHOLMOD_ZOMPLEX) ? F->z : NULL, beta [0], Common->quick_return_if_not_posdef, L->x, &minor) ;
+    }
+    else if (dtype == B200_DOUBLE)
         st = b200_super_numeric_d (ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
             (const double *) A->x, beta [0], Common->quick_return_if_not_posdef, (double *) L->x, &minor) ;
     else if (dtype == B200_SINGLE)
@@ -221,44 +230,38 @@ static int shim_worker (cholmod_sparse *A, double beta [2], cholmod_factor *L, c
 int rd_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_DOUBLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_DOUBLE) ;
 }
 
 int rs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_SINGLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_SINGLE) ;
 }
 
 // cd_/zd_ (complex double L; A complex or zomplex) and cs_/zs_ (complex single)
 int cd_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_COMPLEX_DOUBLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_COMPLEX_DOUBLE) ;
 }
 
 int zd_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_COMPLEX_DOUBLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_COMPLEX_DOUBLE) ;
 }
 
 int cs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_COMPLEX_SINGLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_COMPLEX_SINGLE) ;
 }
 
 int zs_cholmod_l_b200_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [2],
     cholmod_factor *L, cholmod_common *Common)
 {
-    (void) F ;
-    return shim_worker (A, beta, L, Common, B200_COMPLEX_SINGLE) ;
+    return shim_worker (A, F, beta, L, Common, B200_COMPLEX_SINGLE) ;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -276,13 +279,16 @@ int cholmod_l_super_numeric (cholmod_sparse *A, cholmod_sparse *F, double beta [
     // libcholmod the environment variable is the switch.
     const char *env = getenv ("CHOLMOD_USE_GPU") ;
     int want = Common && (Common->useGPU == 1 || (env && atoi (env) == 1)) ;
-    // scope of the module: int64, symmetric / Hermitian with the lower triangle stored, real, complex or
-    // zomplex, double or single (the type checks are the reference's, cholmod_super_numeric.c:166-180)
+    // scope of the module: int64; symmetric / Hermitian with the lower triangle stored, or unsymmetric with
+    // F = A^H given; real, complex or zomplex; double or single (the argument checks are the reference's,
+    // cholmod_super_numeric.c:127-180; anything they would reject is left for the reference to reject)
     int cplx = A && (A->xtype == CHOLMOD_COMPLEX || A->xtype == CHOLMOD_ZOMPLEX) ;
-    int ours = want && A && L && L->is_super && A->stype < 0 && (A->xtype == CHOLMOD_REAL || cplx)
+    int shape = A && L && ((A->stype < 0 && A->nrow == A->ncol && A->nrow == L->n)
+        || (A->stype == 0 && A->nrow == L->n && F && F->stype == 0 && F->nrow == A->ncol && F->ncol == A->nrow
+            && F->xtype == A->xtype && F->dtype == A->dtype && F->itype == CHOLMOD_LONG)) ;
+    int ours = want && shape && L->is_super && (A->xtype == CHOLMOD_REAL || cplx)
         && A->itype == CHOLMOD_LONG && L->itype == CHOLMOD_LONG
-        && (L->xtype == CHOLMOD_PATTERN || L->xtype == (cplx ? CHOLMOD_COMPLEX : CHOLMOD_REAL))
-        && A->nrow == A->ncol && A->nrow == L->n ;
+        && (L->xtype == CHOLMOD_PATTERN || L->xtype == (cplx ? CHOLMOD_COMPLEX : CHOLMOD_REAL)) ;
     if (!ours)
     {
         super_numeric_fn next = (super_numeric_fn) dlsym (RTLD_NEXT, "cholmod_l_super_numeric") ;

@@ -143,6 +143,57 @@ __global__ void __launch_bounds__ (256) k_scatter_A (int64_t kfirst, int64_t kla
     if (beta != (typename num<T>::real) 0) col [k - k1] += from_real<T> (beta) ;
 }
 
+// The unsymmetric case (A->stype == 0, SNW:471-506): the matrix to factorize is A*F with F = A(:,f)^H given
+// explicitly (both already row-permuted by the caller, cholmod_factorize.c:236-247).  One thread per column k
+// of L forms column k of A*F restricted to the pattern of L:
+//     L (i,k) += A (i,j) * F (j,k)   for every j in the pattern of F (:,k), every i >= k in A (:,j)
+// The thread owns its column, so the sums need no atomics.  A is nrow-by-ncol, F ncol-by-nrow.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_scatter_AF (int64_t kfirst, int64_t klast,
+    const int64_t *__restrict__ Ap, const int64_t *__restrict__ Ai, const int64_t *__restrict__ Anz,
+    const T *__restrict__ Ax, const int64_t *__restrict__ Fp, const int64_t *__restrict__ Fi,
+    const int64_t *__restrict__ Fnz, const T *__restrict__ Fx, const int32_t *__restrict__ supermap,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, typename num<T>::real beta, T *__restrict__ Lx)
+{
+    int64_t k = kfirst + (int64_t) blockIdx.x * blockDim.x + threadIdx.x ;
+    if (k >= klast) return ;
+    int32_t s = supermap [k] ;
+    int64_t k1 = super [s], k2 = super [s+1], psi = pi [s] ;
+    int64_t nsrow = pi [s+1] - psi, nscol = k2 - k1 ;
+    T *col = Lx + px [s] + (k - k1) * nsrow ;
+    int64_t pf = Fp [k], pfend = Fnz ? pf + Fnz [k] : Fp [k+1] ;
+    for ( ; pf < pfend ; pf++)
+    {
+        const int64_t j = Fi [pf] ;
+        const T fjk = Fx [pf] ;
+        int64_t p = Ap [j], pend = Anz ? p + Anz [j] : Ap [j+1] ;
+        for ( ; p < pend ; p++)
+        {
+            int64_t i = Ai [p] ;
+            if (i < k) continue ;
+            int64_t pos ;
+            if (i < k2)
+            {
+                pos = i - k1 ;
+            }
+            else
+            {
+                int64_t lo = nscol, hi = nsrow ;
+                while (lo < hi)
+                {
+                    int64_t mid = (lo + hi) >> 1 ;
+                    if ((int64_t) Ls [psi + mid] < i) lo = mid + 1 ; else hi = mid ;
+                }
+                if (lo >= nsrow || (int64_t) Ls [psi + lo] != i) continue ;
+                pos = lo ;
+            }
+            col [pos] += Ax [p] * fjk ;
+        }
+    }
+    if (beta != (typename num<T>::real) 0) col [k - k1] += from_real<T> (beta) ;
+}
+
 // ---------------------------------------------------------------------------------------------
 // small updates: one warp per 32 x 8 tile, operands straight from L1/L2
 // ---------------------------------------------------------------------------------------------

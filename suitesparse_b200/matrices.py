@@ -107,6 +107,32 @@ def hermitian(n, Ap, Ai, Ax):
     return n, Ap, Ai, z.astype(np.complex128)
 
 
+def aat2d(nx, ny=None, complex_phases=False):
+    """An unsymmetric (CHOLMOD stype 0) test matrix for the A*A' case: A = [D | E], n = nx*ny rows, one column
+    per grid node (D = 0.5 I) and one per grid edge (E = the edge-node incidence matrix, +1 / -1), so that
+    A*A' = 0.25 I + the 5-point graph Laplacian.  With complex_phases the edge entries get deterministic
+    phases and A*A^H is Hermitian positive definite.  Returns (nrow, ncol, Ap, Ai, Ax), CSC, sorted."""
+    ny = nx if ny is None else ny
+    n = nx * ny
+    x, y = np.meshgrid(np.arange(nx), np.arange(ny), indexing="ij")
+    node = (x + nx * y).ravel()
+    xr, yr = x.ravel(), y.ravel()
+    rows, cols, vals = [node], [node], [np.full(n, 0.5)]
+    ncol = n
+    for dx, dy in ((1, 0), (0, 1)):
+        ok = (xr + dx < nx) & (yr + dy < ny)
+        a, b = node[ok], (xr[ok] + dx) + nx * (yr[ok] + dy)
+        e = ncol + np.arange(a.size)
+        rows += [a, b]; cols += [e, e]; vals += [np.full(a.size, 1.0), np.full(a.size, -1.0)]
+        ncol += a.size
+    rows, cols, vals = np.concatenate(rows), np.concatenate(cols), np.concatenate(vals)
+    if complex_phases:
+        vals = vals * np.exp(1j * (0.29 * ((5 * rows + 3 * cols) % 13) + 0.05))
+    A = sp.coo_matrix((vals, (rows, cols)), shape=(n, ncol)).tocsc()
+    A.sort_indices()
+    return n, ncol, A.indptr.astype(np.int64), A.indices.astype(np.int64), A.data
+
+
 def rhs(n):
     """The demo's right-hand side b_i = 1 + i/n (CHOLMOD/Demo/cholmod_dl_demo.c:243-249)."""
     return 1.0 + np.arange(n, dtype=np.float64) / n

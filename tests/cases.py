@@ -56,6 +56,33 @@ class Case:
         return self.ref.resid(x, b)
 
 
+class CaseAAT:
+    """The unsymmetric case: reference analysis of A*A^H, the seam pair S = A(p,:), F = S^H, and the
+    reference CPU factor of S*F + beta*I."""
+
+    def __init__(self, size, ordering, single=False, cplx=False, zomplex=False, beta=0.0, factor=True):
+        self.nrow, self.ncol, self.Ap, self.Ai, self.Ax = M.aat2d(size, complex_phases=cplx)
+        self.n, self.beta = self.nrow, beta
+        self.ref = refd.Ref()
+        self.ref.set_matrix_rect(self.nrow, self.ncol, self.Ap, self.Ai, self.Ax, single=single, zomplex=zomplex)
+        self.ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
+        self.sym = self.ref.symbolic()
+        self.Sp, self.Si, self.Sx = self.ref.seam()
+        self.Fp, self.Fi, self.Fx = self.ref.seam_F()
+        if factor:
+            self.status = self.ref.super_numeric(beta)
+            self.Lref = self.ref.Lx().copy()
+            self.minor = self.ref.geti("minor")
+
+    rel_err = Case.rel_err
+
+    def dense_product(self):
+        """A*A^H + beta*I as a dense array (small cases only)."""
+        import scipy.sparse as sp
+        A = sp.csc_matrix((self.Ax, self.Ai, self.Ap), shape=(self.nrow, self.ncol))
+        return (A @ A.conj().T).toarray() + self.beta * np.eye(self.nrow)
+
+
 @functools.lru_cache(maxsize=None)
 def get_case(kind, size, ordering, single=False, shift_diag=None, beta=0.0, hermitian=False, zomplex=False):
     return Case(kind, size, ordering, single=single, shift_diag=shift_diag, beta=beta, hermitian=hermitian,

@@ -11,8 +11,9 @@ from numpy.lib.stride_tricks import as_strided
 from suitesparse_b200 import b200
 
 
-def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None):
-    """What k_scatter_A does (Lx already zero on the touched supernodes)."""
+def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None, F=None):
+    """What k_scatter_A does (Lx already zero on the touched supernodes); with F = (Fp, Fi, Fx) what
+    k_scatter_AF does: column k of S*F, gathered entry by entry."""
     n = sym["n"]
     klast = n if klast is None else klast
     sup, pi, px, Ls = sym["super"], sym["pi"], sym["px"], sym["s"]
@@ -23,8 +24,13 @@ def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None):
         nsrow = pi[s + 1] - pi[s]
         rows = Ls[pi[s]:pi[s + 1]]
         base = px[s] + (k - k1) * nsrow
-        for p in range(Sp[k], Sp[k + 1]):
-            i = Si[p]
+        if F is None:
+            entries = [(Si[p], Sx[p], False) for p in range(Sp[k], Sp[k + 1])]
+        else:
+            Fp, Fi, Fx = F
+            entries = [(Si[p], Sx[p] * Fx[pf], True) for pf in range(Fp[k], Fp[k + 1])
+                       for p in range(Sp[Fi[pf]], Sp[Fi[pf] + 1])]
+        for i, v, add in entries:
             if i < k:
                 continue
             if i < k2:
@@ -33,7 +39,7 @@ def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None):
                 pos = np.searchsorted(rows, i)
                 if pos >= nsrow or rows[pos] != i:
                     continue
-            Lx[base + pos] = Sx[p]
+            Lx[base + pos] = Lx[base + pos] + v if add else v
         if beta != 0:
             Lx[base + (k - k1)] += beta
 

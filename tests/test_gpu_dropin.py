@@ -45,6 +45,16 @@ for use_gpu in (0, 1):
     bz = M.rhs(nz_) * (1 + 0.5j)
     out[use_gpu]["z_resid"] = r3.resid(r3.solve(bz), bz)
     out[use_gpu]["z_Lx"] = r3.Lx().copy()
+    # unsymmetric A (stype 0): cholmod_l_factorize_p builds F = A(p,:)' itself and factorizes A*A' + beta*I
+    nr, nc, Rp, Ri, Rx = M.aat2d(30)
+    r4 = refd.Ref(); r4.seti("useGPU", use_gpu); r4.set_matrix_rect(nr, nc, Rp, Ri, Rx)
+    r4.analyze(refd.CHOLMOD_AMD, refd.CHOLMOD_SUPERNODAL)
+    out[use_gpu]["u_status"] = r4.factorize(0.5)
+    out[use_gpu]["u_Lx"] = r4.Lx().copy()
+    xu = r4.solve(M.rhs(nr))
+    import scipy.sparse as sp
+    Au = sp.csc_matrix((Rx, Ri, Rp), shape=(nr, nc))
+    out[use_gpu]["u_resid"] = float(np.max(np.abs(Au @ (Au.T @ xu) + 0.5 * xu - M.rhs(nr))))
 import ctypes
 shim = ctypes.CDLL(%(shim)r)
 res = dict(
@@ -58,6 +68,9 @@ res = dict(
     z_status=[out[0]["z_status"], out[1]["z_status"]], z_resid=[out[0]["z_resid"], out[1]["z_resid"]],
     z_err=float(np.max(np.abs(out[0]["z_Lx"] - out[1]["z_Lx"])) / np.max(np.abs(out[0]["z_Lx"]))),
     z_identical=bool(np.array_equal(out[0]["z_Lx"], out[1]["z_Lx"])), z_dtype=str(out[1]["z_Lx"].dtype),
+    u_status=[out[0]["u_status"], out[1]["u_status"]], u_resid=[out[0]["u_resid"], out[1]["u_resid"]],
+    u_err=float(np.max(np.abs(out[0]["u_Lx"] - out[1]["u_Lx"])) / np.max(np.abs(out[0]["u_Lx"]))),
+    u_identical=bool(np.array_equal(out[0]["u_Lx"], out[1]["u_Lx"])),
     dealloc=int(shim.cholmod_l_b200_deallocate(None)))
 print("RESULT " + json.dumps(res))
 """
@@ -82,4 +95,7 @@ def test_unmodified_cholmod_factorize_runs_on_the_gpu():
     # the Hermitian (zomplex in, complex out) factorization went through the same door
     assert res["z_status"] == [0, 0] and res["z_dtype"] == "complex128"
     assert res["z_err"] <= 1e-10 and res["z_resid"][1] <= 1e-12 and not res["z_identical"]
+    # and so did the unsymmetric A*A' factorization
+    assert res["u_status"] == [0, 0] and res["u_err"] <= 1e-10 and res["u_resid"][1] <= 1e-10
+    assert not res["u_identical"]
     assert res["dealloc"] == 1

@@ -8,7 +8,7 @@ import pytest
 
 from oracle import refd
 from suitesparse_b200 import matrices as M
-from cases import Case, get_case
+from cases import Case, CaseAAT, get_case
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 needs_ref = pytest.mark.skipif(not refd.have_ref(), reason="oracle/_ref/libref_driver.so not built")
@@ -63,6 +63,37 @@ def test_port_hermitian(zomplex, single):
         xx = np.empty(c.n, dtype=np.complex128); xx[c.sym["Perm"]] = x
         xr = c.ref.solve(b)
         assert np.max(np.abs(xx - xr)) <= 1e-12 * np.max(np.abs(xr))
+
+
+@needs_ref
+@pytest.mark.parametrize("cplx,zomplex,single,beta", [(False, False, False, 0.0), (False, False, True, 0.25),
+                                                      (True, False, False, 0.5), (True, True, False, 0.0)])
+def test_port_unsymmetric_aat(cplx, zomplex, single, beta):
+    """A->stype == 0: S*F + beta*I is factorized, F = S^H given explicitly (SNW:471-506)."""
+    c = CaseAAT(12, refd.CHOLMOD_AMD, single=single, cplx=cplx, zomplex=zomplex, beta=beta)
+    assert c.status == refd.CHOLMOD_OK and c.minor == c.n
+    st, minor, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx, beta=beta, F=(c.Fp, c.Fi, c.Fx))
+    assert st == 0 and minor == c.n and Lp.dtype == c.Lref.dtype
+    assert c.rel_err(Lp) <= (1e-5 if single else 1e-13)
+    if not single:
+        # L L^H really is P (A A^H + beta I) P': solve through the port and check against the dense product
+        b = M.rhs(c.n) * ((1 + 0.5j) if cplx else 1.0)
+        perm = c.sym["Perm"]
+        x = refd.port_solve(c.sym, Lp, b[perm])
+        xx = np.empty_like(x); xx[perm] = x
+        assert np.max(np.abs(c.dense_product() @ xx - b)) <= 1e-11 * np.max(np.abs(b))
+
+
+@needs_ref
+def test_port_unsymmetric_not_posdef():
+    c = CaseAAT(10, refd.CHOLMOD_AMD, beta=-0.3, factor=False)      # A A' + beta I is indefinite
+    c.ref.super_numeric(-0.3)
+    assert c.ref.geti("status") == refd.CHOLMOD_NOT_POSDEF
+    Lref, minor_ref = c.ref.Lx().copy(), c.ref.geti("minor")
+    st, minor, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx, beta=-0.3, F=(c.Fp, c.Fi, c.Fx))
+    assert st == 1 and minor == minor_ref
+    assert np.array_equal(Lp == 0, Lref == 0)
+    assert np.max(np.abs(Lp - Lref)) <= 1e-12 * max(1.0, np.max(np.abs(Lref)))
 
 
 @needs_ref

@@ -10,7 +10,7 @@ import pytest
 
 from oracle import refd
 from suitesparse_b200 import b200
-from cases import Case, get_case
+from cases import Case, CaseAAT, get_case
 import plan_interp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -83,6 +83,19 @@ def test_plan_reproduces_reference_factor_hermitian(kind, size, ordering, dtype)
     launches = F.plan_table("launches", b200.LAUNCH_DT)
     has_inv = np.isin(launches["kind"], (b200.K_TRSM_INV32, b200.K_TRSM_INV64)).any()
     assert has_inv == (not single) or not np.isin(launches["kind"], b200.K_TRSM_KINDS).any()
+
+
+@needs_ref
+@pytest.mark.parametrize("cplx", [False, True])
+def test_plan_unsymmetric_aat(cplx):
+    """stype 0: only the scatter differs (column k of S*F instead of column k of S); the plan is the same."""
+    c = CaseAAT(14, refd.CHOLMOD_AMD, cplx=cplx, beta=0.125)
+    dtype = np.complex128 if cplx else np.float64
+    F = b200.Factor(c.sym, dtype=dtype, device=-1)
+    Lx = np.zeros(c.sym["xsize"], dtype=dtype)
+    plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.125, Lx, F=(c.Fp, c.Fi, c.Fx))
+    assert plan_interp.run_plan(F, Lx) is None
+    assert c.rel_err(Lx) <= 1e-12
 
 
 def test_plan_structure():
