@@ -224,7 +224,9 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
 /* Set an integer option by name.  "profile" = 1 brackets every kernel launch of the next factorizations
  * with CUDA events and accumulates device time per kernel kind ("ms_kind0".."ms_kind4" in
  * b200_get_double; kinds: 0 SIMT update, 1 DMMA 64x64 update, 2 DMMA 128x128 update, 3 POTRF, 4 TRSM;
- * "flops_kind<k>" are the algorithmic flops of each kind).  Profiling serialises nothing but adds
+ * "flops_kind<k>" are the algorithmic flops of each kind; "ms_launch<i>" / "ms_launch_start<i>" are the
+ * duration and start time of launch i of the plan, in the order of the "launches" table of
+ * b200_plan_export).  Profiling serialises nothing but adds
  * event overhead: never time a benchmark step with it on. */
 int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 

@@ -117,9 +117,12 @@ struct b200_factor
     DevBuf<unsigned char> d_Fx ;
     DevBuf<unsigned long long> d_minor ;
     DevBuf<unsigned char> d_winv ;          // scratch: inverses of the diagonal blocks of one launch
-    DevBuf<double> d_X ;
+    DevBuf<double> d_X, d_Y ;               // solve: right-hand sides / forward results of the wide supernodes
+    DevBuf<unsigned char> d_solveW ;        // solve: inverses of the 64 x 64 diagonal blocks of the wide supernodes
+    DevBuf<int> d_solve_cnt ;               // solve: finished-tile counters (block x rhs), zero between solves
+    bool solve_w_valid = false ;            // d_solveW belongs to the factor values now in d_Lx
     // solve schedule (built at the first solve)
-    struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;  // kind 0: one CTA per supernode, 1: diag, 2: gemv
+    struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;  // kind 0: one CTA per supernode, 2: block step of the wide ones
     std::vector<SolveLaunch> solve_launches ;
     bool solve_ready = false ;
     DevBuf<int32_t> d_ssmall ;
@@ -140,6 +143,7 @@ struct b200_factor
     double ms_kind [K_NKINDS] = {} ;
     int64_t launches_kind [K_NKINDS] = {} ;
     float ms_level_end [64] = {} ;          // profile mode: end time of each etree level on the device timeline
+    std::vector<float> ms_launch, ms_launch_start ;     // profile mode: duration / start time of every plan launch
     float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
     size_t device_bytes = 0 ;
 } ;
@@ -220,14 +224,10 @@ int kernel_attrs (int device)
     CK (cudaFuncSetAttribute (k_solve_bwd<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
     CK (cudaFuncSetAttribute (k_solve_fwd<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr fwd") ;
     CK (cudaFuncSetAttribute (k_solve_bwd<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), "attr bwd") ;
-    CK (cudaFuncSetAttribute (k_solve_diag<zdouble, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int) solve_diag_smem_bytes<zdouble> ()), "attr diag") ;
-    CK (cudaFuncSetAttribute (k_solve_diag<zdouble, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int) solve_diag_smem_bytes<zdouble> ()), "attr diag") ;
-    CK (cudaFuncSetAttribute (k_solve_diag<cfloat, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int) solve_diag_smem_bytes<cfloat> ()), "attr diag") ;
-    CK (cudaFuncSetAttribute (k_solve_diag<cfloat, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int) solve_diag_smem_bytes<cfloat> ()), "attr diag") ;
+    CK (cudaFuncSetAttribute (k_solve_inv<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<double> ()), "attr inv") ;
+    CK (cudaFuncSetAttribute (k_solve_inv<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<float> ()), "attr inv") ;
+    CK (cudaFuncSetAttribute (k_solve_inv<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<zdouble> ()), "attr inv") ;
+    CK (cudaFuncSetAttribute (k_solve_inv<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<cfloat> ()), "attr inv") ;
     if (device < 64) g_attr_done [device] = true ;
     return B200_OK ;
 }
@@ -383,12 +383,17 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         CK (cudaStreamSynchronize (f->stream), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream2), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream4), "profile sync") ;
-        size_t e = 0 ;
+        size_t e = 0, li = 0 ;
+        f->ms_launch.assign (P.launches.size (), 0.f) ;
+        f->ms_launch_start.assign (P.launches.size (), 0.f) ;
         for (const Launch &L : P.launches)
         {
+            const size_t idx = li++ ;
             if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.kind == K_BCAST || L.count <= 0) continue ;
             float ms = 0 ;
             cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
+            f->ms_launch [idx] = ms ;
+            cudaEventElapsedTime (&f->ms_launch_start [idx], f->prof_ev [0], f->prof_ev [e]) ;
             e += 2 ;
             f->ms_kind [L.kind] += ms ;
             f->launches_kind [L.kind]++ ;
@@ -617,7 +622,8 @@ void b200_destroy (b200_factor *f)
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
         f->d_Ax.release () ; f->d_Fp.release () ; f->d_Fi.release () ; f->d_Fnz.release () ; f->d_Fx.release () ;
-        f->d_minor.release () ; f->d_X.release () ; f->d_winv.release () ;
+        f->d_minor.release () ; f->d_X.release () ; f->d_Y.release () ; f->d_solveW.release () ; f->d_solve_cnt.release () ;
+        f->d_winv.release () ;
         f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
@@ -688,6 +694,8 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "ms_launch_start", 15)) { size_t k = (size_t) atoll (name + 15) ; return k < f->ms_launch_start.size () ? f->ms_launch_start [k] : -1 ; }
+    if (!strncmp (name, "ms_launch", 9)) { size_t k = (size_t) atoll (name + 9) ; return k < f->ms_launch.size () ? f->ms_launch [k] : -1 ; }
     if (!strncmp (name, "ms_level_end", 12)) { int k = atoi (name + 12) ; return (k >= 0 && k < 64) ? f->ms_level_end [k] : -1 ; }
     if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.flops_kind [name [10] - '0'] ;
     return -1 ;
@@ -854,6 +862,7 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     struct Reset { b200_factor *f ; ~Reset () { f->copy_dst = nullptr ; } } reset { f } ;
     const unsigned long long big = ~0ull ;
     f->kernel_launches = 0 ; f->nccl_calls = 0 ;
+    f->solve_w_valid = false ;              // the solve's block inverses belong to the previous factor
     for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
     for (int k = 0 ; k < 64 ; k++) f->ms_level_end [k] = 0 ;
     CK (cudaEventRecord (f->ev [2], s), "record") ;
@@ -928,6 +937,7 @@ int b200_upload_factor (b200_factor *f, const void *Lx)
     size_t bytes = (size_t) f->plan.xsize * f->esize ;
     if (bytes == 0) return B200_OK ;
     if (!Lx) return B200_INVALID ;
+    f->solve_w_valid = false ;
     CK (cudaMemcpyAsync (f->d_Lx.p, Lx, bytes, cudaMemcpyHostToDevice, f->stream), "H2D Lx") ;
     CK (cudaStreamSynchronize (f->stream), "H2D Lx") ;
     return B200_OK ;
@@ -1070,12 +1080,13 @@ static int solve_T (b200_factor *f, int nrhs)
     const int64_t cap = (200 * 1024) / (int64_t) sizeof (XT) ;
     const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
     XT *X = reinterpret_cast<XT *> (f->d_X.p) ;
+    XT *Y = reinterpret_cast<XT *> (f->d_Y.p) ;
     if (!f->solve_ready)
     {
         // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_BIG columns
         // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
-        // over the level: diagonal block (k_solve_diag), then the rows below it spread over 256-row tiles
-        // (k_solve_gemv).  The backward sweep is the same list read in reverse with the transposed kernels.
+        // over the level, one launch per step: the rows below the diagonal block spread over 256-row tiles
+        // (k_solve_fwd_blk).  The backward sweep is the same list read in reverse (k_solve_bwd_blk).
         constexpr int64_t SOLVE_BIG = 256, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
         std::vector<int32_t> small ;
         std::vector<SolveBlk> blks ;
@@ -1097,26 +1108,48 @@ static int solve_T (b200_factor *f, int nrhs)
             if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
             for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
             {
-                const size_t b0 = blks.size (), t0 = tiles.size () ;
+                const size_t t0 = tiles.size () ;
                 for (int32_t sn : big)
                 {
                     const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
                     if (nscol <= c0) continue ;
                     const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
+                    const int32_t blk = (int32_t) blks.size () ;
                     blks.push_back ({ sn, (int32_t) c0, jb, 0 }) ;
+                    const size_t tb = tiles.size () ;
                     for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
-                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, 0 }) ;
+                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
+                    // a block with nothing below it still needs its diagonal solve
+                    if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
+                    tiles [tb].writer = 1 ;
+                    for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
                 }
-                f->solve_launches.push_back ({ 1, (int64_t) b0, (int64_t) (blks.size () - b0), 0 }) ;
-                if (tiles.size () > t0) f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
+                f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
             }
         }
         bool ok = f->d_ssmall.upload (small, s) == cudaSuccess ;
         ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
         ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
+        ok = ok && f->d_solveW.alloc (blks.size () * (size_t) (SOLVE_WLD * SOLVE_WLD) * sizeof (XT)) == cudaSuccess ;
         if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
         CK (cudaStreamSynchronize (s), "solve plan upload") ;
         f->solve_ready = true ;
+        f->solve_w_valid = false ;
+    }
+    const size_t nblk = f->d_sblk.n ;
+    XT *Winv = reinterpret_cast<XT *> (f->d_solveW.p) ;
+    if (nblk > 0)
+    {
+        if (!f->solve_w_valid)
+        {
+            k_solve_inv<T><<<(unsigned) nblk, 256, solve_inv_smem_bytes<T> (), s>>> (f->d_sblk.p, f->d_pi.p, f->d_px.p, Lx, Winv) ;
+            f->solve_w_valid = true ;
+        }
+        if (f->d_solve_cnt.n < nblk * (size_t) nrhs)
+        {
+            if (f->d_solve_cnt.alloc (nblk * (size_t) nrhs) != cudaSuccess) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
+            CK (cudaMemsetAsync (f->d_solve_cnt.p, 0, f->d_solve_cnt.bytes (), s), "solve counters") ;
+        }
     }
     const size_t nl = f->solve_launches.size () ;
     for (size_t pass = 0 ; pass < 2 ; pass++)
@@ -1136,23 +1169,14 @@ static int solve_T (b200_factor *f, int nrhs)
                     k_solve_bwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, X, P.n, nrhs, cap) ;
             }
-            else if (L.kind == 1)
-            {
-                if (pass == 0)
-                    k_solve_diag<T, false><<<grid, 64, solve_diag_smem_bytes<T> (), s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        Lx, X, P.n, nrhs) ;
-                else
-                    k_solve_diag<T, true><<<grid, 64, solve_diag_smem_bytes<T> (), s>>> (f->d_sblk.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        Lx, X, P.n, nrhs) ;
-            }
             else
             {
                 if (pass == 0)
-                    k_solve_gemv<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, X, P.n, nrhs) ;
+                    k_solve_fwd_blk<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, Winv, X, Y, P.n, nrhs) ;
                 else
-                    k_solve_gemvt<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, X, P.n, nrhs) ;
+                    k_solve_bwd_blk<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
             }
         }
     }
@@ -1171,6 +1195,7 @@ static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs,
     if (n == 0 || nrhs == 0) return B200_OK ;
     size_t cnt = (size_t) n * (size_t) nrhs * (want_complex ? 2 : 1) ;      // doubles
     if (f->d_X.n < cnt && f->d_X.alloc (cnt) != cudaSuccess) return B200_OUT_OF_MEMORY ;
+    if (f->d_Y.n < cnt && f->d_Y.alloc (cnt) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     cudaStream_t s = f->stream ;
     CK (cudaMemcpyAsync (f->d_X.p, B, cnt * 8, cudaMemcpyHostToDevice, s), "H2D B") ;
     CK (cudaEventRecord (f->ev [0], s), "record") ;

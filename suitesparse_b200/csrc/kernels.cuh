@@ -975,6 +975,64 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
     }
 }
 
+// W = L^{-1} of a (padded) 64 x 64 lower triangular block held in shared memory, by a CTA of 256 threads:
+// s [c * PB_LD + r] = L (r,c), rsq [r] = 1 / L (r,r), result w [r * PB_LD + c] = W (r,c), tmp = 32 x 33 scratch.
+template <typename T>
+__device__ __forceinline__ void inv64_lower (const T *s, T *w, const T *rsq, T *tmp)
+{
+    const T one = from_real<T> (1), zero = from_real<T> (0) ;
+    // W = L^{-1} of the (padded) 64 x 64 block, block-recursively, so that the serial chain is 16 rows
+    // instead of 64:  (A) the four 16 x 16 diagonal blocks are inverted side by side, row by row --
+    // W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr), column c owned by the 4
+    // consecutive lanes 4c..4c+3 which split the sum;  (B), (C) the off-diagonal blocks follow from
+    // W21 = -W22 * L21 * W11, first for the two 16-blocks inside each 32-block, then for the 32-block.
+    {
+        const int c = threadIdx.x >> 2, part = threadIdx.x & 3 ;
+        const int b0 = c & ~15 ;
+        for (int rl = 0 ; rl < 16 ; rl++)
+        {
+            const int rr = b0 + rl ;
+            T acc = zero ;
+            for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
+            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? one : zero) - acc) * real_ (rsq [rr]) ;
+            __syncwarp () ;
+        }
+    }
+    __syncthreads () ;
+    #pragma unroll 1
+    for (int pass = 0 ; pass < 2 ; pass++)
+    {
+        const int nb = pass ? 32 : 16 ;
+        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31)
+        // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
+        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        {
+            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
+            const int i = el % nb, j = el / nb ;
+            if (j >= nb) continue ;
+            const int c0 = half * 32, r0 = c0 + nb ;
+            T acc = zero ;
+            for (int k = j ; k < nb ; k++) acc += s [(c0 + k) * PB_LD + r0 + i] * w [(c0 + k) * PB_LD + c0 + j] ;
+            tmp [(half * 16 + i) * 33 + j] = acc ;
+        }
+        __syncthreads () ;
+        // step 2: W (r0+i, c0+j) = - sum_{k <= i} W (r0+i, r0+k) tmp (k,j)
+        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        {
+            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
+            const int i = el % nb, j = el / nb ;
+            if (j >= nb) continue ;
+            const int c0 = half * 32, r0 = c0 + nb ;
+            T acc = zero ;
+            for (int k = 0 ; k <= i ; k++) acc += w [(r0 + i) * PB_LD + r0 + k] * tmp [(half * 16 + k) * 33 + j] ;
+            w [(r0 + i) * PB_LD + c0 + j] = -acc ;
+        }
+        __syncthreads () ;
+    }
+}
+
 template <typename T> constexpr size_t potrf_smem_bytes ()
 {
     return (size_t) (2 * POTRF_NB * PB_LD + 2 * (4 * POTRF_NB + 4) + 3 * POTRF_NB + 32 * 33) * sizeof (T) ;
@@ -1114,57 +1172,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     }
     if (b.slot < 0) return ;
     __syncthreads () ;
-    // W = L^{-1} of the (padded) 64 x 64 block, block-recursively, so that the serial chain is 16 rows
-    // instead of 64:  (A) the four 16 x 16 diagonal blocks are inverted side by side, row by row --
-    // W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr), column c owned by the 4
-    // consecutive lanes 4c..4c+3 which split the sum;  (B), (C) the off-diagonal blocks follow from
-    // W21 = -W22 * L21 * W11, first for the two 16-blocks inside each 32-block, then for the 32-block.
-    {
-        const int c = threadIdx.x >> 2, part = threadIdx.x & 3 ;
-        const int b0 = c & ~15 ;
-        for (int rl = 0 ; rl < 16 ; rl++)
-        {
-            const int rr = b0 + rl ;
-            T acc = zero ;
-            for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
-            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? one : zero) - acc) * real_ (rsq [rr]) ;
-            __syncwarp () ;
-        }
-    }
-    __syncthreads () ;
-    T *tmp = rsq + POTRF_NB ;                   // [32][33] scratch of the off-diagonal products
-    #pragma unroll 1
-    for (int pass = 0 ; pass < 2 ; pass++)
-    {
-        const int nb = pass ? 32 : 16 ;
-        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31)
-        // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
-        for (int e = threadIdx.x ; e < 1024 ; e += 256)
-        {
-            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
-            const int i = el % nb, j = el / nb ;
-            if (j >= nb) continue ;
-            const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = zero ;
-            for (int k = j ; k < nb ; k++) acc += s [(c0 + k) * PB_LD + r0 + i] * w [(c0 + k) * PB_LD + c0 + j] ;
-            tmp [(half * 16 + i) * 33 + j] = acc ;
-        }
-        __syncthreads () ;
-        // step 2: W (r0+i, c0+j) = - sum_{k <= i} W (r0+i, r0+k) tmp (k,j)
-        for (int e = threadIdx.x ; e < 1024 ; e += 256)
-        {
-            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
-            const int i = el % nb, j = el / nb ;
-            if (j >= nb) continue ;
-            const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = zero ;
-            for (int k = 0 ; k <= i ; k++) acc += w [(r0 + i) * PB_LD + r0 + k] * tmp [(half * 16 + k) * 33 + j] ;
-            w [(r0 + i) * PB_LD + c0 + j] = -acc ;
-        }
-        __syncthreads () ;
-    }
+    inv64_lower<T> (s, w, rsq, rsq + POTRF_NB) ;      // tmp: [32][33] scratch after the three 64-vectors
     T *W = winv + (int64_t) b.slot * (WINV_LD * WINV_LD) ;
     for (int e = threadIdx.x ; e < nbk * nbk ; e += 256)
     {
@@ -1485,87 +1493,102 @@ __global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__
 // many CTAs, instead of one CTA walking thousands of columns one by one
 // ---------------------------------------------------------------------------------------------
 
-struct SolveBlk  { int32_t s, c0, jb, pad ; } ;                     // 64-wide diagonal block of supernode s
-struct SolveTile { int32_t s, c0, jb, r0, nrows, p0, p1, p2 ; } ;   // rows [r0, r0+nrows) of s below that block
+// Diagonal block q of a wide supernode and one 256-row tile below it.  The 64 x 64 diagonal blocks are
+// inverted once per factorization (k_solve_inv), so that a block step is ONE launch: forward, every tile
+// CTA forms y = W * x_blk itself (4096 multiply-adds, W comes from L2) and subtracts L (rows, blk) * y from
+// the rows it owns; backward, the tiles subtract L (rows, blk)^H * x [rows] from the block's entries and the
+// CTA that finishes last multiplies by W^H.
+struct SolveBlk  { int32_t s, c0, jb, pad ; } ;
+struct SolveTile { int32_t s, c0, jb, r0, nrows, writer, ntiles, blk ; } ;   // tile `writer` stores y; ntiles per block
 
-template <typename T> constexpr size_t solve_diag_smem_bytes ()
+constexpr int SOLVE_WLD = 64 ;      // an inverse is a 64 x 64 column-major array, lower triangular, identity padded
+
+template <typename T> constexpr size_t solve_inv_smem_bytes ()
 {
-    return (size_t) (64 * 65 + 64) * sizeof (typename solve_x<T>::type) ;
+    return (size_t) (2 * POTRF_NB * PB_LD + POTRF_NB + 32 * 33) * sizeof (typename solve_x<T>::type) ;
 }
 
-// forward, diagonal block:  x_blk <- L_blk \ x_blk     (the dtrsv / dtrsm of SSOL:93, :204)
-// backward (TRANS):         x_blk <- L_blk^H \ x_blk   (SSOL:386-402)
-template <typename T, bool TRANS>
-__global__ void __launch_bounds__ (64) k_solve_diag (const SolveBlk *__restrict__ blks,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
+// W = (diagonal block)^{-1}, in the precision of the solve
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_inv (const SolveBlk *__restrict__ blks,
+    const int64_t *__restrict__ pi, const int64_t *__restrict__ px, const T *__restrict__ Lx,
+    typename solve_x<T>::type *__restrict__ Winv)
 {
     typedef typename solve_x<T>::type XT ;
     extern __shared__ __align__ (16) unsigned char solve_smem [] ;
-    XT *sL = reinterpret_cast<XT *> (solve_smem) ;          // sL [c * 65 + r] = L (r,c), lower
-    XT *sx = sL + 64 * 65 ;                                 // [64]
+    XT *s = reinterpret_cast<XT *> (solve_smem) ;       // s [c * PB_LD + r] = L (r,c)
+    XT *w = s + POTRF_NB * PB_LD ;
+    XT *rsq = w + POTRF_NB * PB_LD ;
+    XT *tmp = rsq + POTRF_NB ;
     const SolveBlk b = blks [blockIdx.x] ;
-    const int64_t k1 = super [b.s], nsrow = pi [b.s+1] - pi [b.s] ;
+    const int64_t nsrow = pi [b.s+1] - pi [b.s] ;
     const T *L = Lx + px [b.s] + b.c0 + (int64_t) b.c0 * nsrow ;
-    const int jb = b.jb, tid = threadIdx.x ;
-    for (int e = tid ; e < jb * jb ; e += 64)
+    const int jb = b.jb ;
+    const XT one = from_real<XT> (1), zero = from_real<XT> (0) ;
+    for (int e = threadIdx.x ; e < POTRF_NB * POTRF_NB ; e += 256)
     {
-        const int r = e % jb, c = e / jb ;
-        if (r >= c) sL [c * 65 + r] = cvt<XT> (L [r + (int64_t) c * nsrow]) ;
+        const int r = e % POTRF_NB, c = e / POTRF_NB ;
+        XT v ;
+        if (r < jb && c < jb) v = (r >= c) ? cvt<XT> (L [r + (int64_t) c * nsrow]) : zero ;
+        else v = (r == c) ? one : zero ;
+        s [c * PB_LD + r] = v ;
     }
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    __syncthreads () ;
+    if (threadIdx.x < POTRF_NB) rsq [threadIdx.x] = from_real<XT> (1.0 / real_ (s [threadIdx.x * PB_LD + threadIdx.x])) ;
+    __syncthreads () ;
+    inv64_lower<XT> (s, w, rsq, tmp) ;
+    XT *W = Winv + (int64_t) blockIdx.x * (SOLVE_WLD * SOLVE_WLD) ;
+    for (int e = threadIdx.x ; e < POTRF_NB * POTRF_NB ; e += 256)
     {
-        XT *x = X + (int64_t) rhs * n + k1 + b.c0 ;
-        if (tid < jb) sx [tid] = x [tid] ;
-        __syncthreads () ;
-        if (!TRANS)
-        {
-            for (int j = 0 ; j < jb ; j++)
-            {
-                if (tid == j) sx [j] = sx [j] / real_ (sL [j * 65 + j]) ;
-                __syncthreads () ;
-                if (tid > j && tid < jb) sx [tid] -= sL [j * 65 + tid] * sx [j] ;
-                __syncthreads () ;
-            }
-        }
-        else
-        {
-            for (int j = jb - 1 ; j >= 0 ; j--)
-            {
-                if (tid == j) sx [j] = sx [j] / real_ (sL [j * 65 + j]) ;
-                __syncthreads () ;
-                if (tid < j) sx [tid] -= mulc (sx [j], sL [tid * 65 + j]) ;
-                __syncthreads () ;
-            }
-        }
-        if (tid < jb) x [tid] = sx [tid] ;
-        __syncthreads () ;
+        const int r = e % POTRF_NB, c = e / POTRF_NB ;
+        W [r + c * SOLVE_WLD] = (r >= c) ? w [r * PB_LD + c] : zero ;
     }
 }
 
-// forward, rows below the block:  x [rows] -= L (rows, blk) * x_blk     (the dgemv / dgemm of SSOL:100, :212);
-// rows inside the supernode are its own unknowns, rows below it belong to ancestors and are shared with
-// the siblings of the level, hence the atomics
+__device__ __forceinline__ double ldcg_ (const double *p) { return __ldcg (p) ; }
+__device__ __forceinline__ cx<double> ldcg_ (const cx<double> *p)
+{
+    double2 v = __ldcg (reinterpret_cast<const double2 *> (p)) ;
+    return { v.x, v.y } ;
+}
+
+// forward block step:  y = L_blk \ x_blk  (dtrsv / dtrsm of SSOL:93, :204);  x [rows] -= L (rows, blk) * y  (the dgemv /
+// dgemm of SSOL:100, :212).  Rows inside the supernode are its own later unknowns, rows below it belong to
+// ancestors and are shared with the siblings of the level, hence the atomics.  y goes to Y (not back into X: the
+// other tiles of the launch are still reading x_blk).
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_gemv (const SolveTile *__restrict__ tiles,
+__global__ void __launch_bounds__ (256) k_solve_fwd_blk (const SolveTile *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
 {
     typedef typename solve_x<T>::type XT ;
-    __shared__ XT xb [64] ;
+    __shared__ XT xb [64], yb [64] ;
     const SolveTile t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
     const T *L = Lx + px [t.s] + (int64_t) t.c0 * nsrow ;
-    const int row = t.r0 + threadIdx.x ;
+    const XT *W = Winv + (int64_t) t.blk * (SOLVE_WLD * SOLVE_WLD) ;
+    const int tid = threadIdx.x, row = t.r0 + tid ;
+    const XT zero = from_real<XT> (0) ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        XT *x = X + (int64_t) rhs * n ;
-        if (threadIdx.x < t.jb) xb [threadIdx.x] = x [k1 + t.c0 + threadIdx.x] ;
+        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
+        if (tid < 64) xb [tid] = (tid < t.jb) ? x [k1 + t.c0 + tid] : zero ;
         __syncthreads () ;
-        if ((int) threadIdx.x < t.nrows)
         {
-            XT acc = from_real<XT> (0) ;
-            for (int j = 0 ; j < t.jb ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * xb [j] ;
+            const int r = tid >> 2, part = tid & 3 ;
+            XT acc = zero ;
+            for (int c = part ; c <= r ; c += 4) acc += W [r + c * SOLVE_WLD] * xb [c] ;
+            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+            if (part == 0) yb [r] = acc ;
+        }
+        __syncthreads () ;
+        if (t.writer && tid < t.jb) y [k1 + t.c0 + tid] = yb [tid] ;
+        if (tid < t.nrows)
+        {
+            XT acc = zero ;
+            for (int j = 0 ; j < t.jb ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * yb [j] ;
             const int64_t dst = (row < nscol) ? k1 + row : (int64_t) Ls [psi + row] ;
             atomic_sub (x + dst, acc) ;
         }
@@ -1573,33 +1596,60 @@ __global__ void __launch_bounds__ (256) k_solve_gemv (const SolveTile *__restric
     }
 }
 
-// backward, rows below the block:  x_blk -= L (rows, blk)^H * x [rows]     (SSOL:386: dgemv "C");
-// thread (j, part) walks down column j of the tile, 4 threads per column
+// backward block step:  Y_blk -= L (rows, blk)^H * x [rows]  (SSOL:386, dgemv "C") by every tile, then the tile that
+// finishes last does  x_blk = L_blk^H \ Y_blk = W^H * Y_blk  (SSOL:386-402).  counters [blk * nrhs + rhs] counts the
+// finished tiles and is left at zero for the next solve.
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_gemvt (const SolveTile *__restrict__ tiles,
+__global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs)
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
 {
     typedef typename solve_x<T>::type XT ;
-    __shared__ XT xr [256] ;
+    __shared__ XT xr [256], yb [64] ;
+    __shared__ int is_last ;
     const SolveTile t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
-    const int j = threadIdx.x >> 2, part = threadIdx.x & 3 ;
+    const int tid = threadIdx.x, j = tid >> 2, part = tid & 3 ;
     const T *Lc = Lx + px [t.s] + (int64_t) (t.c0 + j) * nsrow + t.r0 ;
+    const XT *W = Winv + (int64_t) t.blk * (SOLVE_WLD * SOLVE_WLD) ;
+    const XT zero = from_real<XT> (0) ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
-        XT *x = X + (int64_t) rhs * n ;
-        if ((int) threadIdx.x < t.nrows)
+        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
+        if (tid < t.nrows)
         {
-            const int row = t.r0 + threadIdx.x ;
-            xr [threadIdx.x] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
+            const int row = t.r0 + tid ;
+            xr [tid] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
         }
         __syncthreads () ;
-        XT acc = from_real<XT> (0) ;
+        XT acc = zero ;
         if (j < t.jb) for (int r = part ; r < t.nrows ; r += 4) acc += mulc (xr [r], cvt<XT> (Lc [r])) ;
         acc += shfl_xor_ (0xffffffffu, acc, 1) ;
         acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-        if (part == 0 && j < t.jb) atomic_sub (x + k1 + t.c0 + j, acc) ;
+        if (part == 0 && j < t.jb && t.nrows > 0) atomic_sub (y + k1 + t.c0 + j, acc) ;
+        __threadfence () ;
+        __syncthreads () ;
+        if (tid == 0)
+        {
+            int *cnt = counters + (int64_t) t.blk * nrhs + rhs ;
+            const int done = atomicAdd (cnt, 1) ;
+            is_last = (done == t.ntiles - 1) ;
+            if (is_last) *cnt = 0 ;
+        }
+        __syncthreads () ;
+        if (is_last)
+        {
+            __threadfence () ;
+            if (tid < 64) yb [tid] = (tid < t.jb) ? ldcg_ (y + k1 + t.c0 + tid) : zero ;
+            __syncthreads () ;
+            // x_c = sum_{r >= c} conj (W (r,c)) * y_r : thread (c, part) walks down column c of W
+            XT a2 = zero ;
+            for (int r = j + part ; r < 64 ; r += 4) a2 += mulc (yb [r], W [r + j * SOLVE_WLD]) ;
+            a2 += shfl_xor_ (0xffffffffu, a2, 1) ;
+            a2 += shfl_xor_ (0xffffffffu, a2, 2) ;
+            if (part == 0 && j < t.jb) x [k1 + t.c0 + j] = a2 ;
+        }
         __syncthreads () ;
     }
 }
