@@ -120,7 +120,9 @@ struct b200_factor
     DevBuf<double> d_X, d_Y ;               // solve: right-hand sides / forward results of the wide supernodes
     DevBuf<unsigned char> d_solveW ;        // solve: inverses of the 64 x 64 diagonal blocks of the wide supernodes
     DevBuf<int> d_solve_cnt ;               // solve: finished-tile counters (block x rhs), zero between solves
-    bool solve_w_valid = false ;            // d_solveW belongs to the factor values now in d_Lx
+    bool solve_w_valid = false ;
+    double ms_solve_part [4] = {} ;         // profile mode: small fwd, wide fwd, small bwd, wide bwd
+    int64_t solve_launch_count [4] = {} ;            // d_solveW belongs to the factor values now in d_Lx
     // solve schedule (built at the first solve)
     struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;  // kind 0: one CTA per supernode, 2: block step of the wide ones
     std::vector<SolveLaunch> solve_launches ;
@@ -694,6 +696,8 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
+    if (!strncmp (name, "solve_launches", 14) && name [14] >= '0' && name [14] < '4') return (double) f->solve_launch_count [name [14] - '0'] ;
     if (!strncmp (name, "ms_launch_start", 15)) { size_t k = (size_t) atoll (name + 15) ; return k < f->ms_launch_start.size () ? f->ms_launch_start [k] : -1 ; }
     if (!strncmp (name, "ms_launch", 9)) { size_t k = (size_t) atoll (name + 9) ; return k < f->ms_launch.size () ? f->ms_launch [k] : -1 ; }
     if (!strncmp (name, "ms_level_end", 12)) { int k = atoi (name + 12) ; return (k >= 0 && k < 64) ? f->ms_level_end [k] : -1 ; }
@@ -1077,17 +1081,16 @@ static int solve_T (b200_factor *f, int nrhs)
     const Plan &P = f->plan ;
     cudaStream_t s = f->stream ;
     typedef typename solve_x<T>::type XT ;
-    const int64_t cap = (200 * 1024) / (int64_t) sizeof (XT) ;
     const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
     XT *X = reinterpret_cast<XT *> (f->d_X.p) ;
     XT *Y = reinterpret_cast<XT *> (f->d_Y.p) ;
     if (!f->solve_ready)
     {
-        // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_BIG columns
+        // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_SMALL columns
         // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
         // over the level, one launch per step: the rows below the diagonal block spread over 256-row tiles
         // (k_solve_fwd_blk).  The backward sweep is the same list read in reverse (k_solve_bwd_blk).
-        constexpr int64_t SOLVE_BIG = 256, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
+        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
         std::vector<int32_t> small ;
         std::vector<SolveBlk> blks ;
         std::vector<SolveTile> tiles ;
@@ -1152,6 +1155,14 @@ static int solve_T (b200_factor *f, int nrhs)
         }
     }
     const size_t nl = f->solve_launches.size () ;
+    size_t nev = 0 ;
+    if (f->profile)
+        while (f->prof_ev.size () < 4 * nl)
+        {
+            cudaEvent_t e ;
+            CK (cudaEventCreate (&e), "profile event") ;
+            f->prof_ev.push_back (e) ;
+        }
     for (size_t pass = 0 ; pass < 2 ; pass++)
     {
         for (size_t q = 0 ; q < nl ; q++)
@@ -1159,15 +1170,16 @@ static int solve_T (b200_factor *f, int nrhs)
             const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
             if (L.count <= 0) continue ;
             const unsigned grid = (unsigned) L.count ;
+            if (f->profile) cudaEventRecord (f->prof_ev [nev++], s) ;
             if (L.kind == 0)
             {
-                const size_t sm = (size_t) std::min (L.maxcol, cap) * sizeof (XT) ;
+                const size_t sm = solve_small_smem_bytes<T> (L.maxcol) ;
                 if (pass == 0)
-                    k_solve_fwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, X, P.n, nrhs, cap) ;
+                    k_solve_fwd<T><<<grid, 128, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, X, P.n, nrhs, (int) L.maxcol) ;
                 else
-                    k_solve_bwd<T><<<grid, 256, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        f->d_Ls.p, Lx, X, P.n, nrhs, cap) ;
+                    k_solve_bwd<T><<<grid, 128, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                        f->d_Ls.p, Lx, X, P.n, nrhs, (int) L.maxcol) ;
             }
             else
             {
@@ -1178,9 +1190,27 @@ static int solve_T (b200_factor *f, int nrhs)
                     k_solve_bwd_blk<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
             }
+            if (f->profile) cudaEventRecord (f->prof_ev [nev++], s) ;
         }
     }
     CK (cudaGetLastError (), "solve kernels") ;
+    if (f->profile)
+    {
+        CK (cudaStreamSynchronize (s), "profile sync") ;
+        for (int k = 0 ; k < 4 ; k++) { f->ms_solve_part [k] = 0 ; f->solve_launch_count [k] = 0 ; }
+        size_t e = 0 ;
+        for (size_t pass = 0 ; pass < 2 ; pass++)
+            for (size_t q = 0 ; q < nl ; q++)
+            {
+                const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
+                if (L.count <= 0) continue ;
+                float ms = 0 ;
+                cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
+                e += 2 ;
+                const int k = (int) pass * 2 + (L.kind == 0 ? 0 : 1) ;
+                f->ms_solve_part [k] += ms ; f->solve_launch_count [k]++ ;
+            }
+    }
     return B200_OK ;
 }
 

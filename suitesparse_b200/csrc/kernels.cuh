@@ -1393,42 +1393,66 @@ __global__ void __launch_bounds__ (TRSM_ROWS) k_trsm (const TrsmTile *__restrict
 template <typename T> struct solve_x { typedef double type ; } ;
 template <typename R> struct solve_x<cx<R>> { typedef cx<double> type ; } ;
 
+// Supernodes of at most SOLVE_SMALL columns: one CTA of 128 threads each.  The diagonal block goes to shared
+// memory once (pitch mc+1, mc = the widest supernode of the launch), the triangular solve is done by ONE warp
+// with the unknowns in registers (two per lane, the pivot broadcast by shuffle: no barrier, no memory latency
+// inside the serial chain), the rows below by all threads with independent loads.
+constexpr int SOLVE_SMALL = 64 ;
+
+template <typename T> inline size_t solve_small_smem_bytes (int64_t mc)
+{
+    return (size_t) (mc * (mc + 1) + mc + 128) * sizeof (typename solve_x<T>::type) ;
+}
+
 // forward:  x1 <- L11 \ x1 ;  x [rows below] -= L21 * x1      (SSOL:20-303; atomics because siblings of
 // one level update common ancestor rows concurrently)
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_fwd (const int32_t *__restrict__ list,
+__global__ void __launch_bounds__ (128) k_solve_fwd (const int32_t *__restrict__ list,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
     const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs,
-    int64_t smem_cap)
+    int mc)
 {
     typedef typename solve_x<T>::type XT ;
     extern __shared__ __align__ (16) unsigned char solve_smem [] ;
-    XT *sx_smem = reinterpret_cast<XT *> (solve_smem) ;      // [min (nscol, smem_cap)]
+    const int ld = mc + 1 ;
+    XT *sL = reinterpret_cast<XT *> (solve_smem) ;          // sL [c * ld + r] = L (r,c), r >= c
+    XT *sx = sL + mc * ld ;                                 // [mc]
     const int s = list [blockIdx.x] ;
-    const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
+    const int64_t k1 = super [s], psi = pi [s], nsrow = pi [s+1] - psi ;
+    const int nscol = (int) (super [s+1] - k1) ;
     const T *L = Lx + px [s] ;
+    const int tid = threadIdx.x, lane = tid & 31 ;
+    const XT zero = from_real<XT> (0) ;
+    for (int e = tid ; e < nscol * nscol ; e += 128)
+    {
+        const int r = e % nscol, c = e / nscol ;
+        if (r >= c) sL [c * ld + r] = cvt<XT> (L [r + (int64_t) c * nsrow]) ;
+    }
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
         XT *x = X + (int64_t) rhs * n ;
-        // work in shared memory when the supernode's columns fit, else in place in global memory
-        const bool in_smem = nscol <= smem_cap ;
-        XT *sx = in_smem ? sx_smem : x + k1 ;
-        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) sx [j] = x [k1 + j] ;
+        if (tid < nscol) sx [tid] = x [k1 + tid] ;
         __syncthreads () ;
-        for (int64_t j = 0 ; j < nscol ; j++)
+        if (tid < 32)
         {
-            XT xj = sx [j] / (double) real_ (L [j + j * nsrow]) ;
-            __syncthreads () ;
-            if (threadIdx.x == 0) sx [j] = xj ;
-            for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
-                sx [i] -= cvt<XT> (L [i + j * nsrow]) * xj ;
-            __syncthreads () ;
+            XT a0 = (lane < nscol) ? sx [lane] : zero, a1 = (lane + 32 < nscol) ? sx [lane + 32] : zero ;
+            for (int j = 0 ; j < nscol ; j++)
+            {
+                const XT xj = shfl_ (0xffffffffu, (j < 32) ? a0 : a1, j & 31) / real_ (sL [j * ld + j]) ;
+                if (lane == (j & 31)) { if (j < 32) a0 = xj ; else a1 = xj ; }
+                if (lane > j && lane < nscol) a0 -= sL [j * ld + lane] * xj ;
+                if (lane + 32 > j && lane + 32 < nscol) a1 -= sL [j * ld + lane + 32] * xj ;
+            }
+            if (lane < nscol) sx [lane] = a0 ;
+            if (lane + 32 < nscol) sx [lane + 32] = a1 ;
         }
-        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) x [k1 + j] = sx [j] ;
-        for (int64_t i = nscol + threadIdx.x ; i < nsrow ; i += blockDim.x)
+        __syncthreads () ;
+        if (tid < nscol) x [k1 + tid] = sx [tid] ;
+        for (int64_t i = nscol + tid ; i < nsrow ; i += 128)
         {
-            XT acc = from_real<XT> (0) ;
-            for (int64_t j = 0 ; j < nscol ; j++) acc += cvt<XT> (L [i + j * nsrow]) * sx [j] ;
+            XT acc = zero ;
+            #pragma unroll 8
+            for (int j = 0 ; j < nscol ; j++) acc += cvt<XT> (L [i + (int64_t) j * nsrow]) * sx [j] ;
             atomic_sub (x + Ls [psi + i], acc) ;
         }
         __syncthreads () ;
@@ -1437,53 +1461,67 @@ __global__ void __launch_bounds__ (256) k_solve_fwd (const int32_t *__restrict__
 
 // backward:  x1 <- L11^H \ (x1 - L21^H * x [rows below])        (SSOL:309-586)
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_bwd (const int32_t *__restrict__ list,
+__global__ void __launch_bounds__ (128) k_solve_bwd (const int32_t *__restrict__ list,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
     const int32_t *__restrict__ Ls, const T *__restrict__ Lx, typename solve_x<T>::type *X, int64_t n, int nrhs,
-    int64_t smem_cap)
+    int mc)
 {
     typedef typename solve_x<T>::type XT ;
     extern __shared__ __align__ (16) unsigned char solve_smem [] ;
-    XT *sx_smem = reinterpret_cast<XT *> (solve_smem) ;      // [min (nscol, smem_cap)]
-    __shared__ XT red [8] ;
+    const int ld = mc + 1 ;
+    XT *sL = reinterpret_cast<XT *> (solve_smem) ;
+    XT *sx = sL + mc * ld ;                                 // [mc]
+    XT *xr = sx + mc ;                                      // [128] the unknowns of a chunk of rows below
     const int s = list [blockIdx.x] ;
-    const int64_t k1 = super [s], nscol = super [s+1] - k1, psi = pi [s], nsrow = pi [s+1] - psi ;
+    const int64_t k1 = super [s], psi = pi [s], nsrow = pi [s+1] - psi ;
+    const int nscol = (int) (super [s+1] - k1) ;
     const T *L = Lx + px [s] ;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5 ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
     const XT zero = from_real<XT> (0) ;
+    for (int e = tid ; e < nscol * nscol ; e += 128)
+    {
+        const int r = e % nscol, c = e / nscol ;
+        if (r >= c) sL [c * ld + r] = cvt<XT> (L [r + (int64_t) c * nsrow]) ;
+    }
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
         XT *x = X + (int64_t) rhs * n ;
-        const bool in_smem = nscol <= smem_cap ;
-        XT *sx = in_smem ? sx_smem : x + k1 ;
-        // sx [j] = x [k1+j] - sum_{i >= nscol} conj (L (i,j)) * x [Ls [i]] : one warp per column
-        for (int64_t j = warp ; j < nscol ; j += nwarps)
+        if (tid < nscol) sx [tid] = x [k1 + tid] ;
+        // sx [j] -= sum_{i >= nscol} conj (L (i,j)) * x [Ls [i]], 128 rows at a time, a warp per column
+        for (int64_t i0 = nscol ; i0 < nsrow ; i0 += 128)
         {
-            XT acc = zero ;
-            for (int64_t i = nscol + lane ; i < nsrow ; i += 32)
-                acc += mulc (x [Ls [psi + i]], cvt<XT> (L [i + j * nsrow])) ;
-            for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
-            if (lane == 0) sx [j] = x [k1 + j] - acc ;
+            __syncthreads () ;
+            xr [tid] = (i0 + tid < nsrow) ? x [Ls [psi + i0 + tid]] : zero ;
+            __syncthreads () ;
+            for (int j = warp ; j < nscol ; j += 4)
+            {
+                const T *Lj = L + i0 + (int64_t) j * nsrow ;
+                XT acc = zero ;
+                #pragma unroll
+                for (int k = 0 ; k < 4 ; k++)
+                {
+                    const int i = lane + 32 * k ;
+                    if (i0 + i < nsrow) acc += mulc (xr [i], cvt<XT> (Lj [i])) ;
+                }
+                for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
+                if (lane == 0) sx [j] -= acc ;              // column j belongs to this warp alone
+            }
         }
         __syncthreads () ;
-        for (int64_t j = nscol - 1 ; j >= 0 ; j--)
+        if (tid < 32)
         {
-            // xj = (sx [j] - sum_{i > j, i < nscol} conj (L (i,j)) * sx [i]) / L (j,j)
-            XT acc = zero ;
-            for (int64_t i = j + 1 + threadIdx.x ; i < nscol ; i += blockDim.x)
-                acc += mulc (sx [i], cvt<XT> (L [i + j * nsrow])) ;
-            for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
-            if (lane == 0) red [warp] = acc ;
-            __syncthreads () ;
-            if (threadIdx.x == 0)
+            // L11^H x = sx: after x_j is known, row j of L takes it out of the earlier unknowns
+            XT a0 = (lane < nscol) ? sx [lane] : zero, a1 = (lane + 32 < nscol) ? sx [lane + 32] : zero ;
+            for (int j = nscol - 1 ; j >= 0 ; j--)
             {
-                XT tot = zero ;
-                for (int w = 0 ; w < nwarps ; w++) tot += red [w] ;
-                sx [j] = (sx [j] - tot) / (double) real_ (L [j + j * nsrow]) ;
+                const XT xj = shfl_ (0xffffffffu, (j < 32) ? a0 : a1, j & 31) / real_ (sL [j * ld + j]) ;
+                if (lane == (j & 31)) { if (j < 32) a0 = xj ; else a1 = xj ; }
+                if (lane < j) a0 -= mulc (xj, sL [lane * ld + j]) ;
+                if (lane + 32 < j) a1 -= mulc (xj, sL [(lane + 32) * ld + j]) ;
             }
-            __syncthreads () ;
+            if (lane < nscol) x [k1 + lane] = a0 ;
+            if (lane + 32 < nscol) x [k1 + lane + 32] = a1 ;
         }
-        if (in_smem) for (int64_t j = threadIdx.x ; j < nscol ; j += blockDim.x) x [k1 + j] = sx [j] ;
         __syncthreads () ;
     }
 }
@@ -1576,9 +1614,14 @@ __global__ void __launch_bounds__ (256) k_solve_fwd_blk (const SolveTile *__rest
         if (tid < 64) xb [tid] = (tid < t.jb) ? x [k1 + t.c0 + tid] : zero ;
         __syncthreads () ;
         {
+            // all 16 loads of a thread are issued before the first is used
             const int r = tid >> 2, part = tid & 3 ;
+            XT wv [16] ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++) wv [k] = (part + 4 * k <= r) ? W [r + (part + 4 * k) * SOLVE_WLD] : zero ;
             XT acc = zero ;
-            for (int c = part ; c <= r ; c += 4) acc += W [r + c * SOLVE_WLD] * xb [c] ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++) acc += wv [k] * xb [part + 4 * k] ;
             acc += shfl_xor_ (0xffffffffu, acc, 1) ;
             acc += shfl_xor_ (0xffffffffu, acc, 2) ;
             if (part == 0) yb [r] = acc ;
@@ -1588,7 +1631,12 @@ __global__ void __launch_bounds__ (256) k_solve_fwd_blk (const SolveTile *__rest
         if (tid < t.nrows)
         {
             XT acc = zero ;
-            for (int j = 0 ; j < t.jb ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * yb [j] ;
+            if (t.jb == 64)
+            {
+                #pragma unroll 16
+                for (int j = 0 ; j < 64 ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * yb [j] ;
+            }
+            else for (int j = 0 ; j < t.jb ; j++) acc += cvt<XT> (L [row + (int64_t) j * nsrow]) * yb [j] ;
             const int64_t dst = (row < nscol) ? k1 + row : (int64_t) Ls [psi + row] ;
             atomic_sub (x + dst, acc) ;
         }
@@ -1611,7 +1659,7 @@ __global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__rest
     const SolveTile t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
     const int tid = threadIdx.x, j = tid >> 2, part = tid & 3 ;
-    const T *Lc = Lx + px [t.s] + (int64_t) (t.c0 + j) * nsrow + t.r0 ;
+    const T *Lbase = Lx + px [t.s] + (int64_t) t.c0 * nsrow + t.r0 ;     // first row of the tile, first column of the block
     const XT *W = Winv + (int64_t) t.blk * (SOLVE_WLD * SOLVE_WLD) ;
     const XT zero = from_real<XT> (0) ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
@@ -1623,11 +1671,27 @@ __global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__rest
             xr [tid] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
         }
         __syncthreads () ;
-        XT acc = zero ;
-        if (j < t.jb) for (int r = part ; r < t.nrows ; r += 4) acc += mulc (xr [r], cvt<XT> (Lc [r])) ;
-        acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-        acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-        if (part == 0 && j < t.jb && t.nrows > 0) atomic_sub (y + k1 + t.c0 + j, acc) ;
+        // warp w takes columns 8w .. 8w+7; its lanes run down the 256 rows of the tile, 32 at a time (coalesced,
+        // 8 independent loads per column), then the warp adds up
+        if (t.nrows > 0)
+        {
+            const int lane = tid & 31, warp = tid >> 5 ;
+            for (int jj = 0 ; jj < 8 ; jj++)
+            {
+                const int jc = warp * 8 + jj ;
+                if (jc >= t.jb) break ;
+                const T *Lj = Lbase + (int64_t) jc * nsrow ;
+                XT acc = zero ;
+                #pragma unroll
+                for (int k = 0 ; k < 8 ; k++)
+                {
+                    const int r = lane + 32 * k ;
+                    if (r < t.nrows) acc += mulc (xr [r], cvt<XT> (Lj [r])) ;
+                }
+                for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
+                if (lane == 0) atomic_sub (y + k1 + t.c0 + jc, acc) ;
+            }
+        }
         __threadfence () ;
         __syncthreads () ;
         if (tid == 0)
@@ -1644,8 +1708,12 @@ __global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__rest
             if (tid < 64) yb [tid] = (tid < t.jb) ? ldcg_ (y + k1 + t.c0 + tid) : zero ;
             __syncthreads () ;
             // x_c = sum_{r >= c} conj (W (r,c)) * y_r : thread (c, part) walks down column c of W
+            XT wv [16] ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++) wv [k] = (part + 4 * k >= j) ? W [part + 4 * k + j * SOLVE_WLD] : zero ;
             XT a2 = zero ;
-            for (int r = j + part ; r < 64 ; r += 4) a2 += mulc (yb [r], W [r + j * SOLVE_WLD]) ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++) a2 += mulc (yb [part + 4 * k], wv [k]) ;
             a2 += shfl_xor_ (0xffffffffu, a2, 1) ;
             a2 += shfl_xor_ (0xffffffffu, a2, 2) ;
             if (part == 0 && j < t.jb) x [k1 + t.c0 + j] = a2 ;

@@ -27,9 +27,10 @@ from oracle import refd
 from suitesparse_b200 import b200, matrices as M
 from cases import Case
 out = []
-for kind, size, shift in (("lap3d7", 30, None), ("lap2d9", 150, None), ("lap3d7", 14, (1500, -1.0))):
-    c = Case(kind, size, refd.CHOLMOD_METIS, shift_diag=shift)
-    F = b200.Factor(c.sym, device=rank, nranks=world, rank=rank)
+for kind, size, shift, herm in (("lap3d7", 30, None, False), ("lap2d9", 150, None, False),
+                                ("lap3d7", 14, (1500, -1.0), False), ("lap3d7", 24, None, True)):
+    c = Case(kind, size, refd.CHOLMOD_METIS, shift_diag=shift, hermitian=herm)
+    F = b200.Factor(c.sym, dtype=c.Lref.dtype, device=rank, nranks=world, rank=rank)
     F.comm_init_torch()
     res = {}
     for rep in range(2):                                    # twice: the context is reusable
@@ -42,8 +43,8 @@ for kind, size, shift in (("lap3d7", 30, None), ("lap2d9", 150, None), ("lap3d7"
         res = dict(status=st, minor=F.minor, err=c.rel_err(Lx), ref_status=c.status, ref_minor=c.minor,
                    zero_same=bool(np.array_equal(Lx == 0, c.Lref == 0)), nccl=F.geti("nccl_calls"), ntop=F.geti("ntop"))
     if shift is None:
-        b = M.rhs(c.n)
-        x = np.empty(c.n); x[c.sym["Perm"]] = F.solve(b[c.sym["Perm"]])
+        b = M.rhs(c.n) * ((1 + 0.5j) if herm else 1.0)
+        x = np.empty_like(b); x[c.sym["Perm"]] = F.solve(b[c.sym["Perm"]])
         res["resid"] = c.ref.resid(x, b)
     out.append(res)
     F.close()
@@ -69,8 +70,8 @@ def test_factorization_over_several_gpus(world):
     allres = json.loads(line[len("RESULT "):])
     assert len(allres) == world
     for per_rank in allres:
-        ok1, ok2, bad = per_rank
-        for ok in (ok1, ok2):
+        ok1, ok2, bad, okz = per_rank          # okz: the Hermitian (complex double) case, (re,im) pairs on the wire
+        for ok in (ok1, ok2, okz):
             assert ok["status"] == 0 and ok["err"] <= 1e-10 and ok["resid"] <= 1e-12
             assert ok["nccl"] > 0
         assert ok1["ntop"] > 0
