@@ -97,6 +97,7 @@ struct b200_factor
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
     cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
     cudaStream_t stream4 = nullptr ;        // communication stream: every NCCL call of this context
+    std::vector<cudaStream_t> gstreams ;    // subtree-group streams of a single-GPU plan: [2g] chain, [2g+1] look-ahead
     cudaEvent_t ev_comm [2] = {} ;
     void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
     ncclComm_t comm = nullptr ;             // multi-GPU: communicator over the ranks of the plan (b200_comm_init)
@@ -241,8 +242,21 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
 {
     T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
     T *winv = reinterpret_cast<T *> (f->d_winv.p) ;
-    const cudaStream_t streams [2] = { f->stream, f->stream2 } ;
     size_t nev = 0 ;
+    while ((int) f->gstreams.size () < P.nstreams - 4)
+    {
+        // same priorities as the main pair: chains high, look-ahead updates low
+        int lo = 0, hi = 0 ;
+        CK (cudaDeviceGetStreamPriorityRange (&lo, &hi), "priority range") ;
+        cudaStream_t g ;
+        CK (cudaStreamCreateWithPriority (&g, cudaStreamNonBlocking, (f->gstreams.size () & 1) ? lo : hi), "group stream") ;
+        f->gstreams.push_back (g) ;
+    }
+    auto stream_of = [&] (int id) -> cudaStream_t
+    {
+        return (id == 0) ? f->stream : (id == 1) ? f->stream2 : (id == 2) ? f->stream3 : (id == 3) ? f->stream4
+            : f->gstreams [(size_t) (id - 4)] ;
+    } ;
     while ((int64_t) f->plan_ev.size () < (int64_t) P.nevents)
     {
         cudaEvent_t e ;
@@ -274,7 +288,8 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             }
             continue ;
         }
-        const cudaStream_t st = (L.stream == 3) ? f->stream4 : streams [L.stream ? 1 : 0] ;
+        if (L.stream < 0 || L.stream >= std::max (4, P.nstreams)) return B200_INVALID ;
+        const cudaStream_t st = stream_of (L.stream) ;
         if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
         if (L.kind == K_BCAST)
         {
@@ -385,6 +400,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         CK (cudaStreamSynchronize (f->stream), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream2), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream4), "profile sync") ;
+        for (cudaStream_t g : f->gstreams) CK (cudaStreamSynchronize (g), "profile sync") ;
         size_t e = 0, li = 0 ;
         f->ms_launch.assign (P.launches.size (), 0.f) ;
         f->ms_launch_start.assign (P.launches.size (), 0.f) ;
@@ -633,6 +649,7 @@ void b200_destroy (b200_factor *f)
         if (f->comm) { NcclApi *nc = nccl_api () ; if (nc) nc->CommDestroy (f->comm) ; f->comm = nullptr ; }
         cudaStreamSynchronize (f->stream2) ;
         cudaStreamDestroy (f->stream2) ;
+        for (cudaStream_t g : f->gstreams) { cudaStreamSynchronize (g) ; cudaStreamDestroy (g) ; }
         if (f->stream3) { cudaStreamSynchronize (f->stream3) ; cudaStreamDestroy (f->stream3) ; }
         if (f->stream4) { cudaStreamSynchronize (f->stream4) ; cudaStreamDestroy (f->stream4) ; }
         for (auto &e : f->ev_comm) if (e) cudaEventDestroy (e) ;
@@ -668,6 +685,10 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "rank")) return P.rank ;
     if (!strcmp (name, "nccl_calls")) return f->nccl_calls ;
     if (!strcmp (name, "nbcasts")) return (int64_t) P.bcasts.size () ;
+    if (!strcmp (name, "ngroups")) return P.ngroups ;
+    if (!strcmp (name, "fork_lo")) return P.fork_lo ;
+    if (!strcmp (name, "fork_hi")) return P.fork_hi ;
+    if (!strcmp (name, "nstreams")) return P.nstreams ;
     if (!strcmp (name, "ntop")) { int64_t c = 0 ; for (char t : P.top) c += t ; return c ; }
     if (!strcmp (name, "profile")) return f->profile ;
     if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] < '0' + K_NKINDS) return f->launches_kind [name [13] - '0'] ;
@@ -726,6 +747,7 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
     else if (!strcmp (which, "bcasts")) { src = P.bcasts.data () ; bytes = P.bcasts.size () * sizeof (BcastSeg) ; }
     else if (!strcmp (which, "owner")) { src = P.owner.data () ; bytes = P.owner.size () * sizeof (int32_t) ; }
     else if (!strcmp (which, "top")) { src = P.top.data () ; bytes = P.top.size () ; }
+    else if (!strcmp (which, "group")) { src = P.group.data () ; bytes = P.group.size () * sizeof (int32_t) ; }
     else return -1 ;
     if (!out) return (int64_t) bytes ;
     if ((int64_t) bytes > out_bytes) return -1 ;

@@ -192,8 +192,10 @@ void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t 
 // later block by that block's owner -- a 1-D block-cyclic right-looking Cholesky.
 void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma,
-    char *copied = nullptr)
+    char *copied = nullptr, int sm = 0, int sl = 1, int32_t slot_base = 0)
 {
+    // sm / sl: the stream of the panel chain and the look-ahead stream of this call (0 / 1 unless the level
+    // is being factorized group by group, see build_plan); slot_base: first inverse slot it may use
     int64_t maxcol = 0 ;
     for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
     std::vector<PotrfBlk> pb [3] ;      // jb <= 16, <= 32, <= 64
@@ -212,7 +214,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             for (auto &v : pb) v.clear () ;
             for (auto &v : tt) v.clear () ;
             std::vector<PotrfBlk> small ;
-            int32_t nslots = 0 ;
+            int32_t nslots = slot_base ;
             for (int64_t q = 0 ; q < ns ; q++)
             {
                 const int64_t s = S [q] ;
@@ -261,7 +263,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
             if (!small.empty ())
             {
-                Launch L = make_launch (K_FACTOR_SMALL, (int64_t) out.potrf.size (), (int64_t) small.size (), level, 0) ;
+                Launch L = make_launch (K_FACTOR_SMALL, (int64_t) out.potrf.size (), (int64_t) small.size (), level, sm) ;
                 L.wait_ev = pending_wait ; pending_wait = -1 ;
                 out.count_kind [L.kind] += L.count ;
                 out.potrf.insert (out.potrf.end (), small.begin (), small.end ()) ;
@@ -270,7 +272,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             for (int c = 0 ; c < 3 ; c++)
             {
                 if (pb [c].empty ()) continue ;
-                Launch L = make_launch (K_POTRF16 + c, (int64_t) out.potrf.size (), (int64_t) pb [c].size (), level, 0) ;
+                Launch L = make_launch (K_POTRF16 + c, (int64_t) out.potrf.size (), (int64_t) pb [c].size (), level, sm) ;
                 L.wait_ev = pending_wait ; pending_wait = -1 ;
                 out.count_kind [L.kind] += L.count ;
                 out.potrf.insert (out.potrf.end (), pb [c].begin (), pb [c].end ()) ;
@@ -279,18 +281,18 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             for (int c = 0 ; c < 3 ; c++)
             {
                 if (tt [c].empty ()) continue ;
-                Launch L = make_launch (K_TRSM + c, (int64_t) out.trsm.size (), (int64_t) tt [c].size (), level, 0) ;
+                Launch L = make_launch (K_TRSM + c, (int64_t) out.trsm.size (), (int64_t) tt [c].size (), level, sm) ;
                 out.count_kind [L.kind] += L.count ;
                 out.trsm.insert (out.trsm.end (), tt [c].begin (), tt [c].end ()) ;
                 out.launches.push_back (L) ;
             }
-            flush_tiles (out, sink, level) ;
+            flush_tiles (out, sink, level, sm) ;
         }
         if (pending_wait >= 0)
         {
             // this rank had no panel work in block T: the wait still has to be honoured before the
             // broadcast / updates below may overwrite or read what Ub(T-2) touched
-            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = pending_wait ;
+            Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.wait_ev = pending_wait ;
             out.launches.push_back (J) ;
             pending_wait = -1 ;
         }
@@ -385,7 +387,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             // off the owner's critical path, and evF says "panel T is on this rank"
             const int evP = out.nevents++ ;
             evF = out.nevents++ ;
-            Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evP ;
+            Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.rec_ev = evP ;
             out.launches.push_back (J) ;
             Launch Bc = make_launch (K_BCAST, (int64_t) bcast_first, (int64_t) bcast_count, level, 3) ;
             Bc.wait_ev = evP ; Bc.rec_ev = evF ;
@@ -397,11 +399,11 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         {
             // F(T) ends here on the main stream
             evF = out.nevents++ ; if (any_b) evB = out.nevents++ ;
-            if (!out.launches.empty () && out.launches.back ().stream == 0 && out.launches.back ().rec_ev < 0)
+            if (!out.launches.empty () && out.launches.back ().stream == sm && out.launches.back ().rec_ev < 0)
                 out.launches.back ().rec_ev = evF ;
             else
             {
-                Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.rec_ev = evF ;
+                Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.rec_ev = evF ;
                 out.launches.push_back (J) ;
             }
         }
@@ -411,8 +413,8 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             C.wait_ev = evF ;
             out.launches.push_back (C) ;
         }
-        flush_tiles (out, sink, level, 0, foreign_ua ? evF : -1, -1) ;  // Ua(T), main stream
-        if (any_b) flush_tiles (out, later, level, 1, evF, evB) ;  // Ub(T), look-ahead stream
+        flush_tiles (out, sink, level, sm, foreign_ua ? evF : -1, -1) ; // Ua(T), main stream
+        if (any_b) flush_tiles (out, later, level, sl, evF, evB) ; // Ub(T), look-ahead stream
         evB_prev2 = evB_prev ;
         evB_prev = evB ;
     }
@@ -421,7 +423,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
     for (int ev : { evB_prev2, evB_prev, last_bcast_ev })
     {
         if (ev < 0) continue ;
-        Launch J = make_launch (K_JOIN, 0, 0, level, 0) ; J.wait_ev = ev ;
+        Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.wait_ev = ev ;
         out.launches.push_back (J) ;
     }
 }
@@ -486,6 +488,71 @@ int partition (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *
             if (P.top [s] || P.sroot [s] != r) return B200_INVALID ;
     (void) px ;
     return B200_OK ;
+}
+
+// Decide whether and where a single-GPU plan forks into subtree groups (see build_plan).
+void plan_groups (Plan &P, const int64_t *super, const int64_t *pi)
+{
+    const int64_t nsuper = P.nsuper ;
+    P.ngroups = 1 ; P.fork_lo = P.fork_hi = -1 ;
+    P.group.assign ((size_t) nsuper, -1) ;
+    int want = 8 ;
+    if (const char *e = getenv ("CHOLMOD_B200_GROUPS")) want = atoi (e) ;
+    if (P.nranks > 1 || want < 2 || P.nlevels < 4) return ;
+    want = std::min (want, 16) ;
+    // fork_lo: the first level with fewer than 2048 supernodes; fork_hi: the first level after it with fewer
+    // than 8 supernodes or a supernode of 2048 columns or more (from there on a level fills the machine)
+    int lo = -1, hi = -1 ;
+    for (int lev = 0 ; lev < P.nlevels ; lev++)
+    {
+        const int64_t cnt = P.level_ptr [lev+1] - P.level_ptr [lev] ;
+        int64_t maxcol = 0 ;
+        for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++)
+            maxcol = std::max (maxcol, super [P.level_list [q] + 1] - super [P.level_list [q]]) ;
+        if (lo < 0) { if (cnt < 2048) lo = lev ; else continue ; }
+        if (cnt < 8 || maxcol >= 2048) { hi = lev ; break ; }
+    }
+    if (lo < 0) return ;
+    if (hi < 0) hi = P.nlevels ;
+    if (hi - lo < 2) return ;
+    // subtree work below fork_hi
+    std::vector<double> sub ((size_t) nsuper, 0.0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        double nscol = (double) (super [s+1] - super [s]), nsrow = (double) (pi [s+1] - pi [s]) ;
+        sub [s] = nscol * nscol * nscol / 3.0 + nscol * nscol * (nsrow - nscol) + nsrow * nscol ;
+    }
+    for (const Pair &pr : P.pairs)
+    {
+        double K = (double) (super [pr.d+1] - super [pr.d]) ;
+        sub [pr.s] += K * pr.ndrow1 * (2.0 * pr.ndrow2 - pr.ndrow1) ;
+    }
+    std::vector<int64_t> roots ;
+    for (int64_t s = 0 ; s < nsuper ; s++)      // children precede parents
+    {
+        if (P.level [s] >= hi) continue ;
+        const int64_t p = P.parent [s] ;
+        if (p >= 0 && P.level [p] < hi) sub [p] += sub [s] ; else roots.push_back (s) ;
+    }
+    std::sort (roots.begin (), roots.end (), [&] (int64_t a, int64_t b) { return sub [a] != sub [b] ? sub [a] > sub [b] : a < b ; }) ;
+    // only subtrees that reach into the forked levels matter for the balance; count them
+    int64_t tall = 0 ;
+    for (int64_t r : roots) if (P.level [r] >= lo) tall++ ;
+    const int G = (int) std::min<int64_t> (want, tall) ;
+    if (G < 2) return ;
+    std::vector<double> load ((size_t) G, 0.0) ;
+    for (int64_t r : roots)
+    {
+        int g = (int) (std::min_element (load.begin (), load.end ()) - load.begin ()) ;
+        load [g] += sub [r] ;
+        P.group [r] = g ;
+    }
+    for (int64_t s = nsuper - 1 ; s >= 0 ; s--)
+    {
+        if (P.level [s] >= hi || P.group [s] >= 0) continue ;
+        P.group [s] = P.group [P.parent [s]] ;      // the parent is below fork_hi too, and already has its group
+    }
+    P.ngroups = G ; P.fork_lo = lo ; P.fork_hi = hi ;
 }
 
 }   // namespace
@@ -650,14 +717,80 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         if (nsuper - P.level_ptr [lev+1] <= 1024) { first_ckpt = lev ; break ; }
     std::vector<char> copied ((size_t) nsuper, 0) ;
 
+    // Single GPU: subtree groups.  A level with thousands of supernodes fills the machine when all of them
+    // are advanced in lock-step, and the few huge supernodes at the top are bound by their updates; the
+    // levels in between -- tens of supernodes a few hundred to a few thousand columns wide -- are bound by
+    // the latency of their panel chains, one level after the other.  Those levels [fork_lo, fork_hi) are
+    // therefore factorized by subtree: the subtrees hanging below level fork_hi are dealt to `ngroups` groups
+    // (largest first, to the least loaded), every group walks ITS supernodes level by level on its own
+    // stream pair, and the chains of different groups overlap.  Nothing crosses between groups (an update
+    // only ever goes from a supernode to one of its ancestors), so the only events are a fork and a join.
+    plan_groups (P, super, pi) ;
+    std::vector<int32_t> group_slot_base ((size_t) P.ngroups + 1, 0) ;
+    if (P.ngroups > 1)
+    {
+        // inverse slots: a group never needs more than its supernode count on one level
+        std::vector<int32_t> need ((size_t) P.ngroups, 0), cnt ((size_t) P.ngroups, 0) ;
+        for (int lev = P.fork_lo ; lev < P.fork_hi ; lev++)
+        {
+            std::fill (cnt.begin (), cnt.end (), 0) ;
+            for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++) cnt [P.group [P.level_list [q]]]++ ;
+            for (int g = 0 ; g < P.ngroups ; g++) need [g] = std::max (need [g], cnt [g]) ;
+        }
+        for (int g = 0 ; g < P.ngroups ; g++) group_slot_base [g+1] = group_slot_base [g] + need [g] ;
+        P.nstreams = 4 + 2 * P.ngroups ;
+    }
+
     // the launch plan, level by level: (1) every descendant update whose target lives on the level,
     // (2) the blocked factorization of the level's supernodes, (3) broadcasts of finished local subtrees
     TileSink sink ;
     std::vector<int64_t> ncols ;
+    std::vector<int32_t> Sg ;
     for (int lev = 0 ; lev < nlevels ; lev++)
     {
         const int32_t *S = P.level_list.data () + P.level_ptr [lev] ;
         const int64_t ns = P.level_ptr [lev+1] - P.level_ptr [lev] ;
+        if (P.ngroups > 1 && lev >= P.fork_lo && lev < P.fork_hi)
+        {
+            if (lev == P.fork_lo)
+            {
+                // fork: every group's chain stream starts after what the main stream has done so far
+                const int evFork = P.nevents++ ;
+                Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evFork ;
+                P.launches.push_back (J) ;
+                for (int g = 0 ; g < P.ngroups ; g++)
+                {
+                    Launch W = make_launch (K_JOIN, 0, 0, lev, 4 + 2 * g) ; W.wait_ev = evFork ;
+                    P.launches.push_back (W) ;
+                }
+            }
+            for (int g = 0 ; g < P.ngroups ; g++)
+            {
+                Sg.clear () ;
+                for (int64_t q = 0 ; q < ns ; q++) if (P.group [S [q]] == g) Sg.push_back (S [q]) ;
+                if (Sg.empty ()) continue ;
+                const int sm = 4 + 2 * g, sl = 5 + 2 * g ;
+                for (int32_t sn : Sg) plan_updates_into (P, P, own, super, pi, px, sn, sink, use_dmma) ;
+                flush_tiles (P, sink, lev, sm) ;
+                ncols.resize (Sg.size ()) ;
+                for (size_t q = 0 ; q < Sg.size () ; q++) ncols [q] = super [Sg [q] + 1] - super [Sg [q]] ;
+                plan_factor (P, own, super, pi, px, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma,
+                    nullptr, sm, sl, group_slot_base [g]) ;
+            }
+            if (lev == P.fork_hi - 1)
+            {
+                // join: the main stream goes on when every group is through
+                for (int g = 0 ; g < P.ngroups ; g++)
+                {
+                    const int evDone = P.nevents++ ;
+                    Launch J = make_launch (K_JOIN, 0, 0, lev, 4 + 2 * g) ; J.rec_ev = evDone ;
+                    P.launches.push_back (J) ;
+                    Launch W = make_launch (K_JOIN, 0, 0, lev, 0) ; W.wait_ev = evDone ;
+                    P.launches.push_back (W) ;
+                }
+            }
+            continue ;      // what these levels finished goes to the host at the first checkpoint after the join
+        }
         for (int64_t q = 0 ; q < ns ; q++) plan_updates_into (P, P, own, super, pi, px, S [q], sink, use_dmma) ;
         flush_tiles (P, sink, lev) ;
         ncols.resize ((size_t) ns) ;

@@ -115,6 +115,11 @@ struct Plan
     int64_t count_kind [K_NKINDS] = {} ;    // list entries (tiles / blocks) per launch kind
     int64_t winv_slots = 0 ;                // inverse slots (64 x 64 values each) the largest launch needs
     int32_t nevents = 0 ;                   // events the look-ahead schedule uses
+    // single-GPU plans: the levels [fork_lo, fork_hi) are factorized subtree group by subtree group, each
+    // group on its own pair of streams (4 + 2g: panel chain, 5 + 2g: look-ahead), see build_plan
+    int32_t nstreams = 4 ;                  // stream ids a launch may carry: 0 main, 1 look-ahead, 2 copy, 3 comm, 4.. groups
+    int32_t ngroups = 1, fork_lo = -1, fork_hi = -1 ;
+    std::vector<int32_t> group ;            // [nsuper] group of a supernode below fork_hi (else -1)
 
     std::vector<int32_t> level ;        // [nsuper] height above the leaves in the supernodal etree
     std::vector<int64_t> parent ;       // [nsuper] etree parent or -1

@@ -52,11 +52,14 @@ def _schedule(launches, prefer):
     """Order the launches the way two CUDA streams could legally execute them: each stream in order, a
     launch with wait_ev only after that event was recorded.  prefer = 0 runs the main stream as far as
     it can before the look-ahead stream gets a turn; prefer = 1 the other way round."""
-    queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in (0, 1, 2, 3)}
-    pos, recorded, order = {0: 0, 1: 0, 2: 0, 3: 0}, set(), []
-    # stream 2 is the copy stream, 3 the communication stream: prefer = 0 / 1 also make them the last / the
-    # first to run when they can
-    pref = {0: (0, 1, 3, 2), 1: (2, 3, 1, 0)}[prefer]
+    ids = sorted(set([0, 1, 2, 3]) | set(int(v) for v in np.unique(launches["stream"])))
+    queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in ids}
+    pos, recorded, order = {st: 0 for st in ids}, set(), []
+    # stream 2 is the copy stream, 3 the communication stream, 4.. the subtree-group streams (even: panel chain,
+    # odd: look-ahead): prefer = 0 runs main, look-ahead, the groups in order, communication, copy; prefer = 1
+    # the exact reverse
+    groups = [st for st in ids if st >= 4]
+    pref = {0: [0, 1] + groups + [3, 2], 1: [2, 3] + groups[::-1] + [1, 0]}[prefer]
     # cudaStreamWaitEvent on an event that the host has not recorded yet is a no-op: every wait must come
     # after its record in issue (= list) order
     rec_at = {int(L["rec_ev"]): i for i, L in enumerate(launches) if L["rec_ev"] >= 0}
@@ -70,7 +73,7 @@ def _schedule(launches, prefer):
         w = int(launches[queues[st][pos[st]]]["wait_ev"])
         return w < 0 or w in recorded
 
-    while any(pos[st] < len(queues[st]) for st in (0, 1, 2, 3)):
+    while any(pos[st] < len(queues[st]) for st in ids):
         cand = [st for st in pref if ready(st)]
         assert cand, "dead-lock in the launch plan's event graph"
         st = cand[0]
@@ -95,7 +98,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
     relmap = tables["relmap"]
     minor = None
     launches = tables["launches"]
-    for st1 in launches[launches["stream"] == 1]:
+    for st1 in launches[(launches["stream"] == 1) | ((launches["stream"] >= 5) & (launches["stream"] % 2 == 1))]:
         assert st1["wait_ev"] >= 0 or st1["kind"] != b200.K_JOIN
     for idx in _schedule(launches, prefer):
         L = launches[idx]
