@@ -59,3 +59,26 @@ def test_aat_not_posdef_and_port():
     stp, _, Lp = refd.port_factor(c.sym, c.Sp, c.Si, c.Sx, beta=0.5, F=(c.Fp, c.Fi, c.Fx))
     assert st == stp == 0 and np.max(np.abs(Lx - Lp)) <= TOL_L * np.max(np.abs(Lp))
     F.close()
+
+
+def test_aat_unpacked_operands():
+    """A and F unpacked (A->nz / F->nz non-NULL, slack after every column), as the seam allows (SNW:437-506)."""
+    c = CaseAAT(16, refd.CHOLMOD_AMD, beta=0.25)
+
+    def unpack(p, i, x, ncols):
+        cnt = np.diff(p)
+        up = np.zeros(ncols + 1, dtype=np.int64)
+        up[1:] = np.cumsum(cnt + 2)
+        ui = np.zeros(up[-1], dtype=np.int64)
+        ux = np.full(up[-1], 777.0)                 # slack entries must never be read
+        for k in range(ncols):
+            ui[up[k]:up[k] + cnt[k]] = i[p[k]:p[k + 1]]
+            ux[up[k]:up[k] + cnt[k]] = x[p[k]:p[k + 1]]
+        return up, ui, ux, cnt.astype(np.int64)
+
+    Sp, Si, Sx, Snz = unpack(c.Sp, c.Si, c.Sx, c.ncol)
+    Fp, Fi, Fx, Fnz = unpack(c.Fp, c.Fi, c.Fx, c.n)
+    F = b200.Factor(c.sym, device=0)
+    st, Lx = F.super_numeric_aat(c.ncol, Sp, Si, Sx, Fp, Fi, Fx, beta=0.25, Anz=Snz, Fnz=Fnz)
+    assert st == b200.OK and c.rel_err(Lx) <= TOL_L
+    F.close()

@@ -136,3 +136,31 @@ def test_hermitian_dense_supernode():
     x = F.solve(A @ np.ones(n, dtype=np.complex128))
     assert np.max(np.abs(x - 1.0)) <= 1e-10
     F.close()
+
+
+def test_hermitian_unpacked_and_diagonal_imaginary_part_ignored():
+    """Unpacked, unsorted columns with a strictly-upper extra entry, and garbage in the imaginary part of the
+    diagonal of A: zpotrf (and so the reference) only ever reads the real part."""
+    c = get_case("lap2d5", 30, refd.CHOLMOD_AMD, hermitian=True)
+    n, Sp, Si, Sx = c.n, c.Sp, c.Si, c.Sx.copy()
+    Sx[Sp[:-1]] += 0.375j                                   # first entry of a sorted lower column = the diagonal
+    assert np.all(Si[Sp[:-1]] == np.arange(n))
+    rng = np.random.default_rng(9)
+    cnt = np.diff(Sp)
+    Up = np.zeros(n + 1, dtype=np.int64)
+    Up[1:] = np.cumsum(cnt + 3)
+    Ui = np.zeros(Up[-1], dtype=np.int64)
+    Ux = np.full(Up[-1], 99.0 + 1j)
+    Unz = np.zeros(n, dtype=np.int64)
+    for k in range(n):
+        rows, vals = Si[Sp[k]:Sp[k + 1]], Sx[Sp[k]:Sp[k + 1]]
+        if k > 0:
+            rows, vals = np.append(rows, k - 1), np.append(vals, 5.0 - 2j)      # strictly upper: ignored
+        perm = rng.permutation(len(rows))
+        Ui[Up[k]:Up[k] + len(rows)] = rows[perm]
+        Ux[Up[k]:Up[k] + len(rows)] = vals[perm]
+        Unz[k] = len(rows)
+    F = b200.Factor(c.sym, dtype=np.complex128, device=0)
+    st, Lx = F.super_numeric(Up, Ui, Ux, Anz=Unz)
+    assert st == b200.OK and c.rel_err(Lx) <= TOL_L
+    F.close()
