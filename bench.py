@@ -148,7 +148,7 @@ def run_reference(args):
     out = {
         "impl": "reference", "metric": METRIC, "value": gf, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][3], "sample": CPU_SAMPLE[3]},
         "cpu_baseline": {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": CPU_SAMPLE[3]},
         "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
