@@ -94,6 +94,20 @@ template <typename R> __device__ __forceinline__ cx<R> shfl_xor_ (unsigned mask,
     return { __shfl_xor_sync (mask, v.re, o), __shfl_xor_sync (mask, v.im, o) } ;
 }
 
+// 1 / d for a pivot.  An IEEE double division is a long dependent instruction sequence, and the panel chain
+// has one on its critical path per column: the hardware seed (relative error 2^-23) and two Newton steps give
+// the reciprocal to within an ulp or two in a fraction of the latency.  d <= 0 or NaN (matrix not positive
+// definite) gives garbage, as a division would: the column is reported through `minor` either way.
+__device__ __forceinline__ float rcp_ (float d) { return 1.0f / d ; }
+__device__ __forceinline__ double rcp_ (double d)
+{
+    double r ;
+    asm ("rcp.approx.ftz.f64 %0, %1;" : "=d" (r) : "d" (d)) ;
+    r = fma (fma (-d, r, 1.0), r, r) ;
+    r = fma (fma (-d, r, 1.0), r, r) ;
+    return r ;
+}
+
 // ---------------------------------------------------------------------------------------------
 // scatter A
 // ---------------------------------------------------------------------------------------------
@@ -892,12 +906,12 @@ __global__ void __launch_bounds__ (64) k_potrf_reg (const PotrfBlk *__restrict__
         __syncthreads () ;
         const R d = real_ (cb [j]) ;            // the pivot: only its real part exists (zpotrf)
         if (r == j && j < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-        const T t = a [j] * ((R) 1 / d) ;
+        const T t = a [j] * rcp_ (d) ;
         #pragma unroll
         for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= mulc (t, cb [c]) ;
         const R ljj = sqrt (d) ;
         if (r == j) a [j] = from_real<T> (ljj) ;
-        else if (r > j) a [j] = a [j] / ljj ;
+        else if (r > j) a [j] = a [j] * rcp_ (ljj) ;
     }
     #pragma unroll
     for (int c = 0 ; c < NB ; c++) if (r < jb && c <= r) D [r + c * lda] = a [c] ;
@@ -936,12 +950,12 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
         __syncthreads () ;
         const R d = real_ (cb [j]) ;            // the pivot: only its real part exists (zpotrf)
         if (r == j && j < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
-        const T t = a [j] * ((R) 1 / d) ;
+        const T t = a [j] * rcp_ (d) ;
         #pragma unroll
         for (int c = j + 1 ; c < NB ; c++) if (c <= r) a [c] -= mulc (t, cb [c]) ;
         const R ljj = sqrt (d) ;
         if (r == j) a [j] = from_real<T> (ljj) ;
-        else if (r > j) a [j] = a [j] / ljj ;
+        else if (r > j) a [j] = a [j] * rcp_ (ljj) ;
     }
     #pragma unroll
     for (int c = 0 ; c < NB ; c++)
@@ -1005,37 +1019,52 @@ __device__ __forceinline__ void inv64_lower (const T *s, T *w, const T *rsq, T *
     for (int pass = 0 ; pass < 2 ; pass++)
     {
         const int nb = pass ? 32 : 16 ;
-        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31)
-        // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
-        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31).
+        // A thread owns 4 entries of the product and advances their 4 sums together, so that four independent
+        // shared-memory loads and multiply-adds are in flight instead of one dependent chain.
+        int ei [4], ej [4], ec0 [4], er0 [4], et [4] ;
+        bool ok [4] ;
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++)
         {
+            const int e = (int) threadIdx.x + 256 * u ;
             const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
-            const int i = el % nb, j = el / nb ;
-            if (j >= nb) continue ;
-            const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = zero ;
-            for (int k = j ; k < nb ; k++) acc += s [(c0 + k) * PB_LD + r0 + i] * w [(c0 + k) * PB_LD + c0 + j] ;
-            tmp [(half * 16 + i) * 33 + j] = acc ;
+            ei [u] = el % nb ; ej [u] = el / nb ; ok [u] = ej [u] < nb ;
+            ec0 [u] = half * 32 ; er0 [u] = ec0 [u] + nb ; et [u] = half * 16 ;
         }
+        // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
+        T acc [4] = { zero, zero, zero, zero } ;
+        #pragma unroll 4
+        for (int k = 0 ; k < nb ; k++)
+        {
+            #pragma unroll
+            for (int u = 0 ; u < 4 ; u++)
+                if (ok [u] && k >= ej [u])
+                    acc [u] += s [(ec0 [u] + k) * PB_LD + er0 [u] + ei [u]] * w [(ec0 [u] + k) * PB_LD + ec0 [u] + ej [u]] ;
+        }
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++) if (ok [u]) tmp [(et [u] + ei [u]) * 33 + ej [u]] = acc [u] ;
         __syncthreads () ;
         // step 2: W (r0+i, c0+j) = - sum_{k <= i} W (r0+i, r0+k) tmp (k,j)
-        for (int e = threadIdx.x ; e < 1024 ; e += 256)
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++) acc [u] = zero ;
+        #pragma unroll 4
+        for (int k = 0 ; k < nb ; k++)
         {
-            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
-            const int i = el % nb, j = el / nb ;
-            if (j >= nb) continue ;
-            const int c0 = half * 32, r0 = c0 + nb ;
-            T acc = zero ;
-            for (int k = 0 ; k <= i ; k++) acc += w [(r0 + i) * PB_LD + r0 + k] * tmp [(half * 16 + k) * 33 + j] ;
-            w [(r0 + i) * PB_LD + c0 + j] = -acc ;
+            #pragma unroll
+            for (int u = 0 ; u < 4 ; u++)
+                if (ok [u] && k <= ei [u])
+                    acc [u] += w [(er0 [u] + ei [u]) * PB_LD + er0 [u] + k] * tmp [(et [u] + k) * 33 + ej [u]] ;
         }
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++) if (ok [u]) w [(er0 [u] + ei [u]) * PB_LD + ec0 [u] + ej [u]] = -acc [u] ;
         __syncthreads () ;
     }
 }
 
 template <typename T> constexpr size_t potrf_smem_bytes ()
 {
-    return (size_t) (2 * POTRF_NB * PB_LD + 2 * (4 * POTRF_NB + 4) + 3 * POTRF_NB + 32 * 33) * sizeof (T) ;
+    return (size_t) (2 * POTRF_NB * PB_LD + 2 * (4 * POTRF_NB + 8) + 3 * POTRF_NB + 32 * 33) * sizeof (T) ;
 }
 
 // Wider blocks (16 < jb <= 64): one CTA of 256 threads per block.  The block lives in registers as a
@@ -1055,7 +1084,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     extern __shared__ __align__ (16) unsigned char smem_raw [] ;
     T *s = reinterpret_cast<T *> (smem_raw) ;           // s [c * PB_LD + r] = L (r,c), lower part
     T *w = s + POTRF_NB * PB_LD ;                       // w [r * PB_LD + c] = W (r,c), lower part
-    constexpr int CB = 4 * POTRF_NB + 4 ;               // one buffer: 4 columns of 64 + their 4 pivots
+    constexpr int CB = 4 * POTRF_NB + 8 ;               // one buffer: 4 columns of 64, their 4 pivots, the 4 reciprocals
     T *colbuf = w + POTRF_NB * PB_LD ;                  // [2][CB] the 4 columns of a panel, double buffered
     T *dvec = colbuf + 2 * CB ;                         // [64] pivots d_j
     T *sqv = dvec + POTRF_NB ;                          // [64] sqrt (d_j)
@@ -1089,11 +1118,13 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
         {
             const unsigned mask = 0xFFFFu << (lane & 16) ;
             const int src = (int) (lane & 16) | jt ;           // the lane with ti == jt in this half-warp
+            R rdv [4] ;
             #pragma unroll
             for (int jj = 0 ; jj < 4 ; jj++)
             {
                 const R d = __shfl_sync (mask, real_ (a [jj][jj]), src) ;
-                const R rd = (R) 1 / d ;
+                const R rd = rcp_ (d) ;
+                rdv [jj] = rd ;
                 #pragma unroll
                 for (int cc = jj + 1 ; cc < 4 ; cc++)
                 {
@@ -1107,13 +1138,13 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             {
                 #pragma unroll
                 for (int i = 0 ; i < 4 ; i++) cb [q * POTRF_NB + 4 * ti + i] = a [i][q] ;
-                if (ti == jt) cb [4 * POTRF_NB + q] = a [q][q] ;
+                if (ti == jt) { cb [4 * POTRF_NB + q] = a [q][q] ; cb [4 * POTRF_NB + 4 + q] = from_real<T> (rdv [q]) ; }
             }
         }
         __syncthreads () ;
         R rd [4] ;
         #pragma unroll
-        for (int q = 0 ; q < 4 ; q++) rd [q] = (R) 1 / real_ (cb [4 * POTRF_NB + q]) ;
+        for (int q = 0 ; q < 4 ; q++) rd [q] = real_ (cb [4 * POTRF_NB + 4 + q]) ;   // 1 / d_q, from the owners
         if (threadIdx.x == 0)
         {
             #pragma unroll
@@ -1148,14 +1179,14 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
     {
         const R q = (threadIdx.x < 4 * njt) ? sqrt (real_ (dvec [threadIdx.x])) : (R) 1 ;
         sqv [threadIdx.x] = from_real<T> (q) ;
-        rsq [threadIdx.x] = from_real<T> ((R) 1 / q) ;
+        rsq [threadIdx.x] = from_real<T> (rcp_ (q)) ;
     }
     __syncthreads () ;
     #pragma unroll
     for (int jc = 0 ; jc < 4 ; jc++)
     {
         const int c = 4 * tj + jc ;
-        const R ljj = real_ (sqv [c]) ;
+        const R ljj = real_ (sqv [c]), rl = real_ (rsq [c]) ;
         #pragma unroll
         for (int i = 0 ; i < 4 ; i++)
         {
@@ -1163,7 +1194,7 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             if (r < c) continue ;
             if (r < jb && c < jb)
             {
-                const T v = (r == c) ? from_real<T> (ljj) : a [i][jc] / ljj ;
+                const T v = (r == c) ? from_real<T> (ljj) : a [i][jc] * rl ;
                 s [c * PB_LD + r] = v ;
                 D [r + c * lda] = v ;
             }
