@@ -10,6 +10,8 @@
 #include <cstring>
 #include <numeric>
 #include <cstdlib>
+#include <chrono>
+#include <cstdio>
 
 namespace b200 {
 
@@ -118,7 +120,9 @@ void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_e
         auto &v = sink.cls [c] ;
         if (v.empty ()) continue ;
         // longest tiles first: the CTAs still running when the launch drains are then the short ones
-        std::stable_sort (v.begin (), v.end (), [] (const UpdTile &a, const UpdTile &b) { return (a.k1 - a.k0) > (b.k1 - b.k0) ; }) ;
+        // (the one-warp tiles of the SIMT class are all short: their order does not matter)
+        if (c != K_UPD_SIMT)
+            std::stable_sort (v.begin (), v.end (), [] (const UpdTile &a, const UpdTile &b) { return (a.k1 - a.k0) > (b.k1 - b.k0) ; }) ;
         P.launches.push_back (make_launch (c, (int64_t) P.tiles.size (), (int64_t) v.size (), level, stream)) ;
         P.count_kind [c] += (int64_t) v.size () ;
         P.tiles.insert (P.tiles.end (), v.begin (), v.end ()) ;
@@ -565,6 +569,16 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
     P = Plan () ;
     P.n = n ; P.nsuper = nsuper ; P.nranks = nranks ; P.rank = rank ;
+    // CHOLMOD_B200_PLAN_TIMING=1: where the planner's own time goes (stderr)
+    const bool timing = getenv ("CHOLMOD_B200_PLAN_TIMING") != nullptr ;
+    auto t_last = std::chrono::steady_clock::now () ;
+    auto lap = [&] (const char *what)
+    {
+        if (!timing) return ;
+        auto now = std::chrono::steady_clock::now () ;
+        fprintf (stderr, "cholmod_b200 plan: %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli> (now - t_last).count ()) ;
+        t_last = now ;
+    } ;
     if (const char *e = getenv ("CHOLMOD_B200_DIST_RUN")) P.dist_run = std::max (1, atoi (e)) ;
     if (nsuper == 0)
     {
@@ -616,6 +630,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         for (int64_t s = 0 ; s < nsuper ; s++) P.level_list [w [P.level [s]]++] = (int32_t) s ;
     }
 
+    lap ("checks, etree, levels") ;
     // enumerate the update pairs (d -> s) by walking the rows of every descendant
     std::vector<Pair> &pairs = P.pairs ;
     std::vector<int64_t> &tcount = P.target_ptr ;
@@ -650,6 +665,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         for (size_t k = 0 ; k < pairs.size () ; k++) P.target_list [w [pairs [k].s]++] = (int32_t) k ;
     }
 
+    lap ("update pairs") ;
     // relative maps: position of every remaining row of d inside the row list of s
     P.pair_map.resize (pairs.size ()) ;
     {
@@ -685,6 +701,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         }
     }
 
+    lap ("relative maps") ;
     // flop counts of the dense factorizations
     for (int64_t s = 0 ; s < nsuper ; s++)
     {
@@ -725,7 +742,9 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     // (largest first, to the least loaded), every group walks ITS supernodes level by level on its own
     // stream pair, and the chains of different groups overlap.  Nothing crosses between groups (an update
     // only ever goes from a supernode to one of its ancestors), so the only events are a fork and a join.
+    lap ("partition, copy-out setup") ;
     plan_groups (P, super, pi) ;
+    lap ("subtree groups") ;
     std::vector<int32_t> group_slot_base ((size_t) P.ngroups + 1, 0) ;
     if (P.ngroups > 1)
     {
@@ -746,6 +765,9 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     TileSink sink ;
     std::vector<int64_t> ncols ;
     std::vector<int32_t> Sg ;
+    P.items.reserve (pairs.size () + (size_t) nsuper / 4 + 1024) ;
+    P.tiles.reserve (2 * pairs.size () + 1024) ;
+    P.potrf.reserve ((size_t) nsuper + 1024) ;
     for (int lev = 0 ; lev < nlevels ; lev++)
     {
         const int32_t *S = P.level_list.data () + P.level_ptr [lev] ;
@@ -846,6 +868,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
             }
         }
     }
+    lap ("items, tiles, launches") ;
     if (P.items.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;
     return B200_OK ;
 }
