@@ -991,73 +991,73 @@ __global__ void __launch_bounds__ (64) k_factor_small (const PotrfBlk *__restric
 
 // W = L^{-1} of a (padded) 64 x 64 lower triangular block held in shared memory, by a CTA of 256 threads:
 // s [c * PB_LD + r] = L (r,c), rsq [r] = 1 / L (r,r), result w [r * PB_LD + c] = W (r,c), tmp = 32 x 33 scratch.
+// Block-recursive, so that the serial chain is 16 rows instead of 64:
+//  (A) the four 16 x 16 diagonal blocks: thread c < 64 solves L16 * w = e_c for ITS column by forward
+//      substitution entirely in registers (no shuffle, no barrier inside the chain; the entries of L are
+//      broadcast reads);
+//  (B), (C) the off-diagonal blocks follow from W21 = -W22 * (L21 * W11), first for the two 16-blocks inside each
+//      32-block, then for the 32-block.  In both products a thread owns nb/8 entries of one column j (rows
+//      tt%8, tt%8+8, ...): the operand that depends on j alone is loaded once for all of them, the other one
+//      is conflict-free across the lanes.
 template <typename T>
 __device__ __forceinline__ void inv64_lower (const T *s, T *w, const T *rsq, T *tmp)
 {
     const T one = from_real<T> (1), zero = from_real<T> (0) ;
-    // W = L^{-1} of the (padded) 64 x 64 block, block-recursively, so that the serial chain is 16 rows
-    // instead of 64:  (A) the four 16 x 16 diagonal blocks are inverted side by side, row by row --
-    // W (rr,c) = (delta - sum_{c <= k < rr} L (rr,k) W (k,c)) / L (rr,rr), column c owned by the 4
-    // consecutive lanes 4c..4c+3 which split the sum;  (B), (C) the off-diagonal blocks follow from
-    // W21 = -W22 * L21 * W11, first for the two 16-blocks inside each 32-block, then for the 32-block.
+    if (threadIdx.x < POTRF_NB)
     {
-        const int c = threadIdx.x >> 2, part = threadIdx.x & 3 ;
-        const int b0 = c & ~15 ;
+        const int c = threadIdx.x, b0 = c & ~15, cl = c & 15 ;
+        T wc [16] ;
+        #pragma unroll
         for (int rl = 0 ; rl < 16 ; rl++)
         {
-            const int rr = b0 + rl ;
-            T acc = zero ;
-            for (int k = c + part ; k < rr ; k += 4) acc += s [k * PB_LD + rr] * w [k * PB_LD + c] ;
-            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-            if (part == 0 && rr >= c) w [rr * PB_LD + c] = (((rr == c) ? one : zero) - acc) * real_ (rsq [rr]) ;
-            __syncwarp () ;
+            T acc0 = zero, acc1 = zero ;
+            #pragma unroll
+            for (int kl = 0 ; kl + 1 < rl ; kl += 2)
+            {
+                acc0 += s [(b0 + kl) * PB_LD + b0 + rl] * wc [kl] ;
+                acc1 += s [(b0 + kl + 1) * PB_LD + b0 + rl] * wc [kl + 1] ;
+            }
+            if (rl & 1) acc0 += s [(b0 + rl - 1) * PB_LD + b0 + rl] * wc [rl - 1] ;
+            // rows above the diagonal of column c come out as exact zeros: (0 - 0) * rsq
+            wc [rl] = (((rl == cl) ? one : zero) - (acc0 + acc1)) * real_ (rsq [b0 + rl]) ;
         }
+        #pragma unroll
+        for (int rl = 0 ; rl < 16 ; rl++) if (rl >= cl) w [(b0 + rl) * PB_LD + c] = wc [rl] ;
     }
     __syncthreads () ;
     #pragma unroll 1
     for (int pass = 0 ; pass < 2 ; pass++)
     {
-        const int nb = pass ? 32 : 16 ;
-        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31).
-        // A thread owns 4 entries of the product and advances their 4 sums together, so that four independent
-        // shared-memory loads and multiply-adds are in flight instead of one dependent chain.
-        int ei [4], ej [4], ec0 [4], er0 [4], et [4] ;
-        bool ok [4] ;
-        #pragma unroll
-        for (int u = 0 ; u < 4 ; u++)
-        {
-            const int e = (int) threadIdx.x + 256 * u ;
-            const int half = pass ? 0 : (e >> 9), el = pass ? e : (e & 511) ;
-            ei [u] = el % nb ; ej [u] = el / nb ; ok [u] = ej [u] < nb ;
-            ec0 [u] = half * 32 ; er0 [u] = ec0 [u] + nb ; et [u] = half * 16 ;
-        }
+        // pass 0: blocks (rows 16..31, cols 0..15) and (rows 48..63, cols 32..47); pass 1: (rows 32..63, cols 0..31)
+        const int nb = pass ? 32 : 16, nu = nb >> 3 ;
+        const int half = (int) threadIdx.x / (8 * nb), tt = (int) threadIdx.x % (8 * nb) ;
+        const int j = tt >> 3, i0 = tt & 7 ;               // entries (i0 + 8u, j), u < nu
+        const int c0 = half * 32, r0 = c0 + nb, t0 = half * 16 ;
         // step 1: tmp (i,j) = sum_{k >= j} L (r0+i, c0+k) W (c0+k, c0+j)
         T acc [4] = { zero, zero, zero, zero } ;
-        #pragma unroll 4
-        for (int k = 0 ; k < nb ; k++)
+        for (int k = j ; k < nb ; k++)
         {
+            const T wk = w [(c0 + k) * PB_LD + c0 + j] ;
+            const T *sk = s + (c0 + k) * PB_LD + r0 + i0 ;
             #pragma unroll
-            for (int u = 0 ; u < 4 ; u++)
-                if (ok [u] && k >= ej [u])
-                    acc [u] += s [(ec0 [u] + k) * PB_LD + er0 [u] + ei [u]] * w [(ec0 [u] + k) * PB_LD + ec0 [u] + ej [u]] ;
+            for (int u = 0 ; u < 4 ; u++) if (u < nu) acc [u] += sk [8 * u] * wk ;
         }
         #pragma unroll
-        for (int u = 0 ; u < 4 ; u++) if (ok [u]) tmp [(et [u] + ei [u]) * 33 + ej [u]] = acc [u] ;
+        for (int u = 0 ; u < 4 ; u++) if (u < nu) tmp [(t0 + i0 + 8 * u) * 33 + j] = acc [u] ;
         __syncthreads () ;
         // step 2: W (r0+i, c0+j) = - sum_{k <= i} W (r0+i, r0+k) tmp (k,j)
         #pragma unroll
         for (int u = 0 ; u < 4 ; u++) acc [u] = zero ;
-        #pragma unroll 4
-        for (int k = 0 ; k < nb ; k++)
+        const int imax = i0 + 8 * (nu - 1) ;
+        for (int k = 0 ; k <= imax ; k++)
         {
+            const T tk = tmp [(t0 + k) * 33 + j] ;
             #pragma unroll
             for (int u = 0 ; u < 4 ; u++)
-                if (ok [u] && k <= ei [u])
-                    acc [u] += w [(er0 [u] + ei [u]) * PB_LD + er0 [u] + k] * tmp [(et [u] + k) * 33 + ej [u]] ;
+                if (u < nu && k <= i0 + 8 * u) acc [u] += w [(r0 + i0 + 8 * u) * PB_LD + r0 + k] * tk ;
         }
         #pragma unroll
-        for (int u = 0 ; u < 4 ; u++) if (ok [u]) w [(er0 [u] + ei [u]) * PB_LD + ec0 [u] + ej [u]] = -acc [u] ;
+        for (int u = 0 ; u < 4 ; u++) if (u < nu) w [(r0 + i0 + 8 * u) * PB_LD + c0 + j] = -acc [u] ;
         __syncthreads () ;
     }
 }
@@ -1106,42 +1106,45 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
             a [i][jc] = (r < jb && c < jb && r >= c) ? D [r + c * lda] : ((r == c) ? one : zero) ;
         }
     const int njt = (jb + 3) >> 2 ;
-    // One barrier per PANEL of 4 columns: the 16 owners of tile column jt (one half-warp: threadIdx =
-    // 16 tj + ti) first factorize their 4 columns among themselves, getting the pivot and the pivot-row
-    // entries from the diagonal-tile thread by shuffles; then the panel is published and every later
-    // tile column takes a rank-4 update.
+    // One barrier per PANEL of 4 columns.  The 16 owners of tile column jt (one half-warp: threadIdx = 16 tj + ti)
+    // factorize their 4 columns among themselves, getting the pivot and the pivot-row entries from the
+    // diagonal-tile thread by shuffles, and publish the panel; every later tile column then takes a rank-4
+    // update.  The owners of panel jt+1 take theirs first and factorize at once, while the other tile columns
+    // are still being updated: the serial part of the next panel hides behind the update of this one.
     const unsigned lane = threadIdx.x & 31 ;
-    for (int jt = 0 ; jt < njt ; jt++)
+    auto factor_panel = [&] (int jt)
     {
         T *cb = colbuf + (jt & 1) * CB ;
-        if (tj == jt)
+        const unsigned mask = 0xFFFFu << (lane & 16) ;
+        const int src = (int) (lane & 16) | jt ;               // the lane with ti == jt in this half-warp
+        R rdv [4] ;
+        #pragma unroll
+        for (int jj = 0 ; jj < 4 ; jj++)
         {
-            const unsigned mask = 0xFFFFu << (lane & 16) ;
-            const int src = (int) (lane & 16) | jt ;           // the lane with ti == jt in this half-warp
-            R rdv [4] ;
+            const R d = __shfl_sync (mask, real_ (a [jj][jj]), src) ;
+            const R rd = rcp_ (d) ;
+            rdv [jj] = rd ;
             #pragma unroll
-            for (int jj = 0 ; jj < 4 ; jj++)
+            for (int cc = jj + 1 ; cc < 4 ; cc++)
             {
-                const R d = __shfl_sync (mask, real_ (a [jj][jj]), src) ;
-                const R rd = rcp_ (d) ;
-                rdv [jj] = rd ;
+                const T f = conj_ (shfl_ (mask, a [cc][jj], src)) * rd ;       // conj (A (4jt+cc, j)) / d_j
                 #pragma unroll
-                for (int cc = jj + 1 ; cc < 4 ; cc++)
-                {
-                    const T f = conj_ (shfl_ (mask, a [cc][jj], src)) * rd ;   // conj (A (4jt+cc, j)) / d_j
-                    #pragma unroll
-                    for (int i = 0 ; i < 4 ; i++) a [i][cc] -= a [i][jj] * f ;
-                }
-            }
-            #pragma unroll
-            for (int q = 0 ; q < 4 ; q++)
-            {
-                #pragma unroll
-                for (int i = 0 ; i < 4 ; i++) cb [q * POTRF_NB + 4 * ti + i] = a [i][q] ;
-                if (ti == jt) { cb [4 * POTRF_NB + q] = a [q][q] ; cb [4 * POTRF_NB + 4 + q] = from_real<T> (rdv [q]) ; }
+                for (int i = 0 ; i < 4 ; i++) a [i][cc] -= a [i][jj] * f ;
             }
         }
-        __syncthreads () ;
+        #pragma unroll
+        for (int q = 0 ; q < 4 ; q++)
+        {
+            #pragma unroll
+            for (int i = 0 ; i < 4 ; i++) cb [q * POTRF_NB + 4 * ti + i] = a [i][q] ;
+            if (ti == jt) { cb [4 * POTRF_NB + q] = a [q][q] ; cb [4 * POTRF_NB + 4 + q] = from_real<T> (rdv [q]) ; }
+        }
+    } ;
+    if (tj == 0) factor_panel (0) ;
+    for (int jt = 0 ; jt < njt ; jt++)
+    {
+        __syncthreads () ;                                      // panel jt is published
+        const T *cb = colbuf + (jt & 1) * CB ;
         R rd [4] ;
         #pragma unroll
         for (int q = 0 ; q < 4 ; q++) rd [q] = real_ (cb [4 * POTRF_NB + 4 + q]) ;   // 1 / d_q, from the owners
@@ -1173,6 +1176,8 @@ __global__ void __launch_bounds__ (256) k_potrf_tile (const PotrfBlk *__restrict
                     for (int i = 0 ; i < 4 ; i++) a [i][jc] -= ar [i] * ac [jc] ;
             }
         }
+        // the other buffer held panel jt-1, which everybody has finished reading before the barrier above
+        if (tj == jt + 1 && jt + 1 < njt) factor_panel (jt + 1) ;
     }
     __syncthreads () ;
     if (threadIdx.x < POTRF_NB)
