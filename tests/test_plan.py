@@ -179,3 +179,67 @@ def test_repair_plan_semantics_match_reference_notposdef():
     minor = plan_interp.run_plan(F, Lx)
     assert minor == c.minor
     F.close()
+
+
+@needs_ref
+def test_subtree_groups_structure_and_equivalence():
+    """Single-GPU plans fork the middle levels into subtree groups (plan.cpp: plan_groups): a group is closed
+    under taking descendants inside the forked levels, only those levels use the group streams, and the
+    lock-step plan (CHOLMOD_B200_GROUPS=1) gives the same factor."""
+    c = get_case("lap3d7", 22, refd.CHOLMOD_METIS)
+    F8 = b200.Factor(c.sym, device=-1)
+    lo, hi, G = F8.geti("fork_lo"), F8.geti("fork_hi"), F8.geti("ngroups")
+    assert G > 1 and 0 <= lo < hi <= F8.geti("nlevels") and F8.geti("nstreams") == 4 + 2 * G
+    level = F8.plan_table("level", np.int32)
+    parent = F8.plan_table("parent", np.int64)
+    group = F8.plan_table("group", np.int32)
+    below = level < hi
+    assert np.all(group[below] >= 0) and np.all(group[below] < G) and np.all(group[~below] == -1)
+    kids = np.nonzero(below & (parent >= 0))[0]
+    inside = kids[level[parent[kids]] < hi]
+    assert np.array_equal(group[inside], group[parent[inside]])
+    L = F8.plan_table("launches", b200.LAUNCH_DT)
+    on_group = L["stream"] >= 4
+    assert on_group.any() and np.all((L["level"][on_group] >= lo) & (L["level"][on_group] < hi))
+    work = (L["count"] > 0) & (L["kind"] < len(b200.KIND_NAMES))
+    forked = (L["level"] >= lo) & (L["level"] < hi)
+    assert np.all(L["stream"][work & forked] >= 4)          # nothing of a forked level runs on the main pair
+    os.environ["CHOLMOD_B200_GROUPS"] = "1"
+    try:
+        F1 = b200.Factor(c.sym, device=-1)
+    finally:
+        os.environ.pop("CHOLMOD_B200_GROUPS", None)
+    assert F1.geti("ngroups") == 1 and F1.plan_table("launches", b200.LAUNCH_DT)["stream"].max() <= 2
+    out = []
+    for F in (F1, F8):
+        Lx = np.zeros(c.sym["xsize"])
+        plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
+        assert plan_interp.run_plan(F, Lx, prefer=1) is None
+        assert c.rel_err(Lx) <= 1e-12
+        out.append(Lx)
+    assert np.max(np.abs(out[0] - out[1])) <= 1e-12 * np.max(np.abs(out[0]))
+    # same work either way
+    for k in range(len(b200.KIND_NAMES)):
+        assert F1.getd("flops_kind%d" % k) == pytest.approx(F8.getd("flops_kind%d" % k), rel=1e-12)
+
+
+def test_fp64_tensor_instructions_are_in_the_library():
+    """The update kernels really are on the FP64 tensor pipe (SASS DMMA) and staged with cp.async (LDGSTS)."""
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-sass", b200.LIB_PATH], stdout=subprocess.PIPE, text=True).stdout
+    if not out.strip():
+        pytest.skip("cuobjdump not available")
+    seen = {}
+    cur = None
+    for ln in out.splitlines():
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            cur = m.group(1)
+            continue
+        if cur and "DMMA" in ln:
+            seen.setdefault(cur, set()).add("DMMA")
+        if cur and "LDGSTS" in ln:
+            seen.setdefault(cur, set()).add("LDGSTS")
+    for name in ("k_upd_dmma", "k_upd_zmma", "k_trsm_inv", "k_trsm_zinv"):
+        hits = [f for f, v in seen.items() if name in f and "DMMA" in v and "LDGSTS" in v]
+        assert hits, name
