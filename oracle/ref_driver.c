@@ -163,7 +163,7 @@ int refd_read_matrix (void *hv, const char *path)
     cholmod_l_free_factor (&h->L, &h->cm) ;
     h->A = cholmod_l_read_sparse2 (f, CHOLMOD_DOUBLE, &h->cm) ;
     fclose (f) ;
-    return (h->A && h->A->stype != 0) ? 0 : -2 ;
+    return h->A ? 0 : -2 ;
 }
 
 // ordering: CHOLMOD_NATURAL 0, GIVEN 1 (unused), AMD 2, METIS 3, NESDIS 4; -1 = default strategy.
@@ -353,6 +353,8 @@ int64_t refd_get_int (void *hv, const char *name)
     if (h->F && !strcmp (name, "nnzF")) return ((int64_t *) h->F->p) [h->F->ncol] ;
     if (h->A && !strcmp (name, "nnzA")) return ((int64_t *) h->A->p) [h->A->ncol] ;
     if (h->A && !strcmp (name, "stypeA")) return h->A->stype ;
+    if (h->A && !strcmp (name, "xtypeA")) return h->A->xtype ;
+    if (h->A && !strcmp (name, "dtypeA")) return h->A->dtype ;
     if (h->S && !strcmp (name, "nnzS")) return ((int64_t *) h->S->p) [h->S->ncol] ;
     if (!L) return -1 ;
     if (!strcmp (name, "is_super")) return L->is_super ;

@@ -164,12 +164,13 @@ class Ref:
         rc = self.lib.refd_read_matrix(self.h, path.encode())
         if rc:
             raise RuntimeError("refd_read_matrix failed: %d" % rc)
+        self.xtype = self.geti("xtypeA")            # 1 real, 2 complex, 3 zomplex
+        self.single = self.geti("dtypeA") == 4
 
     def matrix(self):
-        n, nz = self.geti("n"), self.geti("nnzA")
-        xd = np.float32 if self.single else np.float64
-        return (n, _view(self._ptr("Ap"), n + 1, np.int64).copy(), _view(self._ptr("Ai"), nz, np.int64).copy(),
-                _view(self._ptr("Ax"), nz, xd).copy(), self.geti("stypeA"))
+        n = self.geti("n")
+        Ap, Ai, Ax = self._csc("A", self.geti("ncol"), self.geti("nnzA"))
+        return (n, Ap, Ai, Ax, self.geti("stypeA"))
 
     def analyze(self, ordering=CHOLMOD_AMD, supernodal=CHOLMOD_SUPERNODAL):
         rc = self.lib.refd_analyze(self.h, ordering, supernodal)

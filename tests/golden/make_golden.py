@@ -21,13 +21,17 @@ REF_DEMO = "/root/reference/CHOLMOD/Demo/Matrix"
 def dump(name, ref, beta=0.0):
     sym = ref.symbolic()
     Sp, Si, Sx = ref.seam()
-    status = ref.super_numeric(beta)
     n, Ap, Ai, Ax, stype = ref.matrix()
+    extra = {}
+    if stype == 0:          # unsymmetric: S = A(p,:), and F = S^H goes to the numeric phase with it
+        Fp, Fi, Fx = ref.seam_F()
+        extra = dict(Fp=Fp, Fi=Fi, Fx=Fx, ncol=ref.geti("ncol"))
+    status = ref.super_numeric(beta)
     np.savez_compressed(
         os.path.join(HERE, name + ".npz"), n=sym["n"], nsuper=sym["nsuper"], xsize=sym["xsize"], fl=sym["fl"],
         lnz=sym["lnz"], Perm=sym["Perm"], super=sym["super"], pi=sym["pi"], px=sym["px"], s=sym["s"],
         Ap=Ap, Ai=Ai, Ax=Ax, stype=stype, Sp=Sp, Si=Si, Sx=Sx, beta=beta, status=status,
-        minor=ref.geti("minor"), Lx=ref.Lx().copy())
+        minor=ref.geti("minor"), Lx=ref.Lx().copy(), **extra)
     print(name, "n", sym["n"], "nsuper", sym["nsuper"], "xsize", sym["xsize"], "status", status,
           "minor", ref.geti("minor"))
 
@@ -42,10 +46,10 @@ def synthetic(name, gen, size, ordering, beta=0.0, neg=None, hermitian=False):
     dump(name, r, beta)
 
 
-def demo(name, fname):
+def demo(name, fname, beta=0.0):
     r = refd.Ref(); r.read_matrix(os.path.join(REF_DEMO, fname))
     r.analyze(refd.CHOLMOD_AMD, refd.CHOLMOD_SUPERNODAL)
-    dump(name, r)
+    dump(name, r, beta)
 
 
 if __name__ == "__main__":
@@ -65,3 +69,8 @@ if __name__ == "__main__":
     # the reference's own ctest matrices (CHOLMOD/CMakeLists.txt:835-878); bcsstk02 is its "supernodal" test
     demo("bcsstk01", "bcsstk01.tri")
     demo("bcsstk02", "bcsstk02.tri")
+    # the other three ctest matrices; "demo_" fixtures are checked by the CPU oracle test only.  lp_afiro is
+    # unsymmetric (A*A' + beta*I with the demo's beta = 1e-6, cholmod_dl_demo.c:150), c.tri is complex Hermitian
+    demo("demo_lp_afiro", "lp_afiro.tri", beta=1e-6)
+    demo("demo_c", "c.tri")
+    demo("demo_can24", "can___24.mtx")

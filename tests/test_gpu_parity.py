@@ -50,6 +50,8 @@ def test_factor_matches_reference(kind, size, ordering):
 
 def test_golden_fixtures_on_gpu():
     for f in sorted(glob.glob(os.path.join(HERE, "golden", "*.npz"))):
+        if os.path.basename(f).startswith("demo_"):
+            continue                    # CPU-side pinning of the oracle only (tests/test_oracle.py)
         g = np.load(f)
         sym = dict(n=int(g["n"]), nsuper=int(g["nsuper"]), xsize=int(g["xsize"]), super=g["super"], pi=g["pi"],
                    px=g["px"], s=g["s"])

@@ -147,7 +147,8 @@ def test_golden_fixtures():
         g = np.load(f)
         sym = dict(n=int(g["n"]), nsuper=int(g["nsuper"]), xsize=int(g["xsize"]), super=g["super"], pi=g["pi"],
                    px=g["px"], s=g["s"])
-        st, minor, Lp = refd.port_factor(sym, g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]))
+        F = (g["Fp"], g["Fi"], g["Fx"]) if "Fp" in g.files else None     # the unsymmetric fixtures carry F = S^H
+        st, minor, Lp = refd.port_factor(sym, g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]), F=F)
         assert st == int(g["status"]) and minor == int(g["minor"]), f
         Lref = g["Lx"]
         assert np.max(np.abs(Lp - Lref)) <= 1e-13 * max(1.0, np.max(np.abs(Lref))), f
