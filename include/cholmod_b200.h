@@ -221,13 +221,15 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
 /* --- diagnostics (the reference's counterparts are the BLAS_TIMER counters and cholmod_gpu_stats,
  * CHOLMOD/Check/cholmod_check.c:615-674) -------------------------------------------------------- */
 
-/* Set an integer option by name.  "profile" = 1 brackets every kernel launch of the next factorizations
- * with CUDA events and accumulates device time per kernel kind ("ms_kind0".."ms_kind4" in
- * b200_get_double; kinds: 0 SIMT update, 1 DMMA 64x64 update, 2 DMMA 128x128 update, 3 POTRF, 4 TRSM;
- * "flops_kind<k>" are the algorithmic flops of each kind; "ms_launch<i>" / "ms_launch_start<i>" are the
- * duration and start time of launch i of the plan, in the order of the "launches" table of
- * b200_plan_export).  Profiling serialises nothing but adds
- * event overhead: never time a benchmark step with it on. */
+/* Set an integer option by name.  "profile" = 1 brackets every kernel launch of the next factorizations (and
+ * solves) with CUDA events and accumulates device time per kernel kind: "ms_kind<k>", "launches_kind<k>" and the
+ * algorithmic "flops_kind<k>" in b200_get_double / b200_get_int, k = 0 SIMT update, 1 tensor update 64x64,
+ * 2 tensor update 128x64, 3..5 POTRF of <= 16 / 32 / 64 columns, 6 TRSM by substitution, 7..8 TRSM through the
+ * 32 / 64-wide inverse, 9 whole small supernodes; "ms_launch<i>" / "ms_launch_start<i>" are the duration and
+ * start time of launch i of the plan, in the order of the "launches" table of b200_plan_export; "ms_level_end<l>"
+ * when etree level l was finished; "ms_solve_part0..3" the solve's small-forward, wide-forward, small-backward
+ * and wide-backward parts.  Profiling serialises nothing but adds event overhead: never time a benchmark step
+ * with it on. */
 int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 
 /* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):
