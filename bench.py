@@ -12,9 +12,15 @@ reference's own host code as BASELINE.json's north_star prescribes).  Prints ONE
              factorization, D2H of all of L->x, timed on the host clock around the call.
   roofline   the dominant kernel (128x64 DMMA update) against the FP64 tensor peak measured live on
              this device with a register-resident DMMA loop (MEASURED_PEAKS.json has no FP64 figure).
-  cpu_baseline  the reference CPU supernodal path (oracle/_ref, all host cores) on a bounded sample.
+  cpu_baseline  the reference CPU supernodal path (oracle/_ref, all host cores) on the workload itself: one
+             factorization, whose factor is also the full-size parity check (`check.max_dL_rel`).
 
-`--impl reference` times the reference's CPU cholmod_l_factorize on the bounded sample instead.
+`--impl reference` times the reference's CPU cholmod_l_factorize on the SAME workload (all host cores).  One
+config-2 factorization takes the better part of a minute on the box, so when `--steps K --warmup W` would not
+fit the time budget (B200_REF_BUDGET_S, default 600 s) it runs 1 warm-up and as many timed factorizations as
+fit (at least 3) and prints the `steps` it actually ran.
+`--impl reference-gpu` does the same with the reference's own cuBLAS-offload GPU branch (CHOLMOD/GPU built
+for sm_100 by oracle/Makefile into oracle/_ref_cuda/), the kernel-level bar of SURVEY.md 2.3.
 """
 import argparse
 import json
@@ -41,17 +47,15 @@ WORKLOADS = {
     "lap3d7_64": ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262k), double, METIS"),
     "lap3d7_40": ("lap3d7", 40, 3, "3-D 7-point Laplacian 40^3 (n=64k), double, METIS"),
 }
-CPU_SAMPLE = ("lap3d7", 64, 3, "3-D 7-point Laplacian 64^3 (n=262144), METIS: same generator and ordering as the "
-              "workload, reduced so one CPU factorization takes ~10 s")
-
-
-def analyze(kind, size, ordering, nthreads=0, single=False):
+def analyze(kind, size, ordering, nthreads=0, single=False, use_gpu=False):
     """Reference host analysis (ordering, etree, supernodes) + the seam matrix."""
     from oracle import refd
     from suitesparse_b200 import matrices
     gen = getattr(matrices, kind)
     n, Ap, Ai, Ax = gen(size)
     ref = refd.Ref(nthreads)
+    if use_gpu:
+        ref.seti("useGPU", 1)
     ref.set_matrix(n, Ap, Ai, Ax, -1, single=single)
     t = time.time()
     ref.analyze(ordering, refd.CHOLMOD_SUPERNODAL)
@@ -120,40 +124,78 @@ def ncu_traffic():
         return None
 
 
-def cpu_reference_steps(steps, warmup, nthreads):
-    """Reference CPU cholmod_l_factorize on the bounded sample; returns (GFLOP/s, ms/step, cores, fl)."""
-    kind, size, ordering, _ = CPU_SAMPLE
-    ref, _ = analyze(kind, size, ordering, nthreads)
-    fl = ref.getd("fl")
-    for _ in range(warmup):
+def reference_config(desc, sym):
+    """The `config` both arms print: the workload, named and sized the same way."""
+    return {"workload": desc, "n": int(sym["n"]), "nsuper": int(sym["nsuper"]), "fl": sym["fl"], "lnz": sym["lnz"],
+            "xsize": int(sym["xsize"])}
+
+
+def run_reference(args, gpu_branch=False):
+    """The reference's own cholmod_l_factorize on the workload: CPU supernodal path (all host cores), or with
+    gpu_branch its cuBLAS-offload GPU path (oracle/_ref_cuda, Common->useGPU = 1)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    t_start = time.time()
+    budget = float(os.environ.get("B200_REF_BUDGET_S", "600"))
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(ncores))
+    impl = "reference-gpu" if gpu_branch else "reference"
+    if gpu_branch:
+        os.environ["B200_REFD_FLAVOUR"] = "cuda"        # oracle/refd.py loads oracle/_ref_cuda/ instead of _ref/
+        os.environ["CHOLMOD_USE_GPU"] = "1"
+        from oracle import refd
+        if not refd.have_ref():
+            print(json.dumps({"impl": impl, "unavailable": "oracle/_ref_cuda (reference built with CHOLMOD_HAS_CUDA) is not here"}))
+            return
+    kind, size, ordering, desc = WORKLOADS[args.workload]
+    ref, t_an = analyze(kind, size, ordering, ncores, use_gpu=gpu_branch)
+    sym = ref.symbolic()
+    fl = sym["fl"]
+    st = ref.factorize(0.0)                  # warm-up 1 (also the estimate of what fits)
+    assert st == 0, st
+    t1 = ref.getd("t_factor")
+    warm, steps = args.warmup, args.steps
+    left = budget - (time.time() - t_start)
+    if (max(warm, 1) - 1 + steps) * t1 > left:
+        warm = 1
+        steps = int(min(args.steps, max(3, left // max(t1, 1e-9))))
+    for _ in range(max(warm, 1) - 1):
         ref.factorize(0.0)
     ts = []
     for _ in range(steps):
         st = ref.factorize(0.0)
         assert st == 0, st
         ts.append(ref.getd("t_factor"))
+    b = __import__("suitesparse_b200.matrices", fromlist=["rhs"]).rhs(sym["n"])
+    resid = ref.resid(ref.solve(b), b)
     cores = ref.geti("nthreads_max")
     t = float(np.sum(ts))
-    ref.close()
-    return fl * steps / t / 1e9, 1e3 * t / steps, cores, fl
-
-
-def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    ncores = os.cpu_count() or 1
-    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(ncores))
-    gf, ms, cores, fl = cpu_reference_steps(args.steps, args.warmup, ncores)
+    gf = fl * steps / t / 1e9
+    ms = 1e3 * t / steps
+    sample = "the workload itself: %d timed cholmod_l_factorize calls after %d warm-up (median %.2f s)" % (
+        steps, max(warm, 1), float(np.median(ts)))
     out = {
-        "impl": "reference", "metric": METRIC, "value": gf, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][3], "sample": CPU_SAMPLE[3]},
-        "cpu_baseline": {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": CPU_SAMPLE[3]},
+        "impl": impl, "metric": METRIC, "value": gf, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": max(warm, 1), "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": reference_config(desc, sym),
+        "cpu_baseline": {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "analyze_s": t_an, "scaled_residual": resid,
+        "blas": os.path.basename(os.environ.get("B200_REF_BLAS", "OpenBLAS 0.3.15 (opencv wheel), %d threads" % ncores)),
     }
+    if gpu_branch:
+        out["reference_gpu"] = {"useGPU": ref.geti("useGPU"), "nsuper": int(sym["nsuper"]),
+                                "note": "CHOLMOD/GPU cuBLAS-offload branch, nvcc -arch=sm_100, one GPU; its analysis "
+                                        "limits supernode sizes to the device buffers, so nsuper differs from the CPU build",
+                                "gpu_stats": dict({k: ref.geti(k) for k in ("gpu_syrk_calls", "gpu_gemm_calls", "gpu_potrf_calls",
+                                                                              "gpu_trsm_calls", "cpu_syrk_calls", "cpu_gemm_calls",
+                                                                              "cpu_potrf_calls", "cpu_trsm_calls")},
+                                                  **{k: ref.getd(k) for k in ("gpu_syrk_time", "gpu_gemm_time", "gpu_potrf_time",
+                                                                              "gpu_trsm_time")})}
+    ref.close()
     print(json.dumps(out))
 
 
@@ -163,15 +205,15 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--single", action="store_true", help="single precision (config 5b); the roofline stays FP64-tensor "
                     "and is then only informative: single precision runs on the FP32 FMA pipe")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    if args.impl == "reference":
-        return run_reference(args)
+    if args.impl != "b200":
+        return run_reference(args, gpu_branch=(args.impl == "reference-gpu"))
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -206,6 +248,14 @@ def main():
         F.comm_init_torch()
     t_plan = time.time() - t0
     Lx_host = np.empty(sym["xsize"], dtype=fdtype) if rank == 0 else None
+    # what a one-shot cholmod_factorize pays on top of a steady-state step: the context (plan + tables + arena,
+    # `plan_s`) and, in the first host-buffer call, page-locking the caller's L->x (cudaHostRegister)
+    first_call_ms = None
+    if world == 1 and not args.no_e2e:
+        t0 = time.time()
+        st, _ = F.super_numeric(Sp, Si, Sx, Lx=Lx_host)
+        assert st == b200.OK, st
+        first_call_ms = 1e3 * (time.time() - t0)
 
     def barrier():
         torch.cuda.synchronize()
@@ -266,7 +316,9 @@ def main():
         e2e = {"value": fl / t_e2e / 1e9, "unit": UNIT, "ms_per_step": 1e3 * t_e2e,
                "h2d_bytes_per_step": int(Sp.nbytes + Si.nbytes + Sx.nbytes),
                "d2h_bytes_per_step": int(sym["xsize"] * np.dtype(fdtype).itemsize),
-               "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h")}
+               "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h"),
+               "first_call_ms": first_call_ms, "context_build_ms": 1e3 * t_plan,
+               "e2e_first_call_ms": (first_call_ms + 1e3 * t_plan) if first_call_ms is not None else None}
 
     # one profiled (untimed) factorization for the per-kernel breakdown; collective, so every rank runs it
     F.seti("profile", 1)
@@ -354,20 +406,31 @@ def main():
     check = {"solve_ms": F.getd("ms_solve"), "solve_first_ms": solve_first_ms, "scaled_residual": ref.resid(xs, bvec),
              "tolerance": 1e-5 if args.single else 1e-12}
 
-    # ---- CPU baseline: the reference on a bounded sample, rank 0, N = 1 only ----------------------------
+    # ---- CPU baseline: the reference's CPU path on the workload itself, rank 0, N = 1 only; its factor is the
+    # full-size parity check of ours (north_star: max|dL|/max|L| <= 1e-10) ----------------------------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         ncores = os.cpu_count() or 1
-        gf, ms, cores, _ = cpu_reference_steps(1, 1, ncores)
-        cpu = {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference", "sample": CPU_SAMPLE[3],
-               "ms_per_factorization": ms}
+        ref.seti("nthreads_max", ncores)
+        st = ref.factorize(0.0)
+        assert st == 0, st
+        t_ref = ref.getd("t_factor")
+        cpu = {"value": fl / t_ref / 1e9, "unit": UNIT, "cores": ref.geti("nthreads_max"), "kind": "reference",
+               "sample": "the workload itself, one cholmod_l_factorize (numeric phase) after the shared analysis",
+               "ms_per_factorization": 1e3 * t_ref}
+        if not args.no_e2e:
+            Lref = ref.Lx()
+            scale, err = float(np.max(np.abs(Lref))), 0.0
+            for a in range(0, Lref.size, 1 << 26):
+                err = max(err, float(np.max(np.abs(Lx_host[a:a + (1 << 26)].astype(np.float64) - Lref[a:a + (1 << 26)]))))
+            check["max_dL_rel"] = err / scale
+            check["max_dL_tolerance"] = 1e-4 if args.single else 1e-10
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32" if args.single else "f64", "data": "synthetic",
-        "config": {"workload": desc, "n": int(sym["n"]), "nsuper": int(sym["nsuper"]), "fl": fl, "lnz": sym["lnz"],
-                   "xsize": int(sym["xsize"]), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
+        "config": {**reference_config(desc, sym), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
                    "relmap_len": F.geti("relmap_len"), "device_bytes": F.geti("device_bytes"),
                    "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * 8 / 1e9),
                    "parallelism": ("one factorization over %d GPUs: etree subtrees per GPU + block-cyclic top separators, "

@@ -201,7 +201,7 @@ int b200_solve_z (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
  * of jb columns.  `stream` is a cudaStream_t passed as a pointer (NULL = the default stream).  The call
  * returns after the stream has finished the work.
  *
- * Limits: jb <= B200_NOALLOC_MAX_COLS and nrows <= B200_NOALLOC_MAX_ROWS; anything larger is refused with
+ * Limits: jb <= B200_NOALLOC_MAX_COLS, nrows <= B200_NOALLOC_MAX_ROWS and lda <= 2^31-1; anything larger is refused with
  * B200_TOO_LARGE and a message on stderr (the fixed scratch cannot hold it; use b200_create +
  * b200_super_numeric_d).  B200_INVALID for a NULL panel or inconsistent sizes.
  * Returns B200_OK, or B200_NOT_POSDEF with *info = the 1-based column of the first pivot that is not

@@ -339,6 +339,7 @@ int refd_set_int (void *hv, const char *name, int64_t v)
     if (!strcmp (name, "print")) { h->cm.print = (int) v ; return 0 ; }
     if (!strcmp (name, "try_catch")) { h->cm.try_catch = (int) v ; return 0 ; }
     if (!strcmp (name, "useGPU")) { h->cm.useGPU = (int) v ; return 0 ; }
+    if (!strcmp (name, "maxGpuMemBytes")) { h->cm.maxGpuMemBytes = (size_t) v ; return 0 ; }
     return -1 ;
 }
 
@@ -348,6 +349,16 @@ int64_t refd_get_int (void *hv, const char *name)
     cholmod_factor *L = h->L ;
     if (!strcmp (name, "status")) return h->cm.status ;
     if (!strcmp (name, "nthreads_max")) return h->cm.nthreads_max ;
+    if (!strcmp (name, "useGPU")) return h->cm.useGPU ;
+    if (!strcmp (name, "gpu_syrk_calls")) return (int64_t) h->cm.cholmod_gpu_syrk_calls ;
+    if (!strcmp (name, "gpu_gemm_calls")) return (int64_t) h->cm.cholmod_gpu_gemm_calls ;
+    if (!strcmp (name, "gpu_potrf_calls")) return (int64_t) h->cm.cholmod_gpu_potrf_calls ;
+    if (!strcmp (name, "gpu_trsm_calls")) return (int64_t) h->cm.cholmod_gpu_trsm_calls ;
+    if (!strcmp (name, "cpu_syrk_calls")) return (int64_t) h->cm.cholmod_cpu_syrk_calls ;
+    if (!strcmp (name, "cpu_gemm_calls")) return (int64_t) h->cm.cholmod_cpu_gemm_calls ;
+    if (!strcmp (name, "cpu_potrf_calls")) return (int64_t) h->cm.cholmod_cpu_potrf_calls ;
+    if (!strcmp (name, "cpu_trsm_calls")) return (int64_t) h->cm.cholmod_cpu_trsm_calls ;
+    if (!strcmp (name, "maxGpuMemBytes")) return (int64_t) h->cm.maxGpuMemBytes ;
     if (h->A && !strcmp (name, "n")) return (int64_t) h->A->nrow ;
     if (h->A && !strcmp (name, "ncol")) return (int64_t) h->A->ncol ;
     if (h->F && !strcmp (name, "nnzF")) return ((int64_t *) h->F->p) [h->F->ncol] ;
@@ -380,6 +391,11 @@ double refd_get_double (void *hv, const char *name)
     if (!strcmp (name, "t_analyze")) return h->t_analyze ;
     if (!strcmp (name, "t_factor")) return h->t_factor ;
     if (!strcmp (name, "t_solve")) return h->t_solve ;
+    if (!strcmp (name, "gpu_syrk_time")) return h->cm.cholmod_gpu_syrk_time ;
+    if (!strcmp (name, "gpu_gemm_time")) return h->cm.cholmod_gpu_gemm_time ;
+    if (!strcmp (name, "gpu_potrf_time")) return h->cm.cholmod_gpu_potrf_time ;
+    if (!strcmp (name, "gpu_trsm_time")) return h->cm.cholmod_gpu_trsm_time ;
+    if (!strcmp (name, "maxGpuMemFraction")) return h->cm.maxGpuMemFraction ;
     return -1 ;
 }
 

@@ -11,7 +11,9 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_REF = os.path.join(_HERE, "_ref")
+# B200_REFD_FLAVOUR=cuda: the reference built with CHOLMOD_HAS_CUDA (its own cuBLAS-offload GPU branch,
+# oracle/Makefile target `cuda`), used by `bench.py --impl reference-gpu` only
+_REF = os.path.join(_HERE, "_ref_cuda" if os.environ.get("B200_REFD_FLAVOUR") == "cuda" else "_ref")
 
 CHOLMOD_NATURAL, CHOLMOD_GIVEN, CHOLMOD_AMD, CHOLMOD_METIS, CHOLMOD_NESDIS = 0, 1, 2, 3, 4
 CHOLMOD_SIMPLICIAL, CHOLMOD_AUTO, CHOLMOD_SUPERNODAL = 0, 1, 2

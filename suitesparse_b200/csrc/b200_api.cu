@@ -728,7 +728,7 @@ double b200_get_double (const b200_factor *f, const char *name)
 
 // Copy plan tables to caller buffers (tests of the host planner; works on a device < 0 context).
 // which: "level" int32[nsuper], "relmap" int32[relmap_len], "items" (nitems x 48 bytes),
-// "tiles" (ntiles x 16), "potrf" (npotrf x 24), "trsm" (ntrsm x 32), "launches" (nlaunches x 24),
+// "tiles" (ntiles x 20), "potrf" (npotrf x 24), "trsm" (ntrsm x 32), "launches" (nlaunches x 24),
 // "parent" int64[nsuper].  Returns the number of bytes written, or -1.
 int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, int64_t out_bytes)
 {

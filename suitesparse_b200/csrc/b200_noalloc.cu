@@ -22,6 +22,7 @@
 #include "plan.hpp"
 #include "kernels.cuh"
 #include <cstdio>
+#include <cstdint>
 #include <mutex>
 
 using namespace b200 ;
@@ -114,6 +115,12 @@ extern "C" int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_
         fprintf (stderr, "cholmod_b200: b200_panel_factor_noalloc_d: invalid argument "
             "(need d_panel != NULL, 1 <= jb <= nrows <= lda)\n") ;
         return B200_INVALID ;
+    }
+    if (lda > (int64_t) INT32_MAX)
+    {
+        // the tile descriptors carry the leading dimension as a 32-bit integer
+        fprintf (stderr, "cholmod_b200: b200_panel_factor_noalloc_d: lda = %lld exceeds 2^31-1\n", (long long) lda) ;
+        return B200_TOO_LARGE ;
     }
     if (jb > NA_MAX_COLS || nrows > NA_MAX_ROWS)
     {

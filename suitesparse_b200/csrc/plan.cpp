@@ -88,7 +88,7 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
             {
                 UpdTile t ;
                 t.item = item_id ;
-                t.ti = (uint16_t) ti ; t.tj = (uint16_t) tj ;
+                t.ti = (int32_t) ti ; t.tj = (int32_t) tj ;
                 t.k0 = (int32_t) k0 ; t.k1 = (int32_t) std::min<int64_t> (K, k0 + kchunk) ;
                 out.push_back (t) ;
             }
@@ -760,6 +760,28 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         P.nstreams = 4 + 2 * P.ngroups ;
     }
 
+    // checkpoint after level `lev`: all maximal runs of finished, not yet copied supernodes go to the host
+    auto checkpoint = [&] (int lev)
+    {
+        const size_t copy_first = P.copies.size () ;
+        for (int64_t s = 0 ; s < nsuper ; )
+        {
+            if (copied [s] || avail_level (s) > lev) { s++ ; continue ; }
+            int64_t e = s ;
+            while (e < nsuper && !copied [e] && avail_level (e) <= lev) copied [e++] = 1 ;
+            CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ;
+            P.copies.push_back (c) ;
+            s = e ;
+        }
+        if (P.copies.size () == copy_first) return ;
+        const int evL = P.nevents++ ;
+        Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evL ;
+        P.launches.push_back (J) ;
+        Launch C = make_launch (K_COPYOUT, (int64_t) copy_first, (int64_t) (P.copies.size () - copy_first), lev, 2) ;
+        C.wait_ev = evL ;
+        P.launches.push_back (C) ;
+    } ;
+
     // the launch plan, level by level: (1) every descendant update whose target lives on the level,
     // (2) the blocked factorization of the level's supernodes, (3) broadcasts of finished local subtrees
     TileSink sink ;
@@ -845,28 +867,19 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 P.launches.push_back (W) ;
             }
         }
-        if (ckpt)
-        {
-            const size_t copy_first = P.copies.size () ;
-            for (int64_t s = 0 ; s < nsuper ; )
-            {
-                if (copied [s] || avail_level (s) > lev) { s++ ; continue ; }
-                int64_t e = s ;
-                while (e < nsuper && !copied [e] && avail_level (e) <= lev) copied [e++] = 1 ;
-                CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ;
-                P.copies.push_back (c) ;
-                s = e ;
-            }
-            if (P.copies.size () > copy_first)
-            {
-                const int evL = P.nevents++ ;
-                Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evL ;
-                P.launches.push_back (J) ;
-                Launch C = make_launch (K_COPYOUT, (int64_t) copy_first, (int64_t) (P.copies.size () - copy_first), lev, 2) ;
-                C.wait_ev = evL ;
-                P.launches.push_back (C) ;
-            }
-        }
+        if (ckpt) checkpoint (lev) ;
+    }
+    // Whatever no checkpoint has sent yet goes now.  This is the only copy-out of a plan whose subtree-group
+    // fork runs to the last level (a forest of many equal trees: the forked levels skip the checkpoints).
+    checkpoint (nlevels - 1) ;
+    if (nranks == 1)
+    {
+        // the segments must cover [0, xsize) exactly once: the drop-in calls return the host copy they made
+        std::vector<CopySeg> segs (P.copies) ;
+        std::sort (segs.begin (), segs.end (), [] (const CopySeg &a, const CopySeg &b) { return a.off < b.off ; }) ;
+        int64_t at = 0 ;
+        for (const CopySeg &c : segs) { if (c.off != at || c.len <= 0) return B200_INVALID ; at += c.len ; }
+        if (at != P.xsize) return B200_INVALID ;
     }
     lap ("items, tiles, launches") ;
     if (P.items.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;

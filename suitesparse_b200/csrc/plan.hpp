@@ -30,7 +30,7 @@ struct UpdItem
 struct UpdTile
 {
     int32_t item ;
-    uint16_t ti, tj ;
+    int32_t ti, tj ;    // 32 bits: a supernode may have up to 2^30 rows (build_plan), i.e. 2^25 SIMT tile rows
     int32_t k0, k1 ;
 } ;
 

@@ -96,3 +96,27 @@ class CaseAAT:
 def get_case(kind, size, ordering, single=False, shift_diag=None, beta=0.0, hermitian=False, zomplex=False):
     return Case(kind, size, ordering, single=single, shift_diag=shift_diag, beta=beta, hermitian=hermitian,
                 zomplex=zomplex)
+
+
+class Forest:
+    """kron(I_k, A): k copies of one case side by side, as a case of its own (symbolic factor, seam matrix,
+    reference factor are the copies' concatenation).  The supernodal etree is then a forest of k equal trees:
+    every level holds at least k supernodes."""
+
+    def __init__(self, c, copies):
+        n, ns, ss, xs = c.sym["n"], c.sym["nsuper"], int(c.sym["pi"][-1]), c.sym["xsize"]
+        nnz = int(c.Sp[-1])
+        cat = np.concatenate
+        self.n = n * copies
+        self.sym = dict(n=n * copies, nsuper=ns * copies, xsize=xs * copies,
+                        super=cat([c.sym["super"][:-1] + k * n for k in range(copies)] + [[n * copies]]),
+                        pi=cat([c.sym["pi"][:-1] + k * ss for k in range(copies)] + [[ss * copies]]),
+                        px=cat([c.sym["px"][:-1] + k * xs for k in range(copies)] + [[xs * copies]]),
+                        s=cat([c.sym["s"] + k * n for k in range(copies)]))
+        self.Sp = cat([c.Sp[:-1] + k * nnz for k in range(copies)] + [[nnz * copies]])
+        self.Si = cat([c.Si + k * n for k in range(copies)])
+        self.Sx = np.tile(c.Sx, copies)
+        self.Lref = np.tile(c.Lref, copies)
+        self.status, self.minor = c.status, c.minor
+
+    rel_err = Case.rel_err

@@ -11,6 +11,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "slow: a BASELINE-size case (tens of seconds: the reference CPU factorization beside ours)")
 
 
 @pytest.fixture(scope="session", autouse=True)

@@ -10,7 +10,7 @@ import pytest
 
 from oracle import refd
 from suitesparse_b200 import b200, matrices as M
-from cases import Case, get_case
+from cases import Case, Forest, get_case
 
 pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -49,19 +49,40 @@ def test_factor_matches_reference(kind, size, ordering):
 
 
 def test_golden_fixtures_on_gpu():
+    """Every committed fixture, the reference's five ctest matrices included: bcsstk01/02 and can___24 (real
+    symmetric), c.tri (complex Hermitian), lp_afiro (unsymmetric: A*A' + 1e-6 I through the A*F seam)."""
+    seen = set()
     for f in sorted(glob.glob(os.path.join(HERE, "golden", "*.npz"))):
-        if os.path.basename(f).startswith("demo_"):
-            continue                    # CPU-side pinning of the oracle only (tests/test_oracle.py)
         g = np.load(f)
+        seen.add(os.path.basename(f)[:-4])
         sym = dict(n=int(g["n"]), nsuper=int(g["nsuper"]), xsize=int(g["xsize"]), super=g["super"], pi=g["pi"],
                    px=g["px"], s=g["s"])
         F = b200.Factor(sym, dtype=g["Sx"].dtype, device=0)      # the Hermitian fixtures are complex128
-        st, Lx = F.super_numeric(g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]))
+        if int(g["stype"]) == 0:
+            st, Lx = F.super_numeric_aat(int(g["ncol"]), g["Sp"], g["Si"], g["Sx"], g["Fp"], g["Fi"], g["Fx"],
+                                         beta=float(g["beta"]))
+        else:
+            st, Lx = F.super_numeric(g["Sp"], g["Si"], g["Sx"], beta=float(g["beta"]))
         assert st == int(g["status"]) and F.minor == int(g["minor"]), f
         Lref = g["Lx"]
         assert np.max(np.abs(Lx - Lref)) <= TOL_L * max(1.0, np.max(np.abs(Lref))), f
         assert np.array_equal(Lx == 0, Lref == 0), f
         F.close()
+    assert {"bcsstk01", "bcsstk02", "demo_lp_afiro", "demo_c", "demo_can24"} <= seen
+
+
+@pytest.mark.parametrize("kind,size,ordering,copies", [("lap3d7", 12, refd.CHOLMOD_METIS, 8),
+                                                       ("lap2d9", 30, refd.CHOLMOD_METIS, 16)])
+def test_block_diagonal_forest(kind, size, ordering, copies):
+    """kron(I_k, A): the etree is a forest of k equal trees, the subtree-group fork of the plan runs to the
+    last level, and the host copy of L->x must still be complete (it is all the drop-in call returns)."""
+    f = Forest(get_case(kind, size, ordering), copies)
+    F = b200.Factor(f.sym, device=0)
+    Lx = np.full(f.sym["xsize"], np.nan)
+    st, Lx = F.super_numeric(f.Sp, f.Si, f.Sx, Lx=Lx)
+    assert st == b200.OK and np.all(np.isfinite(Lx)) and f.rel_err(Lx) <= TOL_L
+    assert f.rel_err(F.download_factor()) <= TOL_L
+    F.close()
 
 
 def test_port_agrees_too():
@@ -232,3 +253,45 @@ def test_full_size_properties_config2_shape():
     host[:] = Lx
     assert ref.resid(ref.solve(b), b) <= TOL_RES
     F.close()
+
+
+def _full_size(kind, size, single=False):
+    """Reference analysis + reference CPU factor + our factor at a BASELINE.json size; returns the two figures of
+    north_star: max|dL|/max|L| and the scaled residual of our device solve."""
+    n, Ap, Ai, Ax = getattr(M, kind)(size)
+    ref = refd.Ref(0)
+    ref.set_matrix(n, Ap, Ai, Ax, -1, single=single)
+    ref.analyze(refd.CHOLMOD_METIS, refd.CHOLMOD_SUPERNODAL)
+    sym = ref.symbolic()
+    Sp, Si, Sx = ref.seam()
+    dt = np.float32 if single else np.float64
+    F = b200.Factor(sym, dtype=dt, device=0)
+    st, Lx = F.super_numeric(Sp, Si, Sx)
+    assert st == b200.OK and F.minor == n
+    assert ref.factorize(0.0) == 0
+    Lref = ref.Lx()
+    scale = float(np.max(np.abs(Lref)))
+    err = 0.0
+    for a in range(0, Lx.size, 1 << 26):            # chunked: the factors are gigabytes
+        err = max(err, float(np.max(np.abs(Lx[a:a + (1 << 26)].astype(np.float64) - Lref[a:a + (1 << 26)]))))
+    b = M.rhs(n)
+    x = unpermute(sym, F.solve(b[sym["Perm"]]))
+    res = ref.resid(x, b)
+    F.close()
+    ref.close()
+    return err / scale, res
+
+
+@pytest.mark.slow
+@pytest.mark.parametrize("kind,size,single,tol_l,tol_r", [
+    ("lap3d7", 100, False, TOL_L, TOL_RES),         # config 2 itself (root supernode: 14.9k columns)
+    ("el27", 40, False, TOL_L, TOL_RES),            # config 3 shape at 40^3 x 3 dof
+    ("lap2d9", 1000, False, TOL_L, TOL_RES),        # config 5 shape at 1000^2, double ...
+    ("lap2d9", 1000, True, 1e-4, 1e-5),             # ... and single (config 5b)
+])
+def test_factor_values_at_benchmark_sizes(kind, size, single, tol_l, tol_r):
+    """north_star's value bar where the big fronts stress it: explicit 64 x 64 inverses instead of
+    substitution, split-K atomics, thousands of accumulated updates per entry."""
+    err, res = _full_size(kind, size, single)
+    assert err <= tol_l, err
+    assert res <= tol_r, res

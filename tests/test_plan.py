@@ -10,7 +10,7 @@ import pytest
 
 from oracle import refd
 from suitesparse_b200 import b200
-from cases import Case, CaseAAT, get_case
+from cases import Case, CaseAAT, Forest, get_case
 import plan_interp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -266,3 +266,34 @@ def test_plan_on_golden_fixtures():
             assert np.max(np.abs(Lx - Lref)) <= 1e-12 * max(1.0, np.max(np.abs(Lref))), f
         else:
             assert minor == int(g["minor"]), f      # the kernels' atomicMin finds the reference's L->minor
+
+
+@needs_ref
+@pytest.mark.parametrize("kind,size,ordering,copies", [("lap3d7", 12, refd.CHOLMOD_METIS, 8),
+                                                       ("lap2d9", 30, refd.CHOLMOD_METIS, 16)])
+def test_forest_whose_fork_runs_to_the_last_level_is_still_copied_out(kind, size, ordering, copies):
+    """kron(I_k, A) has k roots: no level has fewer than 8 supernodes, so the subtree-group fork of the
+    single-GPU plan covers everything up to the last level and no checkpoint follows it.  The copy-out
+    schedule must still deliver every value of L->x (the drop-in calls return nothing else)."""
+    f = Forest(get_case(kind, size, ordering), copies)
+    F = b200.Factor(f.sym, device=-1)
+    assert F.geti("ngroups") > 1 and F.geti("fork_hi") == F.geti("nlevels")
+    copies_tab = F.plan_table("copies", b200.COPY_DT)
+    assert copies_tab["len"].sum() == f.sym["xsize"]
+    for prefer in (0, 1):
+        Lx = np.zeros(f.sym["xsize"])
+        host = np.full(f.sym["xsize"], np.nan)
+        plan_interp.scatter_A(f.sym, f.Sp, f.Si, f.Sx, 0.0, Lx)
+        assert plan_interp.run_plan(F, Lx, prefer=prefer, host=host) is None
+        assert f.rel_err(Lx) <= 1e-12
+        assert np.array_equal(host, Lx)
+    F.close()
+
+
+def test_tile_indices_are_32_bit():
+    """build_plan admits supernodes of up to 2^30 rows, i.e. 2^25 SIMT tile rows: UpdTile.ti/tj must not be
+    16-bit.  (A supernode that tall cannot be planned on the CPU box -- its ancestors are dense -- so the
+    check is on the exported table layout the kernels and the interpreter share.)"""
+    assert b200.TILE_DT["ti"].itemsize == 4 and b200.TILE_DT["tj"].itemsize == 4 and b200.TILE_DT.itemsize == 20
+    hdr = open(os.path.join(ROOT, "suitesparse_b200", "csrc", "plan.hpp")).read()
+    assert re.search(r"int32_t\s+ti\s*,\s*tj", hdr) and "uint16_t" not in hdr

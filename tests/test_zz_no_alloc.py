@@ -112,6 +112,9 @@ def test_noalloc_rejects_what_the_fixed_scratch_cannot_hold():
         b200.panel_factor_noalloc(buf.data_ptr(), b200.NOALLOC_MAX_ROWS + 1, b200.NOALLOC_MAX_ROWS + 1, 8)
     assert e.value.status == b200.TOO_LARGE
     with pytest.raises(b200.B200Error) as e:
+        b200.panel_factor_noalloc(buf.data_ptr(), 2 ** 31, 16, 8)    # lda does not fit the 32-bit descriptors
+    assert e.value.status == b200.TOO_LARGE
+    with pytest.raises(b200.B200Error) as e:
         b200.panel_factor_noalloc(0, 10, 10, 4)
     assert e.value.status == b200.INVALID
     with pytest.raises(b200.B200Error) as e:
