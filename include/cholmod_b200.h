@@ -50,6 +50,13 @@ int b200_device_count (void) ;
  * Returns B200_OK or B200_GPU_PROBLEM. */
 int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes) ;
 
+/* Cap, in bytes, on the device memory all contexts of this library may hold together on `device` (0 = no cap,
+ * the default).  b200_create / b200_create_dist fail with B200_OUT_OF_MEMORY, before allocating anything,
+ * when the new context (symbolic tables + plan + the L->x arena) would not fit under it.  Replaces the pool
+ * sizing of cholmod_l_gpu_allocate from Common->maxGpuMemBytes / maxGpuMemFraction and CHOLMOD_GPU_MEM_BYTES /
+ * CHOLMOD_GPU_MEM_FRACTION (CHOLMOD/GPU/cholmod_gpu.c:426-543, cholmod_super_symbolic.c:264-281). */
+int b200_set_memory_limit (int device, size_t bytes) ;
+
 /* Build the context for one supernodal symbolic factor: L->super [nsuper+1], L->pi [nsuper+1],
  * L->px [nsuper+1], L->s [pi[nsuper]] exactly as cholmod_super_symbolic2 produced them
  * (CHOLMOD/Supernodal/cholmod_super_symbolic.c:147-938).  Computes -- on the host, once -- everything
@@ -84,12 +91,14 @@ int b200_comm_init (b200_factor *f, const void *id128) ;
 /* Release everything.  Replaces cholmod_l_gpu_deallocate / gpu_end (cholmod_gpu.c:187-228, :319-420). */
 void b200_destroy (b200_factor *f) ;
 
-/* Integer property of the context by name: "n", "nsuper", "xsize", "nlevels", "npairs",
+/* Integer property of the context by name: "n", "nsuper", "xsize", "nlevels", "npairs", "npairs_gemm" (pairs
+ * with rows below the ancestor's columns: the reference's dgemm calls), "nsuper_trsm" (its dtrsm calls),
  * "relmap_len", "ntiles", "nlaunches", "device_bytes", "device", "kernel_launches" (kernels launched
  * by the last factorization), "ngpus".  Returns -1 for an unknown name. */
 int64_t b200_get_int (const b200_factor *f, const char *name) ;
 
-/* Floating-point property by name: "flops_executed" (supernodal flop count of the plan:
+/* Floating-point property by name: "flops_syrk", "flops_gemm", "flops_potrf", "flops_trsm" (the flops of the
+ * reference's four BLAS/LAPACK call kinds), "flops_executed" (supernodal flop count of the plan:
  * sum over pairs of ndcol*ndrow1*(2*ndrow2-ndrow1) plus nscol^3/3 + nscol^2*(nsrow-nscol) per
  * supernode), "ms_factor" (device time of the last b200_factor_device, CUDA events), "ms_h2d",
  * "ms_d2h", "ms_scatter", "ms_solve".  Returns -1 for an unknown name. */
@@ -100,7 +109,9 @@ double b200_get_double (const b200_factor *f, const char *name) ;
  * the symmetric case (A->stype < 0, F unused): A = tril (P A P') in CSC (Ap [n+1], Ai, Ax; Anz [n]
  * non-NULL iff A is unpacked; columns may be unsorted; entries outside the pattern of L are dropped,
  * :455-468), beta [0] is added to the diagonal (:510-520).  Fills host Lx [xsize] with the supernodal
- * factor in the reference layout (column-major per supernode, lda = nsrow, :342-348).
+ * factor in the reference layout (column-major per supernode, lda = nsrow, :342-348).  Lx == NULL (any of the
+ * b200_super_numeric_* calls): the factor stays on the device only -- solve with b200_solve_*, fetch it
+ * later with b200_download_factor.
  * Returns B200_OK, or B200_NOT_POSDEF with *minor = the failing column and L zeroed / partially
  * factorized exactly as :1084-1146 prescribe (quick_return_if_not_posdef as in cholmod_common), or a
  * negative status on a fatal error.  *minor = n on success (:1269). */
@@ -181,6 +192,12 @@ int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
 /* The same with a complex factor: X = L^H\(L\B), B and X n-by-nrhs column-major (re,im) pairs of doubles
  * (the "C" variants of the same file). */
 int b200_solve_z (b200_factor *f, const double *B, double *X, int64_t nrhs) ;
+
+/* One sweep only, for callers that drive the two halves themselves as cholmod_solve2 does
+ * (CHOLMOD/Cholesky/cholmod_solve.c:696-708): which = 1 is cholmod_super_lsolve (X = L\B,
+ * CHOLMOD/Supernodal/cholmod_super_solve.c:40-128), which = 2 is cholmod_super_ltsolve (X = L^H\B, :140-230),
+ * which = 3 both (= b200_solve_d / _z).  B and X are doubles, (re,im) pairs for a complex context. */
+int b200_solve_sweep (b200_factor *f, int which, const double *B, double *X, int64_t nrhs) ;
 
 /* --- one panel step without any allocation ---------------------------------------------------------
  * This entry point has no counterpart in the reference.

@@ -27,7 +27,8 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_upload_factor", "b200_solve_d", "b200_version", "b200_set_int", "b200_plan_export",
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
            "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer", "b200_super_numeric_z",
-           "b200_super_numeric_c", "b200_solve_z", "b200_super_numeric_aat", "b200_upload_matrix_aat"]
+           "b200_super_numeric_c", "b200_solve_z", "b200_super_numeric_aat", "b200_upload_matrix_aat",
+           "b200_solve_sweep", "b200_set_memory_limit"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -82,6 +83,8 @@ def lib():
     L.b200_comm_init.argtypes = [vp, vp]; L.b200_comm_init.restype = cint
     L.b200_upload_values.argtypes = [vp, vp]; L.b200_upload_values.restype = cint
     L.b200_forget_host_buffer.argtypes = [vp, vp]; L.b200_forget_host_buffer.restype = cint
+    L.b200_solve_sweep.argtypes = [vp, cint, vp, vp, i64]; L.b200_solve_sweep.restype = cint
+    L.b200_set_memory_limit.argtypes = [cint, C.c_size_t]; L.b200_set_memory_limit.restype = cint
     _lib = L
     return L
 
@@ -92,6 +95,13 @@ def device_count():
 
 def probe(device=0):
     return bool(lib().b200_probe(int(device)))
+
+
+def set_memory_limit(device, nbytes):
+    """Cap on the device memory this library's contexts may hold on `device` (0 = none)."""
+    st = lib().b200_set_memory_limit(int(device), int(nbytes))
+    if st < 0:
+        raise B200Error(st, "b200_set_memory_limit")
 
 
 def panel_factor_noalloc(d_panel, lda, nrows, jb, stream=0):
@@ -309,6 +319,16 @@ class Factor:
         st = fn(self.h, B.ctypes.data, X.ctypes.data, nrhs)
         if st < 0:
             raise B200Error(st, "b200_solve_d")
+        return X
+
+    def solve_sweep(self, which, B):
+        """One half of the solve: which = 1 forward (L y = b), 2 backward (L^H x = y), 3 both."""
+        B = np.asfortranarray(B, dtype=np.complex128 if self.is_complex else np.float64)
+        nrhs = 1 if B.ndim == 1 else B.shape[1]
+        X = np.empty_like(B, order="F")
+        st = self.L.b200_solve_sweep(self.h, int(which), B.ctypes.data, X.ctypes.data, nrhs)
+        if st < 0:
+            raise B200Error(st, "b200_solve_sweep")
         return X
 
     # -- plan introspection (tests of the host planner) ------------------------------------------------

@@ -10,6 +10,7 @@
 #include <new>
 #include <vector>
 #include <type_traits>
+#include <mutex>
 #include <dlfcn.h>
 #include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
 
@@ -37,6 +38,8 @@ NcclApi *nccl_api ()
 {
     static NcclApi api ;
     static bool tried = false ;
+    static std::mutex lock ;
+    std::lock_guard<std::mutex> guard (lock) ;
     if (tried) return api.ok ? &api : nullptr ;
     tried = true ;
     api.handle = dlopen ("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL) ;
@@ -149,6 +152,7 @@ struct b200_factor
     std::vector<float> ms_launch, ms_launch_start ;     // profile mode: duration / start time of every plan launch
     float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
     size_t device_bytes = 0 ;
+    bool mem_counted = false ;              // device_bytes is part of g_mem_held [device]
 } ;
 
 namespace {
@@ -187,9 +191,17 @@ int set_device (const b200_factor *f)
 }
 
 bool g_attr_done [64] = {} ;
+std::mutex g_attr_lock ;
+
+// per-device cap on the device memory the contexts of this library may hold together (0 = no cap), and what
+// they hold now: the counterpart of the pool cholmod_l_gpu_allocate sizes from Common->maxGpuMemBytes /
+// maxGpuMemFraction (CHOLMOD/GPU/cholmod_gpu.c:426-543)
+std::mutex g_mem_lock ;
+size_t g_mem_limit [64] = {}, g_mem_held [64] = {} ;
 
 int kernel_attrs (int device)
 {
+    std::lock_guard<std::mutex> guard (g_attr_lock) ;
     if (device < 64 && g_attr_done [device]) return B200_OK ;
     CK (cudaFuncSetAttribute (k_upd_dmma<BIG_TM, BIG_TN, 32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
         (int) dmma_smem_bytes<BIG_TM, BIG_TN> ()), "attr d128") ;
@@ -566,6 +578,21 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         for (auto &e : f->ev_comm) CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "event") ;
     }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
+    {
+        // refuse before allocating anything if the context cannot fit under the cap set for this device
+        const size_t need = (size_t) (3 * (P.nsuper + 1)) * 8 + (size_t) P.ssize * 4 + (size_t) P.n * 4 + P.relmap.size () * 4
+            + (size_t) P.nsuper * 4 + P.items.size () * sizeof (UpdItem) + P.tiles.size () * sizeof (UpdTile)
+            + P.potrf.size () * sizeof (PotrfBlk) + P.trsm.size () * sizeof (TrsmTile) + (size_t) P.xsize * f->esize
+            + (size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize ;
+        std::lock_guard<std::mutex> guard (g_mem_lock) ;
+        const int d = f->device ;
+        if (d < 64 && g_mem_limit [d] > 0 && g_mem_held [d] + need > g_mem_limit [d])
+        {
+            fprintf (stderr, "cholmod_b200: context needs %.1f MB on device %d, over the limit of %.1f MB (%.1f MB held)\n",
+                need / 1048576.0, d, g_mem_limit [d] / 1048576.0, g_mem_held [d] / 1048576.0) ;
+            return B200_OUT_OF_MEMORY ;
+        }
+    }
     std::vector<int32_t> Ls32 ((size_t) P.ssize) ;
     for (int64_t k = 0 ; k < P.ssize ; k++) Ls32 [k] = (int32_t) Ls [k] ;
     cudaStream_t s = f->stream ;
@@ -589,6 +616,12 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     f->device_bytes = f->d_super.bytes () + f->d_pi.bytes () + f->d_px.bytes () + f->d_Ls.bytes ()
         + f->d_supermap.bytes () + f->d_relmap.bytes () + f->d_level_list.bytes () + f->d_items.bytes ()
         + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () + f->d_winv.bytes () ;
+    if (f->device < 64)
+    {
+        std::lock_guard<std::mutex> guard (g_mem_lock) ;
+        g_mem_held [f->device] += f->device_bytes ;
+        f->mem_counted = true ;
+    }
     return B200_OK ;
 }
 
@@ -627,9 +660,22 @@ b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, 
     return f ;
 }
 
+int b200_set_memory_limit (int device, size_t bytes)
+{
+    if (device < 0 || device >= 64) return B200_INVALID ;
+    std::lock_guard<std::mutex> guard (g_mem_lock) ;
+    g_mem_limit [device] = bytes ;
+    return B200_OK ;
+}
+
 void b200_destroy (b200_factor *f)
 {
     if (!f) return ;
+    if (f->mem_counted && f->device >= 0 && f->device < 64)
+    {
+        std::lock_guard<std::mutex> guard (g_mem_lock) ;
+        g_mem_held [f->device] -= std::min (g_mem_held [f->device], f->device_bytes) ;
+    }
     if (f->device >= 0 && f->stream)
     {
         cudaSetDevice (f->device) ;
@@ -669,6 +715,8 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "ssize")) return P.ssize ;
     if (!strcmp (name, "nlevels")) return P.nlevels ;
     if (!strcmp (name, "npairs")) return P.npairs ;
+    if (!strcmp (name, "npairs_gemm")) return P.npairs_gemm ;
+    if (!strcmp (name, "nsuper_trsm")) return P.nsuper_trsm ;
     if (!strcmp (name, "relmap_len")) return (int64_t) P.relmap.size () ;
     if (!strcmp (name, "nitems")) return (int64_t) P.items.size () ;
     if (!strcmp (name, "ntiles")) return (int64_t) P.tiles.size () ;
@@ -711,6 +759,8 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "flops_update")) return P.flops_update ;
     if (!strcmp (name, "flops_potrf")) return P.flops_potrf ;
     if (!strcmp (name, "flops_trsm")) return P.flops_trsm ;
+    if (!strcmp (name, "flops_syrk")) return P.flops_syrk ;
+    if (!strcmp (name, "flops_gemm")) return P.flops_gemm ;
     if (!strcmp (name, "ms_factor")) return f->ms_factor ;
     if (!strcmp (name, "ms_h2d")) return f->ms_h2d ;
     if (!strcmp (name, "ms_d2h")) return f->ms_d2h ;
@@ -868,7 +918,19 @@ int b200_upload_values (b200_factor *f, const void *Ax)
 // pin the caller's L->x once: later factorizations into the same buffer then copy at PCIe speed
 static void ensure_registered (b200_factor *f, void *Lx, size_t bytes)
 {
-    if (f->reg_ptr == Lx && f->reg_bytes == bytes) return ;
+    if (f->reg_ptr == Lx && f->reg_bytes == bytes)
+    {
+        // same address and size as last time -- but the caller may have freed and re-obtained the memory in
+        // between without telling us (b200_forget_host_buffer): ask the driver whether the first and the last
+        // page are still page-locked mappings before trusting the registration
+        unsigned fl = 0 ;
+        if (bytes == 0 || (cudaHostGetFlags (&fl, Lx) == cudaSuccess
+            && cudaHostGetFlags (&fl, (char *) Lx + (bytes - 1)) == cudaSuccess)) return ;
+        cudaGetLastError () ;
+        cudaHostUnregister (f->reg_ptr) ;
+        cudaGetLastError () ;
+        f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+    }
     if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
     if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterDefault) == cudaSuccess)
     {
@@ -991,8 +1053,7 @@ int b200_super_numeric_d (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
     if (!f || f->dtype != B200_DOUBLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
     int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
     if (st < 0) return st ;
-    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
-    ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (double)) ;
+    if (Lx) ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (double)) ;
     return factor_device_T<double> (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
@@ -1002,8 +1063,7 @@ int b200_super_numeric_s (b200_factor *f, const int64_t *Ap, const int64_t *Ai, 
     if (!f || f->dtype != B200_SINGLE) return f ? B200_INVALID : B200_GPU_PROBLEM ;
     int st = b200_upload_matrix (f, Ap, Ai, Anz, Ax) ;
     if (st < 0) return st ;
-    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
-    ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (float)) ;
+    if (Lx) ensure_registered (f, Lx, (size_t) f->plan.xsize * sizeof (float)) ;
     return factor_device_T<float> (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
@@ -1034,8 +1094,7 @@ static int super_numeric_complex (b200_factor *f, const int64_t *Ap, const int64
     }
     int st = b200_upload_matrix (f, Ap, Ai, Anz, vals) ;
     if (st < 0) return st ;
-    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
-    ensure_registered (f, Lx, (size_t) f->plan.xsize * 2 * sizeof (R)) ;
+    if (Lx) ensure_registered (f, Lx, (size_t) f->plan.xsize * 2 * sizeof (R)) ;
     return factor_device_T<cx<R>> (f, beta, quick, minor, Lx) ;
 }
 
@@ -1090,15 +1149,15 @@ int b200_super_numeric_aat (b200_factor *f, int64_t ncol, const int64_t *Ap, con
     if ((Az && !av) || (Fz && !fv)) return B200_INVALID ;
     int st = b200_upload_matrix_aat (f, ncol, Ap, Ai, Anz, av, Fp, Fi, Fnz, fv) ;
     if (st < 0) return st ;
-    if (!Lx && f->plan.xsize > 0) return B200_INVALID ;
-    ensure_registered (f, Lx, (size_t) f->plan.xsize * f->esize) ;
+    if (Lx) ensure_registered (f, Lx, (size_t) f->plan.xsize * f->esize) ;
     return B200_DISPATCH (f->dtype, factor_device_T) (f, beta, quick_return_if_not_posdef, minor, Lx) ;
 }
 
 }   // extern "C"
 
+// which: bit 0 = the forward sweep (L y = b), bit 1 = the backward sweep (L^H x = y)
 template <typename T>
-static int solve_T (b200_factor *f, int nrhs)
+static int solve_T (b200_factor *f, int nrhs, int which)
 {
     const Plan &P = f->plan ;
     cudaStream_t s = f->stream ;
@@ -1187,6 +1246,11 @@ static int solve_T (b200_factor *f, int nrhs)
         }
     for (size_t pass = 0 ; pass < 2 ; pass++)
     {
+        if (!(which & (1 << pass))) continue ;
+        // the wide supernodes hand their forward results to the backward sweep through Y: a backward sweep on its
+        // own starts from the right-hand side there too
+        if (pass == 1 && which == 2 && nblk > 0)
+            CK (cudaMemcpyAsync (Y, X, (size_t) P.n * (size_t) nrhs * sizeof (XT), cudaMemcpyDeviceToDevice, s), "solve Y <- X") ;
         for (size_t q = 0 ; q < nl ; q++)
         {
             const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
@@ -1214,6 +1278,9 @@ static int solve_T (b200_factor *f, int nrhs)
             }
             if (f->profile) cudaEventRecord (f->prof_ev [nev++], s) ;
         }
+        // a forward sweep on its own: gather the wide supernodes' results (in Y) into X
+        if (pass == 0 && which == 1 && nblk > 0)
+            k_solve_merge<XT><<<(unsigned) nblk, 64, 0, s>>> (f->d_sblk.p, f->d_super.p, X, Y, P.n, nrhs) ;
     }
     CK (cudaGetLastError (), "solve kernels") ;
     if (f->profile)
@@ -1225,7 +1292,7 @@ static int solve_T (b200_factor *f, int nrhs)
             for (size_t q = 0 ; q < nl ; q++)
             {
                 const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
-                if (L.count <= 0) continue ;
+                if (L.count <= 0 || !(which & (1 << pass))) continue ;
                 float ms = 0 ;
                 cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
                 e += 2 ;
@@ -1238,10 +1305,10 @@ static int solve_T (b200_factor *f, int nrhs)
 
 extern "C" {
 
-static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs, bool want_complex)
+static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs, bool want_complex, int which = 3)
 {
     int st = set_device (f) ; if (st) return st ;
-    if (dtype_complex (f->dtype) != want_complex) return B200_INVALID ;
+    if (dtype_complex (f->dtype) != want_complex || which < 1 || which > 3) return B200_INVALID ;
     const int64_t n = f->plan.n ;
     if (nrhs < 0 || (!B && n * nrhs > 0) || (!X && n * nrhs > 0)) return B200_INVALID ;
     if (n == 0 || nrhs == 0) return B200_OK ;
@@ -1251,7 +1318,7 @@ static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs,
     cudaStream_t s = f->stream ;
     CK (cudaMemcpyAsync (f->d_X.p, B, cnt * 8, cudaMemcpyHostToDevice, s), "H2D B") ;
     CK (cudaEventRecord (f->ev [0], s), "record") ;
-    st = B200_DISPATCH (f->dtype, solve_T) (f, (int) nrhs) ;
+    st = B200_DISPATCH (f->dtype, solve_T) (f, (int) nrhs, which) ;
     if (st) return st ;
     CK (cudaEventRecord (f->ev [1], s), "record") ;
     CK (cudaMemcpyAsync (X, f->d_X.p, cnt * 8, cudaMemcpyDeviceToHost, s), "D2H X") ;
@@ -1268,6 +1335,12 @@ int b200_solve_d (b200_factor *f, const double *B, double *X, int64_t nrhs)
 int b200_solve_z (b200_factor *f, const double *B, double *X, int64_t nrhs)
 {
     return solve_host (f, B, X, nrhs, true) ;
+}
+
+int b200_solve_sweep (b200_factor *f, int which, const double *B, double *X, int64_t nrhs)
+{
+    if (!f) return B200_GPU_PROBLEM ;
+    return solve_host (f, B, X, nrhs, dtype_complex (f->dtype), which) ;
 }
 
 }   // extern "C"

@@ -1758,4 +1758,16 @@ __global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__rest
     }
 }
 
+// After a forward sweep on its own (cholmod_super_lsolve without the ltsolve that normally follows): the
+// results of the wide supernodes' columns are in Y, everything else in X; gather them into X.
+template <typename XT>
+__global__ void __launch_bounds__ (64) k_solve_merge (const SolveBlk *__restrict__ blks, const int64_t *__restrict__ super,
+    XT *X, const XT *__restrict__ Y, int64_t n, int nrhs)
+{
+    const SolveBlk b = blks [blockIdx.x] ;
+    const int64_t at = super [b.s] + b.c0 + threadIdx.x ;
+    if ((int) threadIdx.x < b.jb)
+        for (int rhs = 0 ; rhs < nrhs ; rhs++) X [(int64_t) rhs * n + at] = Y [(int64_t) rhs * n + at] ;
+}
+
 }   // namespace b200

@@ -653,6 +653,9 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
             pairs.push_back (pr) ;
             tcount [s+1]++ ;
             P.flops_update += (double) ndcol * (double) pr.ndrow1 * (2.0 * pr.ndrow2 - pr.ndrow1) ;
+            P.flops_syrk += (double) ndcol * (double) pr.ndrow1 * (double) pr.ndrow1 ;
+            P.flops_gemm += 2.0 * (double) ndcol * (double) pr.ndrow1 * (double) (pr.ndrow2 - pr.ndrow1) ;
+            if (pr.ndrow2 > pr.ndrow1) P.npairs_gemm++ ;
             p = q ;
         }
     }
@@ -708,6 +711,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         double nscol = (double) (super [s+1] - super [s]), nsrow = (double) (pi [s+1] - pi [s]) ;
         P.flops_potrf += nscol * nscol * nscol / 3.0 ;
         P.flops_trsm += nscol * nscol * (nsrow - nscol) ;
+        if (nsrow > nscol) P.nsuper_trsm++ ;
     }
 
     // who owns what

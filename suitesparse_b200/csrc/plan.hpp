@@ -111,6 +111,10 @@ struct Plan
     int32_t nlevels = 0 ;
     int64_t npairs = 0 ;
     double flops_update = 0, flops_potrf = 0, flops_trsm = 0 ;
+    // the reference's BLAS call statistics (cholmod_gpu_stats): one dsyrk per pair, one dgemm per pair with rows
+    // below the ancestor's columns, one dpotrf per supernode, one dtrsm per supernode with rows below its block
+    double flops_syrk = 0, flops_gemm = 0 ;
+    int64_t npairs_gemm = 0, nsuper_trsm = 0 ;
     double flops_kind [K_NKINDS] = {} ;     // algorithmic flops executed by each launch kind
     int64_t count_kind [K_NKINDS] = {} ;    // list entries (tiles / blocks) per launch kind
     int64_t winv_slots = 0 ;                // inverse slots (64 x 64 values each) the largest launch needs
