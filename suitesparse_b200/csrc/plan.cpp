@@ -134,20 +134,34 @@ void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_e
     P.launches.back ().rec_ev = rec_ev ;
 }
 
-// The descendant updates into supernode s.  A target that is split over the ranks (top) gets each update
-// as slabs of target columns, one slab per outer block, and this rank keeps the slabs of the blocks it
-// owns: a slab [ja, jb) of an item is the item of the panel rows ja.. (B = its first jb-ja rows), so the
-// same kernels apply.
+// The descendant updates into supernode s; `px` holds the ARENA offsets of the supernodes (Plan::dpx).
+//
+// One GPU (and repair plans): every pair, whole.
+// Distributed, `which` selects the part of the work that is planned:
+//   UPD_ALL            s is an ordinary supernode of one of this rank's subtrees: all its descendants are in the
+//                      same subtree, every pair whole;
+//   UPD_FROM_SUBTREES  s is a top separator: the pairs whose descendant belongs to one of THIS rank's subtrees,
+//                      whole, into this rank's own copy of s -- its contribution block, which the owners of the
+//                      blocks of s later pull (K_PULL);
+//   UPD_FROM_TOP       s is a top separator: the pairs whose descendant is a top separator too (its panels have
+//                      been broadcast).  Each pair is cut into slabs of target columns, one slab per outer block,
+//                      and this rank keeps the slabs of the blocks it owns: a slab [ja, jb) of an item is the item
+//                      of the panel rows ja.. (B = its first jb-ja rows), so the same kernels apply.
+enum { UPD_ALL = 0, UPD_FROM_SUBTREES = 1, UPD_FROM_TOP = 2 } ;
+
 void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t *super, const int64_t *pi,
-    const int64_t *px, int64_t s, TileSink &sink, bool use_dmma)
+    const int64_t *px, int64_t s, TileSink &sink, bool use_dmma, int which = UPD_ALL)
 {
-    const bool split = own.is_top (s) ;
-    if (!split && !own.mine (s, 0)) return ;
+    const bool dist = own.dist () ;
+    const bool split = own.is_top (s) && which == UPD_FROM_TOP ;
+    if (dist && which == UPD_ALL && (own.is_top (s) || !own.mine (s, 0))) return ;
     for (int64_t t = P.target_ptr [s] ; t < P.target_ptr [s+1] ; t++)
     {
         const int32_t pid = P.target_list [t] ;
         const Pair &pr = P.pairs [pid] ;
         const int64_t d = pr.d ;
+        if (dist && which == UPD_FROM_SUBTREES && (P.top [d] || P.owner [d] != P.rank)) continue ;
+        if (dist && which == UPD_FROM_TOP && !P.top [d]) continue ;
         UpdItem it ;
         it.lda = (int32_t) (pi [d+1] - pi [d]) ;
         it.a_off = px [d] + pr.lpos ;
@@ -196,8 +210,10 @@ void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t 
 // later block by that block's owner -- a 1-D block-cyclic right-looking Cholesky.
 void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma,
-    char *copied = nullptr, int sm = 0, int sl = 1, int32_t slot_base = 0)
+    char *copied = nullptr, int sm = 0, int sl = 1, int32_t slot_base = 0, const int64_t *hpx = nullptr)
 {
+    // px: arena offsets (Plan::dpx); hpx: offsets in the caller's L->x (the copy-out needs both; NULL: the same)
+    if (!hpx) hpx = px ;
     // sm / sl: the stream of the panel chain and the look-ahead stream of this call (0 / 1 unless the level
     // is being factorized group by group, see build_plan); slot_base: first inverse slot it may use
     int64_t maxcol = 0 ;
@@ -375,10 +391,17 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             {
                 const int64_t s = S [q] ;
                 const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
-                if (nscol <= OUTER_NB || nscol <= J0) continue ;
-                if (!own.is_top (s) && !own.mine (s, 0)) continue ;     // arrives later, with its subtree
+                if (own.is_top (s))
+                {
+                    // a block of a top separator goes to the host from the rank that owns (and has just
+                    // factorized) it -- every rank's PCIe link carries its share of L->x
+                    if (nscol <= J0) continue ;
+                    copied [s] = 1 ;
+                    if (!own.mine (s, T)) continue ;
+                }
+                else if (nscol <= OUTER_NB || nscol <= J0 || !own.mine (s, 0)) continue ;
                 const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
-                CopySeg c ; c.off = px [s] + J0 * nsrow ; c.len = (Jend - J0) * nsrow ;
+                CopySeg c ; c.off = px [s] + J0 * nsrow ; c.len = (Jend - J0) * nsrow ; c.hoff = hpx [s] + J0 * nsrow ;
                 out.copies.push_back (c) ;
                 copied [s] = 1 ;
             }
@@ -467,6 +490,21 @@ int partition (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *
     }
     const double thresh = total / (4.0 * R) ;
     for (int64_t s = 0 ; s < nsuper ; s++) P.top [s] = (sub [s] > thresh) ? 1 : 0 ;
+    // a subtree's owner also computes the updates of its supernodes into the top separators (its
+    // contribution blocks): that work counts towards the subtree's load
+    {
+        std::vector<double> out ((size_t) nsuper, 0.0) ;
+        for (const Pair &pr : P.pairs)
+            if (!P.top [pr.d] && P.top [pr.s])
+                out [pr.d] += (double) (super [pr.d+1] - super [pr.d]) * pr.ndrow1 * (2.0 * pr.ndrow2 - pr.ndrow1) ;
+        for (int64_t s = 0 ; s < nsuper ; s++)
+        {
+            if (P.top [s]) continue ;
+            sub [s] += out [s] ;
+            const int64_t p = P.parent [s] ;
+            if (p >= 0 && !P.top [p]) out [p] += out [s] ;
+        }
+    }
     // local subtree roots, largest first, to the least loaded rank
     std::vector<int64_t> roots ;
     for (int64_t s = 0 ; s < nsuper ; s++)
@@ -559,16 +597,195 @@ void plan_groups (Plan &P, const int64_t *super, const int64_t *pi)
     P.ngroups = G ; P.fork_lo = lo ; P.fork_hi = hi ;
 }
 
+// The distributed plan of rank P.rank.
+//
+//   arena     the top separators first, at the same offsets on every rank, then this rank's subtrees; other
+//             ranks' subtrees are not stored here at all
+//   phase A   this rank's subtrees, level by level -- no other rank is involved.  Then, into this rank's own
+//             (zero-initialised) copies of the top separators, every update that a supernode of its subtrees
+//             sends there: the rank's CONTRIBUTION BLOCKS
+//   fan-in    all ranks meet (K_BARRIER); the owner of each 256-column block of a top separator adds the
+//             other ranks' contribution blocks to its own, reading them straight out of their arenas (K_PULL)
+//   phase B   the top separators, level by level, 1-D block cyclic: updates between top separators by the
+//             owners of the target blocks, panel chain by the block's owner, finished panels broadcast
+//   copy-out  every rank sends what it owns -- its subtrees after phase A, its blocks of the top separators as
+//             they are finished -- to the same host L->x, each over its own PCIe link
+int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *px, bool use_dmma)
+{
+    const int64_t nsuper = P.nsuper ;
+    const int rank = P.rank, R = P.nranks ;
+    const Own own { &P, false } ;
+    const int nlevels = P.nlevels ;
+    const int64_t last = (P.trunc_s >= 0) ? P.trunc_s : nsuper - 1 ;       // nothing after `last` is computed
+    if (R > 32) return B200_TOO_LARGE ;                                      // PullSeg::mask
+    auto ncol_of = [&] (int64_t s) -> int64_t
+    {
+        return (s == P.trunc_s) ? P.trunc_ncol : super [s+1] - super [s] ;
+    } ;
+
+    // ---- arena layout -------------------------------------------------------------------------------------
+    P.dpx.assign ((size_t) nsuper + 1, -1) ;
+    int64_t at = 0 ;
+    for (int64_t s = 0 ; s < nsuper ; s++) if (P.top [s]) { P.dpx [s] = at ; at += px [s+1] - px [s] ; }
+    P.top_size = at ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+        if (!P.top [s] && P.owner [s] == rank) { P.dpx [s] = at ; at += px [s+1] - px [s] ; }
+    P.dxsize = at ;
+    P.dpx [nsuper] = at ;
+    const int64_t *dpx = P.dpx.data () ;
+
+    // ---- who scatters which column of A, and what this rank owns ---------------------------------------------
+    P.colmine.assign ((size_t) P.n, 0) ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        const int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
+        if (!P.top [s])
+        {
+            if (P.owner [s] != rank) continue ;
+            for (int64_t k = super [s] ; k < super [s+1] ; k++) P.colmine [k] = 1 ;
+            if (!P.owned.empty () && P.owned.back ().hoff + P.owned.back ().len == px [s]
+                && P.owned.back ().off + P.owned.back ().len == dpx [s]) P.owned.back ().len += nscol * nsrow ;
+            else P.owned.push_back (CopySeg { dpx [s], nscol * nsrow, px [s] }) ;
+            continue ;
+        }
+        for (int64_t J0 = 0 ; J0 < nscol ; J0 += OUTER_NB)
+        {
+            if (!own.mine (s, J0 / OUTER_NB)) continue ;
+            const int64_t Jend = std::min (nscol, J0 + OUTER_NB) ;
+            for (int64_t k = super [s] + J0 ; k < super [s] + Jend ; k++) P.colmine [k] = 1 ;
+            P.owned.push_back (CopySeg { dpx [s] + J0 * nsrow, (Jend - J0) * nsrow, px [s] + J0 * nsrow }) ;
+        }
+    }
+
+    TileSink sink ;
+    std::vector<int64_t> ncols ;
+    std::vector<int32_t> Sg ;
+    std::vector<char> copied ((size_t) nsuper, 0) ;
+    const bool copy_early = (P.trunc_s < 0) ;       // a truncated (not positive definite) run is copied at its end
+
+    // ---- phase A: this rank's subtrees -----------------------------------------------------------------------
+    for (int lev = 0 ; lev < nlevels ; lev++)
+    {
+        Sg.clear () ;
+        for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++)
+        {
+            const int32_t s = P.level_list [q] ;
+            if (!P.top [s] && P.owner [s] == rank && s <= last && ncol_of (s) > 0) Sg.push_back (s) ;
+        }
+        if (Sg.empty ()) continue ;
+        for (int32_t s : Sg) plan_updates_into (P, P, own, super, pi, dpx, s, sink, use_dmma, UPD_ALL) ;
+        flush_tiles (P, sink, lev) ;
+        ncols.resize (Sg.size ()) ;
+        for (size_t q = 0 ; q < Sg.size () ; q++) ncols [q] = ncol_of (Sg [q]) ;
+        plan_factor (P, own, super, pi, dpx, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma) ;
+    }
+    // the subtrees are final: they can leave for the host while the rest is computed
+    if (copy_early)
+    {
+        const size_t first = P.copies.size () ;
+        for (const CopySeg &c : P.owned) if (c.off >= P.top_size) P.copies.push_back (c) ;
+        if (P.copies.size () > first)
+        {
+            const int ev = P.nevents++ ;
+            Launch J = make_launch (K_JOIN, 0, 0, 0, 0) ; J.rec_ev = ev ;
+            P.launches.push_back (J) ;
+            Launch C = make_launch (K_COPYOUT, (int64_t) first, (int64_t) (P.copies.size () - first), 0, 2) ;
+            C.wait_ev = ev ;
+            P.launches.push_back (C) ;
+        }
+    }
+    // contribution blocks: what this rank's subtrees send into the top separators, into its own copies of them
+    std::vector<uint32_t> contrib ((size_t) nsuper, 0) ;        // ranks that have something for top separator s
+    int first_top_level = nlevels ;
+    for (int64_t s = 0 ; s < nsuper ; s++)
+    {
+        if (!P.top [s]) continue ;
+        first_top_level = std::min<int> (first_top_level, P.level [s]) ;
+        if (s > last || ncol_of (s) == 0) continue ;
+        for (int64_t t = P.target_ptr [s] ; t < P.target_ptr [s+1] ; t++)
+        {
+            const int64_t d = P.pairs [P.target_list [t]].d ;
+            if (!P.top [d]) contrib [s] |= 1u << P.owner [d] ;
+        }
+        plan_updates_into (P, P, own, super, pi, dpx, s, sink, use_dmma, UPD_FROM_SUBTREES) ;
+    }
+    flush_tiles (P, sink, std::max (0, first_top_level - 1)) ;
+
+    // ---- fan-in --------------------------------------------------------------------------------------------------
+    {
+        const int lev = std::max (0, std::min (first_top_level, nlevels - 1)) ;
+        const int evA = P.nevents++, evM = P.nevents++ ;
+        Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evA ;
+        P.launches.push_back (J) ;
+        Launch B = make_launch (K_BARRIER, 0, 0, lev, 3) ; B.wait_ev = evA ; B.rec_ev = evM ;
+        P.launches.push_back (B) ;
+        const size_t first = P.pulls.size () ;
+        for (int64_t s = 0 ; s < nsuper ; s++)
+        {
+            if (!P.top [s] || s > last || ncol_of (s) == 0) continue ;
+            const uint32_t others = contrib [s] & ~(1u << rank) ;
+            if (!others) continue ;
+            int po = 0 ; for (uint32_t m = others ; m ; m &= m - 1) po++ ;
+            const int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
+            for (int64_t J0 = 0 ; J0 < nscol ; J0 += OUTER_NB)
+            {
+                if (!own.mine (s, J0 / OUTER_NB)) continue ;
+                const int64_t Jend = std::min (nscol, J0 + OUTER_NB) ;
+                PullSeg g ;
+                g.off = dpx [s] + J0 + J0 * nsrow ;        // rows J0.. of columns J0..Jend-1: the lower part
+                g.nrows = (int32_t) (nsrow - J0) ; g.ncols = (int32_t) (Jend - J0) ; g.ld = (int32_t) nsrow ;
+                g.mask = others ;
+                P.pulls.push_back (g) ;
+                P.nvlink_in_values += (int64_t) po * g.nrows * g.ncols ;
+            }
+        }
+        Launch W = make_launch (P.pulls.size () > first ? K_PULL : K_JOIN, (int64_t) first,
+            (int64_t) (P.pulls.size () - first), lev, 0) ;
+        W.wait_ev = evM ;
+        P.launches.push_back (W) ;
+    }
+
+    // ---- phase B: the top separators ---------------------------------------------------------------------------
+    for (int lev = 0 ; lev < nlevels ; lev++)
+    {
+        Sg.clear () ;
+        for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++)
+        {
+            const int32_t s = P.level_list [q] ;
+            if (P.top [s] && s <= last && ncol_of (s) > 0) Sg.push_back (s) ;
+        }
+        if (Sg.empty ()) continue ;
+        for (int32_t s : Sg) plan_updates_into (P, P, own, super, pi, dpx, s, sink, use_dmma, UPD_FROM_TOP) ;
+        flush_tiles (P, sink, lev) ;
+        ncols.resize (Sg.size ()) ;
+        for (size_t q = 0 ; q < Sg.size () ; q++) ncols [q] = ncol_of (Sg [q]) ;
+        plan_factor (P, own, super, pi, dpx, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma,
+            copy_early ? copied.data () : nullptr, 0, 1, 0, px) ;
+    }
+    for (const BcastSeg &b : P.bcasts) if (b.root != rank) P.nvlink_in_values += b.len ;
+    if (copy_early)
+    {
+        // together the segments are exactly what this rank owns
+        int64_t a = 0, b = 0 ;
+        for (const CopySeg &c : P.copies) a += c.len ;
+        for (const CopySeg &c : P.owned) b += c.len ;
+        if (a != b) return B200_INVALID ;
+    }
+    return B200_OK ;
+}
+
 }   // namespace
 
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int64_t *Ls, bool use_dmma, Plan &P, int nranks, int rank)
+    const int64_t *Ls, bool use_dmma, Plan &P, int nranks, int rank, int64_t trunc_s, int64_t trunc_ncol)
 {
     if (n < 0 || nsuper < 0 || !super || !pi || !px || (!Ls && nsuper > 0)) return B200_INVALID ;
     if (nranks < 1 || rank < 0 || rank >= nranks) return B200_INVALID ;
     if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
     P = Plan () ;
     P.n = n ; P.nsuper = nsuper ; P.nranks = nranks ; P.rank = rank ;
+    if (trunc_s >= 0 && (nranks == 1 || trunc_s >= nsuper || trunc_ncol < 0)) return B200_INVALID ;
+    P.trunc_s = trunc_s ; P.trunc_ncol = trunc_ncol ;
     // CHOLMOD_B200_PLAN_TIMING=1: where the planner's own time goes (stderr)
     const bool timing = getenv ("CHOLMOD_B200_PLAN_TIMING") != nullptr ;
     auto t_last = std::chrono::steady_clock::now () ;
@@ -585,6 +802,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         if (n != 0) return B200_INVALID ;
         P.level_ptr.assign (1, 0) ;
         P.target_ptr.assign (1, 0) ;
+        P.dpx.assign (1, 0) ;
         return B200_OK ;
     }
     if (super [0] != 0 || super [nsuper] != n || pi [0] != 0) return B200_INVALID ;
@@ -718,17 +936,19 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     int st = partition (P, super, pi, px) ;
     if (st != B200_OK) return st ;
     const Own own { &P, false } ;
-    // a supernode's values are on this rank once it (top: panel by panel) or, for another rank's subtree,
-    // the root of that subtree is done
-    auto avail_level = [&] (int64_t s) -> int
+    if (nranks > 1)
     {
-        if (nranks == 1 || P.top [s] || P.owner [s] == rank) return P.level [s] ;
-        return P.level [P.sroot [s]] ;
-    } ;
-    std::vector<int64_t> first_of ((size_t) nsuper) ;
-    std::iota (first_of.begin (), first_of.end (), 0) ;
-    for (int64_t s = 0 ; s < nsuper ; s++)
-        if (P.parent [s] >= 0) first_of [P.parent [s]] = std::min (first_of [P.parent [s]], first_of [s]) ;
+        st = build_dist (P, super, pi, px, use_dmma) ;
+        lap ("distributed plan") ;
+        if (st != B200_OK) return st ;
+        if (P.items.size () >= ((size_t) 1 << 31)) return B200_TOO_LARGE ;
+        return B200_OK ;
+    }
+    // one GPU: the arena is L->x itself
+    P.dpx.assign (px, px + nsuper + 1) ;
+    P.dxsize = P.xsize ;
+    P.owned.push_back (CopySeg { 0, P.xsize, 0 }) ;
+    auto avail_level = [&] (int64_t s) -> int { return P.level [s] ; } ;
 
     // Copy-out schedule: from the first level above which at most 1024 supernodes remain, every level end
     // is a checkpoint at which all maximal runs of finished, not yet copied supernodes (contiguous in L->x:
@@ -773,7 +993,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
             if (copied [s] || avail_level (s) > lev) { s++ ; continue ; }
             int64_t e = s ;
             while (e < nsuper && !copied [e] && avail_level (e) <= lev) copied [e++] = 1 ;
-            CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ;
+            CopySeg c ; c.off = px [s] ; c.len = px [e] - px [s] ; c.hoff = c.off ;
             P.copies.push_back (c) ;
             s = e ;
         }
@@ -845,38 +1065,11 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         for (int64_t q = 0 ; q < ns ; q++) ncols [q] = super [S [q] + 1] - super [S [q]] ;
         const bool ckpt = lev >= first_ckpt ;
         plan_factor (P, own, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr) ;
-        if (nranks > 1)
-        {
-            // every local subtree whose root was finished on this level goes to all ranks, as one range
-            const size_t first = P.bcasts.size () ;
-            for (int64_t q = 0 ; q < ns ; q++)
-            {
-                const int64_t r = S [q] ;
-                if (P.top [r] || P.sroot [r] != r) continue ;
-                BcastSeg b ;
-                b.off = px [first_of [r]] ; b.len = px [r+1] - px [first_of [r]] ;
-                b.root = P.owner [r] ; b.pad = 0 ;
-                P.bcasts.push_back (b) ;
-            }
-            if (P.bcasts.size () > first)
-            {
-                // all NCCL traffic is issued on the communication stream, in the same order on every rank
-                const int evS = P.nevents++, evR = P.nevents++ ;
-                Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evS ;
-                P.launches.push_back (J) ;
-                Launch Bc = make_launch (K_BCAST, (int64_t) first, (int64_t) (P.bcasts.size () - first), lev, 3) ;
-                Bc.wait_ev = evS ; Bc.rec_ev = evR ;
-                P.launches.push_back (Bc) ;
-                Launch W = make_launch (K_JOIN, 0, 0, lev, 0) ; W.wait_ev = evR ;
-                P.launches.push_back (W) ;
-            }
-        }
         if (ckpt) checkpoint (lev) ;
     }
     // Whatever no checkpoint has sent yet goes now.  This is the only copy-out of a plan whose subtree-group
     // fork runs to the last level (a forest of many equal trees: the forked levels skip the checkpoints).
     checkpoint (nlevels - 1) ;
-    if (nranks == 1)
     {
         // the segments must cover [0, xsize) exactly once: the drop-in calls return the host copy they made
         std::vector<CopySeg> segs (P.copies) ;

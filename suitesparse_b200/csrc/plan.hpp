@@ -68,7 +68,10 @@ enum LaunchKind : int32_t
     K_NKINDS   = 10,
     K_JOIN     = 10,    // no kernel: only the launch's wait_ev / rec_ev are honoured
     K_COPYOUT  = 11,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
-    K_BCAST    = 12,    // no kernel: BcastSeg list, ncclBroadcast of finished panels / subtrees (main stream)
+    K_BCAST    = 12,    // no kernel: BcastSeg list, ncclBroadcast of finished panels (communication stream)
+    K_BARRIER  = 13,    // no kernel: all ranks meet (a one-word all-reduce on the communication stream)
+    K_PULL     = 14,    // PullSeg list: the owner of a block of a top separator adds the other ranks' contribution
+                        // blocks to its own, reading them from their arenas over NVLink (k_pull_add)
 } ;
 
 struct Launch
@@ -96,11 +99,19 @@ constexpr int BIG_TM = 128, BIG_TN = 64 ;
 // blocks of DIST_RUN * OUTER_NB columns): inside a run the panel chain never waits for a broadcast
 constexpr int DIST_RUN = 4 ;
 
-// A finished, contiguous piece of L->x (offset and length in values) that can go to the host early.
-struct CopySeg { int64_t off, len ; } ;
+// A finished, contiguous piece of L->x that can go to the host early: `len` values at offset `off` of the
+// device arena belong at offset `hoff` of the caller's L->x (the two differ only in a distributed plan, whose
+// arena holds the top separators and this rank's subtrees, nothing else).
+struct CopySeg { int64_t off, len, hoff ; } ;
 
-// A finished, contiguous piece of L->x that its owner rank broadcasts to all other ranks.
+// A finished, contiguous piece of the arena that its owner rank broadcasts to all other ranks.
 struct BcastSeg { int64_t off, len ; int32_t root, pad ; } ;
+
+// Contribution blocks: rows [0, nrows) x columns [0, ncols) with leading dimension ld at arena
+// offset `off` -- the lower part of one 256-column block of a top separator, at the same offset on every rank.
+// Every rank has accumulated there the updates of ITS subtrees; the block's owner adds up the copies of the
+// ranks in `mask` (bit r = rank r has something to contribute).
+struct PullSeg { int64_t off ; int32_t nrows, ncols, ld ; uint32_t mask ; } ;
 
 // One (descendant d, ancestor s) update: rows lpos.. of d; the first ndrow1 fall in the columns of s.
 struct Pair { int32_t d, s, lpos, ndrow1, ndrow2 ; } ;
@@ -134,13 +145,27 @@ struct Plan
     std::vector<PotrfBlk> potrf ;
     std::vector<TrsmTile> trsm ;
     std::vector<Launch> launches ;
-    std::vector<CopySeg> copies ;       // K_COPYOUT segments; together they cover [0, xsize) exactly once
+    std::vector<CopySeg> copies ;       // K_COPYOUT segments; together they cover what this rank owns exactly once
     std::vector<BcastSeg> bcasts ;      // K_BCAST segments (identical on every rank)
+    std::vector<PullSeg> pulls ;        // K_PULL segments of the blocks this rank owns
+    std::vector<CopySeg> owned ;        // everything this rank owns, as maximal runs (one run [0, xsize) on one GPU)
+
+    // device layout: supernode s lives at dpx [s] of the arena (-1: not on this rank), dxsize values in all.
+    // One GPU: dpx == px.  Distributed: the top separators first (same offsets on every rank), then this
+    // rank's subtrees in postorder.
+    std::vector<int64_t> dpx ;
+    int64_t dxsize = 0, top_size = 0 ;
+    std::vector<unsigned char> colmine ;    // [n] distributed: 1 if this rank scatters column k of A (it owns the
+                                            // column's subtree, or the column's block of a top separator)
+    int64_t nvlink_in_values = 0 ;      // what one factorization brings in over NVLink: panels received + blocks pulled
+    int64_t trunc_s = -1, trunc_ncol = 0 ;  // >= 0: supernodes after trunc_s are left zero and trunc_s itself is
+                                            // factorized for its first trunc_ncol columns only (SNW:1084-1146)
 
     // Distribution over the GPUs of one box.  nranks == 1: everything belongs to rank 0.
     // "top" supernodes (the separators whose subtree carries more than 1/(4 nranks) of the work) are split
-    // by outer block columns, block T of s belonging to rank (owner [s] + T) % nranks (1-D block cyclic);
-    // every other supernode belongs, with its whole subtree, to one rank.
+    // by outer block columns, block T of s belonging to rank (owner [s] + T / dist_run) % nranks (1-D block
+    // cyclic); every other supernode belongs, with its whole subtree, to one rank, is stored on that rank only,
+    // and reaches the top separators as that rank's contribution blocks (build_dist in plan.cpp).
     int32_t nranks = 1, rank = 0 ;
     int32_t dist_run = DIST_RUN ;       // outer blocks per block-cyclic unit (env CHOLMOD_B200_DIST_RUN overrides)
     std::vector<char> top ;             // [nsuper]
@@ -161,8 +186,11 @@ struct Plan
 // use_dmma = false (single precision) routes every update through the SIMT kernel class.
 // nranks > 1 builds rank `rank`'s share of the distributed plan: the same launch structure on every rank,
 // each launch holding only the blocks / tiles that rank owns, plus the K_BCAST launches all ranks share.
+// trunc_s >= 0 (distributed plans only): the plan of the not-positive-definite case -- everything up to supernode
+// trunc_s as usual, trunc_s itself for its first trunc_ncol columns, nothing after it.
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int64_t *Ls, bool use_dmma, Plan &plan, int nranks = 1, int rank = 0) ;
+    const int64_t *Ls, bool use_dmma, Plan &plan, int nranks = 1, int rank = 0, int64_t trunc_s = -1,
+    int64_t trunc_ncol = 0) ;
 
 // SNW:1084-1146: a one-supernode plan that re-applies every descendant update to supernode s and then
 // factorizes only its first nscol_new columns (dtrsm on all rows below them).  Reuses P.relmap.
