@@ -74,19 +74,55 @@ b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const
 
 /* --- one factorization spread over the GPUs of one box (the reference has no counterpart: "this version
  * of CHOLMOD can only utilize a single GPU", CHOLMOD/GPU/cholmod_gpu.c:138-143) ------------------------
- * One process per GPU.  Every rank calls b200_create_dist with the same symbolic factor, its own
- * device, the number of ranks and its rank, and gets its share of one common plan: the supernodal etree
- * is cut into independent subtrees, each owned by one rank, and a top part (the big separators) whose
- * supernodes are split over all ranks by 256-column blocks (1-D block cyclic).  Finished subtrees and
- * finished panels of the top part are broadcast from their owner with ncclBroadcast, so at the end every
- * rank holds the whole factor.  Rank 0 makes a NCCL unique id (b200_comm_unique_id, 128 bytes), the host
- * program carries it to the other ranks by any means (torch.distributed, MPI, a file), and every rank
- * calls b200_comm_init before the first factorization.  All ranks must then make the same sequence of
- * b200_factor_device / b200_super_numeric_* calls.  nranks == 1 is b200_create. */
+ * Every rank (one per GPU; one process each, or all in one process -- see b200_multi_create) calls
+ * b200_create_dist with the same symbolic factor, its own device, the number of ranks and its rank, and gets its
+ * share of one common plan:
+ *   - the supernodal etree is cut into independent subtrees, each owned -- stored, factorized, copied to the
+ *     host -- by one rank, and a top part (the big separators) whose supernodes are split over all ranks by
+ *     256-column blocks (1-D block cyclic);
+ *   - the updates a rank's subtrees send into the top separators are accumulated on that rank, in its own
+ *     zero-initialised copies of them: its contribution blocks.  After a barrier the owner of each block adds
+ *     the other ranks' contribution blocks to its own, reading them from their arenas over NVLink;
+ *   - the top separators are then factorized cooperatively; only their finished panels travel
+ *     (ncclBroadcast).
+ * A rank's arena holds the top separators and its own subtrees, nothing else ("device_bytes").  Setting up:
+ * rank 0 makes a NCCL unique id (b200_comm_unique_id, 128 bytes) and every rank an arena handle
+ * (b200_peer_handle, 64 bytes); the host program carries them around by any means (torch.distributed, MPI, a
+ * file); every rank then calls b200_comm_init and, for every other rank, b200_peer_attach.  After that all
+ * ranks make the same sequence of b200_factor_device / b200_super_numeric_* calls.  The host Lx of those calls
+ * receives only what the rank owns, at its place in L->x: hand every rank a pointer to the SAME memory (one
+ * buffer in one process, a shared mapping across processes) and it comes out complete, each rank's share over
+ * its own PCIe link.  b200_download_factor likewise.  A distributed factor is not solved on the device
+ * (b200_solve_* return B200_INVALID): no rank holds all of it.  nranks == 1 is b200_create. */
 b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
     const int64_t *px, const int64_t *s, int dtype, int device, int nranks, int rank, int *status) ;
 int b200_comm_unique_id (void *id128) ;
 int b200_comm_init (b200_factor *f, const void *id128) ;
+
+/* The arena of a distributed context, for the other ranks to attach to: its device address (ranks in the same
+ * process) or a 64-byte inter-process handle (cudaIpcMemHandle_t; ranks in other processes). */
+void *b200_peer_arena (b200_factor *f) ;
+int b200_peer_handle (b200_factor *f, void *handle64) ;
+/* Make rank `rank`'s arena readable from this context's device: pass its address (same process; peer access
+ * between the two devices is enabled) or its handle (other process; opened with cudaIpcOpenMemHandle), the
+ * other argument NULL.  Every other rank has to be attached before the first factorization. */
+int b200_peer_attach (b200_factor *f, int rank, void *arena, const void *handle64) ;
+
+/* The same factorization driven from ONE process: `ngpus` contexts on devices first_device .. first_device +
+ * ngpus - 1, communicator and peer attachments set up inside, one host thread per device for the duration of
+ * a call.  This is the form an unmodified cholmod_l_factorize caller reaches (the shim's CHOLMOD_B200_NGPUS).
+ * b200_multi_super_numeric_d has the contract of b200_super_numeric_d: one host A in, one complete host L->x
+ * out, every device moving its share. */
+typedef struct b200_multi b200_multi ;
+b200_multi *b200_multi_create (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi,
+    const int64_t *px, const int64_t *s, int dtype, int first_device, int ngpus, int *status) ;
+void b200_multi_destroy (b200_multi *m) ;
+int b200_multi_ngpus (const b200_multi *m) ;
+b200_factor *b200_multi_context (b200_multi *m, int rank) ;
+int b200_multi_super_numeric_d (b200_multi *m, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
+    const double *Ax, double beta, int quick_return_if_not_posdef, double *Lx, int64_t *minor) ;
+int b200_multi_download_factor (b200_multi *m, void *Lx) ;
+int b200_multi_forget_host_buffer (b200_multi *m, const void *Lx) ;
 
 /* Release everything.  Replaces cholmod_l_gpu_deallocate / gpu_end (cholmod_gpu.c:187-228, :319-420). */
 void b200_destroy (b200_factor *f) ;
@@ -166,7 +202,8 @@ int b200_upload_values (b200_factor *f, const void *Ax) ;
  * dpotrf/dtrsm (:1023-1181).  Blocks until the device is done.  Returns status and *minor as above. */
 int b200_factor_device (b200_factor *f, double beta, int quick_return_if_not_posdef, int64_t *minor) ;
 
-/* Copy the device-resident factor to host Lx [xsize] (values of the context's dtype).
+/* Copy the device-resident factor (a distributed context: the part this rank owns) to its place in host
+ * Lx [xsize] (values of the context's dtype).
  * Replaces the per-supernode D2H of t_cholmod_gpu.c:1263-1273, :1403-1443. */
 int b200_download_factor (b200_factor *f, void *Lx) ;
 

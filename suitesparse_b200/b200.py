@@ -28,7 +28,9 @@ SYMBOLS = ["b200_probe", "b200_device_count", "b200_memorysize", "b200_create", 
            "b200_dmma_peak_tflops", "b200_panel_factor_noalloc_d", "b200_create_dist", "b200_comm_unique_id",
            "b200_comm_init", "b200_upload_values", "b200_forget_host_buffer", "b200_super_numeric_z",
            "b200_super_numeric_c", "b200_solve_z", "b200_super_numeric_aat", "b200_upload_matrix_aat",
-           "b200_solve_sweep", "b200_set_memory_limit"]
+           "b200_solve_sweep", "b200_set_memory_limit", "b200_peer_arena", "b200_peer_handle", "b200_peer_attach",
+           "b200_multi_create", "b200_multi_destroy", "b200_multi_ngpus", "b200_multi_context",
+           "b200_multi_super_numeric_d", "b200_multi_download_factor", "b200_multi_forget_host_buffer"]
 NOALLOC_MAX_COLS, NOALLOC_MAX_ROWS = 64, 65536
 
 
@@ -85,6 +87,16 @@ def lib():
     L.b200_forget_host_buffer.argtypes = [vp, vp]; L.b200_forget_host_buffer.restype = cint
     L.b200_solve_sweep.argtypes = [vp, cint, vp, vp, i64]; L.b200_solve_sweep.restype = cint
     L.b200_set_memory_limit.argtypes = [cint, C.c_size_t]; L.b200_set_memory_limit.restype = cint
+    L.b200_peer_arena.argtypes = [vp]; L.b200_peer_arena.restype = vp
+    L.b200_peer_handle.argtypes = [vp, vp]; L.b200_peer_handle.restype = cint
+    L.b200_peer_attach.argtypes = [vp, cint, vp, vp]; L.b200_peer_attach.restype = cint
+    L.b200_multi_create.argtypes = [i64, i64, vp, vp, vp, vp, cint, cint, cint, vp]; L.b200_multi_create.restype = vp
+    L.b200_multi_destroy.argtypes = [vp]; L.b200_multi_destroy.restype = None
+    L.b200_multi_ngpus.argtypes = [vp]; L.b200_multi_ngpus.restype = cint
+    L.b200_multi_context.argtypes = [vp, cint]; L.b200_multi_context.restype = vp
+    L.b200_multi_super_numeric_d.argtypes = [vp, vp, vp, vp, vp, dbl, cint, vp, vp]; L.b200_multi_super_numeric_d.restype = cint
+    L.b200_multi_download_factor.argtypes = [vp, vp]; L.b200_multi_download_factor.restype = cint
+    L.b200_multi_forget_host_buffer.argtypes = [vp, vp]; L.b200_multi_forget_host_buffer.restype = cint
     _lib = L
     return L
 
@@ -184,12 +196,30 @@ class Factor:
             raise B200Error(st, "b200_comm_init")
 
     def comm_init_torch(self, group=None):
-        """Bootstrap the communicator through torch.distributed: rank 0 makes the id, everyone gets it."""
-        import torch
+        """Bootstrap a distributed context through torch.distributed: rank 0 makes the NCCL id, everyone gets
+        it; every rank publishes the inter-process handle of its arena and attaches to all the others."""
         import torch.distributed as dist
         ids = [comm_unique_id() if self.rank == 0 else None]
         dist.broadcast_object_list(ids, src=0, group=group)
         self.comm_init(ids[0])
+        handles = [None] * self.nranks
+        dist.all_gather_object(handles, self.peer_handle(), group=group)
+        for r, h in enumerate(handles):
+            if r != self.rank:
+                self.peer_attach(r, handle=h)
+
+    def peer_handle(self):
+        buf = (C.c_char * 64)()
+        st = self.L.b200_peer_handle(self.h, buf)
+        if st < 0:
+            raise B200Error(st, "b200_peer_handle")
+        return bytes(buf)
+
+    def peer_attach(self, rank, arena=None, handle=None):
+        hb = (C.c_char * 64).from_buffer_copy(bytes(handle)) if handle is not None else None
+        st = self.L.b200_peer_attach(self.h, int(rank), C.c_void_p(arena) if arena else None, hb)
+        if st < 0:
+            raise B200Error(st, "b200_peer_attach")
 
     def seti(self, name, value):
         st = self.L.b200_set_int(self.h, name.encode(), int(value))
@@ -351,12 +381,59 @@ TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("j
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
                       ("wait_ev", "<i4"), ("rec_ev", "<i4")])
 K_FACTOR_SMALL = 9
-K_JOIN, K_COPYOUT, K_BCAST = 10, 11, 12
+K_JOIN, K_COPYOUT, K_BCAST, K_BARRIER, K_PULL = 10, 11, 12, 13, 14
 BCAST_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("root", "<i4"), ("pad", "<i4")])
-COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8")])
+COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("hoff", "<i8")])
+PULL_DT = np.dtype([("off", "<i8"), ("nrows", "<i4"), ("ncols", "<i4"), ("ld", "<i4"), ("mask", "<u4")])
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)
 KIND_NAMES = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf16", "potrf32", "potrf64", "trsm_subst", "trsm_inv32",
               "trsm_inv64", "factor_small"]
 TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 64)}
+
+
+class Multi:
+    """One factorization over `ngpus` devices driven from this process (b200_multi_*): host A in, one complete
+    host L->x out, every device moving its share.  Real double symmetric matrices."""
+
+    def __init__(self, sym, first_device=0, ngpus=2):
+        self.L = lib()
+        self.n, self.xsize = int(sym["n"]), int(sym["xsize"])
+        sup, pi, px, s = _i64(sym["super"]), _i64(sym["pi"]), _i64(sym["px"]), _i64(sym["s"])
+        st = C.c_int(0)
+        self.h = self.L.b200_multi_create(self.n, int(sym["nsuper"]), sup.ctypes.data, pi.ctypes.data, px.ctypes.data,
+                                          s.ctypes.data, DOUBLE, int(first_device), int(ngpus), C.byref(st))
+        if not self.h:
+            raise B200Error(st.value, "b200_multi_create")
+        self.ngpus, self.minor = int(ngpus), self.n
+
+    def context_geti(self, rank, name):
+        return int(self.L.b200_get_int(self.L.b200_multi_context(self.h, int(rank)), name.encode()))
+
+    def context_getd(self, rank, name):
+        return float(self.L.b200_get_double(self.L.b200_multi_context(self.h, int(rank)), name.encode()))
+
+    def super_numeric(self, Ap, Ai, Ax, beta=0.0, quick_return=False, Lx=None):
+        Ap, Ai, Ax = _i64(Ap), _i64(Ai), np.ascontiguousarray(Ax, dtype=np.float64)
+        if Lx is None:
+            Lx = np.empty(self.xsize)
+        minor = C.c_int64(-1)
+        st = self.L.b200_multi_super_numeric_d(self.h, Ap.ctypes.data, Ai.ctypes.data, None, Ax.ctypes.data, float(beta),
+                                               int(quick_return), Lx.ctypes.data, C.byref(minor))
+        if st < 0:
+            raise B200Error(st, "b200_multi_super_numeric_d")
+        self.minor = int(minor.value)
+        self._pinned_Lx = Lx
+        return st, Lx
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.b200_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -95,6 +95,16 @@ struct b200_factor
     int device = -1 ;
     size_t esize = 8 ;
     std::vector<int64_t> h_super, h_pi, h_px ;
+    std::vector<int64_t> h_Ls ;             // distributed contexts keep L->s: the not-positive-definite case re-plans
+    // distributed: arena base of every rank as this device sees it (own entry = d_Lx.p); the peers' arenas are
+    // peer-mapped (same process) or opened from their IPC handles (other processes)
+    PeerPtrs peers = {} ;
+    bool peer_ipc [32] = {} ;               // peers.p [r] came from cudaIpcOpenMemHandle and has to be closed
+    int peers_attached = 0 ;
+    DevBuf<unsigned char> d_colmine ;
+    DevBuf<PullSeg> d_pulls ;
+    DevBuf<unsigned long long> d_barrier ;  // the word the K_BARRIER all-reduce works on
+    double ms_pull = 0 ;                    // profile mode: the fan-in kernel (K_PULL)
 
     cudaStream_t stream = nullptr ;         // main stream: everything except the look-ahead updates
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
@@ -250,7 +260,7 @@ int kernel_attrs (int device)
 // run the launch list [first, last) of a plan on the context's stream
 template <typename T>
 int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const UpdTile *tiles,
-    const PotrfBlk *potrf, const TrsmTile *trsm, const int32_t *relmap)
+    const PotrfBlk *potrf, const TrsmTile *trsm, const int32_t *relmap, const PullSeg *pulls = nullptr)
 {
     T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
     T *winv = reinterpret_cast<T *> (f->d_winv.p) ;
@@ -295,7 +305,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             for (int64_t c = L.first ; c < L.first + L.count ; c++)
             {
                 const CopySeg &seg = P.copies [c] ;
-                CK (cudaMemcpyAsync ((char *) f->copy_dst + (size_t) seg.off * sizeof (T), Lx + seg.off,
+                CK (cudaMemcpyAsync ((char *) f->copy_dst + (size_t) seg.hoff * sizeof (T), Lx + seg.off,
                     (size_t) seg.len * sizeof (T), cudaMemcpyDeviceToHost, f->stream3), "copy-out") ;
             }
             continue ;
@@ -323,10 +333,25 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
             continue ;
         }
+        if (L.kind == K_BARRIER)
+        {
+            // all ranks meet: nobody pulls a contribution block before every rank has finished writing its own
+            NcclApi *nc = nccl_api () ;
+            if (!nc || !f->comm) { fprintf (stderr, "cholmod_b200: distributed plan without b200_comm_init\n") ; return B200_INVALID ; }
+            if (nc->AllReduce (f->d_barrier.p, f->d_barrier.p, 1, ncclUint64, ncclSum, f->comm, st) != ncclSuccess) return B200_GPU_PROBLEM ;
+            f->nccl_calls++ ;
+            if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
+            continue ;
+        }
         if (L.kind == K_JOIN || L.count <= 0)
         {
             if (L.rec_ev >= 0) CK (cudaEventRecord (f->plan_ev [L.rec_ev], st), "record event") ;
             continue ;
+        }
+        if (L.kind == K_PULL && (!pulls || f->peers_attached < P.nranks))
+        {
+            fprintf (stderr, "cholmod_b200: distributed plan without b200_peer_attach for every rank\n") ;
+            return B200_INVALID ;
         }
         if (f->profile) cudaEventRecord (f->prof_ev [nev++], st) ;
         switch (L.kind)
@@ -399,6 +424,9 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
                     k_trsm_zinv<64><<<(unsigned) L.count, 256, trsm_zinv_smem_bytes<64> (), st>>> (trsm + L.first, Lx, winv) ;
                 else return B200_INVALID ;
                 break ;
+            case K_PULL:
+                k_pull_add<T><<<dim3 ((unsigned) L.count, OUTER_NB), 256, 0, st>>> (pulls + L.first, Lx, f->peers) ;
+                break ;
             default:
                 return B200_INVALID ;
         }
@@ -419,14 +447,14 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         for (const Launch &L : P.launches)
         {
             const size_t idx = li++ ;
-            if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.kind == K_BCAST || L.count <= 0) continue ;
+            if (L.kind == K_JOIN || L.kind == K_COPYOUT || L.kind == K_BCAST || L.kind == K_BARRIER || L.count <= 0) continue ;
             float ms = 0 ;
             cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
             f->ms_launch [idx] = ms ;
             cudaEventElapsedTime (&f->ms_launch_start [idx], f->prof_ev [0], f->prof_ev [e]) ;
             e += 2 ;
-            f->ms_kind [L.kind] += ms ;
-            f->launches_kind [L.kind]++ ;
+            if (L.kind < K_NKINDS) { f->ms_kind [L.kind] += ms ; f->launches_kind [L.kind]++ ; }
+            else if (L.kind == K_PULL) f->ms_pull += ms ;
             // timeline: when (after the first launch of the plan) the last launch of each level ended
             if (L.level >= 0 && L.level < 64)
             {
@@ -448,11 +476,13 @@ int scatter_A (b200_factor *f, int64_t kfirst, int64_t klast, double beta)
         k_scatter_AF<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
             f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_Fp.p, f->d_Fi.p,
             f->F_unpacked ? f->d_Fnz.p : nullptr, reinterpret_cast<const T *> (f->d_Fx.p), f->d_supermap.p,
-            f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
+            f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p),
+            f->d_colmine.p) ;
     else
     k_scatter_A<T><<<grid, 256, 0, f->stream>>> (kfirst, klast, f->d_Ap.p, f->d_Ai.p,
         f->A_unpacked ? f->d_Anz.p : nullptr, reinterpret_cast<const T *> (f->d_Ax.p), f->d_supermap.p,
-        f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p)) ;
+        f->d_super.p, f->d_pi.p, f->d_px.p, f->d_Ls.p, (typename num<T>::real) beta, reinterpret_cast<T *> (f->d_Lx.p),
+        f->d_colmine.p) ;
     f->kernel_launches++ ;
     CK (cudaGetLastError (), "k_scatter_A") ;
     return B200_OK ;
@@ -582,7 +612,7 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         // refuse before allocating anything if the context cannot fit under the cap set for this device
         const size_t need = (size_t) (3 * (P.nsuper + 1)) * 8 + (size_t) P.ssize * 4 + (size_t) P.n * 4 + P.relmap.size () * 4
             + (size_t) P.nsuper * 4 + P.items.size () * sizeof (UpdItem) + P.tiles.size () * sizeof (UpdTile)
-            + P.potrf.size () * sizeof (PotrfBlk) + P.trsm.size () * sizeof (TrsmTile) + (size_t) P.xsize * f->esize
+            + P.potrf.size () * sizeof (PotrfBlk) + P.trsm.size () * sizeof (TrsmTile) + (size_t) P.dxsize * f->esize
             + (size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize ;
         std::lock_guard<std::mutex> guard (g_mem_lock) ;
         const int d = f->device ;
@@ -599,7 +629,7 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     bool ok = true ;
     ok = ok && f->d_super.upload (f->h_super, s) == cudaSuccess ;
     ok = ok && f->d_pi.upload (f->h_pi, s) == cudaSuccess ;
-    ok = ok && f->d_px.upload (f->h_px, s) == cudaSuccess ;
+    ok = ok && f->d_px.upload (P.dpx, s) == cudaSuccess ;        // ARENA offsets (== L->px on one GPU)
     ok = ok && f->d_Ls.upload (Ls32, s) == cudaSuccess ;
     ok = ok && f->d_supermap.upload (P.supermap, s) == cudaSuccess ;
     ok = ok && f->d_relmap.upload (P.relmap, s) == cudaSuccess ;
@@ -608,14 +638,25 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     ok = ok && f->d_tiles.upload (P.tiles, s) == cudaSuccess ;
     ok = ok && f->d_potrf.upload (P.potrf, s) == cudaSuccess ;
     ok = ok && f->d_trsm.upload (P.trsm, s) == cudaSuccess ;
-    ok = ok && f->d_Lx.alloc ((size_t) P.xsize * f->esize) == cudaSuccess ;
+    // (a distributed arena is never empty: its address is what the other ranks attach to)
+    ok = ok && f->d_Lx.alloc ((size_t) (P.nranks > 1 ? std::max<int64_t> (P.dxsize, 1) : P.dxsize) * f->esize) == cudaSuccess ;
     ok = ok && f->d_minor.alloc (1) == cudaSuccess ;
+    if (P.nranks > 1)
+    {
+        ok = ok && f->d_colmine.upload (P.colmine, s) == cudaSuccess ;
+        ok = ok && f->d_pulls.upload (P.pulls, s) == cudaSuccess ;
+        ok = ok && f->d_barrier.alloc (1) == cudaSuccess ;
+        if (ok) ok = cudaMemsetAsync (f->d_barrier.p, 0, sizeof (unsigned long long), s) == cudaSuccess ;
+        f->peers.p [P.rank] = f->d_Lx.p ;
+        f->peers_attached = 1 ;
+    }
     ok = ok && f->d_winv.alloc ((size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize) == cudaSuccess ;
     if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
     CK (cudaStreamSynchronize (s), "upload symbolic") ;
     f->device_bytes = f->d_super.bytes () + f->d_pi.bytes () + f->d_px.bytes () + f->d_Ls.bytes ()
         + f->d_supermap.bytes () + f->d_relmap.bytes () + f->d_level_list.bytes () + f->d_items.bytes ()
-        + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () + f->d_winv.bytes () ;
+        + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () + f->d_winv.bytes ()
+        + f->d_colmine.bytes () + f->d_pulls.bytes () ;
     if (f->device < 64)
     {
         std::lock_guard<std::mutex> guard (g_mem_lock) ;
@@ -648,6 +689,7 @@ b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, 
             f->h_super.assign (super, super + nsuper + 1) ;
             f->h_pi.assign (pi, pi + nsuper + 1) ;
             f->h_px.assign (px, px + nsuper + 1) ;
+            if (nranks > 1) f->h_Ls.assign (s, s + pi [nsuper]) ;
         }
     }
     catch (const std::bad_alloc &) { *status = B200_OUT_OF_MEMORY ; }
@@ -687,7 +729,9 @@ void b200_destroy (b200_factor *f)
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
         f->d_Ax.release () ; f->d_Fp.release () ; f->d_Fi.release () ; f->d_Fnz.release () ; f->d_Fx.release () ;
         f->d_minor.release () ; f->d_X.release () ; f->d_Y.release () ; f->d_solveW.release () ; f->d_solve_cnt.release () ;
-        f->d_winv.release () ;
+        f->d_winv.release () ; f->d_colmine.release () ; f->d_pulls.release () ; f->d_barrier.release () ;
+        for (int r = 0 ; r < 32 ; r++)
+            if (f->peer_ipc [r] && f->peers.p [r]) { cudaIpcCloseMemHandle (f->peers.p [r]) ; f->peers.p [r] = nullptr ; }
         f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
@@ -733,6 +777,11 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "rank")) return P.rank ;
     if (!strcmp (name, "nccl_calls")) return f->nccl_calls ;
     if (!strcmp (name, "nbcasts")) return (int64_t) P.bcasts.size () ;
+    if (!strcmp (name, "npulls")) return (int64_t) P.pulls.size () ;
+    if (!strcmp (name, "dxsize")) return P.dxsize ;
+    if (!strcmp (name, "top_size")) return P.top_size ;
+    if (!strcmp (name, "nvlink_in_bytes")) return P.nvlink_in_values * (int64_t) f->esize ;
+    if (!strcmp (name, "peers_attached")) return f->peers_attached ;
     if (!strcmp (name, "ngroups")) return P.ngroups ;
     if (!strcmp (name, "fork_lo")) return P.fork_lo ;
     if (!strcmp (name, "fork_hi")) return P.fork_hi ;
@@ -766,6 +815,7 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_d2h")) return f->ms_d2h ;
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
+    if (!strcmp (name, "ms_pull")) return f->ms_pull ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
     if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
     if (!strncmp (name, "solve_launches", 14) && name [14] >= '0' && name [14] < '4') return (double) f->solve_launch_count [name [14] - '0'] ;
@@ -798,6 +848,10 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
     else if (!strcmp (which, "owner")) { src = P.owner.data () ; bytes = P.owner.size () * sizeof (int32_t) ; }
     else if (!strcmp (which, "top")) { src = P.top.data () ; bytes = P.top.size () ; }
     else if (!strcmp (which, "group")) { src = P.group.data () ; bytes = P.group.size () * sizeof (int32_t) ; }
+    else if (!strcmp (which, "dpx")) { src = P.dpx.data () ; bytes = P.dpx.size () * sizeof (int64_t) ; }
+    else if (!strcmp (which, "colmine")) { src = P.colmine.data () ; bytes = P.colmine.size () ; }
+    else if (!strcmp (which, "pulls")) { src = P.pulls.data () ; bytes = P.pulls.size () * sizeof (PullSeg) ; }
+    else if (!strcmp (which, "owned")) { src = P.owned.data () ; bytes = P.owned.size () * sizeof (CopySeg) ; }
     else return -1 ;
     if (!out) return (int64_t) bytes ;
     if ((int64_t) bytes > out_bytes) return -1 ;
@@ -833,6 +887,61 @@ int b200_comm_init (b200_factor *f, const void *id128)
         f->comm = nullptr ;
         return B200_GPU_PROBLEM ;
     }
+    return B200_OK ;
+}
+
+void *b200_peer_arena (b200_factor *f) { return (f && f->device >= 0) ? (void *) f->d_Lx.p : nullptr ; }
+
+int b200_peer_handle (b200_factor *f, void *handle64)
+{
+    int st = set_device (f) ; if (st) return st ;
+    if (!handle64 || !f->d_Lx.p) return B200_INVALID ;
+    static_assert (sizeof (cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes") ;
+    cudaIpcMemHandle_t h ;
+    CK (cudaIpcGetMemHandle (&h, f->d_Lx.p), "cudaIpcGetMemHandle") ;
+    memcpy (handle64, &h, sizeof (h)) ;
+    return B200_OK ;
+}
+
+int b200_peer_attach (b200_factor *f, int rank, void *arena, const void *handle64)
+{
+    int st = set_device (f) ; if (st) return st ;
+    const int R = f->plan.nranks ;
+    if (rank < 0 || rank >= R || R > 32) return B200_INVALID ;
+    if (rank != f->plan.rank)
+    {
+        if (f->peer_ipc [rank] && f->peers.p [rank]) { cudaIpcCloseMemHandle (f->peers.p [rank]) ; f->peer_ipc [rank] = false ; }
+        f->peers.p [rank] = nullptr ;
+        if (arena)
+        {
+            // same process: make the peer's device reachable from ours, then its pointer is good as it is
+            cudaPointerAttributes at ;
+            CK (cudaPointerGetAttributes (&at, arena), "cudaPointerGetAttributes") ;
+            if (at.type != cudaMemoryTypeDevice) return B200_INVALID ;
+            if (at.device != f->device)
+            {
+                int can = 0 ;
+                CK (cudaDeviceCanAccessPeer (&can, f->device, at.device), "cudaDeviceCanAccessPeer") ;
+                if (!can) { fprintf (stderr, "cholmod_b200: device %d cannot reach device %d\n", f->device, at.device) ; return B200_GPU_PROBLEM ; }
+                cudaError_t e = cudaDeviceEnablePeerAccess (at.device, 0) ;
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cuda_ok (e, "cudaDeviceEnablePeerAccess") ; return B200_GPU_PROBLEM ; }
+                cudaGetLastError () ;
+            }
+            f->peers.p [rank] = arena ;
+        }
+        else if (handle64)
+        {
+            cudaIpcMemHandle_t h ;
+            memcpy (&h, handle64, sizeof (h)) ;
+            void *p = nullptr ;
+            CK (cudaIpcOpenMemHandle (&p, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle") ;
+            f->peers.p [rank] = p ; f->peer_ipc [rank] = true ;
+        }
+        else return B200_INVALID ;
+    }
+    int cnt = 0 ;
+    for (int r = 0 ; r < R ; r++) if (f->peers.p [r]) cnt++ ;
+    f->peers_attached = cnt ;
     return B200_OK ;
 }
 
@@ -932,11 +1041,73 @@ static void ensure_registered (b200_factor *f, void *Lx, size_t bytes)
         f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
     }
     if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
-    if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterDefault) == cudaSuccess)
+    {
+        // page-locked already -- by the caller, or by another context of this process that writes into the same
+        // buffer (b200_multi)?  Then there is nothing to do, and nothing of ours to undo later.
+        unsigned fl = 0 ;
+        if (bytes > 0 && cudaHostGetFlags (&fl, Lx) == cudaSuccess
+            && cudaHostGetFlags (&fl, (char *) Lx + (bytes - 1)) == cudaSuccess) return ;
+        cudaGetLastError () ;
+    }
+    // portable: the contexts of several devices in one process (b200_multi) all copy into the same buffer; the
+    // first of them to get here registers it, the others find it registered already
+    if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterPortable) == cudaSuccess)
     {
         f->reg_ptr = Lx ; f->reg_bytes = bytes ;
     }
     else cudaGetLastError () ;
+}
+
+// everything this rank owns (all of L->x on one GPU) from the arena to its place in the caller's L->x
+template <typename T>
+static int copy_owned_to_host (b200_factor *f, void *host_dst, cudaStream_t st)
+{
+    const T *Lx = reinterpret_cast<const T *> (f->d_Lx.p) ;
+    for (const CopySeg &seg : f->plan.owned)
+        if (seg.len > 0)
+            CK (cudaMemcpyAsync ((char *) host_dst + (size_t) seg.hoff * sizeof (T), Lx + seg.off, (size_t) seg.len * sizeof (T),
+                cudaMemcpyDeviceToHost, st), "D2H Lx") ;
+    return B200_OK ;
+}
+
+// SNW:1084-1146 for a distributed factorization.  No rank holds the whole factor, so instead of repairing one
+// supernode every rank re-plans the factorization TRUNCATED at the failing supernode s (everything before s as
+// usual, s itself for its first info-1 columns -- or not at all when info == 1 or quick return is set --,
+// nothing after s, which stays zero) and runs it again.  `minor` is the same on all ranks (all-reduced), so all
+// ranks take this path together.  Rare, and twice the work of a factorization; the values before s come out
+// as in the first run.
+template <typename T>
+static int repair_dist (b200_factor *f, int64_t minor, double beta, int quick)
+{
+    const Plan &P = f->plan ;
+    cudaStream_t st0 = f->stream ;
+    const int64_t s = P.supermap [minor] ;
+    const int64_t k1 = f->h_super [s], nscol = f->h_super [s+1] - k1, nsrow = f->h_pi [s+1] - f->h_pi [s] ;
+    const int64_t info = minor - k1 + 1 ;
+    const int64_t ncol_new = (info == 1 || quick) ? 0 : info - 1 ;
+    Plan R ;
+    int st = build_plan (P.n, P.nsuper, f->h_super.data (), f->h_pi.data (), f->h_px.data (), f->h_Ls.data (),
+        dtype_dmma (f->dtype), R, P.nranks, P.rank, s, ncol_new) ;
+    if (st) return st ;
+    DevBuf<UpdItem> items ; DevBuf<UpdTile> tiles ; DevBuf<PotrfBlk> potrf ; DevBuf<TrsmTile> trsm ; DevBuf<PullSeg> pulls ;
+    bool ok = items.upload (R.items, st0) == cudaSuccess && tiles.upload (R.tiles, st0) == cudaSuccess
+        && potrf.upload (R.potrf, st0) == cudaSuccess && trsm.upload (R.trsm, st0) == cudaSuccess
+        && pulls.upload (R.pulls, st0) == cudaSuccess ;
+    if (!ok) st = B200_OUT_OF_MEMORY ;
+    const unsigned long long big = ~0ull ;
+    T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
+    if (!st && cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, st0) != cudaSuccess) st = B200_GPU_PROBLEM ;
+    if (!st && P.dxsize > 0 && cudaMemsetAsync (Lx, 0, (size_t) P.dxsize * sizeof (T), st0) != cudaSuccess) st = B200_GPU_PROBLEM ;
+    if (!st) st = scatter_A<T> (f, 0, ncol_new > 0 ? k1 + nscol : k1, beta) ;
+    if (!st) st = run_launches<T> (f, R, items.p, tiles.p, potrf.p, trsm.p, f->d_relmap.p, pulls.p) ;
+    if (!st && ncol_new > 0 && P.dpx [s] >= 0
+        && cudaMemsetAsync (Lx + P.dpx [s] + nsrow * ncol_new, 0, (size_t) (nsrow * (nscol - ncol_new)) * sizeof (T), st0) != cudaSuccess)
+        st = B200_GPU_PROBLEM ;
+    if (cudaStreamSynchronize (st0) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
+    if (cudaStreamSynchronize (f->stream2) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
+    if (cudaStreamSynchronize (f->stream4) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
+    items.release () ; tiles.release () ; potrf.release () ; trsm.release () ; pulls.release () ;
+    return st ;
 }
 
 // host_dst != NULL: finished parts of the factor are copied to host_dst [0..xsize) while the rest is still
@@ -953,13 +1124,14 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     f->solve_w_valid = false ;              // the solve's block inverses belong to the previous factor
     for (int k = 0 ; k < K_NKINDS ; k++) { f->ms_kind [k] = 0 ; f->launches_kind [k] = 0 ; }
     for (int k = 0 ; k < 64 ; k++) f->ms_level_end [k] = 0 ;
+    f->ms_pull = 0 ;
     CK (cudaEventRecord (f->ev [2], s), "record") ;
     CK (cudaMemcpyAsync (f->d_minor.p, &big, sizeof (big), cudaMemcpyHostToDevice, s), "minor init") ;
-    if (P.xsize > 0) CK (cudaMemsetAsync (f->d_Lx.p, 0, (size_t) P.xsize * sizeof (T), s), "memset Lx") ;
+    if (P.dxsize > 0) CK (cudaMemsetAsync (f->d_Lx.p, 0, (size_t) P.dxsize * sizeof (T), s), "memset Lx") ;
     int st = scatter_A<T> (f, 0, P.n, beta) ;
     if (st) return st ;
     CK (cudaEventRecord (f->ev [3], s), "record") ;
-    st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p) ;
+    st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p, f->d_pulls.p) ;
     if (st) return st ;
     if (P.nranks > 1)
     {
@@ -987,10 +1159,13 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     // not positive definite: reproduce SNW:1084-1146
     if (minor_out) *minor_out = (int64_t) minor ;
     f->copy_dst = nullptr ;
-    st = repair_not_posdef<T> (f, (int64_t) minor, beta, quick) ;
+    st = (P.nranks > 1) ? repair_dist<T> (f, (int64_t) minor, beta, quick) : repair_not_posdef<T> (f, (int64_t) minor, beta, quick) ;
     if (st < 0) return st ;
     if (host_dst && P.xsize > 0)     // rare path: send the repaired factor again, as a whole
-        CK (cudaMemcpyAsync (host_dst, f->d_Lx.p, (size_t) P.xsize * sizeof (T), cudaMemcpyDeviceToHost, s), "D2H repaired Lx") ;
+    {
+        st = copy_owned_to_host<T> (f, host_dst, s) ;
+        if (st < 0) return st ;
+    }
     CK (cudaStreamSynchronize (s), "repair") ;
     return B200_NOT_POSDEF ;
 }
@@ -1012,7 +1187,8 @@ int b200_download_factor (b200_factor *f, void *Lx)
     if (bytes == 0) return B200_OK ;
     ensure_registered (f, Lx, bytes) ;
     CK (cudaEventRecord (f->ev [5], f->stream), "record") ;
-    CK (cudaMemcpyAsync (Lx, f->d_Lx.p, bytes, cudaMemcpyDeviceToHost, f->stream), "D2H Lx") ;
+    st = B200_DISPATCH (f->dtype, copy_owned_to_host) (f, Lx, f->stream) ;
+    if (st < 0) return st ;
     CK (cudaEventRecord (f->ev [6], f->stream), "record") ;
     CK (cudaStreamSynchronize (f->stream), "D2H Lx") ;
     cudaEventElapsedTime (&f->ms_d2h, f->ev [5], f->ev [6]) ;
@@ -1024,7 +1200,7 @@ int b200_upload_factor (b200_factor *f, const void *Lx)
     int st = set_device (f) ; if (st) return st ;
     size_t bytes = (size_t) f->plan.xsize * f->esize ;
     if (bytes == 0) return B200_OK ;
-    if (!Lx) return B200_INVALID ;
+    if (!Lx || f->plan.nranks > 1) return B200_INVALID ;    // a distributed arena holds only this rank's share
     f->solve_w_valid = false ;
     CK (cudaMemcpyAsync (f->d_Lx.p, Lx, bytes, cudaMemcpyHostToDevice, f->stream), "H2D Lx") ;
     CK (cudaStreamSynchronize (f->stream), "H2D Lx") ;
@@ -1309,6 +1485,12 @@ static int solve_host (b200_factor *f, const double *B, double *X, int64_t nrhs,
 {
     int st = set_device (f) ; if (st) return st ;
     if (dtype_complex (f->dtype) != want_complex || which < 1 || which > 3) return B200_INVALID ;
+    if (f->plan.nranks > 1)
+    {
+        fprintf (stderr, "cholmod_b200: a distributed factor is not solved on the device: no rank holds all of it "
+            "(solve on the host, or upload the assembled L->x into a one-GPU context)\n") ;
+        return B200_INVALID ;
+    }
     const int64_t n = f->plan.n ;
     if (nrhs < 0 || (!B && n * nrhs > 0) || (!X && n * nrhs > 0)) return B200_INVALID ;
     if (n == 0 || nrhs == 0) return B200_OK ;

@@ -122,10 +122,11 @@ __global__ void __launch_bounds__ (256) k_scatter_A (int64_t kfirst, int64_t kla
     const int64_t *__restrict__ Ap, const int64_t *__restrict__ Ai, const int64_t *__restrict__ Anz,
     const T *__restrict__ Ax, const int32_t *__restrict__ supermap, const int64_t *__restrict__ super,
     const int64_t *__restrict__ pi, const int64_t *__restrict__ px, const int32_t *__restrict__ Ls,
-    typename num<T>::real beta, T *__restrict__ Lx)
+    typename num<T>::real beta, T *__restrict__ Lx, const unsigned char *__restrict__ colmine)
 {
     int64_t k = kfirst + (int64_t) blockIdx.x * blockDim.x + threadIdx.x ;
     if (k >= klast) return ;
+    if (colmine && !colmine [k]) return ;       // distributed: another rank holds (the real copy of) this column
     int32_t s = supermap [k] ;
     int64_t k1 = super [s], k2 = super [s+1], psi = pi [s] ;
     int64_t nsrow = pi [s+1] - psi, nscol = k2 - k1 ;
@@ -168,10 +169,12 @@ __global__ void __launch_bounds__ (256) k_scatter_AF (int64_t kfirst, int64_t kl
     const T *__restrict__ Ax, const int64_t *__restrict__ Fp, const int64_t *__restrict__ Fi,
     const int64_t *__restrict__ Fnz, const T *__restrict__ Fx, const int32_t *__restrict__ supermap,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, typename num<T>::real beta, T *__restrict__ Lx)
+    const int32_t *__restrict__ Ls, typename num<T>::real beta, T *__restrict__ Lx,
+    const unsigned char *__restrict__ colmine)
 {
     int64_t k = kfirst + (int64_t) blockIdx.x * blockDim.x + threadIdx.x ;
     if (k >= klast) return ;
+    if (colmine && !colmine [k]) return ;
     int32_t s = supermap [k] ;
     int64_t k1 = super [s], k2 = super [s+1], psi = pi [s] ;
     int64_t nsrow = pi [s+1] - psi, nscol = k2 - k1 ;
@@ -1755,6 +1758,45 @@ __global__ void __launch_bounds__ (256) k_solve_bwd_blk (const SolveTile *__rest
             if (part == 0 && j < t.jb) x [k1 + t.c0 + j] = a2 ;
         }
         __syncthreads () ;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// fan-in of the contribution blocks of the top separators (several GPUs)
+// ---------------------------------------------------------------------------------------------
+
+// arena base address of every rank, as seen from this device: peer-mapped (cudaDeviceEnablePeerAccess within
+// one process, cudaIpcOpenMemHandle across processes), so a plain load travels over NVLink
+struct PeerPtrs { void *p [32] ; } ;
+
+__device__ __forceinline__ float ldcg_ (const float *p) { return __ldcg (p) ; }
+__device__ __forceinline__ cx<float> ldcg_ (const cx<float> *p)
+{
+    float2 v = __ldcg (reinterpret_cast<const float2 *> (p)) ;
+    return { v.x, v.y } ;
+}
+
+// One CTA per (block, column): dst (i, col) += sum over the ranks in mask of their copy of the same entry, for
+// the rows i >= col of the block (its lower part).  The top separators sit at the same arena offset on every
+// rank.  Loads bypass L1 (the peers rewrite this memory in every factorization); a thread's loads from the
+// different peers are independent, consecutive threads read consecutive addresses.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_pull_add (const PullSeg *__restrict__ segs, T *Lx, PeerPtrs peers)
+{
+    const PullSeg g = segs [blockIdx.x] ;
+    const int col = blockIdx.y ;
+    if (col >= g.ncols) return ;
+    const int64_t base = g.off + (int64_t) col * g.ld ;
+    T *dst = Lx + base ;
+    for (int i = col + (int) threadIdx.x ; i < g.nrows ; i += 256)
+    {
+        T acc = dst [i] ;
+        for (uint32_t m = g.mask ; m ; m &= m - 1)
+        {
+            const int r = __ffs ((int) m) - 1 ;
+            acc += ldcg_ (reinterpret_cast<const T *> (peers.p [r]) + base + i) ;
+        }
+        dst [i] = acc ;
     }
 }
 
