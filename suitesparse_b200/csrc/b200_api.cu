@@ -683,7 +683,16 @@ b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, 
     f->dtype = dtype ; f->esize = dtype_esize (dtype) ; f->device = device ;
     try
     {
-        *status = build_plan (n, nsuper, super, pi, px, s, dtype_dmma (dtype), f->plan, nranks, rank) ;
+        // plan-only contexts (device < 0, the CPU tests of the planner) can ask for the truncated plan the
+        // executor builds after a failed pivot (repair_dist): CHOLMOD_B200_TRUNC="<supernode>,<columns>"
+        int64_t trunc_s = -1, trunc_ncol = 0 ;
+        if (device < 0 && nranks > 1)
+            if (const char *e = getenv ("CHOLMOD_B200_TRUNC"))
+            {
+                long long a = -1, b = 0 ;
+                if (sscanf (e, "%lld,%lld", &a, &b) == 2) { trunc_s = a ; trunc_ncol = b ; }
+            }
+        *status = build_plan (n, nsuper, super, pi, px, s, dtype_dmma (dtype), f->plan, nranks, rank, trunc_s, trunc_ncol) ;
         if (*status == B200_OK)
         {
             f->h_super.assign (super, super + nsuper + 1) ;

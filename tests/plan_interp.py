@@ -11,14 +11,18 @@ from numpy.lib.stride_tricks import as_strided
 from suitesparse_b200 import b200
 
 
-def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None, F=None):
+def scatter_A(sym, Sp, Si, Sx, beta, Lx, kfirst=0, klast=None, F=None, px=None, colmine=None):
     """What k_scatter_A does (Lx already zero on the touched supernodes); with F = (Fp, Fi, Fx) what
-    k_scatter_AF does: column k of S*F, gathered entry by entry."""
+    k_scatter_AF does: column k of S*F, gathered entry by entry.  px: the arena offsets of a distributed plan
+    (table "dpx") instead of L->px; colmine: that plan's column ownership mask."""
     n = sym["n"]
     klast = n if klast is None else klast
-    sup, pi, px, Ls = sym["super"], sym["pi"], sym["px"], sym["s"]
+    sup, pi, Ls = sym["super"], sym["pi"], sym["s"]
+    px = sym["px"] if px is None else px
     supermap = np.repeat(np.arange(sym["nsuper"]), np.diff(sup))
     for k in range(kfirst, klast):
+        if colmine is not None and not colmine[k]:
+            continue
         s = supermap[k]
         k1, k2 = sup[s], sup[s + 1]
         nsrow = pi[s + 1] - pi[s]
@@ -86,7 +90,7 @@ def _schedule(launches, prefer):
     return order
 
 
-def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
+def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None, barrier=None, pull=None):
     """Execute every launch of Factor F's plan on the flat factor array Lx.  Returns the smallest failing
     column (what the kernels record through atomicMin) or None.  With `host` (an array like Lx filled with
     NaN) the K_COPYOUT launches copy their segments into it at the moment the schedule reaches them."""
@@ -115,9 +119,25 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None):
             assert L["stream"] == 2
             if host is not None:
                 for seg in F.plan_table("copies", b200.COPY_DT)[first:first + cnt]:
-                    o, ln = int(seg["off"]), int(seg["len"])
-                    assert np.all(np.isnan(host[o:o + ln])), "segment copied twice"
-                    host[o:o + ln] = Lx[o:o + ln]
+                    o, ln, h = int(seg["off"]), int(seg["len"]), int(seg["hoff"])
+                    assert np.all(np.isnan(host[h:h + ln])), "segment copied twice"
+                    host[h:h + ln] = Lx[o:o + ln]
+            continue
+        if kind == b200.K_BARRIER:
+            assert L["stream"] == 3 and barrier is not None
+            barrier()
+            continue
+        if kind == b200.K_PULL:
+            # pull (seg, r) -> rank r's copy of the block as an (nrows x ncols) array; only the lower part counts
+            assert pull is not None
+            for seg in F.plan_table("pulls", b200.PULL_DT)[first:first + cnt]:
+                nr, nc, ld = int(seg["nrows"]), int(seg["ncols"]), int(seg["ld"])
+                mine = _view(Lx, int(seg["off"]), nr, nc, ld)
+                low = np.arange(nr)[:, None] >= np.arange(nc)[None, :]
+                for r in range(32):
+                    if int(seg["mask"]) >> r & 1:
+                        theirs = pull(int(seg["off"]), nr, nc, ld, r)
+                        mine[low] += theirs[low]
             continue
         if kind in b200.TILE_SHAPE:
             TM, TN = b200.TILE_SHAPE[kind]
