@@ -331,6 +331,14 @@ double refd_resid (void *hv, const double *x, const double *b)
     return rn / (an * xn + bn + (n == 0 ? 1 : 0)) ;
 }
 
+// cholmod_l_rcond of the current factor (reads the diagonal of L->x on the host)
+double refd_rcond (void *hv)
+{
+    refd *h = (refd *) hv ;
+    if (!h->L) return -1 ;
+    return cholmod_l_rcond (h->L, &h->cm) ;
+}
+
 int refd_set_int (void *hv, const char *name, int64_t v)
 {
     refd *h = (refd *) hv ;

@@ -62,6 +62,8 @@ def _driver():
         lib.refd_get_int.argtypes = [C.c_void_p, C.c_char_p]
         lib.refd_get_double.restype = C.c_double
         lib.refd_get_double.argtypes = [C.c_void_p, C.c_char_p]
+        lib.refd_rcond.restype = C.c_double
+        lib.refd_rcond.argtypes = [C.c_void_p]
         lib.refd_get_ptr.restype = C.c_void_p
         lib.refd_get_ptr.argtypes = [C.c_void_p, C.c_char_p]
         _lib = lib
@@ -236,6 +238,9 @@ class Ref:
 
     def set_minor(self, minor):
         self.lib.refd_set_minor(self.h, int(minor))
+
+    def rcond(self):
+        return float(_driver().refd_rcond(self.h))
 
     def solve(self, b):
         b = np.asfortranarray(b, dtype=np.float64 if self.xtype == 1 else np.complex128)

@@ -34,6 +34,7 @@
 //                                 cholmod_l_rcond, a host-side solve).  cholmod_l_solve then runs on the device
 //                                 and the 8-59 GB copy of SURVEY.md 8f never happens.  Off by default: a program
 //                                 that reads L->x directly, without going through CHOLMOD, would see stale memory.
+//   CHOLMOD_B200_TRACE=1          one line on stderr per numeric factorization that ran on the device
 //   CHOLMOD_B200_DEVICE_SOLVE=1   device sweeps for cholmod_l_solve without the lazy copy (host L->x is then assumed
 //                                 unmodified since the factorization)
 //
@@ -48,6 +49,7 @@
 #include "../../include/cholmod_b200.h"
 #include <dlfcn.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <pthread.h>
@@ -522,6 +524,9 @@ static int shim_worker (cholmod_sparse *A, cholmod_sparse *F, double beta [2], c
     else
         st = b200_super_numeric_c (s->ctx, (const int64_t *) A->p, (const int64_t *) A->i, Anz,
             (const float *) A->x, (const float *) Az, beta [0], quick, (float *) Lx, &minor) ;
+    if (env_int ("CHOLMOD_B200_TRACE", 0))
+        fprintf (stderr, "cholmod_b200: numeric factorization on device%s %d (n = %lld, status %d)\n",
+            s->multi ? "s from" : "", shim_device (), (long long) L->n, st) ;
     s->last_L = L ; s->last_Lx = L->x ;
     s->values_valid = (st == B200_OK) ;
     s->host_stale = (lazy && st >= 0) ;

@@ -1,7 +1,8 @@
-"""GPU test of the multi-GPU factorization: two (or more) processes, one per GPU, each with its share of
-the distributed plan, NCCL broadcasts of subtrees and panels in between.  Every rank must end with the
-complete factor, within 1e-10 of the reference's; rank 0's host L->x (copy-out schedule) too.
-Skipped when the box has fewer than 2 GPUs."""
+"""GPU test of the multi-GPU factorization, one process per GPU: each rank factorizes its subtrees, accumulates
+its contribution blocks to the top separators, the block owners pull them over NVLink (arenas attached through
+CUDA IPC handles), the top separators are factorized cooperatively (NCCL broadcasts of finished panels), and
+every rank copies what it owns into ONE host L->x (a shared mapping).  That L->x must be within 1e-10 of the
+reference's; a rank's arena must hold only its share.  Skipped when the box has fewer than 2 GPUs."""
 import json
 import os
 import subprocess
@@ -27,27 +28,51 @@ from oracle import refd
 from suitesparse_b200 import b200, matrices as M
 from cases import Case
 out = []
-for kind, size, shift, herm in (("lap3d7", 30, None, False), ("lap2d9", 150, None, False),
-                                ("lap3d7", 14, (1500, -1.0), False), ("lap3d7", 24, None, True)):
+for ci, (kind, size, shift, herm) in enumerate((("lap3d7", 30, None, False), ("lap2d9", 150, None, False),
+                                                ("lap3d7", 14, (1500, -1.0), False), ("lap3d7", 24, None, True))):
     c = Case(kind, size, refd.CHOLMOD_METIS, shift_diag=shift, hermitian=herm)
+    # the caller's ONE host L->x: a shared mapping every rank writes its share into
+    path = "/dev/shm/b200_multi_%%s_%%d.bin" %% (os.environ["MASTER_PORT"], ci)
+    if rank == 0:
+        Lx = np.memmap(path, dtype=c.Lref.dtype, mode="w+", shape=(c.sym["xsize"],))
+    dist.barrier()
+    if rank != 0:
+        Lx = np.memmap(path, dtype=c.Lref.dtype, mode="r+", shape=(c.sym["xsize"],))
     F = b200.Factor(c.sym, dtype=c.Lref.dtype, device=rank, nranks=world, rank=rank)
     F.comm_init_torch()
     res = {}
     for rep in range(2):                                    # twice: the context is reusable
         if rank == 0:
-            st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)     # host buffer in / out on rank 0
-        else:
-            F.upload_matrix(c.Sp, c.Si, c.Sx)
-            st = F.factor_device()
-            Lx = F.download_factor()                        # every rank holds the whole factor
-        res = dict(status=st, minor=F.minor, err=c.rel_err(Lx), ref_status=c.status, ref_minor=c.minor,
-                   zero_same=bool(np.array_equal(Lx == 0, c.Lref == 0)), nccl=F.geti("nccl_calls"), ntop=F.geti("ntop"))
-    if shift is None:
+            Lx[:] = np.nan
+        dist.barrier()
+        st, _ = F.super_numeric(c.Sp, c.Si, c.Sx, Lx=Lx)   # every rank: host A in, its share of L->x out
+        torch.cuda.synchronize(); dist.barrier()
+        res = dict(status=st, minor=F.minor, ref_status=c.status, ref_minor=c.minor, nccl=F.geti("nccl_calls"),
+                   ntop=F.geti("ntop"), dxsize=F.geti("dxsize"), top_size=F.geti("top_size"), xsize=F.geti("xsize"),
+                   npulls=F.geti("npulls"), nvlink=F.geti("nvlink_in_bytes"))
+        if rank == 0:
+            full = np.array(Lx)
+            res.update(err=c.rel_err(full), complete=bool(np.all(np.isfinite(full))),
+                       zero_same=bool(np.array_equal(full == 0, c.Lref == 0)))
+    # a distributed factor is not solved on the device: rank 0 puts the assembled L->x into a one-GPU context
+    try:
+        F.solve(np.ones(c.n, dtype=c.Lref.dtype))
+        res["dist_solve_refused"] = False
+    except b200.B200Error as e:
+        res["dist_solve_refused"] = (e.status == b200.INVALID)
+    if shift is None and rank == 0:
+        G = b200.Factor(c.sym, dtype=c.Lref.dtype, device=0)
+        G.upload_factor(np.array(Lx))
         b = M.rhs(c.n) * ((1 + 0.5j) if herm else 1.0)
-        x = np.empty_like(b); x[c.sym["Perm"]] = F.solve(b[c.sym["Perm"]])
+        x = np.empty_like(b); x[c.sym["Perm"]] = G.solve(b[c.sym["Perm"]])
         res["resid"] = c.ref.resid(x, b)
+        G.close()
     out.append(res)
     F.close()
+    dist.barrier()
+    del Lx
+    if rank == 0:
+        os.unlink(path)
 allres = [None] * world
 dist.all_gather_object(allres, out)
 if rank == 0:
@@ -69,11 +94,18 @@ def test_factorization_over_several_gpus(world):
     line = [ln for ln in outs[0][0].splitlines() if ln.startswith("RESULT ")][-1]
     allres = json.loads(line[len("RESULT "):])
     assert len(allres) == world
-    for per_rank in allres:
+    for r, per_rank in enumerate(allres):
         ok1, ok2, bad, okz = per_rank          # okz: the Hermitian (complex double) case, (re,im) pairs on the wire
         for ok in (ok1, ok2, okz):
-            assert ok["status"] == 0 and ok["err"] <= 1e-10 and ok["resid"] <= 1e-12
-            assert ok["nccl"] > 0
+            assert ok["status"] == 0 and ok["nccl"] > 0 and ok["dist_solve_refused"]
+            if r == 0:
+                assert ok["complete"] and ok["err"] <= 1e-10 and ok["resid"] <= 1e-12
         assert ok1["ntop"] > 0
         assert bad["status"] == 1 == bad["ref_status"] and bad["minor"] == bad["ref_minor"]
-        assert bad["zero_same"] and bad["err"] <= 1e-10
+        if r == 0:
+            assert bad["complete"] and bad["zero_same"] and bad["err"] <= 1e-10
+    # sharded storage: top separators everywhere, every subtree on exactly one rank; somebody pulled over NVLink
+    for k in (0, 1, 3):
+        top = allres[0][k]["top_size"]
+        assert sum(per_rank[k]["dxsize"] - top for per_rank in allres) == allres[0][k]["xsize"] - top
+        assert sum(per_rank[k]["npulls"] for per_rank in allres) > 0 and sum(per_rank[k]["nvlink"] for per_rank in allres) > 0
