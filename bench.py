@@ -241,13 +241,26 @@ def main():
     Sp, Si, Sx = ref.seam()
     fl = sym["fl"]
     t0 = time.time()
-    # N > 1: ONE factorization partitioned over the N GPUs (etree subtrees + block-cyclic top separators,
-    # panels broadcast with NCCL); every rank ends with the whole factor.  Strong scaling: value = fl / t.
+    # N > 1: ONE factorization partitioned over the N GPUs: every rank owns (stores, factorizes, copies out) some
+    # etree subtrees; what they send into the top separators is pulled, as contribution blocks, by the owners of
+    # the separators' 256-column blocks over NVLink; the separators are factorized 1-D block cyclic with their
+    # finished panels broadcast.  Strong scaling: value = fl / t.
     F = b200.Factor(sym, dtype=fdtype, device=local, nranks=world, rank=rank)
     if world > 1:
         F.comm_init_torch()
     t_plan = time.time() - t0
-    Lx_host = np.empty(sym["xsize"], dtype=fdtype) if rank == 0 else None
+    # the caller's ONE host L->x.  With several ranks it is a shared mapping: every rank copies the part of the
+    # factor it owns into it over its own PCIe link.
+    shm_path = None
+    if world == 1:
+        Lx_host = np.empty(sym["xsize"], dtype=fdtype)
+    else:
+        shm_path = "/dev/shm/b200_bench_%s.bin" % os.environ.get("MASTER_PORT", "0")
+        if rank == 0:
+            Lx_host = np.memmap(shm_path, dtype=fdtype, mode="w+", shape=(sym["xsize"],))
+        dist.barrier()
+        if rank != 0:
+            Lx_host = np.memmap(shm_path, dtype=fdtype, mode="r+", shape=(sym["xsize"],))
     # what a one-shot cholmod_factorize pays on top of a steady-state step: the context (plan + tables + arena,
     # `plan_s`) and, in the first host-buffer call, page-locking the caller's L->x (cudaHostRegister)
     first_call_ms = None
@@ -293,13 +306,8 @@ def main():
     e2e = None
     if not args.no_e2e:
         def one_e2e_step():
-            # rank 0 is the caller that owns host A and host L->x; the other ranks take part in the same
-            # factorization (they receive A from their own host copy and keep L on the device)
-            if rank == 0:
-                st, _ = F.super_numeric(Sp, Si, Sx, Lx=Lx_host)
-            else:
-                F.upload_matrix(Sp, Si, Sx)
-                st = F.factor_device()
+            # every rank: host A in (its own PCIe link), its share of the factor out into the one host L->x
+            st, _ = F.super_numeric(Sp, Si, Sx, Lx=Lx_host)
             assert st == b200.OK
         for _ in range(2):                      # first call pins the caller's L->x (once per factor object)
             one_e2e_step()
@@ -314,7 +322,7 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             t_e2e = float(tt.item())
         e2e = {"value": fl / t_e2e / 1e9, "unit": UNIT, "ms_per_step": 1e3 * t_e2e,
-               "h2d_bytes_per_step": int(Sp.nbytes + Si.nbytes + Sx.nbytes),
+               "h2d_bytes_per_step": int(Sp.nbytes + Si.nbytes + Sx.nbytes) * world,
                "d2h_bytes_per_step": int(sym["xsize"] * np.dtype(fdtype).itemsize),
                "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h"),
                "first_call_ms": first_call_ms, "context_build_ms": 1e3 * t_plan,
@@ -325,9 +333,18 @@ def main():
     F.factor_device()
     F.seti("profile", 0)
     nccl_calls = F.geti("nccl_calls")
+    per_rank = None
+    if world > 1:
+        mine = dict(rank=rank, device_bytes=F.geti("device_bytes"), arena_bytes=F.geti("dxsize") * np.dtype(fdtype).itemsize,
+                    nvlink_in_bytes=F.geti("nvlink_in_bytes"), ms_pull=F.getd("ms_pull"), npulls=F.geti("npulls"),
+                    d2h_bytes=sum(int(c["len"]) for c in F.plan_table("owned", b200.COPY_DT)) * np.dtype(fdtype).itemsize)
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
     if rank != 0:
         F.close()
+        del Lx_host
         if world > 1:
+            dist.barrier()
             dist.destroy_process_group()
         return
 
@@ -400,11 +417,18 @@ def main():
     from suitesparse_b200 import matrices
     bvec = matrices.rhs(sym["n"])
     xs = np.empty(sym["n"])
-    xs[sym["Perm"]] = F.solve(bvec[sym["Perm"]])
-    solve_first_ms = F.getd("ms_solve")     # builds the solve schedule and inverts the wide supernodes' diagonal blocks
-    xs[sym["Perm"]] = F.solve(bvec[sym["Perm"]])
-    check = {"solve_ms": F.getd("ms_solve"), "solve_first_ms": solve_first_ms, "scaled_residual": ref.resid(xs, bvec),
+    # several ranks: no rank holds the whole factor; the assembled host L->x goes into a one-GPU context
+    G = F if world == 1 else b200.Factor(sym, dtype=fdtype, device=local)
+    if world > 1:
+        assert np.all(np.isfinite(Lx_host[::4097])), "the ranks' copy-outs left holes in L->x"
+        G.upload_factor(np.array(Lx_host))
+    xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
+    solve_first_ms = G.getd("ms_solve")     # builds the solve schedule and inverts the wide supernodes' diagonal blocks
+    xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
+    check = {"solve_ms": G.getd("ms_solve"), "solve_first_ms": solve_first_ms, "scaled_residual": ref.resid(xs, bvec),
              "tolerance": 1e-5 if args.single else 1e-12}
+    if world > 1:
+        G.close()
 
     # ---- CPU baseline: the reference's CPU path on the workload itself, rank 0, N = 1 only; its factor is the
     # full-size parity check of ours (north_star: max|dL|/max|L| <= 1e-10) ----------------------------------
@@ -433,17 +457,23 @@ def main():
         "config": {**reference_config(desc, sym), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
                    "relmap_len": F.geti("relmap_len"), "device_bytes": F.geti("device_bytes"),
                    "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * 8 / 1e9),
-                   "parallelism": ("one factorization over %d GPUs: etree subtrees per GPU + block-cyclic top separators, "
-                                   "%d NCCL broadcasts per step, %d top supernodes" % (world, nccl_calls, F.geti("ntop")))
+                   "parallelism": ("one factorization over %d GPUs: etree subtrees owned per GPU, their contribution blocks "
+                                   "pulled over NVLink by the owners of the top separators' blocks, top separators 1-D "
+                                   "block cyclic (%d NCCL calls per step, %d top supernodes), every GPU copies its share of "
+                                   "L->x to the host" % (world, nccl_calls, F.geti("ntop")))
                    if world > 1 else "1 GPU",
                    "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
-        "check": check, "hbm_phase": hbm_phase,
+        "check": check, "hbm_phase": hbm_phase, "per_rank": per_rank,
+        "nvlink_bytes_per_step": sum(p["nvlink_in_bytes"] for p in per_rank) if per_rank else 0,
         "kernels": kinds, "level_end_ms": timeline, "cpu_baseline": cpu,
     }
     print(json.dumps(out))
     F.close()
+    del Lx_host
     if world > 1:
+        dist.barrier()
+        os.unlink(shm_path)
         dist.destroy_process_group()
 
 
