@@ -373,7 +373,7 @@ class Factor:
 
 
 ITEM_DT = np.dtype([("a_off", "<i8"), ("c_off", "<i8"), ("map_off", "<i8"), ("lda", "<i4"), ("ldc", "<i4"),
-                    ("M", "<i4"), ("N", "<i4"), ("K", "<i4"), ("pad", "<i4")])
+                    ("M", "<i4"), ("N", "<i4"), ("K", "<i4"), ("shift", "<i4")])
 TILE_DT = np.dtype([("item", "<i4"), ("ti", "<i4"), ("tj", "<i4"), ("k0", "<i4"), ("k1", "<i4")])
 POTRF_DT = np.dtype([("off", "<i8"), ("col", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("slot", "<i4"), ("pad", "<i4")])
 TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("jb", "<i4"), ("nrows", "<i4"),

@@ -110,6 +110,7 @@ struct b200_factor
     cudaStream_t stream2 = nullptr ;        // look-ahead stream (lower priority) of the wide trailing updates
     cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
     cudaStream_t stream4 = nullptr ;        // communication stream: every NCCL call of this context
+    cudaStream_t stream5 = nullptr ;        // far stream: panel rows far below the diagonal block (plan_factor)
     std::vector<cudaStream_t> gstreams ;    // subtree-group streams of a single-GPU plan: [2g] chain, [2g+1] look-ahead
     cudaEvent_t ev_comm [2] = {} ;
     void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
@@ -265,7 +266,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     T *Lx = reinterpret_cast<T *> (f->d_Lx.p) ;
     T *winv = reinterpret_cast<T *> (f->d_winv.p) ;
     size_t nev = 0 ;
-    while ((int) f->gstreams.size () < P.nstreams - 4)
+    while ((int) f->gstreams.size () < P.nstreams - 5)
     {
         // same priorities as the main pair: chains high, look-ahead updates low
         int lo = 0, hi = 0 ;
@@ -277,7 +278,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
     auto stream_of = [&] (int id) -> cudaStream_t
     {
         return (id == 0) ? f->stream : (id == 1) ? f->stream2 : (id == 2) ? f->stream3 : (id == 3) ? f->stream4
-            : f->gstreams [(size_t) (id - 4)] ;
+            : (id == 4) ? f->stream5 : f->gstreams [(size_t) (id - 5)] ;
     } ;
     while ((int64_t) f->plan_ev.size () < (int64_t) P.nevents)
     {
@@ -310,7 +311,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             }
             continue ;
         }
-        if (L.stream < 0 || L.stream >= std::max (4, P.nstreams)) return B200_INVALID ;
+        if (L.stream < 0 || L.stream >= std::max (5, P.nstreams)) return B200_INVALID ;
         const cudaStream_t st = stream_of (L.stream) ;
         if (L.wait_ev >= 0) CK (cudaStreamWaitEvent (st, f->plan_ev [L.wait_ev], 0), "wait event") ;
         if (L.kind == K_BCAST)
@@ -440,6 +441,7 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
         CK (cudaStreamSynchronize (f->stream), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream2), "profile sync") ;
         CK (cudaStreamSynchronize (f->stream4), "profile sync") ;
+        CK (cudaStreamSynchronize (f->stream5), "profile sync") ;
         for (cudaStream_t g : f->gstreams) CK (cudaStreamSynchronize (g), "profile sync") ;
         size_t e = 0, li = 0 ;
         f->ms_launch.assign (P.launches.size (), 0.f) ;
@@ -605,6 +607,8 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
         CK (cudaStreamCreateWithFlags (&f->stream3, cudaStreamNonBlocking), "stream3") ;
         CK (cudaStreamCreateWithPriority (&f->stream4, cudaStreamNonBlocking, hi), "stream4") ;
+        // between the panel chain and the look-ahead updates when the device has more than two priority levels
+        CK (cudaStreamCreateWithPriority (&f->stream5, cudaStreamNonBlocking, (hi < lo - 1) ? hi + 1 : hi), "stream5") ;
         for (auto &e : f->ev_comm) CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "event") ;
     }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
@@ -751,6 +755,7 @@ void b200_destroy (b200_factor *f)
         for (cudaStream_t g : f->gstreams) { cudaStreamSynchronize (g) ; cudaStreamDestroy (g) ; }
         if (f->stream3) { cudaStreamSynchronize (f->stream3) ; cudaStreamDestroy (f->stream3) ; }
         if (f->stream4) { cudaStreamSynchronize (f->stream4) ; cudaStreamDestroy (f->stream4) ; }
+        if (f->stream5) { cudaStreamSynchronize (f->stream5) ; cudaStreamDestroy (f->stream5) ; }
         for (auto &e : f->ev_comm) if (e) cudaEventDestroy (e) ;
         cudaStreamDestroy (f->stream) ;
         cudaGetLastError () ;
@@ -1115,6 +1120,7 @@ static int repair_dist (b200_factor *f, int64_t minor, double beta, int quick)
     if (cudaStreamSynchronize (st0) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
     if (cudaStreamSynchronize (f->stream2) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
     if (cudaStreamSynchronize (f->stream4) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
+    if (cudaStreamSynchronize (f->stream5) != cudaSuccess && !st) st = B200_GPU_PROBLEM ;
     items.release () ; tiles.release () ; potrf.release () ; trsm.release () ; pulls.release () ;
     return st ;
 }

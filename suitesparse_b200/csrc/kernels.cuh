@@ -241,7 +241,7 @@ __global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ 
         #pragma unroll
         for (int jj = 0 ; jj < SIMT_TN ; jj++)
         {
-            T b = (jj < nj) ? Ak [j0 + jj] : zero ;
+            T b = (jj < nj) ? Ak [j0 + jj - it.shift] : zero ;
             acc [jj] += mulc (a, b) ;
         }
     }
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ 
     for (int jj = 0 ; jj < SIMT_TN ; jj++)
     {
         int j = j0 + jj ;
-        if (jj < nj && i >= j)
+        if (jj < nj && i + it.shift >= j)
         {
             int64_t cj = mapped ? (int64_t) map [j] : (int64_t) j ;
             atomic_sub (C + cj * it.ldc, acc [jj]) ;
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
     const int mA = min (TM, it.M - i0), nB = min (TN, it.N - j0) ;
     const int64_t lda = it.lda ;
     const double *A = Lx + it.a_off ;
-    const double *Arow = A + i0, *Brow = A + j0 ;
+    const double *Arow = A + i0, *Brow = A - it.shift + j0 ;     // B (0,0) lies `shift` rows above A (0,0)
     const int kbeg = t.k0, kend = t.k1 ;
     const int nk = (kend - kbeg + DM_KC - 1) / DM_KC ;
 
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
         for (int b = 0 ; b < NTL ; b++) { acc [a][b][0] = 0.0 ; acc [a][b][1] = 0.0 ; }
 
     // a warp whose whole sub-tile lies strictly above the diagonal has nothing to compute
-    const bool warp_live = (i0 + wm * WM + WM - 1) >= (j0 + wn * WN) ;
+    const bool warp_live = (i0 + wm * WM + WM - 1 + it.shift) >= (j0 + wn * WN) ;
 
     #pragma unroll
     for (int s = 0 ; s < DM_STAGES - 1 ; s++)
@@ -432,7 +432,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_dmma (const
             for (int a = 0 ; a < MT ; a++)
             {
                 const int il = wm * WM + a * 8 + fm ;
-                if (il < mA && i0 + il >= j) atomicAdd (Cj + smap_r [il], -acc [a][b][e]) ;
+                if (il < mA && i0 + il + it.shift >= j) atomicAdd (Cj + smap_r [il], -acc [a][b][e]) ;
             }
         }
     }
@@ -524,7 +524,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_zmma (const
     const int lmA = tid % TM, lkA = tid / TM, lmB = tid % TN, lkB = tid / TN ;
     const bool rokA = lmA < mA, rokB = lmB < nB ;
     const zdouble *gA = A + i0 + lmA + (int64_t) (kbeg + lkA) * lda ;
-    const zdouble *gB = A + j0 + lmB + (int64_t) (kbeg + lkB) * lda ;
+    const zdouble *gB = A - it.shift + j0 + lmB + (int64_t) (kbeg + lkB) * lda ;
     const int64_t stepA = (int64_t) KPP_A * lda, stepB = (int64_t) KPP_B * lda ;
     const unsigned sA0 = (unsigned) __cvta_generic_to_shared (sA) + (unsigned) ((lkA * LDA_S + lmA) * 16) ;
     const unsigned sB0 = (unsigned) __cvta_generic_to_shared (sB) + (unsigned) ((lkB * LDB_S + lmB) * 16) ;
@@ -558,7 +558,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_zmma (const
     for (int a = 0 ; a < MT ; a++)
         #pragma unroll
         for (int b = 0 ; b < NTL ; b++) { cre [a][b][0] = 0.0 ; cre [a][b][1] = 0.0 ; cim [a][b][0] = 0.0 ; cim [a][b][1] = 0.0 ; }
-    const bool warp_live = (i0 + wm * WM + WM - 1) >= (j0 + wn * WN) ;
+    const bool warp_live = (i0 + wm * WM + WM - 1 + it.shift) >= (j0 + wn * WN) ;
 
     #pragma unroll
     for (int s = 0 ; s < DM_STAGES - 1 ; s++)
@@ -601,7 +601,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_zmma (const
             for (int a = 0 ; a < MT ; a++)
             {
                 const int il = wm * WM + a * 8 + fm ;
-                if (il < mA && i0 + il >= j)
+                if (il < mA && i0 + il + it.shift >= j)
                 {
                     zdouble *dst = Cj + smap_r [il] ;
                     atomicAdd (&dst->re, -cre [a][b][e]) ;
@@ -666,7 +666,7 @@ __global__ void __launch_bounds__ ((TM / 4) * (TN / 4)) k_upd_cfma (const UpdTil
             const int sz = (m < nB && kb + k < kend) ? ES : 0 ;
             const unsigned d = (unsigned) __cvta_generic_to_shared (sB + (buf * DM_KC + k) * TN + m) ;
             asm volatile ("cp.async.ca.shared.global [%0], [%1], %2, %3;\n"
-                :: "r" (d), "l" (A + j0 + m + (int64_t) (kb + k) * lda), "n" (ES), "r" (sz)) ;
+                :: "r" (d), "l" (A - it.shift + j0 + m + (int64_t) (kb + k) * lda), "n" (ES), "r" (sz)) ;
         }
     } ;
     const T zero = from_real<T> (0) ;
@@ -675,7 +675,7 @@ __global__ void __launch_bounds__ ((TM / 4) * (TN / 4)) k_upd_cfma (const UpdTil
     for (int a = 0 ; a < 4 ; a++)
         #pragma unroll
         for (int b = 0 ; b < 4 ; b++) acc [a][b] = zero ;
-    const bool live = (i0 + tx * 4 + 3) >= (j0 + ty * 4) ;
+    const bool live = (i0 + tx * 4 + 3 + it.shift) >= (j0 + ty * 4) ;
     #pragma unroll
     for (int s = 0 ; s < DM_STAGES - 1 ; s++)
     {
@@ -723,7 +723,7 @@ __global__ void __launch_bounds__ ((TM / 4) * (TN / 4)) k_upd_cfma (const UpdTil
         for (int a = 0 ; a < 4 ; a++)
         {
             const int il = tx * 4 + a ;
-            if (il < mA && i0 + il >= j) atomic_sub (Cj + smap_r [il], acc [a][b]) ;
+            if (il < mA && i0 + il + it.shift >= j) atomic_sub (Cj + smap_r [il], acc [a][b]) ;
         }
     }
 }
@@ -785,7 +785,7 @@ __global__ void __launch_bounds__ ((TM / 8) * (TN / 8)) k_upd_ffma (const UpdTil
             const int sz = (m < nB && kb + k < kend) ? 4 : 0 ;
             const unsigned d = (unsigned) __cvta_generic_to_shared (sB + (buf * DM_KC + k) * TN + m) ;
             asm volatile ("cp.async.ca.shared.global [%0], [%1], 4, %2;\n"
-                :: "r" (d), "l" (A + j0 + m + (int64_t) (kb + k) * lda), "r" (sz)) ;
+                :: "r" (d), "l" (A - it.shift + j0 + m + (int64_t) (kb + k) * lda), "r" (sz)) ;
         }
     } ;
     float acc [8][8] ;
@@ -794,7 +794,7 @@ __global__ void __launch_bounds__ ((TM / 8) * (TN / 8)) k_upd_ffma (const UpdTil
         #pragma unroll
         for (int b = 0 ; b < 8 ; b++) acc [a][b] = 0.f ;
     // a thread whose whole micro-tile lies strictly above the diagonal has nothing to compute
-    const bool live = (i0 + tx * 8 + 7) >= (j0 + ty * 8) ;
+    const bool live = (i0 + tx * 8 + 7 + it.shift) >= (j0 + ty * 8) ;
     #pragma unroll
     for (int s = 0 ; s < DM_STAGES - 1 ; s++)
     {
@@ -843,7 +843,7 @@ __global__ void __launch_bounds__ ((TM / 8) * (TN / 8)) k_upd_ffma (const UpdTil
         for (int a = 0 ; a < 8 ; a++)
         {
             const int il = tx * 8 + a ;
-            if (il < mA && i0 + il >= j) atomicAdd (Cj + smap_r [il], -acc [a][b]) ;
+            if (il < mA && i0 + il + it.shift >= j) atomicAdd (Cj + smap_r [il], -acc [a][b]) ;
         }
     }
 }

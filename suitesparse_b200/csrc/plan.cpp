@@ -61,13 +61,10 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     const int TM = (cls == K_UPD_SIMT) ? SIMT_TM : (cls == K_UPD_D64 ? 64 : BIG_TM) ;
     const int TN = (cls == K_UPD_SIMT) ? SIMT_TN : (cls == K_UPD_D64 ? 64 : BIG_TN) ;
     const int64_t nti = cdiv (M, TM), ntj = cdiv (N, TN) ;
-    // count the tiles that intersect the lower trapezoid
+    // the tiles that hold a wanted entry (i + shift >= j): tile row ti reaches down to row ti*TM + TM-1
+    auto first_ti = [&] (int64_t tj) -> int64_t { return std::max<int64_t> (0, tj * TN - it.shift) / TM ; } ;
     int64_t ntiles = 0 ;
-    for (int64_t tj = 0 ; tj < ntj ; tj++)
-    {
-        int64_t ti0 = (tj * TN) / TM ;          // first tile row whose last row reaches column tj*TN
-        ntiles += nti - ti0 ;
-    }
+    for (int64_t tj = 0 ; tj < ntj ; tj++) ntiles += nti - first_ti (tj) ;
     // split K when a long inner dimension meets few tiles (the output is accumulated with atomics,
     // so partial sums need no workspace)
     int64_t nsplit = 1 ;
@@ -78,11 +75,11 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     }
     int64_t kchunk = cdiv (cdiv (K, nsplit), 16) * 16 ;
     auto &out = sink.cls [cls] ;
-    P.flops_kind [cls] += (double) K * (double) N * (2.0 * (double) M - (double) N) ;
+    P.flops_kind [cls] += (it.shift >= N) ? 2.0 * (double) K * (double) M * (double) N
+        : (double) K * (double) N * (2.0 * (double) M - (double) N) ;
     for (int64_t tj = 0 ; tj < ntj ; tj++)
     {
-        int64_t ti0 = (tj * TN) / TM ;
-        for (int64_t ti = ti0 ; ti < nti ; ti++)
+        for (int64_t ti = first_ti (tj) ; ti < nti ; ti++)
         {
             for (int64_t k0 = 0 ; k0 < K ; k0 += kchunk)
             {
@@ -169,7 +166,7 @@ void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t 
         it.ldc = (int32_t) (pi [s+1] - pi [s]) ;
         it.map_off = P.pair_map [pid] ;
         it.M = pr.ndrow2 ; it.N = pr.ndrow1 ; it.K = (int32_t) (super [d+1] - super [d]) ;
-        it.pad = 0 ;
+        it.shift = 0 ;
         if (!split) { add_item (out, it, sink, use_dmma) ; continue ; }
         const int32_t *map = P.relmap.data () + it.map_off ;    // map [j] < nscol (s) for j < N
         for (int64_t ja = 0 ; ja < it.N ; )
@@ -205,36 +202,102 @@ void plan_updates_into (Plan &out, const Plan &P, const Own &own, const int64_t 
 //     look-ahead:                   [wait eF(T)]  Ub(T)  rec eB(T)       [wait eF(T+1)]  Ub(T+1) ...
 // Ub(T) and Ua(T+1) may touch the same columns concurrently; both only subtract with atomics.
 //
+// Near / far (sf >= 0, supernodes with at least FAR_MIN_ROWS rows beyond the next two diagonal blocks): what
+// the NEXT diagonal block waits for is only the work on the rows close to the diagonal, so only that stays on
+// the main stream.  With D = the diagonal block of T, N1 = the 256 rows below it, far = all rows below N1:
+//     main:   per step  potrf, trsm of the rows of D u N1, inner update of D u N1, rec eS(step) ;
+//             after the last step  rec eN(T) ;  Ua_near(T) = next diagonal block only ;  F(T+1) starts, its first
+//             trsm waits for eM(T)
+//     far:    per step  [wait eS(step)]  trsm of the far rows, inner update of the far rows ;  rec eFar(T) ;
+//             [wait eN(T)]  Ua_mid(T) = rows N1 of block T+1, rec eM(T) ;  Ua_far(T) = its far rows
+//     look-ahead:  [wait eN(T), eFar(T)]  Ub(T)
+// The far stream works through the tall, throughput-bound launches while the main stream is already on the next
+// diagonal block.  An update of a block of rows far below the diagonal is a rectangular product: an UpdItem with
+// shift > 0.  Inverses of the diagonal blocks of such supernodes live in slots that rotate over two outer blocks,
+// because a far trsm may still read the inverse of step j while the main stream factorizes the steps after it.
+//
 // Distributed (top) supernodes: block T is factorized by its owner and then broadcast (K_BCAST, issued
 // by every rank in the same order); Ua(T) is done by the owner of block T+1 and Ub(T) as one slab per
 // later block by that block's owner -- a 1-D block-cyclic right-looking Cholesky.
+constexpr int64_t FAR_MIN_ROWS = 1024 ;     // (CHOLMOD_B200_FAR_MIN overrides it: the CPU tests use small matrices)
+
 void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int32_t *S, const int64_t *ncol_eff, int64_t ns, int level, TileSink &sink, bool use_dmma,
-    char *copied = nullptr, int sm = 0, int sl = 1, int32_t slot_base = 0, const int64_t *hpx = nullptr)
+    char *copied = nullptr, int sm = 0, int sl = 1, int32_t slot_base = 0, const int64_t *hpx = nullptr, int sf = -1)
 {
+    // sm / sl: the stream of the panel chain and the look-ahead stream of this call (0 / 1 unless the level
+    // is being factorized group by group, see build_plan); sf: the far stream, or -1 (no near / far split);
+    // slot_base: first inverse slot it may use
     // px: arena offsets (Plan::dpx); hpx: offsets in the caller's L->x (the copy-out needs both; NULL: the same)
     if (!hpx) hpx = px ;
-    // sm / sl: the stream of the panel chain and the look-ahead stream of this call (0 / 1 unless the level
-    // is being factorized group by group, see build_plan); slot_base: first inverse slot it may use
+    if (!use_dmma) sf = -1 ;
+    int64_t far_min = FAR_MIN_ROWS ;
+    if (const char *e = getenv ("CHOLMOD_B200_FAR_MIN")) far_min = std::max (1, atoi (e)) ;
     int64_t maxcol = 0 ;
     for (int64_t q = 0 ; q < ns ; q++) maxcol = std::max (maxcol, ncol_eff [q]) ;
+    // far_from (q, J0): first far row of supernode q while outer block J0 is factorized, or nsrow (no far part)
+    auto far_from = [&] (int64_t q, int64_t J0) -> int64_t
+    {
+        const int64_t s = S [q], nsrow = pi [s+1] - pi [s] ;
+        const int64_t F = J0 + 2 * OUTER_NB ;
+        if (sf < 0 || ncol_eff [q] <= J0 || nsrow - F < far_min || !own.mine (s, J0 / OUTER_NB)) return nsrow ;
+        return F ;
+    } ;
+    // supernodes that ever have a far part get rotating inverse slots: 2 outer blocks x (OUTER_NB / POTRF_NB) steps
+    constexpr int ROT = 2 * (OUTER_NB / POTRF_NB) ;
+    std::vector<int32_t> farq ((size_t) ns, -1) ;
+    int32_t nfarq = 0 ;
+    for (int64_t q = 0 ; q < ns ; q++)
+        for (int64_t J0 = 0 ; J0 < ncol_eff [q] ; J0 += OUTER_NB)
+            if (far_from (q, J0) < pi [S [q] + 1] - pi [S [q]]) { farq [q] = nfarq++ ; break ; }
+    const int32_t step_slot_base = slot_base + ROT * nfarq ;
+    int64_t stepctr = 0 ;
+
     std::vector<PotrfBlk> pb [3] ;      // jb <= 16, <= 32, <= 64
-    std::vector<TrsmTile> tt [3] ;      // substitution, inverse 32, inverse 64
+    std::vector<TrsmTile> tt [3], ttf [3] ;     // substitution, inverse 32, inverse 64; near and far rows
+    TileSink sinkF ;                    // far updates of the current step / far parts of Ua
     int evB_prev = -1, evB_prev2 = -1 ; // eB(T-1), eB(T-2)
-    int last_bcast_ev = -1 ;
+    int last_bcast_ev = -1, last_far_ev = -1 ;
+    int evM_prev = -1 ;                 // eM(T-1): Ua_mid (T-1) is done (the first trsm of block T waits for it)
+    auto push_trsm = [&] (std::vector<TrsmTile> (&lists) [3], int stream, int wait_ev) -> bool
+    {
+        bool any = false ;
+        for (int c = 0 ; c < 3 ; c++)
+        {
+            if (lists [c].empty ()) continue ;
+            Launch L = make_launch (K_TRSM + c, (int64_t) out.trsm.size (), (int64_t) lists [c].size (), level, stream) ;
+            if (!any) L.wait_ev = wait_ev ;
+            any = true ;
+            out.count_kind [L.kind] += L.count ;
+            out.trsm.insert (out.trsm.end (), lists [c].begin (), lists [c].end ()) ;
+            out.launches.push_back (L) ;
+        }
+        return any ;
+    } ;
+    auto join = [&] (int stream, int wait_ev, int rec_ev)
+    {
+        Launch J = make_launch (K_JOIN, 0, 0, level, stream) ; J.wait_ev = wait_ev ; J.rec_ev = rec_ev ;
+        out.launches.push_back (J) ;
+    } ;
     for (int64_t J0 = 0 ; J0 < maxcol ; J0 += OUTER_NB)
     {
         const int64_t T = J0 / OUTER_NB ;
+        bool block_has_far = false ;
+        for (int64_t q = 0 ; q < ns ; q++) if (far_from (q, J0) < pi [S [q] + 1] - pi [S [q]]) block_has_far = true ;
         // ---- F(T): the panel chain of outer block T -------------------------------------------------
         // it reads columns that Ub(T-2) and earlier wrote; Ub(T-1) is only needed by F(T+1)
         int pending_wait = evB_prev2 ;
         evB_prev2 = -1 ;
-        for (int64_t j0 = J0 ; j0 < std::min (maxcol, J0 + OUTER_NB) ; j0 += POTRF_NB)
+        int trsm_wait = evM_prev ;      // rows N1 of this block got their Ua on the far stream
+        evM_prev = -1 ;
+        for (int64_t j0 = J0 ; j0 < std::min (maxcol, J0 + OUTER_NB) ; j0 += POTRF_NB, stepctr++)
         {
             for (auto &v : pb) v.clear () ;
             for (auto &v : tt) v.clear () ;
+            for (auto &v : ttf) v.clear () ;
             std::vector<PotrfBlk> small ;
-            int32_t nslots = slot_base ;
+            int32_t nslots = step_slot_base ;
+            bool far_step = false ;
             for (int64_t q = 0 ; q < ns ; q++)
             {
                 const int64_t s = S [q] ;
@@ -242,6 +305,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 if (nscol <= j0 || !own.mine (s, T)) continue ;
                 const int64_t jb = std::min<int64_t> (POTRF_NB, nscol - j0) ;
                 const int64_t r0 = j0 + jb ;
+                const int64_t F = far_from (q, J0) ;        // rows [r0, F) near, [F, nsrow) far
                 const int pcls = (jb <= 16) ? 0 : (jb <= 32) ? 1 : 2 ;
                 const bool inv = use_dmma && pcls > 0 && r0 < nsrow ;
                 PotrfBlk b ;
@@ -255,30 +319,46 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                     out.flops_kind [K_FACTOR_SMALL] += (double) jb * jb * jb / 3.0 + (double) (nsrow - nscol) * jb * jb ;
                     continue ;
                 }
-                b.slot = inv ? nslots++ : -1 ; b.pad = 0 ;
+                if (!inv) b.slot = -1 ;
+                else if (farq [q] >= 0) b.slot = slot_base + (int32_t) (stepctr % ROT) * nfarq + farq [q] ;
+                else b.slot = nslots++ ;
+                b.pad = 0 ;
                 pb [pcls].push_back (b) ;
                 out.flops_kind [K_POTRF16 + pcls] += (double) jb * jb * jb / 3.0 ;
                 const int tcls = inv ? pcls : 0 ;
                 for (int64_t r = r0 ; r < nsrow ; r += TRSM_ROWS)
                 {
+                    // tiles are cut at F so that no tile straddles the two zones
+                    const int64_t rend = (r < F) ? std::min (F, nsrow) : nsrow ;
                     TrsmTile t ;
                     t.diag_off = b.off ; t.row_off = px [s] + r + j0 * nsrow ;
                     t.lda = (int32_t) nsrow ; t.jb = (int32_t) jb ;
-                    t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, nsrow - r) ; t.slot = b.slot ;
-                    tt [tcls].push_back (t) ;
+                    t.nrows = (int32_t) std::min<int64_t> (TRSM_ROWS, rend - r) ; t.slot = b.slot ;
+                    ((r < F) ? tt : ttf) [tcls].push_back (t) ;
                     out.flops_kind [K_TRSM + tcls] += (double) t.nrows * jb * jb ;
+                    if (r < F && r + TRSM_ROWS > F) r = F - TRSM_ROWS ;     // the next tile starts at F
                 }
                 // inner update: columns [r0, Jend) of the current outer block, K = jb
                 const int64_t Jend = std::min<int64_t> (nscol, J0 + OUTER_NB) ;
                 if (r0 < Jend)
                 {
                     UpdItem it ;
-                    it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ;
+                    it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.shift = 0 ;
                     it.a_off = px [s] + r0 + j0 * nsrow ;
                     it.c_off = px [s] + r0 + r0 * nsrow ;
-                    it.M = (int32_t) (nsrow - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
+                    it.M = (int32_t) (std::min (F, nsrow) - r0) ; it.N = (int32_t) (Jend - r0) ; it.K = (int32_t) jb ;
                     add_item (out, it, sink, use_dmma) ;
+                    if (F < nsrow)
+                    {
+                        // the far rows: a rectangular block, B = the rows [r0, Jend) of the same columns
+                        it.shift = (int32_t) (F - r0) ;
+                        it.a_off = px [s] + F + j0 * nsrow ;
+                        it.c_off = px [s] + F + r0 * nsrow ;
+                        it.M = (int32_t) (nsrow - F) ;
+                        add_item (out, it, sinkF, use_dmma) ;
+                    }
                 }
+                if (F < nsrow) far_step = true ;
             }
             out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
             if (!small.empty ())
@@ -298,13 +378,15 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 out.potrf.insert (out.potrf.end (), pb [c].begin (), pb [c].end ()) ;
                 out.launches.push_back (L) ;
             }
-            for (int c = 0 ; c < 3 ; c++)
+            if (trsm_wait >= 0) { join (sm, trsm_wait, -1) ; trsm_wait = -1 ; }
+            push_trsm (tt, sm, -1) ;
+            if (far_step)
             {
-                if (tt [c].empty ()) continue ;
-                Launch L = make_launch (K_TRSM + c, (int64_t) out.trsm.size (), (int64_t) tt [c].size (), level, sm) ;
-                out.count_kind [L.kind] += L.count ;
-                out.trsm.insert (out.trsm.end (), tt [c].begin (), tt [c].end ()) ;
-                out.launches.push_back (L) ;
+                // eS: the inverse of this step and the near rows of its columns are there
+                const int evS = out.nevents++ ;
+                join (sm, -1, evS) ;
+                if (!push_trsm (ttf, sf, evS)) join (sf, evS, -1) ;
+                flush_tiles (out, sinkF, level, sf) ;
             }
             flush_tiles (out, sink, level, sm) ;
         }
@@ -312,10 +394,12 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         {
             // this rank had no panel work in block T: the wait still has to be honoured before the
             // broadcast / updates below may overwrite or read what Ub(T-2) touched
-            Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.wait_ev = pending_wait ;
-            out.launches.push_back (J) ;
+            join (sm, pending_wait, -1) ;
             pending_wait = -1 ;
         }
+        if (trsm_wait >= 0) { join (sm, trsm_wait, -1) ; trsm_wait = -1 ; }
+        int evFar = -1 ;                // far (T) is through on the far stream
+        if (block_has_far) { evFar = out.nevents++ ; join (sf, -1, evFar) ; last_far_ev = evFar ; }
 
         // ---- distributed supernodes: the owner of block T sends the finished panel to everyone -----------
         size_t bcast_first = 0, bcast_count = 0 ;
@@ -339,24 +423,63 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
         // ---- outer update of block T -------------------------------------------------------------------
         const int64_t Jn = J0 + OUTER_NB ;      // first column of the next outer block
         TileSink later ;
-        bool any_b = false ;
+        bool any_b = false, any_ua_far = false ;
+        bool ua_reads_far = false ;     // an undivided Ua on the main stream reads far rows of panel T
         for (int64_t q = 0 ; q < ns ; q++)
         {
             const int64_t s = S [q] ;
             const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
             if (nscol <= Jn) continue ;
             UpdItem it ;
-            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.pad = 0 ; it.K = (int32_t) OUTER_NB ;
+            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.shift = 0 ; it.K = (int32_t) OUTER_NB ;
             // Ua: columns [Jn, Jn2) -- the next panel
             const int64_t Jn2 = std::min<int64_t> (nscol, Jn + OUTER_NB) ;
             if (own.mine (s, T + 1))
             {
                 if (own.is_top (s) && !own.mine (s, T)) foreign_ua = true ;
+                const int64_t Fn = far_from (q, Jn) ;       // zones of block T+1: near rows end at Fn
                 it.a_off = px [s] + Jn + J0 * nsrow ;
                 it.c_off = px [s] + Jn + Jn * nsrow ;
-                it.M = (int32_t) (nsrow - Jn) ; it.N = (int32_t) (Jn2 - Jn) ;
-                add_item (out, it, sink, use_dmma) ;
+                it.N = (int32_t) (Jn2 - Jn) ;
+                if (Fn >= nsrow)
+                {
+                    it.M = (int32_t) (nsrow - Jn) ;
+                    add_item (out, it, sink, use_dmma) ;
+                    if (far_from (q, J0) < nsrow) ua_reads_far = true ;
+                }
+                else
+                {
+                    // Ua_near: the next diagonal block only (main stream); Ua_mid: the rows N1 of block T+1, which
+                    // its first trsm needs (far stream, first); Ua_far: its far rows (far stream)
+                    it.M = (int32_t) OUTER_NB ;
+                    add_item (out, it, sink, use_dmma) ;
+                    UpdItem r = it ;
+                    r.shift = (int32_t) OUTER_NB ;
+                    r.a_off = px [s] + Jn + OUTER_NB + J0 * nsrow ;
+                    r.c_off = px [s] + Jn + OUTER_NB + Jn * nsrow ;
+                    r.M = (int32_t) (Fn - (Jn + OUTER_NB)) ;
+                    add_item (out, r, sinkF, use_dmma) ;        // flushed first: Ua_mid
+                    r.shift = (int32_t) (Fn - Jn) ;
+                    r.a_off = px [s] + Fn + J0 * nsrow ;
+                    r.c_off = px [s] + Fn + Jn * nsrow ;
+                    r.M = (int32_t) (nsrow - Fn) ;
+                    add_item (out, r, later, use_dmma) ;        // parked in `later` until Ua_mid is flushed: Ua_far
+                    any_ua_far = true ;
+                }
             }
+        }
+        // Ua_mid and Ua_far go to the far stream now, after far (T) (in order) and the near rows of panel T
+        // (eN, or the broadcast for a panel of another rank); Ub is collected afterwards
+        TileSink ua_far ;
+        if (any_ua_far) { ua_far = later ; later.clear () ; }
+        for (int64_t q = 0 ; q < ns ; q++)
+        {
+            const int64_t s = S [q] ;
+            const int64_t nscol = ncol_eff [q], nsrow = pi [s+1] - pi [s] ;
+            if (nscol <= Jn) continue ;
+            UpdItem it ;
+            it.lda = it.ldc = (int32_t) nsrow ; it.map_off = -1 ; it.shift = 0 ; it.K = (int32_t) OUTER_NB ;
+            const int64_t Jn2 = std::min<int64_t> (nscol, Jn + OUTER_NB) ;
             if (Jn2 >= nscol) continue ;
             // Ub: columns [Jn2, nscol) -- everything after the next panel
             if (!own.is_top (s))
@@ -407,51 +530,62 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             }
         }
         const bool any_copy = out.copies.size () > copy_first ;
+        // eN / evF: the near part of F(T) ends here on the main stream (for a broadcast panel: the panel is here)
         int evF = -1, evB = -1 ;
         if (bcast_count > 0)
         {
-            // F(T) ends here on the main stream (evP); the panels then travel on the communication stream,
-            // off the owner's critical path, and evF says "panel T is on this rank"
+            // the panels travel on the communication stream, off the owner's critical path, once both the near
+            // part (evP, main stream) and the far part (evFar) are finished; evF says "panel T is on this rank"
             const int evP = out.nevents++ ;
             evF = out.nevents++ ;
-            Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.rec_ev = evP ;
-            out.launches.push_back (J) ;
+            join (sm, -1, evP) ;
+            if (evFar >= 0) join (3, evFar, -1) ;
             Launch Bc = make_launch (K_BCAST, (int64_t) bcast_first, (int64_t) bcast_count, level, 3) ;
             Bc.wait_ev = evP ; Bc.rec_ev = evF ;
             out.launches.push_back (Bc) ;
             last_bcast_ev = evF ;
             if (any_b) evB = out.nevents++ ;
         }
-        else if (any_b || any_copy)
+        else if (any_b || any_copy || any_ua_far)
         {
-            // F(T) ends here on the main stream
             evF = out.nevents++ ; if (any_b) evB = out.nevents++ ;
             if (!out.launches.empty () && out.launches.back ().stream == sm && out.launches.back ().rec_ev < 0)
                 out.launches.back ().rec_ev = evF ;
-            else
-            {
-                Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.rec_ev = evF ;
-                out.launches.push_back (J) ;
-            }
+            else join (sm, -1, evF) ;
         }
         if (any_copy)
         {
+            // (a broadcast panel is complete at evF; otherwise the far rows are finished at evFar)
+            if (evFar >= 0 && bcast_count == 0) join (2, evFar, -1) ;
             Launch C = make_launch (K_COPYOUT, (int64_t) copy_first, (int64_t) (out.copies.size () - copy_first), level, 2) ;
             C.wait_ev = evF ;
             out.launches.push_back (C) ;
         }
-        flush_tiles (out, sink, level, sm, foreign_ua ? evF : -1, -1) ; // Ua(T), main stream
-        if (any_b) flush_tiles (out, later, level, sl, evF, evB) ; // Ub(T), look-ahead stream
+        if (ua_reads_far && evFar >= 0) join (sm, evFar, -1) ;
+        flush_tiles (out, sink, level, sm, foreign_ua ? evF : -1, -1) ; // Ua(T) / Ua_near(T), main stream
+        if (any_ua_far)
+        {
+            const int evM = out.nevents++ ;
+            flush_tiles (out, sinkF, level, sf, evF, evM) ;            // Ua_mid(T)
+            flush_tiles (out, ua_far, level, sf) ;                      // Ua_far(T)
+            evM_prev = evM ;
+            last_far_ev = out.nevents++ ;
+            join (sf, -1, last_far_ev) ;
+        }
+        if (any_b)
+        {
+            if (evFar >= 0 && bcast_count == 0) join (sl, evFar, -1) ;
+            flush_tiles (out, later, level, sl, evF, evB) ;            // Ub(T), look-ahead stream
+        }
         evB_prev2 = evB_prev ;
         evB_prev = evB ;
     }
-    // the main stream joins the look-ahead and the communication stream before anything else uses these
+    // the main stream joins the look-ahead, the far and the communication stream before anything else uses these
     // supernodes
-    for (int ev : { evB_prev2, evB_prev, last_bcast_ev })
+    for (int ev : { evB_prev2, evB_prev, last_bcast_ev, last_far_ev, evM_prev })
     {
         if (ev < 0) continue ;
-        Launch J = make_launch (K_JOIN, 0, 0, level, sm) ; J.wait_ev = ev ;
-        out.launches.push_back (J) ;
+        join (sm, ev, -1) ;
     }
 }
 
@@ -677,7 +811,8 @@ int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t 
         flush_tiles (P, sink, lev) ;
         ncols.resize (Sg.size ()) ;
         for (size_t q = 0 ; q < Sg.size () ; q++) ncols [q] = ncol_of (Sg [q]) ;
-        plan_factor (P, own, super, pi, dpx, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma) ;
+        plan_factor (P, own, super, pi, dpx, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma,
+            nullptr, 0, 1, 0, nullptr, 4) ;
     }
     // the subtrees are final: they can leave for the host while the rest is computed
     if (copy_early)
@@ -760,7 +895,7 @@ int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t 
         ncols.resize (Sg.size ()) ;
         for (size_t q = 0 ; q < Sg.size () ; q++) ncols [q] = ncol_of (Sg [q]) ;
         plan_factor (P, own, super, pi, dpx, Sg.data (), ncols.data (), (int64_t) Sg.size (), lev, sink, use_dmma,
-            copy_early ? copied.data () : nullptr, 0, 1, 0, px) ;
+            copy_early ? copied.data () : nullptr, 0, 1, 0, px, 4) ;
     }
     for (const BcastSeg &b : P.bcasts) if (b.root != rank) P.nvlink_in_values += b.len ;
     if (copy_early)
@@ -981,7 +1116,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
             for (int g = 0 ; g < P.ngroups ; g++) need [g] = std::max (need [g], cnt [g]) ;
         }
         for (int g = 0 ; g < P.ngroups ; g++) group_slot_base [g+1] = group_slot_base [g] + need [g] ;
-        P.nstreams = 4 + 2 * P.ngroups ;
+        P.nstreams = 5 + 2 * P.ngroups ;
     }
 
     // checkpoint after level `lev`: all maximal runs of finished, not yet copied supernodes go to the host
@@ -1028,7 +1163,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 P.launches.push_back (J) ;
                 for (int g = 0 ; g < P.ngroups ; g++)
                 {
-                    Launch W = make_launch (K_JOIN, 0, 0, lev, 4 + 2 * g) ; W.wait_ev = evFork ;
+                    Launch W = make_launch (K_JOIN, 0, 0, lev, 5 + 2 * g) ; W.wait_ev = evFork ;
                     P.launches.push_back (W) ;
                 }
             }
@@ -1037,7 +1172,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 Sg.clear () ;
                 for (int64_t q = 0 ; q < ns ; q++) if (P.group [S [q]] == g) Sg.push_back (S [q]) ;
                 if (Sg.empty ()) continue ;
-                const int sm = 4 + 2 * g, sl = 5 + 2 * g ;
+                const int sm = 5 + 2 * g, sl = 6 + 2 * g ;
                 for (int32_t sn : Sg) plan_updates_into (P, P, own, super, pi, px, sn, sink, use_dmma) ;
                 flush_tiles (P, sink, lev, sm) ;
                 ncols.resize (Sg.size ()) ;
@@ -1051,7 +1186,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 for (int g = 0 ; g < P.ngroups ; g++)
                 {
                     const int evDone = P.nevents++ ;
-                    Launch J = make_launch (K_JOIN, 0, 0, lev, 4 + 2 * g) ; J.rec_ev = evDone ;
+                    Launch J = make_launch (K_JOIN, 0, 0, lev, 5 + 2 * g) ; J.rec_ev = evDone ;
                     P.launches.push_back (J) ;
                     Launch W = make_launch (K_JOIN, 0, 0, lev, 0) ; W.wait_ev = evDone ;
                     P.launches.push_back (W) ;
@@ -1064,7 +1199,8 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
         ncols.resize ((size_t) ns) ;
         for (int64_t q = 0 ; q < ns ; q++) ncols [q] = super [S [q] + 1] - super [S [q]] ;
         const bool ckpt = lev >= first_ckpt ;
-        plan_factor (P, own, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr) ;
+        plan_factor (P, own, super, pi, px, S, ncols.data (), ns, lev, sink, use_dmma, ckpt ? copied.data () : nullptr,
+            0, 1, 0, nullptr, 4) ;
         if (ckpt) checkpoint (lev) ;
     }
     // Whatever no checkpoint has sent yet goes now.  This is the only copy-out of a plan whose subtree-group

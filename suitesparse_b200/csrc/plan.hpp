@@ -10,20 +10,22 @@
 
 namespace b200 {
 
-// One dense product  C (M x N) = A (M x K) * B (N x K)',  where B is the first N rows of A and only the
-// lower trapezoid (i >= j) of C is wanted.  It is subtracted from the factor:
+// One dense product  C (M x N) = A (M x K) * B (N x K)',  A and B in the same K columns of one panel, B starting
+// `shift` rows above A (shift = 0: B is the first N rows of A).  Only the entries with  i + shift >= j  are wanted
+// -- the lower trapezoid when shift = 0, everything when shift >= N (a block of rows far below the diagonal).
+// It is subtracted from the factor:
 //   map_off >= 0 :  Lx [c_off + map [i] + map [j] * ldc] -= C (i,j)     (descendant -> ancestor update,
-//                   the dsyrk + dgemm + assembly of SNW:769-930; map = the pair's relative map)
+//                   the dsyrk + dgemm + assembly of SNW:769-930; map = the pair's relative map; shift = 0)
 //   map_off <  0 :  Lx [c_off + i + j * ldc]             -= C (i,j)     (trailing update inside a supernode
-//                   during its blocked dpotrf/dtrsm, SNW:1023-1181)
+//                   during its blocked dpotrf/dtrsm, SNW:1023-1181; c_off = the target's (0,0))
 struct UpdItem
 {
-    int64_t a_off ;     // Lx offset of A (0,0); A is column-major with leading dimension lda
-    int64_t c_off ;     // Lx offset of the target (supernode origin px [s], or C (0,0) when direct)
+    int64_t a_off ;     // arena offset of A (0,0); A is column-major with leading dimension lda
+    int64_t c_off ;     // arena offset of the target (supernode origin, or C (0,0) when direct)
     int64_t map_off ;   // offset into the relative-map table, or -1
     int32_t lda, ldc ;
     int32_t M, N, K ;
-    int32_t pad ;
+    int32_t shift ;     // B (0,0) = A (0,0) - shift rows
 } ;
 
 // One tile of one item: rows [ti*TM, ..), columns [tj*TN, ..), inner range [k0, k1).
@@ -81,7 +83,8 @@ struct Launch
     int64_t first ;     // first entry in the kind's list
     int32_t level ;     // etree level this launch belongs to
     int32_t stream ;    // 0 = main (panel) stream, 1 = look-ahead stream of the wide trailing updates,
-                        // 2 = copy stream (K_COPYOUT), 3 = communication stream (K_BCAST)
+                        // 2 = copy stream (K_COPYOUT), 3 = communication stream (K_BCAST, K_BARRIER),
+                        // 4 = far stream (the rows of a panel far below the diagonal block, see plan_factor)
     int32_t wait_ev ;   // event the stream waits for before this launch, or -1
     int32_t rec_ev ;    // event recorded on the stream after this launch, or -1
 } ;
@@ -131,8 +134,8 @@ struct Plan
     int64_t winv_slots = 0 ;                // inverse slots (64 x 64 values each) the largest launch needs
     int32_t nevents = 0 ;                   // events the look-ahead schedule uses
     // single-GPU plans: the levels [fork_lo, fork_hi) are factorized subtree group by subtree group, each
-    // group on its own pair of streams (4 + 2g: panel chain, 5 + 2g: look-ahead), see build_plan
-    int32_t nstreams = 4 ;                  // stream ids a launch may carry: 0 main, 1 look-ahead, 2 copy, 3 comm, 4.. groups
+    // group on its own pair of streams (5 + 2g: panel chain, 6 + 2g: look-ahead), see build_plan
+    int32_t nstreams = 5 ;                  // stream ids a launch may carry: 0 main, 1 look-ahead, 2 copy, 3 comm, 4 far, 5.. groups
     int32_t ngroups = 1, fork_lo = -1, fork_hi = -1 ;
     std::vector<int32_t> group ;            // [nsuper] group of a supernode below fork_hi (else -1)
 

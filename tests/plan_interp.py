@@ -56,14 +56,16 @@ def _schedule(launches, prefer):
     """Order the launches the way two CUDA streams could legally execute them: each stream in order, a
     launch with wait_ev only after that event was recorded.  prefer = 0 runs the main stream as far as
     it can before the look-ahead stream gets a turn; prefer = 1 the other way round."""
-    ids = sorted(set([0, 1, 2, 3]) | set(int(v) for v in np.unique(launches["stream"])))
+    ids = sorted(set([0, 1, 2, 3, 4]) | set(int(v) for v in np.unique(launches["stream"])))
     queues = {st: [i for i, L in enumerate(launches) if L["stream"] == st] for st in ids}
     pos, recorded, order = {st: 0 for st in ids}, set(), []
-    # stream 2 is the copy stream, 3 the communication stream, 4.. the subtree-group streams (even: panel chain,
-    # odd: look-ahead): prefer = 0 runs main, look-ahead, the groups in order, communication, copy; prefer = 1
+    # stream 2 is the copy stream, 3 the communication stream, 4 the far stream, 5.. the subtree-group streams (odd:
+    # panel chain, even: look-ahead): prefer = 0 runs main, look-ahead, the groups in order, communication, copy; prefer = 1
     # the exact reverse
-    groups = [st for st in ids if st >= 4]
-    pref = {0: [0, 1] + groups + [3, 2], 1: [2, 3] + groups[::-1] + [1, 0]}[prefer]
+    groups = [st for st in ids if st >= 5]
+    # prefer >= 10: a random legal interleaving (the seed)
+    rng = np.random.default_rng(prefer) if prefer >= 10 else None
+    pref = {0: [0, 4, 1] + groups + [3, 2], 1: [2, 3] + groups[::-1] + [1, 4, 0], 2: [4, 1, 0] + groups + [2, 3]}[min(prefer, 2)]
     # cudaStreamWaitEvent on an event that the host has not recorded yet is a no-op: every wait must come
     # after its record in issue (= list) order
     rec_at = {int(L["rec_ev"]): i for i, L in enumerate(launches) if L["rec_ev"] >= 0}
@@ -80,7 +82,7 @@ def _schedule(launches, prefer):
     while any(pos[st] < len(queues[st]) for st in ids):
         cand = [st for st in pref if ready(st)]
         assert cand, "dead-lock in the launch plan's event graph"
-        st = cand[0]
+        st = cand[0] if rng is None else cand[int(rng.integers(len(cand)))]
         i = queues[st][pos[st]]
         order.append(i)
         pos[st] += 1
@@ -102,7 +104,7 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None, barrier=None, 
     relmap = tables["relmap"]
     minor = None
     launches = tables["launches"]
-    for st1 in launches[(launches["stream"] == 1) | ((launches["stream"] >= 5) & (launches["stream"] % 2 == 1))]:
+    for st1 in launches[(launches["stream"] == 1) | ((launches["stream"] >= 6) & (launches["stream"] % 2 == 0))]:
         assert st1["wait_ev"] >= 0 or st1["kind"] != b200.K_JOIN
     for idx in _schedule(launches, prefer):
         L = launches[idx]
@@ -149,13 +151,16 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None, barrier=None, 
                 M, N, lda = int(it["M"]), int(it["N"]), int(it["lda"])
                 i0, j0 = int(t["ti"]) * TM, int(t["tj"]) * TN
                 i1, j1 = min(M, i0 + TM), min(N, j0 + TN)
-                assert i0 < M and j0 < N and i1 - 1 >= j0, "tile outside the lower trapezoid"
+                sh = int(it["shift"])                                   # B starts `sh` rows above A
+                assert i0 < M and j0 < N and i1 - 1 + sh >= j0, "tile without a wanted entry"
+                assert sh == 0 or (sh >= N and it["map_off"] < 0)
                 k0, k1 = int(t["k0"]), int(t["k1"])
                 assert 0 <= k0 < k1 <= it["K"]
                 A = _view(Lx, int(it["a_off"]), M, int(it["K"]), lda)
-                Cpart = A[i0:i1, k0:k1] @ A[j0:j1, k0:k1].conj().T    # A * B^H (B' for real data)
+                B = _view(Lx, int(it["a_off"]) - sh, N, int(it["K"]), lda)
+                Cpart = A[i0:i1, k0:k1] @ B[j0:j1, k0:k1].conj().T    # A * B^H (B' for real data)
                 ii, jj = np.meshgrid(np.arange(i0, i1), np.arange(j0, j1), indexing="ij")
-                keep = ii >= jj
+                keep = ii + sh >= jj
                 if it["map_off"] >= 0:
                     m = relmap[int(it["map_off"]):int(it["map_off"]) + M].astype(np.int64)
                     dst = int(it["c_off"]) + m[ii[keep]] + m[jj[keep]] * int(it["ldc"])

@@ -21,14 +21,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 needs_ref = pytest.mark.skipif(not refd.have_ref(), reason="oracle/_ref/libref_driver.so not built")
 
 
-def run_ranks_as_threads(c, nranks, prefer=0, dist_run=None):
+def run_ranks_as_threads(c, nranks, prefer=0, dist_run=None, far_min=None):
     """All ranks in one process, each with its own arena; a broadcast is two barriers around a copy from the
     root's arena, a pull reads the other rank's arena directly (the barrier of the plan has made it final)."""
     if dist_run is None:
         os.environ.pop("CHOLMOD_B200_DIST_RUN", None)
     else:
         os.environ["CHOLMOD_B200_DIST_RUN"] = str(dist_run)     # read when the plans are built
-    Fs = [b200.Factor(c.sym, device=-1, nranks=nranks, rank=r) for r in range(nranks)]
+    if far_min is not None:
+        os.environ["CHOLMOD_B200_FAR_MIN"] = str(far_min)
+    try:
+        Fs = [b200.Factor(c.sym, device=-1, nranks=nranks, rank=r) for r in range(nranks)]
+    finally:
+        os.environ.pop("CHOLMOD_B200_FAR_MIN", None)
     Lxs = [np.zeros(F.geti("dxsize")) for F in Fs]
     hosts = [np.full(c.sym["xsize"], np.nan) for _ in range(nranks)]
     for F, Lx in zip(Fs, Lxs):
@@ -47,7 +52,7 @@ def run_ranks_as_threads(c, nranks, prefer=0, dist_run=None):
         def pull(off, nr, nc, ld, src):
             return plan_interp._view(Lxs[src], off, nr, nc, ld)
         try:
-            minors[r] = plan_interp.run_plan(Fs[r], Lxs[r], prefer=prefer, host=hosts[r], bcast=bcast,
+            minors[r] = plan_interp.run_plan(Fs[r], Lxs[r], prefer=prefer + (r if prefer >= 10 else 0), host=hosts[r], bcast=bcast,
                                              barrier=barrier.wait, pull=pull)
             barrier.wait()              # nobody leaves (and frees its arena) while another rank may still pull
         except BaseException as e:      # noqa: BLE001 - report and release the other ranks
@@ -106,6 +111,22 @@ def test_distributed_plan_ranks_together_hold_the_reference_factor(kind, size, o
         assert flops.max() <= 0.75 * flops.sum()
     total = sum(Fs[0].getd("flops_%s" % k) for k in ("update", "potrf", "trsm"))
     assert abs(flops.sum() - total) <= 0.05 * total         # slabs, blocks and contribution blocks cover the work once
+    for F in Fs:
+        F.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("nranks,dist_run,prefer", [(2, 1, 0), (2, 4, 31), (3, 2, 41), (4, 1, 51)])
+def test_distributed_plan_with_near_far_split(nranks, dist_run, prefer):
+    """The far stream inside a distributed plan (panels leave when near AND far part are done; the owner of the
+    next block applies Ua_near / Ua_mid / Ua_far), under random interleavings of each rank's streams."""
+    c = get_case("lap3d7", 26, refd.CHOLMOD_METIS)
+    Fs, Lxs, hosts, minors = run_ranks_as_threads(c, nranks, prefer=prefer, dist_run=dist_run, far_min=32)
+    os.environ.pop("CHOLMOD_B200_DIST_RUN", None)
+    assert all(m is None for m in minors)
+    assert c.rel_err(assemble(hosts)) <= 1e-12
+    L = [F.plan_table("launches", b200.LAUNCH_DT) for F in Fs]
+    assert any(np.any((l["stream"] == 4) & (l["count"] > 0) & (l["kind"] < 10)) for l in L)
     for F in Fs:
         F.close()
 

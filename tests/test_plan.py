@@ -189,7 +189,7 @@ def test_subtree_groups_structure_and_equivalence():
     c = get_case("lap3d7", 22, refd.CHOLMOD_METIS)
     F8 = b200.Factor(c.sym, device=-1)
     lo, hi, G = F8.geti("fork_lo"), F8.geti("fork_hi"), F8.geti("ngroups")
-    assert G > 1 and 0 <= lo < hi <= F8.geti("nlevels") and F8.geti("nstreams") == 4 + 2 * G
+    assert G > 1 and 0 <= lo < hi <= F8.geti("nlevels") and F8.geti("nstreams") == 5 + 2 * G
     level = F8.plan_table("level", np.int32)
     parent = F8.plan_table("parent", np.int64)
     group = F8.plan_table("group", np.int32)
@@ -199,11 +199,11 @@ def test_subtree_groups_structure_and_equivalence():
     inside = kids[level[parent[kids]] < hi]
     assert np.array_equal(group[inside], group[parent[inside]])
     L = F8.plan_table("launches", b200.LAUNCH_DT)
-    on_group = L["stream"] >= 4
+    on_group = L["stream"] >= 5
     assert on_group.any() and np.all((L["level"][on_group] >= lo) & (L["level"][on_group] < hi))
     work = (L["count"] > 0) & (L["kind"] < len(b200.KIND_NAMES))
     forked = (L["level"] >= lo) & (L["level"] < hi)
-    assert np.all(L["stream"][work & forked] >= 4)          # nothing of a forked level runs on the main pair
+    assert np.all(L["stream"][work & forked] >= 5)          # nothing of a forked level runs on the main pair
     os.environ["CHOLMOD_B200_GROUPS"] = "1"
     try:
         F1 = b200.Factor(c.sym, device=-1)
@@ -297,3 +297,63 @@ def test_tile_indices_are_32_bit():
     assert b200.TILE_DT["ti"].itemsize == 4 and b200.TILE_DT["tj"].itemsize == 4 and b200.TILE_DT.itemsize == 20
     hdr = open(os.path.join(ROOT, "suitesparse_b200", "csrc", "plan.hpp")).read()
     assert re.search(r"int32_t\s+ti\s*,\s*tj", hdr) and "uint16_t" not in hdr
+
+
+def dense_case(n, seed=5):
+    """One dense supernode: symbolic factor, lower-triangular CSC of a random SPD matrix, numpy's factor."""
+    rng = np.random.default_rng(seed)
+    B = rng.standard_normal((n, n))
+    A = B @ B.T / n + 2.0 * np.eye(n)
+    sym = dict(n=n, nsuper=1, super=np.array([0, n]), pi=np.array([0, n]), px=np.array([0, n * n]), s=np.arange(n), xsize=n * n)
+    Ap = np.zeros(n + 1, dtype=np.int64); Ap[1:] = np.cumsum(n - np.arange(n))
+    Ai = np.concatenate([np.arange(k, n) for k in range(n)])
+    Ax = np.concatenate([A[k:, k] for k in range(n)])
+    return sym, Ap, Ai, Ax, np.linalg.cholesky(A)
+
+
+@pytest.mark.parametrize("far_min", [64, 100000])
+def test_near_far_split_of_the_panel_chain(far_min):
+    """A supernode with rows far below the diagonal block: the far rows' trsm / updates / Ua run on their own stream
+    (rectangular items with shift > 0, rotating inverse slots).  Every legal interleaving of the streams the
+    interpreter knows must give the factor; with the split off the plan is the old one."""
+    n = 1400
+    sym, Ap, Ai, Ax, Lnp = dense_case(n)
+    os.environ["CHOLMOD_B200_FAR_MIN"] = str(far_min)
+    try:
+        F = b200.Factor(sym, device=-1)
+    finally:
+        os.environ.pop("CHOLMOD_B200_FAR_MIN")
+    launches = F.plan_table("launches", b200.LAUNCH_DT)
+    items = F.plan_table("items", b200.ITEM_DT)
+    on_far = (launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < 10)
+    if far_min == 64:
+        assert on_far.sum() > 10 and np.any(items["shift"] > 0) and F.geti("winv_slots") >= 8
+    else:
+        assert on_far.sum() == 0 and not np.any(items["shift"] > 0)
+    for prefer in (0, 1, 2, 11, 12, 13, 14, 15, 16):
+        Lx = np.zeros(n * n)
+        host = np.full(n * n, np.nan)
+        plan_interp.scatter_A(sym, Ap, Ai, Ax, 0.0, Lx)
+        assert plan_interp.run_plan(F, Lx, prefer=prefer, host=host) is None
+        L = np.tril(Lx.reshape(n, n).T)
+        assert np.max(np.abs(L - Lnp)) <= 1e-12 * np.max(np.abs(Lnp)), prefer
+        assert np.array_equal(host, Lx)
+    F.close()
+
+
+@needs_ref
+def test_near_far_split_inside_a_sparse_factor():
+    os.environ["CHOLMOD_B200_FAR_MIN"] = "32"
+    try:
+        c = get_case("lap3d7", 26, refd.CHOLMOD_METIS)
+        F = b200.Factor(c.sym, device=-1)
+    finally:
+        os.environ.pop("CHOLMOD_B200_FAR_MIN")
+    launches = F.plan_table("launches", b200.LAUNCH_DT)
+    assert np.any((launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < 10))
+    for prefer in (0, 1, 2, 21, 22, 23, 24):
+        Lx = np.zeros(c.sym["xsize"])
+        plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
+        assert plan_interp.run_plan(F, Lx, prefer=prefer) is None
+        assert c.rel_err(Lx) <= 1e-12, prefer
+    F.close()
