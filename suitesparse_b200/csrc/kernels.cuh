@@ -606,7 +606,7 @@ __global__ void __launch_bounds__ ((TM / WM) * (TN / WN) * 32) k_upd_zmma (const
                     zdouble *dst = Cj + smap_r [il] ;
                     atomicAdd (&dst->re, -cre [a][b][e]) ;
                     // the diagonal of L1*L1^H is real (zherk leaves its imaginary part exactly zero)
-                    if (i0 + il > j) atomicAdd (&dst->im, -cim [a][b][e]) ;
+                    if (i0 + il + it.shift > j) atomicAdd (&dst->im, -cim [a][b][e]) ;
                 }
             }
         }
