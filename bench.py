@@ -335,7 +335,10 @@ def main():
     nccl_calls = F.geti("nccl_calls")
     per_rank = None
     if world > 1:
-        mine = dict(rank=rank, device_bytes=F.geti("device_bytes"), arena_bytes=F.geti("dxsize") * np.dtype(fdtype).itemsize,
+        mine = dict(rank=rank, ms_factor_profiled=F.getd("ms_factor"), host_registered_bytes=F.geti("host_registered"),
+                    level_end_ms=[round(F.getd("ms_level_end%d" % k), 2) for k in range(F.geti("nlevels"))],
+                    kernel_ms={nm: round(F.getd("ms_kind%d" % k), 2) for k, nm in enumerate(b200.KIND_NAMES)},
+                    device_bytes=F.geti("device_bytes"), arena_bytes=F.geti("dxsize") * np.dtype(fdtype).itemsize,
                     nvlink_in_bytes=F.geti("nvlink_in_bytes"), ms_pull=F.getd("ms_pull"), npulls=F.geti("npulls"),
                     d2h_bytes=sum(int(c["len"]) for c in F.plan_table("owned", b200.COPY_DT)) * np.dtype(fdtype).itemsize)
         per_rank = [None] * world

@@ -380,8 +380,8 @@ TRSM_DT = np.dtype([("diag_off", "<i8"), ("row_off", "<i8"), ("lda", "<i4"), ("j
                     ("slot", "<i4")])
 LAUNCH_DT = np.dtype([("kind", "<i4"), ("count", "<i4"), ("first", "<i8"), ("level", "<i4"), ("stream", "<i4"),
                       ("wait_ev", "<i4"), ("rec_ev", "<i4")])
-K_FACTOR_SMALL = 9
-K_JOIN, K_COPYOUT, K_BCAST, K_BARRIER, K_PULL = 10, 11, 12, 13, 14
+K_FACTOR_SMALL, K_FACTOR_TINY, K_UPD_TINY = 9, 10, 11
+K_JOIN, K_COPYOUT, K_BCAST, K_BARRIER, K_PULL = 12, 13, 14, 15, 16
 BCAST_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("root", "<i4"), ("pad", "<i4")])
 COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("hoff", "<i8")])
 PULL_DT = np.dtype([("off", "<i8"), ("nrows", "<i4"), ("ncols", "<i4"), ("ld", "<i4"), ("mask", "<u4")])
@@ -389,8 +389,9 @@ K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TR
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)
 K_TRSM_KINDS = (K_TRSM, K_TRSM_INV32, K_TRSM_INV64)
 KIND_NAMES = ["upd_simt", "upd_dmma64", "upd_dmma128", "potrf16", "potrf32", "potrf64", "trsm_subst", "trsm_inv32",
-              "trsm_inv64", "factor_small"]
-TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 64)}
+              "trsm_inv64", "factor_small", "factor_tiny", "upd_tiny"]
+# (a K_UPD_TINY "tile" is the whole item)
+TILE_SHAPE = {K_UPD_SIMT: (32, 8), K_UPD_D64: (64, 64), K_UPD_D128: (128, 64), K_UPD_TINY: (1 << 30, 1 << 30)}
 
 
 class Multi:

@@ -399,6 +399,12 @@ int run_launches (b200_factor *f, const Plan &P, const UpdItem *items, const Upd
             case K_POTRF16:
                 k_potrf_reg<T, 16><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
                 break ;
+            case K_FACTOR_TINY:
+                k_factor_tiny<T><<<(unsigned) ((L.count + 127) / 128), 128, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
+                break ;
+            case K_UPD_TINY:
+                k_upd_tiny<T><<<(unsigned) ((L.count + 127) / 128), 128, 0, st>>> (tiles + L.first, L.count, items, relmap, Lx) ;
+                break ;
             case K_FACTOR_SMALL:
                 k_factor_small<T><<<(unsigned) ((L.count + 3) / 4), 64, 0, st>>> (potrf + L.first, L.count, Lx, f->d_minor.p) ;
                 break ;
@@ -796,14 +802,15 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "top_size")) return P.top_size ;
     if (!strcmp (name, "nvlink_in_bytes")) return P.nvlink_in_values * (int64_t) f->esize ;
     if (!strcmp (name, "peers_attached")) return f->peers_attached ;
+    if (!strcmp (name, "host_registered")) return f->reg_ptr ? (int64_t) f->reg_bytes : 0 ;
     if (!strcmp (name, "ngroups")) return P.ngroups ;
     if (!strcmp (name, "fork_lo")) return P.fork_lo ;
     if (!strcmp (name, "fork_hi")) return P.fork_hi ;
     if (!strcmp (name, "nstreams")) return P.nstreams ;
     if (!strcmp (name, "ntop")) { int64_t c = 0 ; for (char t : P.top) c += t ; return c ; }
     if (!strcmp (name, "profile")) return f->profile ;
-    if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] < '0' + K_NKINDS) return f->launches_kind [name [13] - '0'] ;
-    if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.count_kind [name [10] - '0'] ;
+    if (!strncmp (name, "launches_kind", 13) && name [13] >= '0' && name [13] <= '9' && atoi (name + 13) < K_NKINDS) return f->launches_kind [atoi (name + 13)] ;
+    if (!strncmp (name, "tiles_kind", 10) && name [10] >= '0' && name [10] <= '9' && atoi (name + 10) < K_NKINDS) return P.count_kind [atoi (name + 10)] ;
     return -1 ;
 }
 
@@ -830,13 +837,13 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
     if (!strcmp (name, "ms_pull")) return f->ms_pull ;
-    if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] < '0' + K_NKINDS) return f->ms_kind [name [7] - '0'] ;
+    if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '9' && atoi (name + 7) < K_NKINDS) return f->ms_kind [atoi (name + 7)] ;
     if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
     if (!strncmp (name, "solve_launches", 14) && name [14] >= '0' && name [14] < '4') return (double) f->solve_launch_count [name [14] - '0'] ;
     if (!strncmp (name, "ms_launch_start", 15)) { size_t k = (size_t) atoll (name + 15) ; return k < f->ms_launch_start.size () ? f->ms_launch_start [k] : -1 ; }
     if (!strncmp (name, "ms_launch", 9)) { size_t k = (size_t) atoll (name + 9) ; return k < f->ms_launch.size () ? f->ms_launch [k] : -1 ; }
     if (!strncmp (name, "ms_level_end", 12)) { int k = atoi (name + 12) ; return (k >= 0 && k < 64) ? f->ms_level_end [k] : -1 ; }
-    if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] < '0' + K_NKINDS) return P.flops_kind [name [10] - '0'] ;
+    if (!strncmp (name, "flops_kind", 10) && name [10] >= '0' && name [10] <= '9' && atoi (name + 10) < K_NKINDS) return P.flops_kind [atoi (name + 10)] ;
     return -1 ;
 }
 

@@ -263,6 +263,102 @@ __global__ void __launch_bounds__ (256) k_upd_simt (const UpdTile *__restrict__ 
 }
 
 // ---------------------------------------------------------------------------------------------
+// tiny updates and tiny supernodes: one THREAD per object
+// ---------------------------------------------------------------------------------------------
+
+// The bulk of the update pairs near the leaves (K = 1..TINY_K descendant columns, a few dozen target entries):
+// thread t does item tiles [t].item whole.  No shared memory, no idle lanes; the panel entries a thread re-reads
+// for every target column come from L1.
+template <typename T>
+__global__ void __launch_bounds__ (128) k_upd_tiny (const UpdTile *__restrict__ tiles, int ntiles,
+    const UpdItem *__restrict__ items, const int32_t *__restrict__ relmap, T *Lx)
+{
+    const int t = (int) (blockIdx.x * blockDim.x + threadIdx.x) ;
+    if (t >= ntiles) return ;
+    const UpdItem it = items [tiles [t].item] ;
+    const T *A = Lx + it.a_off ;
+    const int64_t lda = it.lda, ldc = it.ldc ;
+    const bool mapped = it.map_off >= 0 ;
+    const int32_t *map = relmap + (mapped ? it.map_off : 0) ;
+    const T zero = from_real<T> (0) ;
+    for (int j = 0 ; j < it.N ; j++)
+    {
+        T b [TINY_K] ;
+        #pragma unroll
+        for (int k = 0 ; k < TINY_K ; k++) b [k] = (k < it.K) ? A [j + k * lda] : zero ;
+        T *Cj = Lx + it.c_off + (mapped ? (int64_t) map [j] : (int64_t) j) * ldc ;
+        for (int i = j ; i < it.M ; i++)
+        {
+            T acc = zero ;
+            #pragma unroll
+            for (int k = 0 ; k < TINY_K ; k++) if (k < it.K) acc += mulc (A [i + k * lda], b [k]) ;
+            atomic_sub (Cj + (mapped ? (int64_t) map [i] : (int64_t) i), acc) ;
+        }
+    }
+}
+
+// Whole supernodes of at most TINY_COLS columns with at most TINY_ROWS rows below the diagonal block (most of the
+// leaves of the etree): thread t factorizes block t -- dpotrf of a <= 4 x 4 block in registers, then the rows
+// below it one after the other by substitution (SNW:1023, :1175).  Same failure rule as the other potrf kernels.
+template <typename T>
+__global__ void __launch_bounds__ (128) k_factor_tiny (const PotrfBlk *__restrict__ blks, int nblks, T *Lx,
+    unsigned long long *minor)
+{
+    const int t = (int) (blockIdx.x * blockDim.x + threadIdx.x) ;
+    if (t >= nblks) return ;
+    const PotrfBlk b = blks [t] ;
+    const int jb = b.jb ;
+    const int64_t lda = b.lda ;
+    T *D = Lx + b.off ;
+    typedef typename num<T>::real R ;
+    const T one = from_real<T> (1), zero = from_real<T> (0) ;
+    T a [TINY_COLS][TINY_COLS] ;        // a [r][c], lower part; identity beyond jb
+    #pragma unroll
+    for (int c = 0 ; c < TINY_COLS ; c++)
+        #pragma unroll
+        for (int r = 0 ; r < TINY_COLS ; r++)
+            a [r][c] = (r < jb && c <= r) ? D [r + c * lda] : ((r == c) ? one : zero) ;
+    R rdiag [TINY_COLS] ;
+    #pragma unroll
+    for (int j = 0 ; j < TINY_COLS ; j++)
+    {
+        const R d = real_ (a [j][j]) ;
+        if (j < jb && !(d > (R) 0)) atomicMin (minor, (unsigned long long) (b.col + j)) ;
+        const R ljj = sqrt (d), rl = (R) 1 / ljj ;
+        rdiag [j] = rl ;
+        a [j][j] = from_real<T> (ljj) ;
+        #pragma unroll
+        for (int r = j + 1 ; r < TINY_COLS ; r++) a [r][j] = a [r][j] * rl ;
+        #pragma unroll
+        for (int c = j + 1 ; c < TINY_COLS ; c++)
+            #pragma unroll
+            for (int r = c ; r < TINY_COLS ; r++) a [r][c] -= mulc (a [r][j], a [c][j]) ;
+    }
+    #pragma unroll
+    for (int c = 0 ; c < TINY_COLS ; c++)
+        #pragma unroll
+        for (int r = 0 ; r < TINY_COLS ; r++)
+            if (r < jb && c <= r) D [r + c * lda] = a [r][c] ;
+    // rows below: x <- x * L11^{-H}
+    for (int64_t row = jb ; row < lda ; row++)
+    {
+        T x [TINY_COLS] ;
+        #pragma unroll
+        for (int j = 0 ; j < TINY_COLS ; j++) x [j] = (j < jb) ? D [row + j * lda] : zero ;
+        #pragma unroll
+        for (int j = 0 ; j < TINY_COLS ; j++)
+        {
+            const T xj = x [j] * rdiag [j] ;
+            x [j] = xj ;
+            #pragma unroll
+            for (int k = j + 1 ; k < TINY_COLS ; k++) x [k] -= mulc (xj, a [k][j]) ;
+        }
+        #pragma unroll
+        for (int j = 0 ; j < TINY_COLS ; j++) if (j < jb) D [row + j * lda] = x [j] ;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // DMMA update kernel
 // ---------------------------------------------------------------------------------------------
 

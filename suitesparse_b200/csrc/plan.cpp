@@ -19,7 +19,7 @@ namespace {
 
 struct TileSink
 {
-    std::vector<UpdTile> cls [3] ;      // per update kernel class
+    std::vector<UpdTile> cls [4] ;      // per update kernel class: SIMT, DMMA 64, DMMA 128 x 64, tiny
     void clear () { for (auto &v : cls) v.clear () ; }
 } ;
 
@@ -47,6 +47,15 @@ void emit_tiles (Plan &P, int32_t item_id, const UpdItem &it, TileSink &sink, bo
     const int64_t M = it.M, N = it.N, K = it.K ;
     int cls ;
     (void) use_dmma ;       // both precisions use the tile classes (double: DMMA, single: FFMA kernels)
+    if (it.shift == 0 && K <= TINY_K && M * N <= TINY_MN)
+    {
+        // one thread does the whole item: a single "tile"
+        P.flops_kind [K_UPD_TINY] += (double) K * (double) N * (2.0 * (double) M - (double) N) ;
+        UpdTile t ;
+        t.item = item_id ; t.ti = 0 ; t.tj = 0 ; t.k0 = 0 ; t.k1 = (int32_t) K ;
+        sink.cls [3].push_back (t) ;
+        return ;
+    }
     if (N < 16 || K < 8 || M * N < 2048)
     {
         cls = K_UPD_SIMT ;
@@ -112,16 +121,17 @@ Launch make_launch (int kind, int64_t first, int64_t count, int level, int strea
 void flush_tiles (Plan &P, TileSink &sink, int level, int stream = 0, int wait_ev = -1, int rec_ev = -1)
 {
     const size_t before = P.launches.size () ;
-    for (int c = 0 ; c < 3 ; c++)
+    for (int c = 0 ; c < 4 ; c++)
     {
         auto &v = sink.cls [c] ;
         if (v.empty ()) continue ;
+        const int kind = (c == 3) ? (int) K_UPD_TINY : c ;
         // longest tiles first: the CTAs still running when the launch drains are then the short ones
-        // (the one-warp tiles of the SIMT class are all short: their order does not matter)
-        if (c != K_UPD_SIMT)
+        // (the one-warp tiles of the SIMT class and the one-thread items are all short: their order does not matter)
+        if (c == K_UPD_D64 || c == K_UPD_D128)
             std::stable_sort (v.begin (), v.end (), [] (const UpdTile &a, const UpdTile &b) { return (a.k1 - a.k0) > (b.k1 - b.k0) ; }) ;
-        P.launches.push_back (make_launch (c, (int64_t) P.tiles.size (), (int64_t) v.size (), level, stream)) ;
-        P.count_kind [c] += (int64_t) v.size () ;
+        P.launches.push_back (make_launch (kind, (int64_t) P.tiles.size (), (int64_t) v.size (), level, stream)) ;
+        P.count_kind [kind] += (int64_t) v.size () ;
         P.tiles.insert (P.tiles.end (), v.begin (), v.end ()) ;
     }
     sink.clear () ;
@@ -295,7 +305,7 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
             for (auto &v : pb) v.clear () ;
             for (auto &v : tt) v.clear () ;
             for (auto &v : ttf) v.clear () ;
-            std::vector<PotrfBlk> small ;
+            std::vector<PotrfBlk> small, tiny ;
             int32_t nslots = step_slot_base ;
             bool far_step = false ;
             for (int64_t q = 0 ; q < ns ; q++)
@@ -311,6 +321,14 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 PotrfBlk b ;
                 b.off = px [s] + j0 + j0 * nsrow ; b.col = super [s] + j0 ;
                 b.lda = (int32_t) nsrow ; b.jb = (int32_t) jb ;
+                if (j0 == 0 && nscol <= TINY_COLS && nsrow - nscol <= TINY_ROWS)
+                {
+                    // a whole tiny supernode (most of the leaves): one thread
+                    b.slot = -1 ; b.pad = 0 ;
+                    tiny.push_back (b) ;
+                    out.flops_kind [K_FACTOR_TINY] += (double) jb * jb * jb / 3.0 + (double) (nsrow - nscol) * jb * jb ;
+                    continue ;
+                }
                 if (j0 == 0 && nscol <= 16 && nsrow - nscol <= SMALL_ROWS)
                 {
                     // a whole small supernode: potrf and the trsm of its few rows in one kernel
@@ -361,12 +379,14 @@ void plan_factor (Plan &out, const Own &own, const int64_t *super, const int64_t
                 if (F < nsrow) far_step = true ;
             }
             out.winv_slots = std::max<int64_t> (out.winv_slots, nslots) ;
-            if (!small.empty ())
+            for (int w = 0 ; w < 2 ; w++)
             {
-                Launch L = make_launch (K_FACTOR_SMALL, (int64_t) out.potrf.size (), (int64_t) small.size (), level, sm) ;
+                std::vector<PotrfBlk> &v = w ? small : tiny ;
+                if (v.empty ()) continue ;
+                Launch L = make_launch (w ? K_FACTOR_SMALL : K_FACTOR_TINY, (int64_t) out.potrf.size (), (int64_t) v.size (), level, sm) ;
                 L.wait_ev = pending_wait ; pending_wait = -1 ;
                 out.count_kind [L.kind] += L.count ;
-                out.potrf.insert (out.potrf.end (), small.begin (), small.end ()) ;
+                out.potrf.insert (out.potrf.end (), v.begin (), v.end ()) ;
                 out.launches.push_back (L) ;
             }
             for (int c = 0 ; c < 3 ; c++)

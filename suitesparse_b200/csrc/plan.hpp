@@ -67,12 +67,14 @@ enum LaunchKind : int32_t
     K_TRSM_INV32 = 7,   // TrsmTile list, product with the inverse of a <= 32-wide block
     K_TRSM_INV64 = 8,   // TrsmTile list, product with the inverse of a <= 64-wide block
     K_FACTOR_SMALL = 9, // PotrfBlk list: whole supernodes of <= 16 columns and few rows, potrf + trsm fused
-    K_NKINDS   = 10,
-    K_JOIN     = 10,    // no kernel: only the launch's wait_ev / rec_ev are honoured
-    K_COPYOUT  = 11,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
-    K_BCAST    = 12,    // no kernel: BcastSeg list, ncclBroadcast of finished panels (communication stream)
-    K_BARRIER  = 13,    // no kernel: all ranks meet (a one-word all-reduce on the communication stream)
-    K_PULL     = 14,    // PullSeg list: the owner of a block of a top separator adds the other ranks' contribution
+    K_FACTOR_TINY = 10, // PotrfBlk list: whole supernodes of <= TINY_COLS columns and <= TINY_ROWS rows below, one THREAD each
+    K_UPD_TINY = 11,    // UpdTile list, one tile = one whole item of a few dozen entries and K <= TINY_K, one THREAD each
+    K_NKINDS   = 12,
+    K_JOIN     = 12,    // no kernel: only the launch's wait_ev / rec_ev are honoured
+    K_COPYOUT  = 13,    // no kernel: CopySeg list, finished parts of L->x go to the host (copy stream)
+    K_BCAST    = 14,    // no kernel: BcastSeg list, ncclBroadcast of finished panels (communication stream)
+    K_BARRIER  = 15,    // no kernel: all ranks meet (a one-word all-reduce on the communication stream)
+    K_PULL     = 16,    // PullSeg list: the owner of a block of a top separator adds the other ranks' contribution
                         // blocks to its own, reading them from their arenas over NVLink (k_pull_add)
 } ;
 
@@ -95,6 +97,11 @@ constexpr int TRSM_ROWS  = 128 ;    // rows per TRSM tile
 constexpr int SMALL_ROWS = 256 ;    // a supernode of <= 16 columns with at most this many rows below its
                                     // diagonal block is factorized by one 16-thread group (K_FACTOR_SMALL)
 constexpr int SIMT_TM = 32, SIMT_TN = 8 ;
+// The leaves of a nested-dissection etree: most supernodes have 1-4 columns and a handful of rows, most update
+// pairs a few dozen entries with K = 1..4.  A warp (or a 16-thread group) per such object idles 30 of its lanes;
+// they get one thread each instead.
+constexpr int TINY_COLS = 4, TINY_ROWS = 64 ;      // K_FACTOR_TINY: nscol <= TINY_COLS, nsrow - nscol <= TINY_ROWS
+constexpr int TINY_K = 4, TINY_MN = 128 ;          // K_UPD_TINY: K <= TINY_K, M * N <= TINY_MN
 // the large DMMA tile: 128 x 64 with 4 warps of 32 x 64, two CTAs per SM so that one CTA's prologue,
 // barriers and epilogue overlap the other's tensor work
 constexpr int BIG_TM = 128, BIG_TN = 64 ;

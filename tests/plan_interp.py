@@ -190,10 +190,10 @@ def run_plan(F, Lx, tables=None, prefer=0, host=None, bcast=None, barrier=None, 
                         Lc[j + 1:, j + 1:] -= np.outer(Lc[j + 1:, j], Lc[j + 1:, j].conj())
                 r, c = np.tril_indices(jb)
                 D[r, c] = Lc[r, c]
-        elif kind == b200.K_FACTOR_SMALL:
+        elif kind in (b200.K_FACTOR_SMALL, b200.K_FACTOR_TINY):
             for b in potrf[first:first + cnt]:
                 jb, lda = int(b["jb"]), int(b["lda"])
-                assert jb <= 16 and lda - jb <= 256
+                assert (jb <= 16 and lda - jb <= 256) if kind == b200.K_FACTOR_SMALL else (jb <= 4 and lda - jb <= 64)
                 P = _view(Lx, int(b["off"]), lda, jb, lda)      # the whole supernode: b.off is its origin
                 Dl = np.tril(P[:jb, :])
                 Lc = Dl + np.tril(Dl, -1).conj().T

@@ -126,7 +126,7 @@ def test_distributed_plan_with_near_far_split(nranks, dist_run, prefer):
     assert all(m is None for m in minors)
     assert c.rel_err(assemble(hosts)) <= 1e-12
     L = [F.plan_table("launches", b200.LAUNCH_DT) for F in Fs]
-    assert any(np.any((l["stream"] == 4) & (l["count"] > 0) & (l["kind"] < 10)) for l in L)
+    assert any(np.any((l["stream"] == 4) & (l["count"] > 0) & (l["kind"] < b200.K_JOIN)) for l in L)
     for F in Fs:
         F.close()
 

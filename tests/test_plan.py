@@ -325,7 +325,7 @@ def test_near_far_split_of_the_panel_chain(far_min):
         os.environ.pop("CHOLMOD_B200_FAR_MIN")
     launches = F.plan_table("launches", b200.LAUNCH_DT)
     items = F.plan_table("items", b200.ITEM_DT)
-    on_far = (launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < 10)
+    on_far = (launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < b200.K_JOIN)
     if far_min == 64:
         assert on_far.sum() > 10 and np.any(items["shift"] > 0) and F.geti("winv_slots") >= 8
     else:
@@ -350,7 +350,7 @@ def test_near_far_split_inside_a_sparse_factor():
     finally:
         os.environ.pop("CHOLMOD_B200_FAR_MIN")
     launches = F.plan_table("launches", b200.LAUNCH_DT)
-    assert np.any((launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < 10))
+    assert np.any((launches["stream"] == 4) & (launches["count"] > 0) & (launches["kind"] < b200.K_JOIN))
     for prefer in (0, 1, 2, 21, 22, 23, 24):
         Lx = np.zeros(c.sym["xsize"])
         plan_interp.scatter_A(c.sym, c.Sp, c.Si, c.Sx, 0.0, Lx)
