@@ -208,6 +208,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sweep", default="", help="diagnostic: ';'-separated planner settings, each a ','-separated list of "
+                    "ENV=value (e.g. 'CHOLMOD_B200_DIST_RUN=1;CHOLMOD_B200_DIST_RUN=4,CHOLMOD_B200_FAR_MIN=100000000'); every "
+                    "setting gets its own context and is timed like `value`, after the main measurement (key `sweep`)")
     ap.add_argument("--single", action="store_true", help="single precision (config 5b); the roofline stays FP64-tensor "
                     "and is then only informative: single precision runs on the FP32 FMA pipe")
     args = ap.parse_args()
@@ -327,6 +330,38 @@ def main():
                "ms_h2d": F.getd("ms_h2d"), "ms_factor": F.getd("ms_factor"), "ms_d2h": F.getd("ms_d2h"),
                "first_call_ms": first_call_ms, "context_build_ms": 1e3 * t_plan,
                "e2e_first_call_ms": (first_call_ms + 1e3 * t_plan) if first_call_ms is not None else None}
+
+    # ---- diagnostic sweep over planner settings (collective: every rank builds and runs every variant) ----------
+    sweep = []
+    for setting in [x for x in args.sweep.split(";") if x.strip()]:
+        kv = dict(item.split("=", 1) for item in setting.split(","))
+        old = {k: os.environ.get(k) for k in kv}
+        os.environ.update(kv)
+        try:
+            F2 = b200.Factor(sym, dtype=fdtype, device=local, nranks=world, rank=rank)
+        finally:
+            for k, v in old.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+        if world > 1:
+            F2.comm_init_torch()
+        F2.upload_matrix(Sp, Si, Sx)
+        for _ in range(3):
+            assert F2.factor_device() == b200.OK
+        barrier()
+        ms2 = 0.0
+        for _ in range(args.steps):
+            assert F2.factor_device() == b200.OK
+            ms2 += F2.getd("ms_factor")
+        barrier()
+        if world > 1:
+            tt = torch.tensor([ms2], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms2 = float(tt.item())
+        sweep.append({"setting": setting, "ms_per_step": ms2 / args.steps})
+        F2.close()
 
     # one profiled (untimed) factorization for the per-kernel breakdown; collective, so every rank runs it
     F.seti("profile", 1)
@@ -467,7 +502,7 @@ def main():
                    if world > 1 else "1 GPU",
                    "analyze_s": t_an, "plan_s": t_plan, "wall_s_timed_region": wall},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "whole_step": whole,
-        "check": check, "hbm_phase": hbm_phase, "per_rank": per_rank,
+        "check": check, "hbm_phase": hbm_phase, "per_rank": per_rank, "sweep": sweep,
         "nvlink_bytes_per_step": sum(p["nvlink_in_bytes"] for p in per_rank) if per_rank else 0,
         "kernels": kinds, "level_end_ms": timeline, "cpu_baseline": cpu,
     }

@@ -11,6 +11,9 @@
 #include <vector>
 #include <type_traits>
 #include <mutex>
+#include <thread>
+#include <algorithm>
+#include <utility>
 #include <dlfcn.h>
 #include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
 
@@ -151,7 +154,8 @@ struct b200_factor
     bool have_F = false, F_unpacked = false ;
     int64_t A_nz = 0 ;
     // host-registered output buffer (pinned once, reused by later factorizations)
-    void *reg_ptr = nullptr ; size_t reg_bytes = 0 ;
+    void *reg_ptr = nullptr ; size_t reg_bytes = 0 ;     // the buffer last prepared by ensure_registered
+    std::vector<std::pair<void *, size_t>> reg_pieces ; // what this context page-locked of it (cudaHostRegister)
 
     int64_t kernel_launches = 0 ;
     int64_t nccl_calls = 0 ;
@@ -162,6 +166,9 @@ struct b200_factor
     float ms_level_end [64] = {} ;          // profile mode: end time of each etree level on the device timeline
     std::vector<float> ms_launch, ms_launch_start ;     // profile mode: duration / start time of every plan launch
     float ms_factor = -1, ms_h2d = -1, ms_d2h = -1, ms_scatter = -1, ms_solve = -1 ;
+    // H2D staging ring for the caller's pageable A arrays (h2d_staged): STAGE_SLOTS chunks of page-locked memory
+    unsigned char *stage = nullptr ;
+    cudaEvent_t stage_ev [8] = {} ;
     size_t device_bytes = 0 ;
     bool mem_counted = false ;              // device_bytes is part of g_mem_held [device]
 } ;
@@ -741,7 +748,7 @@ void b200_destroy (b200_factor *f)
     {
         cudaSetDevice (f->device) ;
         cudaStreamSynchronize (f->stream) ;
-        if (f->reg_ptr) cudaHostUnregister (f->reg_ptr) ;
+        for (auto &pc : f->reg_pieces) cudaHostUnregister (pc.first) ;
         f->d_super.release () ; f->d_pi.release () ; f->d_px.release () ; f->d_Ls.release () ;
         f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
@@ -753,6 +760,7 @@ void b200_destroy (b200_factor *f)
             if (f->peer_ipc [r] && f->peers.p [r]) { cudaIpcCloseMemHandle (f->peers.p [r]) ; f->peers.p [r] = nullptr ; }
         f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
+        if (f->stage) { cudaFreeHost (f->stage) ; for (auto &e : f->stage_ev) if (e) cudaEventDestroy (e) ; }
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
         for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
         if (f->comm) { NcclApi *nc = nccl_api () ; if (nc) nc->CommDestroy (f->comm) ; f->comm = nullptr ; }
@@ -802,7 +810,7 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "top_size")) return P.top_size ;
     if (!strcmp (name, "nvlink_in_bytes")) return P.nvlink_in_values * (int64_t) f->esize ;
     if (!strcmp (name, "peers_attached")) return f->peers_attached ;
-    if (!strcmp (name, "host_registered")) return f->reg_ptr ? (int64_t) f->reg_bytes : 0 ;
+    if (!strcmp (name, "host_registered")) { int64_t b = 0 ; for (auto &pc : f->reg_pieces) b += (int64_t) pc.second ; return b ; }
     if (!strcmp (name, "ngroups")) return P.ngroups ;
     if (!strcmp (name, "fork_lo")) return P.fork_lo ;
     if (!strcmp (name, "fork_hi")) return P.fork_hi ;
@@ -966,6 +974,56 @@ int b200_peer_attach (b200_factor *f, int rank, void *arena, const void *handle6
     return B200_OK ;
 }
 
+// Host -> device copy of a large array in the caller's pageable memory.  cudaMemcpyAsync from pageable memory is
+// one thread of the driver copying into its own bounce buffers (10.8 GB/s measured on the box, 6.6 ms for config
+// 2's A and 30 ms for config 5's, a third of its end-to-end time); here STAGE_THREADS host threads copy 4 MB chunks
+// into a page-locked ring owned by the context and queue the DMA of each chunk behind it, so the memcpy of one chunk
+// overlaps the DMA of the others.  Small arrays take the plain path.
+constexpr size_t STAGE_CHUNK = (size_t) 4 << 20 ;
+constexpr int STAGE_SLOTS = 8, STAGE_THREADS = 4 ;
+
+static int h2d_staged (b200_factor *f, void *dst, const void *src, size_t bytes, cudaStream_t s)
+{
+    if (bytes < 4 * STAGE_CHUNK)
+    {
+        CK (cudaMemcpyAsync (dst, src, bytes, cudaMemcpyHostToDevice, s), "H2D") ;
+        return B200_OK ;
+    }
+    if (!f->stage)
+    {
+        if (cudaHostAlloc ((void **) &f->stage, STAGE_SLOTS * STAGE_CHUNK, cudaHostAllocDefault) != cudaSuccess)
+        {
+            cudaGetLastError () ; f->stage = nullptr ;
+            CK (cudaMemcpyAsync (dst, src, bytes, cudaMemcpyHostToDevice, s), "H2D") ;
+            return B200_OK ;
+        }
+        for (auto &e : f->stage_ev) CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "stage event") ;
+    }
+    const size_t nchunks = (bytes + STAGE_CHUNK - 1) / STAGE_CHUNK ;
+    int status [STAGE_THREADS] = {} ;
+    std::thread th [STAGE_THREADS] ;
+    for (int t = 0 ; t < STAGE_THREADS ; t++)
+        th [t] = std::thread ([=, &status]
+        {
+            if (cudaSetDevice (f->device) != cudaSuccess) { status [t] = 1 ; return ; }
+            size_t turn = 0 ;
+            for (size_t c = (size_t) t ; c < nchunks ; c += STAGE_THREADS, turn++)
+            {
+                // thread t owns the slots t and t + STAGE_THREADS and alternates between them
+                const int slot = t + (int) (turn & 1) * STAGE_THREADS ;
+                const size_t off = c * STAGE_CHUNK, len = std::min (STAGE_CHUNK, bytes - off) ;
+                unsigned char *buf = f->stage + (size_t) slot * STAGE_CHUNK ;
+                if (cudaEventSynchronize (f->stage_ev [slot]) != cudaSuccess) { status [t] = 1 ; return ; }   // its last DMA is done
+                memcpy (buf, (const unsigned char *) src + off, len) ;
+                if (cudaMemcpyAsync ((unsigned char *) dst + off, buf, len, cudaMemcpyHostToDevice, s) != cudaSuccess
+                    || cudaEventRecord (f->stage_ev [slot], s) != cudaSuccess) { status [t] = 1 ; return ; }
+            }
+        }) ;
+    for (auto &t : th) t.join () ;
+    for (int st : status) if (st) { cudaGetLastError () ; return B200_GPU_PROBLEM ; }
+    return B200_OK ;
+}
+
 // one CSC matrix (ncols columns) to the device; returns its entry count through *nz_out
 static int upload_csc (b200_factor *f, int64_t ncols, const int64_t *Ap, const int64_t *Ai, const int64_t *Anz,
     const void *Ax, DevBuf<int64_t> &dp, DevBuf<int64_t> &di, DevBuf<int64_t> &dnz, DevBuf<unsigned char> &dx,
@@ -984,8 +1042,9 @@ static int upload_csc (b200_factor *f, int64_t ncols, const int64_t *Ap, const i
     CK (cudaMemcpyAsync (dp.p, Ap, (size_t) (ncols + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
     if (nz > 0)
     {
-        CK (cudaMemcpyAsync (di.p, Ai, (size_t) nz * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ai") ;
-        CK (cudaMemcpyAsync (dx.p, Ax, (size_t) nz * f->esize, cudaMemcpyHostToDevice, s), "H2D Ax") ;
+        int st = h2d_staged (f, di.p, Ai, (size_t) nz * sizeof (int64_t), s) ;
+        if (!st) st = h2d_staged (f, dx.p, Ax, (size_t) nz * f->esize, s) ;
+        if (st) return st ;
     }
     if (Anz && ncols > 0) CK (cudaMemcpyAsync (dnz.p, Anz, (size_t) ncols * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
     *nz_out = nz ;
@@ -1036,7 +1095,8 @@ int b200_upload_values (b200_factor *f, const void *Ax)
     if (f->A_nz == 0) return B200_OK ;
     if (!Ax) return B200_INVALID ;
     CK (cudaEventRecord (f->ev [0], f->stream), "record") ;
-    CK (cudaMemcpyAsync (f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, cudaMemcpyHostToDevice, f->stream), "H2D Ax") ;
+    st = h2d_staged (f, f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, f->stream) ;
+    if (st) return st ;
     CK (cudaEventRecord (f->ev [1], f->stream), "record") ;
     CK (cudaStreamSynchronize (f->stream), "H2D Ax") ;
     cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
@@ -1045,37 +1105,79 @@ int b200_upload_values (b200_factor *f, const void *Ax)
 
 }   // extern "C"
 
-// pin the caller's L->x once: later factorizations into the same buffer then copy at PCIe speed
+static void unregister_pieces (b200_factor *f)
+{
+    for (auto &pc : f->reg_pieces) { cudaHostUnregister (pc.first) ; cudaGetLastError () ; }
+    f->reg_pieces.clear () ;
+    f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+}
+
+static bool is_page_locked (const void *p, size_t bytes)
+{
+    unsigned fl = 0 ;
+    if (bytes == 0) return true ;
+    if (cudaHostGetFlags (&fl, const_cast<void *> (p)) == cudaSuccess
+        && cudaHostGetFlags (&fl, (char *) const_cast<void *> (p) + (bytes - 1)) == cudaSuccess) return true ;
+    cudaGetLastError () ;
+    return false ;
+}
+
+// Page-lock the caller's L->x once: later factorizations into the same buffer then copy at PCIe speed and
+// overlap with the computation.  One GPU, or several GPUs driven from one process (b200_multi): the whole buffer
+// (portable; the first context to get here registers it, the others find it registered).  One process per GPU:
+// every process page-locks only the pieces of the (shared) buffer that its rank writes -- its subtrees and its
+// blocks of the top separators -- not N times the whole factor.
 static void ensure_registered (b200_factor *f, void *Lx, size_t bytes)
 {
     if (f->reg_ptr == Lx && f->reg_bytes == bytes)
     {
         // same address and size as last time -- but the caller may have freed and re-obtained the memory in
-        // between without telling us (b200_forget_host_buffer): ask the driver whether the first and the last
-        // page are still page-locked mappings before trusting the registration
-        unsigned fl = 0 ;
-        if (bytes == 0 || (cudaHostGetFlags (&fl, Lx) == cudaSuccess
-            && cudaHostGetFlags (&fl, (char *) Lx + (bytes - 1)) == cudaSuccess)) return ;
-        cudaGetLastError () ;
-        cudaHostUnregister (f->reg_ptr) ;
-        cudaGetLastError () ;
-        f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+        // between without telling us (b200_forget_host_buffer): ask the driver whether what we registered is
+        // still a page-locked mapping before trusting it
+        bool ok = true ;
+        for (auto &pc : f->reg_pieces) ok = ok && is_page_locked (pc.first, pc.second) ;
+        if (ok) return ;
     }
-    if (f->reg_ptr) { cudaHostUnregister (f->reg_ptr) ; f->reg_ptr = nullptr ; f->reg_bytes = 0 ; }
+    unregister_pieces (f) ;
+    f->reg_ptr = Lx ; f->reg_bytes = bytes ;
+    bool other_processes = false ;
+    for (int r = 0 ; r < 32 ; r++) other_processes = other_processes || f->peer_ipc [r] ;
+    if (f->plan.nranks > 1 && other_processes)
     {
-        // page-locked already -- by the caller, or by another context of this process that writes into the same
-        // buffer (b200_multi)?  Then there is nothing to do, and nothing of ours to undo later.
-        unsigned fl = 0 ;
-        if (bytes > 0 && cudaHostGetFlags (&fl, Lx) == cudaSuccess
-            && cudaHostGetFlags (&fl, (char *) Lx + (bytes - 1)) == cudaSuccess) return ;
-        cudaGetLastError () ;
+        // page-aligned hulls of the owned runs, merged where they touch or lie within 2 MB of each other
+        const size_t page = 4096, gap = (size_t) 2 << 20 ;
+        std::vector<std::pair<size_t, size_t>> rg ;
+        for (const CopySeg &c : f->plan.owned)
+        {
+            if (c.len <= 0) continue ;
+            size_t a = (size_t) c.hoff * f->esize, b = a + (size_t) c.len * f->esize ;
+            const size_t base = (size_t) (uintptr_t) Lx ;
+            a = ((base + a) / page) * page ; b = ((base + b + page - 1) / page) * page ;
+            a = std::max (a, (base / page) * page) ; b = std::min (b, ((base + bytes + page - 1) / page) * page) ;
+            rg.push_back ({ a, b }) ;
+        }
+        std::sort (rg.begin (), rg.end ()) ;
+        std::vector<std::pair<size_t, size_t>> merged ;
+        for (auto &r : rg)
+        {
+            if (!merged.empty () && r.first <= merged.back ().second + gap) merged.back ().second = std::max (merged.back ().second, r.second) ;
+            else merged.push_back (r) ;
+        }
+        for (auto &r : merged)
+        {
+            void *p = (void *) (uintptr_t) r.first ;
+            const size_t len = r.second - r.first ;
+            if (len < ((size_t) 1 << 16) || is_page_locked (p, len)) continue ;
+            if (cudaHostRegister (p, len, cudaHostRegisterPortable) == cudaSuccess) f->reg_pieces.push_back ({ p, len }) ;
+            else cudaGetLastError () ;
+        }
+        return ;
     }
-    // portable: the contexts of several devices in one process (b200_multi) all copy into the same buffer; the
-    // first of them to get here registers it, the others find it registered already
+    // page-locked already -- by the caller, or by another context of this process that writes into the same
+    // buffer (b200_multi)?  Then there is nothing to do, and nothing of ours to undo later.
+    if (bytes > 0 && is_page_locked (Lx, bytes)) return ;
     if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterPortable) == cudaSuccess)
-    {
-        f->reg_ptr = Lx ; f->reg_bytes = bytes ;
-    }
+        f->reg_pieces.push_back ({ Lx, bytes }) ;
     else cudaGetLastError () ;
 }
 
@@ -1238,9 +1340,7 @@ int b200_forget_host_buffer (b200_factor *f, const void *Lx)
     {
         if (set_device (f)) return B200_GPU_PROBLEM ;
         cudaStreamSynchronize (f->stream3) ;
-        cudaHostUnregister (f->reg_ptr) ;
-        cudaGetLastError () ;
-        f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+        unregister_pieces (f) ;
     }
     return B200_OK ;
 }

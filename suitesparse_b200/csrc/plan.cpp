@@ -36,7 +36,7 @@ struct Own
     int block_owner (int64_t s, int64_t T) const
     {
         if (!dist ()) return D->rank ;
-        return D->top [s] ? (int) ((D->owner [s] + T / D->dist_run) % D->nranks) : D->owner [s] ;
+        return D->top [s] ? (int) ((D->owner [s] + T / D->run [s]) % D->nranks) : D->owner [s] ;
     }
     bool mine (int64_t s, int64_t T) const { return block_owner (s, T) == D->rank ; }
 } ;
@@ -672,9 +672,16 @@ int partition (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *
         P.owner [r] = g ;
     }
     int ntop = 0 ;
+    P.run.assign ((size_t) nsuper, 1) ;
     for (int64_t s = nsuper - 1 ; s >= 0 ; s--)
     {
-        if (P.top [s]) { P.owner [s] = (ntop++) % R ; continue ; }
+        if (P.top [s])
+        {
+            P.owner [s] = (ntop++) % R ;
+            const int64_t nblocks = cdiv (super [s+1] - super [s], OUTER_NB) ;
+            P.run [s] = (P.dist_run > 0) ? P.dist_run : (int32_t) std::max<int64_t> (1, std::min<int64_t> (DIST_RUN, nblocks / (3 * R))) ;
+            continue ;
+        }
         int64_t p = P.parent [s] ;
         if (p >= 0 && !P.top [p]) { P.sroot [s] = P.sroot [p] ; P.owner [s] = P.owner [p] ; }
     }

@@ -177,7 +177,10 @@ struct Plan
     // cyclic); every other supernode belongs, with its whole subtree, to one rank, is stored on that rank only,
     // and reaches the top separators as that rank's contribution blocks (build_dist in plan.cpp).
     int32_t nranks = 1, rank = 0 ;
-    int32_t dist_run = DIST_RUN ;       // outer blocks per block-cyclic unit (env CHOLMOD_B200_DIST_RUN overrides)
+    int32_t dist_run = 0 ;              // outer blocks per block-cyclic unit; 0 = chosen per supernode (env CHOLMOD_B200_DIST_RUN overrides)
+    std::vector<int32_t> run ;          // [nsuper] the unit of top supernode s: about a third of an even share of its
+                                        // blocks, at most DIST_RUN (long runs keep the chain off the broadcasts, short
+                                        // runs balance the update work of a supernode with few blocks)
     std::vector<char> top ;             // [nsuper]
     std::vector<int32_t> owner ;        // [nsuper] owning rank (top: the rank of outer block 0)
     std::vector<int32_t> sroot ;        // [nsuper] root of the local subtree of a non-top supernode
