@@ -287,8 +287,12 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
 int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 
 /* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):
- * "level", "parent", "relmap", "items", "tiles", "potrf", "trsm", "launches" (layouts in
- * csrc/plan.hpp).  Works on a device < 0 context; used by the CPU tests of the planner. */
+ * "level", "parent", "relmap", "pairs", "pair_map", "items", "tiles", "potrf", "trsm", "launches", "copies",
+ * "owned", "bcasts", "pulls", "dpx", "colmine", "owner", "top", "group" (layouts in csrc/plan.hpp).  Works on a
+ * device < 0 context; used by the CPU tests of the planner.  "dev_pairs", "dev_pair_map", "dev_relmap": the
+ * symbolic tables a one-GPU context builds on the device (csrc/symbolic.cuh: the pair walk of
+ * cholmod_super_symbolic.c:896-921 and the relative maps of t_cholmod_super_numeric_worker.c:897-903), copied
+ * back for comparison with the host planner's. */
 int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, int64_t out_bytes) ;
 
 /* Measured FP64 tensor-pipe (DMMA, mma.sync.m8n8k4.f64) peak of `device` in TFLOP/s from a

@@ -384,6 +384,7 @@ K_FACTOR_SMALL, K_FACTOR_TINY, K_UPD_TINY = 9, 10, 11
 K_JOIN, K_COPYOUT, K_BCAST, K_BARRIER, K_PULL = 12, 13, 14, 15, 16
 BCAST_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("root", "<i4"), ("pad", "<i4")])
 COPY_DT = np.dtype([("off", "<i8"), ("len", "<i8"), ("hoff", "<i8")])
+PAIR_DT = np.dtype([("d", "<i4"), ("s", "<i4"), ("lpos", "<i4"), ("ndrow1", "<i4"), ("ndrow2", "<i4")])
 PULL_DT = np.dtype([("off", "<i8"), ("nrows", "<i4"), ("ncols", "<i4"), ("ld", "<i4"), ("mask", "<u4")])
 K_UPD_SIMT, K_UPD_D64, K_UPD_D128, K_POTRF16, K_POTRF32, K_POTRF64, K_TRSM, K_TRSM_INV32, K_TRSM_INV64 = range(9)
 K_POTRF_KINDS = (K_POTRF16, K_POTRF32, K_POTRF64)

@@ -4,6 +4,7 @@
 #include "../../include/cholmod_b200.h"
 #include "plan.hpp"
 #include "kernels.cuh"
+#include "symbolic.cuh"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -123,6 +124,10 @@ struct b200_factor
     // symbolic tables
     DevBuf<int64_t> d_super, d_pi, d_px ;
     DevBuf<int32_t> d_Ls, d_supermap, d_relmap, d_level_list ;
+    DevBuf<Pair> d_pairs ;                  // device-built symbolic tables (symbolic.cuh): the pair list ...
+    DevBuf<int64_t> d_pair_map ;            // ... and where each pair's relative map lies in d_relmap
+    bool device_symbolic = false ;          // d_relmap was built on the device, not uploaded
+    float ms_symbolic = -1 ;
     DevBuf<UpdItem> d_items ;
     DevBuf<UpdTile> d_tiles ;
     DevBuf<PotrfBlk> d_potrf ;
@@ -604,6 +609,69 @@ int b200_memorysize (int device, size_t *free_bytes, size_t *total_bytes)
     return B200_OK ;
 }
 
+// The pair list and the relative maps, on the device, from the symbolic tables already there (symbolic.cuh).
+// Fails with B200_INVALID if the counts disagree with the host planner's or a row of a descendant is missing from
+// its ancestor's pattern.
+static int build_device_symbolic (b200_factor *f)
+{
+    const Plan &P = f->plan ;
+    cudaStream_t s = f->stream ;
+    const int64_t ns = P.nsuper ;
+    if (ns == 0 || P.npairs == 0) { f->device_symbolic = true ; return B200_OK ; }
+    DevBuf<int64_t> cnt, first, len, off ;
+    DevBuf<int32_t> key, key2, idx, order ;
+    DevBuf<unsigned char> tmp ;
+    DevBuf<int> bad ;
+    auto fail = [&] (int st) { cudaGetLastError () ; return st ; } ;
+    if (cnt.alloc ((size_t) ns + 1) != cudaSuccess || first.alloc ((size_t) ns + 1) != cudaSuccess
+        || bad.alloc (1) != cudaSuccess) return fail (B200_OUT_OF_MEMORY) ;
+    CK (cudaEventRecord (f->ev [0], s), "record") ;
+    CK (cudaMemsetAsync (cnt.p, 0, ((size_t) ns + 1) * sizeof (int64_t), s), "memset") ;
+    CK (cudaMemsetAsync (bad.p, 0, sizeof (int), s), "memset") ;
+    const unsigned gd = (unsigned) ((ns + 127) / 128) ;
+    k_sym_pair_count<<<gd, 128, 0, s>>> (ns, f->d_super.p, f->d_pi.p, f->d_Ls.p, f->d_supermap.p, cnt.p) ;
+    size_t tb = 0 ;
+    CK (cub::DeviceScan::ExclusiveSum (nullptr, tb, cnt.p, first.p, (int) (ns + 1), s), "scan size") ;
+    if (tmp.alloc (tb + 16) != cudaSuccess) return fail (B200_OUT_OF_MEMORY) ;
+    CK (cub::DeviceScan::ExclusiveSum (tmp.p, tb, cnt.p, first.p, (int) (ns + 1), s), "scan") ;
+    int64_t np = -1 ;
+    CK (cudaMemcpyAsync (&np, first.p + ns, sizeof (np), cudaMemcpyDeviceToHost, s), "npairs") ;
+    CK (cudaStreamSynchronize (s), "pair count") ;
+    if (np != P.npairs) { fprintf (stderr, "cholmod_b200: device pair count %lld, host %lld\n", (long long) np, (long long) P.npairs) ; return B200_INVALID ; }
+    if (f->d_pairs.alloc ((size_t) np) != cudaSuccess || f->d_pair_map.alloc ((size_t) np) != cudaSuccess
+        || key.alloc ((size_t) np) != cudaSuccess || key2.alloc ((size_t) np) != cudaSuccess
+        || idx.alloc ((size_t) np) != cudaSuccess || order.alloc ((size_t) np) != cudaSuccess
+        || len.alloc ((size_t) np + 1) != cudaSuccess || off.alloc ((size_t) np + 1) != cudaSuccess
+        || f->d_relmap.alloc ((size_t) std::max<int64_t> (P.relmap_len, 1)) != cudaSuccess) return fail (B200_OUT_OF_MEMORY) ;
+    k_sym_pair_emit<<<gd, 128, 0, s>>> (ns, f->d_super.p, f->d_pi.p, f->d_Ls.p, f->d_supermap.p, first.p, f->d_pairs.p, key.p, idx.p) ;
+    // by target, pairs of one target in descendant order (stable): the order the maps are laid out in
+    int bits = 1 ; while (((int64_t) 1 << bits) < ns) bits++ ;
+    size_t sb = 0 ;
+    CK (cub::DeviceRadixSort::SortPairs (nullptr, sb, key.p, key2.p, idx.p, order.p, (int) np, 0, bits, s), "sort size") ;
+    if (sb + 16 > tmp.n && tmp.alloc (sb + 16) != cudaSuccess) return fail (B200_OUT_OF_MEMORY) ;
+    CK (cub::DeviceRadixSort::SortPairs (tmp.p, sb, key.p, key2.p, idx.p, order.p, (int) np, 0, bits, s), "sort") ;
+    CK (cudaMemsetAsync (len.p + np, 0, sizeof (int64_t), s), "memset") ;
+    k_sym_gather_len<<<(unsigned) ((np + 255) / 256), 256, 0, s>>> (np, f->d_pairs.p, order.p, len.p) ;
+    size_t tb2 = 0 ;
+    CK (cub::DeviceScan::ExclusiveSum (nullptr, tb2, len.p, off.p, (int) (np + 1), s), "scan size") ;
+    if (tb2 + 16 > tmp.n && tmp.alloc (tb2 + 16) != cudaSuccess) return fail (B200_OUT_OF_MEMORY) ;
+    CK (cub::DeviceScan::ExclusiveSum (tmp.p, tb2, len.p, off.p, (int) (np + 1), s), "scan") ;
+    k_sym_relmap<<<(unsigned) ((np * 32 + 255) / 256), 256, 0, s>>> (np, f->d_pairs.p, order.p, off.p, f->d_super.p, f->d_pi.p,
+        f->d_Ls.p, f->d_pair_map.p, f->d_relmap.p, bad.p) ;
+    int64_t total = -1 ; int hbad = 0 ;
+    CK (cudaMemcpyAsync (&total, off.p + np, sizeof (total), cudaMemcpyDeviceToHost, s), "relmap length") ;
+    CK (cudaMemcpyAsync (&hbad, bad.p, sizeof (hbad), cudaMemcpyDeviceToHost, s), "flag") ;
+    CK (cudaEventRecord (f->ev [1], s), "record") ;
+    CK (cudaStreamSynchronize (s), "device symbolic") ;
+    CK (cudaGetLastError (), "device symbolic kernels") ;
+    cudaEventElapsedTime (&f->ms_symbolic, f->ev [0], f->ev [1]) ;
+    cnt.release () ; first.release () ; len.release () ; off.release () ; key.release () ; key2.release () ;
+    idx.release () ; order.release () ; tmp.release () ; bad.release () ;
+    if (total != P.relmap_len || hbad) return B200_INVALID ;
+    f->device_symbolic = true ;
+    return B200_OK ;
+}
+
 static int create_device_side (b200_factor *f, const int64_t *Ls)
 {
     const Plan &P = f->plan ;
@@ -627,7 +695,7 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
     {
         // refuse before allocating anything if the context cannot fit under the cap set for this device
-        const size_t need = (size_t) (3 * (P.nsuper + 1)) * 8 + (size_t) P.ssize * 4 + (size_t) P.n * 4 + P.relmap.size () * 4
+        const size_t need = (size_t) (3 * (P.nsuper + 1)) * 8 + (size_t) P.ssize * 4 + (size_t) P.n * 4 + (size_t) P.relmap_len * 4
             + (size_t) P.nsuper * 4 + P.items.size () * sizeof (UpdItem) + P.tiles.size () * sizeof (UpdTile)
             + P.potrf.size () * sizeof (PotrfBlk) + P.trsm.size () * sizeof (TrsmTile) + (size_t) P.dxsize * f->esize
             + (size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize ;
@@ -649,7 +717,7 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     ok = ok && f->d_px.upload (P.dpx, s) == cudaSuccess ;        // ARENA offsets (== L->px on one GPU)
     ok = ok && f->d_Ls.upload (Ls32, s) == cudaSuccess ;
     ok = ok && f->d_supermap.upload (P.supermap, s) == cudaSuccess ;
-    ok = ok && f->d_relmap.upload (P.relmap, s) == cudaSuccess ;
+    if (!P.relmap.empty () || P.relmap_len == 0) ok = ok && f->d_relmap.upload (P.relmap, s) == cudaSuccess ;
     ok = ok && f->d_level_list.upload (P.level_list, s) == cudaSuccess ;
     ok = ok && f->d_items.upload (P.items, s) == cudaSuccess ;
     ok = ok && f->d_tiles.upload (P.tiles, s) == cudaSuccess ;
@@ -670,10 +738,16 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
     ok = ok && f->d_winv.alloc ((size_t) std::max<int64_t> (P.winv_slots, 1) * WINV_LD * WINV_LD * f->esize) == cudaSuccess ;
     if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
     CK (cudaStreamSynchronize (s), "upload symbolic") ;
+    if (P.relmap.empty () && P.relmap_len > 0)
+    {
+        // the relative maps were left out of the host plan: build them here, from the tables just uploaded
+        st = build_device_symbolic (f) ;
+        if (st != B200_OK) return st ;
+    }
     f->device_bytes = f->d_super.bytes () + f->d_pi.bytes () + f->d_px.bytes () + f->d_Ls.bytes ()
         + f->d_supermap.bytes () + f->d_relmap.bytes () + f->d_level_list.bytes () + f->d_items.bytes ()
         + f->d_tiles.bytes () + f->d_potrf.bytes () + f->d_trsm.bytes () + f->d_Lx.bytes () + f->d_winv.bytes ()
-        + f->d_colmine.bytes () + f->d_pulls.bytes () ;
+        + f->d_colmine.bytes () + f->d_pulls.bytes () + f->d_pairs.bytes () + f->d_pair_map.bytes () ;
     if (f->device < 64)
     {
         std::lock_guard<std::mutex> guard (g_mem_lock) ;
@@ -709,7 +783,12 @@ b200_factor *b200_create_dist (int64_t n, int64_t nsuper, const int64_t *super, 
                 long long a = -1, b = 0 ;
                 if (sscanf (e, "%lld,%lld", &a, &b) == 2) { trunc_s = a ; trunc_ncol = b ; }
             }
-        *status = build_plan (n, nsuper, super, pi, px, s, dtype_dmma (dtype), f->plan, nranks, rank, trunc_s, trunc_ncol) ;
+        // the relative maps -- the planner's biggest table -- are built on the device (symbolic.cuh) for a one-GPU
+        // context; plan-only contexts, distributed plans (which read the maps) and CHOLMOD_B200_HOST_RELMAP=1 keep
+        // the host version
+        const bool host_relmap = device < 0 || nranks > 1 || getenv ("CHOLMOD_B200_HOST_RELMAP") != nullptr ;
+        *status = build_plan (n, nsuper, super, pi, px, s, dtype_dmma (dtype), f->plan, nranks, rank, trunc_s, trunc_ncol,
+            host_relmap) ;
         if (*status == B200_OK)
         {
             f->h_super.assign (super, super + nsuper + 1) ;
@@ -751,6 +830,7 @@ void b200_destroy (b200_factor *f)
         for (auto &pc : f->reg_pieces) cudaHostUnregister (pc.first) ;
         f->d_super.release () ; f->d_pi.release () ; f->d_px.release () ; f->d_Ls.release () ;
         f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
+        f->d_pairs.release () ; f->d_pair_map.release () ;
         f->d_items.release () ; f->d_tiles.release () ; f->d_potrf.release () ; f->d_trsm.release () ;
         f->d_Lx.release () ; f->d_Ap.release () ; f->d_Ai.release () ; f->d_Anz.release () ;
         f->d_Ax.release () ; f->d_Fp.release () ; f->d_Fi.release () ; f->d_Fnz.release () ; f->d_Fx.release () ;
@@ -789,7 +869,8 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "npairs")) return P.npairs ;
     if (!strcmp (name, "npairs_gemm")) return P.npairs_gemm ;
     if (!strcmp (name, "nsuper_trsm")) return P.nsuper_trsm ;
-    if (!strcmp (name, "relmap_len")) return (int64_t) P.relmap.size () ;
+    if (!strcmp (name, "relmap_len")) return P.relmap_len ;
+    if (!strcmp (name, "device_symbolic")) return f->device_symbolic ? 1 : 0 ;
     if (!strcmp (name, "nitems")) return (int64_t) P.items.size () ;
     if (!strcmp (name, "ntiles")) return (int64_t) P.tiles.size () ;
     if (!strcmp (name, "npotrf")) return (int64_t) P.potrf.size () ;
@@ -845,6 +926,7 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_scatter")) return f->ms_scatter ;
     if (!strcmp (name, "ms_solve")) return f->ms_solve ;
     if (!strcmp (name, "ms_pull")) return f->ms_pull ;
+    if (!strcmp (name, "ms_symbolic")) return f->ms_symbolic ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '9' && atoi (name + 7) < K_NKINDS) return f->ms_kind [atoi (name + 7)] ;
     if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
     if (!strncmp (name, "solve_launches", 14) && name [14] >= '0' && name [14] < '4') return (double) f->solve_launch_count [name [14] - '0'] ;
@@ -881,6 +963,22 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
     else if (!strcmp (which, "colmine")) { src = P.colmine.data () ; bytes = P.colmine.size () ; }
     else if (!strcmp (which, "pulls")) { src = P.pulls.data () ; bytes = P.pulls.size () * sizeof (PullSeg) ; }
     else if (!strcmp (which, "owned")) { src = P.owned.data () ; bytes = P.owned.size () * sizeof (CopySeg) ; }
+    else if (!strncmp (which, "dev_", 4) && f->device >= 0 && f->device_symbolic)
+    {
+        // the device-built symbolic tables, copied back (tests compare them with the host planner's)
+        const void *dsrc = nullptr ;
+        if (!strcmp (which, "dev_pairs")) { dsrc = f->d_pairs.p ; bytes = f->d_pairs.bytes () ; }
+        else if (!strcmp (which, "dev_pair_map")) { dsrc = f->d_pair_map.p ; bytes = f->d_pair_map.bytes () ; }
+        else if (!strcmp (which, "dev_relmap")) { dsrc = f->d_relmap.p ; bytes = (size_t) P.relmap_len * sizeof (int32_t) ; }
+        else return -1 ;
+        if (!out) return (int64_t) bytes ;
+        if ((int64_t) bytes > out_bytes) return -1 ;
+        if (cudaSetDevice (f->device) != cudaSuccess) return -1 ;
+        if (bytes && cudaMemcpy (out, dsrc, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError () ; return -1 ; }
+        return (int64_t) bytes ;
+    }
+    else if (!strcmp (which, "pairs")) { src = P.pairs.data () ; bytes = P.pairs.size () * sizeof (Pair) ; }
+    else if (!strcmp (which, "pair_map")) { src = P.pair_map.data () ; bytes = P.pair_map.size () * sizeof (int64_t) ; }
     else return -1 ;
     if (!out) return (int64_t) bytes ;
     if ((int64_t) bytes > out_bytes) return -1 ;

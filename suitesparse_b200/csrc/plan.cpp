@@ -939,8 +939,10 @@ int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t 
 }   // namespace
 
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
-    const int64_t *Ls, bool use_dmma, Plan &P, int nranks, int rank, int64_t trunc_s, int64_t trunc_ncol)
+    const int64_t *Ls, bool use_dmma, Plan &P, int nranks, int rank, int64_t trunc_s, int64_t trunc_ncol,
+    bool host_relmap)
 {
+    if (nranks > 1) host_relmap = true ;        // the distributed planner cuts updates by the maps' contents
     if (n < 0 || nsuper < 0 || !super || !pi || !px || (!Ls && nsuper > 0)) return B200_INVALID ;
     if (nranks < 1 || rank < 0 || rank >= nranks) return B200_INVALID ;
     if (n >= (int64_t) 1 << 31 || nsuper >= (int64_t) 1 << 31) return B200_TOO_LARGE ;
@@ -1054,6 +1056,21 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
     {
         int64_t total = 0 ;
         for (size_t k = 0 ; k < pairs.size () ; k++) total += pairs [k].ndrow2 ;
+        P.relmap_len = total ;
+        if (!host_relmap)
+        {
+            // only where each pair's map will lie (the same layout: by target, pairs of a target in order); the maps
+            // themselves are built on the device (symbolic.cuh), which also checks that every row is found
+            int64_t off = 0 ;
+            for (int64_t s = 0 ; s < nsuper ; s++)
+                for (int64_t t = tcount [s] ; t < tcount [s+1] ; t++)
+                {
+                    P.pair_map [P.target_list [t]] = off ;
+                    off += pairs [P.target_list [t]].ndrow2 ;
+                }
+        }
+        else
+        {
         P.relmap.resize ((size_t) total) ;
         std::vector<int32_t> Map ((size_t) n, -1), stamp ((size_t) n, -1) ;
         int64_t off = 0 ;
@@ -1081,6 +1098,7 @@ int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *
                 }
                 off += pr.ndrow2 ;
             }
+        }
         }
     }
 

@@ -149,7 +149,9 @@ struct Plan
     std::vector<int32_t> level ;        // [nsuper] height above the leaves in the supernodal etree
     std::vector<int64_t> parent ;       // [nsuper] etree parent or -1
     std::vector<int32_t> supermap ;     // [n] column -> supernode (cholmod_super_numeric.c:276-285)
-    std::vector<int32_t> relmap ;       // concatenated relative maps of all pairs
+    std::vector<int32_t> relmap ;       // concatenated relative maps of all pairs (empty when they are built on the
+                                        // device instead, symbolic.cuh: only their offsets pair_map exist here then)
+    int64_t relmap_len = 0 ;            // total length of the relative maps
     std::vector<UpdItem> items ;
     std::vector<UpdTile> tiles ;
     std::vector<PotrfBlk> potrf ;
@@ -203,7 +205,7 @@ struct Plan
 // trunc_s as usual, trunc_s itself for its first trunc_ncol columns, nothing after it.
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
     const int64_t *Ls, bool use_dmma, Plan &plan, int nranks = 1, int rank = 0, int64_t trunc_s = -1,
-    int64_t trunc_ncol = 0) ;
+    int64_t trunc_ncol = 0, bool host_relmap = true) ;
 
 // SNW:1084-1146: a one-supernode plan that re-applies every descendant update to supernode s and then
 // factorizes only its first nscol_new columns (dtrsm on all rows below them).  Reuses P.relmap.
