@@ -642,7 +642,10 @@ int partition (Plan &P, const int64_t *super, const int64_t *pi, const int64_t *
         if (p >= 0) { sub [p] += sub [s] ; first [p] = std::min (first [p], first [s]) ; }
         else total += sub [s] ;
     }
-    const double thresh = total / (4.0 * R) ;
+    // (CHOLMOD_B200_TOP_DIV: the 4 of "1/(4 nranks) of all work", for experiments)
+    double top_div = 4.0 ;
+    if (const char *e = getenv ("CHOLMOD_B200_TOP_DIV")) top_div = std::max (0.5, atof (e)) ;
+    const double thresh = total / (top_div * R) ;
     for (int64_t s = 0 ; s < nsuper ; s++) P.top [s] = (sub [s] > thresh) ? 1 : 0 ;
     // a subtree's owner also computes the updates of its supernodes into the top separators (its
     // contribution blocks): that work counts towards the subtree's load
@@ -874,37 +877,60 @@ int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t 
     flush_tiles (P, sink, std::max (0, first_top_level - 1)) ;
 
     // ---- fan-in --------------------------------------------------------------------------------------------------
+    // One barrier, then the pulls level by level on a stream of their own (5): the main stream only waits for the
+    // pulls of the level it is about to factorize, so the big separators' contribution blocks cross NVLink while
+    // the smaller ones below them are already being factorized.
+    std::vector<int> ev_pull ((size_t) nlevels, -1) ;
     {
-        const int lev = std::max (0, std::min (first_top_level, nlevels - 1)) ;
+        const int lev0 = std::max (0, std::min (first_top_level, nlevels - 1)) ;
         const int evA = P.nevents++, evM = P.nevents++ ;
-        Launch J = make_launch (K_JOIN, 0, 0, lev, 0) ; J.rec_ev = evA ;
+        Launch J = make_launch (K_JOIN, 0, 0, lev0, 0) ; J.rec_ev = evA ;
         P.launches.push_back (J) ;
-        Launch B = make_launch (K_BARRIER, 0, 0, lev, 3) ; B.wait_ev = evA ; B.rec_ev = evM ;
+        Launch B = make_launch (K_BARRIER, 0, 0, lev0, 3) ; B.wait_ev = evA ; B.rec_ev = evM ;
         P.launches.push_back (B) ;
-        const size_t first = P.pulls.size () ;
-        for (int64_t s = 0 ; s < nsuper ; s++)
+        P.nstreams = 6 ;
+        bool first_pull = true ;
+        for (int lev = 0 ; lev < nlevels ; lev++)
         {
-            if (!P.top [s] || s > last || ncol_of (s) == 0) continue ;
-            const uint32_t others = contrib [s] & ~(1u << rank) ;
-            if (!others) continue ;
-            int po = 0 ; for (uint32_t m = others ; m ; m &= m - 1) po++ ;
-            const int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
-            for (int64_t J0 = 0 ; J0 < nscol ; J0 += OUTER_NB)
+            const size_t first = P.pulls.size () ;
+            for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++)
             {
-                if (!own.mine (s, J0 / OUTER_NB)) continue ;
-                const int64_t Jend = std::min (nscol, J0 + OUTER_NB) ;
-                PullSeg g ;
-                g.off = dpx [s] + J0 + J0 * nsrow ;        // rows J0.. of columns J0..Jend-1: the lower part
-                g.nrows = (int32_t) (nsrow - J0) ; g.ncols = (int32_t) (Jend - J0) ; g.ld = (int32_t) nsrow ;
-                g.mask = others ;
-                P.pulls.push_back (g) ;
-                P.nvlink_in_values += (int64_t) po * g.nrows * g.ncols ;
+                const int64_t s = P.level_list [q] ;
+                if (!P.top [s] || s > last || ncol_of (s) == 0) continue ;
+                const uint32_t others = contrib [s] & ~(1u << rank) ;
+                if (!others) continue ;
+                int po = 0 ; for (uint32_t m = others ; m ; m &= m - 1) po++ ;
+                const int64_t nscol = super [s+1] - super [s], nsrow = pi [s+1] - pi [s] ;
+                for (int64_t J0 = 0 ; J0 < nscol ; J0 += OUTER_NB)
+                {
+                    if (!own.mine (s, J0 / OUTER_NB)) continue ;
+                    const int64_t Jend = std::min (nscol, J0 + OUTER_NB) ;
+                    PullSeg g ;
+                    g.off = dpx [s] + J0 + J0 * nsrow ;        // rows J0.. of columns J0..Jend-1: the lower part
+                    g.nrows = (int32_t) (nsrow - J0) ; g.ncols = (int32_t) (Jend - J0) ; g.ld = (int32_t) nsrow ;
+                    g.mask = others ;
+                    P.pulls.push_back (g) ;
+                    P.nvlink_in_values += (int64_t) po * g.nrows * g.ncols ;
+                }
             }
+            bool has_top = false ;
+            for (int64_t q = P.level_ptr [lev] ; q < P.level_ptr [lev+1] ; q++) has_top = has_top || P.top [P.level_list [q]] ;
+            if (!has_top) continue ;
+            // (a level without anything to pull still takes its turn: its event orders it after the barrier)
+            ev_pull [lev] = P.nevents++ ;
+            Launch W = make_launch (P.pulls.size () > first ? K_PULL : K_JOIN, (int64_t) first,
+                (int64_t) (P.pulls.size () - first), lev, 5) ;
+            W.wait_ev = first_pull ? evM : -1 ;
+            W.rec_ev = ev_pull [lev] ;
+            first_pull = false ;
+            P.launches.push_back (W) ;
         }
-        Launch W = make_launch (P.pulls.size () > first ? K_PULL : K_JOIN, (int64_t) first,
-            (int64_t) (P.pulls.size () - first), lev, 0) ;
-        W.wait_ev = evM ;
-        P.launches.push_back (W) ;
+        if (first_pull)
+        {
+            // no top separator at all (cannot happen with nranks > 1 and a non-empty factor, but keep the barrier joined)
+            Launch W = make_launch (K_JOIN, 0, 0, lev0, 0) ; W.wait_ev = evM ;
+            P.launches.push_back (W) ;
+        }
     }
 
     // ---- phase B: the top separators ---------------------------------------------------------------------------
@@ -917,6 +943,11 @@ int build_dist (Plan &P, const int64_t *super, const int64_t *pi, const int64_t 
             if (P.top [s] && s <= last && ncol_of (s) > 0) Sg.push_back (s) ;
         }
         if (Sg.empty ()) continue ;
+        if (ev_pull [lev] >= 0)
+        {
+            Launch W = make_launch (K_JOIN, 0, 0, lev, 0) ; W.wait_ev = ev_pull [lev] ;
+            P.launches.push_back (W) ;
+        }
         for (int32_t s : Sg) plan_updates_into (P, P, own, super, pi, dpx, s, sink, use_dmma, UPD_FROM_TOP) ;
         flush_tiles (P, sink, lev) ;
         ncols.resize (Sg.size ()) ;
