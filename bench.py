@@ -376,6 +376,13 @@ def main():
                     device_bytes=F.geti("device_bytes"), arena_bytes=F.geti("dxsize") * np.dtype(fdtype).itemsize,
                     nvlink_in_bytes=F.geti("nvlink_in_bytes"), ms_pull=F.getd("ms_pull"), npulls=F.geti("npulls"),
                     d2h_bytes=sum(int(c["len"]) for c in F.plan_table("owned", b200.COPY_DT)) * np.dtype(fdtype).itemsize)
+        if os.environ.get("B200_BENCH_TIMELINE") and rank in (0, 3):
+            # diagnostic: the profiled pass's device timeline of the upper levels, launch by launch
+            lt = F.plan_table("launches", b200.LAUNCH_DT)
+            lo = int(os.environ["B200_BENCH_TIMELINE"])
+            mine["timeline"] = [(int(L["kind"]), int(L["stream"]), int(L["level"]), int(L["count"]),
+                                 round(F.getd("ms_launch_start%d" % i), 3), round(F.getd("ms_launch%d" % i), 3))
+                                for i, L in enumerate(lt) if L["level"] >= lo and L["kind"] < b200.K_JOIN and L["count"] > 0]
         per_rank = [None] * world
         dist.all_gather_object(per_rank, mine)
     if rank != 0:
