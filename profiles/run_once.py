@@ -23,11 +23,19 @@ ap.add_argument("--peak", action="store_true")
 ap.add_argument("--single", action="store_true")
 args = ap.parse_args()
 if args.peak:
+    # under `ncu --profile-from-start off` only the launches between cudaProfilerStart / Stop are captured: three
+    # measurements on the idle GPU, then three more after ~2 s of continuous DMMA work
+    import torch
+    rt = torch.cuda.cudart()
+    rt.cudaProfilerStart()
     print("fresh", [round(b200.dmma_peak_tflops(0, 40000), 2) for _ in range(3)])
+    rt.cudaProfilerStop()
     t0 = time.time()
     while time.time() - t0 < 2.0:
         b200.dmma_peak_tflops(0, 40000)
+    rt.cudaProfilerStart()
     print("after 2 s of load", [round(b200.dmma_peak_tflops(0, 40000), 2) for _ in range(3)])
+    rt.cudaProfilerStop()
     sys.exit(0)
 kind, size, ordering, desc = bench.WORKLOADS[args.workload]
 ref, _ = bench.analyze(kind, size, ordering, single=args.single)
