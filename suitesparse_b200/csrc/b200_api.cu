@@ -17,6 +17,7 @@
 #include <utility>
 #include <dlfcn.h>
 #include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
+#include <cuda.h>       // types only: the few driver entry points of the green-context API are dlsym'ed
 
 using namespace b200 ;
 
@@ -68,6 +69,44 @@ NcclApi *nccl_api ()
 
 namespace {
 
+// Green contexts (CUDA 12.4+): a spatial partition of the SMs with streams of its own.  Used to keep a few SMs free
+// of the throughput kernels of a distributed plan, so that the latency-bound kernels of the panel chain never wait
+// for a tile of a look-ahead update to drain before they get an SM (reserve_sms_for_chain).  Resolved from the
+// libcuda.so.1 the runtime has already loaded; absent or failing, everything runs on ordinary streams.
+struct GreenApi
+{
+    CUresult (*DeviceGetDevResource) (CUdevice, CUdevResource *, CUdevResourceType) = nullptr ;
+    CUresult (*DevSmResourceSplitByCount) (CUdevResource *, unsigned int *, const CUdevResource *, CUdevResource *, unsigned int, unsigned int) = nullptr ;
+    CUresult (*DevResourceGenerateDesc) (CUdevResourceDesc *, CUdevResource *, unsigned int) = nullptr ;
+    CUresult (*GreenCtxCreate) (CUgreenCtx *, CUdevResourceDesc, CUdevice, unsigned int) = nullptr ;
+    CUresult (*GreenCtxDestroy) (CUgreenCtx) = nullptr ;
+    CUresult (*GreenCtxStreamCreate) (CUstream *, CUgreenCtx, unsigned int, int) = nullptr ;
+    bool ok = false ;
+} ;
+
+GreenApi *green_api ()
+{
+    static GreenApi api ;
+    static bool tried = false ;
+    static std::mutex lock ;
+    std::lock_guard<std::mutex> guard (lock) ;
+    if (tried) return api.ok ? &api : nullptr ;
+    tried = true ;
+    void *h = dlopen ("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL) ;
+    if (!h) return nullptr ;
+    #define B200_CU_SYM(field, name) *(void **) (&api.field) = dlsym (h, name)
+    B200_CU_SYM (DeviceGetDevResource, "cuDeviceGetDevResource") ;
+    B200_CU_SYM (DevSmResourceSplitByCount, "cuDevSmResourceSplitByCount") ;
+    B200_CU_SYM (DevResourceGenerateDesc, "cuDevResourceGenerateDesc") ;
+    B200_CU_SYM (GreenCtxCreate, "cuGreenCtxCreate") ;
+    B200_CU_SYM (GreenCtxDestroy, "cuGreenCtxDestroy") ;
+    B200_CU_SYM (GreenCtxStreamCreate, "cuGreenCtxStreamCreate") ;
+    #undef B200_CU_SYM
+    api.ok = api.DeviceGetDevResource && api.DevSmResourceSplitByCount && api.DevResourceGenerateDesc
+        && api.GreenCtxCreate && api.GreenCtxDestroy && api.GreenCtxStreamCreate ;
+    return api.ok ? &api : nullptr ;
+}
+
 template <typename T> struct DevBuf
 {
     T *p = nullptr ; size_t n = 0 ;
@@ -115,6 +154,8 @@ struct b200_factor
     cudaStream_t stream3 = nullptr ;        // copy stream: early D2H of finished parts of L->x
     cudaStream_t stream4 = nullptr ;        // communication stream: every NCCL call of this context
     cudaStream_t stream5 = nullptr ;        // far stream: panel rows far below the diagonal block (plan_factor)
+    CUgreenCtx green = nullptr ;            // the SM partition stream2 and stream5 live in (distributed contexts), or NULL
+    int reserved_sms = 0 ;                  // SMs outside that partition: only the other streams' kernels reach them
     std::vector<cudaStream_t> gstreams ;    // subtree-group streams of a single-GPU plan: [2g] chain, [2g+1] look-ahead
     cudaEvent_t ev_comm [2] = {} ;
     void *copy_dst = nullptr ;              // host L->x of the factorization in flight (copy-out), or NULL
@@ -686,11 +727,45 @@ static int create_device_side (b200_factor *f, const int64_t *Ls)
         int lo = 0, hi = 0 ;
         CK (cudaDeviceGetStreamPriorityRange (&lo, &hi), "priority range") ;
         CK (cudaStreamCreateWithPriority (&f->stream, cudaStreamNonBlocking, hi), "stream") ;
-        CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
+        // distributed plans: the throughput streams (look-ahead updates, far rows) get all SMs but a few, which stay
+        // free for the panel chain, the broadcasts and the fan-in (CHOLMOD_B200_RESERVE_SMS, default 8 when nranks > 1,
+        // 0 otherwise: on one GPU the updates are the bottleneck, not the chain)
+        {
+            int want = (P.nranks > 1) ? 8 : 0 ;
+            if (const char *e = getenv ("CHOLMOD_B200_RESERVE_SMS")) want = atoi (e) ;
+            GreenApi *ga = (want > 0) ? green_api () : nullptr ;
+            cudaDeviceProp prop ;
+            if (ga && cudaGetDeviceProperties (&prop, f->device) == cudaSuccess && want < prop.multiProcessorCount - 16)
+            {
+                CUdevResource sm, grp, rem ;
+                unsigned int n = 1 ;
+                CUdevResourceDesc desc = nullptr ;
+                CUstream s2 = nullptr, s5 = nullptr ;
+                const unsigned keep = (unsigned) (prop.multiProcessorCount - want) ;
+                bool ok = ga->DeviceGetDevResource ((CUdevice) f->device, &sm, CU_DEV_RESOURCE_TYPE_SM) == CUDA_SUCCESS
+                    && ga->DevSmResourceSplitByCount (&grp, &n, &sm, &rem, 0, keep & ~7u) == CUDA_SUCCESS && n == 1
+                    && ga->DevResourceGenerateDesc (&desc, &grp, 1) == CUDA_SUCCESS
+                    && ga->GreenCtxCreate (&f->green, desc, (CUdevice) f->device, CU_GREEN_CTX_DEFAULT_STREAM) == CUDA_SUCCESS ;
+                if (ok) ok = ga->GreenCtxStreamCreate (&s2, f->green, CU_STREAM_NON_BLOCKING, lo) == CUDA_SUCCESS
+                    && ga->GreenCtxStreamCreate (&s5, f->green, CU_STREAM_NON_BLOCKING, (hi < lo - 1) ? hi + 1 : hi) == CUDA_SUCCESS ;
+                if (ok)
+                {
+                    f->stream2 = (cudaStream_t) s2 ; f->stream5 = (cudaStream_t) s5 ;
+                    f->reserved_sms = prop.multiProcessorCount - (int) grp.sm.smCount ;
+                }
+                else
+                {
+                    if (s2) cudaStreamDestroy ((cudaStream_t) s2) ;
+                    if (f->green) { ga->GreenCtxDestroy (f->green) ; f->green = nullptr ; }
+                    cudaGetLastError () ;
+                }
+            }
+        }
+        if (!f->stream2) CK (cudaStreamCreateWithPriority (&f->stream2, cudaStreamNonBlocking, lo), "stream2") ;
         CK (cudaStreamCreateWithFlags (&f->stream3, cudaStreamNonBlocking), "stream3") ;
         CK (cudaStreamCreateWithPriority (&f->stream4, cudaStreamNonBlocking, hi), "stream4") ;
         // between the panel chain and the look-ahead updates when the device has more than two priority levels
-        CK (cudaStreamCreateWithPriority (&f->stream5, cudaStreamNonBlocking, (hi < lo - 1) ? hi + 1 : hi), "stream5") ;
+        if (!f->stream5) CK (cudaStreamCreateWithPriority (&f->stream5, cudaStreamNonBlocking, (hi < lo - 1) ? hi + 1 : hi), "stream5") ;
         for (auto &e : f->ev_comm) CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "event") ;
     }
     for (auto &e : f->ev) CK (cudaEventCreate (&e), "event") ;
@@ -853,6 +928,7 @@ void b200_destroy (b200_factor *f)
         if (f->stream5) { cudaStreamSynchronize (f->stream5) ; cudaStreamDestroy (f->stream5) ; }
         for (auto &e : f->ev_comm) if (e) cudaEventDestroy (e) ;
         cudaStreamDestroy (f->stream) ;
+        if (f->green) { GreenApi *ga = green_api () ; if (ga) ga->GreenCtxDestroy (f->green) ; f->green = nullptr ; }
         cudaGetLastError () ;
     }
     delete f ;
@@ -892,6 +968,7 @@ int64_t b200_get_int (const b200_factor *f, const char *name)
     if (!strcmp (name, "top_size")) return P.top_size ;
     if (!strcmp (name, "nvlink_in_bytes")) return P.nvlink_in_values * (int64_t) f->esize ;
     if (!strcmp (name, "peers_attached")) return f->peers_attached ;
+    if (!strcmp (name, "reserved_sms")) return f->reserved_sms ;
     if (!strcmp (name, "host_registered")) { int64_t b = 0 ; for (auto &pc : f->reg_pieces) b += (int64_t) pc.second ; return b ; }
     if (!strcmp (name, "ngroups")) return P.ngroups ;
     if (!strcmp (name, "fork_lo")) return P.fork_lo ;
