@@ -89,7 +89,8 @@ b200_factor *b200_create (int64_t n, int64_t nsuper, const int64_t *super, const
  * rank 0 makes a NCCL unique id (b200_comm_unique_id, 128 bytes) and every rank an arena handle
  * (b200_peer_handle, 64 bytes); the host program carries them around by any means (torch.distributed, MPI, a
  * file); every rank then calls b200_comm_init and, for every other rank, b200_peer_attach.  After that all
- * ranks make the same sequence of b200_factor_device / b200_super_numeric_* calls.  The host Lx of those calls
+ * ranks make the same sequence of b200_upload_* / b200_factor_device / b200_super_numeric_* calls, with the same
+ * matrix (rank 0's copy is the one that is used: it goes over PCIe once and to the other GPUs over NVLink).  The host Lx of those calls
  * receives only what the rank owns, at its place in L->x: hand every rank a pointer to the SAME memory (one
  * buffer in one process, a shared mapping across processes) and it comes out complete, each rank's share over
  * its own PCIe link.  b200_download_factor likewise.  A distributed factor is not solved on the device

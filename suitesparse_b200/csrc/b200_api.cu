@@ -1215,14 +1215,33 @@ static int upload_csc (b200_factor *f, int64_t ncols, const int64_t *Ap, const i
     if (di.n < (size_t) nz && di.alloc ((size_t) nz) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     if (dx.n < (size_t) nz * f->esize && dx.alloc ((size_t) nz * f->esize) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     if (Anz && dnz.n < (size_t) ncols && dnz.alloc ((size_t) ncols) != cudaSuccess) return B200_OUT_OF_MEMORY ;
-    CK (cudaMemcpyAsync (dp.p, Ap, (size_t) (ncols + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
-    if (nz > 0)
+    // several ranks with a communicator: every rank was given the same matrix, so only rank 0 sends it over PCIe
+    // and the others receive it over NVLink (one host feeding N GPUs the same 70-350 MB at once is slower than that)
+    NcclApi *nc = (f->plan.nranks > 1 && f->comm) ? nccl_api () : nullptr ;
+    if (!nc || f->plan.rank == 0)
     {
-        int st = h2d_staged (f, di.p, Ai, (size_t) nz * sizeof (int64_t), s) ;
-        if (!st) st = h2d_staged (f, dx.p, Ax, (size_t) nz * f->esize, s) ;
-        if (st) return st ;
+        CK (cudaMemcpyAsync (dp.p, Ap, (size_t) (ncols + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
+        if (nz > 0)
+        {
+            int st = h2d_staged (f, di.p, Ai, (size_t) nz * sizeof (int64_t), s) ;
+            if (!st) st = h2d_staged (f, dx.p, Ax, (size_t) nz * f->esize, s) ;
+            if (st) return st ;
+        }
+        if (Anz && ncols > 0) CK (cudaMemcpyAsync (dnz.p, Anz, (size_t) ncols * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
     }
-    if (Anz && ncols > 0) CK (cudaMemcpyAsync (dnz.p, Anz, (size_t) ncols * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Anz") ;
+    if (nc)
+    {
+        bool ok = nc->GroupStart () == ncclSuccess ;
+        ok = ok && nc->Broadcast (dp.p, dp.p, (size_t) (ncols + 1) * 8, ncclChar, 0, f->comm, s) == ncclSuccess ;
+        if (nz > 0)
+        {
+            ok = ok && nc->Broadcast (di.p, di.p, (size_t) nz * 8, ncclChar, 0, f->comm, s) == ncclSuccess ;
+            ok = ok && nc->Broadcast (dx.p, dx.p, (size_t) nz * f->esize, ncclChar, 0, f->comm, s) == ncclSuccess ;
+        }
+        if (Anz && ncols > 0) ok = ok && nc->Broadcast (dnz.p, dnz.p, (size_t) ncols * 8, ncclChar, 0, f->comm, s) == ncclSuccess ;
+        ok = (nc->GroupEnd () == ncclSuccess) && ok ;
+        if (!ok) return B200_GPU_PROBLEM ;
+    }
     *nz_out = nz ;
     return B200_OK ;
 }
@@ -1271,8 +1290,14 @@ int b200_upload_values (b200_factor *f, const void *Ax)
     if (f->A_nz == 0) return B200_OK ;
     if (!Ax) return B200_INVALID ;
     CK (cudaEventRecord (f->ev [0], f->stream), "record") ;
-    st = h2d_staged (f, f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, f->stream) ;
-    if (st) return st ;
+    NcclApi *nc = (f->plan.nranks > 1 && f->comm) ? nccl_api () : nullptr ;      // as in upload_csc
+    if (!nc || f->plan.rank == 0)
+    {
+        st = h2d_staged (f, f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, f->stream) ;
+        if (st) return st ;
+    }
+    if (nc && nc->Broadcast (f->d_Ax.p, f->d_Ax.p, (size_t) f->A_nz * f->esize, ncclChar, 0, f->comm, f->stream) != ncclSuccess)
+        return B200_GPU_PROBLEM ;
     CK (cudaEventRecord (f->ev [1], f->stream), "record") ;
     CK (cudaStreamSynchronize (f->stream), "H2D Ax") ;
     cudaEventElapsedTime (&f->ms_h2d, f->ev [0], f->ev [1]) ;
