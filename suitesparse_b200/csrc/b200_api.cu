@@ -193,8 +193,7 @@ struct b200_factor
     bool solve_ready = false ;
     DevBuf<int32_t> d_ssmall ;
     DevBuf<SolveBlk> d_sblk ;
-    DevBuf<SolveTile256> d_stile, d_sfirst ;
-    int64_t solve_nsteps = 0 ;
+    DevBuf<SolveTile> d_stile ;
     std::vector<unsigned char> h_Ax ;       // zomplex input (Ax, Az) interleaved before the upload
     std::vector<unsigned char> h_Fx ;
     bool have_A = false, A_unpacked = false ;
@@ -914,7 +913,7 @@ void b200_destroy (b200_factor *f)
         f->d_winv.release () ; f->d_colmine.release () ; f->d_pulls.release () ; f->d_barrier.release () ;
         for (int r = 0 ; r < 32 ; r++)
             if (f->peer_ipc [r] && f->peers.p [r]) { cudaIpcCloseMemHandle (f->peers.p [r]) ; f->peers.p [r] = nullptr ; }
-        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ; f->d_sfirst.release () ;
+        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         if (f->stage) { cudaFreeHost (f->stage) ; for (auto &e : f->stage_ev) if (e) cudaEventDestroy (e) ; }
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
@@ -1670,66 +1669,49 @@ static int solve_T (b200_factor *f, int nrhs, int which)
         // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
         // over the level, one launch per step: the rows below the diagonal block spread over 256-row tiles
         // (k_solve_fwd_blk).  The backward sweep is the same list read in reverse (k_solve_bwd_blk).
-        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_STEP = 256, SOLVE_ROWS = 256 ;
+        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
         std::vector<int32_t> small ;
         std::vector<SolveBlk> blks ;
-        std::vector<SolveTile256> tiles, firsts ;
+        std::vector<SolveTile> tiles ;
         f->solve_launches.clear () ;
-        int32_t nsteps = 0 ;
         for (int lev = 0 ; lev < P.nlevels ; lev++)
         {
             const int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
             const size_t s0 = small.size () ;
-            std::vector<int32_t> big, blk_first ;
+            std::vector<int32_t> big ;
             int64_t maxcol = 0, maxbig = 0 ;
             for (int64_t q = 0 ; q < cnt ; q++)
             {
                 const int32_t sn = P.level_list [first + q] ;
                 const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
-                if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; continue ; }
-                big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ;
-                // the 64 x 64 diagonal blocks of a wide supernode, consecutively (k_solve_inv inverts each once)
-                blk_first.push_back ((int32_t) blks.size ()) ;
-                for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_NB)
-                    blks.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0), 0 }) ;
+                if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; }
+                else { big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ; }
             }
             if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
-            // the first superstep of every wide supernode: its diagonal solve (forward sweep only)
-            const size_t f0 = firsts.size () ;
-            for (size_t b = 0 ; b < big.size () ; b++)
-            {
-                const int32_t sn = big [b] ;
-                const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
-                firsts.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_STEP, nscol), 0, 0, 0, blk_first [b], 0, 0, 0 }) ;
-            }
-            if (firsts.size () > f0) f->solve_launches.push_back ({ 1, (int64_t) f0, (int64_t) (firsts.size () - f0), 0 }) ;
-            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_STEP)
+            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
             {
                 const size_t t0 = tiles.size () ;
-                for (size_t b = 0 ; b < big.size () ; b++)
+                for (int32_t sn : big)
                 {
-                    const int32_t sn = big [b] ;
                     const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
                     if (nscol <= c0) continue ;
-                    const int32_t nb = (int32_t) std::min<int64_t> (SOLVE_STEP, nscol - c0) ;
-                    const int32_t next_nb = (int32_t) std::max<int64_t> (0, std::min<int64_t> (SOLVE_STEP, nscol - (c0 + nb))) ;
-                    const int32_t blk0 = blk_first [b] + (int32_t) (c0 / SOLVE_NB), step = nsteps++ ;
+                    const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
+                    const int32_t blk = (int32_t) blks.size () ;
+                    blks.push_back ({ sn, (int32_t) c0, jb, 0 }) ;
                     const size_t tb = tiles.size () ;
-                    for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_ROWS)
-                        tiles.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0,
-                            blk0, step, (r == c0 + nb) ? next_nb : 0, 0 }) ;
-                    // a superstep with nothing below it still needs its diagonal solve in the backward sweep
-                    if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, nb, (int32_t) (c0 + nb), 0, 0, blk0, step, 0, 0 }) ;
+                    for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
+                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
+                    // a block with nothing below it still needs its diagonal solve
+                    if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
+                    tiles [tb].writer = 1 ;
                     for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
                 }
                 f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
             }
         }
-        f->solve_nsteps = nsteps ;
         bool ok = f->d_ssmall.upload (small, s) == cudaSuccess ;
         ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
         ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
-        ok = ok && f->d_sfirst.upload (firsts, s) == cudaSuccess ;
         ok = ok && f->d_solveW.alloc (blks.size () * (size_t) (SOLVE_WLD * SOLVE_WLD) * sizeof (XT)) == cudaSuccess ;
         if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
         CK (cudaStreamSynchronize (s), "solve plan upload") ;
@@ -1745,9 +1727,9 @@ static int solve_T (b200_factor *f, int nrhs, int which)
             k_solve_inv<T><<<(unsigned) nblk, 256, solve_inv_smem_bytes<T> (), s>>> (f->d_sblk.p, f->d_pi.p, f->d_px.p, Lx, Winv) ;
             f->solve_w_valid = true ;
         }
-        if (f->d_solve_cnt.n < (size_t) f->solve_nsteps * (size_t) nrhs)
+        if (f->d_solve_cnt.n < nblk * (size_t) nrhs)
         {
-            if (f->d_solve_cnt.alloc ((size_t) f->solve_nsteps * (size_t) nrhs) != cudaSuccess) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
+            if (f->d_solve_cnt.alloc (nblk * (size_t) nrhs) != cudaSuccess) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
             CK (cudaMemsetAsync (f->d_solve_cnt.p, 0, f->d_solve_cnt.bytes (), s), "solve counters") ;
         }
     }
@@ -1783,21 +1765,13 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                     k_solve_bwd<T><<<grid, 128, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, X, P.n, nrhs, (int) L.maxcol) ;
             }
-            else if (L.kind == 1)
-            {
-                // the diagonal solve of every wide supernode's first superstep (the later ones are done by the tile
-                // kernel of the superstep before them); nothing to do on the way back
-                if (pass == 0)
-                    k_solve_diag_fwd<T><<<grid, 256, 0, s>>> (f->d_sfirst.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                        Lx, Winv, X, Y, P.n, nrhs) ;
-            }
             else
             {
                 if (pass == 0)
-                    k_solve_fwd256<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                    k_solve_fwd_blk<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, Winv, X, Y, P.n, nrhs) ;
                 else
-                    k_solve_bwd256<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                    k_solve_bwd_blk<T><<<grid, 256, 0, s>>> (f->d_stile.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
             }
             if (f->profile) cudaEventRecord (f->prof_ev [nev++], s) ;

@@ -1896,222 +1896,6 @@ __global__ void __launch_bounds__ (256) k_pull_add (const PullSeg *__restrict__ 
     }
 }
 
-// ---------------------------------------------------------------------------------------------
-// wide supernodes in the solve, 256 columns (4 diagonal blocks) per launch
-// ---------------------------------------------------------------------------------------------
-
-// One 256-row tile of the rows below a 256-column "superstep" [c0, c0+nb) of a wide supernode.  blk0 = index of
-// the superstep's first 64 x 64 inverse in Winv (the blocks of a supernode are consecutive); step = the
-// superstep's number (its counter in the backward sweep); next_nb > 0 marks the tile that holds the rows of
-// the NEXT superstep's diagonal block (forward: that CTA goes straight on and solves it).
-struct SolveTile256 { int32_t s, c0, nb, r0, nrows, ntiles, blk0, step, next_nb, pad ; } ;
-
-// Forward diagonal solve of a superstep, by a CTA of 256 threads: xs [0..nb) (shared) holds the right-hand side of
-// the nb unknowns and is destroyed; ys [0..nb) receives y = L_blk \ xs.  Four sub-steps of 64: y_q = W_q * x_q with
-// the pre-inverted diagonal block, then the rest of the superstep's rows take  x -= L (rows, block q) * y_q.
-template <typename T, typename XT>
-__device__ __forceinline__ void solve_diag256_fwd (const T *__restrict__ Lsn, int64_t nsrow, int c0, int nb,
-    const XT *__restrict__ W0, XT *xs, XT *ys)
-{
-    const int tid = threadIdx.x ;
-    const XT zero = from_real<XT> (0) ;
-    for (int q0 = 0 ; q0 < nb ; q0 += 64)
-    {
-        const int jb = min (64, nb - q0) ;
-        const XT *W = W0 + (int64_t) (q0 >> 6) * (SOLVE_WLD * SOLVE_WLD) ;
-        {
-            const int r = tid >> 2, part = tid & 3 ;
-            XT acc = zero ;
-            #pragma unroll
-            for (int k = 0 ; k < 16 ; k++)
-            {
-                const int c = part + 4 * k ;
-                if (c <= r && c < jb && r < jb) acc += W [r + c * SOLVE_WLD] * xs [q0 + c] ;
-            }
-            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-            if (part == 0 && r < jb) ys [q0 + r] = acc ;
-        }
-        __syncthreads () ;
-        const int i = q0 + jb + tid ;           // a later unknown of the superstep
-        if (i < nb)
-        {
-            const T *Lr = Lsn + (c0 + i) + (int64_t) (c0 + q0) * nsrow ;
-            XT acc = zero ;
-            for (int j = 0 ; j < jb ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * ys [q0 + j] ;
-            xs [i] -= acc ;
-        }
-        __syncthreads () ;
-    }
-}
-
-// First superstep of every wide supernode of a level: y = L_blk \ x_blk, into Y.
-template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_diag_fwd (const SolveTile256 *__restrict__ firsts,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
-    const typename solve_x<T>::type *__restrict__ X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
-{
-    typedef typename solve_x<T>::type XT ;
-    __shared__ XT xs [256], ys [256] ;
-    const SolveTile256 t = firsts [blockIdx.x] ;
-    const int64_t k1 = super [t.s], nsrow = pi [t.s+1] - pi [t.s] ;
-    const T *Lsn = Lx + px [t.s] ;
-    const int tid = threadIdx.x ;
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
-    {
-        if (tid < t.nb) xs [tid] = X [(int64_t) rhs * n + k1 + t.c0 + tid] ;
-        __syncthreads () ;
-        solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
-        if (tid < t.nb) Y [(int64_t) rhs * n + k1 + t.c0 + tid] = ys [tid] ;
-        __syncthreads () ;
-    }
-}
-
-// Forward superstep: every tile subtracts L (rows, superstep) * y from the rows it owns (y = Y of the superstep,
-// written by the previous launch).  Rows inside the supernode's own columns are touched by this CTA alone; rows
-// below it belong to ancestors and are shared with the siblings of the level: atomics.  The tile that holds the
-// rows of the next superstep's diagonal block keeps them in shared memory and solves that block at once, so the
-// next launch finds its y in Y: ONE launch per 256 columns of a wide supernode.
-template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
-    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
-{
-    typedef typename solve_x<T>::type XT ;
-    __shared__ XT yb [256], xs [256], ys [256] ;
-    const SolveTile256 t = tiles [blockIdx.x] ;
-    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
-    const T *Lsn = Lx + px [t.s] ;
-    const int tid = threadIdx.x, row = t.r0 + tid ;
-    const XT zero = from_real<XT> (0) ;
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
-    {
-        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
-        yb [tid] = (tid < t.nb) ? y [k1 + t.c0 + tid] : zero ;
-        __syncthreads () ;
-        XT xnew = zero ;
-        if (tid < t.nrows)
-        {
-            const T *Lr = Lsn + row + (int64_t) t.c0 * nsrow ;
-            XT acc = zero ;
-            #pragma unroll 8
-            for (int j = 0 ; j < t.nb ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yb [j] ;
-            if (row < nscol)
-            {
-                xnew = x [k1 + row] - acc ;          // a later unknown of this supernode: ours alone
-                x [k1 + row] = xnew ;
-            }
-            else atomic_sub (x + Ls [psi + row], acc) ;
-        }
-        if (t.next_nb > 0)
-        {
-            // the next superstep's unknowns are the first next_nb rows of this tile
-            xs [tid] = (tid < t.next_nb) ? xnew : zero ;
-            __syncthreads () ;
-            solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
-                Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
-            if (tid < t.next_nb) y [k1 + t.c0 + t.nb + tid] = ys [tid] ;
-        }
-        __syncthreads () ;
-    }
-}
-
-// Backward superstep: every tile subtracts L (rows, superstep)^H * x [rows] from Y of the superstep (atomics); the
-// CTA that finishes last (counter + fence) then solves the diagonal block backwards, four sub-steps of 64 from the
-// bottom up:  x_q = W_q^H * y_q ;  y_q' -= L (block q, block q')^H * x_q  for the blocks q' above.
-template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_bwd256 (const SolveTile256 *__restrict__ tiles,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
-    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
-{
-    typedef typename solve_x<T>::type XT ;
-    __shared__ XT xr [256], yb [256], xq [64] ;
-    __shared__ int is_last ;
-    const SolveTile256 t = tiles [blockIdx.x] ;
-    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
-    const T *Lsn = Lx + px [t.s] ;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
-    const XT zero = from_real<XT> (0) ;
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
-    {
-        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
-        if (tid < t.nrows)
-        {
-            const int row = t.r0 + tid ;
-            xr [tid] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
-        }
-        __syncthreads () ;
-        if (t.nrows > 0)
-        {
-            // warp w takes the columns w, w + 8, ...; its lanes run down the tile's rows 32 at a time
-            const T *Lbase = Lsn + t.r0 + (int64_t) t.c0 * nsrow ;
-            for (int jc = warp ; jc < t.nb ; jc += 8)
-            {
-                const T *Lj = Lbase + (int64_t) jc * nsrow ;
-                XT acc = zero ;
-                #pragma unroll
-                for (int k = 0 ; k < 8 ; k++)
-                {
-                    const int r = lane + 32 * k ;
-                    if (r < t.nrows) acc += mulc (xr [r], cvt<XT> (Lj [r])) ;
-                }
-                for (int o = 16 ; o > 0 ; o >>= 1) acc += shfl_xor_ (0xffffffffu, acc, o) ;
-                if (lane == 0) atomic_sub (y + k1 + t.c0 + jc, acc) ;
-            }
-        }
-        __threadfence () ;
-        __syncthreads () ;
-        if (tid == 0)
-        {
-            int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
-            const int done = atomicAdd (cnt, 1) ;
-            is_last = (done == t.ntiles - 1) ;
-            if (is_last) *cnt = 0 ;
-        }
-        __syncthreads () ;
-        if (is_last)
-        {
-            __threadfence () ;
-            yb [tid] = (tid < t.nb) ? ldcg_ (y + k1 + t.c0 + tid) : zero ;
-            __syncthreads () ;
-            const int nq = (t.nb + 63) >> 6 ;
-            for (int q = nq - 1 ; q >= 0 ; q--)
-            {
-                const int q0 = q * 64, jb = min (64, t.nb - q0) ;
-                const XT *W = Winv + (int64_t) (t.blk0 + q) * (SOLVE_WLD * SOLVE_WLD) ;
-                {
-                    // x_c = sum_{r >= c} conj (W (r,c)) * y_r : thread (c, part) walks down column c of W
-                    const int c = tid >> 2, part = tid & 3 ;
-                    XT acc = zero ;
-                    #pragma unroll
-                    for (int k = 0 ; k < 16 ; k++)
-                    {
-                        const int r = part + 4 * k ;
-                        if (r >= c && r < jb && c < jb) acc += mulc (yb [q0 + r], W [r + c * SOLVE_WLD]) ;
-                    }
-                    acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-                    acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-                    if (part == 0 && c < jb) { xq [c] = acc ; x [k1 + t.c0 + q0 + c] = acc ; }
-                }
-                __syncthreads () ;
-                // the blocks above: y_c -= sum_r conj (L (block q row r, column c)) * x_q [r], one thread per column
-                if (tid < q0)
-                {
-                    const T *Lc = Lsn + (t.c0 + q0) + (int64_t) (t.c0 + tid) * nsrow ;
-                    XT acc = zero ;
-                    for (int r = 0 ; r < jb ; r++) acc += mulc (xq [r], cvt<XT> (Lc [r])) ;
-                    yb [tid] -= acc ;
-                }
-                __syncthreads () ;
-            }
-        }
-        __syncthreads () ;
-    }
-}
-
 // After a forward sweep on its own (cholmod_super_lsolve without the ltsolve that normally follows): the
 // results of the wide supernodes' columns are in Y, everything else in X; gather them into X.
 template <typename XT>
