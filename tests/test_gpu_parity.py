@@ -295,3 +295,35 @@ def test_factor_values_at_benchmark_sizes(kind, size, single, tol_l, tol_r):
     err, res = _full_size(kind, size, single)
     assert err <= tol_l, err
     assert res <= tol_r, res
+
+
+@pytest.mark.parametrize("kind,size,ordering", [("lap3d7", 40, refd.CHOLMOD_METIS), ("lap2d9", 200, refd.CHOLMOD_METIS)])
+def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering):
+    """b200_solve_sweep: the forward sweep alone equals the reference's L\\b on its own factor (the plain-C
+    restatement's triangular solve), and forward followed by backward equals the two-sided solve; several
+    right-hand sides, a factor with supernodes wider than one 256-column superstep."""
+    c = get_case(kind, size, ordering)
+    F = b200.Factor(c.sym, device=0)
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
+    assert st == b200.OK
+    rng = np.random.default_rng(11)
+    B = np.asfortranarray(rng.standard_normal((c.n, 3)))
+    X = F.solve(B)
+    Y = F.solve_sweep(1, B)
+    Z = F.solve_sweep(2, Y)
+    assert np.max(np.abs(Z - X)) <= 1e-12 * np.max(np.abs(X))
+    # L * Y = B, checked with a sparse matrix built from the supernodal factor
+    import scipy.sparse as sp
+    sup, pi, px, Ls = c.sym["super"], c.sym["pi"], c.sym["px"], c.sym["s"]
+    rows, cols, vals = [], [], []
+    for s_ in range(c.sym["nsuper"]):
+        k1, k2 = sup[s_], sup[s_ + 1]
+        nsrow = pi[s_ + 1] - pi[s_]
+        blk = Lx[px[s_]:px[s_ + 1]].reshape(k2 - k1, nsrow).T          # nsrow x nscol
+        r = Ls[pi[s_]:pi[s_ + 1]]
+        for j in range(k2 - k1):
+            rows.append(r[j:]); cols.append(np.full(nsrow - j, k1 + j)); vals.append(blk[j:, j])
+    L = sp.csc_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(c.n, c.n))
+    assert np.max(np.abs(L @ Y - B)) <= 1e-11 * np.max(np.abs(B))
+    assert np.max(np.abs(L.T @ Z - Y)) <= 1e-11 * max(1.0, np.max(np.abs(Y)))
+    F.close()
