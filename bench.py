@@ -112,14 +112,25 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def ncu_traffic():
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
-    (profiles/r01_ncu_full_k_upd_dmma.json: mean of dram__bytes_read.sum + dram__bytes_write.sum over the
-    captured launches).  A number taken under a profiler, reported only as the traffic figure."""
+def ncu_traffic(avg_launch_ms):
+    """DRAM bytes per launch of the dominant kernel, from the committed `ncu --set full` capture of the benchmarked
+    workload (profiles/r02_ncu_full_dmma_root.json: 22 launches of k_upd_dmma<128,64> at the root of config 2, the
+    multi-thousand-tile descendant and look-ahead updates that carry the step among them).  The capture holds some
+    launches, not all 1355, so the figure is the kernel's DRAM rate over the capture (bytes read + written / time)
+    times the average launch duration measured live -- per launch, like `achieved`.  A number taken under a
+    profiler, reported only as the traffic figure."""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_full_k_upd_dmma.json")))
-        vals = [(float(r["dram__bytes_read.sum"]) + float(r["dram__bytes_write.sum"])) * 1e6 for r in d["launches"]]
-        return float(np.mean(vals)) if vals else None
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_full_dmma_root.json")))
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tscale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}
+        nbytes = ms = 0.0
+        for r in d["launches"]:
+            rd, wr, du = r.get("dram_read"), r.get("dram_write"), r.get("duration")
+            if not all(isinstance(v, float) and v == v for v in (rd, wr, du)):
+                continue
+            nbytes += rd * scale.get(r.get("dram_read_unit", "byte"), 1.0) + wr * scale.get(r.get("dram_write_unit", "byte"), 1.0)
+            ms += du * tscale.get(r.get("duration_unit", "ms"), 1.0)
+        return nbytes / ms * avg_launch_ms if ms > 0 else None
     except Exception:
         return None
 
@@ -429,7 +440,7 @@ def main():
     ach = (dk["gflop"] / 1e3) / (dk["ms"] * 1e-3) if dk["ms"] > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "k_upd_dmma<%s>" % ("128,64,32,64" if dom == "upd_dmma128" else "64,64,32,32"),
                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak > 0 else None,
-                "traffic": ncu_traffic(),
+                "traffic": ncu_traffic(dk["ms"] / max(1, dk["launches"])),
                 "peak_burst": peak_burst, "peak_sustained": peak_sustained,
                 "frac_of_sustained": ach / peak_sustained if peak_sustained > 0 else None,
                 "peak_source": "FP64 DMMA peak measured live by b200_dmma_peak_tflops (MEASURED_PEAKS.json has no FP64 "
