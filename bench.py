@@ -266,9 +266,10 @@ def main():
     # the caller's ONE host L->x.  With several ranks it is a shared mapping: every rank copies the part of the
     # factor it owns into it over its own PCIe link.
     shm_path = None
+    Lx_host = None
     if world == 1:
         Lx_host = np.empty(sym["xsize"], dtype=fdtype)
-    else:
+    elif not args.no_e2e:
         shm_path = "/dev/shm/b200_bench_%s.bin" % os.environ.get("MASTER_PORT", "0")
         if rank == 0:
             Lx_host = np.memmap(shm_path, dtype=fdtype, mode="w+", shape=(sym["xsize"],))
@@ -474,17 +475,21 @@ def main():
     bvec = matrices.rhs(sym["n"])
     xs = np.empty(sym["n"])
     # several ranks: no rank holds the whole factor; the assembled host L->x goes into a one-GPU context
-    G = F if world == 1 else b200.Factor(sym, dtype=fdtype, device=local)
-    if world > 1:
-        assert np.all(np.isfinite(Lx_host[::4097])), "the ranks' copy-outs left holes in L->x"
-        G.upload_factor(np.array(Lx_host))
-    xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
-    solve_first_ms = G.getd("ms_solve")     # builds the solve schedule and inverts the wide supernodes' diagonal blocks
-    xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
-    check = {"solve_ms": G.getd("ms_solve"), "solve_first_ms": solve_first_ms, "scaled_residual": ref.resid(xs, bvec),
-             "tolerance": 1e-5 if args.single else 1e-12}
-    if world > 1:
-        G.close()
+    if world > 1 and Lx_host is None:
+        # --no-e2e with several ranks: the factor never left the GPUs, and no rank holds all of it
+        check = {"skipped": "no host copy of L->x in this run (--no-e2e): the solve check needs the assembled factor"}
+    else:
+        G = F if world == 1 else b200.Factor(sym, dtype=fdtype, device=local)
+        if world > 1:
+            assert np.all(np.isfinite(Lx_host[::4097])), "the ranks' copy-outs left holes in L->x"
+            G.upload_factor(np.array(Lx_host))
+        xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
+        solve_first_ms = G.getd("ms_solve")     # builds the solve schedule and inverts the wide supernodes' diagonal blocks
+        xs[sym["Perm"]] = G.solve(bvec[sym["Perm"]])
+        check = {"solve_ms": G.getd("ms_solve"), "solve_first_ms": solve_first_ms, "scaled_residual": ref.resid(xs, bvec),
+                 "tolerance": 1e-5 if args.single else 1e-12}
+        if world > 1:
+            G.close()
 
     # ---- CPU baseline: the reference's CPU path on the workload itself, rank 0, N = 1 only; its factor is the
     # full-size parity check of ours (north_star: max|dL|/max|L| <= 1e-10) ----------------------------------
@@ -529,7 +534,8 @@ def main():
     del Lx_host
     if world > 1:
         dist.barrier()
-        os.unlink(shm_path)
+        if shm_path and os.path.exists(shm_path):
+            os.unlink(shm_path)
         dist.destroy_process_group()
 
 
