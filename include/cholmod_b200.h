@@ -131,7 +131,11 @@ void b200_destroy (b200_factor *f) ;
 /* Integer property of the context by name: "n", "nsuper", "xsize", "nlevels", "npairs", "npairs_gemm" (pairs
  * with rows below the ancestor's columns: the reference's dgemm calls), "nsuper_trsm" (its dtrsm calls),
  * "relmap_len", "ntiles", "nlaunches", "device_bytes", "device", "kernel_launches" (kernels launched
- * by the last factorization), "ngpus".  Returns -1 for an unknown name. */
+ * by the last factorization), "ngpus", "rank"; for a distributed context "dxsize" (values in this rank's arena),
+ * "top_size" (of which top separators), "npulls", "nvlink_in_bytes" (what one factorization brings in over NVLink),
+ * "peers_attached", "reserved_sms" (SMs the throughput streams stay off), "host_registered" (bytes of the caller's
+ * L->x this context has page-locked); "device_symbolic" (1: pairs and relative maps were built on the device).
+ * Returns -1 for an unknown name. */
 int64_t b200_get_int (const b200_factor *f, const char *name) ;
 
 /* Floating-point property by name: "flops_syrk", "flops_gemm", "flops_potrf", "flops_trsm" (the flops of the
@@ -280,7 +284,8 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
  * solves) with CUDA events and accumulates device time per kernel kind: "ms_kind<k>", "launches_kind<k>" and the
  * algorithmic "flops_kind<k>" in b200_get_double / b200_get_int, k = 0 SIMT update, 1 tensor update 64x64,
  * 2 tensor update 128x64, 3..5 POTRF of <= 16 / 32 / 64 columns, 6 TRSM by substitution, 7..8 TRSM through the
- * 32 / 64-wide inverse, 9 whole small supernodes; "ms_launch<i>" / "ms_launch_start<i>" are the duration and
+ * 32 / 64-wide inverse, 9 whole small supernodes, 10 whole tiny supernodes (one thread each), 11 tiny updates (one
+ * thread each); "ms_launch<i>" / "ms_launch_start<i>" are the duration and
  * start time of launch i of the plan, in the order of the "launches" table of b200_plan_export; "ms_level_end<l>"
  * when etree level l was finished; "ms_solve_part0..3" the solve's small-forward, wide-forward, small-backward
  * and wide-backward parts.  Profiling serialises nothing but adds event overhead: never time a benchmark step

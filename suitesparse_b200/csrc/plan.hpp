@@ -198,9 +198,13 @@ struct Plan
 } ;
 
 // Builds the plan.  Returns 0, or a negative B200_* status (invalid input / too large).
-// use_dmma = false (single precision) routes every update through the SIMT kernel class.
-// nranks > 1 builds rank `rank`'s share of the distributed plan: the same launch structure on every rank,
-// each launch holding only the blocks / tiles that rank owns, plus the K_BCAST launches all ranks share.
+// use_dmma = false (single precision): no inverse-based panel solves, no near / far split.
+// nranks > 1 builds rank `rank`'s share of the distributed plan (build_dist in plan.cpp): its own subtrees, its
+// contribution blocks, the pulls of the blocks it owns, and for the top separators the same launch structure on
+// every rank, each launch holding only the blocks / tiles that rank owns, plus the K_BARRIER and K_BCAST launches
+// all ranks share.
+// host_relmap = false: only the offsets of the relative maps are computed; the maps themselves are built on the
+// device (symbolic.cuh).
 // trunc_s >= 0 (distributed plans only): the plan of the not-positive-definite case -- everything up to supernode
 // trunc_s as usual, trunc_s itself for its first trunc_ncol columns, nothing after it.
 int build_plan (int64_t n, int64_t nsuper, const int64_t *super, const int64_t *pi, const int64_t *px,
