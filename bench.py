@@ -135,10 +135,12 @@ def ncu_traffic(avg_launch_ms):
         return None
 
 
-def reference_config(desc, sym):
-    """The `config` both arms print: the workload, named and sized the same way."""
+def reference_config(desc, sym, esize=8):
+    """The `config` both arms print, key for key: the workload, named and sized the same way, and the cache rule of
+    the timing (every step rewrites all of L->x, which is far larger than any cache on either side)."""
     return {"workload": desc, "n": int(sym["n"]), "nsuper": int(sym["nsuper"]), "fl": sym["fl"], "lnz": sym["lnz"],
-            "xsize": int(sym["xsize"])}
+            "xsize": int(sym["xsize"]),
+            "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * esize / 1e9)}
 
 
 def run_reference(args, gpu_branch=False):
@@ -515,9 +517,9 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32" if args.single else "f64", "data": "synthetic",
-        "config": {**reference_config(desc, sym), "npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
+        "config": reference_config(desc, sym, np.dtype(fdtype).itemsize),
+        "plan": {"npairs": F.geti("npairs"), "nlevels": F.geti("nlevels"),
                    "relmap_len": F.geti("relmap_len"), "device_bytes": F.geti("device_bytes"),
-                   "l2": "inputs larger than L2 (L->x = %.2f GB is rewritten every step)" % (sym["xsize"] * 8 / 1e9),
                    "parallelism": ("one factorization over %d GPUs: etree subtrees owned per GPU, their contribution blocks "
                                    "pulled over NVLink by the owners of the top separators' blocks, top separators 1-D "
                                    "block cyclic (%d NCCL calls per step, %d top supernodes), every GPU copies its share of "
