@@ -1896,6 +1896,263 @@ __global__ void __launch_bounds__ (256) k_pull_add (const PullSeg *__restrict__ 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// wide supernodes in the solve, 256 columns (4 diagonal blocks) per launch  (CHOLMOD_B200_SOLVE256)
+// ---------------------------------------------------------------------------------------------
+
+// One tile of the rows below a 256-column "superstep" [c0, c0+nb) of a wide supernode (64 rows in the forward
+// sweep, 256 in the backward sweep).  blk0 = index of the superstep's first 64 x 64 inverse in Winv (the blocks of a
+// supernode are consecutive); step = the superstep's number (its counters); ntiles = tiles of the superstep;
+// next_nb > 0 (forward) marks a tile that holds rows of the NEXT superstep's diagonal block: the last of those
+// tiles to finish solves that block at once, so a superstep costs one launch.
+struct SolveTile256 { int32_t s, c0, nb, r0, nrows, ntiles, blk0, step, next_nb, pad ; } ;
+
+// Forward diagonal solve of a superstep by a CTA of 256 threads: xs [0..nb) (shared) holds the right-hand side and
+// is destroyed; ys [0..nb) receives y = L_blk \ xs.  Four sub-steps of 64: y_q = W_q * x_q with the pre-inverted
+// diagonal block (4 threads per row), then the later unknowns take x -= L (rows, block q) * y_q, 4 threads per row
+// with 16 independent loads each.
+template <typename T, typename XT>
+__device__ __forceinline__ void solve_diag256_fwd (const T *__restrict__ Lsn, int64_t nsrow, int c0, int nb,
+    const XT *__restrict__ W0, XT *xs, XT *ys)
+{
+    const int tid = threadIdx.x, r4 = tid >> 2, part = tid & 3 ;
+    const XT zero = from_real<XT> (0) ;
+    for (int q0 = 0 ; q0 < nb ; q0 += 64)
+    {
+        const int jb = min (64, nb - q0) ;
+        const XT *W = W0 + (int64_t) (q0 >> 6) * (SOLVE_WLD * SOLVE_WLD) ;
+        {
+            XT acc = zero ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++)
+            {
+                const int c = part + 4 * k ;
+                if (c <= r4 && r4 < jb) acc += W [r4 + c * SOLVE_WLD] * xs [q0 + c] ;
+            }
+            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+            if (part == 0 && r4 < jb) ys [q0 + r4] = acc ;
+        }
+        __syncthreads () ;
+        for (int base = q0 + jb ; base < nb ; base += 64)
+        {
+            const int i = base + r4 ;
+            XT acc = zero ;
+            if (i < nb)
+            {
+                const T *Lr = Lsn + (c0 + i) + (int64_t) (c0 + q0 + 16 * part) * nsrow ;
+                #pragma unroll
+                for (int j = 0 ; j < 16 ; j++)
+                    if (16 * part + j < jb) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * ys [q0 + 16 * part + j] ;
+            }
+            acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+            acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+            if (part == 0 && i < nb) xs [i] -= acc ;
+        }
+        __syncthreads () ;
+    }
+}
+
+// First superstep of every wide supernode of a level: y = L_blk \ x_blk, into Y.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_diag_fwd256 (const SolveTile256 *__restrict__ firsts,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    const typename solve_x<T>::type *__restrict__ X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
+{
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT xs [256], ys [256] ;
+    const SolveTile256 t = firsts [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nsrow = pi [t.s+1] - pi [t.s] ;
+    const T *Lsn = Lx + px [t.s] ;
+    const int tid = threadIdx.x ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        xs [tid] = (tid < t.nb) ? X [(int64_t) rhs * n + k1 + t.c0 + tid] : from_real<XT> (0) ;
+        __syncthreads () ;
+        solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
+        if (tid < t.nb) Y [(int64_t) rhs * n + k1 + t.c0 + tid] = ys [tid] ;
+        __syncthreads () ;
+    }
+}
+
+// Forward superstep, one CTA per 64 rows below it: x [rows] -= L (rows, superstep) * y, four threads per row (one per
+// 64-column block of the superstep, 16 independent loads per batch).  Rows inside the supernode's own columns are
+// touched by this CTA alone; rows below it belong to ancestors and are shared with the siblings of the level:
+// atomics.  The (up to four) tiles that hold the rows of the next superstep's diagonal block count themselves off;
+// the last one solves that block, so the next launch finds its y in Y.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
+{
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT yb [256], xs [256], ys [256] ;
+    __shared__ int is_last ;
+    const SolveTile256 t = tiles [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
+    const T *Lsn = Lx + px [t.s] ;
+    const int tid = threadIdx.x, r4 = tid >> 2, part = tid & 3, row = t.r0 + r4 ;
+    const XT zero = from_real<XT> (0) ;
+    const int jq = min (64, t.nb - 64 * part) ;         // columns of this thread's block of the superstep (may be <= 0)
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
+        yb [tid] = (tid < t.nb) ? y [k1 + t.c0 + tid] : zero ;
+        __syncthreads () ;
+        XT acc = zero ;
+        if (r4 < t.nrows && jq > 0)
+        {
+            const T *Lr = Lsn + row + (int64_t) (t.c0 + 64 * part) * nsrow ;
+            const XT *yq = yb + 64 * part ;
+            #pragma unroll 16
+            for (int j = 0 ; j < 64 ; j++)
+                if (j < jq) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
+        }
+        acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+        acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+        if (part == 0 && r4 < t.nrows)
+        {
+            if (row < nscol) x [k1 + row] -= acc ;       // a later unknown of this supernode: ours alone
+            else atomic_sub (x + Ls [psi + row], acc) ;
+        }
+        if (t.next_nb > 0)
+        {
+            __threadfence () ;
+            __syncthreads () ;
+            if (tid == 0)
+            {
+                int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
+                const int ndiag = (t.next_nb + 63) >> 6 ;
+                const int done = atomicAdd (cnt, 1) ;
+                is_last = (done == ndiag - 1) ;
+                if (is_last) *cnt = 0 ;
+            }
+            __syncthreads () ;
+            if (is_last)
+            {
+                __threadfence () ;
+                xs [tid] = (tid < t.next_nb) ? ldcg_ (x + k1 + t.c0 + t.nb + tid) : zero ;
+                __syncthreads () ;
+                solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
+                    Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
+                if (tid < t.next_nb) y [k1 + t.c0 + t.nb + tid] = ys [tid] ;
+            }
+        }
+        __syncthreads () ;
+    }
+}
+
+// Backward superstep, one CTA per 256 rows below it: Y_blk -= L (rows, superstep)^H * x [rows] (atomics; a warp takes
+// 32 columns, four at a time, its lanes run down the rows: 32 independent loads per batch); the CTA that finishes
+// last then solves the diagonal block backwards, four sub-steps of 64 from the bottom up:
+// x_q = W_q^H * y_q ;  y_c -= L (block q, column c)^H * x_q for the columns c of the blocks above (4 threads per column).
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_bwd256 (const SolveTile256 *__restrict__ tiles,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
+{
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT xr [256], yb [256], xq [64] ;
+    __shared__ int is_last ;
+    const SolveTile256 t = tiles [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
+    const T *Lsn = Lx + px [t.s] ;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r4 = tid >> 2, part = tid & 3 ;
+    const XT zero = from_real<XT> (0) ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
+        if (tid < t.nrows)
+        {
+            const int row = t.r0 + tid ;
+            xr [tid] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
+        }
+        else xr [tid] = zero ;
+        __syncthreads () ;
+        if (t.nrows > 0)
+        {
+            const T *Lbase = Lsn + t.r0 + (int64_t) t.c0 * nsrow ;
+            for (int g = 0 ; g < 8 ; g++)
+            {
+                const int c = warp * 32 + 4 * g ;
+                if (c >= t.nb) break ;
+                XT acc [4] = { zero, zero, zero, zero } ;
+                #pragma unroll
+                for (int k = 0 ; k < 8 ; k++)
+                {
+                    const int r = lane + 32 * k ;
+                    if (r < t.nrows)
+                    {
+                        const XT xv = xr [r] ;
+                        #pragma unroll
+                        for (int u = 0 ; u < 4 ; u++)
+                            if (c + u < t.nb) acc [u] += mulc (xv, cvt<XT> (Lbase [(int64_t) (c + u) * nsrow + r])) ;
+                    }
+                }
+                #pragma unroll
+                for (int u = 0 ; u < 4 ; u++)
+                {
+                    for (int o = 16 ; o > 0 ; o >>= 1) acc [u] += shfl_xor_ (0xffffffffu, acc [u], o) ;
+                    if (lane == 0 && c + u < t.nb) atomic_sub (y + k1 + t.c0 + c + u, acc [u]) ;
+                }
+            }
+        }
+        __threadfence () ;
+        __syncthreads () ;
+        if (tid == 0)
+        {
+            int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
+            const int done = atomicAdd (cnt, 1) ;
+            is_last = (done == t.ntiles - 1) ;
+            if (is_last) *cnt = 0 ;
+        }
+        __syncthreads () ;
+        if (is_last)
+        {
+            __threadfence () ;
+            yb [tid] = (tid < t.nb) ? ldcg_ (y + k1 + t.c0 + tid) : zero ;
+            __syncthreads () ;
+            const int nq = (t.nb + 63) >> 6 ;
+            for (int q = nq - 1 ; q >= 0 ; q--)
+            {
+                const int q0 = q * 64, jb = min (64, t.nb - q0) ;
+                const XT *W = Winv + (int64_t) (t.blk0 + q) * (SOLVE_WLD * SOLVE_WLD) ;
+                {
+                    // x_c = sum_{r >= c} conj (W (r,c)) * y_r : thread (c, part) walks down column c of W
+                    XT acc = zero ;
+                    #pragma unroll
+                    for (int k = 0 ; k < 16 ; k++)
+                    {
+                        const int r = part + 4 * k ;
+                        if (r >= r4 && r < jb && r4 < jb) acc += mulc (yb [q0 + r], W [r + r4 * SOLVE_WLD]) ;
+                    }
+                    acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+                    acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+                    if (part == 0 && r4 < jb) { xq [r4] = acc ; x [k1 + t.c0 + q0 + r4] = acc ; }
+                }
+                __syncthreads () ;
+                for (int base = 0 ; base < q0 ; base += 64)
+                {
+                    const int c = base + r4 ;           // a column of a block above (c < q0 always: q0 is a multiple of 64)
+                    const T *Lc = Lsn + (t.c0 + q0 + 16 * part) + (int64_t) (t.c0 + c) * nsrow ;
+                    XT acc = zero ;
+                    #pragma unroll
+                    for (int r = 0 ; r < 16 ; r++)
+                        if (16 * part + r < jb) acc += mulc (xq [16 * part + r], cvt<XT> (Lc [r])) ;
+                    acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+                    acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+                    if (part == 0) yb [c] -= acc ;
+                }
+                __syncthreads () ;
+            }
+        }
+        __syncthreads () ;
+    }
+}
+
 // After a forward sweep on its own (cholmod_super_lsolve without the ltsolve that normally follows): the
 // results of the wide supernodes' columns are in Y, everything else in X; gather them into X.
 template <typename XT>
