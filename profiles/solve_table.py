@@ -29,5 +29,5 @@ F.seti("profile", 1)
 F.solve(b)
 parts = {k: (round(F.getd("ms_solve_part%d" % i), 3), int(F.getd("solve_launches%d" % i)))
          for i, k in enumerate(["small_fwd", "wide_fwd", "small_bwd", "wide_bwd"])}
-print(json.dumps(dict(workload=name, nrhs=nrhs, solve_ms=ts, profiled_ms=F.getd("ms_solve"), parts_ms_launches=parts,
+print(json.dumps(dict(workload=name, nrhs=nrhs, solve_cols=int(F.getd("solve_cols")), solve_ms=ts, profiled_ms=F.getd("ms_solve"), parts_ms_launches=parts,
                       xsize_gb=sym["xsize"] * 8 / 1e9)))

@@ -15,6 +15,7 @@
 #include <thread>
 #include <algorithm>
 #include <utility>
+#include <map>
 #include <dlfcn.h>
 #include <nccl.h>       // types only: libnccl is dlopen'ed, so a single-GPU user needs no NCCL at all
 #include <cuda.h>       // types only: the few driver entry points of the green-context API are dlsym'ed
@@ -188,12 +189,16 @@ struct b200_factor
     double ms_solve_part [4] = {} ;         // profile mode: small fwd, wide fwd, small bwd, wide bwd
     int64_t solve_launch_count [4] = {} ;            // d_solveW belongs to the factor values now in d_Lx
     // solve schedule (built at the first solve)
-    struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;  // kind 0: one CTA per supernode, 2: block step of the wide ones
+    // kind 0: one CTA per supernode; 2: 64-column block step of the wide ones (both sweeps); 3, 4: first diagonal solves
+    // and forward tiles of a 256-column superstep (forward sweep only); 5: its backward tiles (backward sweep only)
+    struct SolveLaunch { int kind ; int64_t first, count, maxcol ; } ;
     std::vector<SolveLaunch> solve_launches ;
     bool solve_ready = false ;
     DevBuf<int32_t> d_ssmall ;
     DevBuf<SolveBlk> d_sblk ;
     DevBuf<SolveTile> d_stile ;
+    DevBuf<SolveTile256> d_stile256 ;
+    int solve_cols = 64 ;                   // columns of a wide supernode per launch: 64 or 256 (CHOLMOD_B200_SOLVE_COLS)
     std::vector<unsigned char> h_Ax ;       // zomplex input (Ax, Az) interleaved before the upload
     std::vector<unsigned char> h_Fx ;
     bool have_A = false, A_unpacked = false ;
@@ -206,6 +211,20 @@ struct b200_factor
     int64_t kernel_launches = 0 ;
     int64_t nccl_calls = 0 ;
     int profile = 0 ;                       // 1: bracket every launch with events (diagnostic runs only)
+    // The launch list of a one-GPU plan can be captured once as a CUDA graph and replayed by every later
+    // factorization (the list is static).  One graph per destination of the copy-out (NULL = the factor stays on
+    // the device); use_graph: -1 = not decided yet, 0 = plain launches (the default), 1 = graphs.
+    // A graph's copy nodes are bound to the page-locked mapping the destination had at capture: reg_gen (bumped by
+    // every change of this context's registrations) and `pinned` are compared before a replay.
+    struct GraphSlot { void *dst = nullptr ; cudaGraphExec_t exec = nullptr ; int64_t launches = 0 ; uint64_t used = 0 ;
+        uint64_t reg_gen = 0 ; bool pinned = false ; } ;
+    uint64_t reg_gen = 0 ;
+    GraphSlot graphs [2] ;
+    int use_graph = -1 ;
+    uint64_t graph_clock = 0 ;
+    int64_t graph_replays = 0, graph_captures = 0 ;
+    cudaEvent_t ev_fork = nullptr ;
+    std::vector<cudaEvent_t> ev_join ;
     std::vector<cudaEvent_t> prof_ev ;
     double ms_kind [K_NKINDS] = {} ;
     int64_t launches_kind [K_NKINDS] = {} ;
@@ -713,6 +732,8 @@ static int build_device_symbolic (b200_factor *f)
     return B200_OK ;
 }
 
+static void unregister_pieces (b200_factor *f) ;
+
 static int create_device_side (b200_factor *f, const int64_t *Ls)
 {
     const Plan &P = f->plan ;
@@ -902,7 +923,7 @@ void b200_destroy (b200_factor *f)
     {
         cudaSetDevice (f->device) ;
         cudaStreamSynchronize (f->stream) ;
-        for (auto &pc : f->reg_pieces) cudaHostUnregister (pc.first) ;
+        unregister_pieces (f) ;
         f->d_super.release () ; f->d_pi.release () ; f->d_px.release () ; f->d_Ls.release () ;
         f->d_supermap.release () ; f->d_relmap.release () ; f->d_level_list.release () ;
         f->d_pairs.release () ; f->d_pair_map.release () ;
@@ -913,11 +934,14 @@ void b200_destroy (b200_factor *f)
         f->d_winv.release () ; f->d_colmine.release () ; f->d_pulls.release () ; f->d_barrier.release () ;
         for (int r = 0 ; r < 32 ; r++)
             if (f->peer_ipc [r] && f->peers.p [r]) { cudaIpcCloseMemHandle (f->peers.p [r]) ; f->peers.p [r] = nullptr ; }
-        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ;
+        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ; f->d_stile256.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         if (f->stage) { cudaFreeHost (f->stage) ; for (auto &e : f->stage_ev) if (e) cudaEventDestroy (e) ; }
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
         for (auto &e : f->plan_ev) cudaEventDestroy (e) ;
+        for (auto &g : f->graphs) if (g.exec) { cudaGraphExecDestroy (g.exec) ; g.exec = nullptr ; }
+        if (f->ev_fork) cudaEventDestroy (f->ev_fork) ;
+        for (auto &e : f->ev_join) cudaEventDestroy (e) ;
         if (f->comm) { NcclApi *nc = nccl_api () ; if (nc) nc->CommDestroy (f->comm) ; f->comm = nullptr ; }
         cudaStreamSynchronize (f->stream2) ;
         cudaStreamDestroy (f->stream2) ;
@@ -984,6 +1008,7 @@ int b200_set_int (b200_factor *f, const char *name, int64_t value)
 {
     if (!f || !name) return B200_INVALID ;
     if (!strcmp (name, "profile")) { f->profile = value ? 1 : 0 ; return B200_OK ; }
+    if (!strcmp (name, "use_graph")) { f->use_graph = value ? 1 : 0 ; return B200_OK ; }
     return B200_INVALID ;
 }
 
@@ -1006,6 +1031,10 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strcmp (name, "ms_symbolic")) return f->ms_symbolic ;
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '9' && atoi (name + 7) < K_NKINDS) return f->ms_kind [atoi (name + 7)] ;
     if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
+    if (!strcmp (name, "solve_cols")) return f->solve_cols ;
+    if (!strcmp (name, "graph_replays")) return (double) f->graph_replays ;
+    if (!strcmp (name, "graph_captures")) return (double) f->graph_captures ;
+    if (!strcmp (name, "use_graph")) return f->use_graph ;
     if (!strncmp (name, "solve_launches", 14) && name [14] >= '0' && name [14] < '4') return (double) f->solve_launch_count [name [14] - '0'] ;
     if (!strncmp (name, "ms_launch_start", 15)) { size_t k = (size_t) atoll (name + 15) ; return k < f->ms_launch_start.size () ? f->ms_launch_start [k] : -1 ; }
     if (!strncmp (name, "ms_launch", 9)) { size_t k = (size_t) atoll (name + 9) ; return k < f->ms_launch.size () ? f->ms_launch [k] : -1 ; }
@@ -1305,11 +1334,31 @@ int b200_upload_values (b200_factor *f, const void *Ax)
 
 }   // extern "C"
 
+// Host ranges this library has page-locked, process wide, with the number of contexts that rely on each: several
+// contexts may write into one buffer (the devices of b200_multi; the shim's contexts of different threads that meet
+// the same L->x one after the other), and a range must stay locked until the last of them lets go -- another
+// context's copy-out may be in flight into it.
+struct HostReg { size_t bytes ; int refs ; } ;
+static std::mutex g_reg_lock ;
+static std::map<void *, HostReg> g_reg ;
+
 static void unregister_pieces (b200_factor *f)
 {
-    for (auto &pc : f->reg_pieces) { cudaHostUnregister (pc.first) ; cudaGetLastError () ; }
+    std::lock_guard<std::mutex> guard (g_reg_lock) ;
+    for (auto &pc : f->reg_pieces)
+    {
+        auto it = g_reg.find (pc.first) ;
+        if (it == g_reg.end ()) continue ;
+        if (--it->second.refs <= 0)
+        {
+            cudaHostUnregister (pc.first) ;
+            cudaGetLastError () ;
+            g_reg.erase (it) ;
+        }
+    }
     f->reg_pieces.clear () ;
     f->reg_ptr = nullptr ; f->reg_bytes = 0 ;
+    f->reg_gen++ ;
 }
 
 static bool is_page_locked (const void *p, size_t bytes)
@@ -1320,6 +1369,27 @@ static bool is_page_locked (const void *p, size_t bytes)
         && cudaHostGetFlags (&fl, (char *) const_cast<void *> (p) + (bytes - 1)) == cudaSuccess) return true ;
     cudaGetLastError () ;
     return false ;
+}
+
+// take a reference on [p, p + len) if this library has it locked already, else lock it (unless somebody else has)
+static void lock_piece (b200_factor *f, void *p, size_t len)
+{
+    std::lock_guard<std::mutex> guard (g_reg_lock) ;
+    f->reg_gen++ ;
+    auto it = g_reg.find (p) ;
+    if (it != g_reg.end () && it->second.bytes == len)
+    {
+        it->second.refs++ ;
+        f->reg_pieces.push_back ({ p, len }) ;
+        return ;
+    }
+    if (is_page_locked (p, len)) return ;       // the caller's own pinned memory (or an overlapping range of ours)
+    if (cudaHostRegister (p, len, cudaHostRegisterPortable) == cudaSuccess)
+    {
+        g_reg [p] = HostReg { len, 1 } ;
+        f->reg_pieces.push_back ({ p, len }) ;
+    }
+    else cudaGetLastError () ;
 }
 
 // Page-lock the caller's L->x once: later factorizations into the same buffer then copy at PCIe speed and
@@ -1367,18 +1437,13 @@ static void ensure_registered (b200_factor *f, void *Lx, size_t bytes)
         {
             void *p = (void *) (uintptr_t) r.first ;
             const size_t len = r.second - r.first ;
-            if (len < ((size_t) 1 << 16) || is_page_locked (p, len)) continue ;
-            if (cudaHostRegister (p, len, cudaHostRegisterPortable) == cudaSuccess) f->reg_pieces.push_back ({ p, len }) ;
-            else cudaGetLastError () ;
+            if (len >= ((size_t) 1 << 16)) lock_piece (f, p, len) ;
         }
         return ;
     }
     // page-locked already -- by the caller, or by another context of this process that writes into the same
     // buffer (b200_multi)?  Then there is nothing to do, and nothing of ours to undo later.
-    if (bytes > 0 && is_page_locked (Lx, bytes)) return ;
-    if (bytes >= ((size_t) 1 << 20) && cudaHostRegister (Lx, bytes, cudaHostRegisterPortable) == cudaSuccess)
-        f->reg_pieces.push_back ({ Lx, bytes }) ;
-    else cudaGetLastError () ;
+    if (bytes >= ((size_t) 1 << 20)) lock_piece (f, Lx, bytes) ;
 }
 
 // everything this rank owns (all of L->x on one GPU) from the arena to its place in the caller's L->x
@@ -1434,6 +1499,86 @@ static int repair_dist (b200_factor *f, int64_t minor, double beta, int quick)
     return st ;
 }
 
+// The plan's launch list through a CUDA graph: replay the graph captured for this copy-out destination, or capture
+// it now (the launches are recorded, not run), instantiate and launch it.  Returns 1 when the graph ran, 0 when the
+// caller has to issue the launches itself (capture not possible: nothing has run), < 0 on an error.
+template <typename T>
+static int run_graph (b200_factor *f)
+{
+    const Plan &P = f->plan ;
+    cudaStream_t s = f->stream ;
+    b200_factor::GraphSlot *slot = nullptr ;
+    const bool pinned = f->copy_dst && is_page_locked (f->copy_dst, (size_t) P.xsize * sizeof (T)) ;
+    for (auto &g : f->graphs)
+        if (g.exec && g.dst == f->copy_dst)
+        {
+            if (!g.dst || (g.reg_gen == f->reg_gen && g.pinned == pinned)) slot = &g ;
+            else { cudaGraphExecDestroy (g.exec) ; g.exec = nullptr ; }     // the destination's mapping has changed
+        }
+    if (!slot)
+    {
+        // every stream of the plan joins the capture behind the main one, and returns to it at the end
+        std::vector<cudaStream_t> side = { f->stream2, f->stream3, f->stream5 } ;
+        while ((int) f->gstreams.size () < P.nstreams - 5)
+        {
+            int lo = 0, hi = 0 ;
+            CK (cudaDeviceGetStreamPriorityRange (&lo, &hi), "priority range") ;
+            cudaStream_t g ;
+            CK (cudaStreamCreateWithPriority (&g, cudaStreamNonBlocking, (f->gstreams.size () & 1) ? lo : hi), "group stream") ;
+            f->gstreams.push_back (g) ;
+        }
+        for (cudaStream_t g : f->gstreams) side.push_back (g) ;
+        while ((int64_t) f->plan_ev.size () < (int64_t) P.nevents)
+        {
+            cudaEvent_t e ;
+            CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "plan event") ;
+            f->plan_ev.push_back (e) ;
+        }
+        if (!f->ev_fork) CK (cudaEventCreateWithFlags (&f->ev_fork, cudaEventDisableTiming), "fork event") ;
+        while (f->ev_join.size () < side.size ())
+        {
+            cudaEvent_t e ;
+            CK (cudaEventCreateWithFlags (&e, cudaEventDisableTiming), "join event") ;
+            f->ev_join.push_back (e) ;
+        }
+        // nothing of an earlier call may still be running on the side streams when they enter the capture
+        for (cudaStream_t t : side) if (t) CK (cudaStreamSynchronize (t), "side stream") ;
+        if (cudaStreamBeginCapture (s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError () ; return 0 ; }
+        bool ok = cudaEventRecord (f->ev_fork, s) == cudaSuccess ;
+        for (cudaStream_t t : side) if (t) ok = ok && cudaStreamWaitEvent (t, f->ev_fork, 0) == cudaSuccess ;
+        const int64_t before = f->kernel_launches ;
+        int st = ok ? run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p, f->d_pulls.p) : B200_GPU_PROBLEM ;
+        const int64_t launches = f->kernel_launches - before ;
+        f->kernel_launches = before ;
+        for (size_t k = 0 ; k < side.size () ; k++)
+            if (side [k])
+                ok = ok && cudaEventRecord (f->ev_join [k], side [k]) == cudaSuccess && cudaStreamWaitEvent (s, f->ev_join [k], 0) == cudaSuccess ;
+        cudaGraph_t graph = nullptr ;
+        cudaError_t e = cudaStreamEndCapture (s, &graph) ;
+        cudaGraphExec_t exec = nullptr ;
+        if (st == B200_OK && ok && e == cudaSuccess && graph) e = cudaGraphInstantiate (&exec, graph, 0) ;
+        if (graph) cudaGraphDestroy (graph) ;
+        if (st != B200_OK || !ok || e != cudaSuccess || !exec)
+        {
+            cudaGetLastError () ;
+            if (exec) cudaGraphExecDestroy (exec) ;
+            f->use_graph = 0 ;          // this context issues its launches one by one from now on
+            return (st < 0 && st != B200_GPU_PROBLEM) ? st : 0 ;
+        }
+        slot = &f->graphs [0] ;
+        if (f->graphs [0].exec && (!f->graphs [1].exec || f->graphs [1].used < f->graphs [0].used)) slot = &f->graphs [1] ;
+        if (slot->exec) cudaGraphExecDestroy (slot->exec) ;
+        slot->exec = exec ; slot->dst = f->copy_dst ; slot->launches = launches ;
+        slot->reg_gen = f->reg_gen ; slot->pinned = pinned ;
+        f->graph_captures++ ;
+    }
+    slot->used = ++f->graph_clock ;
+    CK (cudaGraphLaunch (slot->exec, s), "graph launch") ;
+    f->kernel_launches += slot->launches ;
+    f->graph_replays++ ;
+    return 1 ;
+}
+
 // host_dst != NULL: finished parts of the factor are copied to host_dst [0..xsize) while the rest is still
 // being computed (the plan's K_COPYOUT schedule); on return the host copy is complete.
 template <typename T>
@@ -1455,7 +1600,20 @@ static int factor_device_T (b200_factor *f, double beta, int quick, int64_t *min
     int st = scatter_A<T> (f, 0, P.n, beta) ;
     if (st) return st ;
     CK (cudaEventRecord (f->ev [3], s), "record") ;
-    st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p, f->d_pulls.p) ;
+    if (f->use_graph < 0)
+    {
+        // opt-in (CHOLMOD_B200_GRAPH=1): measured on config 5 (9725 launches) a replay takes 23.1 ms against 24.4 ms
+        // of plain launches, but capture and instantiation add 0.5 s to the first call (1 s on config 2's 4035)
+        const char *e = getenv ("CHOLMOD_B200_GRAPH") ;
+        f->use_graph = (e && atoi (e) != 0) ? 1 : 0 ;
+    }
+    int ran = 0 ;
+    if (f->use_graph == 1 && P.nranks == 1 && !f->profile)
+    {
+        ran = run_graph<T> (f) ;
+        if (ran < 0) return ran ;
+    }
+    if (!ran) st = run_launches<T> (f, P, f->d_items.p, f->d_tiles.p, f->d_potrf.p, f->d_trsm.p, f->d_relmap.p, f->d_pulls.p) ;
     if (st) return st ;
     if (P.nranks > 1)
     {
@@ -1669,10 +1827,15 @@ static int solve_T (b200_factor *f, int nrhs, int which)
         // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
         // over the level, one launch per step: the rows below the diagonal block spread over 256-row tiles
         // (k_solve_fwd_blk).  The backward sweep is the same list read in reverse (k_solve_bwd_blk).
-        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256 ;
+        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256, SOLVE_SUPER = 256, SOLVE_FROWS = 64 ;
+        const char *ecols = getenv ("CHOLMOD_B200_SOLVE_COLS") ;
+        f->solve_cols = (ecols && atoi (ecols) == 64) ? 64 : 256 ;
         std::vector<int32_t> small ;
         std::vector<SolveBlk> blks ;
         std::vector<SolveTile> tiles ;
+        std::vector<SolveTile256> tiles256 ;
+        std::vector<int32_t> blk_first ((size_t) P.nsuper, -1) ;
+        int32_t nsteps = 0 ;
         f->solve_launches.clear () ;
         for (int lev = 0 ; lev < P.nlevels ; lev++)
         {
@@ -1685,33 +1848,83 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                 const int32_t sn = P.level_list [first + q] ;
                 const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
                 if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; }
-                else { big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ; }
+                else
+                {
+                    // the 64 x 64 diagonal blocks of one supernode are consecutive in blks (and in Winv)
+                    big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ;
+                    blk_first [sn] = (int32_t) blks.size () ;
+                    for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_NB)
+                        blks.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0), 0 }) ;
+                }
             }
             if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
-            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
+            if (f->solve_cols == 64)
             {
-                const size_t t0 = tiles.size () ;
+                for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
+                {
+                    const size_t t0 = tiles.size () ;
+                    for (int32_t sn : big)
+                    {
+                        const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
+                        if (nscol <= c0) continue ;
+                        const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
+                        const int32_t blk = blk_first [sn] + (int32_t) (c0 / SOLVE_NB) ;
+                        const size_t tb = tiles.size () ;
+                        for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
+                            tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
+                        // a block with nothing below it still needs its diagonal solve
+                        if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
+                        tiles [tb].writer = 1 ;
+                        for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
+                    }
+                    f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
+                }
+                continue ;
+            }
+            // 256 columns per launch.  Forward: the first superstep of every wide supernode of the level is solved by
+            // a launch of its own (kind 3); after that the tiles of superstep k (kind 4, 64 rows each) also solve the
+            // diagonal block of superstep k+1.  Backward: tiles of 64 rows too (kind 5), the last one to finish solves
+            // the superstep's own diagonal block.
+            if (!big.empty ())
+            {
+                const size_t t0 = tiles256.size () ;
+                for (int32_t sn : big)
+                {
+                    const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
+                    tiles256.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol), 0, 0, 1, blk_first [sn], 0, 0, 0 }) ;
+                }
+                f->solve_launches.push_back ({ 3, (int64_t) t0, (int64_t) (tiles256.size () - t0), 0 }) ;
+            }
+            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_SUPER)
+            {
+                const size_t tf = tiles256.size () ;
+                std::vector<SolveTile256> back ;
                 for (int32_t sn : big)
                 {
                     const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
                     if (nscol <= c0) continue ;
-                    const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
-                    const int32_t blk = (int32_t) blks.size () ;
-                    blks.push_back ({ sn, (int32_t) c0, jb, 0 }) ;
-                    const size_t tb = tiles.size () ;
-                    for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
-                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
-                    // a block with nothing below it still needs its diagonal solve
-                    if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
-                    tiles [tb].writer = 1 ;
-                    for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
+                    const int32_t nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0) ;
+                    const int32_t next_nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - (c0 + nb)) ;      // 0 at the last one
+                    const int32_t blk0 = blk_first [sn] + (int32_t) (c0 / SOLVE_NB), step = nsteps++ ;
+                    for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
+                        tiles256.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
+                            blk0, step, (r < c0 + nb + next_nb) ? next_nb : 0, 0 }) ;
+                    const size_t tb = back.size () ;
+                    for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
+                        back.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
+                            blk0, step, 0, 0 }) ;
+                    if (back.size () == tb) back.push_back ({ sn, (int32_t) c0, nb, (int32_t) (c0 + nb), 0, 0, blk0, step, 0, 0 }) ;
+                    for (size_t k = tb ; k < back.size () ; k++) back [k].ntiles = (int32_t) (back.size () - tb) ;
                 }
-                f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
+                f->solve_launches.push_back ({ 4, (int64_t) tf, (int64_t) (tiles256.size () - tf), 0 }) ;
+                f->solve_launches.push_back ({ 5, (int64_t) tiles256.size (), (int64_t) back.size (), 0 }) ;
+                tiles256.insert (tiles256.end (), back.begin (), back.end ()) ;
             }
         }
         bool ok = f->d_ssmall.upload (small, s) == cudaSuccess ;
         ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
         ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
+        ok = ok && f->d_stile256.upload (tiles256, s) == cudaSuccess ;
         ok = ok && f->d_solveW.alloc (blks.size () * (size_t) (SOLVE_WLD * SOLVE_WLD) * sizeof (XT)) == cudaSuccess ;
         if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
         CK (cudaStreamSynchronize (s), "solve plan upload") ;
@@ -1752,7 +1965,7 @@ static int solve_T (b200_factor *f, int nrhs, int which)
         for (size_t q = 0 ; q < nl ; q++)
         {
             const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
-            if (L.count <= 0) continue ;
+            if (L.count <= 0 || (pass == 0 && L.kind == 5) || (pass == 1 && (L.kind == 3 || L.kind == 4))) continue ;
             const unsigned grid = (unsigned) L.count ;
             if (f->profile) cudaEventRecord (f->prof_ev [nev++], s) ;
             if (L.kind == 0)
@@ -1765,6 +1978,15 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                     k_solve_bwd<T><<<grid, 128, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, X, P.n, nrhs, (int) L.maxcol) ;
             }
+            else if (L.kind == 3)
+                k_solve_diag_fwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                    Lx, Winv, X, Y, P.n, nrhs) ;
+            else if (L.kind == 4)
+                k_solve_fwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                    f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
+            else if (L.kind == 5)
+                k_solve_bwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
+                    f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
             else
             {
                 if (pass == 0)
@@ -1791,6 +2013,7 @@ static int solve_T (b200_factor *f, int nrhs, int which)
             {
                 const b200_factor::SolveLaunch &L = f->solve_launches [pass == 0 ? q : nl - 1 - q] ;
                 if (L.count <= 0 || !(which & (1 << pass))) continue ;
+                if ((pass == 0 && L.kind == 5) || (pass == 1 && (L.kind == 3 || L.kind == 4))) continue ;
                 float ms = 0 ;
                 cudaEventElapsedTime (&ms, f->prof_ev [e], f->prof_ev [e+1]) ;
                 e += 2 ;

@@ -1911,7 +1911,7 @@ struct SolveTile256 { int32_t s, c0, nb, r0, nrows, ntiles, blk0, step, next_nb,
 // is destroyed; ys [0..nb) receives y = L_blk \ xs.  Four sub-steps of 64: y_q = W_q * x_q with the pre-inverted
 // diagonal block (4 threads per row), then the later unknowns take x -= L (rows, block q) * y_q, 4 threads per row
 // with 16 independent loads each.
-template <typename T, typename XT>
+template <typename T, typename XT, int PRE_MAX>
 __device__ __forceinline__ void solve_diag256_fwd (const T *__restrict__ Lsn, int64_t nsrow, int c0, int nb,
     const XT *__restrict__ W0, XT *xs, XT *ys)
 {
@@ -1921,29 +1921,46 @@ __device__ __forceinline__ void solve_diag256_fwd (const T *__restrict__ Lsn, in
     {
         const int jb = min (64, nb - q0) ;
         const XT *W = W0 + (int64_t) (q0 >> 6) * (SOLVE_WLD * SOLVE_WLD) ;
+        // the entries of L that the update below needs do not depend on y_q: ask for them before the product with
+        // W_q, all of them at once (up to three later 64-row groups, 16 columns each per thread)
+        constexpr int PRE = (sizeof (T) <= 8) ? PRE_MAX : 1 ;   // 16-byte entries: one group ahead, for the registers' sake
+        T lv [PRE][16] ;
+        #pragma unroll
+        for (int g = 0 ; g < PRE ; g++)
         {
+            const int i = q0 + 64 * (g + 1) + r4 ;
+            const T *Lr = Lsn + (c0 + i) + (int64_t) (c0 + q0 + 16 * part) * nsrow ;
+            #pragma unroll
+            for (int j = 0 ; j < 16 ; j++) lv [g][j] = (i < nb) ? Lr [(int64_t) j * nsrow] : T () ;
+        }
+        {
+            XT wv [16] ;
+            #pragma unroll
+            for (int k = 0 ; k < 16 ; k++) wv [k] = (part + 4 * k <= r4) ? W [r4 + (part + 4 * k) * SOLVE_WLD] : zero ;
             XT acc = zero ;
             #pragma unroll
-            for (int k = 0 ; k < 16 ; k++)
-            {
-                const int c = part + 4 * k ;
-                if (c <= r4 && r4 < jb) acc += W [r4 + c * SOLVE_WLD] * xs [q0 + c] ;
-            }
+            for (int k = 0 ; k < 16 ; k++) acc += wv [k] * xs [q0 + part + 4 * k] ;
             acc += shfl_xor_ (0xffffffffu, acc, 1) ;
             acc += shfl_xor_ (0xffffffffu, acc, 2) ;
             if (part == 0 && r4 < jb) ys [q0 + r4] = acc ;
         }
         __syncthreads () ;
-        for (int base = q0 + jb ; base < nb ; base += 64)
+        // rows below block q exist only when the block is a full one (jb == 64)
+        #pragma unroll
+        for (int g = 0 ; g < 3 ; g++)
         {
-            const int i = base + r4 ;
+            const int i = q0 + 64 * (g + 1) + r4 ;
             XT acc = zero ;
-            if (i < nb)
+            if (g < PRE)
+            {
+                #pragma unroll
+                for (int j = 0 ; j < 16 ; j++) acc += cvt<XT> (lv [g < PRE ? g : 0][j]) * ys [q0 + 16 * part + j] ;
+            }
+            else if (i < nb)
             {
                 const T *Lr = Lsn + (c0 + i) + (int64_t) (c0 + q0 + 16 * part) * nsrow ;
                 #pragma unroll
-                for (int j = 0 ; j < 16 ; j++)
-                    if (16 * part + j < jb) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * ys [q0 + 16 * part + j] ;
+                for (int j = 0 ; j < 16 ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * ys [q0 + 16 * part + j] ;
             }
             acc += shfl_xor_ (0xffffffffu, acc, 1) ;
             acc += shfl_xor_ (0xffffffffu, acc, 2) ;
@@ -1970,7 +1987,7 @@ __global__ void __launch_bounds__ (256) k_solve_diag_fwd256 (const SolveTile256 
     {
         xs [tid] = (tid < t.nb) ? X [(int64_t) rhs * n + k1 + t.c0 + tid] : from_real<XT> (0) ;
         __syncthreads () ;
-        solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
+        solve_diag256_fwd<T, XT, 3> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
         if (tid < t.nb) Y [(int64_t) rhs * n + k1 + t.c0 + tid] = ys [tid] ;
         __syncthreads () ;
     }
@@ -1982,7 +1999,7 @@ __global__ void __launch_bounds__ (256) k_solve_diag_fwd256 (const SolveTile256 
 // atomics.  The (up to four) tiles that hold the rows of the next superstep's diagonal block count themselves off;
 // the last one solves that block, so the next launch finds its y in Y.
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
+__global__ void __launch_bounds__ (256, 2) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
     const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
     typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
@@ -2006,9 +2023,12 @@ __global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__re
         {
             const T *Lr = Lsn + row + (int64_t) (t.c0 + 64 * part) * nsrow ;
             const XT *yq = yb + 64 * part ;
-            #pragma unroll 16
-            for (int j = 0 ; j < 64 ; j++)
-                if (j < jq) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
+            if (jq == 64)
+            {
+                #pragma unroll 16
+                for (int j = 0 ; j < 64 ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
+            }
+            else for (int j = 0 ; j < jq ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
         }
         acc += shfl_xor_ (0xffffffffu, acc, 1) ;
         acc += shfl_xor_ (0xffffffffu, acc, 2) ;
@@ -2035,7 +2055,7 @@ __global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__re
                 __threadfence () ;
                 xs [tid] = (tid < t.next_nb) ? ldcg_ (x + k1 + t.c0 + t.nb + tid) : zero ;
                 __syncthreads () ;
-                solve_diag256_fwd<T, XT> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
+                solve_diag256_fwd<T, XT, 2> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
                     Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
                 if (tid < t.next_nb) y [k1 + t.c0 + t.nb + tid] = ys [tid] ;
             }
@@ -2044,18 +2064,45 @@ __global__ void __launch_bounds__ (256) k_solve_fwd256 (const SolveTile256 *__re
     }
 }
 
-// Backward superstep, one CTA per 256 rows below it: Y_blk -= L (rows, superstep)^H * x [rows] (atomics; a warp takes
-// 32 columns, four at a time, its lanes run down the rows: 32 independent loads per batch); the CTA that finishes
+// v [u] (u < 16) summed over the 32 lanes of the warp, 31 shuffles: on return lane l holds the sum of v [l & 15] in
+// v [0].  The first step adds the two half-warps; every later step keeps one half of the remaining values and hands
+// the other half to the partner lane, which keeps those.
+template <typename XT, int H>
+__device__ __forceinline__ void warp_sum_step (XT (&v) [16], int lane)
+{
+    const bool up = (lane & H) != 0 ;
+    #pragma unroll
+    for (int u = 0 ; u < H ; u++)
+    {
+        const XT keep = up ? v [u + H] : v [u], send = up ? v [u] : v [u + H] ;
+        v [u] = keep + shfl_xor_ (0xffffffffu, send, H) ;
+    }
+}
+
+template <typename XT>
+__device__ __forceinline__ void warp_sum16 (XT (&v) [16], int lane)
+{
+    #pragma unroll
+    for (int u = 0 ; u < 16 ; u++) v [u] += shfl_xor_ (0xffffffffu, v [u], 16) ;
+    warp_sum_step<XT, 8> (v, lane) ;
+    warp_sum_step<XT, 4> (v, lane) ;
+    warp_sum_step<XT, 2> (v, lane) ;
+    warp_sum_step<XT, 1> (v, lane) ;
+}
+
+// Backward superstep, one CTA per 64 rows below it: Y_blk -= L (rows, superstep)^H * x [rows] (atomics).  A warp
+// takes 32 columns, 16 at a time; a lane holds two rows of each (32 independent, coalesced loads per pass) and the
+// warp adds up with warp_sum16, so that 16 lanes subtract 16 consecutive entries of Y.  The CTA that finishes
 // last then solves the diagonal block backwards, four sub-steps of 64 from the bottom up:
 // x_q = W_q^H * y_q ;  y_c -= L (block q, column c)^H * x_q for the columns c of the blocks above (4 threads per column).
 template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_bwd256 (const SolveTile256 *__restrict__ tiles,
+__global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8) ? 2 : 1) k_solve_bwd256 (const SolveTile256 *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
     const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
     typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
 {
     typedef typename solve_x<T>::type XT ;
-    __shared__ XT xr [256], yb [256], xq [64] ;
+    __shared__ XT xr [64], yb [256], xq [64] ;
     __shared__ int is_last ;
     const SolveTile256 t = tiles [blockIdx.x] ;
     const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
@@ -2065,39 +2112,47 @@ __global__ void __launch_bounds__ (256) k_solve_bwd256 (const SolveTile256 *__re
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
         XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
-        if (tid < t.nrows)
+        if (tid < 64)
         {
             const int row = t.r0 + tid ;
-            xr [tid] = x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] ;
+            xr [tid] = (tid < t.nrows) ? x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] : zero ;
         }
-        else xr [tid] = zero ;
         __syncthreads () ;
         if (t.nrows > 0)
         {
             const T *Lbase = Lsn + t.r0 + (int64_t) t.c0 * nsrow ;
-            for (int g = 0 ; g < 8 ; g++)
+            const XT x0 = xr [lane], x1 = xr [lane + 32] ;
+            const bool ok0 = lane < t.nrows, ok1 = lane + 32 < t.nrows ;
+            for (int h = 0 ; h < 2 ; h++)
             {
-                const int c = warp * 32 + 4 * g ;
-                if (c >= t.nb) break ;
-                XT acc [4] = { zero, zero, zero, zero } ;
-                #pragma unroll
-                for (int k = 0 ; k < 8 ; k++)
+                const int cb = warp * 32 + 16 * h ;
+                if (cb >= t.nb) break ;
+                T a [16], b [16] ;
+                if (t.nrows == 64 && cb + 16 <= t.nb)
                 {
-                    const int r = lane + 32 * k ;
-                    if (r < t.nrows)
+                    #pragma unroll
+                    for (int u = 0 ; u < 16 ; u++)
                     {
-                        const XT xv = xr [r] ;
-                        #pragma unroll
-                        for (int u = 0 ; u < 4 ; u++)
-                            if (c + u < t.nb) acc [u] += mulc (xv, cvt<XT> (Lbase [(int64_t) (c + u) * nsrow + r])) ;
+                        const T *Lc = Lbase + (int64_t) (cb + u) * nsrow ;
+                        a [u] = Lc [lane] ; b [u] = Lc [lane + 32] ;
                     }
                 }
-                #pragma unroll
-                for (int u = 0 ; u < 4 ; u++)
+                else
                 {
-                    for (int o = 16 ; o > 0 ; o >>= 1) acc [u] += shfl_xor_ (0xffffffffu, acc [u], o) ;
-                    if (lane == 0 && c + u < t.nb) atomic_sub (y + k1 + t.c0 + c + u, acc [u]) ;
+                    #pragma unroll
+                    for (int u = 0 ; u < 16 ; u++)
+                    {
+                        const T *Lc = Lbase + (int64_t) (cb + u) * nsrow ;
+                        const bool cok = cb + u < t.nb ;
+                        a [u] = (cok && ok0) ? Lc [lane] : T () ;
+                        b [u] = (cok && ok1) ? Lc [lane + 32] : T () ;
+                    }
                 }
+                XT v [16] ;
+                #pragma unroll
+                for (int u = 0 ; u < 16 ; u++) v [u] = mulc (x0, cvt<XT> (a [u])) + mulc (x1, cvt<XT> (b [u])) ;
+                warp_sum16<XT> (v, lane) ;
+                if (lane < 16 && cb + lane < t.nb) atomic_sub (y + k1 + t.c0 + cb + lane, v [0]) ;
             }
         }
         __threadfence () ;
@@ -2120,31 +2175,51 @@ __global__ void __launch_bounds__ (256) k_solve_bwd256 (const SolveTile256 *__re
             {
                 const int q0 = q * 64, jb = min (64, t.nb - q0) ;
                 const XT *W = Winv + (int64_t) (t.blk0 + q) * (SOLVE_WLD * SOLVE_WLD) ;
+                // rows of block q in the columns of the blocks above it: independent of x_q, asked for first
+                constexpr int PRE = (sizeof (T) <= 8) ? 2 : 1 ;
+                T lv [PRE][16] ;
+                #pragma unroll
+                for (int g = 0 ; g < PRE ; g++)
+                {
+                    const T *Lc = Lsn + (t.c0 + q0 + 16 * part) + (int64_t) (t.c0 + 64 * g + r4) * nsrow ;
+                    #pragma unroll
+                    for (int r = 0 ; r < 16 ; r++) lv [g][r] = (64 * g < q0 && 16 * part + r < jb) ? Lc [r] : T () ;
+                }
                 {
                     // x_c = sum_{r >= c} conj (W (r,c)) * y_r : thread (c, part) walks down column c of W
+                    XT wv [16] ;
+                    #pragma unroll
+                    for (int k = 0 ; k < 16 ; k++) wv [k] = (part + 4 * k >= r4) ? W [part + 4 * k + r4 * SOLVE_WLD] : zero ;
                     XT acc = zero ;
                     #pragma unroll
                     for (int k = 0 ; k < 16 ; k++)
-                    {
-                        const int r = part + 4 * k ;
-                        if (r >= r4 && r < jb && r4 < jb) acc += mulc (yb [q0 + r], W [r + r4 * SOLVE_WLD]) ;
-                    }
+                        if (part + 4 * k < jb) acc += mulc (yb [q0 + part + 4 * k], wv [k]) ;
                     acc += shfl_xor_ (0xffffffffu, acc, 1) ;
                     acc += shfl_xor_ (0xffffffffu, acc, 2) ;
                     if (part == 0 && r4 < jb) { xq [r4] = acc ; x [k1 + t.c0 + q0 + r4] = acc ; }
                 }
                 __syncthreads () ;
-                for (int base = 0 ; base < q0 ; base += 64)
+                #pragma unroll
+                for (int g = 0 ; g < 3 ; g++)
                 {
-                    const int c = base + r4 ;           // a column of a block above (c < q0 always: q0 is a multiple of 64)
-                    const T *Lc = Lsn + (t.c0 + q0 + 16 * part) + (int64_t) (t.c0 + c) * nsrow ;
+                    const int c = 64 * g + r4 ;         // a column of a block above (c < q0 when 64 g < q0: q0 is a multiple of 64)
                     XT acc = zero ;
-                    #pragma unroll
-                    for (int r = 0 ; r < 16 ; r++)
-                        if (16 * part + r < jb) acc += mulc (xq [16 * part + r], cvt<XT> (Lc [r])) ;
+                    if (g < PRE)
+                    {
+                        #pragma unroll
+                        for (int r = 0 ; r < 16 ; r++)
+                            if (16 * part + r < jb) acc += mulc (xq [16 * part + r], cvt<XT> (lv [g < PRE ? g : 0][r])) ;
+                    }
+                    else if (64 * g < q0)
+                    {
+                        const T *Lc = Lsn + (t.c0 + q0 + 16 * part) + (int64_t) (t.c0 + c) * nsrow ;
+                        #pragma unroll
+                        for (int r = 0 ; r < 16 ; r++)
+                            if (16 * part + r < jb) acc += mulc (xq [16 * part + r], cvt<XT> (Lc [r])) ;
+                    }
                     acc += shfl_xor_ (0xffffffffu, acc, 1) ;
                     acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-                    if (part == 0) yb [c] -= acc ;
+                    if (part == 0 && 64 * g < q0) yb [c] -= acc ;
                 }
                 __syncthreads () ;
             }

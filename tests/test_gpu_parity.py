@@ -297,11 +297,16 @@ def test_factor_values_at_benchmark_sizes(kind, size, single, tol_l, tol_r):
     assert res <= tol_r, res
 
 
-@pytest.mark.parametrize("kind,size,ordering", [("lap3d7", 40, refd.CHOLMOD_METIS), ("lap2d9", 200, refd.CHOLMOD_METIS)])
-def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering):
+@pytest.mark.parametrize("cols", [256, 64])
+@pytest.mark.parametrize("kind,size,ordering", [("lap3d7", 40, refd.CHOLMOD_METIS), ("lap3d7", 33, refd.CHOLMOD_METIS),
+                                                ("lap2d9", 200, refd.CHOLMOD_METIS)])
+def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering, cols, monkeypatch):
     """b200_solve_sweep: the forward sweep alone equals the reference's L\\b on its own factor (the plain-C
     restatement's triangular solve), and forward followed by backward equals the two-sided solve; several
-    right-hand sides, a factor with supernodes wider than one 256-column superstep."""
+    right-hand sides, factors with supernodes wider than one 256-column superstep (root separators of 1600 =
+    6 x 256 + 64 and 1089 = 4 x 256 + 65 columns: ragged last supersteps and a one-column last block), with both
+    schedules of the wide supernodes (256 columns per launch, the default, and 64)."""
+    monkeypatch.setenv("CHOLMOD_B200_SOLVE_COLS", str(cols))
     c = get_case(kind, size, ordering)
     F = b200.Factor(c.sym, device=0)
     st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
@@ -326,4 +331,60 @@ def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering):
     L = sp.csc_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(c.n, c.n))
     assert np.max(np.abs(L @ Y - B)) <= 1e-11 * np.max(np.abs(B))
     assert np.max(np.abs(L.T @ Z - Y)) <= 1e-11 * max(1.0, np.max(np.abs(Y)))
+    F.close()
+
+
+@pytest.mark.parametrize("kind,size,ordering,dtype", [
+    ("lap2d9", 120, refd.CHOLMOD_METIS, "double"), ("lap3d7", 16, refd.CHOLMOD_METIS, "double"),
+    ("lap2d5", 30, refd.CHOLMOD_AMD, "double"), ("lap2d5", 40, refd.CHOLMOD_AMD, "single")])
+def test_graph_replay_matches_plain_launches(kind, size, ordering, dtype):
+    """The launch list captured as a CUDA graph (use_graph = 1, CHOLMOD_B200_GRAPH=1; off by default):
+    the capture call, its replays with other values, a second graph for the device-resident form, and a
+    not-positive-definite matrix through the same graph all give what the plain launches give."""
+    single = dtype == "single"
+    c = get_case(kind, size, ordering, single=single)
+    tol = 2e-4 if single else TOL_L
+    F = b200.Factor(c.sym, device=0, dtype=np.float32 if single else np.float64)
+    F.seti("use_graph", 1)
+    Lbuf = np.empty(F.xsize, dtype=F.dtype)
+    for rep, scale in enumerate([1.0, 2.0, 0.5]):
+        st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx * scale, Lx=Lbuf)
+        assert st == b200.OK
+        assert np.max(np.abs(Lx / np.sqrt(scale) - c.Lref)) <= tol * np.max(np.abs(c.Lref))
+        assert F.getd("graph_captures") == 1 and F.getd("graph_replays") == rep + 1
+    launches = F.getd("kernel_launches")
+    # the factor stays on the device: another destination, another graph
+    F.upload_matrix(c.Sp, c.Si, c.Sx)
+    for rep in range(2):
+        assert F.factor_device() == b200.OK
+        assert F.getd("graph_captures") == 2
+    # back to the first destination: its graph is still there
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx, Lx=Lbuf)
+    assert st == b200.OK and F.getd("graph_captures") == 2 and c.rel_err(Lx.astype(np.float64)) <= tol
+    assert F.getd("kernel_launches") == launches
+    # a download into another host array moves the context's page-locked registration away from Lbuf: the graph
+    # whose copy nodes were bound to that mapping must not be replayed (it is captured again instead)
+    assert c.rel_err(F.download_factor().astype(np.float64)) <= tol
+    st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx * 2.0, Lx=Lbuf)
+    assert st == b200.OK and np.max(np.abs(Lx / np.sqrt(2.0) - c.Lref)) <= tol * np.max(np.abs(c.Lref))
+    assert F.getd("graph_captures") == 3
+    # plain launches on the same context give the same number of launches and the same factor
+    F.seti("use_graph", 0)
+    st, Lx2 = F.super_numeric(c.Sp, c.Si, c.Sx)
+    assert st == b200.OK and F.getd("kernel_launches") == launches
+    assert np.max(np.abs(Lx2.astype(np.float64) - Lx.astype(np.float64))) <= tol * np.max(np.abs(c.Lref))
+    # not positive definite through the graph: same status, minor and zero pattern as through plain launches
+    Sx = c.Sx.copy()
+    col = c.n // 2
+    Sx[c.Sp[col]] = -1.0                # first entry of the column is its diagonal in the lower-triangular seam
+    if c.Si[c.Sp[col]] == col:
+        st0, L0 = F.super_numeric(c.Sp, c.Si, Sx)
+        m0 = F.minor
+        F.seti("use_graph", 1)
+        st1, L1 = F.super_numeric(c.Sp, c.Si, Sx, Lx=Lbuf)
+        assert st0 == st1 == b200.NOT_POSDEF and F.minor == m0
+        assert np.array_equal(L0 == 0, L1 == 0)
+        assert np.max(np.abs(L0.astype(np.float64) - L1.astype(np.float64))) <= tol * max(1.0, float(np.max(np.abs(L0))))
+        st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx, Lx=Lbuf)
+        assert st == b200.OK and c.rel_err(Lx.astype(np.float64)) <= tol
     F.close()
