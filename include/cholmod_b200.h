@@ -289,7 +289,15 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
  * start time of launch i of the plan, in the order of the "launches" table of b200_plan_export; "ms_level_end<l>"
  * when etree level l was finished; "ms_solve_part0..3" the solve's small-forward, wide-forward, small-backward
  * and wide-backward parts.  Profiling serialises nothing but adds event overhead: never time a benchmark step
- * with it on. */
+ * with it on.
+ * "use_graph" = 1 (or CHOLMOD_B200_GRAPH=1 in the environment; one-GPU contexts): the launch list is captured once
+ * per copy-out destination as a CUDA graph and replayed by later factorizations ("graph_captures",
+ * "graph_replays" in b200_get_double).  A graph is captured again when the page-locked registration of its
+ * destination has changed.  Off by default: on config 5 a replay takes 23.1 ms against 24.4 ms of plain launches,
+ * but the first call pays 0.5-1 s for capture and instantiation.
+ * The solve of supernodes wider than 64 columns advances 256 columns per launch; CHOLMOD_B200_SOLVE_COLS=64 in the
+ * environment (read at a context's first solve) selects the older 64-column schedule ("solve_cols" in
+ * b200_get_double). */
 int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 
 /* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):
