@@ -198,7 +198,10 @@ struct b200_factor
     DevBuf<SolveBlk> d_sblk ;
     DevBuf<SolveTile> d_stile ;
     DevBuf<SolveTile256> d_stile256 ;
+    DevBuf<SolveBlk> d_sstep ;              // solve: the 256-column supersteps { s, c0, nb, first 64 x 64 inverse }
+    DevBuf<unsigned char> d_solveW256 ;     // solve: inverses of the supersteps' whole diagonal blocks (or empty)
     int solve_cols = 64 ;                   // columns of a wide supernode per launch: 64 or 256 (CHOLMOD_B200_SOLVE_COLS)
+    int solve_pdl = 1 ;                     // superstep kernels launched programmatically dependent (CHOLMOD_B200_SOLVE_PDL)
     std::vector<unsigned char> h_Ax ;       // zomplex input (Ax, Az) interleaved before the upload
     std::vector<unsigned char> h_Fx ;
     bool have_A = false, A_unpacked = false ;
@@ -326,6 +329,10 @@ int kernel_attrs (int device)
     CK (cudaFuncSetAttribute (k_solve_inv<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<float> ()), "attr inv") ;
     CK (cudaFuncSetAttribute (k_solve_inv<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<zdouble> ()), "attr inv") ;
     CK (cudaFuncSetAttribute (k_solve_inv<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv_smem_bytes<cfloat> ()), "attr inv") ;
+    CK (cudaFuncSetAttribute (k_solve_inv256<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv256_smem_bytes<double> ()), "attr inv256") ;
+    CK (cudaFuncSetAttribute (k_solve_inv256<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv256_smem_bytes<float> ()), "attr inv256") ;
+    CK (cudaFuncSetAttribute (k_solve_inv256<zdouble>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv256_smem_bytes<zdouble> ()), "attr inv256") ;
+    CK (cudaFuncSetAttribute (k_solve_inv256<cfloat>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) solve_inv256_smem_bytes<cfloat> ()), "attr inv256") ;
     if (device < 64) g_attr_done [device] = true ;
     return B200_OK ;
 }
@@ -934,7 +941,7 @@ void b200_destroy (b200_factor *f)
         f->d_winv.release () ; f->d_colmine.release () ; f->d_pulls.release () ; f->d_barrier.release () ;
         for (int r = 0 ; r < 32 ; r++)
             if (f->peer_ipc [r] && f->peers.p [r]) { cudaIpcCloseMemHandle (f->peers.p [r]) ; f->peers.p [r] = nullptr ; }
-        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ; f->d_stile256.release () ;
+        f->d_ssmall.release () ; f->d_sblk.release () ; f->d_stile.release () ; f->d_stile256.release () ; f->d_sstep.release () ; f->d_solveW256.release () ;
         for (auto &e : f->ev) if (e) cudaEventDestroy (e) ;
         if (f->stage) { cudaFreeHost (f->stage) ; for (auto &e : f->stage_ev) if (e) cudaEventDestroy (e) ; }
         for (auto &e : f->prof_ev) cudaEventDestroy (e) ;
@@ -1032,6 +1039,16 @@ double b200_get_double (const b200_factor *f, const char *name)
     if (!strncmp (name, "ms_kind", 7) && name [7] >= '0' && name [7] <= '9' && atoi (name + 7) < K_NKINDS) return f->ms_kind [atoi (name + 7)] ;
     if (!strncmp (name, "ms_solve_part", 13) && name [13] >= '0' && name [13] < '4') return f->ms_solve_part [name [13] - '0'] ;
     if (!strcmp (name, "solve_cols")) return f->solve_cols ;
+    if (!strcmp (name, "solve_w256_bytes")) return (double) f->d_solveW256.n ;
+#ifdef B200_SOLVE_TRACE
+    if (!strncmp (name, "solve_trace", 11))
+    {
+        unsigned long long h [32] ;
+        const int k = atoi (name + 11) ;
+        if (k < 0 || k >= 32 || cudaMemcpyFromSymbol (h, g_solve_trace, sizeof (h)) != cudaSuccess) return -1 ;
+        return (double) h [k] ;
+    }
+#endif
     if (!strcmp (name, "graph_replays")) return (double) f->graph_replays ;
     if (!strcmp (name, "graph_captures")) return (double) f->graph_captures ;
     if (!strcmp (name, "use_graph")) return f->use_graph ;
@@ -1830,12 +1847,13 @@ static int solve_T (b200_factor *f, int nrhs, int which)
         constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256, SOLVE_SUPER = 256, SOLVE_FROWS = 64 ;
         const char *ecols = getenv ("CHOLMOD_B200_SOLVE_COLS") ;
         f->solve_cols = (ecols && atoi (ecols) == 64) ? 64 : 256 ;
+        if (const char *e = getenv ("CHOLMOD_B200_SOLVE_PDL")) f->solve_pdl = atoi (e) != 0 ;
         std::vector<int32_t> small ;
         std::vector<SolveBlk> blks ;
         std::vector<SolveTile> tiles ;
         std::vector<SolveTile256> tiles256 ;
-        std::vector<int32_t> blk_first ((size_t) P.nsuper, -1) ;
-        int32_t nsteps = 0 ;
+        std::vector<int32_t> blk_first ((size_t) P.nsuper, -1), step_first ((size_t) P.nsuper, -1) ;
+        std::vector<SolveBlk> steps ;
         f->solve_launches.clear () ;
         for (int lev = 0 ; lev < P.nlevels ; lev++)
         {
@@ -1855,6 +1873,12 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                     blk_first [sn] = (int32_t) blks.size () ;
                     for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_NB)
                         blks.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0), 0 }) ;
+                    // and so are its supersteps
+                    step_first [sn] = (int32_t) steps.size () ;
+                    if (f->solve_cols != 64)
+                        for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_SUPER)
+                            steps.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0),
+                                blk_first [sn] + (int32_t) (c0 / SOLVE_NB) }) ;
                 }
             }
             if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
@@ -1891,7 +1915,7 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                 for (int32_t sn : big)
                 {
                     const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
-                    tiles256.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol), 0, 0, 1, blk_first [sn], 0, 0, 0 }) ;
+                    tiles256.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol), 0, 0, 1, blk_first [sn], step_first [sn], 0, 0 }) ;
                 }
                 f->solve_launches.push_back ({ 3, (int64_t) t0, (int64_t) (tiles256.size () - t0), 0 }) ;
             }
@@ -1905,7 +1929,7 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                     if (nscol <= c0) continue ;
                     const int32_t nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0) ;
                     const int32_t next_nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - (c0 + nb)) ;      // 0 at the last one
-                    const int32_t blk0 = blk_first [sn] + (int32_t) (c0 / SOLVE_NB), step = nsteps++ ;
+                    const int32_t blk0 = blk_first [sn] + (int32_t) (c0 / SOLVE_NB), step = step_first [sn] + (int32_t) (c0 / SOLVE_SUPER) ;
                     for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
                         tiles256.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
                             blk0, step, (r < c0 + nb + next_nb) ? next_nb : 0, 0 }) ;
@@ -1925,6 +1949,18 @@ static int solve_T (b200_factor *f, int nrhs, int which)
         ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
         ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
         ok = ok && f->d_stile256.upload (tiles256, s) == cudaSuccess ;
+        ok = ok && f->d_sstep.upload (steps, s) == cudaSuccess ;
+        // the whole-block inverses are an accelerator, not a requirement: without the memory for them (or with
+        // CHOLMOD_B200_SOLVE_W256=0) the diagonal solves go through the 64 x 64 inverses
+        f->d_solveW256.release () ;
+        const char *ew = getenv ("CHOLMOD_B200_SOLVE_W256") ;
+        if (ok && !steps.empty () && !(ew && atoi (ew) == 0))
+        {
+            size_t free_b = 0, total_b = 0 ;
+            const size_t need = steps.size () * (size_t) (SOLVE_W256_LD * SOLVE_W256_LD) * sizeof (XT) ;
+            if (cudaMemGetInfo (&free_b, &total_b) == cudaSuccess && need < free_b / 2
+                && f->d_solveW256.alloc (need) != cudaSuccess) cudaGetLastError () ;
+        }
         ok = ok && f->d_solveW.alloc (blks.size () * (size_t) (SOLVE_WLD * SOLVE_WLD) * sizeof (XT)) == cudaSuccess ;
         if (!ok) { cudaGetLastError () ; return B200_OUT_OF_MEMORY ; }
         CK (cudaStreamSynchronize (s), "solve plan upload") ;
@@ -1933,11 +1969,15 @@ static int solve_T (b200_factor *f, int nrhs, int which)
     }
     const size_t nblk = f->d_sblk.n ;
     XT *Winv = reinterpret_cast<XT *> (f->d_solveW.p) ;
+    const XT *W256 = reinterpret_cast<const XT *> (f->d_solveW256.p) ;
     if (nblk > 0)
     {
         if (!f->solve_w_valid)
         {
             k_solve_inv<T><<<(unsigned) nblk, 256, solve_inv_smem_bytes<T> (), s>>> (f->d_sblk.p, f->d_pi.p, f->d_px.p, Lx, Winv) ;
+            if (f->d_solveW256.p && f->d_sstep.n > 0)
+                k_solve_inv256<T><<<(unsigned) f->d_sstep.n, 256, solve_inv256_smem_bytes<T> (), s>>> (f->d_sstep.p, f->d_pi.p, f->d_px.p,
+                    Lx, Winv, reinterpret_cast<XT *> (f->d_solveW256.p)) ;
             f->solve_w_valid = true ;
         }
         if (f->d_solve_cnt.n < nblk * (size_t) nrhs)
@@ -1978,15 +2018,26 @@ static int solve_T (b200_factor *f, int nrhs, int which)
                     k_solve_bwd<T><<<grid, 128, sm, s>>> (f->d_ssmall.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
                         f->d_Ls.p, Lx, X, P.n, nrhs, (int) L.maxcol) ;
             }
-            else if (L.kind == 3)
-                k_solve_diag_fwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                    Lx, Winv, X, Y, P.n, nrhs) ;
-            else if (L.kind == 4)
-                k_solve_fwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                    f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
-            else if (L.kind == 5)
-                k_solve_bwd256<T><<<grid, 256, 0, s>>> (f->d_stile256.p + L.first, f->d_super.p, f->d_pi.p, f->d_px.p,
-                    f->d_Ls.p, Lx, Winv, X, Y, f->d_solve_cnt.p, P.n, nrhs) ;
+            else if (L.kind >= 3 && L.kind <= 5)
+            {
+                cudaLaunchConfig_t cfg = {} ;
+                cfg.gridDim = dim3 (grid) ; cfg.blockDim = dim3 (256) ; cfg.dynamicSmemBytes = 0 ; cfg.stream = s ;
+                cudaLaunchAttribute at [1] ;
+                at [0].id = cudaLaunchAttributeProgrammaticStreamSerialization ;
+                at [0].val.programmaticStreamSerializationAllowed = 1 ;
+                cfg.attrs = at ; cfg.numAttrs = f->solve_pdl ? 1 : 0 ;
+                const SolveTile256 *tl = f->d_stile256.p + L.first ;
+                const int64_t *dsuper = f->d_super.p, *dpi = f->d_pi.p, *dpx = f->d_px.p ;
+                const int32_t *dLs = f->d_Ls.p ;
+                const XT *cW = Winv, *cX = X ;
+                int *cnt = f->d_solve_cnt.p ;
+                const int64_t nn = P.n ;
+                cudaError_t e ;
+                if (L.kind == 3) e = cudaLaunchKernelEx (&cfg, k_solve_diag_fwd256<T>, tl, dsuper, dpi, dpx, Lx, cW, W256, cX, Y, nn, nrhs) ;
+                else if (L.kind == 4) e = cudaLaunchKernelEx (&cfg, k_solve_fwd256<T>, tl, dsuper, dpi, dpx, dLs, Lx, cW, W256, X, Y, cnt, nn, nrhs) ;
+                else e = cudaLaunchKernelEx (&cfg, k_solve_bwd256<T>, tl, dsuper, dpi, dpx, dLs, Lx, cW, W256, X, Y, cnt, nn, nrhs) ;
+                CK (e, "superstep launch") ;
+            }
             else
             {
                 if (pass == 0)

@@ -1907,6 +1907,69 @@ __global__ void __launch_bounds__ (256) k_pull_add (const PullSeg *__restrict__ 
 // tiles to finish solves that block at once, so a superstep costs one launch.
 struct SolveTile256 { int32_t s, c0, nb, r0, nrows, ntiles, blk0, step, next_nb, pad ; } ;
 
+// Programmatic dependent launch: a superstep kernel launched with the programmatic-stream-serialization attribute is
+// scheduled while its predecessor drains; it may read only what no kernel of the solve writes (the schedule, the
+// factor, the inverses) before solve_pdl_wait (), which returns once the predecessor has completed and its writes
+// are visible, and then lets its own successor in.  Without the attribute both instructions do nothing.
+__device__ __forceinline__ void solve_pdl_wait ()
+{
+    asm volatile ("griddepcontrol.wait;" ::: "memory") ;
+    asm volatile ("griddepcontrol.launch_dependents;") ;
+}
+
+// Diagnostic build (-DB200_SOLVE_TRACE): SM-clock stamps at the phase boundaries of the CTA that ends up doing the
+// diagonal solve, summed over the launches ([0..15] forward, [16..31] backward; slot 15 / 31 counts the launches).
+#ifdef B200_SOLVE_TRACE
+__device__ unsigned long long g_solve_trace [32] ;
+#define SOLVE_TR(k) do { if (threadIdx.x == 0) tr [k] = clock64 () ; } while (0)
+#define SOLVE_TR_DECL long long tr [10] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }
+#define SOLVE_TR_FLUSH(base, cnt) do { if (threadIdx.x == 0) { for (int k_ = 1 ; k_ < (cnt) ; k_++) \
+    atomicAdd (&g_solve_trace [(base) + k_ - 1], (unsigned long long) (tr [k_] - tr [k_-1])) ; \
+    atomicAdd (&g_solve_trace [(base) + 15], 1ull) ; } } while (0)
+#else
+#define SOLVE_TR(k) do { } while (0)
+#define SOLVE_TR_DECL do { } while (0)
+#define SOLVE_TR_FLUSH(base, cnt) do { } while (0)
+#endif
+
+// Ask L2 for what the diagonal solve of the superstep [c0, c0+nb) will read -- its 64 x 64 inverses and the lower
+// triangle of its diagonal block -- long before the CTA that does the solve is known: one CTA of 256 threads, a few
+// lines per thread.  A hint only; every address lies inside Winv or inside the supernode's columns.
+template <typename T, typename XT>
+__device__ __forceinline__ void solve_diag256_prefetch (const T *__restrict__ Lsn, int64_t nsrow, int c0, int nb,
+    const XT *__restrict__ W0)
+{
+    const int tid = threadIdx.x ;
+    const char *wp = reinterpret_cast<const char *> (W0) ;
+    const int wbytes = ((nb + 63) >> 6) * SOLVE_WLD * SOLVE_WLD * (int) sizeof (XT) ;
+    for (int off = tid * 128 ; off < wbytes ; off += 256 * 128)
+        asm volatile ("prefetch.global.L2 [%0];" :: "l" (wp + off)) ;
+    constexpr int PER = 128 / (int) sizeof (T) ;            // entries per 128 bytes
+    const int chunks = (nb + PER - 1) / PER ;
+    for (int e = tid ; e < nb * chunks ; e += 256)
+    {
+        const int j = e / chunks, r = (e % chunks) * PER ;
+        if (r + PER > j)                                    // the chunk reaches below the diagonal
+        {
+            const T *q = Lsn + (c0 + max (r, j)) + (int64_t) (c0 + j) * nsrow ;
+            asm volatile ("prefetch.global.L2 [%0];" :: "l" (q)) ;
+        }
+    }
+}
+
+// the same for a whole-block inverse: the lower triangle of W256 below nb
+template <typename XT>
+__device__ __forceinline__ void solve_w256_prefetch (const XT *__restrict__ W, int nb)
+{
+    constexpr int PER = 128 / (int) sizeof (XT) ;
+    const int chunks = (nb + PER - 1) / PER ;
+    for (int e = threadIdx.x ; e < nb * chunks ; e += 256)
+    {
+        const int c = e / chunks, r = (e % chunks) * PER ;
+        if (r + PER > c) asm volatile ("prefetch.global.L2 [%0];" :: "l" (W + max (r, c) + (int64_t) c * 256)) ;
+    }
+}
+
 // Forward diagonal solve of a superstep by a CTA of 256 threads: xs [0..nb) (shared) holds the right-hand side and
 // is destroyed; ys [0..nb) receives y = L_blk \ xs.  Four sub-steps of 64: y_q = W_q * x_q with the pre-inverted
 // diagonal block (4 threads per row), then the later unknowns take x -= L (rows, block q) * y_q, 4 threads per row
@@ -1970,100 +2033,6 @@ __device__ __forceinline__ void solve_diag256_fwd (const T *__restrict__ Lsn, in
     }
 }
 
-// First superstep of every wide supernode of a level: y = L_blk \ x_blk, into Y.
-template <typename T>
-__global__ void __launch_bounds__ (256) k_solve_diag_fwd256 (const SolveTile256 *__restrict__ firsts,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
-    const typename solve_x<T>::type *__restrict__ X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
-{
-    typedef typename solve_x<T>::type XT ;
-    __shared__ XT xs [256], ys [256] ;
-    const SolveTile256 t = firsts [blockIdx.x] ;
-    const int64_t k1 = super [t.s], nsrow = pi [t.s+1] - pi [t.s] ;
-    const T *Lsn = Lx + px [t.s] ;
-    const int tid = threadIdx.x ;
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
-    {
-        xs [tid] = (tid < t.nb) ? X [(int64_t) rhs * n + k1 + t.c0 + tid] : from_real<XT> (0) ;
-        __syncthreads () ;
-        solve_diag256_fwd<T, XT, 3> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
-        if (tid < t.nb) Y [(int64_t) rhs * n + k1 + t.c0 + tid] = ys [tid] ;
-        __syncthreads () ;
-    }
-}
-
-// Forward superstep, one CTA per 64 rows below it: x [rows] -= L (rows, superstep) * y, four threads per row (one per
-// 64-column block of the superstep, 16 independent loads per batch).  Rows inside the supernode's own columns are
-// touched by this CTA alone; rows below it belong to ancestors and are shared with the siblings of the level:
-// atomics.  The (up to four) tiles that hold the rows of the next superstep's diagonal block count themselves off;
-// the last one solves that block, so the next launch finds its y in Y.
-template <typename T>
-__global__ void __launch_bounds__ (256, 2) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
-    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
-    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
-    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
-{
-    typedef typename solve_x<T>::type XT ;
-    __shared__ XT yb [256], xs [256], ys [256] ;
-    __shared__ int is_last ;
-    const SolveTile256 t = tiles [blockIdx.x] ;
-    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
-    const T *Lsn = Lx + px [t.s] ;
-    const int tid = threadIdx.x, r4 = tid >> 2, part = tid & 3, row = t.r0 + r4 ;
-    const XT zero = from_real<XT> (0) ;
-    const int jq = min (64, t.nb - 64 * part) ;         // columns of this thread's block of the superstep (may be <= 0)
-    for (int rhs = 0 ; rhs < nrhs ; rhs++)
-    {
-        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
-        yb [tid] = (tid < t.nb) ? y [k1 + t.c0 + tid] : zero ;
-        __syncthreads () ;
-        XT acc = zero ;
-        if (r4 < t.nrows && jq > 0)
-        {
-            const T *Lr = Lsn + row + (int64_t) (t.c0 + 64 * part) * nsrow ;
-            const XT *yq = yb + 64 * part ;
-            if (jq == 64)
-            {
-                #pragma unroll 16
-                for (int j = 0 ; j < 64 ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
-            }
-            else for (int j = 0 ; j < jq ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
-        }
-        acc += shfl_xor_ (0xffffffffu, acc, 1) ;
-        acc += shfl_xor_ (0xffffffffu, acc, 2) ;
-        if (part == 0 && r4 < t.nrows)
-        {
-            if (row < nscol) x [k1 + row] -= acc ;       // a later unknown of this supernode: ours alone
-            else atomic_sub (x + Ls [psi + row], acc) ;
-        }
-        if (t.next_nb > 0)
-        {
-            __threadfence () ;
-            __syncthreads () ;
-            if (tid == 0)
-            {
-                int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
-                const int ndiag = (t.next_nb + 63) >> 6 ;
-                const int done = atomicAdd (cnt, 1) ;
-                is_last = (done == ndiag - 1) ;
-                if (is_last) *cnt = 0 ;
-            }
-            __syncthreads () ;
-            if (is_last)
-            {
-                __threadfence () ;
-                xs [tid] = (tid < t.next_nb) ? ldcg_ (x + k1 + t.c0 + t.nb + tid) : zero ;
-                __syncthreads () ;
-                solve_diag256_fwd<T, XT, 2> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
-                    Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
-                if (tid < t.next_nb) y [k1 + t.c0 + t.nb + tid] = ys [tid] ;
-            }
-        }
-        __syncthreads () ;
-    }
-}
-
 // v [u] (u < 16) summed over the 32 lanes of the warp, 31 shuffles: on return lane l holds the sum of v [l & 15] in
 // v [0].  The first step adds the two half-warps; every later step keeps one half of the remaining values and hands
 // the other half to the partner lane, which keeps those.
@@ -2090,6 +2059,296 @@ __device__ __forceinline__ void warp_sum16 (XT (&v) [16], int lane)
     warp_sum_step<XT, 1> (v, lane) ;
 }
 
+// ---- the whole 256 x 256 diagonal block of a superstep inverted (once per factorization) -----------------------
+// The serial part of a superstep is its diagonal solve; with the four 64 x 64 inverses it is four dependent
+// sub-steps of two memory round trips each, all through one SM (measured: 27k of the 50k cycles of a forward
+// launch).  With W256 = (diagonal block)^{-1} it is one triangular matrix-vector product with every load
+// independent.  W256 of superstep `step` is a 256 x 256 column-major array at W256 + step * 65536; only its lower
+// triangle below nb is written and read.
+
+constexpr int SOLVE_W256_LD = 256 ;
+template <typename T> constexpr size_t solve_inv256_smem_bytes ()
+{
+    return (size_t) (2 * 64 * 64) * sizeof (typename solve_x<T>::type) ;
+}
+
+// C (64 x 64) += A * B with A in As [k * 64 + row], B in Bt [k * 64 + col]; thread (ty, tx) holds C (4 ty + a, 4 tx + b)
+template <typename XT>
+__device__ __forceinline__ void mm64_acc (const XT *As, const XT *Bt, int ty, int tx, XT (&acc) [4][4])
+{
+    #pragma unroll 4
+    for (int k = 0 ; k < 64 ; k++)
+    {
+        XT a [4], b [4] ;
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++) { a [u] = As [k * 64 + 4 * ty + u] ; b [u] = Bt [k * 64 + 4 * tx + u] ; }
+        #pragma unroll
+        for (int u = 0 ; u < 4 ; u++)
+            #pragma unroll
+            for (int v = 0 ; v < 4 ; v++) acc [u][v] += a [u] * b [v] ;
+    }
+}
+
+// One CTA per superstep (steps [blockIdx.x] = { s, c0, nb, first 64 x 64 inverse }): block (i,j) of the inverse, i > j,
+// is  - W_ii * sum_{k = j .. i-1} L_ik * W_kj  (blocks of 64; W_ii are the inverses k_solve_inv left in Winv).
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_inv256 (const SolveBlk *__restrict__ steps,
+    const int64_t *__restrict__ pi, const int64_t *__restrict__ px, const T *__restrict__ Lx,
+    const typename solve_x<T>::type *__restrict__ Winv, typename solve_x<T>::type *W256all)
+{
+    typedef typename solve_x<T>::type XT ;
+    extern __shared__ __align__ (16) unsigned char solve_smem [] ;
+    XT *As = reinterpret_cast<XT *> (solve_smem) ;
+    XT *Bt = As + 64 * 64 ;
+    const SolveBlk b = steps [blockIdx.x] ;
+    const int64_t nsrow = pi [b.s+1] - pi [b.s] ;
+    const T *Lsn = Lx + px [b.s] ;
+    const int c0 = b.c0, nb = b.jb, nq = (nb + 63) >> 6 ;
+    const XT *W64 = Winv + (int64_t) b.pad * (SOLVE_WLD * SOLVE_WLD) ;
+    XT *W = W256all + (int64_t) blockIdx.x * (SOLVE_W256_LD * SOLVE_W256_LD) ;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15 ;
+    const XT zero = from_real<XT> (0) ;
+    // the diagonal blocks: copies of the 64 x 64 inverses (lower triangles)
+    for (int q = 0 ; q < nq ; q++)
+        for (int e = tid ; e < 64 * 64 ; e += 256)
+        {
+            const int r = e & 63, c = e >> 6 ;
+            if (r >= c && 64 * q + r < nb) W [(64 * q + r) + (int64_t) (64 * q + c) * SOLVE_W256_LD] = W64 [(int64_t) q * (SOLVE_WLD * SOLVE_WLD) + r + c * SOLVE_WLD] ;
+        }
+    __syncthreads () ;
+    for (int j = 0 ; j + 1 < nq ; j++)
+        for (int i = j + 1 ; i < nq ; i++)
+        {
+            const int ri = min (64, nb - 64 * i) ;              // rows of block row i (block column j < i is a full one)
+            XT acc [4][4] ;
+            #pragma unroll
+            for (int u = 0 ; u < 4 ; u++)
+                #pragma unroll
+                for (int v = 0 ; v < 4 ; v++) acc [u][v] = zero ;
+            for (int k = j ; k < i ; k++)
+            {
+                // A = L (block i, block k), B = W (block k, block j): lower triangular when k == j
+                for (int e = tid ; e < 64 * 64 ; e += 256)
+                {
+                    const int r = e & 63, c = e >> 6 ;
+                    As [c * 64 + r] = (r < ri) ? cvt<XT> (Lsn [(c0 + 64 * i + r) + (int64_t) (c0 + 64 * k + c) * nsrow]) : zero ;
+                    Bt [r * 64 + c] = (k > j || r >= c) ? W [(64 * k + r) + (int64_t) (64 * j + c) * SOLVE_W256_LD] : zero ;
+                }
+                __syncthreads () ;
+                mm64_acc<XT> (As, Bt, ty, tx, acc) ;
+                __syncthreads () ;
+            }
+            // W (i,j) = - W_ii * S
+            #pragma unroll
+            for (int u = 0 ; u < 4 ; u++)
+                #pragma unroll
+                for (int v = 0 ; v < 4 ; v++) { Bt [(4 * ty + u) * 64 + 4 * tx + v] = acc [u][v] ; acc [u][v] = zero ; }
+            for (int e = tid ; e < 64 * 64 ; e += 256)
+            {
+                const int r = e & 63, c = e >> 6 ;
+                As [c * 64 + r] = W64 [(int64_t) i * (SOLVE_WLD * SOLVE_WLD) + r + c * SOLVE_WLD] ;     // zero above the diagonal
+            }
+            __syncthreads () ;
+            mm64_acc<XT> (As, Bt, ty, tx, acc) ;
+            #pragma unroll
+            for (int u = 0 ; u < 4 ; u++)
+                #pragma unroll
+                for (int v = 0 ; v < 4 ; v++)
+                    if (4 * ty + u < ri) { XT neg = zero ; neg -= acc [u][v] ; W [(64 * i + 4 * ty + u) + (int64_t) (64 * j + 4 * tx + v) * SOLVE_W256_LD] = neg ; }
+            __syncthreads () ;
+        }
+}
+
+// ys [0..nb) = W256 * xs [0..nb) (lower triangular), by a CTA of 256 threads.  Thread (h, p) takes the rows p and
+// 255 - p (together 257 entries, so the threads are balanced) and the columns of parity h; every load is
+// independent, consecutive threads read consecutive rows.  red: 512 entries of scratch.
+template <typename XT>
+__device__ __forceinline__ void solve_diag256w_fwd (const XT *__restrict__ W, int nb, const XT *xs, XT *ys, XT *red)
+{
+    const int tid = threadIdx.x, h = tid >> 7, p = tid & 127, ra = p, rb = 255 - p ;
+    const XT zero = from_real<XT> (0) ;
+    XT acca = zero, accb = zero ;
+    const XT *Wa = W + ra, *Wb = W + rb ;
+    const int la = (ra < nb) ? ra : -1, lb = (rb < nb) ? rb : -1 ;     // last column of each row (none if the row is not there)
+    #pragma unroll 2
+    for (int c0 = h ; c0 <= lb || c0 <= la ; c0 += 16)
+    {
+        XT va [8], vb [8] ;
+        #pragma unroll
+        for (int u = 0 ; u < 8 ; u++)
+        {
+            const int c = c0 + 2 * u ;
+            va [u] = (c <= la) ? Wa [(int64_t) c * SOLVE_W256_LD] : zero ;
+            vb [u] = (c <= lb) ? Wb [(int64_t) c * SOLVE_W256_LD] : zero ;
+        }
+        #pragma unroll
+        for (int u = 0 ; u < 8 ; u++)
+        {
+            const int c = c0 + 2 * u ;
+            const XT xv = (c < 256) ? xs [c] : zero ;
+            acca += va [u] * xv ; accb += vb [u] * xv ;
+        }
+    }
+    red [h * 256 + ra] = acca ; red [h * 256 + rb] = accb ;
+    __syncthreads () ;
+    ys [tid] = red [tid] + red [256 + tid] ;
+    __syncthreads () ;
+}
+
+// xo [c] = sum_{r >= c} conj (W256 (r,c)) * yb [r] for c < nb, by a CTA of 256 threads: warp w takes the columns
+// 16 w + u and 255 - (16 w + u), u < 16 (balanced), its lanes run down the rows (coalesced), warp_sum16 adds up.
+// Lane l < 16 of warp w returns column 16 w + l in x0 and column 255 - (16 w + l) in x1.
+template <typename XT>
+__device__ __forceinline__ void solve_diag256w_bwd (const XT *__restrict__ W, int nb, const XT *yb, XT &x0, XT &x1)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5 ;
+    const XT zero = from_real<XT> (0) ;
+    #pragma unroll
+    for (int pass = 0 ; pass < 2 ; pass++)
+    {
+        XT v [16] ;
+        #pragma unroll
+        for (int u = 0 ; u < 16 ; u++) v [u] = zero ;
+        const int cfirst = pass ? 255 - (16 * warp + 15) : 16 * warp ;      // the smallest column of the pass
+        if (cfirst < nb)
+            #pragma unroll 2
+            for (int k = cfirst >> 5 ; 32 * k < nb ; k++)
+            {
+                const int r = lane + 32 * k ;
+                const XT yv = (r < nb) ? yb [r] : zero ;
+                XT w [16] ;
+                #pragma unroll
+                for (int u = 0 ; u < 16 ; u++)
+                {
+                    const int c = pass ? 255 - (16 * warp + u) : 16 * warp + u ;
+                    w [u] = (r >= c && r < nb) ? W [r + (int64_t) c * SOLVE_W256_LD] : zero ;
+                }
+                #pragma unroll
+                for (int u = 0 ; u < 16 ; u++) v [u] += mulc (yv, w [u]) ;
+            }
+        warp_sum16<XT> (v, lane) ;
+        if (pass) x1 = v [0] ; else x0 = v [0] ;
+    }
+}
+
+// First superstep of every wide supernode of a level: y = L_blk \ x_blk, into Y.
+template <typename T>
+__global__ void __launch_bounds__ (256) k_solve_diag_fwd256 (const SolveTile256 *__restrict__ firsts,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    const typename solve_x<T>::type *__restrict__ W256,
+    const typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int64_t n, int nrhs)
+{
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT xs [256], ys [256], red [512] ;
+    const SolveTile256 t = firsts [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nsrow = pi [t.s+1] - pi [t.s] ;
+    const T *Lsn = Lx + px [t.s] ;
+    const int tid = threadIdx.x ;
+    if (W256) solve_w256_prefetch<XT> (W256 + (int64_t) t.step * (SOLVE_W256_LD * SOLVE_W256_LD), t.nb) ;
+    solve_pdl_wait () ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        xs [tid] = (tid < t.nb) ? X [(int64_t) rhs * n + k1 + t.c0 + tid] : from_real<XT> (0) ;
+        __syncthreads () ;
+        if (W256) solve_diag256w_fwd<XT> (W256 + (int64_t) t.step * (SOLVE_W256_LD * SOLVE_W256_LD), t.nb, xs, ys, red) ;
+        else solve_diag256_fwd<T, XT, 3> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
+        if (tid < t.nb) Y [(int64_t) rhs * n + k1 + t.c0 + tid] = ys [tid] ;
+        __syncthreads () ;
+    }
+}
+
+// Forward superstep, one CTA per 64 rows below it: x [rows] -= L (rows, superstep) * y, four threads per row (one per
+// 64-column block of the superstep, 16 independent loads per batch).  Rows inside the supernode's own columns are
+// touched by this CTA alone; rows below it belong to ancestors and are shared with the siblings of the level:
+// atomics.  The (up to four) tiles that hold the rows of the next superstep's diagonal block count themselves off;
+// the last one solves that block, so the next launch finds its y in Y.
+template <typename T>
+__global__ void __launch_bounds__ (256, 2) k_solve_fwd256 (const SolveTile256 *__restrict__ tiles,
+    const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
+    const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    const typename solve_x<T>::type *__restrict__ W256,
+    typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
+{
+    typedef typename solve_x<T>::type XT ;
+    __shared__ XT yb [256], xs [256], ys [256], red [512] ;
+    __shared__ int is_last ;
+    const SolveTile256 t = tiles [blockIdx.x] ;
+    const int64_t k1 = super [t.s], nscol = super [t.s+1] - k1, psi = pi [t.s], nsrow = pi [t.s+1] - psi ;
+    const T *Lsn = Lx + px [t.s] ;
+    const int tid = threadIdx.x, r4 = tid >> 2, part = tid & 3, row = t.r0 + r4 ;
+    const XT zero = from_real<XT> (0) ;
+    const int jq = min (64, t.nb - 64 * part) ;         // columns of this thread's block of the superstep (may be <= 0)
+    SOLVE_TR_DECL ;
+    SOLVE_TR (0) ;
+    if (t.next_nb > 0 && t.r0 == t.c0 + t.nb)
+    {
+        if (W256) solve_w256_prefetch<XT> (W256 + (int64_t) (t.step + 1) * (SOLVE_W256_LD * SOLVE_W256_LD), t.next_nb) ;
+        else solve_diag256_prefetch<T, XT> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
+            Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD)) ;
+    }
+    solve_pdl_wait () ;
+    for (int rhs = 0 ; rhs < nrhs ; rhs++)
+    {
+        XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
+        yb [tid] = (tid < t.nb) ? y [k1 + t.c0 + tid] : zero ;
+        __syncthreads () ;
+        SOLVE_TR (1) ;
+        XT acc = zero ;
+        if (r4 < t.nrows && jq > 0)
+        {
+            const T *Lr = Lsn + row + (int64_t) (t.c0 + 64 * part) * nsrow ;
+            const XT *yq = yb + 64 * part ;
+            if (jq == 64)
+            {
+                #pragma unroll 16
+                for (int j = 0 ; j < 64 ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
+            }
+            else for (int j = 0 ; j < jq ; j++) acc += cvt<XT> (Lr [(int64_t) j * nsrow]) * yq [j] ;
+        }
+        acc += shfl_xor_ (0xffffffffu, acc, 1) ;
+        acc += shfl_xor_ (0xffffffffu, acc, 2) ;
+        SOLVE_TR (2) ;
+        if (part == 0 && r4 < t.nrows)
+        {
+            if (row < nscol) x [k1 + row] -= acc ;       // a later unknown of this supernode: ours alone
+            else atomic_sub (x + Ls [psi + row], acc) ;
+        }
+        SOLVE_TR (3) ;
+        if (t.next_nb > 0)
+        {
+            __threadfence () ;
+            __syncthreads () ;
+            SOLVE_TR (4) ;
+            if (tid == 0)
+            {
+                int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
+                const int ndiag = (t.next_nb + 63) >> 6 ;
+                const int done = atomicAdd (cnt, 1) ;
+                is_last = (done == ndiag - 1) ;
+                if (is_last) *cnt = 0 ;
+            }
+            __syncthreads () ;
+            SOLVE_TR (5) ;
+            if (is_last)
+            {
+                __threadfence () ;
+                xs [tid] = (tid < t.next_nb) ? ldcg_ (x + k1 + t.c0 + t.nb + tid) : zero ;
+                __syncthreads () ;
+                SOLVE_TR (6) ;
+                if (W256) solve_diag256w_fwd<XT> (W256 + (int64_t) (t.step + 1) * (SOLVE_W256_LD * SOLVE_W256_LD), t.next_nb, xs, ys, red) ;
+                else solve_diag256_fwd<T, XT, 2> (Lsn, nsrow, t.c0 + t.nb, t.next_nb,
+                    Winv + (int64_t) (t.blk0 + ((t.nb + 63) >> 6)) * (SOLVE_WLD * SOLVE_WLD), xs, ys) ;
+                SOLVE_TR (7) ;
+                if (tid < t.next_nb) y [k1 + t.c0 + t.nb + tid] = ys [tid] ;
+                SOLVE_TR (8) ;
+                SOLVE_TR_FLUSH (0, 9) ;
+            }
+        }
+        __syncthreads () ;
+    }
+}
+
 // Backward superstep, one CTA per 64 rows below it: Y_blk -= L (rows, superstep)^H * x [rows] (atomics).  A warp
 // takes 32 columns, 16 at a time; a lane holds two rows of each (32 independent, coalesced loads per pass) and the
 // warp adds up with warp_sum16, so that 16 lanes subtract 16 consecutive entries of Y.  The CTA that finishes
@@ -2099,6 +2358,7 @@ template <typename T>
 __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8) ? 2 : 1) k_solve_bwd256 (const SolveTile256 *__restrict__ tiles,
     const int64_t *__restrict__ super, const int64_t *__restrict__ pi, const int64_t *__restrict__ px,
     const int32_t *__restrict__ Ls, const T *__restrict__ Lx, const typename solve_x<T>::type *__restrict__ Winv,
+    const typename solve_x<T>::type *__restrict__ W256,
     typename solve_x<T>::type *X, typename solve_x<T>::type *Y, int *counters, int64_t n, int nrhs)
 {
     typedef typename solve_x<T>::type XT ;
@@ -2109,6 +2369,14 @@ __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8
     const T *Lsn = Lx + px [t.s] ;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r4 = tid >> 2, part = tid & 3 ;
     const XT zero = from_real<XT> (0) ;
+    SOLVE_TR_DECL ;
+    SOLVE_TR (0) ;
+    if (t.r0 == t.c0 + t.nb)
+    {
+        if (W256) solve_w256_prefetch<XT> (W256 + (int64_t) t.step * (SOLVE_W256_LD * SOLVE_W256_LD), t.nb) ;
+        else solve_diag256_prefetch<T, XT> (Lsn, nsrow, t.c0, t.nb, Winv + (int64_t) t.blk0 * (SOLVE_WLD * SOLVE_WLD)) ;
+    }
+    solve_pdl_wait () ;
     for (int rhs = 0 ; rhs < nrhs ; rhs++)
     {
         XT *x = X + (int64_t) rhs * n, *y = Y + (int64_t) rhs * n ;
@@ -2118,6 +2386,7 @@ __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8
             xr [tid] = (tid < t.nrows) ? x [(row < nscol) ? k1 + row : (int64_t) Ls [psi + row]] : zero ;
         }
         __syncthreads () ;
+        SOLVE_TR (1) ;
         if (t.nrows > 0)
         {
             const T *Lbase = Lsn + t.r0 + (int64_t) t.c0 * nsrow ;
@@ -2155,8 +2424,10 @@ __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8
                 if (lane < 16 && cb + lane < t.nb) atomic_sub (y + k1 + t.c0 + cb + lane, v [0]) ;
             }
         }
+        SOLVE_TR (2) ;
         __threadfence () ;
         __syncthreads () ;
+        SOLVE_TR (3) ;
         if (tid == 0)
         {
             int *cnt = counters + (int64_t) t.step * nrhs + rhs ;
@@ -2165,12 +2436,25 @@ __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8
             if (is_last) *cnt = 0 ;
         }
         __syncthreads () ;
+        SOLVE_TR (4) ;
         if (is_last)
         {
             __threadfence () ;
             yb [tid] = (tid < t.nb) ? ldcg_ (y + k1 + t.c0 + tid) : zero ;
             __syncthreads () ;
-            const int nq = (t.nb + 63) >> 6 ;
+            SOLVE_TR (5) ;
+            if (W256)
+            {
+                XT x0, x1 ;
+                solve_diag256w_bwd<XT> (W256 + (int64_t) t.step * (SOLVE_W256_LD * SOLVE_W256_LD), t.nb, yb, x0, x1) ;
+                if (lane < 16)
+                {
+                    const int ca = 16 * warp + lane, cb = 255 - ca ;
+                    if (ca < t.nb) x [k1 + t.c0 + ca] = x0 ;
+                    if (cb < t.nb) x [k1 + t.c0 + cb] = x1 ;
+                }
+            }
+            const int nq = W256 ? 0 : (t.nb + 63) >> 6 ;
             for (int q = nq - 1 ; q >= 0 ; q--)
             {
                 const int q0 = q * 64, jb = min (64, t.nb - q0) ;
@@ -2223,6 +2507,8 @@ __global__ void __launch_bounds__ (256, (sizeof (typename solve_x<T>::type) <= 8
                 }
                 __syncthreads () ;
             }
+            SOLVE_TR (6) ;
+            SOLVE_TR_FLUSH (16, 7) ;
         }
         __syncthreads () ;
     }
