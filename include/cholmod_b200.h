@@ -295,9 +295,12 @@ int b200_panel_factor_noalloc_d (double *d_panel, int64_t lda, int64_t nrows, in
  * "graph_replays" in b200_get_double).  A graph is captured again when the page-locked registration of its
  * destination has changed.  Off by default: on config 5 a replay takes 23.1 ms against 24.4 ms of plain launches,
  * but the first call pays 0.5-1 s for capture and instantiation.
- * The solve of supernodes wider than 64 columns advances 256 columns per launch; CHOLMOD_B200_SOLVE_COLS=64 in the
- * environment (read at a context's first solve) selects the older 64-column schedule ("solve_cols" in
- * b200_get_double). */
+ * The solve of supernodes wider than 64 columns advances 256 columns per launch, with the whole 256 x 256 diagonal
+ * block of every such superstep inverted once per factorization (512 KB each; "solve_w256_bytes" in
+ * b200_get_double) and the superstep kernels launched programmatically dependent.  Environment, read at a context's
+ * first solve: CHOLMOD_B200_SOLVE_COLS=64 selects the older 64-column schedule ("solve_cols"),
+ * CHOLMOD_B200_SOLVE_W256=0 the diagonal solve through the 64 x 64 inverses (also used when the memory for the
+ * 256 x 256 ones is not there), CHOLMOD_B200_SOLVE_PDL=0 plain launches. */
 int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 
 /* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):

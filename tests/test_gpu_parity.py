@@ -297,16 +297,24 @@ def test_factor_values_at_benchmark_sizes(kind, size, single, tol_l, tol_r):
     assert res <= tol_r, res
 
 
-@pytest.mark.parametrize("cols", [256, 64])
+SOLVE_MODES = {"default": {}, "cols64": {"CHOLMOD_B200_SOLVE_COLS": "64"}, "no_w256": {"CHOLMOD_B200_SOLVE_W256": "0"},
+               "no_pdl": {"CHOLMOD_B200_SOLVE_PDL": "0"}}
+
+
+@pytest.mark.parametrize("mode", sorted(SOLVE_MODES))
 @pytest.mark.parametrize("kind,size,ordering", [("lap3d7", 40, refd.CHOLMOD_METIS), ("lap3d7", 33, refd.CHOLMOD_METIS),
                                                 ("lap2d9", 200, refd.CHOLMOD_METIS)])
-def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering, cols, monkeypatch):
+def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering, mode, monkeypatch):
     """b200_solve_sweep: the forward sweep alone equals the reference's L\\b on its own factor (the plain-C
     restatement's triangular solve), and forward followed by backward equals the two-sided solve; several
     right-hand sides, factors with supernodes wider than one 256-column superstep (root separators of 1600 =
     6 x 256 + 64 and 1089 = 4 x 256 + 65 columns: ragged last supersteps and a one-column last block), with both
-    schedules of the wide supernodes (256 columns per launch, the default, and 64)."""
-    monkeypatch.setenv("CHOLMOD_B200_SOLVE_COLS", str(cols))
+    schedules of the wide supernodes (256 columns per launch, the default, and 64), with and without the
+    whole-block inverses and the programmatic dependent launch."""
+    for k in ("CHOLMOD_B200_SOLVE_COLS", "CHOLMOD_B200_SOLVE_W256", "CHOLMOD_B200_SOLVE_PDL"):
+        monkeypatch.delenv(k, raising=False)
+    for k, v in SOLVE_MODES[mode].items():
+        monkeypatch.setenv(k, v)
     c = get_case(kind, size, ordering)
     F = b200.Factor(c.sym, device=0)
     st, Lx = F.super_numeric(c.Sp, c.Si, c.Sx)
@@ -317,6 +325,9 @@ def test_one_sided_sweeps_compose_to_the_solve(kind, size, ordering, cols, monke
     Y = F.solve_sweep(1, B)
     Z = F.solve_sweep(2, Y)
     assert np.max(np.abs(Z - X)) <= 1e-12 * np.max(np.abs(X))
+    assert F.getd("solve_cols") == (64 if mode == "cols64" else 256)
+    has_wide = bool(np.any(np.diff(c.sym["super"]) > 64))
+    assert (F.getd("solve_w256_bytes") > 0) == (mode in ("default", "no_pdl") and has_wide)
     # L * Y = B, checked with a sparse matrix built from the supernodal factor
     import scipy.sparse as sp
     sup, pi, px, Ls = c.sym["super"], c.sym["pi"], c.sym["px"], c.sym["s"]
