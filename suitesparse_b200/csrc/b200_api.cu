@@ -144,6 +144,7 @@ struct b200_factor
     // peer-mapped (same process) or opened from their IPC handles (other processes)
     PeerPtrs peers = {} ;
     bool peer_ipc [32] = {} ;               // peers.p [r] came from cudaIpcOpenMemHandle and has to be closed
+    bool one_process = false ;              // peers attached by address: all ranks are threads of this process
     int peers_attached = 0 ;
     DevBuf<unsigned char> d_colmine ;
     DevBuf<PullSeg> d_pulls ;
@@ -1178,6 +1179,7 @@ int b200_peer_attach (b200_factor *f, int rank, void *arena, const void *handle6
                 cudaGetLastError () ;
             }
             f->peers.p [rank] = arena ;
+            f->one_process = true ;
         }
         else if (handle64)
         {
@@ -1261,8 +1263,11 @@ static int upload_csc (b200_factor *f, int64_t ncols, const int64_t *Ap, const i
     if (dx.n < (size_t) nz * f->esize && dx.alloc ((size_t) nz * f->esize) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     if (Anz && dnz.n < (size_t) ncols && dnz.alloc ((size_t) ncols) != cudaSuccess) return B200_OUT_OF_MEMORY ;
     // several ranks with a communicator: every rank was given the same matrix, so only rank 0 sends it over PCIe
-    // and the others receive it over NVLink (one host feeding N GPUs the same 70-350 MB at once is slower than that)
-    NcclApi *nc = (f->plan.nranks > 1 && f->comm) ? nccl_api () : nullptr ;
+    // and the others receive it over NVLink (one host feeding N GPUs the same 70-350 MB at once is slower than that).
+    // Not when the ranks are threads of one process: a rank that is already inside its broadcast kernel waits for
+    // rank 0, and rank 0's allocations and pageable copies above can wait for that rank's device (peer access makes
+    // an allocation a matter of every device): every rank uploads its own copy then.
+    NcclApi *nc = (f->plan.nranks > 1 && f->comm && !f->one_process) ? nccl_api () : nullptr ;
     if (!nc || f->plan.rank == 0)
     {
         CK (cudaMemcpyAsync (dp.p, Ap, (size_t) (ncols + 1) * sizeof (int64_t), cudaMemcpyHostToDevice, s), "H2D Ap") ;
@@ -1335,7 +1340,7 @@ int b200_upload_values (b200_factor *f, const void *Ax)
     if (f->A_nz == 0) return B200_OK ;
     if (!Ax) return B200_INVALID ;
     CK (cudaEventRecord (f->ev [0], f->stream), "record") ;
-    NcclApi *nc = (f->plan.nranks > 1 && f->comm) ? nccl_api () : nullptr ;      // as in upload_csc
+    NcclApi *nc = (f->plan.nranks > 1 && f->comm && !f->one_process) ? nccl_api () : nullptr ;      // as in upload_csc
     if (!nc || f->plan.rank == 0)
     {
         st = h2d_staged (f, f->d_Ax.p, Ax, (size_t) f->A_nz * f->esize, f->stream) ;
