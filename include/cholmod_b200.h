@@ -306,7 +306,9 @@ int b200_set_int (b200_factor *f, const char *name, int64_t value) ;
 /* Copy one table of the host-side launch plan to `out` (or return its size in bytes when out == NULL):
  * "level", "parent", "relmap", "pairs", "pair_map", "items", "tiles", "potrf", "trsm", "launches", "copies",
  * "owned", "bcasts", "pulls", "dpx", "colmine", "owner", "top", "group" (layouts in csrc/plan.hpp).  Works on a
- * device < 0 context; used by the CPU tests of the planner.  "dev_pairs", "dev_pair_map", "dev_relmap": the
+ * device < 0 context; used by the CPU tests of the planner.  "solve_small", "solve_blks", "solve_steps",
+ * "solve_tiles", "solve_tiles256", "solve_launches": the schedule of the device solve (layouts in csrc/kernels.cuh
+ * and tests/solve_interp.py, which replays it on the host).  "dev_pairs", "dev_pair_map", "dev_relmap": the
  * symbolic tables a one-GPU context builds on the device (csrc/symbolic.cuh: the pair walk of
  * cholmod_super_symbolic.c:896-921 and the relative maps of t_cholmod_super_numeric_worker.c:897-903), copied
  * back for comparison with the host planner's. */

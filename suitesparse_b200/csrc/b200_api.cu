@@ -1065,6 +1065,128 @@ double b200_get_double (const b200_factor *f, const char *name)
 // which: "level" int32[nsuper], "relmap" int32[relmap_len], "items" (nitems x 48 bytes),
 // "tiles" (ntiles x 20), "potrf" (npotrf x 24), "trsm" (ntrsm x 32), "launches" (nlaunches x 24),
 // "parent" int64[nsuper].  Returns the number of bytes written, or -1.
+}   // extern "C"
+
+// The solve schedule (host only; b200_plan_export "solve_*" hands it to the CPU tests, which replay it).  Per level:
+// supernodes of at most SOLVE_SMALL columns get one CTA each (k_solve_fwd / k_solve_bwd, kind 0); wider ones advance
+// 256 columns ("superstep") per launch, batched over the level -- or 64 columns per launch with
+// CHOLMOD_B200_SOLVE_COLS=64 (kind 2).  The backward sweep reads the same list in reverse.
+struct SolveSchedule
+{
+    int cols = 256 ;
+    std::vector<int32_t> small ;
+    std::vector<SolveBlk> blks, steps ;         // 64 x 64 diagonal blocks; supersteps { s, c0, nb, first block }
+    std::vector<SolveTile> tiles ;
+    std::vector<SolveTile256> tiles256 ;
+    std::vector<b200_factor::SolveLaunch> launches ;
+} ;
+
+static void build_solve_schedule (const Plan &P, const std::vector<int64_t> &h_super, const std::vector<int64_t> &h_pi,
+    SolveSchedule &S)
+{
+    constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256, SOLVE_SUPER = 256, SOLVE_FROWS = 64 ;
+    const char *ecols = getenv ("CHOLMOD_B200_SOLVE_COLS") ;
+    S.cols = (ecols && atoi (ecols) == 64) ? 64 : 256 ;
+    std::vector<int32_t> &small = S.small ;
+    std::vector<SolveBlk> &blks = S.blks, &steps = S.steps ;
+    std::vector<SolveTile> &tiles = S.tiles ;
+    std::vector<SolveTile256> &tiles256 = S.tiles256 ;
+    std::vector<int32_t> blk_first ((size_t) P.nsuper, -1), step_first ((size_t) P.nsuper, -1) ;
+    small.clear () ; blks.clear () ; steps.clear () ; tiles.clear () ; tiles256.clear () ; S.launches.clear () ;
+    for (int lev = 0 ; lev < P.nlevels ; lev++)
+    {
+        const int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
+        const size_t s0 = small.size () ;
+        std::vector<int32_t> big ;
+        int64_t maxcol = 0, maxbig = 0 ;
+        for (int64_t q = 0 ; q < cnt ; q++)
+        {
+            const int32_t sn = P.level_list [first + q] ;
+            const int64_t nscol = h_super [sn+1] - h_super [sn] ;
+            if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; }
+            else
+            {
+                // the 64 x 64 diagonal blocks of one supernode are consecutive in blks (and in Winv)
+                big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ;
+                blk_first [sn] = (int32_t) blks.size () ;
+                for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_NB)
+                    blks.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0), 0 }) ;
+                // and so are its supersteps
+                step_first [sn] = (int32_t) steps.size () ;
+                if (S.cols != 64)
+                    for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_SUPER)
+                        steps.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0),
+                            blk_first [sn] + (int32_t) (c0 / SOLVE_NB) }) ;
+            }
+        }
+        if (small.size () > s0) S.launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
+        if (S.cols == 64)
+        {
+            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
+            {
+                const size_t t0 = tiles.size () ;
+                for (int32_t sn : big)
+                {
+                    const int64_t nscol = h_super [sn+1] - h_super [sn], nsrow = h_pi [sn+1] - h_pi [sn] ;
+                    if (nscol <= c0) continue ;
+                    const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
+                    const int32_t blk = blk_first [sn] + (int32_t) (c0 / SOLVE_NB) ;
+                    const size_t tb = tiles.size () ;
+                    for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
+                        tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
+                    // a block with nothing below it still needs its diagonal solve
+                    if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
+                    tiles [tb].writer = 1 ;
+                    for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
+                }
+                S.launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
+            }
+            continue ;
+        }
+        // 256 columns per launch.  Forward: the first superstep of every wide supernode of the level is solved by
+        // a launch of its own (kind 3); after that the tiles of superstep k (kind 4, 64 rows each) also solve the
+        // diagonal block of superstep k+1.  Backward: tiles of 64 rows too (kind 5), the last one to finish solves
+        // the superstep's own diagonal block.
+        if (!big.empty ())
+        {
+            const size_t t0 = tiles256.size () ;
+            for (int32_t sn : big)
+            {
+                const int64_t nscol = h_super [sn+1] - h_super [sn] ;
+                tiles256.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol), 0, 0, 1, blk_first [sn], step_first [sn], 0, 0 }) ;
+            }
+            S.launches.push_back ({ 3, (int64_t) t0, (int64_t) (tiles256.size () - t0), 0 }) ;
+        }
+        for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_SUPER)
+        {
+            const size_t tf = tiles256.size () ;
+            std::vector<SolveTile256> back ;
+            for (int32_t sn : big)
+            {
+                const int64_t nscol = h_super [sn+1] - h_super [sn], nsrow = h_pi [sn+1] - h_pi [sn] ;
+                if (nscol <= c0) continue ;
+                const int32_t nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0) ;
+                const int32_t next_nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - (c0 + nb)) ;      // 0 at the last one
+                const int32_t blk0 = blk_first [sn] + (int32_t) (c0 / SOLVE_NB), step = step_first [sn] + (int32_t) (c0 / SOLVE_SUPER) ;
+                for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
+                    tiles256.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
+                        blk0, step, (r < c0 + nb + next_nb) ? next_nb : 0, 0 }) ;
+                const size_t tb = back.size () ;
+                for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
+                    back.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
+                        blk0, step, 0, 0 }) ;
+                if (back.size () == tb) back.push_back ({ sn, (int32_t) c0, nb, (int32_t) (c0 + nb), 0, 0, blk0, step, 0, 0 }) ;
+                for (size_t k = tb ; k < back.size () ; k++) back [k].ntiles = (int32_t) (back.size () - tb) ;
+            }
+            S.launches.push_back ({ 4, (int64_t) tf, (int64_t) (tiles256.size () - tf), 0 }) ;
+            S.launches.push_back ({ 5, (int64_t) tiles256.size (), (int64_t) back.size (), 0 }) ;
+            tiles256.insert (tiles256.end (), back.begin (), back.end ()) ;
+        }
+    }
+}
+
+extern "C" {
+
 int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, int64_t out_bytes)
 {
     if (!f || !which) return -1 ;
@@ -1100,6 +1222,26 @@ int64_t b200_plan_export (const b200_factor *f, const char *which, void *out, in
         if (cudaSetDevice (f->device) != cudaSuccess) return -1 ;
         if (bytes && cudaMemcpy (out, dsrc, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError () ; return -1 ; }
         return (int64_t) bytes ;
+    }
+    else if (!strncmp (which, "solve_", 6))
+    {
+        // the solve schedule, built on request (host only): "solve_small" int32, "solve_blks" / "solve_steps" SolveBlk,
+        // "solve_tiles" SolveTile, "solve_tiles256" SolveTile256, "solve_launches" { kind, first, count, maxcol } int64
+        static thread_local SolveSchedule S ;
+        static thread_local std::vector<int64_t> flat ;
+        build_solve_schedule (P, f->h_super, f->h_pi, S) ;
+        if (!strcmp (which, "solve_small")) { src = S.small.data () ; bytes = S.small.size () * sizeof (int32_t) ; }
+        else if (!strcmp (which, "solve_blks")) { src = S.blks.data () ; bytes = S.blks.size () * sizeof (SolveBlk) ; }
+        else if (!strcmp (which, "solve_steps")) { src = S.steps.data () ; bytes = S.steps.size () * sizeof (SolveBlk) ; }
+        else if (!strcmp (which, "solve_tiles")) { src = S.tiles.data () ; bytes = S.tiles.size () * sizeof (SolveTile) ; }
+        else if (!strcmp (which, "solve_tiles256")) { src = S.tiles256.data () ; bytes = S.tiles256.size () * sizeof (SolveTile256) ; }
+        else if (!strcmp (which, "solve_launches"))
+        {
+            flat.clear () ;
+            for (const auto &L : S.launches) { flat.push_back (L.kind) ; flat.push_back (L.first) ; flat.push_back (L.count) ; flat.push_back (L.maxcol) ; }
+            src = flat.data () ; bytes = flat.size () * sizeof (int64_t) ;
+        }
+        else return -1 ;
     }
     else if (!strcmp (which, "pairs")) { src = P.pairs.data () ; bytes = P.pairs.size () * sizeof (Pair) ; }
     else if (!strcmp (which, "pair_map")) { src = P.pair_map.data () ; bytes = P.pair_map.size () * sizeof (int64_t) ; }
@@ -1845,111 +1987,16 @@ static int solve_T (b200_factor *f, int nrhs, int which)
     XT *Y = reinterpret_cast<XT *> (f->d_Y.p) ;
     if (!f->solve_ready)
     {
-        // The solve schedule, built at the first solve.  Per level: supernodes of at most SOLVE_SMALL columns
-        // get one CTA each (k_solve_fwd / k_solve_bwd); wider ones are swept 64 columns at a time, batched
-        // over the level, one launch per step: the rows below the diagonal block spread over 256-row tiles
-        // (k_solve_fwd_blk).  The backward sweep is the same list read in reverse (k_solve_bwd_blk).
-        constexpr int64_t SOLVE_BIG = SOLVE_SMALL, SOLVE_NB = 64, SOLVE_ROWS = 256, SOLVE_SUPER = 256, SOLVE_FROWS = 64 ;
-        const char *ecols = getenv ("CHOLMOD_B200_SOLVE_COLS") ;
-        f->solve_cols = (ecols && atoi (ecols) == 64) ? 64 : 256 ;
+        // the schedule is built (and uploaded) at the first solve
         if (const char *e = getenv ("CHOLMOD_B200_SOLVE_PDL")) f->solve_pdl = atoi (e) != 0 ;
-        std::vector<int32_t> small ;
-        std::vector<SolveBlk> blks ;
-        std::vector<SolveTile> tiles ;
-        std::vector<SolveTile256> tiles256 ;
-        std::vector<int32_t> blk_first ((size_t) P.nsuper, -1), step_first ((size_t) P.nsuper, -1) ;
-        std::vector<SolveBlk> steps ;
-        f->solve_launches.clear () ;
-        for (int lev = 0 ; lev < P.nlevels ; lev++)
-        {
-            const int64_t first = P.level_ptr [lev], cnt = P.level_ptr [lev+1] - first ;
-            const size_t s0 = small.size () ;
-            std::vector<int32_t> big ;
-            int64_t maxcol = 0, maxbig = 0 ;
-            for (int64_t q = 0 ; q < cnt ; q++)
-            {
-                const int32_t sn = P.level_list [first + q] ;
-                const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
-                if (nscol <= SOLVE_BIG) { small.push_back (sn) ; maxcol = std::max (maxcol, nscol) ; }
-                else
-                {
-                    // the 64 x 64 diagonal blocks of one supernode are consecutive in blks (and in Winv)
-                    big.push_back (sn) ; maxbig = std::max (maxbig, nscol) ;
-                    blk_first [sn] = (int32_t) blks.size () ;
-                    for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_NB)
-                        blks.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0), 0 }) ;
-                    // and so are its supersteps
-                    step_first [sn] = (int32_t) steps.size () ;
-                    if (f->solve_cols != 64)
-                        for (int64_t c0 = 0 ; c0 < nscol ; c0 += SOLVE_SUPER)
-                            steps.push_back ({ sn, (int32_t) c0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0),
-                                blk_first [sn] + (int32_t) (c0 / SOLVE_NB) }) ;
-                }
-            }
-            if (small.size () > s0) f->solve_launches.push_back ({ 0, (int64_t) s0, (int64_t) (small.size () - s0), maxcol }) ;
-            if (f->solve_cols == 64)
-            {
-                for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_NB)
-                {
-                    const size_t t0 = tiles.size () ;
-                    for (int32_t sn : big)
-                    {
-                        const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
-                        if (nscol <= c0) continue ;
-                        const int32_t jb = (int32_t) std::min<int64_t> (SOLVE_NB, nscol - c0) ;
-                        const int32_t blk = blk_first [sn] + (int32_t) (c0 / SOLVE_NB) ;
-                        const size_t tb = tiles.size () ;
-                        for (int64_t r = c0 + jb ; r < nsrow ; r += SOLVE_ROWS)
-                            tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_ROWS, nsrow - r), 0, 0, blk }) ;
-                        // a block with nothing below it still needs its diagonal solve
-                        if (tiles.size () == tb) tiles.push_back ({ sn, (int32_t) c0, jb, (int32_t) (c0 + jb), 0, 0, 0, blk }) ;
-                        tiles [tb].writer = 1 ;
-                        for (size_t k = tb ; k < tiles.size () ; k++) tiles [k].ntiles = (int32_t) (tiles.size () - tb) ;
-                    }
-                    f->solve_launches.push_back ({ 2, (int64_t) t0, (int64_t) (tiles.size () - t0), 0 }) ;
-                }
-                continue ;
-            }
-            // 256 columns per launch.  Forward: the first superstep of every wide supernode of the level is solved by
-            // a launch of its own (kind 3); after that the tiles of superstep k (kind 4, 64 rows each) also solve the
-            // diagonal block of superstep k+1.  Backward: tiles of 64 rows too (kind 5), the last one to finish solves
-            // the superstep's own diagonal block.
-            if (!big.empty ())
-            {
-                const size_t t0 = tiles256.size () ;
-                for (int32_t sn : big)
-                {
-                    const int64_t nscol = f->h_super [sn+1] - f->h_super [sn] ;
-                    tiles256.push_back ({ sn, 0, (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol), 0, 0, 1, blk_first [sn], step_first [sn], 0, 0 }) ;
-                }
-                f->solve_launches.push_back ({ 3, (int64_t) t0, (int64_t) (tiles256.size () - t0), 0 }) ;
-            }
-            for (int64_t c0 = 0 ; c0 < maxbig ; c0 += SOLVE_SUPER)
-            {
-                const size_t tf = tiles256.size () ;
-                std::vector<SolveTile256> back ;
-                for (int32_t sn : big)
-                {
-                    const int64_t nscol = f->h_super [sn+1] - f->h_super [sn], nsrow = f->h_pi [sn+1] - f->h_pi [sn] ;
-                    if (nscol <= c0) continue ;
-                    const int32_t nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - c0) ;
-                    const int32_t next_nb = (int32_t) std::min<int64_t> (SOLVE_SUPER, nscol - (c0 + nb)) ;      // 0 at the last one
-                    const int32_t blk0 = blk_first [sn] + (int32_t) (c0 / SOLVE_NB), step = step_first [sn] + (int32_t) (c0 / SOLVE_SUPER) ;
-                    for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
-                        tiles256.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
-                            blk0, step, (r < c0 + nb + next_nb) ? next_nb : 0, 0 }) ;
-                    const size_t tb = back.size () ;
-                    for (int64_t r = c0 + nb ; r < nsrow ; r += SOLVE_FROWS)
-                        back.push_back ({ sn, (int32_t) c0, nb, (int32_t) r, (int32_t) std::min<int64_t> (SOLVE_FROWS, nsrow - r), 0,
-                            blk0, step, 0, 0 }) ;
-                    if (back.size () == tb) back.push_back ({ sn, (int32_t) c0, nb, (int32_t) (c0 + nb), 0, 0, blk0, step, 0, 0 }) ;
-                    for (size_t k = tb ; k < back.size () ; k++) back [k].ntiles = (int32_t) (back.size () - tb) ;
-                }
-                f->solve_launches.push_back ({ 4, (int64_t) tf, (int64_t) (tiles256.size () - tf), 0 }) ;
-                f->solve_launches.push_back ({ 5, (int64_t) tiles256.size (), (int64_t) back.size (), 0 }) ;
-                tiles256.insert (tiles256.end (), back.begin (), back.end ()) ;
-            }
-        }
+        SolveSchedule S ;
+        build_solve_schedule (P, f->h_super, f->h_pi, S) ;
+        f->solve_cols = S.cols ;
+        f->solve_launches = S.launches ;
+        const std::vector<int32_t> &small = S.small ;
+        const std::vector<SolveBlk> &blks = S.blks, &steps = S.steps ;
+        const std::vector<SolveTile> &tiles = S.tiles ;
+        const std::vector<SolveTile256> &tiles256 = S.tiles256 ;
         bool ok = f->d_ssmall.upload (small, s) == cudaSuccess ;
         ok = ok && f->d_sblk.upload (blks, s) == cudaSuccess ;
         ok = ok && f->d_stile.upload (tiles, s) == cudaSuccess ;
