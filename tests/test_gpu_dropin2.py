@@ -223,7 +223,7 @@ def test_several_gpus_behind_cholmod_factorize(ngpus):
     share of L->x into the caller's one host array)."""
     if b200.device_count() < ngpus:
         pytest.skip("needs %d GPUs" % ngpus)
-    res = run_child(NGPUS, {"CHOLMOD_B200_NGPUS": str(ngpus)})
+    res = run_child(NGPUS, {"CHOLMOD_B200_NGPUS": str(ngpus)}, timeout=240)     # normally 15-30 s
     for kind in ("lap3d7", "lap2d9"):
         for ok in res[kind]["ok"]:
             assert ok["status"] == 0 and ok["err"] <= 1e-10 and ok["resid"] <= 1e-12
